@@ -1,0 +1,123 @@
+// fiode_b200/csrc/common.cuh -- shared device helpers for the FI-ODE hot path (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include "../../include/fiode_b200.h"
+
+namespace fiode {
+
+constexpr int NH = 10;    // ODE state width (classes)            dynamics/classification.py:32
+constexpr int NM = 128;   // MLP width                             dynamics/classification.py:35
+constexpr int SROW = 12;  // padded row stride (floats) of 10-wide smem rows (16-B aligned)
+
+// thread-local error string for the C-ABI (fiode_last_error)
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);
+#define FIODE_CUDA(x) do { cudaError_t e__ = (x); if (e__ != cudaSuccess) return ::fiode::cuda_fail(e__, #x); } while (0)
+
+int sm_count();
+void count_launch(int n);
+
+// ---- Dormand-Prince(5,4) tableau (torchdiffeq 0.2.2 dopri5.py) -------------
+static __device__ __constant__ const float kBeta[6][6] = {
+    {(float)(1.0 / 5), 0, 0, 0, 0, 0},
+    {(float)(3.0 / 40), (float)(9.0 / 40), 0, 0, 0, 0},
+    {(float)(44.0 / 45), (float)(-56.0 / 15), (float)(32.0 / 9), 0, 0, 0},
+    {(float)(19372.0 / 6561), (float)(-25360.0 / 2187), (float)(64448.0 / 6561), (float)(-212.0 / 729), 0, 0},
+    {(float)(9017.0 / 3168), (float)(-355.0 / 33), (float)(46732.0 / 5247), (float)(49.0 / 176),
+     (float)(-5103.0 / 18656), 0},
+    {(float)(35.0 / 384), 0.f, (float)(500.0 / 1113), (float)(125.0 / 192), (float)(-2187.0 / 6784),
+     (float)(11.0 / 84)}};
+static __device__ __constant__ const float kCErr[7] = {
+    (float)(35.0 / 384 - 1951.0 / 21600), 0.f, (float)(500.0 / 1113 - 22642.0 / 50085),
+    (float)(125.0 / 192 - 451.0 / 720), (float)(-2187.0 / 6784 + 12231.0 / 42400),
+    (float)(11.0 / 84 - 649.0 / 6300), (float)(-1.0 / 60)};
+static __device__ __constant__ const float kCMid[7] = {
+    (float)(6025192743.0 / 30085553152.0 / 2), 0.f, (float)(51252292925.0 / 65400821598.0 / 2),
+    (float)(-2691868925.0 / 45128329728.0 / 2), (float)(187940372067.0 / 1594534317056.0 / 2),
+    (float)(-1776094331.0 / 19743644256.0 / 2), (float)(11237099.0 / 235043384.0 / 2)};
+
+// fp64 step-size controller fed by the fp32 error ratio (torchdiffeq misc._optimal_step_size)
+__device__ __forceinline__ double next_dt(double dt, float ratio) {
+    if (ratio == 0.f) return dt * 10.0;
+    double dfac = (ratio < 1.f) ? 1.0 : 0.2;
+    double f = 0.9 / pow((double)ratio, 0.2);
+    // torch.min(ifactor, torch.max(f, dfactor)) : NaN propagates like torch.max/min
+    if (!(f == f)) return dt * f;
+    f = f > dfac ? f : dfac;
+    f = f < 10.0 ? f : 10.0;
+    return dt * f;
+}
+
+// Hairer initial step from the three fp32 norms (torchdiffeq misc._select_initial_step, order arg 4)
+__device__ __forceinline__ float init_h0(float d0, float d1) {
+    return (d0 < 1e-5f || d1 < 1e-5f) ? 1e-6f : 0.01f * d0 / d1;
+}
+__device__ __forceinline__ double init_dt(float h0, float d1, float d2) {
+    float h1 = (d1 <= 1e-15f && d2 <= 1e-15f) ? fmaxf(1e-6f, h0 * 1e-3f) : powf(0.01f / fmaxf(d1, d2), 0.2f);
+    return (double)fminf(100.f * h0, h1);
+}
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// order-preserving float <-> uint map so that atomicMax works on floats of either sign
+__device__ __forceinline__ unsigned f2ord(float f) {
+    unsigned u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(unsigned u) {
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+
+// ---- barrier projection, one row per thread (barrier_projection.py:232-255) -------------------
+// Runs max_iter bisection midpoints; bit k of the returned word is set when |sum v| >= tol at
+// midpoint k (NOT converged), mu_k is written to mus[k*mu_stride].  The caller combines the
+// not-converged words of every row of the batch (OR) to find the batch-global stop iteration.
+__device__ __forceinline__ unsigned bisect_all(const float (&ft)[NH], const float (&lo)[NH], int max_iter,
+                                               float tol, float* mus, int mu_stride) {
+    float hi = ft[0] - lo[0], lw = ft[0];
+#pragma unroll
+    for (int j = 1; j < NH; ++j) { hi = fmaxf(hi, ft[j] - lo[j]); lw = fminf(lw, ft[j]); }
+    unsigned notconv = 0;
+    for (int k = 0; k < max_iter; ++k) {
+        float mu = (hi - lw) / 2.f + lw;
+        float e = 0.f;
+#pragma unroll
+        for (int j = 0; j < NH; ++j) e += fmaxf(ft[j] - mu, lo[j]);
+        mus[k * mu_stride] = mu;
+        if (!(fabsf(e) < tol)) notconv |= (1u << k);
+        if (e > 0.f) lw = mu;
+        if (e < 0.f) hi = mu;
+    }
+    return notconv;
+}
+// stop iteration from the OR of the not-converged words: first k whose bit is clear, else the last
+__device__ __forceinline__ int stop_iter(unsigned notconv_or, int max_iter) {
+    unsigned conv = ~notconv_or & (max_iter >= 32 ? 0xffffffffu : ((1u << max_iter) - 1u));
+    return conv ? (__ffs(conv) - 1) : (max_iter - 1);
+}
+
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
+
+}  // namespace fiode

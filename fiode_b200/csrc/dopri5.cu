@@ -1,0 +1,444 @@
+// fiode_b200/csrc/dopri5.cu -- device-resident adaptive Dormand-Prince solver for the FI-ODE
+// simplex dynamics.  One cooperative persistent kernel per solve; no host sync per step.
+//
+// Replaces torchdiffeq==0.2.2 odeint(..., method='dopri5') as called at the reference's
+// models.py:236-241 (func = dyn_fun.ode_forward, dynamics/classification.py:104-132).
+// Semantics follow SURVEY.md Appendix A: fp32 state/stages, fp64 time + controller, batch-global
+// RMS error norm, accept iff ratio <= 1, dense output inside the last accepted step; the barrier
+// projection keeps the reference's batch-global stop iteration (barrier_projection.py:247).
+//
+// Work split: the batch is cut into contiguous slabs of R rows, one slab per CTA for the whole
+// solve.  All row state (y, 7 stages, interpolant, MLP activations) lives in that CTA's shared
+// memory; the 128x128 mixing matrix lives in registers (64 per thread).  The only global traffic
+// per RHS evaluation is one grid barrier carrying a 32-bit OR word (projection stop iteration);
+// per step one more barrier carries the error-norm partial sums (ordered, deterministic).
+#include "common.cuh"
+#include <cooperative_groups.h>
+
+namespace fiode {
+
+constexpr int kThreads = 256;
+constexpr int kMaxGrid = 1024;
+constexpr int kMaxIter = 32;
+
+struct SolveCtl {                 // lives at the start of the caller's workspace (zeroed per solve)
+    unsigned count;               // monotonic arrival counter
+    unsigned orw[3];              // rotating OR words (projection not-converged bits)
+    double slots[2][2 * kMaxGrid];  // per-CTA partial sums, double-buffered by barrier parity
+};
+
+struct SolveArgs {
+    fiode_dyn_weights w;
+    const float* h0; const float* s; int s_rows; int B; int R;
+    const double* t; int nt; float rtol, atol; long long max_steps;
+    float* out; fiode_solve_stats* stats; SolveCtl* ctl;
+};
+
+struct Red { double s0, s1; unsigned orw; };
+
+// One grid-wide barrier that also (a) ORs a 32-bit word and (b) sums two doubles in CTA order.
+// Caller passes the CTA-level values in thread 0.
+__device__ __forceinline__ Red grid_reduce(SolveCtl* ctl, unsigned& epoch, double s0, double s1, unsigned orw,
+                                           bool want_sums, Red* sh) {
+    const unsigned G = gridDim.x, e = epoch;
+    if (threadIdx.x == 0) {
+        if (want_sums) {
+            double* sl = ctl->slots[e & 1];
+            __stcg(sl + 2 * blockIdx.x, s0);
+            __stcg(sl + 2 * blockIdx.x + 1, s1);
+        }
+        if (orw) atomicOr(&ctl->orw[e % 3], orw);
+        __threadfence();
+        atomicAdd(&ctl->count, 1u);
+        const unsigned target = (e + 1u) * G;
+        while (ld_acquire_u32(&ctl->count) < target) {}
+        if (blockIdx.x == 0) __stcg(&ctl->orw[(e + 2) % 3], 0u);
+        sh->orw = __ldcg(&ctl->orw[e % 3]);
+    }
+    __syncthreads();
+    if (want_sums && threadIdx.x < 32) {
+        const double* sl = ctl->slots[e & 1];
+        double a0 = 0, a1 = 0;
+        for (unsigned i = threadIdx.x; i < G; i += 32) { a0 += __ldcg(sl + 2 * i); a1 += __ldcg(sl + 2 * i + 1); }
+        a0 = warp_sum(a0); a1 = warp_sum(a1);
+        if (threadIdx.x == 0) { sh->s0 = a0; sh->s1 = a1; }
+    }
+    if (want_sums) __syncthreads();
+    epoch = e + 1;
+    return *sh;
+}
+
+// CTA-level sum of a per-thread double pair -> valid in thread 0
+__device__ __forceinline__ void cta_sum2(double& a, double& b, double* scratch /*[16]*/) {
+    a = warp_sum(a); b = warp_sum(b);
+    const int w = threadIdx.x >> 5;
+    if ((threadIdx.x & 31) == 0) { scratch[w] = a; scratch[8 + w] = b; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double x = 0, y = 0;
+#pragma unroll
+        for (int i = 0; i < kThreads / 32; ++i) { x += scratch[i]; y += scratch[8 + i]; }
+        a = x; b = y;
+    }
+    __syncthreads();
+}
+
+struct Smem {
+    float *c, *z1, *z2;          // [Rp][128]
+    float *y, *ys, *ft, *lo;     // [Rp][SROW]
+    float *k;                    // [7][Rp][SROW]
+    float *ce, *cd, *cc, *cb, *ca;  // interpolant coefficients [Rp][SROW]
+    float *mus;                  // [kMaxIter][Rp]
+    double* red;                 // [16]
+    Red* rr;
+    unsigned* orw;
+};
+
+// One evaluation of f(h) for the CTA's slab: ys -> kout (both [Rp][SROW] in smem).
+// Follows classification.py:96-115 + barrier_projection.py:232-255.
+__device__ __forceinline__ void eval_rhs(const SolveArgs& a, const Smem& S, int R, int Rp, const float (&q1)[NH],
+                                         const float4 (&q2)[16], const float (&q3)[16], float b2j, float b3o,
+                                         float* kout, unsigned& epoch) {
+    const int t = threadIdx.x;
+    // layer 1: z1[r][j] = relu(c[r][j] + Q1[j,:] . h[r,:])
+    {
+        const int j = t & 127;
+        for (int r = t >> 7; r < R; r += 2) {
+            const float4 h0 = *reinterpret_cast<const float4*>(S.ys + r * SROW);
+            const float4 h1 = *reinterpret_cast<const float4*>(S.ys + r * SROW + 4);
+            const float2 h2 = *reinterpret_cast<const float2*>(S.ys + r * SROW + 8);
+            float z = S.c[r * NM + j];
+            z = fmaf(q1[0], h0.x, z); z = fmaf(q1[1], h0.y, z); z = fmaf(q1[2], h0.z, z); z = fmaf(q1[3], h0.w, z);
+            z = fmaf(q1[4], h1.x, z); z = fmaf(q1[5], h1.y, z); z = fmaf(q1[6], h1.z, z); z = fmaf(q1[7], h1.w, z);
+            z = fmaf(q1[8], h2.x, z); z = fmaf(q1[9], h2.y, z);
+            S.z1[r * NM + j] = fmaxf(z, 0.f);
+        }
+    }
+    __syncthreads();
+    // layer 2: thread (j, kh) owns Q2[j][kh*64 .. +64) in registers; 4 rows per pass for ILP
+    {
+        const int j = t >> 1, kh = t & 1;
+        for (int r = 0; r < Rp; r += 4) {
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+            const float4* z0 = reinterpret_cast<const float4*>(S.z1 + (r + 0) * NM + kh * 64);
+            const float4* z1 = reinterpret_cast<const float4*>(S.z1 + (r + 1) * NM + kh * 64);
+            const float4* z2 = reinterpret_cast<const float4*>(S.z1 + (r + 2) * NM + kh * 64);
+            const float4* z3 = reinterpret_cast<const float4*>(S.z1 + (r + 3) * NM + kh * 64);
+#pragma unroll
+            for (int kk = 0; kk < 16; ++kk) {
+                const float4 q = q2[kk];
+                float4 v = z0[kk];
+                a0 = fmaf(q.x, v.x, a0); a0 = fmaf(q.y, v.y, a0); a0 = fmaf(q.z, v.z, a0); a0 = fmaf(q.w, v.w, a0);
+                v = z1[kk];
+                a1 = fmaf(q.x, v.x, a1); a1 = fmaf(q.y, v.y, a1); a1 = fmaf(q.z, v.z, a1); a1 = fmaf(q.w, v.w, a1);
+                v = z2[kk];
+                a2 = fmaf(q.x, v.x, a2); a2 = fmaf(q.y, v.y, a2); a2 = fmaf(q.z, v.z, a2); a2 = fmaf(q.w, v.w, a2);
+                v = z3[kk];
+                a3 = fmaf(q.x, v.x, a3); a3 = fmaf(q.y, v.y, a3); a3 = fmaf(q.z, v.z, a3); a3 = fmaf(q.w, v.w, a3);
+            }
+            a0 += __shfl_xor_sync(0xffffffffu, a0, 1);
+            a1 += __shfl_xor_sync(0xffffffffu, a1, 1);
+            a2 += __shfl_xor_sync(0xffffffffu, a2, 1);
+            a3 += __shfl_xor_sync(0xffffffffu, a3, 1);
+            if (kh == 0) {
+                S.z2[(r + 0) * NM + j] = fmaxf(a0 + b2j, 0.f);
+                S.z2[(r + 1) * NM + j] = fmaxf(a1 + b2j, 0.f);
+            } else {
+                S.z2[(r + 2) * NM + j] = fmaxf(a2 + b2j, 0.f);
+                S.z2[(r + 3) * NM + j] = fmaxf(a3 + b2j, 0.f);
+            }
+        }
+    }
+    __syncthreads();
+    // layer 3: 8 threads per output, 3 rows x 10 outputs per pass (threads 240..255 shadow group 0)
+    {
+        const int g = (t >> 3) % 30, ks = t & 7, o = g % NH, rr = g / NH;
+        for (int r0 = 0; r0 < R; r0 += 3) {
+            const int r = min(r0 + rr, Rp - 1);
+            const float4* z = reinterpret_cast<const float4*>(S.z2 + r * NM + ks * 16);
+            float acc = 0.f;
+#pragma unroll
+            for (int kk = 0; kk < 4; ++kk) {
+                const float4 v = z[kk];
+                acc = fmaf(q3[4 * kk + 0], v.x, acc); acc = fmaf(q3[4 * kk + 1], v.y, acc);
+                acc = fmaf(q3[4 * kk + 2], v.z, acc); acc = fmaf(q3[4 * kk + 3], v.w, acc);
+            }
+            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+            acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+            if (ks == 0 && t < 240 && r0 + rr < R) S.ft[(r0 + rr) * SROW + o] = acc + b3o;
+        }
+    }
+    __syncthreads();
+    // barrier projection, pass A: one row per thread, all max_iter midpoints, record mu_k + mask
+    unsigned nc = 0;
+    if (t < R) {
+        float ft[NH], lo[NH];
+#pragma unroll
+        for (int i = 0; i < NH; ++i) {
+            const float h = S.ys[t * SROW + i];
+            lo[i] = -a.w.alpha_1 * (expf(a.w.sigma_1 * h) - 1.f);
+            float f = S.ft[t * SROW + i];
+            if (a.w.scale_nominal) {
+                const float up = a.w.alpha_2 * (1.f - h);
+                f = (up - lo[i]) * sigmoidf_(f) + lo[i];
+                S.ft[t * SROW + i] = f;
+            }
+            ft[i] = f;
+            S.lo[t * SROW + i] = lo[i];
+        }
+        nc = bisect_all(ft, lo, a.w.max_iter, a.w.tol, S.mus + t, Rp);
+    }
+    if (t < 64) {  // R <= 64 -> rows live in warps 0 and 1
+        nc = __reduce_or_sync(0xffffffffu, nc);
+        if ((t & 31) == 0 && nc) atomicOr(S.orw, nc);
+    }
+    __syncthreads();
+    unsigned cta_or = 0;
+    if (t == 0) { cta_or = *S.orw; *S.orw = 0; }
+    const Red red = grid_reduce(a.ctl, epoch, 0.0, 0.0, cta_or, false, S.rr);
+    const int K = stop_iter(red.orw, a.w.max_iter);
+    // pass B: v = max(ftilde - mu_K, lower)
+    for (int e = t; e < R * NH; e += kThreads) {
+        const int r = e / NH, i = e - r * NH;
+        kout[r * SROW + i] = fmaxf(S.ft[r * SROW + i] - S.mus[K * Rp + r], S.lo[r * SROW + i]);
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const SolveArgs a) {
+    extern __shared__ float4 smem4[];
+    const int t = threadIdx.x;
+    const int row0 = blockIdx.x * a.R;
+    const int R = max(0, min(a.R, a.B - row0));
+    const int Rp = (a.R + 3) & ~3;
+
+    Smem S;
+    float* p = reinterpret_cast<float*>(smem4);
+    S.c = p; p += Rp * NM; S.z1 = p; p += Rp * NM; S.z2 = p; p += Rp * NM;
+    S.y = p; p += Rp * SROW; S.ys = p; p += Rp * SROW; S.ft = p; p += Rp * SROW; S.lo = p; p += Rp * SROW;
+    S.k = p; p += 7 * Rp * SROW;
+    S.ce = p; p += Rp * SROW; S.cd = p; p += Rp * SROW; S.cc = p; p += Rp * SROW; S.cb = p; p += Rp * SROW;
+    S.ca = p; p += Rp * SROW;
+    S.mus = p; p += kMaxIter * Rp;
+    S.red = reinterpret_cast<double*>(p); p += 32;
+    S.rr = reinterpret_cast<Red*>(p); p += 8;
+    S.orw = reinterpret_cast<unsigned*>(p); p += 4;
+
+    // ---- one-time setup: weights to registers, c = b1 + bx + Qx s, y = h0 -----------------------
+    float q1[NH]; float4 q2[16]; float q3[16]; float b2j, b3o;
+    {
+        const int j = t & 127;
+#pragma unroll
+        for (int i = 0; i < NH; ++i) q1[i] = a.w.Q1[j * NH + i];
+        const int j2 = t >> 1, kh = t & 1;
+        const float4* src = reinterpret_cast<const float4*>(a.w.Q2 + j2 * NM + kh * 64);
+#pragma unroll
+        for (int kk = 0; kk < 16; ++kk) q2[kk] = src[kk];
+        b2j = a.w.b2[j2];
+        const int g = (t >> 3) % 30, ks = t & 7, o = g % NH;
+#pragma unroll
+        for (int kk = 0; kk < 16; ++kk) q3[kk] = a.w.Q3[o * NM + ks * 16 + kk];
+        b3o = a.w.b3[o];
+        for (int e = t; e < Rp * NM; e += kThreads) { S.z1[e] = 0.f; S.z2[e] = 0.f; }
+        float qx[NH];
+#pragma unroll
+        for (int i = 0; i < NH; ++i) qx[i] = a.w.Qx[j * NH + i];
+        const float bj = a.w.b1[j] + a.w.bx[j];
+        for (int r = t >> 7; r < Rp; r += 2) {
+            float z = 0.f;
+            if (r < R) {
+                const float* sr = a.s + (size_t)(a.s_rows == 1 ? 0 : row0 + r) * NH;
+                // (Q1 h + b1) + (Qx s + bx) is regrouped as Q1 h + (Qx s + (b1 + bx)): <= 1 ulp apart
+#pragma unroll
+                for (int i = 0; i < NH; ++i) z = fmaf(qx[i], sr[i], z);
+                z += bj;
+            }
+            S.c[r * NM + j] = z;
+        }
+        for (int e = t; e < Rp * SROW; e += kThreads) {
+            const int r = e / SROW, i = e - r * SROW;
+            const float v = (r < R && i < NH) ? a.h0[(size_t)(row0 + r) * NH + i] : 0.f;
+            S.y[e] = v; S.ys[e] = v;
+            S.ce[e] = v; S.cd[e] = v; S.cc[e] = v; S.cb[e] = v; S.ca[e] = v;  // interp_coeff = [y0]*5
+        }
+        for (int e = t; e < R * NH; e += kThreads) {
+            const int r = e / NH, i = e - r * NH;
+            a.out[(size_t)(row0 + r) * NH + i] = a.h0[(size_t)(row0 + r) * NH + i];  // solution[0] = y0
+        }
+        if (t == 0) *S.orw = 0;
+    }
+    __syncthreads();
+
+    unsigned epoch = 0;
+    const double inv_n = 1.0 / ((double)a.B * NH);
+    const size_t out_stride = (size_t)a.B * NH;
+    float* k0 = S.k;
+    auto kst = [&](int s) { return S.k + s * Rp * SROW; };
+
+    int n_accept = 0, n_reject = 0, nfe = 0, status = 0, n_logged = 0;
+    double tcur = a.t[0], t_left = tcur, dt;
+
+    // ---- f0 and the initial step (misc._select_initial_step) ------------------------------------
+    eval_rhs(a, S, R, Rp, q1, q2, q3, b2j, b3o, k0, epoch); ++nfe;
+    float h0s;
+    {
+        double s0 = 0, s1 = 0;
+        for (int e = t; e < R * NH; e += kThreads) {
+            const int r = e / NH, i = e - r * NH;
+            const float y = S.y[r * SROW + i], f = k0[r * SROW + i];
+            const float sc = a.atol + fabsf(y) * a.rtol;
+            const float u = y / sc, v = f / sc;
+            s0 += (double)u * u; s1 += (double)v * v;
+        }
+        cta_sum2(s0, s1, S.red);
+        const Red rd = grid_reduce(a.ctl, epoch, s0, s1, 0u, true, S.rr);
+        const float d0 = sqrtf((float)(rd.s0 * inv_n)), d1 = sqrtf((float)(rd.s1 * inv_n));
+        h0s = init_h0(d0, d1);
+        for (int e = t; e < R * NH; e += kThreads) {
+            const int r = e / NH, i = e - r * NH;
+            S.ys[r * SROW + i] = S.y[r * SROW + i] + h0s * k0[r * SROW + i];
+        }
+        __syncthreads();
+        eval_rhs(a, S, R, Rp, q1, q2, q3, b2j, b3o, kst(1), epoch); ++nfe;
+        double s2 = 0, dummy = 0;
+        for (int e = t; e < R * NH; e += kThreads) {
+            const int r = e / NH, i = e - r * NH;
+            const float sc = a.atol + fabsf(S.y[r * SROW + i]) * a.rtol;
+            const float u = (kst(1)[r * SROW + i] - k0[r * SROW + i]) / sc;
+            s2 += (double)u * u;
+        }
+        cta_sum2(s2, dummy, S.red);
+        const Red rd2 = grid_reduce(a.ctl, epoch, s2, 0.0, 0u, true, S.rr);
+        const float d2 = sqrtf((float)(rd2.s0 * inv_n)) / h0s;
+        dt = init_dt(h0s, d1, d2);
+    }
+
+    // ---- main loop: integrate through each requested output time ---------------------------------
+    long long nsteps_total = 0;
+    for (int it = 1; it < a.nt && status == 0; ++it) {
+        const double tnext = a.t[it];
+        long long nsteps = 0;
+        while (tnext > tcur) {
+            if (nsteps >= a.max_steps) { status = 3; break; }
+            if (!(tcur + dt > tcur)) { status = 1; break; }
+            const float dtf = (float)dt;
+            // stages 1..6
+            for (int s = 0; s < 6; ++s) {
+                for (int e = t; e < R * NH; e += kThreads) {
+                    const int r = e / NH, i = e - r * NH, o = r * SROW + i;
+                    float acc = kst(0)[o] * (kBeta[s][0] * dtf);
+                    for (int j = 1; j <= s; ++j) acc = fmaf(kst(j)[o], kBeta[s][j] * dtf, acc);
+                    S.ys[o] = S.y[o] + acc;
+                }
+                __syncthreads();
+                eval_rhs(a, S, R, Rp, q1, q2, q3, b2j, b3o, kst(s + 1), epoch); ++nfe;
+            }
+            // error estimate + norm (+ count of non-finite entries of the step's start state)
+            double se = 0, nonfin = 0;
+            for (int e = t; e < R * NH; e += kThreads) {
+                const int r = e / NH, i = e - r * NH, o = r * SROW + i;
+                float err = kst(0)[o] * (dtf * kCErr[0]);
+#pragma unroll
+                for (int j = 1; j < 7; ++j) err = fmaf(kst(j)[o], dtf * kCErr[j], err);
+                const float y0 = S.y[o], y1 = S.ys[o];
+                const float tol = a.atol + a.rtol * fmaxf(fabsf(y0), fabsf(y1));
+                const float q = err / tol;
+                se += (double)q * q;
+                if (!isfinite(y0)) nonfin += 1.0;
+            }
+            cta_sum2(se, nonfin, S.red);
+            const Red rd = grid_reduce(a.ctl, epoch, se, nonfin, 0u, true, S.rr);
+            if (rd.s1 > 0.0) { status = 2; break; }
+            const float ratio = fabsf(sqrtf((float)(rd.s0 * inv_n)));
+            if (blockIdx.x == 0 && t == 0 && n_logged < FIODE_LOG_STEPS) {
+                a.stats->dts[n_logged] = dt; a.stats->ratios[n_logged] = ratio;
+            }
+            if (n_logged < FIODE_LOG_STEPS) ++n_logged;
+            if (ratio <= 1.f) {
+                // accept: fit the quartic interpolant (interp._interp_fit), advance, FSAL
+                for (int e = t; e < R * NH; e += kThreads) {
+                    const int r = e / NH, i = e - r * NH, o = r * SROW + i;
+                    float mid = kst(0)[o] * (dtf * kCMid[0]);
+#pragma unroll
+                    for (int j = 1; j < 7; ++j) mid = fmaf(kst(j)[o], dtf * kCMid[j], mid);
+                    const float y0 = S.y[o], y1 = S.ys[o], f0 = kst(0)[o], f1 = kst(6)[o];
+                    const float ym = y0 + mid;
+                    S.ca[o] = 2.f * dtf * (f1 - f0) - 8.f * (y1 + y0) + 16.f * ym;
+                    S.cb[o] = dtf * (5.f * f0 - 3.f * f1) + 18.f * y0 + 14.f * y1 - 32.f * ym;
+                    S.cc[o] = dtf * (f1 - 4.f * f0) - 11.f * y0 - 5.f * y1 + 16.f * ym;
+                    S.cd[o] = dtf * f0;
+                    S.ce[o] = y0;
+                    S.y[o] = y1;
+                    kst(0)[o] = f1;
+                }
+                __syncthreads();
+                t_left = tcur; tcur = tcur + dt; ++n_accept;
+            } else {
+                ++n_reject;
+            }
+            dt = next_dt(dt, ratio);
+            ++nsteps; ++nsteps_total;
+        }
+        if (status) break;
+        // dense output at tnext inside [t_left, tcur] (interp._interp_evaluate)
+        const float x = (float)((tnext - t_left) / (tcur - t_left));
+        for (int e = t; e < R * NH; e += kThreads) {
+            const int r = e / NH, i = e - r * NH, o = r * SROW + i;
+            float total = S.ce[o] + x * S.cd[o];
+            float xp = x * x; total = total + xp * S.cc[o];
+            xp = xp * x; total = total + xp * S.cb[o];
+            xp = xp * x; total = total + xp * S.ca[o];
+            a.out[it * out_stride + (size_t)(row0 + r) * NH + i] = total;
+        }
+    }
+    if (blockIdx.x == 0 && t == 0) {
+        a.stats->n_accept = n_accept; a.stats->n_reject = n_reject; a.stats->nfe = nfe;
+        a.stats->status = status; a.stats->t_final = tcur; a.stats->last_dt = dt;
+        a.stats->n_logged = n_logged;
+    }
+}
+
+static size_t solver_smem_bytes(int R) {
+    const int Rp = (R + 3) & ~3;
+    size_t f = (size_t)3 * Rp * NM + (size_t)(4 + 7 + 5) * Rp * SROW + (size_t)kMaxIter * Rp + 32 + 8 + 4;
+    return f * sizeof(float);
+}
+
+}  // namespace fiode
+
+using namespace fiode;
+
+extern "C" size_t fiode_dopri5_workspace_bytes(int B) { (void)B; return sizeof(SolveCtl); }
+
+extern "C" int fiode_dopri5_simplex(const fiode_dyn_weights* w, const float* h0, const float* s, int s_rows,
+                                    int B, const double* t, int nt, double rtol, double atol,
+                                    long long max_num_steps, float* out, fiode_solve_stats* stats, void* ws,
+                                    size_t ws_bytes, int rows_per_cta, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!w || !h0 || !s || !t || !out || !stats || !ws) { set_error("fiode_dopri5_simplex: null pointer"); return -1; }
+    if (B <= 0 || nt < 1) { set_error("fiode_dopri5_simplex: B=%d nt=%d", B, nt); return -1; }
+    if (s_rows != 1 && s_rows != B) { set_error("fiode_dopri5_simplex: s_rows must be 1 or B"); return -1; }
+    if (ws_bytes < sizeof(SolveCtl)) { set_error("fiode_dopri5_simplex: workspace too small"); return -1; }
+    if (w->max_iter < 1 || w->max_iter > kMaxIter) { set_error("fiode_dopri5_simplex: max_iter must be in [1,32]"); return -1; }
+    const int nsm = sm_count();
+    int R = rows_per_cta;
+    if (R <= 0) {  // auto: spread over the SMs, at least 2 rows per CTA
+        R = (B + nsm - 1) / nsm;
+        if (R < 2) R = 2;
+    }
+    if (R > 64) { set_error("fiode_dopri5_simplex: batch %d needs %d rows per CTA (> 64); split the batch", B, R); return -2; }
+    const int G = (B + R - 1) / R;
+    if (G > nsm || G > kMaxGrid) { set_error("fiode_dopri5_simplex: grid %d exceeds co-resident CTAs %d", G, nsm); return -2; }
+    const size_t smem = solver_smem_bytes(R);
+    FIODE_CUDA(cudaFuncSetAttribute(dopri5_simplex_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    FIODE_CUDA(cudaMemsetAsync(ws, 0, sizeof(SolveCtl), st));
+    SolveArgs a;
+    a.w = *w; a.h0 = h0; a.s = s; a.s_rows = s_rows; a.B = B; a.R = R; a.t = t; a.nt = nt;
+    a.rtol = (float)rtol; a.atol = (float)atol; a.max_steps = max_num_steps; a.out = out; a.stats = stats;
+    a.ctl = reinterpret_cast<SolveCtl*>(ws);
+    void* args[] = {&a};
+    FIODE_CUDA(cudaLaunchCooperativeKernel((void*)dopri5_simplex_kernel, dim3(G), dim3(kThreads), args, smem, st));
+    count_launch(1);
+    return 0;
+}

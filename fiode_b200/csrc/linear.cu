@@ -1,0 +1,163 @@
+// fiode_b200/csrc/linear.cu -- fp32 "NT" GEMM  C[m][n] = sum_k A[m][k] * B[n][k]  (both K-major)
+// with deterministic split-K, + bias, + GroupSort epilogue.
+//
+// Replaces F.linear(X, Q, b) at libs/ortho_conv/layers.py:105 (CayleyLinear.forward) for the
+// backbone head 4096->512->512->10, and serves the Cayley weight preparation (cayley.cu).
+// FP32 FFMA on purpose: SURVEY section 8(d) asks tensor cores only where 3xTF32 holds rtol 1e-4 -- the
+// tcgen05 3xTF32 variant is the planned replacement for the M>=256 head GEMM.
+//
+// CTA tile 64x64, 128 threads, thread tile 8(m, strided by 8) x 4(n, strided by 16); smem tiles keep
+// K contiguous ([row][32+4]) so global->smem is a straight 16-byte cp.async and both operands
+// are read back as float4 along K (12 LDS.128 per 128 FFMA).
+#include "common.cuh"
+#include <cuda_pipeline.h>
+
+namespace fiode {
+
+constexpr int GT = 64, GK = 32, GS = GK + 4, GTHREADS = 128;
+
+__global__ void __launch_bounds__(GTHREADS) gemm_nt_kernel(const float* __restrict__ A, int lda,
+                                                           const float* __restrict__ Bm, int ldb, int M, int N, int K,
+                                                           int k_per_split, float* __restrict__ part /*[splits][M][N]*/) {
+    __shared__ __align__(16) float As[2][GT * GS];
+    __shared__ __align__(16) float Bs[2][GT * GS];
+    const int t = threadIdx.x;
+    const int m0 = blockIdx.y * GT, n0 = blockIdx.x * GT;
+    const int k_begin = blockIdx.z * k_per_split, k_end = min(K, k_begin + k_per_split);
+    const int tn = t & 15, tm = t >> 4;
+    float acc[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    auto load_tile = [&](int buf, int k0) {
+        // 64 rows x 8 float4 per operand = 512 float4 -> 4 per thread per operand
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int e = t + i * GTHREADS, r = e >> 3, q = e & 7;
+            const int k = k0 + q * 4;
+            float* da = &As[buf][r * GS + q * 4];
+            float* db = &Bs[buf][r * GS + q * 4];
+            if (m0 + r < M && k + 3 < k_end) __pipeline_memcpy_async(da, A + (size_t)(m0 + r) * lda + k, 16);
+            else {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) da[c] = (m0 + r < M && k + c < k_end) ? A[(size_t)(m0 + r) * lda + k + c] : 0.f;
+            }
+            if (n0 + r < N && k + 3 < k_end) __pipeline_memcpy_async(db, Bm + (size_t)(n0 + r) * ldb + k, 16);
+            else {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) db[c] = (n0 + r < N && k + c < k_end) ? Bm[(size_t)(n0 + r) * ldb + k + c] : 0.f;
+            }
+        }
+        __pipeline_commit();
+    };
+
+    const int n_tiles = (k_end - k_begin + GK - 1) / GK;
+    if (n_tiles > 0) load_tile(0, k_begin);
+    for (int it = 0; it < n_tiles; ++it) {
+        const int buf = it & 1;
+        if (it + 1 < n_tiles) { load_tile(buf ^ 1, k_begin + (it + 1) * GK); __pipeline_wait_prior(1); }
+        else __pipeline_wait_prior(0);
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < GK / 4; ++q) {
+            float4 a[8], b[4];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) a[i] = *reinterpret_cast<const float4*>(&As[buf][(tm + 8 * i) * GS + q * 4]);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = *reinterpret_cast<const float4*>(&Bs[buf][(tn + 16 * j) * GS + q * 4]);
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    acc[i][j] = fmaf(a[i].x, b[j].x, acc[i][j]);
+                    acc[i][j] = fmaf(a[i].y, b[j].y, acc[i][j]);
+                    acc[i][j] = fmaf(a[i].z, b[j].z, acc[i][j]);
+                    acc[i][j] = fmaf(a[i].w, b[j].w, acc[i][j]);
+                }
+        }
+        __syncthreads();
+    }
+    float* dst = part + (size_t)blockIdx.z * M * N;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int m = m0 + tm + 8 * i;
+        if (m >= M) continue;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int n = n0 + tn + 16 * j;
+            if (n < N) dst[(size_t)m * N + n] = acc[i][j];
+        }
+    }
+}
+
+// y[m][n] = alpha * sum_s part[s][m][n] (+ bias[n]) (+ beta * addend[m][n]), optional GroupSort over n halves
+__global__ void gemm_epilogue_kernel(const float* __restrict__ part, int splits, int M, int N,
+                                     const float* __restrict__ bias, float alpha, int group_sort,
+                                     float* __restrict__ y, int ldy) {
+    const size_t MN = (size_t)M * N;
+    if (group_sort) {
+        const int half = N / 2;
+        const size_t total = (size_t)M * half;
+        for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+            const size_t m = e / half; const int n = (int)(e - m * half);
+            float u = 0.f, w = 0.f;
+            for (int s = 0; s < splits; ++s) { u += part[s * MN + m * N + n]; w += part[s * MN + m * N + n + half]; }
+            u = alpha * u + (bias ? bias[n] : 0.f);
+            w = alpha * w + (bias ? bias[n + half] : 0.f);
+            y[m * ldy + n] = fmaxf(u, w);
+            y[m * ldy + n + half] = fminf(u, w);
+        }
+    } else {
+        for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < MN; e += (size_t)gridDim.x * blockDim.x) {
+            const size_t m = e / N; const int n = (int)(e - m * N);
+            float u = 0.f;
+            for (int s = 0; s < splits; ++s) u += part[s * MN + e];
+            y[m * ldy + n] = alpha * u + (bias ? bias[n] : 0.f);
+        }
+    }
+}
+
+size_t gemm_nt_workspace(int M, int N, int K) {
+    // worst-case split count is bounded by 32
+    (void)K;
+    return (size_t)32 * M * N * sizeof(float);
+}
+
+// C = alpha * A B^T (+bias) (+GroupSort), deterministic split-K sized to fill the GPU
+int gemm_nt(const float* A, int lda, const float* Bm, int ldb, int M, int N, int K, const float* bias, float alpha,
+            int group_sort, float* y, int ldy, float* ws, size_t ws_bytes, cudaStream_t st) {
+    const int tiles = ((M + GT - 1) / GT) * ((N + GT - 1) / GT);
+    int splits = 1;
+    const int target = 4 * sm_count();
+    while (splits < 32 && tiles * splits < target && K / (splits * 2) >= 64) splits *= 2;
+    if ((size_t)splits * M * N * sizeof(float) > ws_bytes) { set_error("gemm_nt: workspace too small"); return -1; }
+    int kps = (K + splits - 1) / splits;
+    kps = (kps + GK - 1) / GK * GK;
+    splits = (K + kps - 1) / kps;
+    dim3 grid((N + GT - 1) / GT, (M + GT - 1) / GT, splits);
+    gemm_nt_kernel<<<grid, GTHREADS, 0, st>>>(A, lda, Bm, ldb, M, N, K, kps, ws);
+    const size_t total = group_sort ? (size_t)M * (N / 2) : (size_t)M * N;
+    gemm_epilogue_kernel<<<(unsigned)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096), 256, 0, st>>>(
+        ws, splits, M, N, bias, alpha, group_sort, y, ldy);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "gemm_nt launch");
+    count_launch(2);
+    return 0;
+}
+
+}  // namespace fiode
+
+using namespace fiode;
+
+extern "C" size_t fiode_linear_workspace_bytes(int M, int N, int K) { return gemm_nt_workspace(M, N, K); }
+
+extern "C" int fiode_linear_fwd(const float* X, const float* Q, const float* bias, int M, int N, int K,
+                                int group_sort, float* y, void* ws, size_t ws_bytes, void* stream) {
+    if (!X || !Q || !y || !ws) { set_error("fiode_linear_fwd: null pointer"); return -1; }
+    if (M <= 0 || N <= 0 || K <= 0 || (K & 3)) { set_error("fiode_linear_fwd: bad sizes (K must be a multiple of 4)"); return -1; }
+    if (group_sort && (N & 1)) { set_error("fiode_linear_fwd: GroupSort needs an even width"); return -1; }
+    return gemm_nt(X, K, Q, K, M, N, K, bias, 1.f, group_sort, y, N, reinterpret_cast<float*>(ws), ws_bytes,
+                   (cudaStream_t)stream);
+}

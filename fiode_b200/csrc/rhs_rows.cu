@@ -1,0 +1,465 @@
+// fiode_b200/csrc/rhs_rows.cu -- the FI-ODE right-hand side over MANY rows (certification grid,
+// FI-loss boundary samples): persistent CTAs, 64-row tiles, FFMA register-tiled 128x128 mixing.
+//
+// Replaces dynamics/classification.py:96-126 (_h_dot_raw + eval_dot_light) +
+// barrier_projection/barrier_projection.py:232-255 evaluated over N rows, and the body of the
+// certification loop robustness/certify_lipschitz.py:115-134.
+//
+// Per 64-row tile (128 threads, 2 CTAs/SM so one CTA's latency-bound projection overlaps the
+// other's FFMA loop):
+//   L1  z1T[k][r] = relu(c[k] + Q1[k,:] . h[r,:])            (c = b1 + bx + Qx s, per image)
+//   L2  acc[4 rows][16 cols] += z1T[k][rows] * Q2T[k][cols]   (64 FFMA per 5 LDS.128)
+//   L3  per-thread partial ftilde over its 16 columns -> smem -> ordered 8-way sum
+//   P   bisection projection, one row per thread, all max_iter midpoints
+// The projection's stop iteration is GLOBAL over the rows of one reference call
+// (barrier_projection.py:247); it is only known after every row has been seen.  Two epilogues:
+//   kStore    write ftilde (N,10) + OR the not-converged words; a finishing kernel then replays the
+//             bisection to the global stop iteration K.
+//   kCertify  track, for every candidate K, the running max of the violation (max is exactly what
+//             certify_lipschitz.py:131-134 consumes); the finishing kernel picks the K the
+//             reference would have stopped at.  One pass, bit-faithful to the batch-global rule.
+#include "common.cuh"
+
+namespace fiode {
+
+constexpr int TR = 64;        // rows per tile
+constexpr int RT = 128;       // threads per CTA
+constexpr int Q1S = 12;       // Q1s row: 10 weights, c, pad
+constexpr int kIt = 32;       // max candidates tracked
+
+enum { kStore = 0, kCertify = 1 };
+
+struct RowsArgs {
+    fiode_dyn_weights w;
+    // kStore
+    const float* h; const float* s; long long N; long long s_rows; long long s_group;
+    float* ft_out; unsigned* notconv;              // (N,10), 1 word
+    // kCertify
+    const uint8_t* gridz; const float* lut; int T; long long Ng; long long chunk; int n_chunks;
+    const int* labels; int M; int P;               // images in this launch, CTAs per image
+    float sa, sqrtn, sqrt2, dist, inv_T;           // fp32 roundings of the python-double constants
+    unsigned* cmax;                                // (M, n_chunks, 2, kIt) ordered-uint maxima
+    unsigned* cnot;                                // (M, n_chunks) not-converged OR words
+};
+
+struct RowsSmem {
+    float* Q2T;   // [128][128]
+    float* z1T;   // [128][TR]   (aliased by part[10][TR*10] after the mixing loop)
+    float* Q1s;   // [128][Q1S]
+    float* Q3s;   // [10][128]
+    float* b2s;   // [128]
+    float* b3s;   // [16]
+    float* hs;    // [TR][10]
+    float* ft;    // [TR][10]
+};
+
+__device__ __forceinline__ RowsSmem carve(float* p) {
+    RowsSmem S;
+    S.Q2T = p; p += NM * NM; S.z1T = p; p += NM * TR; S.Q1s = p; p += NM * Q1S; S.Q3s = p; p += NH * NM;
+    S.b2s = p; p += NM; S.b3s = p; p += 16; S.hs = p; p += TR * NH; S.ft = p; p += TR * NH;
+    return S;
+}
+constexpr size_t kRowsSmemBytes =
+    (size_t)(NM * NM + NM * TR + NM * Q1S + NH * NM + NM + 16 + TR * NH + TR * NH) * sizeof(float);
+static_assert(2 * (kRowsSmemBytes + 1024) <= 228 * 1024, "two CTAs per SM must fit");
+
+__device__ __forceinline__ void stage_weights(const fiode_dyn_weights& w, const RowsSmem& S) {
+    const int t = threadIdx.x;
+    for (int e = t; e < NM * NM / 4; e += RT) {   // float4 along k, lanes along j: conflict-free transpose
+        const int j = e & 127, kk = e >> 7;
+        const float4 v = *reinterpret_cast<const float4*>(w.Q2 + j * NM + kk * 4);
+        S.Q2T[(kk * 4 + 0) * NM + j] = v.x; S.Q2T[(kk * 4 + 1) * NM + j] = v.y;
+        S.Q2T[(kk * 4 + 2) * NM + j] = v.z; S.Q2T[(kk * 4 + 3) * NM + j] = v.w;
+    }
+    for (int e = t; e < NM * NH; e += RT) {
+        const int k = e / NH, i = e - k * NH;
+        S.Q1s[k * Q1S + i] = w.Q1[e];
+    }
+    for (int e = t; e < NH * NM; e += RT) S.Q3s[e] = w.Q3[e];
+    for (int e = t; e < NM; e += RT) { S.b2s[e] = w.b2[e]; S.Q1s[e * Q1S + 11] = 0.f; }
+    if (t < 16) S.b3s[t] = t < NH ? w.b3[t] : 0.f;
+}
+
+// c[k] = b1[k] + bx[k] + Qx[k,:] . s  -> Q1s[k][10]
+__device__ __forceinline__ void set_static_feature(const fiode_dyn_weights& w, const RowsSmem& S, const float* s) {
+    const int k = threadIdx.x;   // RT == NM
+    float z = 0.f;
+#pragma unroll
+    for (int i = 0; i < NH; ++i) z = fmaf(__ldg(w.Qx + k * NH + i), __ldg(s + i), z);
+    S.Q1s[k * Q1S + 10] = z + (w.b1[k] + w.bx[k]);
+}
+
+// MLP over the tile whose h rows are in S.hs; result ftilde in S.ft ([TR][10]).
+__device__ __forceinline__ void tile_mlp(const RowsSmem& S) {
+    const int t = threadIdx.x;
+    // ---- L1: thread = (row pair rp / rp+32, k quarter) --------------------------------------
+    {
+        const int rp = t & 31, kq = t >> 5;
+        float ha[NH], hb[NH];
+#pragma unroll
+        for (int i = 0; i < NH; i += 2) {
+            const float2 a = *reinterpret_cast<const float2*>(S.hs + rp * NH + i);
+            const float2 b = *reinterpret_cast<const float2*>(S.hs + (rp + 32) * NH + i);
+            ha[i] = a.x; ha[i + 1] = a.y; hb[i] = b.x; hb[i + 1] = b.y;
+        }
+#pragma unroll 4
+        for (int k = kq * 32; k < kq * 32 + 32; ++k) {
+            const float4 q0 = *reinterpret_cast<const float4*>(S.Q1s + k * Q1S);
+            const float4 q1 = *reinterpret_cast<const float4*>(S.Q1s + k * Q1S + 4);
+            const float4 q2 = *reinterpret_cast<const float4*>(S.Q1s + k * Q1S + 8);
+            float za = q2.z, zb = q2.z;
+            za = fmaf(q0.x, ha[0], za); zb = fmaf(q0.x, hb[0], zb);
+            za = fmaf(q0.y, ha[1], za); zb = fmaf(q0.y, hb[1], zb);
+            za = fmaf(q0.z, ha[2], za); zb = fmaf(q0.z, hb[2], zb);
+            za = fmaf(q0.w, ha[3], za); zb = fmaf(q0.w, hb[3], zb);
+            za = fmaf(q1.x, ha[4], za); zb = fmaf(q1.x, hb[4], zb);
+            za = fmaf(q1.y, ha[5], za); zb = fmaf(q1.y, hb[5], zb);
+            za = fmaf(q1.z, ha[6], za); zb = fmaf(q1.z, hb[6], zb);
+            za = fmaf(q1.w, ha[7], za); zb = fmaf(q1.w, hb[7], zb);
+            za = fmaf(q2.x, ha[8], za); zb = fmaf(q2.x, hb[8], zb);
+            za = fmaf(q2.y, ha[9], za); zb = fmaf(q2.y, hb[9], zb);
+            S.z1T[k * TR + rp] = fmaxf(za, 0.f);
+            S.z1T[k * TR + rp + 32] = fmaxf(zb, 0.f);
+        }
+    }
+    __syncthreads();
+    // ---- L2: thread = (row group rg: rows 4rg..4rg+3, col group cg: cols 32q + 4cg + i) ------
+    const int cg = t & 7, rg = t >> 3;
+    float acc[4][16];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int c = 0; c < 16; ++c) acc[r][c] = 0.f;
+#pragma unroll 2
+    for (int k = 0; k < NM; ++k) {
+        const float4 a = *reinterpret_cast<const float4*>(S.z1T + k * TR + rg * 4);
+        const float av[4] = {a.x, a.y, a.z, a.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const float4 b = *reinterpret_cast<const float4*>(S.Q2T + k * NM + q * 32 + cg * 4);
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                acc[r][q * 4 + 0] = fmaf(av[r], b.x, acc[r][q * 4 + 0]);
+                acc[r][q * 4 + 1] = fmaf(av[r], b.y, acc[r][q * 4 + 1]);
+                acc[r][q * 4 + 2] = fmaf(av[r], b.z, acc[r][q * 4 + 2]);
+                acc[r][q * 4 + 3] = fmaf(av[r], b.w, acc[r][q * 4 + 3]);
+            }
+        }
+    }
+    // bias + relu
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const float4 b = *reinterpret_cast<const float4*>(S.b2s + q * 32 + cg * 4);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            acc[r][q * 4 + 0] = fmaxf(acc[r][q * 4 + 0] + b.x, 0.f);
+            acc[r][q * 4 + 1] = fmaxf(acc[r][q * 4 + 1] + b.y, 0.f);
+            acc[r][q * 4 + 2] = fmaxf(acc[r][q * 4 + 2] + b.z, 0.f);
+            acc[r][q * 4 + 3] = fmaxf(acc[r][q * 4 + 3] + b.w, 0.f);
+        }
+    }
+    __syncthreads();                         // everyone is done reading z1T -> reuse it as part[][]
+    // ---- L3 partials over this thread's 16 columns ---------------------------------------------
+    float* part = S.z1T;                     // [10][TR*10]
+#pragma unroll 2
+    for (int o = 0; o < NH; ++o) {
+        float p0 = 0.f, p1 = 0.f, p2 = 0.f, p3 = 0.f;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const float4 w3 = *reinterpret_cast<const float4*>(S.Q3s + o * NM + q * 32 + cg * 4);
+            p0 = fmaf(w3.x, acc[0][q * 4], p0); p0 = fmaf(w3.y, acc[0][q * 4 + 1], p0);
+            p0 = fmaf(w3.z, acc[0][q * 4 + 2], p0); p0 = fmaf(w3.w, acc[0][q * 4 + 3], p0);
+            p1 = fmaf(w3.x, acc[1][q * 4], p1); p1 = fmaf(w3.y, acc[1][q * 4 + 1], p1);
+            p1 = fmaf(w3.z, acc[1][q * 4 + 2], p1); p1 = fmaf(w3.w, acc[1][q * 4 + 3], p1);
+            p2 = fmaf(w3.x, acc[2][q * 4], p2); p2 = fmaf(w3.y, acc[2][q * 4 + 1], p2);
+            p2 = fmaf(w3.z, acc[2][q * 4 + 2], p2); p2 = fmaf(w3.w, acc[2][q * 4 + 3], p2);
+            p3 = fmaf(w3.x, acc[3][q * 4], p3); p3 = fmaf(w3.y, acc[3][q * 4 + 1], p3);
+            p3 = fmaf(w3.z, acc[3][q * 4 + 2], p3); p3 = fmaf(w3.w, acc[3][q * 4 + 3], p3);
+        }
+        float* dst = part + o * (TR * NH) + (rg * 4) * NH + cg;
+        dst[0] = p0; dst[NH] = p1; dst[2 * NH] = p2; dst[3 * NH] = p3;
+    }
+    __syncthreads();
+    // ---- L3 ordered 8-way sum: item = (o, r), r fastest across lanes --------------------------------
+#pragma unroll
+    for (int i = 0; i < (TR * NH) / RT; ++i) {
+        const int idx = t + i * RT, r = idx & (TR - 1), o = idx >> 6;
+        const float2* src = reinterpret_cast<const float2*>(part + o * (TR * NH) + r * NH);
+        const float2 u0 = src[0], u1 = src[1], u2 = src[2], u3 = src[3];
+        S.ft[r * NH + o] = (((u0.x + u0.y) + (u1.x + u1.y)) + ((u2.x + u2.y) + (u3.x + u3.y))) + S.b3s[o];
+    }
+    __syncthreads();
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(RT, 2) rhs_rows_kernel(const RowsArgs a) {
+    extern __shared__ float4 smem4[];
+    const RowsSmem S = carve(reinterpret_cast<float*>(smem4));
+    const int t = threadIdx.x;
+    stage_weights(a.w, S);
+    __syncthreads();
+
+    if (MODE == kStore) {
+        // tiles never straddle an s-group: tile = (group, 64-row block inside the group)
+        const long long group = a.s_rows == 1 ? a.N : a.s_group;
+        const long long blocks_per_group = (group + TR - 1) / TR;
+        const long long n_groups = (a.N + group - 1) / group;
+        const long long n_tiles = n_groups * blocks_per_group;
+        long long cur_group = -1;
+        unsigned notconv = 0;
+        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const long long gi = tile / blocks_per_group, bi = tile - gi * blocks_per_group;
+            const long long row0 = gi * group + bi * TR;
+            const long long gend = min(a.N, (gi + 1) * group);
+            const int rows = (int)min((long long)TR, gend - row0);
+            if (gi != cur_group) {
+                cur_group = gi;
+                set_static_feature(a.w, S, a.s + (a.s_rows == 1 ? 0 : gi) * NH);
+            }
+            for (int e = t; e < TR * NH; e += RT)
+                S.hs[e] = e < rows * NH ? a.h[row0 * NH + e] : 0.f;
+            __syncthreads();
+            tile_mlp(S);
+            if (t < rows) {
+                float ft[NH], lo[NH];
+#pragma unroll
+                for (int i = 0; i < NH; ++i) {
+                    const float h = S.hs[t * NH + i];
+                    lo[i] = -a.w.alpha_1 * (expf(a.w.sigma_1 * h) - 1.f);
+                    float f = S.ft[t * NH + i];
+                    if (a.w.scale_nominal) f = (a.w.alpha_2 * (1.f - h) - lo[i]) * sigmoidf_(f) + lo[i];
+                    ft[i] = f;
+                    a.ft_out[(row0 + t) * NH + i] = f;
+                }
+                // mask-only bisection (mu_k not kept; the finishing kernel replays to K)
+                float hi = ft[0] - lo[0], lw = ft[0];
+#pragma unroll
+                for (int j = 1; j < NH; ++j) { hi = fmaxf(hi, ft[j] - lo[j]); lw = fminf(lw, ft[j]); }
+                for (int k = 0; k < a.w.max_iter; ++k) {
+                    const float mu = (hi - lw) / 2.f + lw;
+                    float e = 0.f;
+#pragma unroll
+                    for (int j = 0; j < NH; ++j) e += fmaxf(ft[j] - mu, lo[j]);
+                    if (!(fabsf(e) < a.w.tol)) notconv |= (1u << k);
+                    if (e > 0.f) lw = mu;
+                    if (e < 0.f) hi = mu;
+                }
+            }
+            __syncthreads();
+        }
+        notconv = __reduce_or_sync(0xffffffffu, notconv);
+        if ((t & 31) == 0 && notconv) atomicOr(a.notconv, notconv);
+    } else {
+        // ---- certification: CTA = (image m, lane p of P); streams grid tiles of every chunk -----
+        const int m = blockIdx.x / a.P, p = blockIdx.x - m * a.P;
+        if (m >= a.M) return;
+        const int label = a.labels[m];
+        set_static_feature(a.w, S, a.s + (size_t)m * NH);
+        for (int ch = 0; ch < a.n_chunks; ++ch) {
+            const long long c0 = (long long)ch * a.chunk;
+            const long long c1 = (ch == a.n_chunks - 1) ? a.Ng : min(a.Ng, c0 + a.chunk);
+            const long long n_tiles = (c1 - c0 + TR - 1) / TR;
+            float m1[kIt], m2[kIt];
+#pragma unroll
+            for (int k = 0; k < kIt; ++k) { m1[k] = -INFINITY; m2[k] = -INFINITY; }
+            unsigned notconv = 0;
+            for (long long tile = p; tile < n_tiles; tile += a.P) {
+                const long long row0 = c0 + tile * TR;
+                const int rows = (int)min((long long)TR, c1 - row0);
+                // grid numerators -> eta = z/T (fp64 quotient rounded to fp32 == LUT), label swap
+                for (int e = t; e < TR * NH; e += RT) {
+                    float v = 0.f;
+                    if (e < rows * NH) {
+                        const int r = e / NH, i = e - r * NH;
+                        const int src = (i == 0) ? label : (i == label ? 0 : i);   // eval_utils.py:64-67
+                        v = a.lut[a.gridz[(row0 + r) * NH + src]];
+                    }
+                    S.hs[e] = v;
+                }
+                __syncthreads();
+                tile_mlp(S);
+                if (t < rows) {
+                    float ft[NH], lo[NH], emax = -INFINITY;
+#pragma unroll
+                    for (int i = 0; i < NH; ++i) {
+                        const float h = S.hs[t * NH + i];
+                        emax = fmaxf(emax, h);
+                        lo[i] = -a.w.alpha_1 * (expf(a.w.sigma_1 * h) - 1.f);
+                        float f = S.ft[t * NH + i];
+                        if (a.w.scale_nominal) f = (a.w.alpha_2 * (1.f - h) - lo[i]) * sigmoidf_(f) + lo[i];
+                        ft[i] = f;
+                    }
+                    unsigned wrong = 0;                       // certify_lipschitz.py:126-128
+#pragma unroll
+                    for (int i = 0; i < NH; ++i)
+                        if (S.hs[t * NH + i] == emax && i != label) wrong |= 1u << i;
+                    // certify_lipschitz.py:122-124
+                    const float Lf = a.sqrtn * (a.sa * expf(a.w.sigma_1 * (emax + a.inv_T))) + 1.f;
+                    const float perturb = (a.sqrt2 * Lf) * a.dist;
+                    float hi = ft[0] - lo[0], lw = ft[0];
+#pragma unroll
+                    for (int j = 1; j < NH; ++j) { hi = fmaxf(hi, ft[j] - lo[j]); lw = fminf(lw, ft[j]); }
+#pragma unroll
+                    for (int k = 0; k < kIt; ++k) {
+                        if (k < a.w.max_iter) {
+                            const float mu = (hi - lw) / 2.f + lw;
+                            float e = 0.f, fw = -INFINITY, fy = 0.f;
+#pragma unroll
+                            for (int j = 0; j < NH; ++j) {
+                                const float v = fmaxf(ft[j] - mu, lo[j]);
+                                e += v;
+                                if (wrong & (1u << j)) fw = fmaxf(fw, v);
+                                if (j == label) fy = v;
+                            }
+                            const float hx = -fy + fw;         // certify_lipschitz.py:41
+                            m2[k] = fmaxf(m2[k], hx);
+                            m1[k] = fmaxf(m1[k], hx + perturb);
+                            if (!(fabsf(e) < a.w.tol)) notconv |= (1u << k);
+                            if (e > 0.f) lw = mu;
+                            if (e < 0.f) hi = mu;
+                        }
+                    }
+                }
+                __syncthreads();
+            }
+            // CTA reduce (rows live in warps 0,1) and publish
+            if (t < 64) {
+                notconv = __reduce_or_sync(0xffffffffu, notconv);
+                unsigned* dst = a.cmax + ((size_t)m * a.n_chunks + ch) * 2 * kIt;
+#pragma unroll
+                for (int k = 0; k < kIt; ++k) {
+                    const float x1 = warp_max(m1[k]), x2 = warp_max(m2[k]);
+                    if ((t & 31) == 0 && k < a.w.max_iter) {
+                        atomicMax(dst + k, f2ord(x1));
+                        atomicMax(dst + kIt + k, f2ord(x2));
+                    }
+                }
+                if ((t & 31) == 0 && notconv) atomicOr(a.cnot + (size_t)m * a.n_chunks + ch, notconv);
+            }
+        }
+    }
+}
+
+// finishing kernel for kStore: replay the bisection to the global stop iteration K
+__global__ void rhs_finish_kernel(const float* __restrict__ ft, const float* __restrict__ h, long long N,
+                                  fiode_dyn_weights w, const unsigned* __restrict__ notconv, float* __restrict__ f,
+                                  float* __restrict__ mu_out, int* __restrict__ n_iter) {
+    const long long r = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const int K = stop_iter(*notconv, w.max_iter);
+    if (r == 0 && n_iter) *n_iter = K + 1;
+    if (r >= N) return;
+    float v[NH], lo[NH];
+#pragma unroll
+    for (int i = 0; i < NH; ++i) {
+        v[i] = ft[r * NH + i];
+        lo[i] = -w.alpha_1 * (expf(w.sigma_1 * h[r * NH + i]) - 1.f);
+    }
+    float hi = v[0] - lo[0], lw = v[0], mu = 0.f;
+#pragma unroll
+    for (int j = 1; j < NH; ++j) { hi = fmaxf(hi, v[j] - lo[j]); lw = fminf(lw, v[j]); }
+    for (int k = 0; k <= K; ++k) {
+        mu = (hi - lw) / 2.f + lw;
+        float e = 0.f;
+#pragma unroll
+        for (int j = 0; j < NH; ++j) e += fmaxf(v[j] - mu, lo[j]);
+        if (e > 0.f) lw = mu;
+        if (e < 0.f) hi = mu;
+    }
+#pragma unroll
+    for (int i = 0; i < NH; ++i) f[r * NH + i] = fmaxf(v[i] - mu, lo[i]);
+    if (mu_out) mu_out[r] = mu;
+}
+
+// finishing kernel for kCertify: per image, pick each chunk's stop iteration, max over chunks
+// (certify_lipschitz.py:131-143): out[m] = {max violation, max violation_larger_T}
+__global__ void certify_finish_kernel(const unsigned* __restrict__ cmax, const unsigned* __restrict__ cnot, int M,
+                                      int n_chunks, int max_iter, float kappa, float* __restrict__ out,
+                                      int* __restrict__ iters) {
+    const int m = blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= M) return;
+    float v1 = -INFINITY, v2 = -INFINITY;
+    for (int ch = 0; ch < n_chunks; ++ch) {
+        const int K = stop_iter(cnot[(size_t)m * n_chunks + ch], max_iter);
+        const unsigned* src = cmax + ((size_t)m * n_chunks + ch) * 2 * kIt;
+        v1 = fmaxf(v1, ord2f(src[K]) + kappa);          // (h + perturb) + kappa
+        v2 = fmaxf(v2, ord2f(src[kIt + K]) + kappa);    // h + kappa
+        if (iters) iters[(size_t)m * n_chunks + ch] = K + 1;
+    }
+    out[2 * m] = v1;
+    out[2 * m + 1] = v2;
+}
+
+}  // namespace fiode
+
+using namespace fiode;
+
+extern "C" size_t fiode_rhs_workspace_bytes(long long N) { return (size_t)N * NH * sizeof(float) + 256; }
+
+extern "C" int fiode_rhs_fwd(const fiode_dyn_weights* w, const float* h, const float* s, long long N,
+                             long long s_rows, long long s_group, float* f, float* ftilde, float* mu, int* n_iter,
+                             void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!w || !h || !s || !f || !ws) { set_error("fiode_rhs_fwd: null pointer"); return -1; }
+    if (N <= 0) { set_error("fiode_rhs_fwd: N=%lld", N); return -1; }
+    if (s_rows != 1 && (s_group <= 0 || s_rows * s_group < N)) {
+        set_error("fiode_rhs_fwd: s_rows=%lld s_group=%lld do not cover N=%lld", s_rows, s_group, N); return -1; }
+    if (w->max_iter < 1 || w->max_iter > kIt) { set_error("fiode_rhs_fwd: max_iter must be in [1,32]"); return -1; }
+    if (ws_bytes < fiode_rhs_workspace_bytes(N)) { set_error("fiode_rhs_fwd: workspace too small"); return -1; }
+    unsigned* notconv = reinterpret_cast<unsigned*>(ws);
+    float* ft = ftilde ? ftilde : reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + 256);
+    FIODE_CUDA(cudaMemsetAsync(notconv, 0, sizeof(unsigned), st));
+    FIODE_CUDA(cudaFuncSetAttribute(rhs_rows_kernel<kStore>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)kRowsSmemBytes));
+    RowsArgs a{};
+    a.w = *w; a.h = h; a.s = s; a.N = N; a.s_rows = s_rows; a.s_group = s_group; a.ft_out = ft; a.notconv = notconv;
+    const long long group = s_rows == 1 ? N : s_group;
+    const long long n_tiles = ((N + group - 1) / group) * ((group + TR - 1) / TR);
+    const int grid = (int)min((long long)2 * sm_count(), n_tiles);
+    rhs_rows_kernel<kStore><<<grid, RT, kRowsSmemBytes, st>>>(a);
+    rhs_finish_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(ft, h, N, *w, notconv, f, mu, n_iter);
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(2);
+    return 0;
+}
+
+extern "C" size_t fiode_certify_workspace_bytes(int M, int n_chunks) {
+    return (size_t)M * n_chunks * (2 * kIt + 1) * sizeof(unsigned);
+}
+
+extern "C" int fiode_certify_grid(const fiode_dyn_weights* w, const uint8_t* gridz, long long Ng, int T,
+                                  const float* lut, const float* s, const int* labels, int M, int batches,
+                                  float kappa, float* out, int* iters, void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!w || !gridz || !lut || !s || !labels || !out || !ws) { set_error("fiode_certify_grid: null pointer"); return -1; }
+    if (M <= 0 || Ng <= 0 || batches <= 0 || T <= 0) { set_error("fiode_certify_grid: bad sizes"); return -1; }
+    if (w->max_iter < 1 || w->max_iter > kIt) { set_error("fiode_certify_grid: max_iter must be in [1,32]"); return -1; }
+    // chunking of certify_lipschitz.py:100-102, 116-119
+    const long long chunk = Ng / batches;
+    if (chunk == 0) { set_error("fiode_certify_grid: grid has fewer rows (%lld) than batches (%d)", Ng, batches); return -1; }
+    const int n_chunks = batches + ((Ng % batches) != 0 ? 1 : 0);
+    if (ws_bytes < fiode_certify_workspace_bytes(M, n_chunks)) { set_error("fiode_certify_grid: workspace too small"); return -1; }
+    unsigned* cmax = reinterpret_cast<unsigned*>(ws);
+    unsigned* cnot = cmax + (size_t)M * n_chunks * 2 * kIt;
+    FIODE_CUDA(cudaMemsetAsync(ws, 0, fiode_certify_workspace_bytes(M, n_chunks), st));  // ord(0) < ord(any float)
+    FIODE_CUDA(cudaFuncSetAttribute(rhs_rows_kernel<kCertify>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)kRowsSmemBytes));
+    RowsArgs a{};
+    a.w = *w; a.s = s; a.gridz = gridz; a.lut = lut; a.T = T; a.Ng = Ng; a.chunk = chunk; a.n_chunks = n_chunks;
+    a.labels = labels; a.M = M; a.cmax = cmax; a.cnot = cnot;
+    const int slots = 2 * sm_count();
+    int P = slots / M; if (P < 1) P = 1;
+    const long long max_tiles = (chunk + TR - 1) / TR + 1;
+    if (P > max_tiles) P = (int)max_tiles;
+    a.P = P;
+    // certify_lipschitz.py:122-124: Lf = sqrt(N) * (sigma_1*alpha_1*exp(sigma_1*eta_ub)) + 1 ; perturb = (sqrt(2)*Lf)*dist
+    a.sa = (float)((double)w->sigma_1 * (double)w->alpha_1);
+    a.sqrtn = (float)sqrt((double)NH);
+    a.sqrt2 = (float)sqrt(2.0);
+    a.dist = (float)(sqrt((double)NH) / (double)T);
+    a.inv_T = (float)(1.0 / (double)T);
+    rhs_rows_kernel<kCertify><<<M * P, RT, kRowsSmemBytes, st>>>(a);
+    certify_finish_kernel<<<(M + 127) / 128, 128, 0, st>>>(cmax, cnot, M, n_chunks, w->max_iter, kappa, out, iters);
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(2);
+    return 0;
+}

@@ -1,0 +1,159 @@
+/* fiode_b200.h -- C ABI of libfiode_b200.so (hand-written CUDA for sm_100a).
+ *
+ * The reference (yjhuangcd/FI-ODE) has NO FFI on this path: it is eager PyTorch calling
+ * torchdiffeq.  The entry points below are therefore what a binding for the path *would* bind:
+ * one per replaceable seam of SURVEY.md section 8(b).  Each cites the reference interface it replaces
+ * (paths relative to the reference checkout).
+ *
+ * Conventions
+ *   - every function returns 0 on success, <0 on error; fiode_last_error() gives the message
+ *     (thread-local);
+ *   - all tensor arguments are raw DEVICE pointers to contiguous fp32 (unless stated), owned by
+ *     the caller; nothing is allocated behind the caller's back -- scratch comes from
+ *     *_workspace_bytes() + a caller-provided workspace;
+ *   - `stream` is a cudaStream_t passed as void*; all work is stream-ordered, no host sync;
+ *   - no exceptions, no torch types.
+ */
+#ifndef FIODE_B200_H
+#define FIODE_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* fiode_last_error(void);
+int fiode_version(void);
+/* number of kernels this library has launched since load / since the last reset (bench.py's
+ * gpu_launches claim is read from here) */
+long long fiode_launch_count(void);
+void fiode_reset_launch_count(void);
+
+/* ---- Cayley transform (weight preparation, cached per weight version by the host) ----------
+ * replaces libs/ortho_conv/layers.py:50-60 `cayley` as used by CayleyLinear.forward (:103-104)
+ * and CayleyConv.forward (:82).                                                              */
+
+/* Q = cayley(alpha * W / ||W||_F), W row-major (cout, cin) real.  Q row-major (cout, cin).
+ * alpha is read from device memory (1 float).                                               */
+size_t fiode_cayley_linear_workspace_bytes(int cout, int cin);
+int fiode_cayley_linear(const float* W, const float* alpha, int cout, int cin, float* Q,
+                        void* ws, size_t ws_bytes, void* stream);
+
+/* lazily-created CayleyConv.alpha = || wfft ||_F over the half spectrum (layers.py:80-81).
+ * w: (cout, cin, k, k); n = spatial size seen by the layer.  alpha_out: 1 float (device).     */
+int fiode_conv_alpha_init(const float* w, int cout, int cin, int k, int n, float* alpha_out,
+                          void* ws, size_t ws_bytes, void* stream);
+/* Per-frequency orthogonal mixing matrices of a CayleyConv (layers.py:74-82):
+ * Qf[phi] = cayley(alpha * wfft[phi] / ||wfft||), phi = u*(n/2+1)+v, stored as interleaved
+ * complex64 (F, cout, cin).  For k == 1 the spectrum is frequency independent and real
+ * (SURVEY App. C-1): then Qf is (cout, cin) real fp32.                                       */
+size_t fiode_cayley_conv_workspace_bytes(int cout, int cin, int k, int n);
+int fiode_cayley_conv(const float* w, const float* alpha, int cout, int cin, int k, int n,
+                      float* Qf, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- backbone forward ------------------------------------------------------------------------
+ * replaces models.py:23-35 Normalize + libs/ortho_conv/models_ortho.py:12-28 KWLarge_Concat
+ * (4 x [CayleyConv, GroupSort], Flatten, 2 x [CayleyLinear, GroupSort], fc) in eval mode.     */
+typedef struct fiode_backbone_weights {
+    const float* mu;   /* (3)  */
+    const float* std;  /* (3)  */
+    const float* Qf0;  /* (544, 32, 3) complex64 interleaved : conv 3->32 @32x32, k=3      */
+    const float* b0;   /* (32) */
+    const float* Q2;   /* (32, 128) real : stride-2 conv as 1x1 on space-to-depth, @16x16  */
+    const float* b2;   /* (32) */
+    const float* Qf4;  /* (144, 64, 32) complex64 : conv 32->64 @16x16, k=3                */
+    const float* b4;   /* (64) */
+    const float* Q6;   /* (64, 256) real : stride-2 conv as 1x1, @8x8                      */
+    const float* b6;   /* (64) */
+    const float* Q9;   /* (512, 4096) */
+    const float* b9;   /* (512) */
+    const float* Q11;  /* (512, 512) */
+    const float* b11;  /* (512) */
+    const float* Qfc;  /* (10, 512) */
+    const float* bfc;  /* (10) */
+} fiode_backbone_weights;
+size_t fiode_backbone_workspace_bytes(int B);
+/* x: (B,3,32,32) in [0,1]; s_out: (B,10) */
+int fiode_backbone_fwd(const fiode_backbone_weights* w, const float* x, int B, float* s_out,
+                       void* ws, size_t ws_bytes, void* stream);
+
+/* single layers (the reference's nn.Module.forward seams; used by the per-layer parity tests) */
+/* CayleyConv.forward, k=3 (layers.py:72-86): x (B,cin,n,n) -> y (B,cout,n,n), optional fused
+ * GroupSort (layers.py:127-131).  n in {8,16,32}.                                             */
+size_t fiode_cayley_conv_fwd_workspace_bytes(int B, int cin, int cout, int n);
+int fiode_cayley_conv_fwd(const float* x, const float* Qf, const float* bias, int B, int cin, int cout,
+                          int n, int group_sort, float* y, void* ws, size_t ws_bytes, void* stream);
+/* F.linear(X, Q, b) (layers.py:105): X (M,K), Q (N,K), y (M,N); optional fused GroupSort.     */
+int fiode_linear_fwd(const float* X, const float* Q, const float* bias, int M, int N, int K,
+                     int group_sort, float* y, void* stream);
+/* einops 'b c (w 2) (h 2) -> b (c 4) w h' (layers.py:45-48) */
+int fiode_space_to_depth(const float* x, int B, int C, int n, float* y, void* stream);
+int fiode_group_sort(const float* x, int B, int C, int inner, float* y, void* stream);
+
+/* ---- ODE right-hand side -----------------------------------------------------------------------
+ * replaces dynamics/classification.py:96-126 (_h_dot_raw, eval_dot, eval_dot_light) with
+ * barrier_projection/barrier_projection.py:217-269 (FastBarrierProjectionNoUpper.forward).
+ * Q* are the Cayley-transformed matrices (CayleyLinear.Q), row-major (out, in).              */
+typedef struct fiode_dyn_weights {
+    const float* Q1;  /* hidden_to_mlp.Q (128,10) */
+    const float* b1;  /* (128) */
+    const float* Qx;  /* U_x.Q (128,10) */
+    const float* bx;  /* (128) */
+    const float* Q2;  /* mlp_to_mlp.Q (128,128) */
+    const float* b2;  /* (128) */
+    const float* Q3;  /* mlp_to_hidden.Q (10,128) */
+    const float* b3;  /* (10) */
+    float alpha_1, alpha_2, sigma_1;
+    int scale_nominal;
+    int max_iter; /* 30 (classification.py:63) */
+    float tol;    /* 1e-4 */
+} fiode_dyn_weights;
+
+/* f = eval_dot_light(h, s): h (N,10); s (s_rows,10) with s_rows in {1, N} (row r uses
+ * s[r % s_rows] when s_rows == 1, else s[r / s_group] -- s_group rows of h share one s row,
+ * which is how compute_loss expands static_state, pl_modules.py:395-400).
+ * The projection's stop iteration is global over the N rows of the call, like the reference.
+ * Optional outputs (may be NULL): ftilde (N,10) pre-projection nominal, mu (N), n_iter (1 int). */
+size_t fiode_rhs_workspace_bytes(long long N);
+int fiode_rhs_fwd(const fiode_dyn_weights* w, const float* h, const float* s, long long N,
+                  long long s_rows, long long s_group, float* f, float* ftilde, float* mu,
+                  int* n_iter, void* ws, size_t ws_bytes, void* stream);
+
+/* autograd.Function seam: FastBarrierProjectionNoUpper(max_iter, tol).apply(lower, nominal)
+ * (barrier_projection.py:217-313).  forward -> v, mu; backward -> d_lower, d_nominal.          */
+int fiode_barrier_project_fwd(const float* lower, const float* upper /* NULL = no upper */,
+                              const float* nominal, long long N, int max_iter, float tol, float* v,
+                              float* mu, int* n_iter, void* ws, size_t ws_bytes, void* stream);
+int fiode_barrier_project_bwd(const float* grad_v, const float* v, const float* mu, const float* nominal,
+                              long long N, float* d_lower, float* d_nominal, void* stream);
+
+/* ---- device-resident adaptive dopri5 -----------------------------------------------------------
+ * replaces torchdiffeq==0.2.2 odeint(func, y0, t, rtol, atol, method='dopri5') as called at
+ * models.py:236-241 with func = IVP.h_dot -> dyn_fun.ode_forward (classification.py:128-132).
+ * One cooperative persistent kernel: 7 FSAL stages, batch-global RMS error norm, fp64 controller,
+ * accept/reject and dense output all on the device -- zero host syncs.                         */
+typedef struct fiode_solve_stats {
+    int n_accept, n_reject, nfe;
+    int status;        /* 0 ok; 1 'underflow in dt'; 2 'non-finite values in state'; 3 'max_num_steps exceeded' */
+    double t_final;    /* right edge of the last accepted step */
+    double last_dt;
+    int n_logged;      /* attempts recorded below (first FIODE_LOG_STEPS) */
+    int pad_;
+    double dts[64];
+    float ratios[64];
+} fiode_solve_stats;
+#define FIODE_LOG_STEPS 64
+
+size_t fiode_dopri5_workspace_bytes(int B);
+/* h0 (B,10); s (s_rows,10), s_rows in {1,B}; t: nt fp64 output times on the DEVICE (increasing);
+ * out (nt,B,10); stats: device struct; rows_per_cta 0 = auto.                                 */
+int fiode_dopri5_simplex(const fiode_dyn_weights* w, const float* h0, const float* s, int s_rows, int B,
+                         const double* t, int nt, double rtol, double atol, long long max_num_steps,
+                         float* out, fiode_solve_stats* stats, void* ws, size_t ws_bytes,
+                         int rows_per_cta, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FIODE_B200_H */
