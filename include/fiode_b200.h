@@ -19,16 +19,22 @@
 #include <stddef.h>
 #include <stdint.h>
 
+#if defined(__GNUC__)
+#define FIODE_API __attribute__((visibility("default")))
+#else
+#define FIODE_API
+#endif
+
 #ifdef __cplusplus
 extern "C" {
 #endif
 
-const char* fiode_last_error(void);
-int fiode_version(void);
+FIODE_API const char* fiode_last_error(void);
+FIODE_API int fiode_version(void);
 /* number of kernels this library has launched since load / since the last reset (bench.py's
  * gpu_launches claim is read from here) */
-long long fiode_launch_count(void);
-void fiode_reset_launch_count(void);
+FIODE_API long long fiode_launch_count(void);
+FIODE_API void fiode_reset_launch_count(void);
 
 /* ---- Cayley transform (weight preparation, cached per weight version by the host) ----------
  * replaces libs/ortho_conv/layers.py:50-60 `cayley` as used by CayleyLinear.forward (:103-104)
@@ -36,20 +42,20 @@ void fiode_reset_launch_count(void);
 
 /* Q = cayley(alpha * W / ||W||_F), W row-major (cout, cin) real.  Q row-major (cout, cin).
  * alpha is read from device memory (1 float).                                               */
-size_t fiode_cayley_linear_workspace_bytes(int cout, int cin);
-int fiode_cayley_linear(const float* W, const float* alpha, int cout, int cin, float* Q,
+FIODE_API size_t fiode_cayley_linear_workspace_bytes(int cout, int cin);
+FIODE_API int fiode_cayley_linear(const float* W, const float* alpha, int cout, int cin, float* Q,
                         void* ws, size_t ws_bytes, void* stream);
 
 /* lazily-created CayleyConv.alpha = || wfft ||_F over the half spectrum (layers.py:80-81).
  * w: (cout, cin, k, k); n = spatial size seen by the layer.  alpha_out: 1 float (device).     */
-int fiode_conv_alpha_init(const float* w, int cout, int cin, int k, int n, float* alpha_out,
+FIODE_API int fiode_conv_alpha_init(const float* w, int cout, int cin, int k, int n, float* alpha_out,
                           void* ws, size_t ws_bytes, void* stream);
 /* Per-frequency orthogonal mixing matrices of a CayleyConv (layers.py:74-82):
  * Qf[phi] = cayley(alpha * wfft[phi] / ||wfft||), phi = u*(n/2+1)+v, stored as interleaved
  * complex64 (F, cout, cin).  For k == 1 the spectrum is frequency independent and real
  * (SURVEY App. C-1): then Qf is (cout, cin) real fp32.                                       */
-size_t fiode_cayley_conv_workspace_bytes(int cout, int cin, int k, int n);
-int fiode_cayley_conv(const float* w, const float* alpha, int cout, int cin, int k, int n,
+FIODE_API size_t fiode_cayley_conv_workspace_bytes(int cout, int cin, int k, int n);
+FIODE_API int fiode_cayley_conv(const float* w, const float* alpha, int cout, int cin, int k, int n,
                       float* Qf, void* ws, size_t ws_bytes, void* stream);
 
 /* ---- backbone forward ------------------------------------------------------------------------
@@ -73,23 +79,29 @@ typedef struct fiode_backbone_weights {
     const float* Qfc;  /* (10, 512) */
     const float* bfc;  /* (10) */
 } fiode_backbone_weights;
-size_t fiode_backbone_workspace_bytes(int B);
+FIODE_API size_t fiode_backbone_workspace_bytes(int B);
 /* x: (B,3,32,32) in [0,1]; s_out: (B,10) */
-int fiode_backbone_fwd(const fiode_backbone_weights* w, const float* x, int B, float* s_out,
+FIODE_API int fiode_backbone_fwd(const fiode_backbone_weights* w, const float* x, int B, float* s_out,
                        void* ws, size_t ws_bytes, void* stream);
 
 /* single layers (the reference's nn.Module.forward seams; used by the per-layer parity tests) */
 /* CayleyConv.forward, k=3 (layers.py:72-86): x (B,cin,n,n) -> y (B,cout,n,n), optional fused
  * GroupSort (layers.py:127-131).  n in {8,16,32}.                                             */
-size_t fiode_cayley_conv_fwd_workspace_bytes(int B, int cin, int cout, int n);
-int fiode_cayley_conv_fwd(const float* x, const float* Qf, const float* bias, int B, int cin, int cout,
+FIODE_API size_t fiode_cayley_conv_fwd_workspace_bytes(int B, int cin, int cout, int n);
+FIODE_API int fiode_cayley_conv_fwd(const float* x, const float* Qf, const float* bias, int B, int cin, int cout,
                           int n, int group_sort, float* y, void* ws, size_t ws_bytes, void* stream);
 /* F.linear(X, Q, b) (layers.py:105): X (M,K), Q (N,K), y (M,N); optional fused GroupSort.     */
-int fiode_linear_fwd(const float* X, const float* Q, const float* bias, int M, int N, int K,
-                     int group_sort, float* y, void* stream);
+FIODE_API size_t fiode_linear_workspace_bytes(int M, int N, int K);
+FIODE_API int fiode_linear_fwd(const float* X, const float* Q, const float* bias, int M, int N, int K,
+                     int group_sort, float* y, void* ws, size_t ws_bytes, void* stream);
+/* stride-2 CayleyConv (StridedConv pre-hook layers.py:24-48 + CayleyConv.forward with k=1, whose
+ * spectrum is frequency independent and real): space-to-depth + real orthogonal
+ * 1x1 conv + bias (+GroupSort).  x (B,cin,n,n) -> y (B,cout,n/2,n/2); Q (cout, 4*cin).          */
+FIODE_API int fiode_conv1x1_s2d_fwd(const float* x, const float* Q, const float* bias, int B, int cin, int cout,
+                          int n, int group_sort, float* y, void* stream);
 /* einops 'b c (w 2) (h 2) -> b (c 4) w h' (layers.py:45-48) */
-int fiode_space_to_depth(const float* x, int B, int C, int n, float* y, void* stream);
-int fiode_group_sort(const float* x, int B, int C, int inner, float* y, void* stream);
+FIODE_API int fiode_space_to_depth(const float* x, int B, int C, int n, float* y, void* stream);
+FIODE_API int fiode_group_sort(const float* x, int B, int C, int inner, float* y, void* stream);
 
 /* ---- ODE right-hand side -----------------------------------------------------------------------
  * replaces dynamics/classification.py:96-126 (_h_dot_raw, eval_dot, eval_dot_light) with
@@ -115,18 +127,32 @@ typedef struct fiode_dyn_weights {
  * which is how compute_loss expands static_state, pl_modules.py:395-400).
  * The projection's stop iteration is global over the N rows of the call, like the reference.
  * Optional outputs (may be NULL): ftilde (N,10) pre-projection nominal, mu (N), n_iter (1 int). */
-size_t fiode_rhs_workspace_bytes(long long N);
-int fiode_rhs_fwd(const fiode_dyn_weights* w, const float* h, const float* s, long long N,
+FIODE_API size_t fiode_rhs_workspace_bytes(long long N);
+FIODE_API int fiode_rhs_fwd(const fiode_dyn_weights* w, const float* h, const float* s, long long N,
                   long long s_rows, long long s_group, float* f, float* ftilde, float* mu,
                   int* n_iter, void* ws, size_t ws_bytes, void* stream);
 
 /* autograd.Function seam: FastBarrierProjectionNoUpper(max_iter, tol).apply(lower, nominal)
  * (barrier_projection.py:217-313).  forward -> v, mu; backward -> d_lower, d_nominal.          */
-int fiode_barrier_project_fwd(const float* lower, const float* upper /* NULL = no upper */,
+FIODE_API int fiode_barrier_project_fwd(const float* lower, const float* upper /* NULL = no upper */,
                               const float* nominal, long long N, int max_iter, float tol, float* v,
                               float* mu, int* n_iter, void* ws, size_t ws_bytes, void* stream);
-int fiode_barrier_project_bwd(const float* grad_v, const float* v, const float* mu, const float* nominal,
+FIODE_API int fiode_barrier_project_bwd(const float* grad_v, const float* v, const float* mu, const float* nominal,
                               long long N, float* d_lower, float* d_nominal, void* stream);
+
+/* ---- Lipschitz grid certification ----------------------------------------------------------------
+ * replaces the per-image body of robustness/certify_lipschitz.py:104-143 (h_vdot :37-42, Lf_eta /
+ * perturb :122-124, tie mask :126-128, running maxima :131-134) for M images at once.
+ * gridz: (Ng,10) uint8 numerators z of the canonical label-0 grid eta = z/T (eval_utils.py:31-61);
+ * the per-label column swap (eval_utils.py:64-69) is applied on load.  lut: (T+1) floats,
+ * lut[z] = float32(z / T) (what grid.float() holds).  s: (M,10) static features; labels: (M).
+ * `batches` reproduces the reference's chunking (:100-102, :116-119) because the projection's stop
+ * iteration is global per chunk.  out: (M,2) = {max(h+perturb+kappa), max(h+kappa)};
+ * iters (may be NULL): (M, n_chunks) bisection iterations the reference would have run.        */
+FIODE_API size_t fiode_certify_workspace_bytes(int M, int n_chunks);
+FIODE_API int fiode_certify_grid(const fiode_dyn_weights* w, const uint8_t* gridz, long long Ng, int T,
+                       const float* lut, const float* s, const int* labels, int M, int batches,
+                       float kappa, float* out, int* iters, void* ws, size_t ws_bytes, void* stream);
 
 /* ---- device-resident adaptive dopri5 -----------------------------------------------------------
  * replaces torchdiffeq==0.2.2 odeint(func, y0, t, rtol, atol, method='dopri5') as called at
@@ -145,10 +171,10 @@ typedef struct fiode_solve_stats {
 } fiode_solve_stats;
 #define FIODE_LOG_STEPS 64
 
-size_t fiode_dopri5_workspace_bytes(int B);
+FIODE_API size_t fiode_dopri5_workspace_bytes(int B);
 /* h0 (B,10); s (s_rows,10), s_rows in {1,B}; t: nt fp64 output times on the DEVICE (increasing);
  * out (nt,B,10); stats: device struct; rows_per_cta 0 = auto.                                 */
-int fiode_dopri5_simplex(const fiode_dyn_weights* w, const float* h0, const float* s, int s_rows, int B,
+FIODE_API int fiode_dopri5_simplex(const fiode_dyn_weights* w, const float* h0, const float* s, int s_rows, int B,
                          const double* t, int nt, double rtol, double atol, long long max_num_steps,
                          float* out, fiode_solve_stats* stats, void* ws, size_t ws_bytes,
                          int rows_per_cta, void* stream);

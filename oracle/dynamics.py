@@ -88,7 +88,9 @@ def project_no_upper_backward(g, v, mu, lower, nominal):
     active = (v - nominal + mu) > 0            # lower bound active
     free = ~active
     m = free.sum(dim=-1, keepdim=True).to(g.dtype)
-    mean_free = (g * free).sum(dim=-1, keepdim=True) / m
+    # m == 0 (every slot on its lower bound): the reference's masks are empty, so the 1/0 is never
+    # scattered -> d_lower = g, d_nominal = 0 (barrier_projection.py:296-309)
+    mean_free = torch.where(m > 0, (g * free).sum(dim=-1, keepdim=True) / m.clamp(min=1), torch.zeros_like(m))
     d_nom = torch.where(free, g - mean_free, torch.zeros_like(g))
     d_low = torch.where(active, g - mean_free, torch.zeros_like(g))
     return d_low, d_nom

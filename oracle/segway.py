@@ -55,7 +55,19 @@ def barrier_hdot(x, ctrl, P):
 
 
 def grid_axes(sizes, r):
-    return [np.arange(-float(sizes[i]), float(sizes[i]), float(r[i])) for i in range(3)]
+    """np.arange(-sizes[i], sizes[i], r[i]) exactly as certify_segway.py:55-57 calls it, i.e. with
+    0-dim float32 torch tensors: numpy then takes start, start+step and the length
+    ceil((stop-start)/step) from float32 tensor arithmetic, and fills start + i*(next-start) in
+    float64 (PyArray_ArangeObj).  Returns float64 axes (cast to float32 by the caller)."""
+    axes = []
+    for i in range(3):
+        size, step = np.float32(sizes[i]), np.float32(r[i])
+        start, stop = np.float32(-size), size
+        nxt = np.float32(start + step)
+        length = int(np.ceil(np.float32(np.float32(stop - start) / step)))
+        delta = np.float64(nxt) - np.float64(start)
+        axes.append(np.float64(start) + np.arange(length, dtype=np.float64) * delta)
+    return axes
 
 
 def grid_uniform_3d(sizes, r):

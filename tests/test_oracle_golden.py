@@ -1,0 +1,195 @@
+"""Pin the oracle (CPU restatement) against golden vectors produced by the reference's OWN modules
+(tests/golden/make_golden.py).  CPU only; these are the tests that make the oracle trustworthy."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import layers as ol, dynamics as od, certify as oc, sampler as osamp, segway as oseg, dopri5 as odp
+from tests import fixtures as fx
+
+PM, DYN = fx.PM, fx.DYN
+
+
+def test_cayley_known_answers():
+    g = fx.load_golden('layers.pt')['cayley']
+    for name, c in g.items():
+        Q = ol.cayley(c['W'])
+        assert torch.equal(Q, c['Q']), name                      # same torch ops on the same CPU
+        # orthogonality invariant (FFT Convolutions.ipynb cell 61 / SURVEY section 4)
+        Qm = Q if Q.dim() == 3 else Q[None]
+        small = min(Qm.shape[-2:])
+        gram = Qm.conj().transpose(1, 2) @ Qm if Qm.shape[-2] >= Qm.shape[-1] else Qm @ Qm.conj().transpose(1, 2)
+        assert (gram - torch.eye(small)).abs().max() < 5e-5, name
+
+
+def test_backbone_layers_match_reference(sd):
+    g = fx.load_golden('layers.pt')
+    x, acts = g['x'], g['acts']
+    gp = lambda k: sd[PM + k]
+    h = (x - gp('0.mu')) / gp('0.std')
+    assert torch.equal(h, acts['normalize'])
+    for idx, stride, _n in ol.CONV_LAYERS:
+        p = f'1.model.{idx}.'
+        h = ol.cayley_conv(h, gp(p + 'weight'), gp(p + 'bias'), gp(p + 'alpha'), stride)
+        torch.testing.assert_close(h, acts[f'model.{idx}'], rtol=0, atol=1e-6)
+        h = ol.group_sort(h)
+        torch.testing.assert_close(h, acts[f'model.{idx + 1}'], rtol=0, atol=1e-6)
+    s8 = ol.backbone_forward(fx.synth_images(8), sd, PM)
+    torch.testing.assert_close(s8, g['s8'], rtol=0, atol=2e-6)
+
+
+def test_conv_alpha_init_matches_lazy_alpha(sd):
+    for idx, _stride, n in ol.CONV_LAYERS:
+        a = ol.conv_alpha_init(sd[PM + f'1.model.{idx}.weight'], n)
+        assert abs(a - float(sd[PM + f'1.model.{idx}.alpha'])) <= 1e-6 * a
+
+
+@pytest.mark.parametrize('sn', [False, True])
+def test_rhs_matches_reference(sd, sn):
+    g = fx.load_golden('rhs.pt')[f'sn{int(sn)}']
+    cfg = fx.dyn_cfg(scale_nominal=sn)
+    Q = od.dyn_Q(sd, DYN)
+    assert torch.equal(od.h_dot_raw(g['h'], g['s_rows'], sd, Q, DYN), g['raw'])
+    assert torch.equal(od.eval_dot(g['h'], g['s_rows'], sd, cfg, Q, DYN), g['f_rows'])
+    assert torch.equal(od.eval_dot(g['h'], g['s_one'], sd, cfg, Q, DYN), g['f_one'])
+    f = g['f_rows']
+    assert f.sum(1).abs().max() < 1e-4 + 1e-5          # invariant: sum_j f_j = 0 up to the stop tol
+    lower = -cfg['alpha_1'] * (torch.exp(cfg['sigma_1'] * g['h']) - 1)
+    assert (f >= lower - 1e-6).all()
+
+
+def test_projection_forward_backward():
+    g = fx.load_golden('rhs.pt')['proj']
+    v, mu, n_iter = od.project_no_upper(g['lower'], g['nominal'])
+    assert torch.equal(v, g['v']) and 1 <= n_iter <= 30
+    d_low, d_nom = od.project_no_upper_backward(g['gout'], v, mu, g['lower'], g['nominal'])
+    torch.testing.assert_close(d_low, g['d_lower'], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(d_nom, g['d_nominal'], rtol=1e-5, atol=1e-6)
+    v_up, _, _ = od.project_with_upper(g['lower'], g['upper'], g['nominal'])
+    assert torch.equal(v_up, g['v_upper'])
+
+
+@pytest.mark.parametrize('case', ['c2_b256_tol1e-3', 'c5_b64_tol1e-5', 'c5_b64_tol1e-2', 'stress_a'])
+def test_ivp_matches_reference(sd, case):
+    c = fx.load_golden('ivp.pt')[case]
+    cfg = fx.dyn_cfg(**c['kw'])
+    y, s, st = od.ivp_forward(fx.synth_images(c['B']), sd, cfg, t_max=c['t_max'], tol=c['tol'], return_stats=True)
+    torch.testing.assert_close(s, c['s'], rtol=0, atol=2e-6)
+    want = c['stats']
+    assert (st.n_accept, st.n_reject, st.nfe) == (want['n_accept'], want['n_reject'], want['nfe'])
+    torch.testing.assert_close(y, c['y'], rtol=1e-4, atol=1e-6)
+    assert (y.sum(1) - 1).abs().max() < 1e-3            # trajectories stay on the simplex up to tol
+
+
+def test_dopri5_against_scipy_rk45():
+    """Independent anchor for the restated solver: linear test problem vs closed form, and the
+    accepted-step count vs scipy's RK45 (same tableau, different controller) order of magnitude."""
+    A = torch.tensor([[-0.5, 2.0], [-2.0, -0.5]])
+    f = lambda t, y: y @ A.T
+    y0 = torch.tensor([[1.0, 0.0]])
+    sol, st = odp.odeint_dopri5(f, y0, torch.tensor([0.0, 1.0, 2.5]), 1e-6, 1e-8, return_stats=True)
+    for i, t in enumerate((0.0, 1.0, 2.5)):
+        exact = math.exp(-0.5 * t) * np.array([math.cos(2 * t), -math.sin(2 * t)])
+        assert np.abs(sol[i, 0].numpy() - exact).max() < 2e-5
+    assert st.nfe == 2 + 6 * (st.n_accept + st.n_reject)
+    from scipy.integrate import solve_ivp
+    r = solve_ivp(lambda t, y: A.numpy().astype(np.float64) @ y, (0, 2.5), [1.0, 0.0], rtol=1e-6, atol=1e-8)
+    assert 0.5 < st.n_accept / (len(r.t) - 1) < 2.0
+
+
+def test_dopri5_error_messages():
+    with pytest.raises(AssertionError, match='underflow in dt'):
+        odp.odeint_dopri5(lambda t, y: y * float('inf'), torch.ones(3), torch.tensor([0., 1.]), 1e-3, 1e-3)
+
+
+def test_samplers_match_reference():
+    g = fx.load_golden('fi.pt')
+    for name, c in g.items():
+        parts = []
+        for kind, var in zip(c['kinds'], c['variates']):
+            if var is None:
+                continue
+            if kind == 'UniformSimplexSampling':
+                parts.append(osamp.uniform_simplex(var))
+            elif kind == 'CorrectConeSampling':
+                parts.append(osamp.correct_cone(var, c['y']))
+            else:
+                parts.append(osamp.decision_boundary(var, c['y']))
+        h = osamp.composite(parts, c['B'])
+        assert torch.equal(h, c['h']), name
+        assert osamp.split_counts(c['S'], c['mix']) == c['counts']
+
+
+@pytest.mark.parametrize('name', ['uniform_sn1', 'mixed_sn0', 'boundary_sn0'])
+def test_fi_loss_matches_reference(sd, name):
+    c = fx.load_golden('fi.pt')[name]
+    cfg = fx.dyn_cfg(scale_nominal=c['scale_nominal'])
+    params = {k: v.clone().requires_grad_(True) for k, v in sd.items() if v.is_floating_point()}
+    s = ol.backbone_forward(c['x'], params, PM)
+    S = c['S']
+    s_rows = s[:, None].expand(-1, S, -1).flatten(0, 1)
+    y_rows = c['y'][:, None].expand(-1, S).flatten(0, 1)
+    loss, V, Vdot, eff = od.fi_loss(c['h'], s_rows, y_rows, params, cfg, kappa=2.0, prefix=DYN)
+    torch.testing.assert_close(loss.detach(), c['loss'], rtol=1e-5, atol=1e-6)
+    assert eff == int(c['logged']['effective_batch_size'])
+    loss.backward()
+    for k, gref in c['grads'].items():
+        if k.endswith('alpha') and 'param_map.1.model' in k and int(k.split('.')[-2]) in (0, 2, 4, 6):
+            continue    # lazy conv alpha: leaf in the oracle, re-wrapped tensor in the reference (App. B-1)
+        torch.testing.assert_close(params[k].grad, gref, rtol=2e-3, atol=2e-6, msg=lambda m, k=k: f'{k}: {m}')
+    with torch.no_grad():
+        f = od.eval_dot(c['h'], s_rows.detach(), sd, cfg, None, DYN)
+        mac = od.mean_active_constraints(c['h'], f, cfg)
+    assert abs(float(mac) - c['logged']['mean_active_constraints']) < 1e-6
+
+
+def test_grid_counts_and_sets():
+    g = fx.load_golden('certify.pt')
+    for (n, T), want in g['counts'].items():
+        assert oc.count_boundary_points(n, T) == want, (n, T)
+    assert g['counts'][(10, 40)] == 41320837
+    z = oc.boundary_grid_numerators(4, 8)
+    assert sorted(map(tuple, z.tolist())) == sorted(map(tuple, g['grid_4_8'].tolist()))
+    z10 = oc.boundary_grid_numerators(10, 10)
+    assert z10.shape[0] == g['counts'][(10, 10)]
+    assert np.array_equal(np.unique(z10.astype(np.uint8), axis=0), g['grid_10_10_sorted'].numpy())
+
+
+@pytest.mark.parametrize('key', ['T10_sn0_shift0.0', 'T10_sn1_shift0.0', 'T20_sn0_shift14.0', 'T20_sn0_shift1.5'])
+def test_certify_matches_reference(sd, key):
+    c = fx.load_golden('certify.pt')[key]
+    cfg = fx.dyn_cfg(scale_nominal=c['scale_nominal'])
+    sd2 = dict(sd)
+    if c['shift']:
+        e = torch.zeros(10); e[3] = 1.0
+        sd2[DYN + 'mlp_to_hidden.bias'] = sd[DYN + 'mlp_to_hidden.bias'] + c['shift'] * (e - 0.1)
+    z = oc.boundary_grid_numerators(10, c['T'])
+    Q = od.dyn_Q(sd2, DYN)
+    M = 3 if c['T'] == 20 else c['labels'].shape[0]
+    idx = [0, 3, 5][:M] if c['T'] == 20 else list(range(M))
+    for m in idx:
+        label = int(c['labels'][m])
+        G = oc.grid_for_label(z, c['T'], label)
+        v1, v2 = oc.certify_image(G, c['s'][m:m + 1], label, sd2, cfg, eps=c['eps'], T=c['T'],
+                                  batches=c['batches'], prefix=DYN, Q=Q)
+        # row order differs from the reference's DP order, so the chunk-global bisection stop differs:
+        # results agree to the projection tolerance, verdicts agree outside it
+        assert abs(v1 - float(c['out'][m, 0])) < 2e-4, (m, v1, c['out'][m])
+        assert abs(v2 - float(c['out'][m, 1])) < 2e-4
+        if abs(float(c['out'][m, 0])) > 2e-4:
+            assert (v1 < 0) == (float(c['out'][m, 0]) < 0)
+
+
+def test_segway_matches_reference():
+    g = fx.load_golden('segway.pt')
+    r = [g['r']] * 3
+    eta, val, mask = oseg.certify_grid(g['ctrl'], g['P'], g['sizes'].tolist(), r, level=g['level'])
+    assert int(mask.sum()) == g['mask_count']
+    assert torch.equal(mask.nonzero()[:, 0].int(), g['mask_idx'])
+    torch.testing.assert_close(val, g['val'], rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(oseg.closed_loop(eta, g['ctrl']), g['f'], rtol=1e-6, atol=1e-6)
+    xs, us = oseg.simulate(g['x0'], g['ctrl'], g['ts'])
+    torch.testing.assert_close(xs, g['xs'], rtol=1e-6, atol=1e-7)
+    torch.testing.assert_close(us, g['us'], rtol=1e-6, atol=1e-7)
