@@ -12,27 +12,70 @@ LIB_PATH = _HERE / 'libfiode_b200.so'
 
 _lib = None
 
+P, I, LL, F32, F64, SZ = C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_double, C.c_size_t
+
 
 class FiodeError(RuntimeError):
     pass
 
 
 class DynWeights(C.Structure):
-    _fields_ = [('Q1', C.c_void_p), ('b1', C.c_void_p), ('Qx', C.c_void_p), ('bx', C.c_void_p),
-                ('Q2', C.c_void_p), ('b2', C.c_void_p), ('Q3', C.c_void_p), ('b3', C.c_void_p),
-                ('alpha_1', C.c_float), ('alpha_2', C.c_float), ('sigma_1', C.c_float),
-                ('scale_nominal', C.c_int), ('max_iter', C.c_int), ('tol', C.c_float)]
+    _fields_ = [('Q1', P), ('b1', P), ('Qx', P), ('bx', P), ('Q2', P), ('b2', P), ('Q3', P), ('b3', P),
+                ('alpha_1', F32), ('alpha_2', F32), ('sigma_1', F32),
+                ('scale_nominal', I), ('max_iter', I), ('tol', F32)]
 
 
 class BackboneWeights(C.Structure):
-    _fields_ = [(n, C.c_void_p) for n in ('mu', 'std', 'Qf0', 'b0', 'Q2', 'b2', 'Qf4', 'b4', 'Q6', 'b6',
-                                          'Q9', 'b9', 'Q11', 'b11', 'Qfc', 'bfc')]
+    _fields_ = [(n, P) for n in ('mu', 'std', 'Qf0', 'b0', 'Q2', 'b2', 'Qf4', 'b4', 'Q6', 'b6',
+                                 'Q9', 'b9', 'Q11', 'b11', 'Qfc', 'bfc')]
 
 
 class SolveStats(C.Structure):
-    _fields_ = [('n_accept', C.c_int), ('n_reject', C.c_int), ('nfe', C.c_int), ('status', C.c_int),
-                ('t_final', C.c_double), ('last_dt', C.c_double), ('n_logged', C.c_int), ('pad_', C.c_int),
-                ('dts', C.c_double * 64), ('ratios', C.c_float * 64)]
+    _fields_ = [('n_accept', I), ('n_reject', I), ('nfe', I), ('status', I),
+                ('t_final', F64), ('last_dt', F64), ('n_logged', I), ('pad_', I),
+                ('dts', F64 * 64), ('ratios', F32 * 64)]
+
+
+class SegwayWeights(C.Structure):
+    _fields_ = [('W0', P), ('b0', P), ('W1', P), ('b1', P), ('W2', P), ('b2', P), ('P', P)]
+
+
+# name -> (restype, argtypes): every entry point of include/fiode_b200.h
+SIGNATURES = {
+    'fiode_last_error': (C.c_char_p, []),
+    'fiode_version': (I, []),
+    'fiode_launch_count': (LL, []),
+    'fiode_reset_launch_count': (None, []),
+    'fiode_cayley_linear_workspace_bytes': (SZ, [I, I]),
+    'fiode_cayley_linear': (I, [P, P, I, I, P, P, SZ, P]),
+    'fiode_conv_alpha_init': (I, [P, I, I, I, I, P, P, SZ, P]),
+    'fiode_cayley_conv_workspace_bytes': (SZ, [I, I, I, I]),
+    'fiode_cayley_conv': (I, [P, P, I, I, I, I, P, P, SZ, P]),
+    'fiode_backbone_workspace_bytes': (SZ, [I]),
+    'fiode_backbone_fwd': (I, [C.POINTER(BackboneWeights), P, I, P, P, SZ, P]),
+    'fiode_cayley_conv_fwd_workspace_bytes': (SZ, [I, I, I, I]),
+    'fiode_cayley_conv_fwd': (I, [P, P, P, I, I, I, I, I, P, P, SZ, P]),
+    'fiode_linear_workspace_bytes': (SZ, [I, I, I]),
+    'fiode_linear_fwd': (I, [P, P, P, I, I, I, I, P, P, SZ, P]),
+    'fiode_conv1x1_s2d_fwd': (I, [P, P, P, I, I, I, I, I, P, P]),
+    'fiode_space_to_depth': (I, [P, I, I, I, P, P]),
+    'fiode_group_sort': (I, [P, I, I, I, P, P]),
+    'fiode_rhs_workspace_bytes': (SZ, [LL]),
+    'fiode_rhs_fwd': (I, [C.POINTER(DynWeights), P, P, LL, LL, LL, P, P, P, P, P, SZ, P]),
+    'fiode_barrier_project_fwd': (I, [P, P, P, LL, I, F32, P, P, P, P, SZ, P]),
+    'fiode_barrier_project_bwd': (I, [P, P, P, P, LL, P, P, P]),
+    'fiode_certify_workspace_bytes': (SZ, [I, I]),
+    'fiode_certify_grid': (I, [C.POINTER(DynWeights), P, LL, I, P, P, P, I, I, F32, P, P, P, SZ, P]),
+    'fiode_dopri5_workspace_bytes': (SZ, [I]),
+    'fiode_dopri5_simplex': (I, [C.POINTER(DynWeights), P, P, I, I, P, I, F64, F64, LL, P, P, P, SZ, I, P]),
+}
+
+
+def declared_symbols():
+    """Entry points named in include/fiode_b200.h (parsed, so the header stays the source of truth)."""
+    import re
+    hdr = (_HERE.parent / 'include' / 'fiode_b200.h').read_text()
+    return sorted(set(re.findall(r'\b(fiode_[a-z0-9_]+)\s*\(', hdr)))
 
 
 def lib() -> C.CDLL:
@@ -42,17 +85,13 @@ def lib() -> C.CDLL:
         if not LIB_PATH.exists():
             raise FiodeError(f'{LIB_PATH} is missing: run `python -m fiode_b200.build` '
                              '(there is no CPU / PyTorch fallback for the fiode_b200 hot path)')
-        _lib = C.CDLL(str(LIB_PATH))
-        _lib.fiode_last_error.restype = C.c_char_p
-        _lib.fiode_launch_count.restype = C.c_longlong
-        for name in dir(_lib):
-            pass
-        for fn in SIZE_T_FUNCS:
-            getattr(_lib, fn).restype = C.c_size_t
+        L = C.CDLL(str(LIB_PATH))
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
     return _lib
-
-
-SIZE_T_FUNCS = ()
 
 
 def check(rc: int, what: str = ''):
@@ -65,7 +104,9 @@ def ptr(t):
     """Raw device pointer of a contiguous CUDA tensor (or None)."""
     if t is None:
         return None
-    assert t.is_cuda and t.is_contiguous(), 'fiode_b200 needs contiguous CUDA tensors'
+    if not t.is_cuda:
+        raise FiodeError('fiode_b200 runs on CUDA tensors only (no CPU fallback); got a CPU tensor')
+    assert t.is_contiguous(), 'fiode_b200 needs contiguous tensors'
     return C.c_void_p(t.data_ptr())
 
 

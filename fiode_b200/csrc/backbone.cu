@@ -1,0 +1,98 @@
+// fiode_b200/csrc/backbone.cu -- forward of the static-feature backbone s = param_map(x).
+//
+// Replaces models.py:17-35 (Normalize + make_ortho_KWLarge_Concat) and
+// libs/ortho_conv/models_ortho.py:12-28 (KWLarge_Concat: 4 x [CayleyConv, GroupSort], Flatten,
+// 2 x [CayleyLinear, GroupSort], fc) in eval mode, with every Cayley matrix prepared once per
+// weight version (cayley.cu).  The two stride-2 layers are real 1x1 convolutions on the
+// space-to-depth tensor and run without any FFT.
+//
+// The batch is processed in slabs so that the per-layer activations of a slab stay L2-resident
+// (126 MB) between the producing and the consuming kernel.
+#include "common.cuh"
+
+namespace fiode {
+int launch_rfft2(const float* x, int n_img, int C, int n, const float* mu, const float* sd, float2* Xf, cudaStream_t st);
+int launch_irfft2(const float2* Yf, int B, int C, int n, const float* bias, int gs, float* y, cudaStream_t st);
+int launch_mix(const float2* Xf, const float2* Qf, int B, int F, int cout, int cin, float2* Yf, cudaStream_t st);
+int launch_conv1x1(const float* x, const float* Q, const float* bias, int B, int cin, int cout, int n, int gs, float* y,
+                   cudaStream_t st);
+int gemm_nt(const float* A, int lda, const float* Bm, int ldb, int M, int N, int K, const float* bias, float alpha,
+            int group_sort, float* y, int ldy, float* ws, size_t ws_bytes, cudaStream_t st);
+size_t gemm_nt_workspace(int M, int N, int K);
+
+constexpr int kSlab = 128;   // images per slab: ~0.55 MB of activations per image -> ~70 MB per slab
+
+struct SlabLayout {
+    size_t xf0, yf0, a0, a2, xf4, yf4, a4, a6, l9, l11, gws, total, gws_bytes;
+};
+static size_t al(size_t x) { return (x + 255) & ~(size_t)255; }
+static SlabLayout slab_layout(int S) {
+    SlabLayout L; size_t o = 0;
+    auto take = [&](size_t bytes) { size_t r = o; o += al(bytes); return r; };
+    L.xf0 = take((size_t)S * 3 * 544 * 8);
+    L.yf0 = take((size_t)S * 32 * 544 * 8);
+    L.a0 = take((size_t)S * 32 * 1024 * 4);
+    L.a2 = take((size_t)S * 32 * 256 * 4);
+    L.xf4 = take((size_t)S * 32 * 144 * 8);
+    L.yf4 = take((size_t)S * 64 * 144 * 8);
+    L.a4 = take((size_t)S * 64 * 256 * 4);
+    L.a6 = take((size_t)S * 4096 * 4);
+    L.l9 = take((size_t)S * 512 * 4);
+    L.l11 = take((size_t)S * 512 * 4);
+    L.gws_bytes = gemm_nt_workspace(S, 512, 4096);
+    const size_t g2 = gemm_nt_workspace(S, 512, 512), g3 = gemm_nt_workspace(S, 10, 512);
+    if (g2 > L.gws_bytes) L.gws_bytes = g2;
+    if (g3 > L.gws_bytes) L.gws_bytes = g3;
+    L.gws = take(L.gws_bytes);
+    L.total = o;
+    return L;
+}
+}  // namespace fiode
+
+using namespace fiode;
+
+extern "C" size_t fiode_backbone_workspace_bytes(int B) {
+    const int S = B < kSlab ? B : kSlab;
+    return slab_layout(S).total;
+}
+
+extern "C" int fiode_backbone_fwd(const fiode_backbone_weights* w, const float* x, int B, float* s_out, void* ws,
+                                  size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!w || !x || !s_out || !ws) { set_error("fiode_backbone_fwd: null pointer"); return -1; }
+    if (B <= 0) { set_error("fiode_backbone_fwd: B=%d", B); return -1; }
+    const int S = B < kSlab ? B : kSlab;
+    const SlabLayout L = slab_layout(S);
+    if (ws_bytes < L.total) { set_error("fiode_backbone_fwd: workspace too small (%zu < %zu)", ws_bytes, L.total); return -1; }
+    char* base = reinterpret_cast<char*>(ws);
+    float2* xf0 = (float2*)(base + L.xf0); float2* yf0 = (float2*)(base + L.yf0);
+    float* a0 = (float*)(base + L.a0); float* a2 = (float*)(base + L.a2);
+    float2* xf4 = (float2*)(base + L.xf4); float2* yf4 = (float2*)(base + L.yf4);
+    float* a4 = (float*)(base + L.a4); float* a6 = (float*)(base + L.a6);
+    float* l9 = (float*)(base + L.l9); float* l11 = (float*)(base + L.l11);
+    float* gws = (float*)(base + L.gws);
+    int rc;
+    for (int b0 = 0; b0 < B; b0 += S) {
+        const int nb = (B - b0) < S ? (B - b0) : S;
+        const float* xs = x + (size_t)b0 * 3 * 1024;
+        // model.0: CayleyConv(3, 32, 3) @32x32 + GroupSort (Normalize fused into the FFT load)
+        if ((rc = launch_rfft2(xs, nb * 3, 3, 32, w->mu, w->std, xf0, st))) return rc;
+        if ((rc = launch_mix(xf0, (const float2*)w->Qf0, nb, 544, 32, 3, yf0, st))) return rc;
+        if ((rc = launch_irfft2(yf0, nb, 32, 32, w->b0, 1, a0, st))) return rc;
+        // model.2: CayleyConv(32, 32, 3, stride=2) == orthogonal 1x1 on space-to-depth + GroupSort
+        if ((rc = launch_conv1x1(a0, w->Q2, w->b2, nb, 32, 32, 32, 1, a2, st))) return rc;
+        // model.4: CayleyConv(32, 64, 3) @16x16 + GroupSort
+        if ((rc = launch_rfft2(a2, nb * 32, 32, 16, nullptr, nullptr, xf4, st))) return rc;
+        if ((rc = launch_mix(xf4, (const float2*)w->Qf4, nb, 144, 64, 32, yf4, st))) return rc;
+        if ((rc = launch_irfft2(yf4, nb, 64, 16, w->b4, 1, a4, st))) return rc;
+        // model.6: CayleyConv(64, 64, 3, stride=2) + GroupSort -> (nb, 64, 8, 8) == Flatten 4096
+        if ((rc = launch_conv1x1(a4, w->Q6, w->b6, nb, 64, 64, 16, 1, a6, st))) return rc;
+        // model.9 / model.11 / fc
+        if ((rc = gemm_nt(a6, 4096, w->Q9, 4096, nb, 512, 4096, w->b9, 1.f, 1, l9, 512, gws, L.gws_bytes, st))) return rc;
+        if ((rc = gemm_nt(l9, 512, w->Q11, 512, nb, 512, 512, w->b11, 1.f, 1, l11, 512, gws, L.gws_bytes, st))) return rc;
+        if ((rc = gemm_nt(l11, 512, w->Qfc, 512, nb, 10, 512, w->bfc, 1.f, 0, s_out + (size_t)b0 * 10, 10, gws,
+                          L.gws_bytes, st))) return rc;
+    }
+    FIODE_CUDA(cudaGetLastError());
+    return 0;
+}

@@ -1,0 +1,376 @@
+// fiode_b200/csrc/cayley.cu -- Cayley transform of the layer weights (weight preparation, run once
+// per weight version and cached by the host; the reference redoes it on EVERY forward).
+//
+// Replaces libs/ortho_conv/layers.py:50-60 `cayley`, as used by
+//   * CayleyLinear.forward :103-104   Q = cayley(alpha * W / ||W||_F)           (real, any shape)
+//   * CayleyConv.forward   :74-82     Q[phi] = cayley(alpha * wfft[phi] / ||wfft||_F) per frequency
+// and the lazily created CayleyConv.alpha = ||wfft||_F (:80-81).
+//
+//   W (R x n after the plain transpose of :54-55 when cin > cout), U = W[:n], V = W[n:]
+//   A = U - U^H + V^H V ;  M = (I + A)^-1 ;  Q = [ M (I - A) ; -2 V M ]
+//
+// I + A has the positive-definite Hermitian part I + V^H V, so Gauss-Jordan elimination needs no
+// pivoting.  Real path: GEMMs (linear.cu) + a ping-pong Gauss-Jordan kernel (cooperative grid for
+// n = 512, one CTA for n <= 128).  Complex path: one CTA per frequency, everything in shared
+// memory; the weight spectrum is the direct 9-tap sum of SURVEY App. C-1 (no FFT of the weights).
+#include "common.cuh"
+#include "fft.cuh"
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
+
+namespace fiode {
+
+int gemm_nt(const float* A, int lda, const float* Bm, int ldb, int M, int N, int K, const float* bias, float alpha,
+            int group_sort, float* y, int ldy, float* ws, size_t ws_bytes, cudaStream_t st);
+size_t gemm_nt_workspace(int M, int N, int K);
+
+// ---- Frobenius norm, deterministic two-stage --------------------------------------------------
+constexpr int kNormBlocks = 128;
+__global__ void __launch_bounds__(256) sumsq_partial_kernel(const float* __restrict__ x, size_t n,
+                                                            double* __restrict__ part) {
+    __shared__ double sh[8];
+    double acc = 0;
+    for (size_t e = blockIdx.x * 256 + threadIdx.x; e < n; e += (size_t)gridDim.x * 256) {
+        const double v = x[e];
+        acc += v * v;
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0;
+        for (int i = 0; i < 8; ++i) s += sh[i];
+        part[blockIdx.x] = s;
+    }
+}
+// scale[0] = alpha / (sqrt(sum part) * mult) ; scale[1] = sqrt(sum part) * mult
+__global__ void norm_finalize_kernel(const double* __restrict__ part, int np, const float* __restrict__ alpha,
+                                     float mult, float* __restrict__ scale) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        double s = 0;
+        for (int i = 0; i < np; ++i) s += part[i];
+        const float nrm = (float)sqrt(s) * mult;
+        scale[1] = nrm;
+        scale[0] = alpha ? alpha[0] / nrm : 1.f / nrm;
+    }
+}
+
+// Ws (R x n) = scale * (tr ? W^T : W) ; Vt (n x (R-n)) = transpose of Ws[n:]
+__global__ void cayley_prep1_kernel(const float* __restrict__ W, int cout, int cin, int tr,
+                                    const float* __restrict__ scale, float* __restrict__ Ws,
+                                    float* __restrict__ Vt) {
+    const int R = tr ? cin : cout, n = tr ? cout : cin;
+    const float sc = scale[0];
+    const size_t total = (size_t)R * n;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const int r = (int)(e / n), c = (int)(e - (size_t)r * n);
+        const float v = sc * (tr ? W[(size_t)c * cin + r] : W[(size_t)r * cin + c]);
+        Ws[e] = v;
+        if (r >= n) Vt[(size_t)c * (R - n) + (r - n)] = v;
+    }
+}
+// IpA = I + U - U^T + G ; ImAT = (I - A)^T = I - (U^T - U + G^T)
+__global__ void cayley_prep2_kernel(const float* __restrict__ Ws, const float* __restrict__ G, int n, int has_v,
+                                    float* __restrict__ IpA, float* __restrict__ ImAT) {
+    const int total = n * n;
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+        const int i = e / n, j = e - i * n;
+        const float uij = Ws[i * n + j], uji = Ws[j * n + i];
+        const float gij = has_v ? G[i * n + j] : 0.f, gji = has_v ? G[j * n + i] : 0.f;
+        const float d = (i == j) ? 1.f : 0.f;
+        IpA[e] = d + ((uij - uji) + gij);
+        ImAT[e] = d - ((uji - uij) + gji);
+    }
+}
+__global__ void transpose_kernel(const float* __restrict__ x, int rows, int cols, float* __restrict__ y) {
+    __shared__ float tile[32][33];
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int r = r0 + i, c = c0 + threadIdx.x;
+        if (r < rows && c < cols) tile[i][threadIdx.x] = x[(size_t)r * cols + c];
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int c = c0 + i, r = r0 + threadIdx.x;
+        if (r < rows && c < cols) y[(size_t)c * rows + r] = tile[threadIdx.x][i];
+    }
+}
+
+// Ping-pong Gauss-Jordan inversion without pivoting: after n steps the inverse is in (n even ? X : Y).
+// Cooperative launch (grid.sync per pivot).  out[i][j] depends on in[i][j], in[i][k], in[k][j], in[k][k].
+__global__ void __launch_bounds__(256) gj_inverse_kernel(float* X, float* Y, int n) {
+    cg::grid_group grid = cg::this_grid();
+    const int total = n * n;
+    const int tid = blockIdx.x * blockDim.x + threadIdx.x, nth = gridDim.x * blockDim.x;
+    for (int k = 0; k < n; ++k) {
+        const float* in = (k & 1) ? Y : X;
+        float* out = (k & 1) ? X : Y;
+        const float ip = 1.f / __ldcg(in + k * n + k);
+        for (int e = tid; e < total; e += nth) {
+            const int i = e / n, j = e - i * n;
+            float v;
+            if (i == k) v = (j == k) ? ip : __ldcg(in + e) * ip;
+            else {
+                const float f = __ldcg(in + i * n + k);
+                v = (j == k) ? -f * ip : fmaf(-f, __ldcg(in + k * n + j) * ip, __ldcg(in + e));
+            }
+            out[e] = v;
+        }
+        grid.sync();
+    }
+}
+
+static int gj_inverse(float* X, float* Y, int n, float** result, cudaStream_t st) {
+    int grid = (n * n + 256 * 4 - 1) / (256 * 4);
+    const int cap = sm_count() * 2;
+    if (grid > cap) grid = cap;
+    if (grid < 1) grid = 1;
+    void* args[] = {&X, &Y, &n};
+    cudaError_t e = cudaLaunchCooperativeKernel((void*)gj_inverse_kernel, dim3(grid), dim3(256), args, 0, st);
+    if (e != cudaSuccess) return cuda_fail(e, "gj_inverse launch");
+    count_launch(1);
+    *result = (n & 1) ? Y : X;
+    return 0;
+}
+
+static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+size_t cayley_linear_ws(int cout, int cin) {
+    const size_t R = cout > cin ? cout : cin, n = cout > cin ? cin : cout;
+    size_t b = 0;
+    b += align256(kNormBlocks * sizeof(double)) + 256;   // partials + scale
+    b += align256(R * n * 4);                            // Ws
+    b += align256(n * (R - n) * 4 + 4);                  // Vt
+    b += 6 * align256(n * n * 4);                        // G, IpA(X), Y, ImAT, Mt, spare
+    b += align256(R * n * 4);                            // Qfull
+    b += align256(gemm_nt_workspace((int)R, (int)n, (int)R));
+    return b;
+}
+
+// Q = cayley(alpha * W / (||W||_F * norm_mult))
+int cayley_linear_impl(const float* W, const float* alpha, int cout, int cin, float norm_mult, float* Q, void* ws,
+                       size_t ws_bytes, cudaStream_t st) {
+    if (ws_bytes < cayley_linear_ws(cout, cin)) { set_error("cayley_linear: workspace too small"); return -1; }
+    const int tr = cin > cout;
+    const int R = tr ? cin : cout, n = tr ? cout : cin;
+    char* p = reinterpret_cast<char*>(ws);
+    auto take = [&](size_t bytes) { void* r = p; p += align256(bytes); return r; };
+    double* part = (double*)take(kNormBlocks * sizeof(double));
+    float* scale = (float*)take(256);
+    float* Ws = (float*)take((size_t)R * n * 4);
+    float* Vt = (float*)take((size_t)n * (R - n) * 4 + 4);
+    float* G = (float*)take((size_t)n * n * 4);
+    float* X = (float*)take((size_t)n * n * 4);
+    float* Y = (float*)take((size_t)n * n * 4);
+    float* ImAT = (float*)take((size_t)n * n * 4);
+    float* Mt = (float*)take((size_t)n * n * 4);
+    take((size_t)n * n * 4);
+    float* Qfull = (float*)take((size_t)R * n * 4);
+    float* gws = (float*)p;
+    const size_t gws_bytes = ws_bytes - (size_t)(p - reinterpret_cast<char*>(ws));
+
+    const size_t total = (size_t)cout * cin;
+    sumsq_partial_kernel<<<kNormBlocks, 256, 0, st>>>(W, total, part);
+    norm_finalize_kernel<<<1, 32, 0, st>>>(part, kNormBlocks, alpha, norm_mult, scale);
+    const unsigned blocks = (unsigned)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
+    cayley_prep1_kernel<<<blocks, 256, 0, st>>>(W, cout, cin, tr, scale, Ws, Vt);
+    count_launch(3);
+    int rc;
+    const int has_v = R > n;
+    if (has_v && (rc = gemm_nt(Vt, R - n, Vt, R - n, n, n, R - n, nullptr, 1.f, 0, G, n, gws, gws_bytes, st))) return rc;
+    cayley_prep2_kernel<<<(n * n + 255) / 256, 256, 0, st>>>(Ws, G, n, has_v, X, ImAT);
+    count_launch(1);
+    float* M = nullptr;
+    if ((rc = gj_inverse(X, Y, n, &M, st))) return rc;
+    float* out_top = tr ? Qfull : Q;
+    if ((rc = gemm_nt(M, n, ImAT, n, n, n, n, nullptr, 1.f, 0, out_top, n, gws, gws_bytes, st))) return rc;
+    if (has_v) {
+        transpose_kernel<<<dim3((n + 31) / 32, (n + 31) / 32), dim3(32, 8), 0, st>>>(M, n, n, Mt);
+        count_launch(1);
+        if ((rc = gemm_nt(Ws + (size_t)n * n, n, Mt, n, R - n, n, n, nullptr, -2.f, 0, out_top + (size_t)n * n, n, gws,
+                          gws_bytes, st)))
+            return rc;
+    }
+    if (tr) {   // Q (cout x cin) = Qfull^T, plain transpose (layers.py:54-55)
+        transpose_kernel<<<dim3((n + 31) / 32, (R + 31) / 32), dim3(32, 8), 0, st>>>(Qfull, R, n, Q);
+        count_launch(1);
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "cayley_linear");
+    return 0;
+}
+
+// ---- convolution weight spectrum ----------------------------------------------------------------
+// wfft[phi][o][i] = sum_{a,b<k} w[o,i,a,b] exp(+2 pi i (u (a-s) + v (b-s)) / n), s = (k-1)/2  (App. C-1)
+__device__ __forceinline__ float2 conv_spectrum_at(const float* __restrict__ w, int k, int n, int u, int v) {
+    const int s = (k - 1) / 2;
+    float2 acc = make_float2(0.f, 0.f);
+    for (int a = 0; a < k; ++a)
+        for (int b = 0; b < k; ++b) {
+            int m = (u * (a - s) + v * (b - s)) % n;
+            if (m < 0) m += n;
+            float sn, cs;
+            sincospif(2.f * (float)m / (float)n, &sn, &cs);
+            const float wv = w[a * k + b];
+            acc.x = fmaf(wv, cs, acc.x);
+            acc.y = fmaf(wv, sn, acc.y);
+        }
+    return acc;
+}
+
+__global__ void __launch_bounds__(256) conv_spectrum_sumsq_kernel(const float* __restrict__ w, int cout, int cin,
+                                                                  int k, int n, double* __restrict__ part) {
+    __shared__ double sh[8];
+    const int phi = blockIdx.x, H = n / 2 + 1, u = phi / H, v = phi - u * H;
+    double acc = 0;
+    for (int e = threadIdx.x; e < cout * cin; e += 256) {
+        const float2 z = conv_spectrum_at(w + (size_t)e * k * k, k, n, u, v);
+        acc += (double)z.x * z.x + (double)z.y * z.y;
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0;
+        for (int i = 0; i < 8; ++i) s += sh[i];
+        part[phi] = s;
+    }
+}
+__global__ void conv_alpha_finalize_kernel(const double* __restrict__ part, int F, float* __restrict__ alpha_out) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        double s = 0;
+        for (int i = 0; i < F; ++i) s += part[i];
+        alpha_out[0] = (float)sqrt(s);
+    }
+}
+
+// One CTA per frequency: Q[phi] = cayley(alpha * wfft[phi] / ||wfft||).  cout >= cin.
+// smem (float2): Wf[cout][cin], X[cin][cin], Y[cin][cin], A[cin][cin]
+__global__ void __launch_bounds__(256) cayley_conv_kernel(const float* __restrict__ w, const float* __restrict__ alpha,
+                                                          const double* __restrict__ part, int F, int cout, int cin,
+                                                          int k, int n, float2* __restrict__ Qf) {
+    extern __shared__ float4 smem4[];
+    float2* Wf = reinterpret_cast<float2*>(smem4);
+    float2* X = Wf + cout * cin;
+    float2* Y = X + cin * cin;
+    float2* A = Y + cin * cin;
+    __shared__ float sc_sh;
+    const int t = threadIdx.x, phi = blockIdx.x, H = n / 2 + 1, u = phi / H, v = phi - u * H;
+    if (t == 0) {
+        double s = 0;
+        for (int i = 0; i < F; ++i) s += part[i];
+        sc_sh = alpha[0] / (float)sqrt(s);
+    }
+    __syncthreads();
+    const float sc = sc_sh;
+    for (int e = t; e < cout * cin; e += 256) {
+        const float2 z = conv_spectrum_at(w + (size_t)e * k * k, k, n, u, v);
+        Wf[e] = make_float2(sc * z.x, sc * z.y);
+    }
+    __syncthreads();
+    const int nv = cout - cin;
+    // A = U - U^H + V^H V ; X = I + A
+    for (int e = t; e < cin * cin; e += 256) {
+        const int i = e / cin, j = e - i * cin;
+        const float2 uij = Wf[i * cin + j], uji = Wf[j * cin + i];
+        float2 g = make_float2(0.f, 0.f);
+        for (int r = 0; r < nv; ++r) cfma(g, cconj(Wf[(cin + r) * cin + i]), Wf[(cin + r) * cin + j]);
+        const float2 a = make_float2(uij.x - uji.x + g.x, uij.y + uji.y + g.y);
+        A[e] = a;
+        X[e] = make_float2((i == j ? 1.f : 0.f) + a.x, a.y);
+    }
+    __syncthreads();
+    // ping-pong Gauss-Jordan (complex, no pivoting)
+    for (int kk = 0; kk < cin; ++kk) {
+        const float2* in = (kk & 1) ? Y : X;
+        float2* out = (kk & 1) ? X : Y;
+        const float2 p = in[kk * cin + kk];
+        const float den = 1.f / (p.x * p.x + p.y * p.y);
+        const float2 ip = make_float2(p.x * den, -p.y * den);
+        for (int e = t; e < cin * cin; e += 256) {
+            const int i = e / cin, j = e - i * cin;
+            float2 r;
+            if (i == kk) r = (j == kk) ? ip : cmul(in[e], ip);
+            else {
+                const float2 f = in[i * cin + kk];
+                if (j == kk) { const float2 q = cmul(f, ip); r = make_float2(-q.x, -q.y); }
+                else { const float2 q = cmul(f, cmul(in[kk * cin + j], ip)); r = csub(in[e], q); }
+            }
+            out[e] = r;
+        }
+        __syncthreads();
+    }
+    const float2* M = (cin & 1) ? Y : X;
+    float2* dst = Qf + (size_t)phi * cout * cin;
+    // top: M (I - A) ; bottom: -2 V M
+    for (int e = t; e < cout * cin; e += 256) {
+        const int i = e / cin, j = e - i * cin;
+        float2 acc = make_float2(0.f, 0.f);
+        if (i < cin) {
+            for (int r = 0; r < cin; ++r) {
+                const float2 a = A[r * cin + j];
+                const float2 ima = make_float2((r == j ? 1.f : 0.f) - a.x, -a.y);
+                cfma(acc, M[i * cin + r], ima);
+            }
+        } else {
+            for (int r = 0; r < cin; ++r) cfma(acc, Wf[i * cin + r], M[r * cin + j]);
+            acc = make_float2(-2.f * acc.x, -2.f * acc.y);
+        }
+        dst[e] = acc;
+    }
+}
+
+}  // namespace fiode
+
+using namespace fiode;
+
+extern "C" size_t fiode_cayley_linear_workspace_bytes(int cout, int cin) { return cayley_linear_ws(cout, cin); }
+
+extern "C" int fiode_cayley_linear(const float* W, const float* alpha, int cout, int cin, float* Q, void* ws,
+                                   size_t ws_bytes, void* stream) {
+    if (!W || !alpha || !Q || !ws) { set_error("fiode_cayley_linear: null pointer"); return -1; }
+    if (cout <= 0 || cin <= 0) { set_error("fiode_cayley_linear: bad shape"); return -1; }
+    return cayley_linear_impl(W, alpha, cout, cin, 1.f, Q, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+static size_t conv_part_bytes(int n) { return align256((size_t)n * (n / 2 + 1) * sizeof(double)); }
+
+extern "C" int fiode_conv_alpha_init(const float* w, int cout, int cin, int k, int n, float* alpha_out, void* ws,
+                                     size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!w || !alpha_out || !ws) { set_error("fiode_conv_alpha_init: null pointer"); return -1; }
+    if (ws_bytes < conv_part_bytes(n)) { set_error("fiode_conv_alpha_init: workspace too small"); return -1; }
+    const int F = n * (n / 2 + 1);
+    conv_spectrum_sumsq_kernel<<<F, 256, 0, st>>>(w, cout, cin, k, n, (double*)ws);
+    conv_alpha_finalize_kernel<<<1, 32, 0, st>>>((const double*)ws, F, alpha_out);
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(2);
+    return 0;
+}
+
+extern "C" size_t fiode_cayley_conv_workspace_bytes(int cout, int cin, int k, int n) {
+    if (k == 1) return cayley_linear_ws(cout, cin);
+    return conv_part_bytes(n);
+}
+
+extern "C" int fiode_cayley_conv(const float* w, const float* alpha, int cout, int cin, int k, int n, float* Qf,
+                                 void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!w || !alpha || !Qf || !ws) { set_error("fiode_cayley_conv: null pointer"); return -1; }
+    const int F = n * (n / 2 + 1);
+    if (k == 1) {
+        // wfft[phi] = w[:, :, 0, 0] for every phi  =>  ||wfft||_F = sqrt(F) ||w||_F, one real Q (App. C-1)
+        return cayley_linear_impl(w, alpha, cout, cin, sqrtf((float)F), Qf, ws, ws_bytes, st);
+    }
+    if (cout < cin) { set_error("fiode_cayley_conv: k>1 needs cout >= cin (got %d < %d)", cout, cin); return -1; }
+    if (ws_bytes < conv_part_bytes(n)) { set_error("fiode_cayley_conv: workspace too small"); return -1; }
+    const size_t smem = (size_t)(cout * cin + 3 * cin * cin) * sizeof(float2);
+    if (smem > 200 * 1024) { set_error("fiode_cayley_conv: layer too large for the in-smem solver"); return -1; }
+    FIODE_CUDA(cudaFuncSetAttribute(cayley_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    conv_spectrum_sumsq_kernel<<<F, 256, 0, st>>>(w, cout, cin, k, n, (double*)ws);
+    cayley_conv_kernel<<<F, 256, smem, st>>>(w, alpha, (const double*)ws, F, cout, cin, k, n,
+                                             reinterpret_cast<float2*>(Qf));
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(2);
+    return 0;
+}

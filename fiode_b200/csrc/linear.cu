@@ -18,7 +18,7 @@ constexpr int GT = 64, GK = 32, GS = GK + 4, GTHREADS = 128;
 
 __global__ void __launch_bounds__(GTHREADS) gemm_nt_kernel(const float* __restrict__ A, int lda,
                                                            const float* __restrict__ Bm, int ldb, int M, int N, int K,
-                                                           int k_per_split, float* __restrict__ part /*[splits][M][N]*/) {
+                                                           int k_per_split, int vec_ok, float* __restrict__ part /*[splits][M][N]*/) {
     __shared__ __align__(16) float As[2][GT * GS];
     __shared__ __align__(16) float Bs[2][GT * GS];
     const int t = threadIdx.x;
@@ -39,12 +39,12 @@ __global__ void __launch_bounds__(GTHREADS) gemm_nt_kernel(const float* __restri
             const int k = k0 + q * 4;
             float* da = &As[buf][r * GS + q * 4];
             float* db = &Bs[buf][r * GS + q * 4];
-            if (m0 + r < M && k + 3 < k_end) __pipeline_memcpy_async(da, A + (size_t)(m0 + r) * lda + k, 16);
+            if (vec_ok && m0 + r < M && k + 3 < k_end) __pipeline_memcpy_async(da, A + (size_t)(m0 + r) * lda + k, 16);
             else {
 #pragma unroll
                 for (int c = 0; c < 4; ++c) da[c] = (m0 + r < M && k + c < k_end) ? A[(size_t)(m0 + r) * lda + k + c] : 0.f;
             }
-            if (n0 + r < N && k + 3 < k_end) __pipeline_memcpy_async(db, Bm + (size_t)(n0 + r) * ldb + k, 16);
+            if (vec_ok && n0 + r < N && k + 3 < k_end) __pipeline_memcpy_async(db, Bm + (size_t)(n0 + r) * ldb + k, 16);
             else {
 #pragma unroll
                 for (int c = 0; c < 4; ++c) db[c] = (n0 + r < N && k + c < k_end) ? Bm[(size_t)(n0 + r) * ldb + k + c] : 0.f;
@@ -119,25 +119,30 @@ __global__ void gemm_epilogue_kernel(const float* __restrict__ part, int splits,
     }
 }
 
+static int gemm_splits(int M, int N, int K) {
+    const int tiles = ((M + GT - 1) / GT) * ((N + GT - 1) / GT);
+    int splits = 1;
+    const int target = 4 * sm_count();
+    while (splits < 32 && tiles * splits < target && K / (splits * 2) >= 64) splits *= 2;
+    return splits;
+}
 size_t gemm_nt_workspace(int M, int N, int K) {
-    // worst-case split count is bounded by 32
-    (void)K;
-    return (size_t)32 * M * N * sizeof(float);
+    return (size_t)gemm_splits(M, N, K) * M * N * sizeof(float) + 256;
 }
 
 // C = alpha * A B^T (+bias) (+GroupSort), deterministic split-K sized to fill the GPU
 int gemm_nt(const float* A, int lda, const float* Bm, int ldb, int M, int N, int K, const float* bias, float alpha,
             int group_sort, float* y, int ldy, float* ws, size_t ws_bytes, cudaStream_t st) {
-    const int tiles = ((M + GT - 1) / GT) * ((N + GT - 1) / GT);
-    int splits = 1;
-    const int target = 4 * sm_count();
-    while (splits < 32 && tiles * splits < target && K / (splits * 2) >= 64) splits *= 2;
+    int splits = gemm_splits(M, N, K);
     if ((size_t)splits * M * N * sizeof(float) > ws_bytes) { set_error("gemm_nt: workspace too small"); return -1; }
     int kps = (K + splits - 1) / splits;
     kps = (kps + GK - 1) / GK * GK;
     splits = (K + kps - 1) / kps;
     dim3 grid((N + GT - 1) / GT, (M + GT - 1) / GT, splits);
-    gemm_nt_kernel<<<grid, GTHREADS, 0, st>>>(A, lda, Bm, ldb, M, N, K, kps, ws);
+    // 16-byte cp.async needs 16-byte aligned rows on both operands; otherwise scalar loads
+    const int vec_ok = ((lda & 3) == 0) && ((ldb & 3) == 0) && ((reinterpret_cast<uintptr_t>(A) & 15) == 0) &&
+                       ((reinterpret_cast<uintptr_t>(Bm) & 15) == 0);
+    gemm_nt_kernel<<<grid, GTHREADS, 0, st>>>(A, lda, Bm, ldb, M, N, K, kps, vec_ok, ws);
     const size_t total = group_sort ? (size_t)M * (N / 2) : (size_t)M * N;
     gemm_epilogue_kernel<<<(unsigned)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096), 256, 0, st>>>(
         ws, splits, M, N, bias, alpha, group_sort, y, ldy);
@@ -156,7 +161,7 @@ extern "C" size_t fiode_linear_workspace_bytes(int M, int N, int K) { return gem
 extern "C" int fiode_linear_fwd(const float* X, const float* Q, const float* bias, int M, int N, int K,
                                 int group_sort, float* y, void* ws, size_t ws_bytes, void* stream) {
     if (!X || !Q || !y || !ws) { set_error("fiode_linear_fwd: null pointer"); return -1; }
-    if (M <= 0 || N <= 0 || K <= 0 || (K & 3)) { set_error("fiode_linear_fwd: bad sizes (K must be a multiple of 4)"); return -1; }
+    if (M <= 0 || N <= 0 || K <= 0) { set_error("fiode_linear_fwd: bad sizes"); return -1; }
     if (group_sort && (N & 1)) { set_error("fiode_linear_fwd: GroupSort needs an even width"); return -1; }
     return gemm_nt(X, K, Q, K, M, N, K, bias, 1.f, group_sort, y, N, reinterpret_cast<float*>(ws), ws_bytes,
                    (cudaStream_t)stream);

@@ -1,0 +1,94 @@
+"""Cayley-orthogonal layers with the reference's names, constructor arguments and state_dict keys
+(libs/ortho_conv/layers.py), running on libfiode_b200.so.
+
+Differences a maintainer should know about:
+  * the Cayley matrices are cached per *weight version* (the reference recomputes the conv ones on
+    every forward and never invalidates the linear ones in eval mode, layers.py:72-86, 103-105);
+  * forward only (inference / certification).  Training goes through the fused FI-loss op, which has
+    its own hand-written backward.
+"""
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+from . import ops
+
+
+def cayley(W):
+    """libs/ortho_conv/layers.py:50-60 for a real 2-D weight."""
+    assert W.dim() == 2 and not W.is_complex(), 'fiode_b200.layers.cayley handles real (cout, cin) matrices'
+    return ops.cayley_linear(W, W.norm())
+
+
+class GroupSort(nn.Module):
+    """layers.py:127-131."""
+    def forward(self, x):
+        return ops.group_sort(x)
+
+
+def _version(*ts):
+    return tuple((t.data_ptr(), t._version) for t in ts)
+
+
+class CayleyLinear(nn.Linear):
+    """layers.py:88-105.  ``Q`` holds the cached orthogonal matrix like the reference attribute."""
+    def __init__(self, in_features, out_features, bias=True):
+        super().__init__(in_features, out_features, bias)
+        self.alpha = nn.Parameter(torch.ones(1, dtype=torch.float32))
+        self.alpha.data = self.weight.norm()
+        self._q_key = None
+
+    def reset_parameters(self):
+        std = 1 / self.weight.shape[1] ** 0.5
+        nn.init.uniform_(self.weight, -std, std)
+        if self.bias is not None:
+            self.bias.data.uniform_(-std, std)
+        self.Q = None
+
+    def orthogonal_weight(self):
+        key = _version(self.weight, self.alpha)
+        if self.Q is None or self._q_key != key:
+            self.Q = ops.cayley_linear(self.weight, self.alpha)
+            self._q_key = key
+        return self.Q
+
+    def forward(self, X, group_sort=False):
+        return ops.linear_fwd(X, self.orthogonal_weight(), self.bias, group_sort)
+
+
+class CayleyConv(nn.Conv2d):
+    """layers.py:24-48 (StridedConv: stride 2 is emulated by space-to-depth, 4x in_channels,
+    kernel // 2) + :62-86 (CayleyConv).  ``alpha`` is created lazily at the first forward, as in the
+    reference (:80-81), or loaded from a checkpoint that already has it."""
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, bias=True):
+        self.striding = stride == 2
+        if self.striding:
+            in_channels, kernel_size = 4 * in_channels, max(1, kernel_size // 2)
+        super().__init__(in_channels, out_channels, kernel_size, stride=1, padding=kernel_size // 2, bias=bias)
+        self.register_parameter('alpha', None)
+        self.Qf = None
+        self._q_key = None
+
+    def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
+        k = prefix + 'alpha'
+        if k in state_dict and self.alpha is None:
+            self.alpha = nn.Parameter(torch.zeros((), dtype=torch.float32, device=self.weight.device))
+        super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)
+
+    def orthogonal_spectrum(self, n):
+        if self.alpha is None:
+            self.alpha = nn.Parameter(ops.conv_alpha_init(self.weight, n))
+        key = _version(self.weight, self.alpha) + (n,)
+        if self.Qf is None or self._q_key != key:
+            self.Qf = ops.cayley_conv(self.weight, self.alpha, n)
+            self._q_key = key
+        return self.Qf
+
+    def forward(self, x, group_sort=False):
+        n = x.shape[-1] // (2 if self.striding else 1)
+        Qf = self.orthogonal_spectrum(n)
+        if self.striding:
+            assert self.kernel_size[0] == 1
+            return ops.conv1x1_s2d_fwd(x, Qf, self.bias, group_sort)
+        return ops.cayley_conv_fwd(x, Qf, self.bias, group_sort)

@@ -1,0 +1,114 @@
+"""models.py / libs/ortho_conv/models_ortho.py of the reference on libfiode_b200.so: Normalize,
+KWLarge_Concat, make_ortho_KWLarge_Concat and IVP (same constructor arguments, attribute names
+and state_dict keys)."""
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+from . import ops
+from ._lib import BackboneWeights, ptr
+from .layers import CayleyConv, CayleyLinear, GroupSort
+from .odeint import odeint
+from .dynamics.output_coordinates import DefaultOutputFun
+
+
+class Normalize(nn.Module):
+    """models.py:17-26."""
+    def __init__(self, mu, std):
+        super().__init__()
+        self.register_buffer('mu', torch.tensor(mu, dtype=torch.float32).view(-1, 1, 1))
+        self.register_buffer('std', torch.tensor(std, dtype=torch.float32).view(-1, 1, 1))
+
+    def forward(self, x):
+        raise RuntimeError('Normalize is fused into the backbone kernel; call the param_map Sequential '
+                           '(fiode_b200.models.ParamMap) rather than this layer alone')
+
+
+class KWLarge_Concat(nn.Module):
+    """libs/ortho_conv/models_ortho.py:3-28 (w=1, CIFAR)."""
+    def __init__(self, conv=CayleyConv, linear=CayleyLinear, w=1, out_dim=128, act='GroupSort'):
+        super().__init__()
+        assert w == 1 and act == 'GroupSort' and out_dim < 512, \
+            'the fused B200 backbone covers the configuration the FI-ODE CIFAR configs use'
+        self.out_dim = out_dim
+        self.act = GroupSort()
+        self.model = nn.Sequential(
+            conv(3, 32, 3), self.act,
+            conv(32, 32, 3, stride=2), self.act,
+            conv(32, 64, 3), self.act,
+            conv(64, 64, 3, stride=2), self.act,
+            nn.Flatten(),
+            linear(4096, 512), self.act,
+            linear(512, 512), self.act)
+        self.fc = linear(512, out_dim)
+
+    def forward(self, x):
+        """Layer-by-layer path (un-normalised input): each layer is one C-ABI call."""
+        m = self.model
+        h = m[0](x, group_sort=True)
+        h = m[2](h, group_sort=True)
+        h = m[4](h, group_sort=True)
+        h = m[6](h, group_sort=True)
+        h = h.flatten(1)
+        h = m[9](h, group_sort=True)
+        h = m[11](h, group_sort=True)
+        return self.fc(h)
+
+
+class ParamMap(nn.Sequential):
+    """nn.Sequential(Normalize, KWLarge_Concat) (models.py:29-35) whose forward is ONE fused call
+    (fiode_backbone_fwd) when out_dim == 10."""
+    def backbone_weights(self):
+        norm, net = self[0], self[1]
+        m = net.model
+        t = dict(mu=norm.mu.reshape(-1), std=norm.std.reshape(-1),
+                 Qf0=torch.view_as_real(m[0].orthogonal_spectrum(32)), b0=m[0].bias,
+                 Q2=m[2].orthogonal_spectrum(16), b2=m[2].bias,
+                 Qf4=torch.view_as_real(m[4].orthogonal_spectrum(16)), b4=m[4].bias,
+                 Q6=m[6].orthogonal_spectrum(8), b6=m[6].bias,
+                 Q9=m[9].orthogonal_weight(), b9=m[9].bias, Q11=m[11].orthogonal_weight(), b11=m[11].bias,
+                 Qfc=net.fc.orthogonal_weight(), bfc=net.fc.bias)
+        t = {k: v.detach().float().contiguous() for k, v in t.items()}
+        bw = BackboneWeights(**{k: ptr(v) for k, v in t.items()})
+        return bw, t
+
+    def forward(self, x):
+        assert self[1].out_dim == 10
+        bw, keep = self.backbone_weights()
+        return ops.backbone_fwd(bw, x, keep)
+
+
+def make_ortho_KWLarge_Concat(n_in_channels, n_outputs, mu=None, std=None, out_dim=128, act='GroupSort'):
+    """models.py:29-35."""
+    return ParamMap(Normalize(mu, std), KWLarge_Concat(out_dim=out_dim, act=act))
+
+
+class IVP(nn.Module):
+    """models.py:185-242: init_coordinates -> odeint(dopri5) -> output_fun."""
+    def __init__(self, n_input, n_output, dyn_fun, init_coordinates, output_fun=DefaultOutputFun(), ode_tol=1e-2,
+                 ts=torch.linspace(0, 1, 200)):
+        super().__init__()
+        self.n_input, self.n_output = n_input, n_output
+        self.dyn_fun = dyn_fun
+        self.ode_tol = ode_tol
+        self.register_buffer('ts', ts)
+        self.output_fun = output_fun
+        self.init_coordinates = init_coordinates
+
+    def h_dot(self, t, h):
+        return self.dyn_fun.ode_forward(t, h)
+
+    def forward(self, x, ts=None, int_params=None, use_adjoint=False, return_traj=False):
+        solution = self.integrate(x, ts=ts, int_params=int_params, use_adjoint=use_adjoint)
+        return self.output_fun(solution) if return_traj else self.output_fun(solution)[-1]
+
+    def integrate(self, x, ts=None, int_params=None, use_adjoint=False):
+        assert not use_adjoint, 'the adjoint solve stays on the reference (unused by the FI-ODE configs)'
+        if ts is None:
+            ts = self.ts
+        if int_params is None:
+            int_params = dict(rtol=self.ode_tol, atol=self.ode_tol)
+        static_state, state = self.init_coordinates(x, self.dyn_fun)
+        self.dyn_fun.static_state = static_state
+        return odeint(self.h_dot, state, ts, **int_params)

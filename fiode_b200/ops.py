@@ -1,0 +1,235 @@
+"""Tensor-level wrappers over the C ABI (include/fiode_b200.h).  PyTorch is used for device memory
+and streams only; every computation below happens in libfiode_b200.so.  CUDA tensors only."""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import DynWeights, BackboneWeights, SolveStats, check, lib, ptr, stream_ptr
+
+NH = 10
+
+
+def _f32(t):
+    return t.detach().to(torch.float32).contiguous()
+
+
+def _ws(nbytes, device):
+    return torch.empty(max(int(nbytes), 256), dtype=torch.uint8, device=device)
+
+
+# ---- Cayley weight preparation ------------------------------------------------------------------
+def cayley_linear(weight, alpha):
+    """Q = cayley(alpha * W / ||W||)  (libs/ortho_conv/layers.py:103-104)."""
+    W = _f32(weight)
+    cout, cin = W.shape
+    a = _f32(alpha).reshape(1)
+    Q = torch.empty_like(W)
+    n = lib().fiode_cayley_linear_workspace_bytes(cout, cin)
+    ws = _ws(n, W.device)
+    check(lib().fiode_cayley_linear(ptr(W), ptr(a), cout, cin, ptr(Q), ptr(ws), n, stream_ptr()), 'fiode_cayley_linear')
+    return Q
+
+
+def conv_alpha_init(weight, n):
+    """CayleyConv's lazily created alpha = ||wfft||_F (layers.py:80-81) as a 0-dim device tensor."""
+    w = _f32(weight)
+    cout, cin, k, _ = w.shape
+    out = torch.empty(1, dtype=torch.float32, device=w.device)
+    nb = lib().fiode_cayley_conv_workspace_bytes(cout, cin, max(k, 2), n)
+    ws = _ws(nb, w.device)
+    check(lib().fiode_conv_alpha_init(ptr(w), cout, cin, k, n, ptr(out), ptr(ws), nb, stream_ptr()),
+          'fiode_conv_alpha_init')
+    return out.reshape(())
+
+
+def cayley_conv(weight, alpha, n):
+    """Per-frequency orthogonal matrices of a CayleyConv (layers.py:74-82).  k=3 -> complex64
+    (F, cout, cin); k=1 -> real (cout, cin) shared by every frequency."""
+    w = _f32(weight)
+    cout, cin, k, _ = w.shape
+    a = _f32(alpha).reshape(1)
+    F = n * (n // 2 + 1)
+    if k == 1:
+        Q = torch.empty(cout, cin, dtype=torch.float32, device=w.device)
+    else:
+        Q = torch.empty(F, cout, cin, 2, dtype=torch.float32, device=w.device)
+    nb = lib().fiode_cayley_conv_workspace_bytes(cout, cin, k, n)
+    ws = _ws(nb, w.device)
+    check(lib().fiode_cayley_conv(ptr(w), ptr(a), cout, cin, k, n, ptr(Q), ptr(ws), nb, stream_ptr()), 'fiode_cayley_conv')
+    return Q if k == 1 else torch.view_as_complex(Q)
+
+
+# ---- layers ---------------------------------------------------------------------------------------
+def cayley_conv_fwd(x, Qf, bias, group_sort=False):
+    x = _f32(x)
+    B, cin, n, _ = x.shape
+    Qr = torch.view_as_real(Qf).contiguous() if Qf.is_complex() else Qf.contiguous()
+    cout = Qr.shape[1]
+    y = torch.empty(B, cout, n, n, dtype=torch.float32, device=x.device)
+    nb = lib().fiode_cayley_conv_fwd_workspace_bytes(B, cin, cout, n)
+    ws = _ws(nb, x.device)
+    check(lib().fiode_cayley_conv_fwd(ptr(x), ptr(Qr), ptr(_f32(bias)) if bias is not None else None, B, cin, cout, n,
+                                      int(group_sort), ptr(y), ptr(ws), nb, stream_ptr()), 'fiode_cayley_conv_fwd')
+    return y
+
+
+def conv1x1_s2d_fwd(x, Q, bias, group_sort=False):
+    x = _f32(x)
+    B, cin, n, _ = x.shape
+    cout = Q.shape[0]
+    y = torch.empty(B, cout, n // 2, n // 2, dtype=torch.float32, device=x.device)
+    check(lib().fiode_conv1x1_s2d_fwd(ptr(x), ptr(_f32(Q)), ptr(_f32(bias)) if bias is not None else None, B, cin, cout,
+                                      n, int(group_sort), ptr(y), stream_ptr()), 'fiode_conv1x1_s2d_fwd')
+    return y
+
+
+def linear_fwd(X, Q, bias, group_sort=False):
+    X = _f32(X)
+    lead = X.shape[:-1]
+    X2 = X.reshape(-1, X.shape[-1])
+    M, K = X2.shape
+    N = Q.shape[0]
+    y = torch.empty(M, N, dtype=torch.float32, device=X.device)
+    nb = lib().fiode_linear_workspace_bytes(M, N, K)
+    ws = _ws(nb, X.device)
+    check(lib().fiode_linear_fwd(ptr(X2), ptr(_f32(Q)), ptr(_f32(bias)) if bias is not None else None, M, N, K,
+                                 int(group_sort), ptr(y), ptr(ws), nb, stream_ptr()), 'fiode_linear_fwd')
+    return y.reshape(*lead, N)
+
+
+def space_to_depth(x):
+    x = _f32(x)
+    B, Cc, n, _ = x.shape
+    y = torch.empty(B, 4 * Cc, n // 2, n // 2, dtype=torch.float32, device=x.device)
+    check(lib().fiode_space_to_depth(ptr(x), B, Cc, n, ptr(y), stream_ptr()), 'fiode_space_to_depth')
+    return y
+
+
+def group_sort(x):
+    x = _f32(x)
+    B, Cc = x.shape[:2]
+    inner = x[0, 0].numel() if x.dim() > 2 else 1
+    y = torch.empty_like(x)
+    check(lib().fiode_group_sort(ptr(x), B, Cc, inner, ptr(y), stream_ptr()), 'fiode_group_sort')
+    return y
+
+
+def backbone_fwd(bw: BackboneWeights, x, keep=()):
+    """s = param_map(x) for the CIFAR KWLarge_Concat backbone.  ``keep`` holds the tensors the struct
+    points into (so they outlive the asynchronous launch)."""
+    x = _f32(x)
+    B = x.shape[0]
+    s = torch.empty(B, NH, dtype=torch.float32, device=x.device)
+    nb = lib().fiode_backbone_workspace_bytes(B)
+    ws = _ws(nb, x.device)
+    check(lib().fiode_backbone_fwd(C.byref(bw), ptr(x), B, ptr(s), ptr(ws), nb, stream_ptr()), 'fiode_backbone_fwd')
+    return s
+
+
+# ---- dynamics -------------------------------------------------------------------------------------
+def rhs_fwd(dw: DynWeights, h, s, s_group=None, return_aux=False):
+    """f = eval_dot_light(h, s) (dynamics/classification.py:117-126).  s: (1,10) broadcast, (N,10)
+    per row, or (G,10) with ``s_group`` consecutive rows of h sharing one s row."""
+    h = _f32(h)
+    s = _f32(s)
+    N = h.shape[0]
+    if s.shape[0] == 1:
+        s_rows, sg = 1, N
+    elif s_group is not None:
+        s_rows, sg = s.shape[0], int(s_group)
+    else:
+        assert s.shape[0] == N, 'static state must have 1 or N rows'
+        s_rows, sg = N, 1
+    f = torch.empty_like(h)
+    ft = torch.empty_like(h) if return_aux else None
+    mu = torch.empty(N, dtype=torch.float32, device=h.device) if return_aux else None
+    it = torch.empty(1, dtype=torch.int32, device=h.device) if return_aux else None
+    nb = lib().fiode_rhs_workspace_bytes(N)
+    ws = _ws(nb, h.device)
+    check(lib().fiode_rhs_fwd(C.byref(dw), ptr(h), ptr(s), N, s_rows, sg, ptr(f), ptr(ft), ptr(mu), ptr(it), ptr(ws), nb,
+                              stream_ptr()), 'fiode_rhs_fwd')
+    return (f, ft, mu, it) if return_aux else f
+
+
+def barrier_project_fwd(lower, nominal, upper=None, max_iter=30, tol=1e-4):
+    lower, nominal = _f32(lower), _f32(nominal)
+    upper = _f32(upper) if upper is not None else None
+    N = nominal.shape[0]
+    v = torch.empty_like(nominal)
+    mu = torch.empty(N, dtype=torch.float32, device=nominal.device)
+    it = torch.empty(1, dtype=torch.int32, device=nominal.device)
+    ws = _ws(256, nominal.device)
+    check(lib().fiode_barrier_project_fwd(ptr(lower), ptr(upper), ptr(nominal), N, max_iter, tol, ptr(v), ptr(mu), ptr(it),
+                                          ptr(ws), 256, stream_ptr()), 'fiode_barrier_project_fwd')
+    return v, mu, it
+
+
+def barrier_project_bwd(grad_v, v, mu, nominal):
+    grad_v, v, mu, nominal = _f32(grad_v), _f32(v), _f32(mu), _f32(nominal)
+    N = nominal.shape[0]
+    dl, dn = torch.empty_like(nominal), torch.empty_like(nominal)
+    check(lib().fiode_barrier_project_bwd(ptr(grad_v), ptr(v), ptr(mu), ptr(nominal), N, ptr(dl), ptr(dn), stream_ptr()),
+          'fiode_barrier_project_bwd')
+    return dl, dn
+
+
+def certify_grid(dw: DynWeights, gridz, T, s, labels, kappa, batches=10, return_iters=False):
+    """Per-image maxima of the Lipschitz grid check (robustness/certify_lipschitz.py:104-143).
+    gridz: (Ng,10) uint8 numerators of the canonical label-0 grid; returns (M,2)."""
+    assert gridz.dtype == torch.uint8 and gridz.is_cuda
+    gridz = gridz.contiguous()
+    s = _f32(s)
+    labels = labels.to(torch.int32).contiguous()
+    M, Ng = s.shape[0], gridz.shape[0]
+    lut = (torch.arange(T + 1, dtype=torch.float64) / T).float().to(s.device)   # what grid.float() holds
+    n_chunks = batches + (1 if Ng % batches else 0)
+    out = torch.empty(M, 2, dtype=torch.float32, device=s.device)
+    iters = torch.empty(M, n_chunks, dtype=torch.int32, device=s.device) if return_iters else None
+    nb = lib().fiode_certify_workspace_bytes(M, n_chunks)
+    ws = _ws(nb, s.device)
+    check(lib().fiode_certify_grid(C.byref(dw), ptr(gridz), Ng, T, ptr(lut), ptr(s), ptr(labels), M, batches, float(kappa),
+                                   ptr(out), ptr(iters), ptr(ws), nb, stream_ptr()), 'fiode_certify_grid')
+    return (out, iters) if return_iters else out
+
+
+class SolveResult:
+    """Device-resident result of one dopri5 solve.  ``stats()`` is the only host sync."""
+    ERRORS = {1: 'underflow in dt {}', 2: 'non-finite values in state `y`', 3: 'max_num_steps exceeded'}
+
+    def __init__(self, out, stats_buf):
+        self.out = out
+        self._buf = stats_buf
+        self._stats = None
+
+    def stats(self) -> SolveStats:
+        if self._stats is None:
+            raw = self._buf.cpu().numpy().tobytes()
+            self._stats = SolveStats.from_buffer_copy(raw[:C.sizeof(SolveStats)])
+        return self._stats
+
+    def raise_for_status(self):
+        st = self.stats()
+        if st.status:   # same exception type and message as torchdiffeq 0.2.2
+            raise AssertionError(self.ERRORS[st.status].format(st.last_dt))
+        return self
+
+
+def dopri5_simplex(dw: DynWeights, h0, s, t, rtol, atol, max_num_steps=2 ** 31 - 1, rows_per_cta=0):
+    """Device-resident adaptive dopri5 over the simplex dynamics (replaces torchdiffeq.odeint at
+    models.py:236-241).  h0 (B,10); s (1|B,10); t 1-D fp64 (device).  Returns SolveResult with
+    out (len(t), B, 10)."""
+    h0, s = _f32(h0), _f32(s)
+    B = h0.shape[0]
+    t = t.detach().to(device=h0.device, dtype=torch.float64).contiguous()
+    nt = t.numel()
+    out = torch.empty(nt, B, NH, dtype=torch.float32, device=h0.device)
+    stats = torch.zeros(C.sizeof(SolveStats), dtype=torch.uint8, device=h0.device)
+    nb = lib().fiode_dopri5_workspace_bytes(B)
+    ws = _ws(nb, h0.device)
+    check(lib().fiode_dopri5_simplex(C.byref(dw), ptr(h0), ptr(s), s.shape[0], B, ptr(t), nt, float(rtol), float(atol),
+                                     int(max_num_steps), ptr(out), ptr(stats), ptr(ws), nb, int(rows_per_cta),
+                                     stream_ptr()), 'fiode_dopri5_simplex')
+    return SolveResult(out, stats)

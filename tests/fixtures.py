@@ -66,3 +66,27 @@ def simplex_rows(N, seed=7, off_simplex=0.0):
     if off_simplex:
         h = h + off_simplex * (torch.rand(N, 10, generator=g) - 0.5)
     return h
+
+
+MU = (0.485, 0.456, 0.406)
+STD = (0.225, 0.225, 0.225)
+
+
+def build_b200_model(sd, device='cuda', t_max=1.0, **dyn_kw):
+    """The fiode_b200 module tree assembled like the reference's ``module.model`` (an IVP) and loaded
+    from a reference-layout state_dict -- exercises the checkpoint-key compatibility too."""
+    import torch
+    from fiode_b200 import models
+    from fiode_b200.dynamics.classification import OrthoClassDynProjectSimplexLips
+    from fiode_b200.dynamics.init_coordinates import UniformInitFun
+    kw = dict(n_hidden=10, activation='ReLU', mlp_size=128, alpha_1=100., alpha_2=20., sigma_1=0.02, x_dim=10,
+              cayley=True, dropout=0.5, scale_nominal=False, kappa=2.0, kappa_length=0)
+    kw.update(dyn_kw)
+    param_map = models.make_ortho_KWLarge_Concat(3, 10, mu=MU, std=STD, out_dim=10, act='GroupSort')
+    dyn = OrthoClassDynProjectSimplexLips(**kw)
+    ivp = models.IVP(3072, 10, dyn, UniformInitFun((10,), param_map=param_map), ts=torch.linspace(0., t_max, 2))
+    own = {k[len('model.'):]: v for k, v in sd.items() if k.startswith('model.')}
+    missing, unexpected = ivp.load_state_dict(own, strict=False)
+    assert not unexpected, unexpected
+    assert all('static_state' in m for m in missing), missing
+    return ivp.to(device).eval()

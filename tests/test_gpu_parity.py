@@ -1,0 +1,253 @@
+"""Parity of the CUDA path (through the C ABI, via fiode_b200.ops / the mirrored modules) against the
+oracle and the golden vectors produced by the reference's own modules.  Runs on the B200 box:
+nothing here reads /root/reference.  Tolerances: fp32 rtol 1e-4 (BASELINE north_star), identical
+accepted/rejected step counts, identical verdicts outside the stated margin."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import layers as ol, dynamics as od, certify as oc, dopri5 as odp
+from tests import fixtures as fx
+
+pytestmark = pytest.mark.gpu
+PM, DYN = fx.PM, fx.DYN
+DEV = 'cuda'
+
+
+@pytest.fixture(scope='module')
+def ops():
+    from fiode_b200 import ops as _ops
+    return _ops
+
+
+@pytest.fixture(scope='module')
+def ivp(sd):
+    return fx.build_b200_model(sd)
+
+
+def dev(t):
+    return t.to(DEV)
+
+
+# ---- Cayley weight preparation ------------------------------------------------------------------
+@pytest.mark.parametrize('shape', [(128, 10), (10, 128), (128, 128), (10, 512), (512, 512), (512, 4096), (32, 128)])
+def test_cayley_linear(ops, shape):
+    g = torch.Generator().manual_seed(shape[0] * 7 + shape[1])
+    W = (torch.rand(shape, generator=g) * 2 - 1) / math.sqrt(shape[1])
+    alpha = W.norm() * 1.25
+    want = ol.cayley_linear_Q(W, alpha)
+    got = ops.cayley_linear(dev(W), dev(alpha)).cpu()
+    assert (got - want).abs().max() < 2e-6, (got - want).abs().max()
+    small = min(shape)
+    gram = got.T @ got if shape[0] >= shape[1] else got @ got.T
+    assert (gram - torch.eye(small)).abs().max() < 2e-5        # orthogonality invariant
+
+
+def test_cayley_known_answers(ops):
+    g = fx.load_golden('layers.pt')['cayley']
+    from fiode_b200.layers import cayley
+    for name in ('real_128x10', 'real_10x128', 'real_128x128'):
+        got = cayley(dev(g[name]['W'])).cpu()
+        assert (got - g[name]['Q']).abs().max() < 2e-6, name
+
+
+def test_cayley_conv_spectra(ops, sd):
+    for idx, _stride, n in ol.CONV_LAYERS:
+        w = sd[PM + f'1.model.{idx}.weight']
+        a0 = ops.conv_alpha_init(dev(w), n).cpu()
+        assert abs(float(a0) - float(sd[PM + f'1.model.{idx}.alpha'])) <= 2e-6 * float(a0)
+        alpha = sd[PM + f'1.model.{idx}.alpha'] * 0.9
+        want = ol.cayley_conv_Q(w, alpha, n)
+        got = ops.cayley_conv(dev(w), dev(alpha), n).cpu()
+        if w.shape[-1] == 1:                       # frequency independent and real (App. C-1)
+            assert want.imag.abs().max() < 1e-6
+            assert (got[None] - want.real).abs().max() < 3e-6, idx
+        else:
+            assert (torch.view_as_real(got) - torch.view_as_real(want)).abs().max() < 3e-6, idx
+
+
+# ---- backbone ---------------------------------------------------------------------------------------
+def test_backbone_layers_match_reference(ops, ivp):
+    g = fx.load_golden('layers.pt')
+    acts = g['acts']
+    pm = ivp.init_coordinates.param_map
+    m = pm[1].model
+    h = dev(acts['normalize'])
+    for idx in (0, 2, 4, 6):
+        pre = m[idx](h).cpu()
+        torch.testing.assert_close(pre, acts[f'model.{idx}'], rtol=1e-4, atol=2e-5)
+        h2 = m[idx](h, group_sort=True)
+        torch.testing.assert_close(h2.cpu(), acts[f'model.{idx + 1}'], rtol=1e-4, atol=2e-5)
+        torch.testing.assert_close(ops.group_sort(dev(acts[f'model.{idx}'])).cpu(), acts[f'model.{idx + 1}'],
+                                   rtol=0, atol=0)
+        h = dev(acts[f'model.{idx + 1}'])
+    h = h.flatten(1)
+    for idx in (9, 11):
+        torch.testing.assert_close(m[idx](h).cpu(), acts[f'model.{idx}'], rtol=1e-4, atol=2e-5)
+        h = dev(acts[f'model.{idx + 1}'])
+    torch.testing.assert_close(pm[1].fc(h).cpu(), acts['fc'], rtol=1e-4, atol=2e-5)
+    s2d = ops.space_to_depth(dev(acts['model.1'])).cpu()
+    assert torch.equal(s2d, ol.space_to_depth(acts['model.1']))
+
+
+@pytest.mark.parametrize('B', [1, 8, 300])
+def test_backbone_fused(ops, ivp, sd, B):
+    g = fx.load_golden('layers.pt')
+    x = fx.synth_images(B)
+    s = ivp.init_coordinates.param_map(dev(x)).cpu()
+    if B == 8:
+        torch.testing.assert_close(s, g['s8'], rtol=1e-4, atol=2e-5)
+    want = ol.backbone_forward(x[:16], sd, PM)
+    torch.testing.assert_close(s[:16], want[:B], rtol=1e-4, atol=2e-5)
+    if B > 16:    # slab tail: the same image must give the same feature wherever it sits in the batch
+        s_tail = ivp.init_coordinates.param_map(dev(x[-5:].contiguous())).cpu()
+        torch.testing.assert_close(s_tail, s[-5:], rtol=1e-5, atol=2e-6)
+
+
+# ---- right-hand side ----------------------------------------------------------------------------------
+@pytest.mark.parametrize('sn', [False, True])
+def test_rhs_matches_reference(ops, sd, sn):
+    g = fx.load_golden('rhs.pt')[f'sn{int(sn)}']
+    dyn = fx.build_b200_model(sd, scale_nominal=sn).dyn_fun
+    f_rows = dyn.eval_dot_light(dev(g['h']), dev(g['s_rows'])).cpu()
+    f_one = dyn.eval_dot(0.0, (dev(g['h']),), dev(g['s_one'])).cpu()
+    raw = dyn._h_dot_raw(dev(g['h']), dev(g['s_rows'])).cpu()
+    torch.testing.assert_close(raw, g['raw'], rtol=1e-4, atol=1e-5)
+    # values are O(alpha_1) = O(100): rtol 1e-4 plus the projection's own stop tolerance 1e-4
+    torch.testing.assert_close(f_rows, g['f_rows'], rtol=1e-4, atol=2e-4)
+    torch.testing.assert_close(f_one, g['f_one'], rtol=1e-4, atol=2e-4)
+    assert f_rows.sum(1).abs().max() < 1e-4 + 1e-5
+    lower = -100. * (torch.exp(0.02 * g['h']) - 1)
+    assert (f_rows >= lower - 1e-6).all()
+    # same number of bisection iterations as the reference's batch-global stop rule
+    _, n_it = od.eval_dot(g['h'], g['s_rows'], sd, fx.dyn_cfg(scale_nominal=sn), None, DYN, return_iters=True)
+    got_it = int(ops.rhs_fwd(dyn.dyn_weights(), dev(g['h']), dev(g['s_rows']), return_aux=True)[3].item())
+    assert abs(got_it - n_it) <= 1, (got_it, n_it)
+
+
+def test_rhs_grouped_static_state(ops, sd):
+    """compute_loss expands static_state as s[:, None].expand(-1, S, -1).flatten(0, 1) (pl_modules.py:395-400)."""
+    dyn = fx.build_b200_model(sd).dyn_fun
+    B, S = 5, 77
+    h = fx.simplex_rows(B * S, seed=21)
+    s = torch.randn(B, 10, generator=torch.Generator().manual_seed(22)) * 0.5
+    s_rows = s[:, None].expand(-1, S, -1).flatten(0, 1).contiguous()
+    a = ops.rhs_fwd(dyn.dyn_weights(), dev(h), dev(s), s_group=S).cpu()
+    b = ops.rhs_fwd(dyn.dyn_weights(), dev(h), dev(s_rows)).cpu()
+    want = od.eval_dot(h, s_rows, sd, fx.dyn_cfg(), None, DYN)
+    torch.testing.assert_close(a, want, rtol=1e-4, atol=2e-4)
+    torch.testing.assert_close(b, want, rtol=1e-4, atol=2e-4)
+
+
+def test_rhs_large_invariants(ops, sd):
+    """Size-independent properties at certification scale (1M rows): sum f = 0, f >= lower."""
+    dyn = fx.build_b200_model(sd).dyn_fun
+    h = dev(fx.simplex_rows(1 << 20, seed=31))
+    s = dev(torch.randn(1, 10, generator=torch.Generator().manual_seed(32)) * 0.5)
+    f = dyn.eval_dot_light(h, s)
+    assert float(f.sum(1).abs().max()) < 1e-4 + 2e-5
+    assert bool((f >= -100. * (torch.exp(0.02 * h) - 1) - 1e-5).all())
+    sub = slice(123456, 123456 + 64)      # the same rows evaluated alone agree up to the stop tolerance
+    f_sub = dyn.eval_dot_light(h[sub].contiguous(), s)
+    torch.testing.assert_close(f_sub, f[sub], rtol=1e-4, atol=2e-4)
+
+
+def test_projection_forward_backward(ops):
+    g = fx.load_golden('rhs.pt')['proj']
+    from fiode_b200.barrier_projection import FastBarrierProjectionNoUpper, FastBarrierProjection
+    lo, no = dev(g['lower']).requires_grad_(True), dev(g['nominal']).requires_grad_(True)
+    v = FastBarrierProjectionNoUpper(max_iter=30, tol=1e-4, verbose=False)(lo, no)
+    assert torch.equal(v.detach().cpu(), g['v'])                      # same fp32 operations, same order
+    v.backward(dev(g['gout']))
+    torch.testing.assert_close(lo.grad.cpu(), g['d_lower'], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(no.grad.cpu(), g['d_nominal'], rtol=1e-5, atol=1e-6)
+    v_up = FastBarrierProjection(max_iter=30, tol=1e-4)(dev(g['lower']), dev(g['upper']), dev(g['nominal']))
+    assert torch.equal(v_up.cpu(), g['v_upper'])
+
+
+# ---- dopri5 --------------------------------------------------------------------------------------------
+@pytest.mark.parametrize('case', ['c2_b256_tol1e-3', 'c5_b64_tol1e-5', 'c5_b64_tol1e-2', 'stress_a', 'stress_b'])
+def test_ivp_matches_reference(sd, case):
+    c = fx.load_golden('ivp.pt')[case]
+    ivp = fx.build_b200_model(sd, t_max=c['t_max'], **c['kw'])
+    x = dev(fx.synth_images(c['B']))
+    from fiode_b200.odeint import odeint
+    s, state = ivp.init_coordinates(x, ivp.dyn_fun)
+    torch.testing.assert_close(s.cpu(), c['s'], rtol=1e-4, atol=2e-5)
+    ivp.dyn_fun.static_state = s
+    ts = torch.linspace(0., c['t_max'], 2)
+    res = odeint(ivp.h_dot, state, ts, rtol=c['tol'], atol=c['tol'], method='dopri5', return_result=True)
+    st, want = res.stats(), c['stats']
+    assert (st.n_accept, st.n_reject, st.nfe) == (want['n_accept'], want['n_reject'], want['nfe']), \
+        (st.n_accept, st.n_reject, st.nfe, list(st.ratios[:st.n_logged]), want['ratios'])
+    n = min(st.n_logged, len(want['dts']))
+    np.testing.assert_allclose(np.array(st.dts[:n]), np.array(want['dts'][:n]), rtol=2e-3)
+    y = res.out[-1].cpu()
+    torch.testing.assert_close(y, c['y'], rtol=1e-4, atol=2e-5)
+    assert torch.equal(res.out[0].cpu(), state[0].cpu())
+    # the module-level call (IVP.forward) gives the same thing
+    y2 = ivp(x, ts=ts, int_params=dict(method='dopri5', rtol=c['tol'], atol=c['tol']))
+    assert torch.equal(y2.cpu(), y)
+
+
+def test_ivp_rows_per_cta_invariance(sd):
+    """The batch-global norm and stop rule make the result independent of how rows are split over CTAs."""
+    ivp = fx.build_b200_model(sd)
+    from fiode_b200 import ops
+    x = dev(fx.synth_images(96))
+    s, state = ivp.init_coordinates(x, ivp.dyn_fun)
+    t = torch.tensor([0., 0.4, 1.0], dtype=torch.float64)
+    outs = [ops.dopri5_simplex(ivp.dyn_fun.dyn_weights(), state[0], s, t, 1e-4, 1e-4, rows_per_cta=r) for r in (1, 7, 64)]
+    for o in outs[1:]:
+        assert o.stats().nfe == outs[0].stats().nfe
+        torch.testing.assert_close(o.out, outs[0].out, rtol=1e-6, atol=1e-7)
+    want = od.ivp_forward(fx.synth_images(96), sd, fx.dyn_cfg(), t_max=1.0, tol=1e-4, t_steps=3, return_traj=True)
+    t3 = torch.linspace(0., 1., 3)
+    assert abs(float(t3[1]) - 0.5) < 1e-6
+    out2 = ops.dopri5_simplex(ivp.dyn_fun.dyn_weights(), state[0], s, t3, 1e-4, 1e-4)
+    torch.testing.assert_close(out2.out.cpu(), want[0], rtol=1e-4, atol=2e-5)
+
+
+def test_dopri5_error_status(sd):
+    ivp = fx.build_b200_model(sd)
+    from fiode_b200 import ops
+    h0 = torch.full((4, 10), float('nan'), device=DEV)
+    s = torch.zeros(1, 10, device=DEV)
+    res = ops.dopri5_simplex(ivp.dyn_fun.dyn_weights(), h0, s, torch.tensor([0., 1.]), 1e-3, 1e-3)
+    with pytest.raises(AssertionError):
+        res.raise_for_status()
+    h0 = torch.full((4, 10), 0.1, device=DEV)
+    res = ops.dopri5_simplex(ivp.dyn_fun.dyn_weights(), h0, s, torch.tensor([0., 1.]), 1e-9, 1e-9, max_num_steps=3)
+    with pytest.raises(AssertionError, match='max_num_steps exceeded'):
+        res.raise_for_status()
+
+
+# ---- certification --------------------------------------------------------------------------------------
+@pytest.mark.parametrize('key', ['T10_sn0_shift0.0', 'T10_sn1_shift0.0', 'T20_sn0_shift14.0', 'T20_sn0_shift1.5'])
+def test_certify_matches_reference(ops, sd, key):
+    c = fx.load_golden('certify.pt')[key]
+    sd2 = dict(sd)
+    if c['shift']:
+        e = torch.zeros(10); e[3] = 1.0
+        sd2[DYN + 'mlp_to_hidden.bias'] = sd[DYN + 'mlp_to_hidden.bias'] + c['shift'] * (e - 0.1)
+    dyn = fx.build_b200_model(sd2, scale_nominal=c['scale_nominal']).dyn_fun
+    z = oc.boundary_grid_numerators(10, c['T'])
+    gz = dev(torch.from_numpy(z.astype(np.uint8)))
+    out = ops.certify_grid(dyn.dyn_weights(), gz, c['T'], dev(c['s']), dev(c['labels']), c['kappa'],
+                           batches=c['batches']).cpu().double()
+    want = c['out']
+    # grid row order differs from the reference's DP order -> chunk-global bisection stops differ:
+    # values agree to the projection tolerance; verdicts agree outside it (margin-listed otherwise)
+    close = (want[:, 0].abs() <= 3e-4)
+    assert (out - want).abs().max() < 3e-4 + 1e-4 * want.abs().max(), (out, want)
+    assert torch.equal((out[:, 0] < 0)[~close], (want[:, 0] < 0)[~close])
+    # and against the oracle run on the SAME row order: chunk stop iterations must agree too
+    cfg = fx.dyn_cfg(scale_nominal=c['scale_nominal'])
+    Q = od.dyn_Q(sd2, DYN)
+    for m in (0, 3):
+        label = int(c['labels'][m])
+        v1, v2 = oc.certify_image(oc.grid_for_label(z, c['T'], label), c['s'][m:m + 1], label, sd2, cfg, eps=c['eps'],
+                                  T=c['T'], batches=c['batches'], prefix=DYN, Q=Q)
+        assert abs(float(out[m, 0]) - v1) < 2e-4 + 1e-4 * abs(v1) and abs(float(out[m, 1]) - v2) < 2e-4 + 1e-4 * abs(v2)
