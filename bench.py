@@ -1,0 +1,381 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the FI-ODE hot path on B200 (contract: see README / DESIGN.md).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1]): CIFAR-10 Cayley ortho-conv neural ODE inference, dopri5
+rtol=atol=1e-3, t_max=1, batch 256, synthetic 3x32x32 inputs, random-init weights.  One *step* is one
+pass of the hot path over ``--solves-per-step`` independent batch-256 solves (each keeps its own
+batch-wide RMS error norm and batch-global projection stop rule, exactly like one reference call);
+metric = batch-256 ODE solves per second, whole job.  A secondary ``certify`` object reports the
+certify_lipschitz grid-check throughput (grid points x images per second).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+METRIC = 'ODE-solves/s (CIFAR dopri5 b=256)'
+UNIT = 'batch-256 solves/s'
+B = 256
+TOL = 1e-3
+T_MAX = 1.0
+MU = (0.485, 0.456, 0.406)
+STD = (0.225, 0.225, 0.225)
+RHS_FLOP = 37888                     # per row per RHS evaluation
+BACKBONE_FLOP = 1.31e7               # per image, minimal algorithm
+FFMA_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12     # fp32 FFMA pipe at max clock, for context
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return dict(hbm=d['hbm_gbs'], bf16=d['bf16_tflops'], bf16_sustained=d.get('bf16_tflops_sustained'),
+                    source='measured')
+    return dict(hbm=6650.0, bf16=1590.0, bf16_sustained=1400.0, source='fallback')
+
+
+# ---- synthetic model ------------------------------------------------------------------------------
+def build_model(device, scale_nominal=False):
+    """Random-init weights of the named architecture under torch.manual_seed(0), built through the
+    fiode_b200 module tree (same constructors / init distributions as the reference classes)."""
+    from fiode_b200 import models
+    from fiode_b200.dynamics.classification import OrthoClassDynProjectSimplexLips
+    from fiode_b200.dynamics.init_coordinates import UniformInitFun
+    torch.manual_seed(0)
+    param_map = models.make_ortho_KWLarge_Concat(3, 10, mu=MU, std=STD, out_dim=10, act='GroupSort')
+    dyn = OrthoClassDynProjectSimplexLips(n_hidden=10, activation='ReLU', mlp_size=128, alpha_1=100., alpha_2=20.,
+                                          sigma_1=0.02, x_dim=10, cayley=True, dropout=0.5,
+                                          scale_nominal=scale_nominal, kappa=2.0, kappa_length=0)
+    ivp = models.IVP(3072, 10, dyn, UniformInitFun((10,), param_map=param_map), ts=torch.linspace(0., T_MAX, 2))
+    return ivp.to(device).eval()
+
+
+def cpu_state_dict(ivp):
+    """Reference-layout state_dict (CPU) of the benchmark model, for the oracle / CPU baseline."""
+    return {'model.' + k: v.detach().cpu() for k, v in ivp.state_dict().items() if v is not None}
+
+
+class ClockSampler:
+    QUERY = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
+             'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+             'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index = index
+        self.f = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(['nvidia-smi', f'--query-gpu={self.QUERY}', '--format=csv,noheader,nounits',
+                                       '-i', str(self.index), '-lms', '100'], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=['nvidia-smi unavailable'])
+        time.sleep(0.15)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        rows = [r.split(',') for r in open(self.f.name).read().strip().splitlines() if r.count(',') >= 8]
+        os.unlink(self.f.name)
+        if not rows:
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=['no samples'])
+        sm = sorted(float(r[1]) for r in rows)
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = [n for i, n in enumerate(names) if any('Active' in r[5 + i] and 'Not' not in r[5 + i] for r in rows)]
+        return dict(sm_mhz=sm[len(sm) // 2], sm_max_mhz=float(rows[0][2]), reasons=reasons, samples=len(rows),
+                    power_w_max=max(float(r[3]) for r in rows))
+
+
+# ---- reference arm (CPU) ----------------------------------------------------------------------------
+def cpu_solve_rate(sd, n_solves, threads):
+    """The oracle port of the reference path (backbone + restated torchdiffeq dopri5) on host cores."""
+    from oracle import dynamics as od
+    torch.set_num_threads(threads)
+    cfg = dict(alpha_1=100., alpha_2=20., sigma_1=0.02, scale_nominal=False)
+    g = torch.Generator().manual_seed(1234)
+    x = torch.rand(B, 3, 32, 32, generator=g)
+    od.ivp_forward(x, sd, cfg, t_max=T_MAX, tol=TOL)          # warm-up
+    t0 = time.perf_counter()
+    for _ in range(n_solves):
+        od.ivp_forward(x, sd, cfg, t_max=T_MAX, tol=TOL)
+    dt = time.perf_counter() - t0
+    return n_solves / dt, dt
+
+
+def reference_state_dict():
+    """Weights for the CPU arm without touching the GPU: same constructors, same seed."""
+    from tests import fixtures as fx
+    return fx.synth_state_dict()
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    sd = reference_state_dict()
+    per_step = 2
+    t_all = []
+    from oracle import dynamics as od
+    torch.set_num_threads(threads)
+    cfg = dict(alpha_1=100., alpha_2=20., sigma_1=0.02, scale_nominal=False)
+    x = torch.rand(B, 3, 32, 32, generator=torch.Generator().manual_seed(1234))
+    for i in range(args.warmup + args.steps):
+        t0 = time.perf_counter()
+        for _ in range(per_step):
+            od.ivp_forward(x, sd, cfg, t_max=T_MAX, tol=TOL)
+        if i >= args.warmup:
+            t_all.append(time.perf_counter() - t0)
+    total = sum(t_all)
+    value = per_step * args.steps / total
+    line = dict(metric=METRIC, value=value, unit=UNIT, impl='reference', n_gpus=args.gpus, steps=args.steps,
+                warmup=args.warmup, ms_per_step=1e3 * total / args.steps, higher_is_better=True, scaling='weak',
+                vs_baseline=None, dtype='f32', data='synthetic',
+                config=dict(workload='cifar_cayley_node_inference_dopri5_b256_tol1e-3_tmax1', batch=B,
+                            solves_per_step=per_step, note='oracle port of the reference path on host cores '
+                            '(reference checkout and torchdiffeq absent on the GPU box)'),
+                cpu_baseline=dict(value=value, unit=UNIT, cores=threads, kind='port',
+                                  sample=f'{per_step} batch-256 solves per step x {args.steps} steps'),
+                e2e=dict(value=value, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+    print(json.dumps(line))
+
+
+# ---- B200 arm -------------------------------------------------------------------------------------------
+def timed(fn, iters, stream=None):
+    """CUDA-event time (ms) of ``iters`` calls of fn on the current stream."""
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1)
+
+
+def certify_bench(ivp, device, pk, iters=3):
+    """Secondary metric: certify_lipschitz grid check, M images x the T=20 decision-boundary grid."""
+    from fiode_b200 import ops, grid as fgrid
+    import fiode_b200
+    T, M = 20, 296
+    gz = fgrid.boundary_grid_numerators(10, T, device=device)
+    g = torch.Generator().manual_seed(1236)
+    s = (torch.randn(M, 10, generator=g) * 0.5).to(device)
+    labels = torch.randint(0, 10, (M,), generator=g).to(device)
+    kappa = math.sqrt(2) * (1 / 0.225) * 0.141
+    dw = ivp.dyn_fun.dyn_weights()
+    fn = lambda: ops.certify_grid(dw, gz, T, s, labels, kappa, batches=10)
+    fn(); fn()
+    c0 = fiode_b200.launch_count()
+    ms = timed(fn, iters) / iters
+    launches = (fiode_b200.launch_count() - c0) // iters
+    units = M * gz.shape[0]
+    tf = units * RHS_FLOP / (ms * 1e-3) / 1e12
+    return dict(metric='certified grid pts/s (certify_lipschitz, image x grid-point pairs)', value=units / (ms * 1e-3),
+                unit='grid pts/s', workload=f'grid_{T} ({gz.shape[0]} pts/label) x {M} images, L2 norm, batches=10',
+                ms=ms, gpu_launches=launches,
+                roofline=dict(bound='tensor', achieved=tf, peak=pk['bf16'], unit='TFLOP/s', frac=tf / pk['bf16'],
+                              traffic=None, peak_source=pk['source'],
+                              note='fp32 FFMA kernel: %.3f of the %.1f TFLOP/s fp32 FFMA pipe' % (tf / FFMA_PEAK_TFLOPS,
+                                                                                                  FFMA_PEAK_TFLOPS)))
+
+
+def run_b200(args):
+    import torch.distributed as dist
+    import fiode_b200
+    from fiode_b200 import ops
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    assert torch.cuda.is_available(), 'bench.py needs a CUDA device (there is no CPU fallback)'
+    torch.cuda.set_device(local)
+    device = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=device)
+    pk = peaks()
+    G = args.solves_per_step
+    ivp = build_model(device)
+    ts = torch.linspace(0., T_MAX, 2)
+    int_params = dict(method='dopri5', rtol=TOL, atol=TOL, options=dict(check=False))
+
+    # inputs: NBUF rotating device-resident sets, together larger than the 126 MB L2
+    per_set = G * B * 3 * 32 * 32 * 4
+    NBUF = max(2, int(math.ceil(160e6 / per_set)))
+    gen = torch.Generator().manual_seed(1234 + rank)
+    x_host = [torch.rand(G, B, 3, 32, 32, generator=gen).pin_memory() for _ in range(min(NBUF, 2))]
+    x_dev = [x_host[i % len(x_host)].to(device) + 0 for i in range(NBUF)]
+    y_dev = torch.empty(G, B, 10, device=device)
+    y_host = torch.empty(G, B, 10).pin_memory()
+
+    def step(xs, out):
+        for g_ in range(G):
+            out[g_] = ivp(xs[g_], ts=ts, int_params=int_params)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing (value) ------------------------------------------------------------
+    for i in range(args.warmup):
+        step(x_dev[i % NBUF], y_dev)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    fiode_b200.reset_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        step(x_dev[i % NBUF], y_dev)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    launches = fiode_b200.launch_count()
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms], device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max = float(t.item())
+    value = world * G * args.steps / (ms_max * 1e-3)
+
+    # ---- end to end through the public API with host buffers (e2e) ------------------------------
+    def e2e_step(i):
+        xd = x_dev[i % NBUF]
+        xd.copy_(x_host[i % len(x_host)], non_blocking=True)
+        step(xd, y_dev)
+        y_host.copy_(y_dev, non_blocking=True)
+        torch.cuda.synchronize()                       # the caller needs the result on the host
+    for i in range(max(1, args.warmup // 2)):
+        e2e_step(i)
+    barrier()
+    t0 = time.perf_counter()
+    e0.record()
+    for i in range(args.steps):
+        e2e_step(i)
+    e1.record()
+    torch.cuda.synchronize()
+    e2e_ms = e0.elapsed_time(e1)
+    t = torch.tensor([e2e_ms], device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * G * args.steps / (float(t.item()) * 1e-3)
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # ---- per-kernel shares and the roofline of the dominant kernel (rank 0, same stream) ----------
+    x1 = x_dev[0][0]
+    s, state = ivp.init_coordinates(x1, ivp.dyn_fun)
+    ivp.dyn_fun.static_state = s
+    dw = ivp.dyn_fun.dyn_weights()
+    t_dev = ts.to(device=device, dtype=torch.float64)
+    res = ops.dopri5_simplex(dw, state[0], s, t_dev, TOL, TOL)
+    st = res.stats()
+    it = 50
+    ms_solve = timed(lambda: ops.dopri5_simplex(dw, state[0], s, t_dev, TOL, TOL), it) / it
+    pm = ivp.init_coordinates.param_map
+    bw, keep = pm.backbone_weights()
+    xs = [x_dev[i % NBUF][j] for i in range(NBUF) for j in range(G)]
+    cnt = [0]
+
+    def bb():
+        ops.backbone_fwd(bw, xs[cnt[0] % len(xs)]); cnt[0] += 1
+    bb(); bb()
+    ms_bb = timed(bb, it) / it
+    solve_flop = st.nfe * RHS_FLOP * B
+    bb_flop = BACKBONE_FLOP * B
+    tf_solve = solve_flop / (ms_solve * 1e-3) / 1e12
+    tf_bb = bb_flop / (ms_bb * 1e-3) / 1e12
+    dominant = 'dopri5_simplex_kernel' if ms_solve >= ms_bb else 'backbone (10 kernels; top: gemm_nt_kernel 4096->512)'
+    tf = tf_solve if ms_solve >= ms_bb else tf_bb
+    roofline = dict(bound='tensor', achieved=tf, peak=pk['bf16'], unit='TFLOP/s', frac=tf / pk['bf16'], traffic=None,
+                    kernel=dominant, peak_source=pk['source'],
+                    note='fp32 FFMA kernels (no tensor-core use yet): %.3f of the %.1f TFLOP/s fp32 FFMA pipe; the '
+                         'b=256 solve is latency-bound (%.0f dependent RHS evaluations)' % (
+                             tf / FFMA_PEAK_TFLOPS, FFMA_PEAK_TFLOPS, st.nfe),
+                    parts=dict(dopri5_ms=ms_solve, dopri5_tflops=tf_solve, backbone_ms=ms_bb, backbone_tflops=tf_bb,
+                               nfe=st.nfe, n_accept=st.n_accept, n_reject=st.n_reject))
+
+    # ---- CPU baseline beside it (bounded sample) ----------------------------------------------------
+    cpu = None
+    if not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        n_cpu = 6
+        rate, secs = cpu_solve_rate(cpu_state_dict(ivp), n_cpu, threads)
+        cpu = dict(value=rate, unit=UNIT, cores=threads, kind='port',
+                   sample=f'{n_cpu} batch-256 solves (backbone + dopri5) in {secs:.1f} s on the same weights')
+        # and the answer check that makes the timing meaningful
+        from oracle import dynamics as od
+        xc = x_host[0][0]
+        want = od.ivp_forward(xc, cpu_state_dict(ivp), dict(alpha_1=100., alpha_2=20., sigma_1=0.02, scale_nominal=False),
+                              t_max=T_MAX, tol=TOL)
+        got = ivp(xc.to(device), ts=ts, int_params=int_params).cpu()
+        cpu['max_abs_diff_vs_cuda'] = float((got - want).abs().max())
+
+    cert = None
+    if not args.no_certify:
+        try:
+            cert = certify_bench(ivp, device, pk)
+        except Exception as e:       # secondary metric must not take the headline down
+            cert = dict(error=repr(e))
+
+    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
+                ms_per_step=ms_max / args.steps, higher_is_better=True, scaling='weak', vs_baseline=None,
+                dtype='f32', data='synthetic',
+                config=dict(workload='cifar_cayley_node_inference_dopri5_b256_tol1e-3_tmax1', batch=B,
+                            solves_per_step=G, images_per_step=G * B, rtol=TOL, atol=TOL, t_max=T_MAX,
+                            weights='random init, seed 0', l2='inputs rotate over %d device buffers (%.0f MB > L2)' % (
+                                NBUF, NBUF * per_set / 1e6), parallelism=f'independent batches x{world}'),
+                images_per_s=value * B,
+                e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=per_set, d2h_bytes_per_step=G * B * 10 * 4),
+                gpu_launches=launches, clocks=clocks, roofline=roofline, cpu_baseline=cpu, certify=cert)
+    print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--solves-per-step', type=int, default=16)
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-certify', action='store_true')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == '__main__':
+    main()

@@ -66,6 +66,9 @@ SIGNATURES = {
     'fiode_barrier_project_bwd': (I, [P, P, P, P, LL, P, P, P]),
     'fiode_certify_workspace_bytes': (SZ, [I, I]),
     'fiode_certify_grid': (I, [C.POINTER(DynWeights), P, LL, I, P, P, P, I, I, F32, P, P, P, SZ, P]),
+    'fiode_grid_count': (LL, [I, I]),
+    'fiode_grid_workspace_bytes': (SZ, [I, I]),
+    'fiode_grid_enumerate': (I, [I, I, LL, LL, P, P, SZ, P]),
     'fiode_dopri5_workspace_bytes': (SZ, [I]),
     'fiode_dopri5_simplex': (I, [C.POINTER(DynWeights), P, P, I, I, P, I, F64, F64, LL, P, P, P, SZ, I, P]),
 }

@@ -118,6 +118,20 @@ __device__ __forceinline__ int stop_iter(unsigned notconv_or, int max_iter) {
     return conv ? (__ffs(conv) - 1) : (max_iter - 1);
 }
 
-__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + expf(-x)); }
+// exp rounded correctly to fp32 (via fp64).  `lower` = -alpha_1 (e^{sigma_1 h} - 1) cancels ~9 bits, so a
+// 1-ulp difference in exp moves it by ~1e-5: the correctly rounded value is the one every
+// libm-quality reference path (torch CPU: SLEEF u10) agrees on.  B200 fp64 rate makes this cheap.
+__device__ __forceinline__ float exp_cr(float x) { return (float)exp((double)x); }
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.f / (1.f + exp_cr(-x)); }
+// dynamics/classification.py:108: lower = -alpha_1 * (exp(sigma_1 * h) - 1)
+__device__ __forceinline__ float barrier_lower(float alpha_1, float sigma_1, float h) {
+    return -alpha_1 * (exp_cr(sigma_1 * h) - 1.f);
+}
+// classification.py:109-111: f = (upper - lower) * sigmoid(f) + lower, upper = alpha_2 (1 - h); separate
+// roundings like the reference's separate torch ops (no FMA contraction)
+__device__ __forceinline__ float scale_nominal_f(float alpha_2, float h, float lo, float f) {
+    const float up = alpha_2 * (1.f - h);
+    return __fadd_rn(__fmul_rn(up - lo, sigmoidf_(f)), lo);
+}
 
 }  // namespace fiode

@@ -177,11 +177,10 @@ __device__ __forceinline__ void eval_rhs(const SolveArgs& a, const Smem& S, int 
 #pragma unroll
         for (int i = 0; i < NH; ++i) {
             const float h = S.ys[t * SROW + i];
-            lo[i] = -a.w.alpha_1 * (expf(a.w.sigma_1 * h) - 1.f);
+            lo[i] = barrier_lower(a.w.alpha_1, a.w.sigma_1, h);
             float f = S.ft[t * SROW + i];
             if (a.w.scale_nominal) {
-                const float up = a.w.alpha_2 * (1.f - h);
-                f = (up - lo[i]) * sigmoidf_(f) + lo[i];
+                f = scale_nominal_f(a.w.alpha_2, h, lo[i], f);
                 S.ft[t * SROW + i] = f;
             }
             ft[i] = f;

@@ -225,9 +225,9 @@ __global__ void __launch_bounds__(RT, 2) rhs_rows_kernel(const RowsArgs a) {
 #pragma unroll
                 for (int i = 0; i < NH; ++i) {
                     const float h = S.hs[t * NH + i];
-                    lo[i] = -a.w.alpha_1 * (expf(a.w.sigma_1 * h) - 1.f);
+                    lo[i] = barrier_lower(a.w.alpha_1, a.w.sigma_1, h);
                     float f = S.ft[t * NH + i];
-                    if (a.w.scale_nominal) f = (a.w.alpha_2 * (1.f - h) - lo[i]) * sigmoidf_(f) + lo[i];
+                    if (a.w.scale_nominal) f = scale_nominal_f(a.w.alpha_2, h, lo[i], f);
                     ft[i] = f;
                     a.ft_out[(row0 + t) * NH + i] = f;
                 }
@@ -284,9 +284,9 @@ __global__ void __launch_bounds__(RT, 2) rhs_rows_kernel(const RowsArgs a) {
                     for (int i = 0; i < NH; ++i) {
                         const float h = S.hs[t * NH + i];
                         emax = fmaxf(emax, h);
-                        lo[i] = -a.w.alpha_1 * (expf(a.w.sigma_1 * h) - 1.f);
+                        lo[i] = barrier_lower(a.w.alpha_1, a.w.sigma_1, h);
                         float f = S.ft[t * NH + i];
-                        if (a.w.scale_nominal) f = (a.w.alpha_2 * (1.f - h) - lo[i]) * sigmoidf_(f) + lo[i];
+                        if (a.w.scale_nominal) f = scale_nominal_f(a.w.alpha_2, h, lo[i], f);
                         ft[i] = f;
                     }
                     unsigned wrong = 0;                       // certify_lipschitz.py:126-128
@@ -294,7 +294,7 @@ __global__ void __launch_bounds__(RT, 2) rhs_rows_kernel(const RowsArgs a) {
                     for (int i = 0; i < NH; ++i)
                         if (S.hs[t * NH + i] == emax && i != label) wrong |= 1u << i;
                     // certify_lipschitz.py:122-124
-                    const float Lf = a.sqrtn * (a.sa * expf(a.w.sigma_1 * (emax + a.inv_T))) + 1.f;
+                    const float Lf = __fadd_rn(__fmul_rn(a.sqrtn, a.sa * exp_cr(a.w.sigma_1 * (emax + a.inv_T))), 1.f);
                     const float perturb = (a.sqrt2 * Lf) * a.dist;
                     float hi = ft[0] - lo[0], lw = ft[0];
 #pragma unroll
@@ -352,7 +352,7 @@ __global__ void rhs_finish_kernel(const float* __restrict__ ft, const float* __r
 #pragma unroll
     for (int i = 0; i < NH; ++i) {
         v[i] = ft[r * NH + i];
-        lo[i] = -w.alpha_1 * (expf(w.sigma_1 * h[r * NH + i]) - 1.f);
+        lo[i] = barrier_lower(w.alpha_1, w.sigma_1, h[r * NH + i]);
     }
     float hi = v[0] - lo[0], lw = v[0], mu = 0.f;
 #pragma unroll

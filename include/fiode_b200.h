@@ -154,6 +154,16 @@ FIODE_API int fiode_certify_grid(const fiode_dyn_weights* w, const uint8_t* grid
                        const float* lut, const float* s, const int* labels, int M, int batches,
                        float kappa, float* out, int* iters, void* ws, size_t ws_bytes, void* stream);
 
+/* ---- decision-boundary grid -----------------------------------------------------------------------
+ * replaces robustness/eval_utils.py:31-61 sample_decision_boundary and :72-89
+ * count_samples_decision_boundary: the set { z in Z^n_{>=0} : sum z = T, z_0 = max_{i>=1} z_i } in a
+ * canonical order (by z_0, then lexicographic), as uint8 numerators (eta = z / T).  Rows
+ * [first, first + count) are written to out (count, n) -- the grid can be generated in shards.   */
+FIODE_API long long fiode_grid_count(int n, int T);
+FIODE_API size_t fiode_grid_workspace_bytes(int n, int T);
+FIODE_API int fiode_grid_enumerate(int n, int T, long long first, long long count, uint8_t* out, void* ws,
+                         size_t ws_bytes, void* stream);
+
 /* ---- device-resident adaptive dopri5 -----------------------------------------------------------
  * replaces torchdiffeq==0.2.2 odeint(func, y0, t, rtol, atol, method='dopri5') as called at
  * models.py:236-241 with func = IVP.h_dot -> dyn_fun.ode_forward (classification.py:128-132).

@@ -1,0 +1,58 @@
+"""CPU-only checks of the host side: the C-ABI library loads and exports every symbol that
+include/fiode_b200.h declares, the ctypes table covers them, host-only entry points work, and the
+product path fails loudly (no CPU fallback)."""
+import pytest
+import torch
+
+from tests import fixtures as fx
+
+
+def test_library_exports_every_declared_symbol():
+    import __graft_entry__ as ge
+    ge.build()
+    from fiode_b200 import _lib
+    L = _lib.lib()
+    declared = _lib.declared_symbols()
+    assert len(declared) >= 29
+    for name in declared:
+        assert hasattr(L, name), name
+        assert name in _lib.SIGNATURES, f'{name} has no ctypes signature'
+    assert L.fiode_version() >= 100
+    assert L.fiode_last_error() is not None
+
+
+def test_grid_count_matches_reference_counter():
+    """fiode_grid_count is host-only; the golden counts come from the reference's own
+    count_samples_decision_boundary (robustness/eval_utils.py:72-89)."""
+    from fiode_b200 import grid
+    g = fx.load_golden('certify.pt')
+    for (n, T), want in g['counts'].items():
+        assert grid.count_samples_decision_boundary(n, T) == want, (n, T)
+    assert grid.count_samples_decision_boundary(10, 40) == 41320837
+
+
+def test_no_cpu_fallback():
+    from fiode_b200 import ops, FiodeError
+    from fiode_b200.layers import CayleyLinear
+    lin = CayleyLinear(10, 128)
+    with pytest.raises(FiodeError, match='no CPU fallback'):
+        lin(torch.zeros(4, 10))
+    with pytest.raises(FiodeError):
+        ops.barrier_project_fwd(torch.zeros(4, 10), torch.zeros(4, 10))
+
+
+def test_error_string_convention():
+    from fiode_b200 import _lib
+    L = _lib.lib()
+    rc = L.fiode_grid_count(1, 40)          # n < 2 is rejected on the host, before any CUDA call
+    assert rc == -1 and b'fiode_grid_count' in L.fiode_last_error()
+
+
+def test_state_dict_keys_match_reference_layout(sd):
+    """The mirrored module tree loads a reference-layout (Lightning) state_dict: same names, same shapes."""
+    ivp = fx.build_b200_model(sd, device='cpu')
+    own = ivp.state_dict()
+    for k, v in sd.items():
+        k2 = k[len('model.'):]
+        assert k2 in own and tuple(own[k2].shape) == tuple(v.shape), k
+        assert torch.equal(own[k2], v), k
