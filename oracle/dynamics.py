@@ -118,7 +118,9 @@ def eval_dot(h, s, sd, cfg, Q=None, prefix='', masks=None, differentiable=False,
         f_t = (upper - lower) * torch.sigmoid(f_t) + lower
     if differentiable:
         return _ProjFn.apply(lower, f_t)
-    v, _mu, n_iter = project_no_upper(lower, f_t)
+    # classification.py:63-64 fixes max_iter=30, tol=1e-4; tests may run the bisection to convergence
+    # (proj_tol=0) to take its ~1e-5 quantisation of mu out of a solver comparison
+    v, _mu, n_iter = project_no_upper(lower, f_t, cfg.get('proj_max_iter', 30), cfg.get('proj_tol', 1e-4))
     return (v, n_iter) if return_iters else v
 
 
