@@ -66,6 +66,11 @@ SIGNATURES = {
     'fiode_barrier_project_bwd': (I, [P, P, P, P, LL, P, P, P]),
     'fiode_certify_workspace_bytes': (SZ, [I, I]),
     'fiode_certify_grid': (I, [C.POINTER(DynWeights), P, LL, I, P, P, P, I, I, F32, P, P, P, SZ, P]),
+    'fiode_sampler_fill': (I, [I, P, P, I, I, I, I, P, P]),
+    'fiode_fi_loss_workspace_bytes': (SZ, [LL, I]),
+    'fiode_fi_loss_fwd': (I, [C.POINTER(DynWeights), P, P, P, I, I, F32, P, P, P, P, P, P, P, P, P, P, P, SZ, P]),
+    'fiode_fi_loss_bwd': (I, [C.POINTER(DynWeights), P, P, P, I, I, F32, F32, P, P, P, P, P, P, P, P, P,
+                              P, P, P, P, P, P, P, P, P, SZ, P]),
     'fiode_grid_count': (LL, [I, I]),
     'fiode_grid_workspace_bytes': (SZ, [I, I]),
     'fiode_grid_enumerate': (I, [I, I, LL, LL, P, P, SZ, P]),

@@ -152,6 +152,82 @@ int gemm_nt(const float* A, int lda, const float* Bm, int ldb, int M, int N, int
     return 0;
 }
 
+
+// ---- "TN" GEMM: C[m][n] = sum_k A[k][m] * B[k][n]  (reductions over rows: weight gradients) -----
+// split-K over gridDim.z with deterministic partials, same epilogue as gemm_nt.
+__global__ void __launch_bounds__(256) gemm_tn_kernel(const float* __restrict__ A, int lda, const float* __restrict__ Bm,
+                                                      int ldb, int M, int N, long long K, long long k_per_split,
+                                                      float* __restrict__ part) {
+    __shared__ float As[16][64 + 4];
+    __shared__ float Bs[16][64 + 4];
+    const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
+    const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+    const long long k_begin = blockIdx.z * k_per_split, k_end = min(K, k_begin + k_per_split);
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    for (long long k0 = k_begin; k0 < k_end; k0 += 16) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int e = t + i * 256, kk = e >> 6, c = e & 63;
+            const long long k = k0 + kk;
+            As[kk][c] = (k < k_end && m0 + c < M) ? A[k * lda + m0 + c] : 0.f;
+            Bs[kk][c] = (k < k_end && n0 + c < N) ? Bm[k * ldb + n0 + c] : 0.f;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int kk = 0; kk < 16; ++kk) {
+            const float4 a = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
+            const float4 b = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+            const float av[4] = {a.x, a.y, a.z, a.w}, bv[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], bv[j], acc[i][j]);
+        }
+        __syncthreads();
+    }
+    float* dst = part + (size_t)blockIdx.z * M * N;
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int m = m0 + ty * 4 + i, n = n0 + tx * 4 + j;
+            if (m < M && n < N) dst[(size_t)m * N + n] = acc[i][j];
+        }
+}
+
+static int gemm_tn_splits(int M, int N, long long K) {
+    const int tiles = ((M + 63) / 64) * ((N + 63) / 64);
+    long long splits = (2ll * sm_count() + tiles - 1) / tiles;
+    const long long max_by_k = (K + 255) / 256;
+    if (splits > max_by_k) splits = max_by_k;
+    if (splits > 256) splits = 256;
+    if (splits < 1) splits = 1;
+    return (int)splits;
+}
+size_t gemm_tn_workspace(int M, int N, long long K) { return (size_t)gemm_tn_splits(M, N, K) * M * N * sizeof(float) + 256; }
+
+int gemm_tn(const float* A, int lda, const float* Bm, int ldb, int M, int N, long long K, float alpha, float* y, int ldy,
+            float* ws, size_t ws_bytes, cudaStream_t st) {
+    int splits = gemm_tn_splits(M, N, K);
+    if ((size_t)splits * M * N * sizeof(float) > ws_bytes) { set_error("gemm_tn: workspace too small"); return -1; }
+    long long kps = (K + splits - 1) / splits;
+    kps = (kps + 15) / 16 * 16;
+    splits = (int)((K + kps - 1) / kps);
+    dim3 grid((N + 63) / 64, (M + 63) / 64, splits);
+    gemm_tn_kernel<<<grid, 256, 0, st>>>(A, lda, Bm, ldb, M, N, K, kps, ws);
+    const size_t total = (size_t)M * N;
+    gemm_epilogue_kernel<<<(unsigned)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096), 256, 0, st>>>(
+        ws, splits, M, N, nullptr, alpha, 0, y, ldy);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "gemm_tn launch");
+    count_launch(2);
+    return 0;
+}
+
 }  // namespace fiode
 
 using namespace fiode;

@@ -34,6 +34,8 @@ struct RowsArgs {
     // kStore
     const float* h; const float* s; long long N; long long s_rows; long long s_group;
     float* ft_out; unsigned* notconv;              // (N,10), 1 word
+    const float* m1; const float* m2;              // optional dropout masks (N,128), already scaled by 1/(1-p)
+    float* z1_out; float* z2_out;                  // optional activations (N,128) for the backward
     // kCertify
     const uint8_t* gridz; const float* lut; int T; long long Ng; long long chunk; int n_chunks;
     const int* labels; int M; int P;               // images in this launch, CTAs per image
@@ -90,7 +92,10 @@ __device__ __forceinline__ void set_static_feature(const fiode_dyn_weights& w, c
 }
 
 // MLP over the tile whose h rows are in S.hs; result ftilde in S.ft ([TR][10]).
-__device__ __forceinline__ void tile_mlp(const RowsSmem& S) {
+struct TileAux {   // kStore extras (all optional): dropout masks in, activations out
+    const float* m1; const float* m2; float* z1_out; float* z2_out; long long row0; int rows;
+};
+__device__ __forceinline__ void tile_mlp(const RowsSmem& S, const TileAux aux = TileAux{nullptr, nullptr, nullptr, nullptr, 0, 0}) {
     const int t = threadIdx.x;
     // ---- L1: thread = (row pair rp / rp+32, k quarter) --------------------------------------
     {
@@ -118,11 +123,21 @@ __device__ __forceinline__ void tile_mlp(const RowsSmem& S) {
             za = fmaf(q1.w, ha[7], za); zb = fmaf(q1.w, hb[7], zb);
             za = fmaf(q2.x, ha[8], za); zb = fmaf(q2.x, hb[8], zb);
             za = fmaf(q2.y, ha[9], za); zb = fmaf(q2.y, hb[9], zb);
+            if (aux.m1) {   // classification.py:98: act(dropout(z))
+                if (rp < aux.rows) za *= aux.m1[(aux.row0 + rp) * NM + k];
+                if (rp + 32 < aux.rows) zb *= aux.m1[(aux.row0 + rp + 32) * NM + k];
+            }
             S.z1T[k * TR + rp] = fmaxf(za, 0.f);
             S.z1T[k * TR + rp + 32] = fmaxf(zb, 0.f);
         }
     }
     __syncthreads();
+    if (aux.z1_out) {
+        for (int e = t; e < TR * NM; e += RT) {
+            const int r = e >> 7, k = e & 127;
+            if (r < aux.rows) aux.z1_out[(aux.row0 + r) * NM + k] = S.z1T[k * TR + r];
+        }
+    }
     // ---- L2: thread = (row group rg: rows 4rg..4rg+3, col group cg: cols 32q + 4cg + i) ------
     const int cg = t & 7, rg = t >> 3;
     float acc[4][16];
@@ -152,10 +167,17 @@ __device__ __forceinline__ void tile_mlp(const RowsSmem& S) {
         const float4 b = *reinterpret_cast<const float4*>(S.b2s + q * 32 + cg * 4);
 #pragma unroll
         for (int r = 0; r < 4; ++r) {
-            acc[r][q * 4 + 0] = fmaxf(acc[r][q * 4 + 0] + b.x, 0.f);
-            acc[r][q * 4 + 1] = fmaxf(acc[r][q * 4 + 1] + b.y, 0.f);
-            acc[r][q * 4 + 2] = fmaxf(acc[r][q * 4 + 2] + b.z, 0.f);
-            acc[r][q * 4 + 3] = fmaxf(acc[r][q * 4 + 3] + b.w, 0.f);
+            float4 mk = make_float4(1.f, 1.f, 1.f, 1.f);
+            const int row = rg * 4 + r;
+            if (aux.m2 && row < aux.rows)
+                mk = *reinterpret_cast<const float4*>(aux.m2 + (aux.row0 + row) * NM + q * 32 + cg * 4);
+            acc[r][q * 4 + 0] = fmaxf((acc[r][q * 4 + 0] + b.x) * mk.x, 0.f);
+            acc[r][q * 4 + 1] = fmaxf((acc[r][q * 4 + 1] + b.y) * mk.y, 0.f);
+            acc[r][q * 4 + 2] = fmaxf((acc[r][q * 4 + 2] + b.z) * mk.z, 0.f);
+            acc[r][q * 4 + 3] = fmaxf((acc[r][q * 4 + 3] + b.w) * mk.w, 0.f);
+            if (aux.z2_out && row < aux.rows)
+                *reinterpret_cast<float4*>(aux.z2_out + (aux.row0 + row) * NM + q * 32 + cg * 4) =
+                    make_float4(acc[r][q * 4 + 0], acc[r][q * 4 + 1], acc[r][q * 4 + 2], acc[r][q * 4 + 3]);
         }
     }
     __syncthreads();                         // everyone is done reading z1T -> reuse it as part[][]
@@ -219,7 +241,7 @@ __global__ void __launch_bounds__(RT, 2) rhs_rows_kernel(const RowsArgs a) {
             for (int e = t; e < TR * NH; e += RT)
                 S.hs[e] = e < rows * NH ? a.h[row0 * NH + e] : 0.f;
             __syncthreads();
-            tile_mlp(S);
+            tile_mlp(S, TileAux{a.m1, a.m2, a.z1_out, a.z2_out, row0, rows});
             if (t < rows) {
                 float ft[NH], lo[NH];
 #pragma unroll
@@ -395,30 +417,44 @@ using namespace fiode;
 
 extern "C" size_t fiode_rhs_workspace_bytes(long long N) { return (size_t)N * NH * sizeof(float) + 256; }
 
+namespace fiode {
+// ftilde (N,10) [post scale_nominal] + OR of the not-converged words of every row; optional dropout masks / activations
+int launch_rows_store(const fiode_dyn_weights* w, const float* h, const float* s, long long N, long long s_rows,
+                      long long s_group, float* ft, unsigned* notconv, const float* m1, const float* m2, float* z1,
+                      float* z2, cudaStream_t st) {
+    if (s_rows != 1 && (s_group <= 0 || s_rows * s_group < N)) {
+        set_error("rhs: s_rows=%lld s_group=%lld do not cover N=%lld", s_rows, s_group, N); return -1; }
+    if (w->max_iter < 1 || w->max_iter > kIt) { set_error("rhs: max_iter must be in [1,32]"); return -1; }
+    FIODE_CUDA(cudaMemsetAsync(notconv, 0, sizeof(unsigned), st));
+    FIODE_CUDA(cudaFuncSetAttribute(rhs_rows_kernel<kStore>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)kRowsSmemBytes));
+    RowsArgs a{};
+    a.w = *w; a.h = h; a.s = s; a.N = N; a.s_rows = s_rows; a.s_group = s_group; a.ft_out = ft; a.notconv = notconv;
+    a.m1 = m1; a.m2 = m2; a.z1_out = z1; a.z2_out = z2;
+    const long long group = s_rows == 1 ? N : s_group;
+    const long long n_tiles = ((N + group - 1) / group) * ((group + TR - 1) / TR);
+    const int grid = (int)min((long long)2 * sm_count(), n_tiles);
+    rhs_rows_kernel<kStore><<<grid, RT, kRowsSmemBytes, st>>>(a);
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(1);
+    return 0;
+}
+}  // namespace fiode
+
 extern "C" int fiode_rhs_fwd(const fiode_dyn_weights* w, const float* h, const float* s, long long N,
                              long long s_rows, long long s_group, float* f, float* ftilde, float* mu, int* n_iter,
                              void* ws, size_t ws_bytes, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     if (!w || !h || !s || !f || !ws) { set_error("fiode_rhs_fwd: null pointer"); return -1; }
     if (N <= 0) { set_error("fiode_rhs_fwd: N=%lld", N); return -1; }
-    if (s_rows != 1 && (s_group <= 0 || s_rows * s_group < N)) {
-        set_error("fiode_rhs_fwd: s_rows=%lld s_group=%lld do not cover N=%lld", s_rows, s_group, N); return -1; }
-    if (w->max_iter < 1 || w->max_iter > kIt) { set_error("fiode_rhs_fwd: max_iter must be in [1,32]"); return -1; }
     if (ws_bytes < fiode_rhs_workspace_bytes(N)) { set_error("fiode_rhs_fwd: workspace too small"); return -1; }
     unsigned* notconv = reinterpret_cast<unsigned*>(ws);
     float* ft = ftilde ? ftilde : reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + 256);
-    FIODE_CUDA(cudaMemsetAsync(notconv, 0, sizeof(unsigned), st));
-    FIODE_CUDA(cudaFuncSetAttribute(rhs_rows_kernel<kStore>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)kRowsSmemBytes));
-    RowsArgs a{};
-    a.w = *w; a.h = h; a.s = s; a.N = N; a.s_rows = s_rows; a.s_group = s_group; a.ft_out = ft; a.notconv = notconv;
-    const long long group = s_rows == 1 ? N : s_group;
-    const long long n_tiles = ((N + group - 1) / group) * ((group + TR - 1) / TR);
-    const int grid = (int)min((long long)2 * sm_count(), n_tiles);
-    rhs_rows_kernel<kStore><<<grid, RT, kRowsSmemBytes, st>>>(a);
+    int rc = launch_rows_store(w, h, s, N, s_rows, s_group, ft, notconv, nullptr, nullptr, nullptr, nullptr, st);
+    if (rc) return rc;
     rhs_finish_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(ft, h, N, *w, notconv, f, mu, n_iter);
     FIODE_CUDA(cudaGetLastError());
-    count_launch(2);
+    count_launch(1);
     return 0;
 }
 

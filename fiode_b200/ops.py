@@ -233,3 +233,62 @@ def dopri5_simplex(dw: DynWeights, h0, s, t, rtol, atol, max_num_steps=2 ** 31 -
                                      int(max_num_steps), ptr(out), ptr(stats), ptr(ws), nb, int(rows_per_cta),
                                      stream_ptr()), 'fiode_dopri5_simplex')
     return SolveResult(out, stats)
+
+
+# ---- forward-invariance training workload ---------------------------------------------------------------
+SAMPLER_KINDS = dict(uniform=0, correct_cone=1, decision_boundary=2)
+
+
+def sampler_fill(kind, e, y, h, s0):
+    """Write n samples per image into h (B,S,10) at sample offset s0 from Exp(1) variates e."""
+    e = _f32(e)
+    B, S = h.shape[0], h.shape[1]
+    n = e.shape[0] if kind == 'uniform' else e.shape[1]
+    yy = y.to(torch.int32).contiguous() if y is not None else None
+    check(lib().fiode_sampler_fill(SAMPLER_KINDS[kind], ptr(e), ptr(yy), B, n, S, s0, ptr(h), stream_ptr()),
+          'fiode_sampler_fill')
+
+
+class FiSaved:
+    """Device tensors the FI-loss forward keeps for its backward."""
+    __slots__ = ('h', 's', 'y', 'B', 'S', 'kappa', 'm1', 'm2', 'f', 'ft', 'mu', 'z1', 'z2', 'V', 'Vdot', 'out4', 'dw')
+
+
+def fi_loss_fwd(dw, h, s, y, S, kappa, m1=None, m2=None):
+    """loss = mean relu(Vdot + kappa V) over the B*S samples (pl_modules.py:435-466).  Returns FiSaved;
+    ``out4`` = [loss, effective_batch_size, mean_active_constraints, bisection iterations] on the device."""
+    h, s = _f32(h), _f32(s)
+    B = s.shape[0]
+    N = B * S
+    assert h.shape == (N, NH)
+    dev = h.device
+    sv = FiSaved()
+    sv.h, sv.s, sv.y, sv.B, sv.S, sv.kappa, sv.dw = h, s, y.to(torch.int32).contiguous(), B, S, float(kappa), dw
+    sv.m1 = _f32(m1) if m1 is not None else None
+    sv.m2 = _f32(m2) if m2 is not None else None
+    new = lambda *shape: torch.empty(*shape, dtype=torch.float32, device=dev)
+    sv.f, sv.ft, sv.mu, sv.z1, sv.z2, sv.V, sv.Vdot = new(N, NH), new(N, NH), new(N), new(N, 128), new(N, 128), new(N), new(N)
+    sv.out4 = new(4)
+    nb = lib().fiode_fi_loss_workspace_bytes(N, B)
+    ws = _ws(nb, dev)
+    check(lib().fiode_fi_loss_fwd(C.byref(dw), ptr(h), ptr(s), ptr(sv.y), B, S, sv.kappa, ptr(sv.m1), ptr(sv.m2), ptr(sv.f),
+                                  ptr(sv.ft), ptr(sv.mu), ptr(sv.z1), ptr(sv.z2), ptr(sv.V), ptr(sv.Vdot), ptr(sv.out4),
+                                  ptr(ws), nb, stream_ptr()), 'fiode_fi_loss_fwd')
+    return sv
+
+
+def fi_loss_bwd(sv: FiSaved, grad_loss=1.0):
+    """Gradients of the FI loss w.r.t. Q1, Qx, Q2, Q3, b1(=bx), b2, b3 and s."""
+    dev = sv.h.device
+    new = lambda *shape: torch.empty(*shape, dtype=torch.float32, device=dev)
+    g = dict(Q1=new(128, NH), Qx=new(128, NH), Q2=new(128, 128), Q3=new(NH, 128), b1=new(128), b2=new(128), b3=new(NH),
+             s=new(sv.B, NH))
+    N = sv.B * sv.S
+    nb = lib().fiode_fi_loss_workspace_bytes(N, sv.B)
+    ws = _ws(nb, dev)
+    check(lib().fiode_fi_loss_bwd(C.byref(sv.dw), ptr(sv.h), ptr(sv.s), ptr(sv.y), sv.B, sv.S, sv.kappa, float(grad_loss),
+                                  ptr(sv.m1), ptr(sv.m2), ptr(sv.f), ptr(sv.ft), ptr(sv.mu), ptr(sv.z1), ptr(sv.z2),
+                                  ptr(sv.V), ptr(sv.Vdot), ptr(g['Q1']), ptr(g['Qx']), ptr(g['Q2']), ptr(g['Q3']),
+                                  ptr(g['b1']), ptr(g['b2']), ptr(g['b3']), ptr(g['s']), ptr(ws), nb, stream_ptr()),
+          'fiode_fi_loss_bwd')
+    return g

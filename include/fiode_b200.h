@@ -154,6 +154,37 @@ FIODE_API int fiode_certify_grid(const fiode_dyn_weights* w, const uint8_t* grid
                        const float* lut, const float* s, const int* labels, int M, int batches,
                        float kappa, float* out, int* iters, void* ws, size_t ws_bytes, void* stream);
 
+/* ---- forward-invariance training workload ------------------------------------------------------------
+ * Samplers (sampling/sampler.py): pure functions of pre-drawn Exp(1) variates e (the host draws them
+ * with the framework's RNG, like torch.distributions.Exponential.sample at sampler.py:36,116,142).
+ *   kind 0 UniformSimplexSampling  (:24-38)   e (n,10), one set shared by every image (:209-210)
+ *   kind 1 CorrectConeSampling     (:104-128) e (B,n,10), y (B)
+ *   kind 2 DecisionBoundarySampling(:130-153) e (B,n,9),  y (B)
+ * writes rows [s0, s0+n) of every image's block of the composite sample tensor h (B,S,10)
+ * (CompositeSampler.forward :195-216: cat on the sample axis, flatten to (B*S,10)).            */
+FIODE_API int fiode_sampler_fill(int kind, const float* e, const int* y, int B, int n, int S, int s0, float* h,
+                       void* stream);
+
+/* LyapunovLearning.compute_loss, order 1, act 'relu' (pl_modules.py:390-484) with the DecisionBoundary
+ * candidate (lya_cands.py:79-94): h (B*S,10) samples, s (B,10) static features (row r uses s[r/S],
+ * pl_modules.py:395-400), y (B) labels.  m1/m2: optional dropout masks (B*S,128), already scaled by
+ * 1/(1-p) (classification.py:98,100; NULL = eval).  Saved for the backward: f, ftilde, mu, z1, z2,
+ * V, Vdot.  out4 (device) = {loss, effective_batch_size, mean_active_constraints, bisection iterations}. */
+FIODE_API size_t fiode_fi_loss_workspace_bytes(long long N, int B);
+FIODE_API int fiode_fi_loss_fwd(const fiode_dyn_weights* w, const float* h, const float* s, const int* y, int B, int S,
+                      float kappa, const float* m1, const float* m2, float* f, float* ftilde, float* mu,
+                      float* z1, float* z2, float* V, float* Vdot, float* out4, void* ws, size_t ws_bytes,
+                      void* stream);
+/* Backward of the above (what loss.backward() computes through BarrierProjectionFn.backward
+ * barrier_projection.py:272-311 and F.linear): gradients w.r.t. the four Cayley matrices Q* (same
+ * layouts as fiode_dyn_weights), the biases (db1 is the gradient of hidden_to_mlp.bias AND of
+ * U_x.bias), and the static features ds (B,10).  grad_loss = d(objective)/d(loss).              */
+FIODE_API int fiode_fi_loss_bwd(const fiode_dyn_weights* w, const float* h, const float* s, const int* y, int B, int S,
+                      float kappa, float grad_loss, const float* m1, const float* m2, const float* f,
+                      const float* ftilde, const float* mu, const float* z1, const float* z2, const float* V,
+                      const float* Vdot, float* dQ1, float* dQx, float* dQ2, float* dQ3, float* db1, float* db2,
+                      float* db3, float* ds, void* ws, size_t ws_bytes, void* stream);
+
 /* ---- decision-boundary grid -----------------------------------------------------------------------
  * replaces robustness/eval_utils.py:31-61 sample_decision_boundary and :72-89
  * count_samples_decision_boundary: the set { z in Z^n_{>=0} : sum z = T, z_0 = max_{i>=1} z_i } in a
