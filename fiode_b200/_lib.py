@@ -71,6 +71,9 @@ SIGNATURES = {
     'fiode_fi_loss_fwd': (I, [C.POINTER(DynWeights), P, P, P, I, I, F32, P, P, P, P, P, P, P, P, P, P, P, SZ, P]),
     'fiode_fi_loss_bwd': (I, [C.POINTER(DynWeights), P, P, P, I, I, F32, F32, P, P, P, P, P, P, P, P, P,
                               P, P, P, P, P, P, P, P, P, SZ, P]),
+    'fiode_segway_grid_workspace_bytes': (SZ, []),
+    'fiode_segway_grid': (I, [C.POINTER(SegwayWeights), P, I, P, I, P, I, F32, F32, LL, LL, LL, P, P, P, P, SZ, P]),
+    'fiode_segway_simulate': (I, [C.POINTER(SegwayWeights), P, I, P, I, F64, F64, P, P, P, P]),
     'fiode_grid_count': (LL, [I, I]),
     'fiode_grid_workspace_bytes': (SZ, [I, I]),
     'fiode_grid_enumerate': (I, [I, I, LL, LL, P, P, SZ, P]),

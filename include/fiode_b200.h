@@ -195,6 +195,35 @@ FIODE_API size_t fiode_grid_workspace_bytes(int n, int T);
 FIODE_API int fiode_grid_enumerate(int n, int T, long long first, long long count, uint8_t* out, void* ws,
                          size_t ws_bytes, void* stream);
 
+/* ---- Segway NN-controller forward invariance (control/) ----------------------------------------------
+ * weights of libs/core/core/controllers/nn_controller.py:6-34 NNController(3 -> 32 -> 32 -> 1) as stored
+ * by nn.Linear (out, in), and P of control/control_utils.py:215-234 LyaQuadratic (3,3) row-major.     */
+typedef struct fiode_segway_weights {
+    const float* W0;  /* model.0.weight (32,3)  */
+    const float* b0;  /* model.0.bias   (32)    */
+    const float* W1;  /* model.2.weight (32,32) */
+    const float* b1;  /* model.2.bias   (32)    */
+    const float* W2;  /* model.4.weight (1,32)  */
+    const float* b2;  /* model.4.bias   (1)     */
+    const float* P;   /* lya.P.weight   (3,3)   */
+} fiode_segway_weights;
+/* control/certify_segway.py:55-59: grid_uniform_3d (grid_sampler.py:109-117, np.meshgrid 'xy' order over
+ * the axes d0 (phi), d1 (v), d2 (phi_dot), given as float32 arrays on the device), reject_sampling
+ * (:91-98) to the shell level_lb <= ||P x||^2 <= level_ub, and val = SegwaySingleBarrierModel(eta)
+ * (control_utils.py:97-106) over grid indices [first, first+count).  Kept points are written in grid
+ * order to eta (M,3) / val (M); stats2 (device) = {M, max val}.  eta/val must hold `capacity` >= M rows. */
+FIODE_API size_t fiode_segway_grid_workspace_bytes(void);
+FIODE_API int fiode_segway_grid(const fiode_segway_weights* w, const float* d0, int n0, const float* d1, int n1,
+                      const float* d2, int n2, float level_lb, float level_ub, long long first, long long count,
+                      long long capacity, float* eta, float* val, float* stats2, void* ws, size_t ws_bytes,
+                      void* stream);
+/* libs/core/core/dynamics/system_dynamics.py:54-91 simulate (processed=True): zero-order hold of
+ * u = ctrl(x) over each [ts[j], ts[j+1]], one dopri5 solve (torchdiffeq semantics, batch-wide RMS norm
+ * over the B <= 32 trajectories) per interval.  x0 (B,3); ts (N) float32; xs (B,N,3); us (B,N-1,1);
+ * stats4 (device) = {status, accepted steps, rejected steps, RHS evaluations}.                       */
+FIODE_API int fiode_segway_simulate(const fiode_segway_weights* w, const float* x0, int B, const float* ts, int N,
+                          double rtol, double atol, float* xs, float* us, int* stats4, void* stream);
+
 /* ---- device-resident adaptive dopri5 -----------------------------------------------------------
  * replaces torchdiffeq==0.2.2 odeint(func, y0, t, rtol, atol, method='dopri5') as called at
  * models.py:236-241 with func = IVP.h_dot -> dyn_fun.ode_forward (classification.py:128-132).

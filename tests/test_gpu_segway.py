@@ -1,0 +1,61 @@
+"""Segway closed loop on the GPU against the golden vectors of the reference's own control/ modules."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import segway as oseg
+from tests import fixtures as fx
+
+pytestmark = pytest.mark.gpu
+
+
+def test_segway_grid_matches_reference():
+    from fiode_b200.control import segway
+    g = fx.load_golden('segway.pt')
+    r = [g['r']] * 3
+    eta, val, vmax = segway.certify_grid(g['ctrl'], g['P'], g['sizes'].tolist(), r, level=g['level'],
+                                         levels=(g['lb'], g['ub']))
+    # the shell test compares an fp32 sum of three squares with the level: a point within one ulp of the
+    # level can fall either side; everything else must be the same point, in the same (grid) order
+    assert abs(eta.shape[0] - g['mask_count']) <= 2
+    if eta.shape[0] == g['mask_count']:
+        axes = oseg.grid_axes(g['sizes'].tolist(), r)
+        grid = oseg.grid_uniform_3d(g['sizes'].tolist(), r)
+        assert torch.equal(eta.cpu(), grid[g['mask_idx'].long()])
+        torch.testing.assert_close(val.cpu(), g['val'], rtol=1e-5, atol=1e-5)
+        assert abs(vmax - g['val_max']) <= 1e-5 * max(1.0, abs(g['val_max']))
+    lb2, ub2 = segway.shell_levels(g['P'], g['level'], g['r'])
+    assert abs(lb2 - g['lb']) < 1e-6 and abs(ub2 - g['ub']) < 1e-6
+
+
+def test_segway_grid_full_size_properties():
+    """BASELINE config 1: r = 0.01 -> 300 x 53 x 300 = 4.77 M grid points.  Properties: every kept point lies
+    in the shell, sharded evaluation equals the one-shot evaluation."""
+    from fiode_b200.control import segway
+    g = fx.load_golden('segway.pt')
+    sizes, r = g['sizes'].tolist(), [0.01] * 3
+    eta, val, vmax = segway.certify_grid(g['ctrl'], g['P'], sizes, r, level=g['level'])
+    axes = segway.grid_axes(sizes, r)
+    assert [len(a) for a in axes] == [53, 300, 300]
+    lb, ub = segway.shell_levels(g['P'], g['level'], 0.01)
+    V = ((eta.double() @ g['P'].double().T.cuda()) ** 2).sum(1)
+    assert bool(((V >= lb - 1e-6) & (V <= ub + 1e-6)).all()) and eta.shape[0] > 1000
+    assert abs(float(val.max()) - vmax) < 1e-6
+    n = 53 * 300 * 300
+    parts = [segway.certify_grid(g['ctrl'], g['P'], sizes, r, level=g['level'], first=f, count=min(n // 3 + 1, n - f))
+             for f in range(0, n, n // 3 + 1)]
+    assert torch.equal(torch.cat([p[0] for p in parts]), eta)
+    assert torch.equal(torch.cat([p[1] for p in parts]), val)
+    # spot-check against the oracle on a slice
+    want = oseg.barrier_hdot(eta[:4096].cpu(), g['ctrl'], g['P'])
+    torch.testing.assert_close(val[:4096].cpu(), want, rtol=1e-5, atol=1e-5)
+
+
+def test_segway_simulate_matches_reference():
+    from fiode_b200.control import segway
+    g = fx.load_golden('segway.pt')
+    xs, us = segway.simulate(g['ctrl'], g['x0'], g['ts'])
+    torch.testing.assert_close(us.cpu(), g['us'], rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(xs.cpu(), g['xs'], rtol=1e-4, atol=1e-5)
+    st = segway.simulate.last_stats
+    assert st['nfe'] == 2 * (len(g['ts']) - 1) + 6 * (st['n_accept'] + st['n_reject'])
