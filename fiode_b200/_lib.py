@@ -79,6 +79,7 @@ SIGNATURES = {
     'fiode_grid_enumerate': (I, [I, I, LL, LL, P, P, SZ, P]),
     'fiode_dopri5_workspace_bytes': (SZ, [I]),
     'fiode_dopri5_simplex': (I, [C.POINTER(DynWeights), P, P, I, I, P, I, F64, F64, LL, P, P, P, SZ, I, P]),
+    'fiode_dopri5_simplex_batched': (I, [C.POINTER(DynWeights), P, P, I, I, I, P, I, F64, F64, LL, P, P, I, P]),
 }
 
 

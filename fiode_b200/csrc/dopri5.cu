@@ -14,6 +14,7 @@
 // per step one more barrier carries the error-norm partial sums (ordered, deterministic).
 #include "common.cuh"
 #include <cooperative_groups.h>
+namespace cg = cooperative_groups;
 
 namespace fiode {
 
@@ -32,27 +33,61 @@ struct SolveArgs {
     const float* h0; const float* s; int s_rows; int B; int R;
     const double* t; int nt; float rtol, atol; long long max_steps;
     float* out; fiode_solve_stats* stats; SolveCtl* ctl;
+    int G, C;                     // cluster mode: G independent solves of B rows each, C CTAs (one cluster) per solve
+};
+
+struct ClusterSlot { double s0, s1; unsigned orw; unsigned pad; };
+
+// who am I inside my solve, and how do its CTAs talk
+struct Comm {
+    int rank, size;               // CTA index / CTA count of this solve
+    unsigned epoch;
+    SolveCtl* ctl;                // cooperative-grid mode: global-memory barrier
+    ClusterSlot* slots;           // cluster mode: [2] in this CTA's shared memory, read by peers through DSMEM
 };
 
 struct Red { double s0, s1; unsigned orw; };
 
-// One grid-wide barrier that also (a) ORs a 32-bit word and (b) sums two doubles in CTA order.
+// One solve-wide barrier that also (a) ORs a 32-bit word and (b) sums two doubles in CTA order.
 // Caller passes the CTA-level values in thread 0.
-__device__ __forceinline__ Red grid_reduce(SolveCtl* ctl, unsigned& epoch, double s0, double s1, unsigned orw,
-                                           bool want_sums, Red* sh) {
-    const unsigned G = gridDim.x, e = epoch;
+//   cooperative-grid mode: arrival counter + rotating OR words + per-CTA slots in global memory;
+//   cluster mode: each CTA publishes into its own shared memory, one hardware cluster barrier, every
+//   CTA then reads its peers' slots over DSMEM in rank order (deterministic).  Slots are double-buffered
+//   by barrier parity, so one barrier per reduction suffices.
+template <bool CLUSTER>
+__device__ __forceinline__ Red comm_reduce(Comm& c, double s0, double s1, unsigned orw, bool want_sums, Red* sh) {
+    const unsigned e = c.epoch;
+    if (CLUSTER) {
+        cg::cluster_group cl = cg::this_cluster();
+        ClusterSlot* mine = c.slots + (e & 1);
+        if (threadIdx.x == 0) { mine->s0 = s0; mine->s1 = s1; mine->orw = orw; }
+        cl.sync();
+        if (threadIdx.x == 0) {
+            double a0 = 0, a1 = 0; unsigned o = 0;
+            for (int r = 0; r < c.size; ++r) {
+                const ClusterSlot* peer = cl.map_shared_rank(c.slots, r) + (e & 1);
+                a0 += peer->s0; a1 += peer->s1; o |= peer->orw;
+            }
+            sh->s0 = a0; sh->s1 = a1; sh->orw = o;
+        }
+        __syncthreads();
+        c.epoch = e + 1;
+        return *sh;
+    }
+    SolveCtl* ctl = c.ctl;
+    const unsigned G = c.size;
     if (threadIdx.x == 0) {
         if (want_sums) {
             double* sl = ctl->slots[e & 1];
-            __stcg(sl + 2 * blockIdx.x, s0);
-            __stcg(sl + 2 * blockIdx.x + 1, s1);
+            __stcg(sl + 2 * c.rank, s0);
+            __stcg(sl + 2 * c.rank + 1, s1);
         }
         if (orw) atomicOr(&ctl->orw[e % 3], orw);
         __threadfence();
         atomicAdd(&ctl->count, 1u);
         const unsigned target = (e + 1u) * G;
         while (ld_acquire_u32(&ctl->count) < target) {}
-        if (blockIdx.x == 0) __stcg(&ctl->orw[(e + 2) % 3], 0u);
+        if (c.rank == 0) __stcg(&ctl->orw[(e + 2) % 3], 0u);
         sh->orw = __ldcg(&ctl->orw[e % 3]);
     }
     __syncthreads();
@@ -64,7 +99,7 @@ __device__ __forceinline__ Red grid_reduce(SolveCtl* ctl, unsigned& epoch, doubl
         if (threadIdx.x == 0) { sh->s0 = a0; sh->s1 = a1; }
     }
     if (want_sums) __syncthreads();
-    epoch = e + 1;
+    c.epoch = e + 1;
     return *sh;
 }
 
@@ -96,9 +131,10 @@ struct Smem {
 
 // One evaluation of f(h) for the CTA's slab: ys -> kout (both [Rp][SROW] in smem).
 // Follows classification.py:96-115 + barrier_projection.py:232-255.
+template <bool CLUSTER>
 __device__ __forceinline__ void eval_rhs(const SolveArgs& a, const Smem& S, int R, int Rp, const float (&q1)[NH],
                                          const float4 (&q2)[16], const float (&q3)[16], float b2j, float b3o,
-                                         float* kout, unsigned& epoch) {
+                                         float* kout, Comm& comm) {
     const int t = threadIdx.x;
     // layer 1: z1[r][j] = relu(c[r][j] + Q1[j,:] . h[r,:])
     {
@@ -195,7 +231,7 @@ __device__ __forceinline__ void eval_rhs(const SolveArgs& a, const Smem& S, int 
     __syncthreads();
     unsigned cta_or = 0;
     if (t == 0) { cta_or = *S.orw; *S.orw = 0; }
-    const Red red = grid_reduce(a.ctl, epoch, 0.0, 0.0, cta_or, false, S.rr);
+    const Red red = comm_reduce<CLUSTER>(comm, 0.0, 0.0, cta_or, false, S.rr);
     const int K = stop_iter(red.orw, a.w.max_iter);
     // pass B: v = max(ftilde - mu_K, lower)
     for (int e = t; e < R * NH; e += kThreads) {
@@ -205,12 +241,20 @@ __device__ __forceinline__ void eval_rhs(const SolveArgs& a, const Smem& S, int 
     __syncthreads();
 }
 
+template <bool CLUSTER>
 __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const SolveArgs a) {
     extern __shared__ float4 smem4[];
     const int t = threadIdx.x;
-    const int row0 = blockIdx.x * a.R;
-    const int R = max(0, min(a.R, a.B - row0));
+    Comm comm;
+    comm.rank = CLUSTER ? (int)(blockIdx.x % a.C) : (int)blockIdx.x;
+    comm.size = CLUSTER ? a.C : (int)gridDim.x;
+    comm.epoch = 0; comm.ctl = a.ctl;
+    const int solve = CLUSTER ? (int)(blockIdx.x / a.C) : 0;
+    const int lrow0 = comm.rank * a.R;                       // first row inside the solve
+    const int R = max(0, min(a.R, a.B - lrow0));
+    const int row0 = solve * a.B + lrow0;                    // first row in the global (G*B) tensors
     const int Rp = (a.R + 3) & ~3;
+    fiode_solve_stats* stats = a.stats + solve;
 
     Smem S;
     float* p = reinterpret_cast<float*>(smem4);
@@ -223,6 +267,7 @@ __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const Solve
     S.red = reinterpret_cast<double*>(p); p += 32;
     S.rr = reinterpret_cast<Red*>(p); p += 8;
     S.orw = reinterpret_cast<unsigned*>(p); p += 4;
+    comm.slots = reinterpret_cast<ClusterSlot*>(p); p += 2 * sizeof(ClusterSlot) / sizeof(float);
 
     // ---- one-time setup: weights to registers, c = b1 + bx + Qx s, y = h0 -----------------------
     float q1[NH]; float4 q2[16]; float q3[16]; float b2j, b3o;
@@ -269,9 +314,8 @@ __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const Solve
     }
     __syncthreads();
 
-    unsigned epoch = 0;
     const double inv_n = 1.0 / ((double)a.B * NH);
-    const size_t out_stride = (size_t)a.B * NH;
+    const size_t out_stride = (size_t)a.B * NH * (CLUSTER ? a.G : 1);
     float* k0 = S.k;
     auto kst = [&](int s) { return S.k + s * Rp * SROW; };
 
@@ -279,7 +323,7 @@ __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const Solve
     double tcur = a.t[0], t_left = tcur, dt;
 
     // ---- f0 and the initial step (misc._select_initial_step) ------------------------------------
-    eval_rhs(a, S, R, Rp, q1, q2, q3, b2j, b3o, k0, epoch); ++nfe;
+    eval_rhs<CLUSTER>(a, S, R, Rp, q1, q2, q3, b2j, b3o, k0, comm); ++nfe;
     float h0s;
     {
         double s0 = 0, s1 = 0;
@@ -291,7 +335,7 @@ __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const Solve
             s0 += (double)u * u; s1 += (double)v * v;
         }
         cta_sum2(s0, s1, S.red);
-        const Red rd = grid_reduce(a.ctl, epoch, s0, s1, 0u, true, S.rr);
+        const Red rd = comm_reduce<CLUSTER>(comm, s0, s1, 0u, true, S.rr);
         const float d0 = sqrtf((float)(rd.s0 * inv_n)), d1 = sqrtf((float)(rd.s1 * inv_n));
         h0s = init_h0(d0, d1);
         for (int e = t; e < R * NH; e += kThreads) {
@@ -299,7 +343,7 @@ __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const Solve
             S.ys[r * SROW + i] = S.y[r * SROW + i] + h0s * k0[r * SROW + i];
         }
         __syncthreads();
-        eval_rhs(a, S, R, Rp, q1, q2, q3, b2j, b3o, kst(1), epoch); ++nfe;
+        eval_rhs<CLUSTER>(a, S, R, Rp, q1, q2, q3, b2j, b3o, kst(1), comm); ++nfe;
         double s2 = 0, dummy = 0;
         for (int e = t; e < R * NH; e += kThreads) {
             const int r = e / NH, i = e - r * NH;
@@ -308,7 +352,7 @@ __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const Solve
             s2 += (double)u * u;
         }
         cta_sum2(s2, dummy, S.red);
-        const Red rd2 = grid_reduce(a.ctl, epoch, s2, 0.0, 0u, true, S.rr);
+        const Red rd2 = comm_reduce<CLUSTER>(comm, s2, 0.0, 0u, true, S.rr);
         const float d2 = sqrtf((float)(rd2.s0 * inv_n)) / h0s;
         dt = init_dt(h0s, d1, d2);
     }
@@ -331,7 +375,7 @@ __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const Solve
                     S.ys[o] = S.y[o] + acc;
                 }
                 __syncthreads();
-                eval_rhs(a, S, R, Rp, q1, q2, q3, b2j, b3o, kst(s + 1), epoch); ++nfe;
+                eval_rhs<CLUSTER>(a, S, R, Rp, q1, q2, q3, b2j, b3o, kst(s + 1), comm); ++nfe;
             }
             // error estimate + norm (+ count of non-finite entries of the step's start state)
             double se = 0, nonfin = 0;
@@ -347,11 +391,11 @@ __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const Solve
                 if (!isfinite(y0)) nonfin += 1.0;
             }
             cta_sum2(se, nonfin, S.red);
-            const Red rd = grid_reduce(a.ctl, epoch, se, nonfin, 0u, true, S.rr);
+            const Red rd = comm_reduce<CLUSTER>(comm, se, nonfin, 0u, true, S.rr);
             if (rd.s1 > 0.0) { status = 2; break; }
             const float ratio = fabsf(sqrtf((float)(rd.s0 * inv_n)));
-            if (blockIdx.x == 0 && t == 0 && n_logged < FIODE_LOG_STEPS) {
-                a.stats->dts[n_logged] = dt; a.stats->ratios[n_logged] = ratio;
+            if (comm.rank == 0 && t == 0 && n_logged < FIODE_LOG_STEPS) {
+                stats->dts[n_logged] = dt; stats->ratios[n_logged] = ratio;
             }
             if (n_logged < FIODE_LOG_STEPS) ++n_logged;
             if (ratio <= 1.f) {
@@ -391,22 +435,34 @@ __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const Solve
             a.out[it * out_stride + (size_t)(row0 + r) * NH + i] = total;
         }
     }
-    if (blockIdx.x == 0 && t == 0) {
-        a.stats->n_accept = n_accept; a.stats->n_reject = n_reject; a.stats->nfe = nfe;
-        a.stats->status = status; a.stats->t_final = tcur; a.stats->last_dt = dt;
-        a.stats->n_logged = n_logged;
+    if (comm.rank == 0 && t == 0) {
+        stats->n_accept = n_accept; stats->n_reject = n_reject; stats->nfe = nfe;
+        stats->status = status; stats->t_final = tcur; stats->last_dt = dt;
+        stats->n_logged = n_logged;
     }
+    if (CLUSTER) cg::this_cluster().sync();     // peers may still be reading this CTA's slots over DSMEM
 }
 
 static size_t solver_smem_bytes(int R) {
     const int Rp = (R + 3) & ~3;
-    size_t f = (size_t)3 * Rp * NM + (size_t)(4 + 7 + 5) * Rp * SROW + (size_t)kMaxIter * Rp + 32 + 8 + 4;
+    size_t f = (size_t)3 * Rp * NM + (size_t)(4 + 7 + 5) * Rp * SROW + (size_t)kMaxIter * Rp + 32 + 8 + 4 + 16;
     return f * sizeof(float);
 }
 
 }  // namespace fiode
 
 using namespace fiode;
+
+static int ensure_smem_attr() {
+    static bool done = false;
+    if (!done) {
+        const int mx = (int)solver_smem_bytes(64);
+        FIODE_CUDA(cudaFuncSetAttribute(dopri5_simplex_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+        FIODE_CUDA(cudaFuncSetAttribute(dopri5_simplex_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+        done = true;
+    }
+    return 0;
+}
 
 extern "C" size_t fiode_dopri5_workspace_bytes(int B) { (void)B; return sizeof(SolveCtl); }
 
@@ -430,14 +486,49 @@ extern "C" int fiode_dopri5_simplex(const fiode_dyn_weights* w, const float* h0,
     const int G = (B + R - 1) / R;
     if (G > nsm || G > kMaxGrid) { set_error("fiode_dopri5_simplex: grid %d exceeds co-resident CTAs %d", G, nsm); return -2; }
     const size_t smem = solver_smem_bytes(R);
-    FIODE_CUDA(cudaFuncSetAttribute(dopri5_simplex_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int rc = ensure_smem_attr();
+    if (rc) return rc;
     FIODE_CUDA(cudaMemsetAsync(ws, 0, sizeof(SolveCtl), st));
     SolveArgs a;
     a.w = *w; a.h0 = h0; a.s = s; a.s_rows = s_rows; a.B = B; a.R = R; a.t = t; a.nt = nt;
     a.rtol = (float)rtol; a.atol = (float)atol; a.max_steps = max_num_steps; a.out = out; a.stats = stats;
-    a.ctl = reinterpret_cast<SolveCtl*>(ws);
+    a.ctl = reinterpret_cast<SolveCtl*>(ws); a.G = 1; a.C = G;
     void* args[] = {&a};
-    FIODE_CUDA(cudaLaunchCooperativeKernel((void*)dopri5_simplex_kernel, dim3(G), dim3(kThreads), args, smem, st));
+    FIODE_CUDA(cudaLaunchCooperativeKernel((void*)dopri5_simplex_kernel<false>, dim3(G), dim3(kThreads), args, smem, st));
+    count_launch(1);
+    return 0;
+}
+
+// G independent solves of B rows each in ONE launch: a thread-block cluster per solve (hardware cluster
+// barrier + DSMEM reductions), so each solve keeps its own batch-wide error norm / projection stop rule.
+extern "C" int fiode_dopri5_simplex_batched(const fiode_dyn_weights* w, const float* h0, const float* s, int s_rows,
+                                            int G, int B, const double* t, int nt, double rtol, double atol,
+                                            long long max_num_steps, float* out, fiode_solve_stats* stats,
+                                            int cluster_size, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!w || !h0 || !s || !t || !out || !stats) { set_error("fiode_dopri5_simplex_batched: null pointer"); return -1; }
+    if (G <= 0 || B <= 0 || nt < 1) { set_error("fiode_dopri5_simplex_batched: G=%d B=%d nt=%d", G, B, nt); return -1; }
+    if (s_rows != 1 && s_rows != G * B) { set_error("fiode_dopri5_simplex_batched: s_rows must be 1 or G*B"); return -1; }
+    if (w->max_iter < 1 || w->max_iter > kMaxIter) { set_error("fiode_dopri5_simplex_batched: max_iter must be in [1,32]"); return -1; }
+    int C = cluster_size;
+    if (C <= 0) { C = 8; while (C > 1 && (B + C - 1) / C < 8) C >>= 1; }     // at least 8 rows per CTA
+    if (C != 1 && C != 2 && C != 4 && C != 8) { set_error("fiode_dopri5_simplex_batched: cluster size must be 1, 2, 4 or 8"); return -1; }
+    const int R = (B + C - 1) / C;
+    if (R > 64) { set_error("fiode_dopri5_simplex_batched: B=%d exceeds %d rows (cluster of %d x 64); use fiode_dopri5_simplex", B, C * 64, C); return -2; }
+    int rc = ensure_smem_attr();
+    if (rc) return rc;
+    SolveArgs a;
+    a.w = *w; a.h0 = h0; a.s = s; a.s_rows = s_rows; a.B = B; a.R = R; a.t = t; a.nt = nt;
+    a.rtol = (float)rtol; a.atol = (float)atol; a.max_steps = max_num_steps; a.out = out; a.stats = stats;
+    a.ctl = nullptr; a.G = G; a.C = C;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(G * C)); cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = solver_smem_bytes(R); cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    FIODE_CUDA(cudaLaunchKernelEx(&cfg, dopri5_simplex_kernel<true>, a));
     count_launch(1);
     return 0;
 }

@@ -292,3 +292,41 @@ def fi_loss_bwd(sv: FiSaved, grad_loss=1.0):
                                   ptr(g['b1']), ptr(g['b2']), ptr(g['b3']), ptr(g['s']), ptr(ws), nb, stream_ptr()),
           'fiode_fi_loss_bwd')
     return g
+
+
+class BatchedSolveResult:
+    """Result of G independent solves in one launch.  ``stats()`` -> list of SolveStats (one host sync)."""
+
+    def __init__(self, out, stats_buf, G):
+        self.out, self._buf, self.G, self._stats = out, stats_buf, G, None
+
+    def stats(self):
+        if self._stats is None:
+            raw = self._buf.cpu().numpy().tobytes()
+            n = C.sizeof(SolveStats)
+            self._stats = [SolveStats.from_buffer_copy(raw[g * n:(g + 1) * n]) for g in range(self.G)]
+        return self._stats
+
+    def raise_for_status(self):
+        for st in self.stats():
+            if st.status:
+                raise AssertionError(SolveResult.ERRORS[st.status].format(st.last_dt))
+        return self
+
+
+def dopri5_simplex_batched(dw: DynWeights, h0, s, G, t, rtol, atol, max_num_steps=2 ** 31 - 1, cluster_size=0):
+    """G independent batch solves (rows g*B .. (g+1)*B-1 form solve g) in ONE launch, a thread-block
+    cluster per solve: each keeps its own batch-wide error norm and projection stop rule, so solve g is
+    what ``dopri5_simplex`` returns for its rows alone.  h0 (G*B,10); s (1|G*B,10).  out (len(t), G*B, 10)."""
+    h0, s = _f32(h0), _f32(s)
+    N = h0.shape[0]
+    assert N % G == 0
+    B = N // G
+    t = t.detach().to(device=h0.device, dtype=torch.float64).contiguous()
+    nt = t.numel()
+    out = torch.empty(nt, N, NH, dtype=torch.float32, device=h0.device)
+    stats = torch.zeros(G * C.sizeof(SolveStats), dtype=torch.uint8, device=h0.device)
+    check(lib().fiode_dopri5_simplex_batched(C.byref(dw), ptr(h0), ptr(s), s.shape[0], G, B, ptr(t), nt, float(rtol),
+                                             float(atol), int(max_num_steps), ptr(out), ptr(stats), int(cluster_size),
+                                             stream_ptr()), 'fiode_dopri5_simplex_batched')
+    return BatchedSolveResult(out, stats, G)

@@ -249,6 +249,16 @@ FIODE_API int fiode_dopri5_simplex(const fiode_dyn_weights* w, const float* h0, 
                          float* out, fiode_solve_stats* stats, void* ws, size_t ws_bytes,
                          int rows_per_cta, void* stream);
 
+/* G independent solves of B rows each (row g*B+r belongs to solve g) in one launch: one thread-block
+ * cluster per solve, so every solve keeps ITS OWN batch-wide RMS norm and projection stop rule -- the
+ * result of solve g equals fiode_dopri5_simplex on rows [g*B, (g+1)*B).  This is how whole batches
+ * shard across SMs (and, one level up, across GPUs).  h0, s (1 | G*B rows), out (nt, G*B, 10),
+ * stats: G structs.  cluster_size 0 = auto (8 CTAs x 32 rows for B = 256); B <= 64 * cluster_size.   */
+FIODE_API int fiode_dopri5_simplex_batched(const fiode_dyn_weights* w, const float* h0, const float* s, int s_rows,
+                                 int G, int B, const double* t, int nt, double rtol, double atol,
+                                 long long max_num_steps, float* out, fiode_solve_stats* stats,
+                                 int cluster_size, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

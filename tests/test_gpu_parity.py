@@ -367,3 +367,27 @@ def test_certify_driver_matches_reference(sd):
     f = od.eval_dot(eta, c['s'][:1], sd2, fx.dyn_cfg(), None, DYN)
     want_hv = -f[:, 3] + f.masked_fill(~ru, -float('inf')).max(-1).values
     torch.testing.assert_close(hv, want_hv, rtol=1e-4, atol=1e-4)
+
+
+@pytest.mark.parametrize('G,B,tol,cluster', [(5, 256, 1e-3, 0), (3, 64, 1e-5, 0), (7, 1, 1e-3, 0), (2, 96, 1e-4, 4),
+                                             (40, 256, 1e-3, 8)])
+def test_batched_cluster_solver_equals_single_solves(sd, G, B, tol, cluster):
+    """One launch, a thread-block cluster per solve: every solve must reproduce the single-solve kernel on
+    its own rows (own batch-wide norm, own projection stop rule) -- bit for bit, counters included."""
+    from fiode_b200 import ops
+    ivp = fx.build_b200_model(sd)
+    dw = ivp.dyn_fun.dyn_weights()
+    gsd = torch.Generator().manual_seed(G * 1000 + B)
+    s = dev(torch.randn(G * B, 10, generator=gsd) * 0.5)
+    h0 = dev(fx.simplex_rows(G * B, seed=G + B))
+    t = torch.tensor([0., 0.3, 1.0], dtype=torch.float64)
+    res = ops.dopri5_simplex_batched(dw, h0, s, G, t, tol, tol, cluster_size=cluster)
+    sts = res.stats()
+    for g in ([0, G - 1] if G > 8 else range(G)):
+        sl = slice(g * B, (g + 1) * B)
+        one = ops.dopri5_simplex(dw, h0[sl].contiguous(), s[sl].contiguous(), t, tol, tol)
+        so = one.stats()
+        assert (sts[g].n_accept, sts[g].n_reject, sts[g].nfe, sts[g].status) == (so.n_accept, so.n_reject, so.nfe, 0)
+        assert list(sts[g].dts[:so.n_logged]) == list(so.dts[:so.n_logged])
+        torch.testing.assert_close(res.out[:, sl], one.out, rtol=1e-6, atol=1e-7)
+    assert len({(st.n_accept, st.n_reject) for st in sts}) >= 1
