@@ -65,6 +65,8 @@ SIGNATURES = {
     'fiode_barrier_project_fwd': (I, [P, P, P, LL, I, F32, P, P, P, P, SZ, P]),
     'fiode_barrier_project_bwd': (I, [P, P, P, P, LL, P, P, P]),
     'fiode_certify_workspace_bytes': (SZ, [I, I]),
+    'fiode_set_mlp_path': (None, [I]),
+    'fiode_get_mlp_path': (I, []),
     'fiode_certify_grid': (I, [C.POINTER(DynWeights), P, LL, I, P, P, P, I, I, F32, P, P, P, SZ, P]),
     'fiode_sampler_fill': (I, [I, P, P, I, I, I, I, P, P]),
     'fiode_fi_loss_workspace_bytes': (SZ, [LL, I]),

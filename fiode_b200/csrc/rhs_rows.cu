@@ -19,30 +19,13 @@
 //             certify_lipschitz.py:131-134 consumes); the finishing kernel picks the K the
 //             reference would have stopped at.  One pass, bit-faithful to the batch-global rule.
 #include "common.cuh"
+#include "rows.cuh"
 
 namespace fiode {
 
 constexpr int TR = 64;        // rows per tile
 constexpr int RT = 128;       // threads per CTA
 constexpr int Q1S = 12;       // Q1s row: 10 weights, c, pad
-constexpr int kIt = 32;       // max candidates tracked
-
-enum { kStore = 0, kCertify = 1 };
-
-struct RowsArgs {
-    fiode_dyn_weights w;
-    // kStore
-    const float* h; const float* s; long long N; long long s_rows; long long s_group;
-    float* ft_out; unsigned* notconv;              // (N,10), 1 word
-    const float* m1; const float* m2;              // optional dropout masks (N,128), already scaled by 1/(1-p)
-    float* z1_out; float* z2_out;                  // optional activations (N,128) for the backward
-    // kCertify
-    const uint8_t* gridz; const float* lut; int T; long long Ng; long long chunk; int n_chunks;
-    const int* labels; int M; int P;               // images in this launch, CTAs per image
-    float sa, sqrtn, sqrt2, dist, inv_T;           // fp32 roundings of the python-double constants
-    unsigned* cmax;                                // (M, n_chunks, 2, kIt) ordered-uint maxima
-    unsigned* cnot;                                // (M, n_chunks) not-converged OR words
-};
 
 struct RowsSmem {
     float* Q2T;   // [128][128]
@@ -394,11 +377,15 @@ __global__ void rhs_finish_kernel(const float* __restrict__ ft, const float* __r
 
 // finishing kernel for kCertify: per image, pick each chunk's stop iteration, max over chunks
 // (certify_lipschitz.py:131-143): out[m] = {max violation, max violation_larger_T}
-__global__ void certify_finish_kernel(const unsigned* __restrict__ cmax, const unsigned* __restrict__ cnot, int M,
-                                      int n_chunks, int max_iter, float kappa, float* __restrict__ out,
-                                      int* __restrict__ iters) {
+__global__ void certify_finish_kernel(const unsigned* __restrict__ cmax, const unsigned* __restrict__ cnot,
+                                      const unsigned* __restrict__ status, int M, int n_chunks, int max_iter,
+                                      float kappa, float* __restrict__ out, int* __restrict__ iters) {
     const int m = blockIdx.x * blockDim.x + threadIdx.x;
     if (m >= M) return;
+    if (status && *status) {   // tensor-core path left the fp16x2 range: make the failure visible, never a verdict
+        out[2 * m] = out[2 * m + 1] = __int_as_float(0x7fc00000);
+        return;
+    }
     float v1 = -INFINITY, v2 = -INFINITY;
     for (int ch = 0; ch < n_chunks; ++ch) {
         const int K = stop_iter(cnot[(size_t)m * n_chunks + ch], max_iter);
@@ -458,44 +445,27 @@ extern "C" int fiode_rhs_fwd(const fiode_dyn_weights* w, const float* h, const f
     return 0;
 }
 
-extern "C" size_t fiode_certify_workspace_bytes(int M, int n_chunks) {
-    return (size_t)M * n_chunks * (2 * kIt + 1) * sizeof(unsigned);
-}
-
-extern "C" int fiode_certify_grid(const fiode_dyn_weights* w, const uint8_t* gridz, long long Ng, int T,
-                                  const float* lut, const float* s, const int* labels, int M, int batches,
-                                  float kappa, float* out, int* iters, void* ws, size_t ws_bytes, void* stream) {
-    cudaStream_t st = (cudaStream_t)stream;
-    if (!w || !gridz || !lut || !s || !labels || !out || !ws) { set_error("fiode_certify_grid: null pointer"); return -1; }
-    if (M <= 0 || Ng <= 0 || batches <= 0 || T <= 0) { set_error("fiode_certify_grid: bad sizes"); return -1; }
-    if (w->max_iter < 1 || w->max_iter > kIt) { set_error("fiode_certify_grid: max_iter must be in [1,32]"); return -1; }
-    // chunking of certify_lipschitz.py:100-102, 116-119
-    const long long chunk = Ng / batches;
-    if (chunk == 0) { set_error("fiode_certify_grid: grid has fewer rows (%lld) than batches (%d)", Ng, batches); return -1; }
-    const int n_chunks = batches + ((Ng % batches) != 0 ? 1 : 0);
-    if (ws_bytes < fiode_certify_workspace_bytes(M, n_chunks)) { set_error("fiode_certify_grid: workspace too small"); return -1; }
-    unsigned* cmax = reinterpret_cast<unsigned*>(ws);
-    unsigned* cnot = cmax + (size_t)M * n_chunks * 2 * kIt;
-    FIODE_CUDA(cudaMemsetAsync(ws, 0, fiode_certify_workspace_bytes(M, n_chunks), st));  // ord(0) < ord(any float)
-    FIODE_CUDA(cudaFuncSetAttribute(rhs_rows_kernel<kCertify>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)kRowsSmemBytes));
-    RowsArgs a{};
-    a.w = *w; a.s = s; a.gridz = gridz; a.lut = lut; a.T = T; a.Ng = Ng; a.chunk = chunk; a.n_chunks = n_chunks;
-    a.labels = labels; a.M = M; a.cmax = cmax; a.cnot = cnot;
-    const int slots = 2 * sm_count();
-    int P = slots / M; if (P < 1) P = 1;
-    const long long max_tiles = (chunk + TR - 1) / TR + 1;
-    if (P > max_tiles) P = (int)max_tiles;
-    a.P = P;
-    // certify_lipschitz.py:122-124: Lf = sqrt(N) * (sigma_1*alpha_1*exp(sigma_1*eta_ub)) + 1 ; perturb = (sqrt(2)*Lf)*dist
-    a.sa = (float)((double)w->sigma_1 * (double)w->alpha_1);
-    a.sqrtn = (float)sqrt((double)NH);
-    a.sqrt2 = (float)sqrt(2.0);
-    a.dist = (float)(sqrt((double)NH) / (double)T);
-    a.inv_T = (float)(1.0 / (double)T);
-    rhs_rows_kernel<kCertify><<<M * P, RT, kRowsSmemBytes, st>>>(a);
-    certify_finish_kernel<<<(M + 127) / 128, 128, 0, st>>>(cmax, cnot, M, n_chunks, w->max_iter, kappa, out, iters);
+namespace fiode {
+int launch_certify_finish(const unsigned* cmax, const unsigned* cnot, const unsigned* status, int M, int n_chunks,
+                          int max_iter, float kappa, float* out, int* iters, cudaStream_t st) {
+    certify_finish_kernel<<<(M + 127) / 128, 128, 0, st>>>(cmax, cnot, status, M, n_chunks, max_iter, kappa, out, iters);
     FIODE_CUDA(cudaGetLastError());
-    count_launch(2);
+    count_launch(1);
     return 0;
 }
+
+int launch_certify_ffma(const RowsArgs& a0, cudaStream_t st) {
+    RowsArgs a = a0;
+    FIODE_CUDA(cudaFuncSetAttribute(rhs_rows_kernel<kCertify>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)kRowsSmemBytes));
+    const int slots = 2 * sm_count();
+    int P = slots / a.M; if (P < 1) P = 1;
+    const long long max_tiles = (a.chunk + TR - 1) / TR + 1;
+    if (P > max_tiles) P = (int)max_tiles;
+    a.P = P;
+    rhs_rows_kernel<kCertify><<<a.M * P, RT, kRowsSmemBytes, st>>>(a);
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(1);
+    return 0;
+}
+}  // namespace fiode

@@ -150,6 +150,13 @@ FIODE_API int fiode_barrier_project_bwd(const float* grad_v, const float* v, con
  * iteration is global per chunk.  out: (M,2) = {max(h+perturb+kappa), max(h+kappa)};
  * iters (may be NULL): (M, n_chunks) bisection iterations the reference would have run.        */
 FIODE_API size_t fiode_certify_workspace_bytes(int M, int n_chunks);
+/* Which pipe evaluates the three dense layers of the dynamics MLP in the row-streaming kernels
+ * (certification, FI loss, RHS over many rows): 0 = tcgen05 tensor cores with the fp16x2 split
+ * (FP32 emulation: x = hi + lo, three MMAs, fp32 accumulate; default), 1 = FP32 FFMA.  The
+ * environment variable FIODE_MLP_PATH=ffma selects 1 at load.  If an activation leaves the fp16x2
+ * range (|x| >= 1023) the tensor-core kernels write NaN results instead of a verdict.            */
+FIODE_API void fiode_set_mlp_path(int path);
+FIODE_API int fiode_get_mlp_path(void);
 FIODE_API int fiode_certify_grid(const fiode_dyn_weights* w, const uint8_t* gridz, long long Ng, int T,
                        const float* lut, const float* s, const int* labels, int M, int batches,
                        float kappa, float* out, int* iters, void* ws, size_t ws_bytes, void* stream);
