@@ -23,6 +23,9 @@ NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', 
               '-Xcompiler', '-fPIC', '-Xcompiler', '-fvisibility=hidden', '--expt-relaxed-constexpr']
 
 
+EXTRA = os.environ.get('FIODE_NVCC_EXTRA', '').split()
+
+
 def _nvcc() -> str:
     for c in (os.environ.get('NVCC'), '/usr/local/cuda/bin/nvcc', 'nvcc'):
         if c and (os.path.sep not in c or os.path.exists(c)):
@@ -50,7 +53,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
 
     def compile_one(job):
         s, o = job
-        cmd = [nvcc] + NVCC_FLAGS + ['-I', str(INCLUDE), '-c', str(s), '-o', str(o)]
+        cmd = [nvcc] + NVCC_FLAGS + EXTRA + ['-I', str(INCLUDE), '-c', str(s), '-o', str(o)]
         if verbose:
             cmd.insert(1, '-Xptxas=-v')
         r = subprocess.run(cmd, capture_output=True, text=True)

@@ -4,10 +4,13 @@
 // dynamics/classification.py:96-126 + barrier_projection/barrier_projection.py:232-255) like the FFMA
 // kernel in rhs_rows.cu, with the three dense layers of the dynamics MLP on tcgen05:
 //
-//   CTA = (image m, part p).  288 threads: two row warpgroups ("slots", 4 warps each; thread = one grid
-//   point = one TMEM lane) + one MMA-issuing warp.  TMEM (512 columns) = 2 slots x {D: 128 fp32 columns,
-//   A: 64 + 64 columns of packed fp16 hi / lo}.  Operand B (the Cayley matrices, fp16x2 split, x64) lives in
-//   shared memory for the whole kernel; the activations never leave TMEM / registers:
+//   CTA = (image m, part p), one per SM.  640 threads in five warpgroups (setmaxnreg re-splits the registers):
+//     2 x row warpgroups ("slots"; thread = one grid point = one TMEM lane): S0, S1, S2 and the D3 read-out
+//     2 x projection warpgroups: S3 on the rows their partner row warp hands over through a shared-memory ring
+//     2 MMA-issuing warps (one thread each, one per slot).
+//   TMEM (512 columns) = 2 slots x {D: 128 fp32 columns, A: 64 + 64 columns of packed fp16 hi / lo}.  Operand B
+//   (the Cayley matrices, fp16x2 split, x64) lives in shared memory for the whole kernel; the activations never
+//   leave TMEM / registers:
 //
 //     S0  grid numerators -> [eta, 1] fp16 hi/lo (LUT)  --tcgen05.st-->  A1           (K = 16)
 //     L1  D1 = A1 . [Q1 | c]^T                          3 MMAs  128x128x16    c = b1 + bx + Qx s (per image)
@@ -18,8 +21,9 @@
 //     S3  ftilde = D3 + b3 -> barrier lower bound (LUT), bisection projection with every candidate stop
 //         iteration tracked (the stop rule is global per reference chunk), running maxima of the violation
 //
-//   The two slots run the same sequence on alternating tiles; while one waits for its MMAs the other
-//   owns the FP32 pipes, and S0 of a slot's next tile is issued before S3 of the current one.
+//   The two slots run the same sequence on alternating tiles; while one waits for its MMAs the other owns the
+//   FP32 pipes, and S0 of a slot's next tile is issued before its D3 hand-over.  Measured bound (ncu, round 1):
+//   instruction issue (60 % busy; ALU pipe 45 %, tensor pipe 34 %), not the tensor pipe.
 //   Numerics: fp16x2 split (see tc.cuh) ~ fp32; everything after D3 is the FFMA kernel's arithmetic.
 #include "common.cuh"
 #include "rows.cuh"
@@ -31,7 +35,10 @@ namespace fiode {
 using namespace tc;
 
 constexpr int TM = 128;                    // rows per tile = TMEM lanes
-constexpr int kTcThreads = 288;            // 8 row warps + 1 MMA warp
+constexpr int kTcThreads = 32 * 20;        // warpgroups: 2 x row, 2 x projection, 1 x {MMA warp + 3 idle}
+constexpr int kMmaWarp = 16;
+constexpr int kRegsRow = 80, kRegsProj = 136, kRegsMma = 40;   // setmaxnreg budgets; launch = 96 x 640
+static_assert(256 * kRegsRow + 256 * kRegsProj + 128 * kRegsMma <= 96 * kTcThreads, "setmaxnreg.inc would block: the CTA pool is what the launch allocated");
 constexpr float kWS = 64.f, kWSInv = 1.f / 64.f;
 
 // shared-memory map (bytes).  B operands: [k chunk of 8 halves][n][8 halves]  (K-major core matrices)
@@ -40,41 +47,72 @@ constexpr int OFF_B2L = 32768;             // Q2 lo
 constexpr int OFF_B1H = 65536;             // [Q1 | c | 0] hi   [2][128][8]
 constexpr int OFF_B1L = 69632;
 constexpr int OFF_B3 = 73728;              // rows 0..15 Q3 hi (10 used), rows 16..31 Q3 lo   [16][32][8]
-constexpr int OFF_B2S = 81920;             // b2 fp32 [128]
+constexpr int OFF_B2S = 81920;             // b2 / 2 fp32 [128]
 constexpr int OFF_B3S = OFF_B2S + 512;     // b3 fp32 [16]
 constexpr int OFF_LUT_HL = OFF_B3S + 64;   // u32 [256]: fp16 hi | lo << 16 of eta(z)
 constexpr int OFF_LUT_LO = OFF_LUT_HL + 1024;   // fp32 [256]: barrier lower bound at eta(z)
 constexpr int OFF_LUT_PT = OFF_LUT_LO + 1024;   // fp32 [256]: Lipschitz perturbation for eta_max = eta(z)
-constexpr int OFF_BARS = OFF_LUT_PT + 1024;     // 4 mbarriers
-constexpr int OFF_TMEM = OFF_BARS + 32;
+constexpr int OFF_BARS = OFF_LUT_PT + 1024;     // mbarriers: A ready [2], D ready [2], ring full [16], ring empty [16]
+constexpr int OFF_TMEM = OFF_BARS + 36 * 8;
+constexpr int OFF_RING = OFF_TMEM + 32;         // [slot 2][quarter 4][entry 2] x { ft [10][32] fp32, z [3][32] u32 }
+constexpr int kRingEntry = 13 * 32 * 4;
 constexpr int kTcSmemBytes = 120 * 1024;   // > half an SM: one CTA (and one 512-column TMEM allocation) per SM
-static_assert(OFF_TMEM + 16 <= kTcSmemBytes, "smem map");
+static_assert(OFF_RING + 16 * kRingEntry <= kTcSmemBytes, "smem map");
+static_assert(OFF_RING % 16 == 0, "ring alignment");
+
+// optional in-kernel stage timers (build with -DFIODE_TC_PROF; read back with fiode_debug_tc_prof)
+#ifdef FIODE_TC_PROF
+__device__ long long g_tc_prof[32];
+#define PROF_DECL long long pacc_[16] = {0}; long long pt_ = clock64(), pn_
+#define PROF(i) do { pn_ = clock64(); pacc_[(i) & 15] += pn_ - pt_; pt_ = pn_; } while (0)
+#define PROF_FLUSH(cond) do { if ((cond) && blockIdx.x == 0 && lane == 0) for (int i_ = 0; i_ < 14; ++i_) if (pacc_[i_]) g_tc_prof[i_] = pacc_[i_]; } while (0)
+#else
+#define PROF_DECL
+#define PROF(i)
+#define PROF_FLUSH(cond)
+#endif
 
 __device__ __forceinline__ void put_b(uint8_t* base, int N, int n, int k, unsigned short v) {
     *reinterpret_cast<unsigned short*>(base + ((size_t)(k >> 3) * N + n) * 16 + (k & 7) * 2) = v;
 }
 
 // S1 / S2: D (128 fp32 columns of this thread's lane) -> relu(D / 64 [+ bias]) -> fp16 hi / lo -> A
+// relu costs no ALU-pipe slot here: with y = x / 2,  y + |y| == relu(x) exactly (|.| is a free FADD source modifier;
+// FMNMX / FSEL / ISETP share the half-rate ALU pipe, which is what bounds this kernel), so D is scaled by 1/128
+// instead of 1/64 and the bias is pre-halved.
+template <bool kBias>
+__device__ __forceinline__ void act16(const uint32_t (&v)[16], uint32_t tA, int c, const float* half_bias) {
+    const float2 sc = make_float2(0.5f * kWSInv, 0.5f * kWSInv), neg1 = make_float2(-1.f, -1.f);
+    uint32_t hi[8], lo[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        float2 x = make_float2(__uint_as_float(v[2 * i]), __uint_as_float(v[2 * i + 1]));
+        if (kBias) x = __ffma2_rn(x, sc, *reinterpret_cast<const float2*>(half_bias + 16 * c + 2 * i));
+        else x = __fmul2_rn(x, sc);
+        x.x = x.x + fabsf(x.x); x.y = x.y + fabsf(x.y);
+        const __half2 h = __float22half2_rn(x);
+        const float2 r = __ffma2_rn(__half22float2(h), neg1, x);      // x - float(h), exact
+        const __half2 l = __float22half2_rn(r);
+        hi[i] = *reinterpret_cast<const uint32_t*>(&h);
+        lo[i] = *reinterpret_cast<const uint32_t*>(&l);
+    }
+    tmem_st8(tA + 8 * c, hi);
+    tmem_st8(tA + 64 + 8 * c, lo);
+}
+// 16-column chunks, the TMEM load of chunk c+1 in flight while chunk c is converted.  (The operand cannot be
+// published in halves to start the MMAs earlier: they overwrite the very D columns still being read here.)
 template <bool kBias>
 __device__ __forceinline__ void act_to_a(uint32_t tD, uint32_t tA, const float* bias) {
-#pragma unroll 1
-    for (int c = 0; c < 4; ++c) {
-        uint32_t v[32], hi[16], lo[16];
-        tmem_ld32(tD + 32 * c, v);
-        tmem_wait_ld();
+    uint32_t v0[16], v1[16];
+    tmem_ld16(tD, v0);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            float x0 = __uint_as_float(v[2 * i]), x1 = __uint_as_float(v[2 * i + 1]);
-            if (kBias) {
-                const float2 b = *reinterpret_cast<const float2*>(bias + 32 * c + 2 * i);
-                x0 = fmaf(x0, kWSInv, b.x); x1 = fmaf(x1, kWSInv, b.y);
-            } else {
-                x0 *= kWSInv; x1 *= kWSInv;
-            }
-            split2(fmaxf(x0, 0.f), fmaxf(x1, 0.f), hi[i], lo[i]);
-        }
-        tmem_st16(tA + 16 * c, hi);
-        tmem_st16(tA + 64 + 16 * c, lo);
+    for (int c = 0; c < 8; c += 2) {
+        tmem_wait_ld();
+        tmem_ld16(tD + 16 * (c + 1), v1);
+        act16<kBias>(v0, tA, c, bias);
+        tmem_wait_ld();
+        if (c + 2 < 8) tmem_ld16(tD + 16 * (c + 2), v0);
+        act16<kBias>(v1, tA, c + 1, bias);
     }
 }
 
@@ -82,7 +120,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) certify_tc_kernel(const RowsArg
     extern __shared__ __align__(1024) uint8_t smem[];
     const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
     const int m = blockIdx.x / a.P, p = blockIdx.x - m * a.P;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BARS);   // [0,1] A ready (slot), [2,3] D ready (slot)
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + OFF_BARS);
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + OFF_TMEM);
     float* b2s = reinterpret_cast<float*>(smem + OFF_B2S);
     float* b3s = reinterpret_cast<float*>(smem + OFF_B3S);
@@ -92,9 +130,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) certify_tc_kernel(const RowsArg
     const int label = a.labels[m];
 
     // ---- one-time setup ---------------------------------------------------------------------------
-    if (warp == 8) tmem_alloc(tmem_slot, 512);
+    if (warp == kMmaWarp) tmem_alloc(tmem_slot, 512);
     if (t == 0) {
         mbar_init(&bars[0], TM); mbar_init(&bars[1], TM); mbar_init(&bars[2], 1); mbar_init(&bars[3], 1);
+        for (int i = 4; i < 36; ++i) mbar_init(&bars[i], 32);
         mbar_init_fence();
     }
     for (int e = t; e < NM * NM; e += kTcThreads) {           // Q2 (n, k) row-major
@@ -123,7 +162,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) certify_tc_kernel(const RowsArg
         if (o < NH) split1(a.w.Q3[o * NM + k] * kWS, h, l);
         put_b(smem + OFF_B3, 32, n, k, n < 16 ? h : l);
     }
-    for (int e = t; e < NM; e += kTcThreads) b2s[e] = a.w.b2[e];
+    for (int e = t; e < NM; e += kTcThreads) b2s[e] = 0.5f * a.w.b2[e];   // pre-halved, see act16
     if (t < 16) b3s[t] = t < NH ? a.w.b3[t] : 0.f;
     for (int z = t; z < 256; z += kTcThreads) {
         const float eta = z <= a.T ? a.lut[z] : 0.f;
@@ -140,7 +179,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) certify_tc_kernel(const RowsArg
     __syncthreads();
     fence_after_sync();
     const uint32_t tmem = *tmem_slot;
-    const long long first_of_slot[2] = {(long long)p, (long long)p + a.P};
     const long long stride = 2LL * a.P;
     auto tiles_in_chunk = [&](int ch) -> long long {
         const long long c0 = (long long)ch * a.chunk;
@@ -148,212 +186,285 @@ __global__ void __launch_bounds__(kTcThreads, 1) certify_tc_kernel(const RowsArg
         return (c1 - c0 + TM - 1) / TM;
     };
 
-    if (warp == 8) {
-        // ================= MMA issuer (one thread) ===================================================
-        if (lane == 0) {
-            long long remaining[2] = {0, 0};
+    if (warp >= kMmaWarp) {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsMma));
+        // ================= MMA issuers: warp 16 -> slot 0, warp 17 -> slot 1 (one thread each) ========
+        // (one issuer per slot on different SM sub-partitions: an issuer shares its scheduler with four
+        //  ALU-bound warps, so its ~10 dependent instructions per MMA take longer than the MMA itself)
+        if (warp < kMmaWarp + 2 && lane == 0) {
+            const int s = warp - kMmaWarp;
+            long long remaining = 0;
             for (int ch = 0; ch < a.n_chunks; ++ch) {
                 const long long nt = tiles_in_chunk(ch);
-                for (int s = 0; s < 2; ++s)
-                    if (nt > first_of_slot[s]) remaining[s] += 3 * ((nt - first_of_slot[s] + stride - 1) / stride);
+                const long long first = (long long)p + (long long)s * a.P;
+                if (nt > first) remaining += (nt - first + stride - 1) / stride;
             }
             const uint32_t sb = smem_u32(smem);
             constexpr uint32_t id128 = idesc_f16(128, 128), id32 = idesc_f16(128, 32), id16 = idesc_f16(128, 16);
-            int stage[2] = {0, 0};
-            uint32_t par[2] = {0, 0};
-            while (remaining[0] > 0 || remaining[1] > 0) {
-#pragma unroll
-                for (int s = 0; s < 2; ++s) {
-                    if (remaining[s] <= 0 || !mbar_test_wait(&bars[s], par[s])) continue;
-                    fence_after_sync();
-                    const uint32_t tD = tmem + s * 256, tA = tD + 128;
-                    if (stage[s] == 0) {
-                        const uint64_t bh = smem_desc(sb + OFF_B1H, NM * 16, 128), bl = smem_desc(sb + OFF_B1L, NM * 16, 128);
-                        mma_ts_f16(tD, tA, bh, id128, 0);
-                        mma_ts_f16(tD, tA + 8, bh, id128, 1);
-                        mma_ts_f16(tD, tA, bl, id128, 1);
-                    } else if (stage[s] == 1) {
-#pragma unroll
-                        for (int ks = 0; ks < 8; ++ks)
-                            mma_ts_f16(tD, tA + ks * 8, smem_desc(sb + OFF_B2H + ks * 2 * NM * 16, NM * 16, 128), id128, ks > 0);
-#pragma unroll
-                        for (int ks = 0; ks < 8; ++ks)
-                            mma_ts_f16(tD, tA + 64 + ks * 8, smem_desc(sb + OFF_B2H + ks * 2 * NM * 16, NM * 16, 128), id128, 1);
-#pragma unroll
-                        for (int ks = 0; ks < 8; ++ks)
-                            mma_ts_f16(tD, tA + ks * 8, smem_desc(sb + OFF_B2L + ks * 2 * NM * 16, NM * 16, 128), id128, 1);
-                    } else {
-#pragma unroll
-                        for (int ks = 0; ks < 8; ++ks)
-                            mma_ts_f16(tD, tA + ks * 8, smem_desc(sb + OFF_B3 + ks * 2 * 32 * 16, 32 * 16, 128), id32, ks > 0);
-#pragma unroll
-                        for (int ks = 0; ks < 8; ++ks)
-                            mma_ts_f16(tD, tA + 64 + ks * 8, smem_desc(sb + OFF_B3 + ks * 2 * 32 * 16, 32 * 16, 128), id16, 1);
-                    }
-                    mma_commit(&bars[2 + s]);
-                    par[s] ^= 1;
-                    stage[s] = stage[s] == 2 ? 0 : stage[s] + 1;
-                    --remaining[s];
-                }
+            const uint32_t tD = tmem + s * 256, tA = tD + 128;
+            const uint64_t b1h = smem_desc(sb + OFF_B1H, NM * 16, 128), b1l = smem_desc(sb + OFF_B1L, NM * 16, 128);
+            const uint64_t b2h = smem_desc(sb + OFF_B2H, NM * 16, 128), b2l = smem_desc(sb + OFF_B2L, NM * 16, 128);
+            const uint64_t b3 = smem_desc(sb + OFF_B3, 32 * 16, 128);
+            constexpr uint64_t k2 = (2 * NM * 16) >> 4, k3 = (2 * 32 * 16) >> 4;   // descriptor step per 16-wide k slab
+            uint64_t* a_rdy = &bars[s];
+            uint64_t* d_rdy = &bars[2 + s];
+            uint32_t par = 0;
+            PROF_DECL;
+            for (; remaining > 0; --remaining) {
+                mbar_wait(a_rdy, par); par ^= 1; fence_after_sync();
+                PROF(10);
+                mma_ts_f16(tD, tA, b1h, id128, 0);
+                mma_ts_f16(tD, tA + 8, b1h, id128, 1);
+                mma_ts_f16(tD, tA, b1l, id128, 1);
+                mma_commit(d_rdy);
+                PROF(11);
+                mbar_wait(a_rdy, par); par ^= 1; fence_after_sync();
+                PROF(10);
+                mma_ts_f16_x8(tD, tA, b2h, k2, id128, 0);          // hi . hi
+                mma_ts_f16_x8(tD, tA + 64, b2h, k2, id128, 1);     // lo . hi
+                mma_ts_f16_x8(tD, tA, b2l, k2, id128, 1);          // hi . lo
+                mma_commit(d_rdy);
+                PROF(12);
+                mbar_wait(a_rdy, par); par ^= 1; fence_after_sync();
+                PROF(10);
+                mma_ts_f16_x8(tD, tA, b3, k3, id32, 0);            // hi . [hi; lo]  (N = 32)
+                mma_ts_f16_x8(tD, tA + 64, b3, k3, id16, 1);       // lo . hi        (N = 16)
+                mma_commit(d_rdy);
+                PROF(13);
             }
+            PROF_FLUSH(s == 0);
         }
     } else {
-        // ================= row warps: slot = warp / 4, TMEM lane = 32 * (warp % 4) + lane ============
-        const int slot = warp >> 2, q = warp & 3;
-        const uint32_t tD = tmem + ((uint32_t)(q * 32) << 16) + slot * 256, tA = tD + 128;
-        uint64_t* a_rdy = &bars[slot];
-        uint64_t* d_rdy = &bars[2 + slot];
-        uint32_t par_d = 0;
-        const int r = q * 32 + lane;
-
+        // row warp w (0..7) and projection warp 8 + w work on the same 32 rows: slot = w / 4, quarter = w % 4
+        const bool is_proj = warp >= 8;
+        const int w = warp & 7;
+        const int slot = w >> 2, q = w & 3;
+        const long long first = (long long)p + (long long)slot * a.P;
+        uint8_t* ring = smem + OFF_RING + (size_t)(w * 2) * kRingEntry;
+        uint64_t* full = &bars[4 + w * 2];
+        uint64_t* empty = &bars[20 + w * 2];
         int ch = 0;
-        long long tile = first_of_slot[slot];
+        long long tile = first;
         auto settle = [&]() -> bool {
-            while (ch < a.n_chunks && tile >= tiles_in_chunk(ch)) { ++ch; tile = first_of_slot[slot]; }
+            while (ch < a.n_chunks && tile >= tiles_in_chunk(ch)) { ++ch; tile = first; }
             return ch < a.n_chunks;
         };
-        // S0: numerators of this thread's grid point (label swap of eval_utils.py:64-67 applied) -> A1
-        auto stage0 = [&](int chx, long long tilex, int (&z)[NH], bool& valid) {
-            const long long c0 = (long long)chx * a.chunk;
-            const long long c1 = (chx == a.n_chunks - 1) ? a.Ng : min(a.Ng, c0 + a.chunk);
-            const long long g = c0 + tilex * TM + r;
-            valid = g < c1;
+        bool have = settle();
+        int e = 0;
+
+        if (!is_proj) {
+            asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsRow));
+            // ================= row warps: TMEM lane = 32 * quarter + lane =============================
+            const uint32_t tD = tmem + ((uint32_t)(q * 32) << 16) + slot * 256, tA = tD + 128;
+            uint64_t* a_rdy = &bars[slot];
+            uint64_t* d_rdy = &bars[2 + slot];
+            uint32_t par_d = 0, par_e = 3;     // ring entries start empty
+            const int r = q * 32 + lane;
+            // S0: numerators of this thread's grid point (label swap of eval_utils.py:64-67 applied) -> A1
+            // the 10 numerator bytes of this thread's grid point, fetched one tile ahead (global-load latency
+            // would otherwise sit on the slot's critical path); raw[5] bit 0 = row exists
+            auto load_z = [&](int chx, long long tilex, unsigned (&raw)[6]) {
+                const long long c0 = (long long)chx * a.chunk;
+                const long long c1 = (chx == a.n_chunks - 1) ? a.Ng : min(a.Ng, c0 + a.chunk);
+                const long long g = c0 + tilex * TM + r;
+                raw[5] = g < c1;
 #pragma unroll
-            for (int i = 0; i < NH; ++i) z[i] = 0;
-            if (valid) {
-                const unsigned short* src = reinterpret_cast<const unsigned short*>(a.gridz + g * NH);
+                for (int i = 0; i < NH / 2; ++i) raw[i] = 0;
+                if (raw[5]) {
+                    const unsigned short* src = reinterpret_cast<const unsigned short*>(a.gridz + g * NH);
+#pragma unroll
+                    for (int i = 0; i < NH / 2; ++i) raw[i] = __ldg(src + i);
+                }
+            };
+            auto stage0 = [&](const unsigned (&raw)[6], uint32_t (&zw)[3]) {
+                const bool valid = raw[5] != 0;
+                int z[NH];
+#pragma unroll
+                for (int i = 0; i < NH / 2; ++i) { z[2 * i] = raw[i] & 0xff; z[2 * i + 1] = raw[i] >> 8; }
+                int zl = z[0];
+#pragma unroll
+                for (int i = 1; i < NH; ++i) if (i == label) zl = z[i];
+                const int z0 = z[0];
+#pragma unroll
+                for (int i = 1; i < NH; ++i) if (i == label) z[i] = z0;
+                z[0] = zl;
+                zw[0] = z[0] | (z[1] << 8) | (z[2] << 16) | (z[3] << 24);
+                zw[1] = z[4] | (z[5] << 8) | (z[6] << 16) | (z[7] << 24);
+                zw[2] = z[8] | (z[9] << 8) | (valid ? 0x80000000u : 0u);
+                uint32_t hi[8], lo[8];
 #pragma unroll
                 for (int i = 0; i < NH / 2; ++i) {
-                    const unsigned v = __ldg(src + i);
-                    z[2 * i] = v & 0xff; z[2 * i + 1] = v >> 8;
+                    const uint32_t u0 = lut_hl[z[2 * i]], u1 = lut_hl[z[2 * i + 1]];
+                    hi[i] = __byte_perm(u0, u1, 0x5410);
+                    lo[i] = __byte_perm(u0, u1, 0x7632);
                 }
-            }
-            int zl = z[0];
-#pragma unroll
-            for (int i = 1; i < NH; ++i) if (i == label) zl = z[i];
-            const int z0 = z[0];
-#pragma unroll
-            for (int i = 1; i < NH; ++i) if (i == label) z[i] = z0;
-            z[0] = zl;
-            uint32_t hi[8], lo[8];
-#pragma unroll
-            for (int i = 0; i < NH / 2; ++i) {
-                const uint32_t u0 = lut_hl[z[2 * i]], u1 = lut_hl[z[2 * i + 1]];
-                hi[i] = __byte_perm(u0, u1, 0x5410);
-                lo[i] = __byte_perm(u0, u1, 0x7632);
-            }
-            hi[5] = 0x3C00u; lo[5] = 0u;          // k = 10: constant 1 -> picks up c
-            hi[6] = hi[7] = lo[6] = lo[7] = 0u;
-            tmem_st8(tA, hi);
-            tmem_st8(tA + 8, lo);
-            tmem_wait_st();
-            fence_before_sync();
-            mbar_arrive(a_rdy);
-        };
-
-        float m1[kIt], m2[kIt];
-#pragma unroll
-        for (int k = 0; k < kIt; ++k) { m1[k] = -INFINITY; m2[k] = -INFINITY; }
-        unsigned notconv = 0;
-        bool bad = false;
-        int zc[NH];
-        bool vc = false;
-        bool have = settle();
-        if (have) stage0(ch, tile, zc, vc);
-        while (have) {
-            const int cur_ch = ch;
-            mbar_wait(d_rdy, par_d); par_d ^= 1; fence_after_sync();              // D1
-            act_to_a<false>(tD, tA, nullptr);
-            tmem_wait_st(); fence_before_sync(); mbar_arrive(a_rdy);
-            mbar_wait(d_rdy, par_d); par_d ^= 1; fence_after_sync();              // D2
-            act_to_a<true>(tD, tA, b2s);
-            tmem_wait_st(); fence_before_sync(); mbar_arrive(a_rdy);
-            mbar_wait(d_rdy, par_d); par_d ^= 1; fence_after_sync();              // D3
-            float ft[NH];
-            {
+                hi[5] = 0x3C00u; lo[5] = 0u;          // k = 10: constant 1 -> picks up c
+                hi[6] = hi[7] = lo[6] = lo[7] = 0u;
+                tmem_st8(tA, hi);
+                tmem_st8(tA + 8, lo);
+                tmem_wait_st();
+                fence_before_sync();
+                mbar_arrive(a_rdy);
+            };
+            uint32_t zc[3] = {0, 0, 0};
+            unsigned raw[6] = {0, 0, 0, 0, 0, 0};
+            if (have) { load_z(ch, tile, raw); stage0(raw, zc); }
+            PROF_DECL;
+#ifdef FIODE_TC_PROF
+#define RPROF(i) PROF(i)
+#else
+#define RPROF(i)
+#endif
+            while (have) {
+                tile += stride;                      // the slot's next tile: numerators requested now, used after D3
+                have = settle();
+                if (have) load_z(ch, tile, raw);
+                mbar_wait(d_rdy, par_d); par_d ^= 1; fence_after_sync();              // D1
+                RPROF(0);
+                act_to_a<false>(tD, tA, nullptr);
+                tmem_wait_st(); fence_before_sync(); mbar_arrive(a_rdy);
+                RPROF(1);
+                mbar_wait(d_rdy, par_d); par_d ^= 1; fence_after_sync();              // D2
+                RPROF(2);
+                act_to_a<true>(tD, tA, b2s);
+                tmem_wait_st(); fence_before_sync(); mbar_arrive(a_rdy);
+                RPROF(3);
+                mbar_wait(d_rdy, par_d); par_d ^= 1; fence_after_sync();              // D3
+                RPROF(4);
                 uint32_t v[32];
                 tmem_ld32(tD, v);
                 tmem_wait_ld();
+                // next tile of this slot first: its layer-1 MMAs overlap the hand-over below
+                uint32_t zn[3] = {0, 0, 0};
+                if (have) stage0(raw, zn);
+                // hand ftilde + numerators to the projection warp
+                RPROF(5);
+                mbar_wait(&empty[e], (par_e >> e) & 1); par_e ^= 1u << e;
+                RPROF(6);
+                float* rf = reinterpret_cast<float*>(ring + e * kRingEntry);
+                uint32_t* rz = reinterpret_cast<uint32_t*>(rf + NH * 32);
 #pragma unroll
                 for (int i = 0; i < NH; ++i)
-                    ft[i] = fmaf(__uint_as_float(v[i]) + __uint_as_float(v[16 + i]), kWSInv, b3s[i]);
+                    rf[i * 32 + lane] = fmaf(__uint_as_float(v[i]) + __uint_as_float(v[16 + i]), kWSInv, b3s[i]);
+                rz[lane] = zc[0]; rz[32 + lane] = zc[1]; rz[64 + lane] = zc[2];
+                mbar_arrive(&full[e]);
+                RPROF(7);
+                e ^= 1;
+                zc[0] = zn[0]; zc[1] = zn[1]; zc[2] = zn[2];
             }
-            // next tile of this slot: its layer-1 MMAs overlap the projection below
-            tile += stride;
-            have = settle();
-            int zn[NH];
-            bool vn = false;
-            if (have) stage0(ch, tile, zn, vn);
-
-            // ---- S3: projection with all candidate stop iterations (rhs_rows.cu kCertify epilogue) ----
-            if (vc) {
-                float lo[NH];
-                int zmax = zc[0];
+            PROF_FLUSH(warp == 0);
+        } else {
+            // ================= projection warps: S3 (rhs_rows.cu kCertify epilogue) ====================
+            asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsProj));
+            float m1[kIt], m2[kIt];
 #pragma unroll
-                for (int i = 0; i < NH; ++i) {
-                    lo[i] = lut_lo[zc[i]];
-                    zmax = max(zmax, zc[i]);
-                    if (a.w.scale_nominal) ft[i] = scale_nominal_f(a.w.alpha_2, a.lut[zc[i]], lo[i], ft[i]);
-                }
-                float chk = 0.f;
+            for (int k = 0; k < kIt; ++k) { m1[k] = -INFINITY; m2[k] = -INFINITY; }
+            unsigned notconv = 0;
+            bool bad = false;
+            uint32_t par_f = 0;
+            PROF_DECL;
+#ifdef FIODE_TC_PROF
+#define PPROF(i) PROF(i)
+#else
+#define PPROF(i)
+#endif
+            while (have) {
+                const int cur_ch = ch;
+                mbar_wait(&full[e], (par_f >> e) & 1); par_f ^= 1u << e;
+                PPROF(8);
+                const float* rf = reinterpret_cast<const float*>(ring + e * kRingEntry);
+                const uint32_t* rz = reinterpret_cast<const uint32_t*>(rf + NH * 32);
+                float ft[NH];
 #pragma unroll
-                for (int i = 0; i < NH; ++i) chk += ft[i];
-                if (!(fabsf(chk) <= 3.0e38f)) bad = true;
-                // max over the tie set W = {i != label : eta_i == eta_max} of max(ft_i - mu, lo_i)
-                //   = max(max_W ft_i - mu, lower(eta_max))   (rounding is monotone; lo_i is equal on W)
-                float FW = -INFINITY, fty = ft[0], loy = lo[0];
+                for (int i = 0; i < NH; ++i) ft[i] = rf[i * 32 + lane];
+                const uint32_t z0 = rz[lane], z1 = rz[32 + lane], z2 = rz[64 + lane];
+                mbar_arrive(&empty[e]);
+                e ^= 1;
+                tile += stride;
+                have = settle();
+                if (z2 & 0x80000000u) {
+                    int zc[NH];
+                    zc[0] = z0 & 0xff; zc[1] = (z0 >> 8) & 0xff; zc[2] = (z0 >> 16) & 0xff; zc[3] = z0 >> 24;
+                    zc[4] = z1 & 0xff; zc[5] = (z1 >> 8) & 0xff; zc[6] = (z1 >> 16) & 0xff; zc[7] = z1 >> 24;
+                    zc[8] = z2 & 0xff; zc[9] = (z2 >> 8) & 0xff;
+                    float lo[NH];
+                    int zmax = zc[0];
 #pragma unroll
-                for (int i = 0; i < NH; ++i) {
-                    if (zc[i] == zmax && i != label) FW = fmaxf(FW, ft[i]);
-                    if (i == label) { fty = ft[i]; loy = lo[i]; }
-                }
-                const float LW = (FW == -INFINITY) ? -INFINITY : lut_lo[zmax];
-                const float perturb = lut_pt[zmax];
-                float hi = ft[0] - lo[0], lw = ft[0];
+                    for (int i = 0; i < NH; ++i) {
+                        lo[i] = lut_lo[zc[i]];
+                        zmax = max(zmax, zc[i]);
+                        if (a.w.scale_nominal) ft[i] = scale_nominal_f(a.w.alpha_2, a.lut[zc[i]], lo[i], ft[i]);
+                    }
+                    float chk = 0.f;
 #pragma unroll
-                for (int j = 1; j < NH; ++j) { hi = fmaxf(hi, ft[j] - lo[j]); lw = fminf(lw, ft[j]); }
+                    for (int i = 0; i < NH; ++i) chk += ft[i];
+                    if (!(fabsf(chk) <= 3.0e38f)) bad = true;
+                    // max over the tie set W = {i != label : eta_i == eta_max} of max(ft_i - mu, lo_i)
+                    //   = max(max_W ft_i - mu, lower(eta_max))   (rounding is monotone; lo_i is equal on W)
+                    float FW = -INFINITY, fty = ft[0], loy = lo[0];
 #pragma unroll
-                for (int k = 0; k < kIt; ++k) {
-                    if (k < a.w.max_iter) {
-                        const float mu = (hi - lw) / 2.f + lw;
-                        float e = 0.f;
+                    for (int i = 0; i < NH; ++i) {
+                        if (zc[i] == zmax && i != label) FW = fmaxf(FW, ft[i]);
+                        if (i == label) { fty = ft[i]; loy = lo[i]; }
+                    }
+                    float LW = (FW == -INFINITY) ? -INFINITY : lut_lo[zmax];
+                    asm volatile("" : "+f"(LW));
+                    float perturb = lut_pt[zmax];
+                    // keep these five in registers: ptxas otherwise re-derives the label selects in every iteration
+                    asm volatile("" : "+f"(fty), "+f"(loy), "+f"(FW), "+f"(perturb));
+                    float hi = ft[0] - lo[0], lw = ft[0];
 #pragma unroll
-                        for (int j = 0; j < NH; ++j) e += fmaxf(ft[j] - mu, lo[j]);
-                        const float fy = fmaxf(fty - mu, loy), fw = fmaxf(FW - mu, LW);
-                        const float hx = -fy + fw;                     // certify_lipschitz.py:41
-                        m2[k] = fmaxf(m2[k], hx);
-                        m1[k] = fmaxf(m1[k], hx + perturb);
-                        if (!(fabsf(e) < a.w.tol)) notconv |= (1u << k);
-                        if (e > 0.f) lw = mu;
-                        if (e < 0.f) hi = mu;
+                    for (int j = 1; j < NH; ++j) { hi = fmaxf(hi, ft[j] - lo[j]); lw = fminf(lw, ft[j]); }
+                    // the bisection runs on the NEGATED bounds: -((hi - lw) / 2 + lw) == ((-hi) - (-lw)) / 2 + (-lw)
+                    // bit for bit (rounding is symmetric), and every use of mu below is "x - mu"
+                    float nhi = -hi, nlw = -lw;
+#pragma unroll
+                    for (int k = 0; k < kIt; ++k) {
+                        if (k < a.w.max_iter) {
+                            const float nm = fmaf(nhi - nlw, 0.5f, nlw);
+                            const float2 nmu = make_float2(nm, nm);
+                            float e_ = 0.f;
+#pragma unroll
+                            for (int j = 0; j < NH; j += 2) {
+                                const float2 d = __fadd2_rn(make_float2(ft[j], ft[j + 1]), nmu);   // ft - mu
+                                e_ += fmaxf(d.x, lo[j]);
+                                e_ += fmaxf(d.y, lo[j + 1]);
+                            }
+                            const float fy = fmaxf(fty + nm, loy), fw = fmaxf(FW + nm, LW);
+                            const float hx = -fy + fw;                     // certify_lipschitz.py:41
+                            m2[k] = fmaxf(m2[k], hx);
+                            m1[k] = fmaxf(m1[k], hx + perturb);
+                            if (!(fabsf(e_) < a.w.tol)) notconv |= (1u << k);
+                            if (e_ > 0.f) nlw = nm;
+                            if (e_ < 0.f) nhi = nm;
+                        }
                     }
                 }
-            }
-            if (!have || ch != cur_ch) {
-                // chunk finished for this slot: warp reduce and publish
-                notconv = __reduce_or_sync(0xffffffffu, notconv);
-                unsigned* dst = a.cmax + ((size_t)m * a.n_chunks + cur_ch) * 2 * kIt;
+                PPROF(9);
+                if (!have || ch != cur_ch) {
+                    // chunk finished for these rows: warp reduce and publish
+                    notconv = __reduce_or_sync(0xffffffffu, notconv);
+                    unsigned* dst = a.cmax + ((size_t)m * a.n_chunks + cur_ch) * 2 * kIt;
 #pragma unroll
-                for (int k = 0; k < kIt; ++k) {
-                    const float x1 = warp_max(m1[k]), x2 = warp_max(m2[k]);
-                    if (lane == 0 && k < a.w.max_iter) {
-                        atomicMax(dst + k, f2ord(x1));
-                        atomicMax(dst + kIt + k, f2ord(x2));
+                    for (int k = 0; k < kIt; ++k) {
+                        const float x1 = warp_max(m1[k]), x2 = warp_max(m2[k]);
+                        if (lane == 0 && k < a.w.max_iter) {
+                            atomicMax(dst + k, f2ord(x1));
+                            atomicMax(dst + kIt + k, f2ord(x2));
+                        }
+                        m1[k] = -INFINITY; m2[k] = -INFINITY;
                     }
-                    m1[k] = -INFINITY; m2[k] = -INFINITY;
+                    if (lane == 0 && notconv) atomicOr(a.cnot + (size_t)m * a.n_chunks + cur_ch, notconv);
+                    notconv = 0;
                 }
-                if (lane == 0 && notconv) atomicOr(a.cnot + (size_t)m * a.n_chunks + cur_ch, notconv);
-                notconv = 0;
             }
-#pragma unroll
-            for (int i = 0; i < NH; ++i) zc[i] = zn[i];
-            vc = vn;
+            if (__any_sync(0xffffffffu, bad) && lane == 0) atomicOr(status, 1u);
+            PROF_FLUSH(warp == 8);
         }
-        if (__any_sync(0xffffffffu, bad) && lane == 0) atomicOr(status, 1u);
     }
     fence_before_sync();
     __syncthreads();
-    if (warp == 8) tmem_dealloc(tmem, 512);
+    if (warp == kMmaWarp) tmem_dealloc(tmem, 512);
 }
 
 static int g_mlp_path = -1;
@@ -383,6 +494,14 @@ int launch_certify_tc(const RowsArgs& a0, cudaStream_t st) {
 }  // namespace fiode
 
 using namespace fiode;
+
+#ifdef FIODE_TC_PROF
+extern "C" __attribute__((visibility("default"))) int fiode_debug_tc_prof(long long* out32, int reset) {
+    if (out32) cudaMemcpyFromSymbol(out32, fiode::g_tc_prof, sizeof(long long) * 32);
+    if (reset) { long long z[32] = {0}; cudaMemcpyToSymbol(fiode::g_tc_prof, z, sizeof(z)); }
+    return 0;
+}
+#endif
 
 extern "C" void fiode_set_mlp_path(int path) { fiode::g_mlp_path = path ? 1 : 0; }
 extern "C" int fiode_get_mlp_path(void) { return fiode::mlp_path(); }

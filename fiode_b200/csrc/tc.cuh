@@ -69,6 +69,45 @@ __device__ __forceinline__ void mma_ss_f16(uint32_t d_tmem, uint64_t a_desc, uin
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
+// Eight MMAs over consecutive 16-wide k slabs of one operand pair, as ONE asm block: the A address advances
+// by 8 TMEM columns and the B descriptor by `b_step` (descriptor units of 16 bytes) per slab.  Written as a
+// dependent add chain on purpose: left to the compiler, all descriptors are precomputed and spilled.
+#define FIODE_MMA_STEP_ "add.s64 bd, bd, %4;\n\tadd.u32 ta, ta, 8;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], [ta], bd, %3, q;\n\t"
+#define FIODE_MMA_HEAD_ \
+        "{\n\t.reg .pred p, q;\n\t.reg .b64 bd;\n\t.reg .b32 ta;\n\t" \
+        "setp.ne.b32 p, %5, 0;\n\tsetp.eq.b32 q, 0, 0;\n\tmov.b64 bd, %2;\n\tmov.b32 ta, %1;\n\t" \
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [ta], bd, %3, p;\n\t"
+__device__ __forceinline__ void mma_ts_f16_x8(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint64_t b_step, uint32_t idesc,
+                                              uint32_t accumulate_first) {
+    asm volatile(FIODE_MMA_HEAD_
+        FIODE_MMA_STEP_ FIODE_MMA_STEP_ FIODE_MMA_STEP_ FIODE_MMA_STEP_ FIODE_MMA_STEP_ FIODE_MMA_STEP_ FIODE_MMA_STEP_
+        "}"
+        ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "l"(b_step), "r"(accumulate_first) : "memory");
+}
+// four consecutive k slabs (half of a 128-deep operand)
+__device__ __forceinline__ void mma_ts_f16_x4(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint64_t b_step, uint32_t idesc,
+                                              uint32_t accumulate_first) {
+    asm volatile(FIODE_MMA_HEAD_
+        FIODE_MMA_STEP_ FIODE_MMA_STEP_ FIODE_MMA_STEP_
+        "}"
+        ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "l"(b_step), "r"(accumulate_first) : "memory");
+}
+#undef FIODE_MMA_HEAD_
+#undef FIODE_MMA_STEP_
+
+// ---- issue from a CONVERGED warp: every lane executes the surrounding code, one elected lane issues.  With
+// warp-uniform operands ptxas keeps addresses / descriptors in uniform registers (no per-MMA R2UR waterfall).
+__device__ __forceinline__ void mma_ts_f16_elect(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p, e;\n\tsetp.ne.b32 p, %4, 0;\n\telect.sync _|e, 0xffffffff;\n\t"
+        "@e tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void mma_commit_elect(uint64_t* bar) {
+    asm volatile("{\n\t.reg .pred e;\n\telect.sync _|e, 0xffffffff;\n\t"
+                 "@e tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar)) : "memory");
+}
+
 // Shared-memory matrix descriptor, K-major, no swizzle.  The operand is stored as 8-row x 16-byte core
 // matrices (128 contiguous bytes each): lbo = byte distance between core matrices adjacent in K,
 // sbo = between core matrices adjacent along M/N.  (Verified on B200 by tools/probe/tc_probe.cu.)

@@ -63,6 +63,10 @@ def certify(model, images, labels, T=40, eps=0.141, batches=10, gridz=None, imag
             for j in range(sel.numel()):
                 y = model(x[j:j + 1], ts=ts, int_params=dict(method='dopri5', rtol=ode_tol, atol=ode_tol))
                 correct[o + j] = float(int(y.argmax(-1)) == int(lab[j]))
+    if bool(torch.isnan(viol).any()):
+        from .._lib import FiodeError
+        raise FiodeError('certify: an activation left the fp16x2 range of the tensor-core path (|x| >= 1023); '
+                         'rerun with FIODE_MLP_PATH=ffma or fiode_set_mlp_path(1)')
     counts = torch.stack([correct.sum(), (viol[:, 0] < 0).float().sum(), (viol[:, 1] < 0).float().sum()]).double()
     fdist.allreduce_sum_(counts)
     v_all = fdist.gather_by_index(n, mine, viol[:, 0])

@@ -391,3 +391,28 @@ def test_batched_cluster_solver_equals_single_solves(sd, G, B, tol, cluster):
         assert list(sts[g].dts[:so.n_logged]) == list(so.dts[:so.n_logged])
         torch.testing.assert_close(res.out[:, sl], one.out, rtol=1e-6, atol=1e-7)
     assert len({(st.n_accept, st.n_reject) for st in sts}) >= 1
+
+
+def test_certify_tensor_core_path_matches_ffma_path(ops, sd):
+    """fiode_certify_grid on tcgen05 (fp16x2 split, default) against the FP32 FFMA kernel on the same inputs:
+    same maxima to 5e-6 (the split is an FP32 emulation), and out-of-range inputs give NaN, never a verdict."""
+    from fiode_b200 import grid as fgrid
+    from fiode_b200._lib import lib
+    ivp = fx.build_b200_model(sd, device='cuda:0')
+    dw = ivp.dyn_fun.dyn_weights()
+    T = 12
+    gz = fgrid.boundary_grid_numerators(10, T, device='cuda:0')
+    g = torch.Generator().manual_seed(11)
+    s = (torch.randn(21, 10, generator=g) * 0.7).cuda()
+    lab = torch.randint(0, 10, (21,), generator=g).cuda()
+    try:
+        lib().fiode_set_mlp_path(1)
+        want = ops.certify_grid(dw, gz, T, s, lab, 0.05, batches=7).cpu()
+        lib().fiode_set_mlp_path(0)
+        got = ops.certify_grid(dw, gz, T, s, lab, 0.05, batches=7).cpu()
+        assert torch.isfinite(got).all()
+        assert (got - want).abs().max().item() < 5e-6
+        bad = ops.certify_grid(dw, gz, T, s * 1e5, lab, 0.05, batches=7).cpu()
+        assert torch.isnan(bad).all()
+    finally:
+        lib().fiode_set_mlp_path(0)

@@ -30,6 +30,19 @@ for path in (1, 0):
     ms = e0.elapsed_time(e1) / 3
     res[path] = (out.cpu(), it.cpu())
     print(f'path {"ffma" if path else "tc  "}: {ms:8.3f} ms  {gz.shape[0] * M / ms * 1e3:.3e} pts/s   out[0]={out[0].tolist()} iters[0]={it[0].tolist()[:4]}')
+L = lib()
+if hasattr(L, 'fiode_debug_tc_prof'):
+    import ctypes
+    buf = (ctypes.c_longlong * 32)()
+    L.fiode_debug_tc_prof(buf, 1)
+    L.fiode_set_mlp_path(0)
+    ops.certify_grid(dw, gz, T, s, lab, 0.1, batches=10); torch.cuda.synchronize()
+    L.fiode_debug_tc_prof(buf, 0)
+    names = ['row: wait D1', 'row: S1', 'row: wait D2', 'row: S2', 'row: wait D3', 'row: D3 read + S0(next)', 'row: wait ring empty',
+             'row: hand-over', 'proj: wait ring full', 'proj: S3', 'mma: idle', 'mma: issue L1', 'mma: issue L2', 'mma: issue L3']
+    ntile = (gz.shape[0] // 10 + 127) // 128 * 10 / 2
+    for i, nme in enumerate(names):
+        print(f'  {nme:28s} {buf[i] / ntile:9.1f} cyc/tile')
 d = (res[0][0] - res[1][0]).abs().max().item()
 print(f'grid {gz.shape[0]} pts x {M} images; max |tc - ffma| = {d:.3e}; iters equal: {bool((res[0][1] == res[1][1]).all())}; '
       f'nan: {bool(torch.isnan(res[0][0]).any())}')
