@@ -9,6 +9,8 @@
 // The batch is processed in slabs so that the per-layer activations of a slab stay L2-resident
 // (126 MB) between the producing and the consuming kernel.
 #include "common.cuh"
+#include "gemm_tc.cuh"
+#include <cstdlib>
 
 namespace fiode {
 int launch_rfft2(const float* x, int n_img, int C, int n, const float* mu, const float* sd, float2* Xf, cudaStream_t st);
@@ -20,10 +22,16 @@ int gemm_nt(const float* A, int lda, const float* Bm, int ldb, int M, int N, int
             int group_sort, float* y, int ldy, float* ws, size_t ws_bytes, cudaStream_t st);
 size_t gemm_nt_workspace(int M, int N, int K);
 
-constexpr int kSlab = 128;   // images per slab: ~0.55 MB of activations per image -> ~70 MB per slab
+// images per slab: ~0.55 MB of activations per image -> L2-resident up to ~200 images; larger slabs fill the SMs better (measured at 4096 images: slab 128 6.4 ms, 1024 3.5 ms, 4096 3.2 ms; FIODE_SLAB overrides)
+static int slab_size() {
+    static int v = 0;
+    if (!v) { const char* e = getenv("FIODE_SLAB"); v = e ? atoi(e) : 4096; if (v < 1) v = 4096; }
+    return v;
+}
+#define kSlab slab_size()
 
 struct SlabLayout {
-    size_t xf0, yf0, a0, a2, xf4, yf4, a4, a6, l9, l11, gws, total, gws_bytes;
+    size_t xf0, yf0, a0, a2, xf4, yf4, a4, a6, l9, l11, gws, p2, p6, p9, p11, total, gws_bytes;
 };
 static size_t al(size_t x) { return (x + 255) & ~(size_t)255; }
 static SlabLayout slab_layout(int S) {
@@ -44,6 +52,9 @@ static SlabLayout slab_layout(int S) {
     if (g2 > L.gws_bytes) L.gws_bytes = g2;
     if (g3 > L.gws_bytes) L.gws_bytes = g3;
     L.gws = take(L.gws_bytes);
+    // fp16x2-split, MMA-tiled copies of the four big weight matrices (tensor-core path)
+    L.p2 = take(gemm_tc_packed_bytes(32, 128)); L.p6 = take(gemm_tc_packed_bytes(64, 256));
+    L.p9 = take(gemm_tc_packed_bytes(512, 4096)); L.p11 = take(gemm_tc_packed_bytes(512, 512));
     L.total = o;
     return L;
 }
@@ -72,6 +83,13 @@ extern "C" int fiode_backbone_fwd(const fiode_backbone_weights* w, const float* 
     float* l9 = (float*)(base + L.l9); float* l11 = (float*)(base + L.l11);
     float* gws = (float*)(base + L.gws);
     int rc;
+    const bool tcp = mlp_path() == 0;
+    if (tcp) {
+        if ((rc = launch_pack_w(w->Q2, 32, 128, gemm_tc_tile(32, 1), 1, base + L.p2, st))) return rc;
+        if ((rc = launch_pack_w(w->Q6, 64, 256, gemm_tc_tile(64, 1), 1, base + L.p6, st))) return rc;
+        if ((rc = launch_pack_w(w->Q9, 512, 4096, gemm_tc_tile(512, 1), 1, base + L.p9, st))) return rc;
+        if ((rc = launch_pack_w(w->Q11, 512, 512, gemm_tc_tile(512, 1), 1, base + L.p11, st))) return rc;
+    }
     for (int b0 = 0; b0 < B; b0 += S) {
         const int nb = (B - b0) < S ? (B - b0) : S;
         const float* xs = x + (size_t)b0 * 3 * 1024;
@@ -80,16 +98,23 @@ extern "C" int fiode_backbone_fwd(const fiode_backbone_weights* w, const float* 
         if ((rc = launch_mix(xf0, (const float2*)w->Qf0, nb, 544, 32, 3, yf0, st))) return rc;
         if ((rc = launch_irfft2(yf0, nb, 32, 32, w->b0, 1, a0, st))) return rc;
         // model.2: CayleyConv(32, 32, 3, stride=2) == orthogonal 1x1 on space-to-depth + GroupSort
-        if ((rc = launch_conv1x1(a0, w->Q2, w->b2, nb, 32, 32, 32, 1, a2, st))) return rc;
+        if ((rc = tcp ? launch_conv1x1_tc(a0, base + L.p2, w->b2, nb, 32, 32, 32, 1, a2, st)
+                      : launch_conv1x1(a0, w->Q2, w->b2, nb, 32, 32, 32, 1, a2, st))) return rc;
         // model.4: CayleyConv(32, 64, 3) @16x16 + GroupSort
         if ((rc = launch_rfft2(a2, nb * 32, 32, 16, nullptr, nullptr, xf4, st))) return rc;
         if ((rc = launch_mix(xf4, (const float2*)w->Qf4, nb, 144, 64, 32, yf4, st))) return rc;
         if ((rc = launch_irfft2(yf4, nb, 64, 16, w->b4, 1, a4, st))) return rc;
         // model.6: CayleyConv(64, 64, 3, stride=2) + GroupSort -> (nb, 64, 8, 8) == Flatten 4096
-        if ((rc = launch_conv1x1(a4, w->Q6, w->b6, nb, 64, 64, 16, 1, a6, st))) return rc;
+        if ((rc = tcp ? launch_conv1x1_tc(a4, base + L.p6, w->b6, nb, 64, 64, 16, 1, a6, st)
+                      : launch_conv1x1(a4, w->Q6, w->b6, nb, 64, 64, 16, 1, a6, st))) return rc;
         // model.9 / model.11 / fc
-        if ((rc = gemm_nt(a6, 4096, w->Q9, 4096, nb, 512, 4096, w->b9, 1.f, 1, l9, 512, gws, L.gws_bytes, st))) return rc;
-        if ((rc = gemm_nt(l9, 512, w->Q11, 512, nb, 512, 512, w->b11, 1.f, 1, l11, 512, gws, L.gws_bytes, st))) return rc;
+        if (tcp) {
+            if ((rc = launch_linear_tc(a6, 4096, base + L.p9, w->b9, nb, 512, 4096, 1, l9, 512, st))) return rc;
+            if ((rc = launch_linear_tc(l9, 512, base + L.p11, w->b11, nb, 512, 512, 1, l11, 512, st))) return rc;
+        } else {
+            if ((rc = gemm_nt(a6, 4096, w->Q9, 4096, nb, 512, 4096, w->b9, 1.f, 1, l9, 512, gws, L.gws_bytes, st))) return rc;
+            if ((rc = gemm_nt(l9, 512, w->Q11, 512, nb, 512, 512, w->b11, 1.f, 1, l11, 512, gws, L.gws_bytes, st))) return rc;
+        }
         if ((rc = gemm_nt(l11, 512, w->Qfc, 512, nb, 10, 512, w->bfc, 1.f, 0, s_out + (size_t)b0 * 10, 10, gws,
                           L.gws_bytes, st))) return rc;
     }

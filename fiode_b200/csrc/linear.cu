@@ -10,6 +10,7 @@
 // K contiguous ([row][32+4]) so global->smem is a straight 16-byte cp.async and both operands
 // are read back as float4 along K (12 LDS.128 per 128 FFMA).
 #include "common.cuh"
+#include "gemm_tc.cuh"
 #include <cuda_pipeline.h>
 
 namespace fiode {
@@ -232,13 +233,22 @@ int gemm_tn(const float* A, int lda, const float* Bm, int ldb, int M, int N, lon
 
 using namespace fiode;
 
-extern "C" size_t fiode_linear_workspace_bytes(int M, int N, int K) { return gemm_nt_workspace(M, N, K); }
+extern "C" size_t fiode_linear_workspace_bytes(int M, int N, int K) {
+    const size_t a = gemm_nt_workspace(M, N, K), b = gemm_tc_packed_bytes(N, K) + 256;
+    return a > b ? a : b;
+}
 
 extern "C" int fiode_linear_fwd(const float* X, const float* Q, const float* bias, int M, int N, int K,
                                 int group_sort, float* y, void* ws, size_t ws_bytes, void* stream) {
     if (!X || !Q || !y || !ws) { set_error("fiode_linear_fwd: null pointer"); return -1; }
     if (M <= 0 || N <= 0 || K <= 0) { set_error("fiode_linear_fwd: bad sizes"); return -1; }
     if (group_sort && (N & 1)) { set_error("fiode_linear_fwd: GroupSort needs an even width"); return -1; }
-    return gemm_nt(X, K, Q, K, M, N, K, bias, 1.f, group_sort, y, N, reinterpret_cast<float*>(ws), ws_bytes,
-                   (cudaStream_t)stream);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (mlp_path() == 0 && gemm_tc_supported(N, K, group_sort) && ws_bytes >= gemm_tc_packed_bytes(N, K)) {
+        // tensor cores (fp16x2 split): split + tile the weights into the workspace, then one persistent GEMM
+        int rc = launch_pack_w(Q, N, K, gemm_tc_tile(N, group_sort), group_sort, ws, st);
+        if (rc) return rc;
+        return launch_linear_tc(X, K, ws, bias, M, N, K, group_sort, y, N, st);
+    }
+    return gemm_nt(X, K, Q, K, M, N, K, bias, 1.f, group_sort, y, N, reinterpret_cast<float*>(ws), ws_bytes, st);
 }

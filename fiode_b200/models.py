@@ -103,6 +103,31 @@ class IVP(nn.Module):
         solution = self.integrate(x, ts=ts, int_params=int_params, use_adjoint=use_adjoint)
         return self.output_fun(solution) if return_traj else self.output_fun(solution)[-1]
 
+    def forward_batches(self, x, ts=None, int_params=None, return_result=False):
+        """G independent batches in ONE pass: x (G, B, C, H, W) -> (G, B, n_output) at ts[-1].
+
+        What ``[self(x[g]) for g in range(G)]`` computes -- every batch keeps its own batch-wide RMS error norm
+        and projection stop rule (models.py:236-241 called once per batch), so accepted / rejected step
+        sequences are those of the single-batch calls -- with the backbone run once over G*B images and the G
+        solves sharing one launch (a thread-block cluster per solve).  This is the unit that shards across
+        SMs and, one level up, across GPUs."""
+        from . import ops
+        G, B = x.shape[:2]
+        if ts is None:
+            ts = self.ts
+        p = dict(rtol=self.ode_tol, atol=self.ode_tol)
+        p.update(int_params or {})
+        assert p.get('method', 'dopri5') == 'dopri5'
+        opts = p.get('options') or {}
+        static_state, state = self.init_coordinates(x.reshape(G * B, *x.shape[2:]), self.dyn_fun)
+        res = ops.dopri5_simplex_batched(self.dyn_fun.dyn_weights(), state[0], static_state, G, ts, p['rtol'], p['atol'],
+                                         max_num_steps=opts.get('max_num_steps', 2 ** 31 - 1))
+        if opts.get('check', True):
+            res.raise_for_status()
+        if return_result:
+            return res
+        return self.output_fun((res.out,))[-1].reshape(G, B, -1)
+
     def integrate(self, x, ts=None, int_params=None, use_adjoint=False):
         assert not use_adjoint, 'the adjoint solve stays on the reference (unused by the FI-ODE configs)'
         if ts is None:

@@ -416,3 +416,61 @@ def test_certify_tensor_core_path_matches_ffma_path(ops, sd):
         assert torch.isnan(bad).all()
     finally:
         lib().fiode_set_mlp_path(0)
+
+
+@pytest.mark.parametrize('M,N,K,gs', [(128, 64, 64, 0), (300, 512, 512, 1), (515, 512, 4096, 1), (77, 128, 128, 0),
+                                      (513, 32, 128, 1)])
+def test_linear_tensor_core_path(ops, M, N, K, gs):
+    """F.linear (+GroupSort) on tcgen05 (fp16x2 split, accumulator segments promoted every 256 k) against an fp64
+    reference and against the FFMA kernel: fp32-level error (the 4096-deep case is where chained tensor-core
+    accumulation would otherwise drift to 5e-5)."""
+    from fiode_b200._lib import lib
+    g = torch.Generator().manual_seed(M + N + K)
+    X = dev(torch.randn(M, K, generator=g))
+    Q = dev(torch.randn(N, K, generator=g) / K ** 0.5)
+    b = dev(torch.randn(N, generator=g))
+    ref = torch.nn.functional.linear(X.double(), Q.double(), b.double())
+    if gs:
+        u, w = ref[:, :N // 2], ref[:, N // 2:]
+        ref = torch.cat([torch.maximum(u, w), torch.minimum(u, w)], 1)
+    try:
+        lib().fiode_set_mlp_path(0)
+        got = ops.linear_fwd(X, Q, b, group_sort=bool(gs)).double()
+        lib().fiode_set_mlp_path(1)
+        ffma = ops.linear_fwd(X, Q, b, group_sort=bool(gs)).double()
+    finally:
+        lib().fiode_set_mlp_path(0)
+    assert (got - ref).abs().max().item() < 1e-5
+    assert (ffma - ref).abs().max().item() < 1e-5
+
+
+def test_backbone_tensor_core_path_matches_ffma_path(ops, sd):
+    from fiode_b200._lib import lib
+    ivp = fx.build_b200_model(sd, device='cuda:0')
+    bw, keep = ivp.init_coordinates.param_map.backbone_weights()
+    x = dev(fx.synth_images(200))
+    try:
+        lib().fiode_set_mlp_path(1)
+        want = ops.backbone_fwd(bw, x)
+        lib().fiode_set_mlp_path(0)
+        got = ops.backbone_fwd(bw, x)
+    finally:
+        lib().fiode_set_mlp_path(0)
+    assert (got - want).abs().max().item() < 1e-5
+
+
+def test_forward_batches_equals_per_batch_forward(sd):
+    """IVP.forward_batches (backbone once over G*B images, one cluster-per-solve launch) == G calls of forward()."""
+    ivp = fx.build_b200_model(sd, device='cuda:0')
+    G, B = 3, 64
+    x = dev(fx.synth_images(G * B)).reshape(G, B, 3, 32, 32)
+    ts = torch.linspace(0., 1., 2)
+    p = dict(method='dopri5', rtol=1e-3, atol=1e-3)
+    got = ivp.forward_batches(x, ts=ts, int_params=p)
+    res = ivp.forward_batches(x, ts=ts, int_params=p, return_result=True)
+    for g in range(G):
+        want = ivp(x[g], ts=ts, int_params=p)
+        one = ivp.integrate(x[g], ts=ts, int_params=dict(p, return_result=True))
+        torch.testing.assert_close(got[g], want, rtol=1e-5, atol=1e-6)
+        a, b = res.stats()[g], one.stats()
+        assert (a.n_accept, a.n_reject, a.nfe) == (b.n_accept, b.n_reject, b.nfe)
