@@ -13,8 +13,13 @@
 #include <cstdlib>
 
 namespace fiode {
-int launch_rfft2(const float* x, int n_img, int C, int n, const float* mu, const float* sd, float2* Xf, cudaStream_t st);
-int launch_irfft2(const float2* Yf, int B, int C, int n, const float* bias, int gs, float* y, cudaStream_t st);
+int launch_rfft2(const float* x, int n_img, int C, int n, const float* mu, const float* sd, float2* Xf, cudaStream_t st,
+                 bool freq_major = false);
+int launch_irfft2(const float2* Yf, int B, int C, int n, const float* bias, int gs, float* y, cudaStream_t st,
+                  bool freq_major = false);
+int launch_irfft32_mix3(const float2* Xf, const float2* Qf, float2* Qt, int B, int C, const float* bias, int gs, float* y,
+                        cudaStream_t st);
+int launch_mix_real_weights(const float2* Qf, int F, int cout, int cin, float* W, cudaStream_t st);
 int launch_mix(const float2* Xf, const float2* Qf, int B, int F, int cout, int cin, float2* Yf, cudaStream_t st);
 int launch_conv1x1(const float* x, const float* Q, const float* bias, int B, int cin, int cout, int n, int gs, float* y,
                    cudaStream_t st);
@@ -31,7 +36,7 @@ static int slab_size() {
 #define kSlab slab_size()
 
 struct SlabLayout {
-    size_t xf0, yf0, a0, a2, xf4, yf4, a4, a6, l9, l11, gws, p2, p6, p9, p11, total, gws_bytes;
+    size_t xf0, yf0, a0, a2, xf4, yf4, a4, a6, l9, l11, gws, p2, p6, p9, p11, w4, p4, qt0, total, gws_bytes;
 };
 static size_t al(size_t x) { return (x + 255) & ~(size_t)255; }
 static SlabLayout slab_layout(int S) {
@@ -55,6 +60,9 @@ static SlabLayout slab_layout(int S) {
     // fp16x2-split, MMA-tiled copies of the four big weight matrices (tensor-core path)
     L.p2 = take(gemm_tc_packed_bytes(32, 128)); L.p6 = take(gemm_tc_packed_bytes(64, 256));
     L.p9 = take(gemm_tc_packed_bytes(512, 4096)); L.p11 = take(gemm_tc_packed_bytes(512, 512));
+    // model.4 mixing as 144 real (128 x 64) matrices: fp32 staging + packed
+    L.qt0 = take((size_t)544 * 32 * 3 * 8);
+    L.w4 = take((size_t)144 * 128 * 64 * 4); L.p4 = take((size_t)144 * gemm_tc_packed_bytes(128, 64));
     L.total = o;
     return L;
 }
@@ -89,21 +97,34 @@ extern "C" int fiode_backbone_fwd(const fiode_backbone_weights* w, const float* 
         if ((rc = launch_pack_w(w->Q6, 64, 256, gemm_tc_tile(64, 1), 1, base + L.p6, st))) return rc;
         if ((rc = launch_pack_w(w->Q9, 512, 4096, gemm_tc_tile(512, 1), 1, base + L.p9, st))) return rc;
         if ((rc = launch_pack_w(w->Q11, 512, 512, gemm_tc_tile(512, 1), 1, base + L.p11, st))) return rc;
+        if ((rc = launch_mix_real_weights((const float2*)w->Qf4, 144, 64, 32, (float*)(base + L.w4), st))) return rc;
+        if ((rc = launch_pack_w((const float*)(base + L.w4), 128, 64, 128, 0, base + L.p4, st, 144))) return rc;
     }
     for (int b0 = 0; b0 < B; b0 += S) {
         const int nb = (B - b0) < S ? (B - b0) : S;
         const float* xs = x + (size_t)b0 * 3 * 1024;
         // model.0: CayleyConv(3, 32, 3) @32x32 + GroupSort (Normalize fused into the FFT load)
         if ((rc = launch_rfft2(xs, nb * 3, 3, 32, w->mu, w->std, xf0, st))) return rc;
-        if ((rc = launch_mix(xf0, (const float2*)w->Qf0, nb, 544, 32, 3, yf0, st))) return rc;
-        if ((rc = launch_irfft2(yf0, nb, 32, 32, w->b0, 1, a0, st))) return rc;
+        if (tcp) {   // mixing fused into the inverse FFT: the 32-channel spectrum never reaches HBM
+            if ((rc = launch_irfft32_mix3(xf0, (const float2*)w->Qf0, (float2*)(base + L.qt0), nb, 32, w->b0, 1, a0, st))) return rc;
+        } else {
+            if ((rc = launch_mix(xf0, (const float2*)w->Qf0, nb, 544, 32, 3, yf0, st))) return rc;
+            if ((rc = launch_irfft2(yf0, nb, 32, 32, w->b0, 1, a0, st))) return rc;
+        }
         // model.2: CayleyConv(32, 32, 3, stride=2) == orthogonal 1x1 on space-to-depth + GroupSort
         if ((rc = tcp ? launch_conv1x1_tc(a0, base + L.p2, w->b2, nb, 32, 32, 32, 1, a2, st)
                       : launch_conv1x1(a0, w->Q2, w->b2, nb, 32, 32, 32, 1, a2, st))) return rc;
         // model.4: CayleyConv(32, 64, 3) @16x16 + GroupSort
-        if ((rc = launch_rfft2(a2, nb * 32, 32, 16, nullptr, nullptr, xf4, st))) return rc;
-        if ((rc = launch_mix(xf4, (const float2*)w->Qf4, nb, 144, 64, 32, yf4, st))) return rc;
-        if ((rc = launch_irfft2(yf4, nb, 64, 16, w->b4, 1, a4, st))) return rc;
+        if (tcp) {   // frequency-major spectra: the mixing of frequency phi is the row-major GEMM (nb x 64) . (128 x 64)^T
+            if ((rc = launch_rfft2(a2, nb * 32, 32, 16, nullptr, nullptr, xf4, st, true))) return rc;
+            if ((rc = launch_linear_tc_batched((const float*)xf4, 64, (long long)nb * 64, base + L.p4, nb, 128, 64, 144,
+                                               (float*)yf4, 128, (long long)nb * 128, st))) return rc;
+            if ((rc = launch_irfft2(yf4, nb, 64, 16, w->b4, 1, a4, st, true))) return rc;
+        } else {
+            if ((rc = launch_rfft2(a2, nb * 32, 32, 16, nullptr, nullptr, xf4, st))) return rc;
+            if ((rc = launch_mix(xf4, (const float2*)w->Qf4, nb, 144, 64, 32, yf4, st))) return rc;
+            if ((rc = launch_irfft2(yf4, nb, 64, 16, w->b4, 1, a4, st))) return rc;
+        }
         // model.6: CayleyConv(64, 64, 3, stride=2) + GroupSort -> (nb, 64, 8, 8) == Flatten 4096
         if ((rc = tcp ? launch_conv1x1_tc(a4, base + L.p6, w->b6, nb, 64, 64, 16, 1, a6, st)
                       : launch_conv1x1(a4, w->Q6, w->b6, nb, 64, 64, 16, 1, a6, st))) return rc;

@@ -24,12 +24,15 @@ template <int n> struct FftCfg {
     static constexpr int THREADS = 128;
 };
 
-template <int n>
+// FM ("frequency-major"): the spectrum is written as Xt[phi][b][c] instead of torch's [b][c][phi], so that the channel
+// mixing of one frequency is a plain row-major (batch x 2C) GEMM operand for the tensor-core kernel (gemm_tc.cu).
+template <int n, bool FM>
 __global__ void __launch_bounds__(128) rfft2_kernel(const float* __restrict__ x, int n_img, int C,
                                                     const float* __restrict__ mu, const float* __restrict__ sd,
                                                     float2* __restrict__ Xf) {
     using Cf = FftCfg<n>;
-    __shared__ float2 R[Cf::CH * n * Cf::RS];
+    constexpr int RSI = n * Cf::RS + 1;           // per-image stride, odd: lanes may run along the image index
+    __shared__ float2 R[Cf::CH * RSI];
     const int img0 = blockIdx.x * Cf::CH;
     // step 1: rows.  task = (channel-image ci, row pair p)
     for (int task = threadIdx.x; task < Cf::CH * (n / 2); task += Cf::THREADS) {
@@ -54,7 +57,7 @@ __global__ void __launch_bounds__(128) rfft2_kernel(const float* __restrict__ x,
             }
         }
         fft_dif<n, false>(z);
-        float2* ra = R + (ci * n + 2 * p) * Cf::RS;
+        float2* ra = R + ci * RSI + 2 * p * Cf::RS;
         float2* rb = ra + Cf::RS;
 #pragma unroll
         for (int v = 0; v <= n / 2; ++v) {
@@ -68,16 +71,22 @@ __global__ void __launch_bounds__(128) rfft2_kernel(const float* __restrict__ x,
     __syncthreads();
     // step 2: columns.  task = (ci, v)
     for (int task = threadIdx.x; task < Cf::CH * Cf::H; task += Cf::THREADS) {
-        const int ci = task / Cf::H, v = task - ci * Cf::H;
+        const int ci = FM ? task % Cf::CH : task / Cf::H, v = FM ? task / Cf::CH : task - ci * Cf::H;
         const int img = img0 + ci;
         if (img >= n_img) continue;
         float2 z[n];
 #pragma unroll
-        for (int a = 0; a < n; ++a) z[a] = R[(ci * n + a) * Cf::RS + v];
+        for (int a = 0; a < n; ++a) z[a] = R[ci * RSI + a * Cf::RS + v];
         fft_dif<n, false>(z);
-        float2* dst = Xf + (size_t)img * n * Cf::H + v;
+        if (FM) {                                  // lanes = consecutive channels of one image: contiguous runs
+            float2* dst = Xf + (size_t)v * n_img + img;        // [(u H + v)][b][c], b C + c == img
 #pragma unroll
-        for (int u = 0; u < n; ++u) dst[u * Cf::H] = z[bitrev<n>(u)];
+            for (int u = 0; u < n; ++u) dst[(size_t)u * Cf::H * n_img] = z[bitrev<n>(u)];
+        } else {
+            float2* dst = Xf + (size_t)img * n * Cf::H + v;
+#pragma unroll
+            for (int u = 0; u < n; ++u) dst[u * Cf::H] = z[bitrev<n>(u)];
+        }
     }
 }
 
@@ -85,15 +94,16 @@ __global__ void __launch_bounds__(128) rfft2_kernel(const float* __restrict__ x,
 // inverse: Yf [img][n][H] -> y [img][n][n] (+bias[c]), optional GroupSort over channel halves
 // CTA handles CH channel-images: with GroupSort they are CH/2 (c, c + C/2) pairs of one batch item.
 // ------------------------------------------------------------------------------------------------
-template <int n>
+template <int n, bool FM>
 __global__ void __launch_bounds__(128) irfft2_kernel(const float2* __restrict__ Yf, int B, int C,
                                                      const float* __restrict__ bias, int group_sort,
                                                      float* __restrict__ y) {
     using Cf = FftCfg<n>;
     constexpr int CH = Cf::CH;
+    constexpr int RSI = n * Cf::RS + 1;
     extern __shared__ float4 smem4[];
-    float2* T = reinterpret_cast<float2*>(smem4);                 // [CH][n][RS]
-    float* out = reinterpret_cast<float*>(T + CH * n * Cf::RS);   // [CH][n][n+1]
+    float2* T = reinterpret_cast<float2*>(smem4);                 // [CH][n][RS] (+1 per image)
+    float* out = reinterpret_cast<float*>(T + CH * RSI + 1);      // [CH][n][n+1]
     // channel-image list of this CTA
     const int groups_per_b = C / CH;              // C is a multiple of CH (32, 64)
     const int b = blockIdx.x / groups_per_b, g = blockIdx.x - b * groups_per_b;
@@ -104,21 +114,27 @@ __global__ void __launch_bounds__(128) irfft2_kernel(const float2* __restrict__ 
     if (b >= B) return;
     // step 1: columns (inverse along u)
     for (int task = threadIdx.x; task < CH * Cf::H; task += Cf::THREADS) {
-        const int ci = task / Cf::H, v = task - ci * Cf::H;
-        const float2* src = Yf + ((size_t)b * C + chan(ci)) * n * Cf::H + v;
+        const int ci = FM ? task % CH : task / Cf::H, v = FM ? task / CH : task - ci * Cf::H;
         float2 z[n];
+        if (FM) {                                  // Yt[(u H + v)][b][co]: lanes read consecutive channels
+            const float2* src = Yf + ((size_t)v * B + b) * C + chan(ci);
 #pragma unroll
-        for (int u = 0; u < n; ++u) z[u] = src[u * Cf::H];
+            for (int u = 0; u < n; ++u) z[u] = src[(size_t)u * Cf::H * B * C];
+        } else {
+            const float2* src = Yf + ((size_t)b * C + chan(ci)) * n * Cf::H + v;
+#pragma unroll
+            for (int u = 0; u < n; ++u) z[u] = src[u * Cf::H];
+        }
         fft_dif<n, true>(z);
 #pragma unroll
-        for (int a = 0; a < n; ++a) T[(ci * n + a) * Cf::RS + v] = z[bitrev<n>(a)];
+        for (int a = 0; a < n; ++a) T[ci * RSI + a * Cf::RS + v] = z[bitrev<n>(a)];
     }
     __syncthreads();
     // step 2: rows, two at a time (C2R: imag of DC / Nyquist ignored)
     const float scale = 1.0f / (float)(n * n);
     for (int task = threadIdx.x; task < CH * (n / 2); task += Cf::THREADS) {
         const int ci = task / (n / 2), p = task - ci * (n / 2);
-        const float2* ta = T + (ci * n + 2 * p) * Cf::RS;
+        const float2* ta = T + ci * RSI + 2 * p * Cf::RS;
         const float2* tb = ta + Cf::RS;
         float2 z[n];
 #pragma unroll
@@ -153,6 +169,125 @@ __global__ void __launch_bounds__(128) irfft2_kernel(const float2* __restrict__ 
             y[((size_t)b * C + chan(ci)) * n * n + px] = out[(ci * n + a) * (n + 1) + k];
         }
     }
+}
+
+// ------------------------------------------------------------------------------------------------
+// model.0 fused: per-frequency mixing (3 -> C channels) + inverse 2-D FFT + bias + GroupSort in one kernel.
+// The 3-channel input spectrum is tiny (13 KB / image), the mixed spectrum is not (139 KB / image): computing
+// Yf[b][co][phi] = sum_c Q[phi][co][c] Xf[b][c][phi] on the fly in the column pass removes its HBM round trip.
+// CTA = IM images x 8 output channels (4 GroupSort pairs); Qt is the spectrum re-laid as [co][c][phi] so that
+// lanes (consecutive phi) read consecutive addresses.  Row-pass results overwrite the T rows they came from.
+// ------------------------------------------------------------------------------------------------
+__global__ void transpose_q_kernel(const float2* __restrict__ Qf, int F, int CC, float2* __restrict__ Qt) {
+    const long long total = (long long)F * CC;
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+        const long long cc = e / F, phi = e - cc * F;       // e indexes the OUTPUT: coalesced writes
+        Qt[e] = Qf[phi * CC + cc];
+    }
+}
+
+template <int IM>
+__global__ void __launch_bounds__(160) irfft32_mix3_kernel(const float2* __restrict__ Xf, const float2* __restrict__ Qt,
+                                                           int B, int C, const float* __restrict__ bias, int group_sort,
+                                                           float* __restrict__ y) {
+    constexpr int n = 32, CH = 8, H = 17, RS = 18, RSI = n * RS + 1, F = n * H, THREADS = 160;   // CH * H = 136 column tasks: one round
+    extern __shared__ float4 smem4[];
+    float2* T = reinterpret_cast<float2*>(smem4);                 // [IM][CH] images of [n][RS] (+1)
+    const int groups_per_b = C / CH;
+    const int bg = blockIdx.x / groups_per_b, g = blockIdx.x - bg * groups_per_b;
+    const int b0 = bg * IM;
+    auto chan = [&](int ci) {
+        if (group_sort) return (ci < CH / 2) ? g * (CH / 2) + ci : C / 2 + g * (CH / 2) + (ci - CH / 2);
+        return g * CH + ci;
+    };
+    // the IM input spectra (3 channels each) are staged once; every thread then reuses each Q value for all IM images
+    float2* Xs = T + IM * CH * RSI + 1;                           // [IM][3][F]
+    for (int e = threadIdx.x; e < IM * 3 * F; e += THREADS) {
+        const int im = e / (3 * F);
+        Xs[e] = (b0 + im < B) ? __ldg(Xf + (size_t)b0 * 3 * F + e) : make_float2(0.f, 0.f);
+    }
+    __syncthreads();
+    // step 1: mix + columns (inverse along u).  task = (channel, v), v fastest
+    for (int task = threadIdx.x; task < CH * H; task += THREADS) {
+        const int ci = task / H, v = task - ci * H;
+        const float2* q = Qt + (size_t)chan(ci) * 3 * F + v;
+        float2 z[IM][n];
+#pragma unroll
+        for (int u = 0; u < n; ++u) {
+            const float2 q0 = __ldg(q + u * H), q1 = __ldg(q + F + u * H), q2 = __ldg(q + 2 * F + u * H);
+#pragma unroll
+            for (int im = 0; im < IM; ++im) {
+                const float2* xs = Xs + im * 3 * F + u * H + v;
+                float2 acc = make_float2(0.f, 0.f);
+                cfma(acc, q0, xs[0]); cfma(acc, q1, xs[F]); cfma(acc, q2, xs[2 * F]);
+                z[im][u] = acc;
+            }
+        }
+#pragma unroll
+        for (int im = 0; im < IM; ++im) {
+            fft_dif<n, true>(z[im]);
+#pragma unroll
+            for (int a = 0; a < n; ++a) T[(im * CH + ci) * RSI + a * RS + v] = z[im][bitrev<n>(a)];
+        }
+    }
+    __syncthreads();
+    // step 2: rows, two at a time; the 2 x 32 real outputs replace the two complex rows they were computed from
+    const float scale = 1.0f / (float)(n * n);
+    for (int task = threadIdx.x; task < IM * CH * (n / 2); task += THREADS) {
+        const int ic = task / (n / 2), p = task - ic * (n / 2), im = ic / CH, ci = ic - im * CH;
+        if (b0 + im >= B) continue;
+        float2* ta = T + ic * RSI + 2 * p * RS;
+        float2* tb = ta + RS;
+        float2 z[n];
+#pragma unroll
+        for (int k = 0; k <= n / 2; ++k) {
+            float2 A = ta[k], Bq = tb[k];
+            if (k == 0 || k == n / 2) { A.y = 0.f; Bq.y = 0.f; }
+            z[k] = make_float2(A.x - Bq.y, A.y + Bq.x);
+            if (k > 0 && k < n / 2) z[n - k] = make_float2(A.x + Bq.y, -A.y + Bq.x);
+        }
+        fft_dif<n, true>(z);
+        const float bs = bias ? bias[chan(ci)] : 0.f;
+        float* oa = reinterpret_cast<float*>(ta);
+        float* ob = reinterpret_cast<float*>(tb);
+#pragma unroll
+        for (int k = 0; k < n; ++k) {
+            const float2 r = z[bitrev<n>(k)];
+            oa[k] = r.x * scale + bs;
+            ob[k] = r.y * scale + bs;
+        }
+    }
+    __syncthreads();
+    auto outp = [&](int ic, int a, int k) { return reinterpret_cast<const float*>(T + ic * RSI + a * RS)[k]; };
+    if (group_sort) {
+        for (int e = threadIdx.x; e < IM * (CH / 2) * n * n; e += THREADS) {
+            const int im = e / ((CH / 2) * n * n), r = e - im * ((CH / 2) * n * n);
+            const int ci = r / (n * n), px = r - ci * (n * n), a = px / n, k = px - a * n;
+            if (b0 + im >= B) continue;
+            const float u = outp(im * CH + ci, a, k), w = outp(im * CH + ci + CH / 2, a, k);
+            y[((size_t)(b0 + im) * C + chan(ci)) * n * n + px] = fmaxf(u, w);
+            y[((size_t)(b0 + im) * C + chan(ci + CH / 2)) * n * n + px] = fminf(u, w);
+        }
+    } else {
+        for (int e = threadIdx.x; e < IM * CH * n * n; e += THREADS) {
+            const int ic = e / (n * n), px = e - ic * (n * n), a = px / n, k = px - a * n, im = ic / CH;
+            if (b0 + im >= B) continue;
+            y[((size_t)(b0 + im) * C + chan(ic - im * CH)) * n * n + px] = outp(ic, a, k);
+        }
+    }
+}
+// Qt: workspace of F * cout * 3 float2
+int launch_irfft32_mix3(const float2* Xf, const float2* Qf, float2* Qt, int B, int C, const float* bias, int gs, float* y,
+                        cudaStream_t st) {
+    constexpr int IM = 2, F = 544;
+    if (C % 8) { set_error("irfft32_mix3: C=%d", C); return -1; }
+    transpose_q_kernel<<<(F * C * 3 + 255) / 256, 256, 0, st>>>(Qf, F, C * 3, Qt);
+    const size_t smem = (size_t)IM * 8 * (32 * 18 + 1) * sizeof(float2) + 16 + (size_t)IM * 3 * F * sizeof(float2);
+    cudaError_t e = cudaFuncSetAttribute(irfft32_mix3_kernel<IM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return cuda_fail(e, "irfft32_mix3 smem attr");
+    irfft32_mix3_kernel<IM><<<((B + IM - 1) / IM) * (C / 8), 160, smem, st>>>(Xf, Qt, B, C, bias, gs, y);
+    count_launch(2);
+    return 0;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -318,28 +453,53 @@ __global__ void group_sort_kernel(const float* __restrict__ x, int B, int C, int
 }
 
 // host-side dispatch helpers used by backbone.cu too
-int launch_rfft2(const float* x, int n_img, int C, int n, const float* mu, const float* sd, float2* Xf, cudaStream_t st) {
-    if (n == 32) rfft2_kernel<32><<<(n_img + FftCfg<32>::CH - 1) / FftCfg<32>::CH, 128, 0, st>>>(x, n_img, C, mu, sd, Xf);
-    else if (n == 16) rfft2_kernel<16><<<(n_img + FftCfg<16>::CH - 1) / FftCfg<16>::CH, 128, 0, st>>>(x, n_img, C, mu, sd, Xf);
-    else { set_error("rfft2: unsupported n=%d (16 or 32)", n); return -1; }
+int launch_rfft2(const float* x, int n_img, int C, int n, const float* mu, const float* sd, float2* Xf, cudaStream_t st,
+                 bool freq_major) {
+    if (n == 32 && !freq_major) rfft2_kernel<32, false><<<(n_img + FftCfg<32>::CH - 1) / FftCfg<32>::CH, 128, 0, st>>>(x, n_img, C, mu, sd, Xf);
+    else if (n == 16 && !freq_major) rfft2_kernel<16, false><<<(n_img + FftCfg<16>::CH - 1) / FftCfg<16>::CH, 128, 0, st>>>(x, n_img, C, mu, sd, Xf);
+    else if (n == 16 && C % FftCfg<16>::CH == 0) rfft2_kernel<16, true><<<(n_img + FftCfg<16>::CH - 1) / FftCfg<16>::CH, 128, 0, st>>>(x, n_img, C, mu, sd, Xf);
+    else { set_error("rfft2: unsupported n=%d (16 or 32), freq_major=%d", n, (int)freq_major); return -1; }
     count_launch(1);
     return 0;
 }
-int launch_irfft2(const float2* Yf, int B, int C, int n, const float* bias, int gs, float* y, cudaStream_t st) {
-    if (n == 32 && C % FftCfg<32>::CH == 0) {
+int launch_irfft2(const float2* Yf, int B, int C, int n, const float* bias, int gs, float* y, cudaStream_t st,
+                  bool freq_major) {
+    if (n == 32 && C % FftCfg<32>::CH == 0 && !freq_major) {
         using Cf = FftCfg<32>;
-        const size_t smem = (size_t)Cf::CH * 32 * (Cf::RS * sizeof(float2) + 33 * sizeof(float));
-        cudaError_t e = cudaFuncSetAttribute(irfft2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        const size_t smem = (size_t)Cf::CH * 32 * (Cf::RS * sizeof(float2) + 33 * sizeof(float)) + (Cf::CH + 2) * sizeof(float2);
+        cudaError_t e = cudaFuncSetAttribute(irfft2_kernel<32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return cuda_fail(e, "irfft2 smem attr");
-        irfft2_kernel<32><<<B * (C / Cf::CH), 128, smem, st>>>(Yf, B, C, bias, gs, y);
+        irfft2_kernel<32, false><<<B * (C / Cf::CH), 128, smem, st>>>(Yf, B, C, bias, gs, y);
     } else if (n == 16 && C % FftCfg<16>::CH == 0) {
         using Cf = FftCfg<16>;
-        const size_t smem = (size_t)Cf::CH * 16 * (Cf::RS * sizeof(float2) + 17 * sizeof(float));
-        irfft2_kernel<16><<<B * (C / Cf::CH), 128, smem, st>>>(Yf, B, C, bias, gs, y);
+        const size_t smem = (size_t)Cf::CH * 16 * (Cf::RS * sizeof(float2) + 17 * sizeof(float)) + (Cf::CH + 2) * sizeof(float2);
+        if (freq_major) irfft2_kernel<16, true><<<B * (C / Cf::CH), 128, smem, st>>>(Yf, B, C, bias, gs, y);
+        else irfft2_kernel<16, false><<<B * (C / Cf::CH), 128, smem, st>>>(Yf, B, C, bias, gs, y);
     } else { set_error("irfft2: unsupported n=%d C=%d", n, C); return -1; }
     count_launch(1);
     return 0;
 }
+// Per-frequency complex mixing as a real GEMM operand: y = Q x with interleaved (re, im) rows / columns
+//   W[phi][2 co + 0][2 ci + 0] =  Re Q   W[phi][2 co + 0][2 ci + 1] = -Im Q
+//   W[phi][2 co + 1][2 ci + 0] =  Im Q   W[phi][2 co + 1][2 ci + 1] =  Re Q          (Q = Qf[phi][co][ci], mix_kernel)
+__global__ void mix_real_weights_kernel(const float2* __restrict__ Qf, long long total, float* __restrict__ W, int cin) {
+    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+        const float2 q = Qf[e];
+        const long long row = e / cin;            // phi * cout + co
+        const int ci = (int)(e - row * cin);
+        float* w0 = W + (row * 2) * (2 * cin) + 2 * ci;
+        float* w1 = w0 + 2 * cin;
+        w0[0] = q.x; w0[1] = -q.y;
+        w1[0] = q.y; w1[1] = q.x;
+    }
+}
+int launch_mix_real_weights(const float2* Qf, int F, int cout, int cin, float* W, cudaStream_t st) {
+    const long long total = (long long)F * cout * cin;
+    mix_real_weights_kernel<<<(unsigned)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048), 256, 0, st>>>(Qf, total, W, cin);
+    count_launch(1);
+    return 0;
+}
+
 template <int COUT, int CIN> static int launch_mix_t(const float2* Xf, const float2* Qf, int B, int F, float2* Yf, cudaStream_t st) {
     const size_t smem = (size_t)4 * CIN * (COUT + 64) * sizeof(float2);
     cudaError_t e = cudaFuncSetAttribute(mix_kernel<COUT, CIN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -393,9 +553,9 @@ extern "C" int fiode_cayley_conv_fwd(const float* x, const float* Qf, const floa
     float2* Xf = reinterpret_cast<float2*>(ws);
     float2* Yf = Xf + (size_t)B * cin * F;
     int rc;
-    if ((rc = launch_rfft2(x, B * cin, cin, n, nullptr, nullptr, Xf, st))) return rc;
+    if ((rc = launch_rfft2(x, B * cin, cin, n, nullptr, nullptr, Xf, st, false))) return rc;
     if ((rc = launch_mix(Xf, reinterpret_cast<const float2*>(Qf), B, F, cout, cin, Yf, st))) return rc;
-    if ((rc = launch_irfft2(Yf, B, cout, n, bias, group_sort, y, st))) return rc;
+    if ((rc = launch_irfft2(Yf, B, cout, n, bias, group_sort, y, st, false))) return rc;
     FIODE_CUDA(cudaGetLastError());
     return 0;
 }

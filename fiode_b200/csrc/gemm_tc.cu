@@ -34,6 +34,7 @@ struct GemmTcArgs {
     const __half* Wp;                 // packed weights, see pack_w_kernel
     const float* bias; int group_sort;
     float* out; long long ldo;        // kLoadRow: out (M, N) row-major; kLoadS2d: out (B, N, n/2, n/2)
+    int nbatch; long long sA, sW, sO; // kLoadRow only: nbatch independent problems (A + f sA, Wp + f sW, out + f sO)
 };
 
 // original output column of local column l of n-tile j.  With GroupSort a tile holds NT/2 columns of the first
@@ -46,10 +47,13 @@ __host__ __device__ __forceinline__ int gt_orig_col(int j, int l, int N, int NT,
 
 // W (N, K) fp32 row-major -> per (n-tile j, k-chunk c) one contiguous block {hi[8][NT][8 halves], lo[8][NT][8 halves]}
 // (K-major 8x16-byte core matrices, the layout tcgen05.mma reads from shared memory), scaled by 64.
-__global__ void pack_w_kernel(const float* __restrict__ W, int N, int K, int NT, int gs, __half* __restrict__ Wp) {
-    const long long total = (long long)N * K;
+__global__ void pack_w_kernel(const float* __restrict__ W0, int N, int K, int NT, int gs, __half* __restrict__ Wp0, int nbatch) {
+    const long long per = (long long)N * K, total = per * nbatch;
     const int kcn = K / GT_KC;
-    for (long long e = blockIdx.x * (long long)blockDim.x + threadIdx.x; e < total; e += (long long)gridDim.x * blockDim.x) {
+    for (long long e0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; e0 < total; e0 += (long long)gridDim.x * blockDim.x) {
+        const long long f = e0 / per, e = e0 - f * per;
+        const float* W = W0 + f * per;
+        __half* Wp = Wp0 + f * per * 2;
         const int k = (int)(e % K);
         const long long jl = e / K;           // tile-major local column index
         const int j = (int)(jl / NT), l = (int)(jl % NT);
@@ -134,7 +138,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
     fence_after_sync();
     const uint32_t tmem = *tmem_slot;
     const int n_nt = a.N / NT, kcn = a.K / GT_KC;
-    const long long tiles = ((a.M + 127) / 128) * n_nt;
+    const long long per_batch = ((a.M + 127) / 128) * n_nt, tiles = per_batch * (a.nbatch > 0 ? a.nbatch : 1);
     const int half_n = a.n / 2, P = half_n * half_n;                      // kLoadS2d geometry
 
     if (warp < 8) {
@@ -146,7 +150,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
         // issue the copies of chunk `it` (if it exists) into own stage `st`
         auto issue = [&](const GtIter& it, int st) {
             if (it.tile < tiles) {
-                const long long mt = it.tile / n_nt;
+                const long long fb = it.tile / per_batch, mt = (it.tile - fb * per_batch) / n_nt;
                 const uint32_t dst = raw0 + st * GT_RAW;
                 if (LOAD == kLoadRow) {       // 16 lanes cover the 256 contiguous bytes of one row
 #pragma unroll
@@ -154,7 +158,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
                         const int rr = q * 32 + 2 * i + (lane >> 4), pc = lane & 15;
                         const long long m = mt * 128 + rr;
                         const bool ok = m < a.M;
-                        cp_async16(dst + rr * 256 + ((pc ^ (rr & 7)) << 4), a.A + (ok ? m : 0) * a.lda + it.c * GT_KC + pc * 4,
+                        cp_async16(dst + rr * 256 + ((pc ^ (rr & 7)) << 4), a.A + fb * a.sA + (ok ? m : 0) * a.lda + it.c * GT_KC + pc * 4,
                                    ok ? 16 : 0);
                     }
                 } else {                      // lane = own pixel; k = 4 ch + 2 dy + dx (einops 'b c (w 2) (h 2) -> b (c 4) w h')
@@ -246,7 +250,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
                 const int b = (int)(it.g & 1), nt = (int)(it.tile % n_nt);
                 mbar_wait(&empty[b], (uint32_t)((it.g >> 1) & 1) ^ 1u);
                 mbar_expect_tx(&b_full[b], kStage);
-                bulk_g2s(wst + b * kStage, a.Wp + ((size_t)nt * kcn + it.c) * (size_t)(2 * NT * GT_KC), kStage, &b_full[b]);
+                bulk_g2s(wst + b * kStage, a.Wp + (it.tile / per_batch) * a.sW + ((size_t)nt * kcn + it.c) * (size_t)(2 * NT * GT_KC), kStage,
+                         &b_full[b]);
             }
         }
     } else {
@@ -278,8 +283,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
                 mbar_arrive(&seg_empty[db]);
             }
             // ---- epilogue: / 64, + bias, GroupSort (layers.py:127-131), store ------------------------------
-            const long long mt = tile / n_nt;
-            const int nt = (int)(tile - mt * n_nt);
+            const long long fb = tile / per_batch, mt = (tile - fb * per_batch) / n_nt;
+            const int nt = (int)(tile % n_nt);
             const long long m = mt * 128 + q * 32 + lane;
             if (m >= a.M) continue;
             const int ca = a.group_sort ? nt * (NT / 2) + hset * W4 : nt * NT + hset * W4;
@@ -292,7 +297,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
                 bb[i] = a.group_sort ? fminf(u, w) : w;
             }
             if (LOAD == kLoadRow) {
-                float* o = a.out + m * a.ldo;
+                float* o = a.out + fb * a.sO + m * a.ldo;
 #pragma unroll
                 for (int i = 0; i < W4; i += 4) {
                     *reinterpret_cast<float4*>(o + ca + i) = make_float4(aa[i], aa[i + 1], aa[i + 2], aa[i + 3]);
@@ -329,10 +334,10 @@ int gemm_tc_tile(int N, int gs) {
     return 32;
 }
 
-int launch_pack_w(const float* W, int N, int K, int NT, int gs, void* Wp, cudaStream_t st) {
-    const long long total = (long long)N * K;
-    const int grid = (int)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
-    pack_w_kernel<<<grid, 256, 0, st>>>(W, N, K, NT, gs, reinterpret_cast<__half*>(Wp));
+int launch_pack_w(const float* W, int N, int K, int NT, int gs, void* Wp, cudaStream_t st, int nbatch) {
+    const long long total = (long long)N * K * nbatch;
+    const int grid = (int)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096);
+    pack_w_kernel<<<grid, 256, 0, st>>>(W, N, K, NT, gs, reinterpret_cast<__half*>(Wp), nbatch);
     FIODE_CUDA(cudaGetLastError());
     count_launch(1);
     return 0;
@@ -342,7 +347,7 @@ template <int LOAD, int NT>
 static int launch_gemm_tc_nt(const GemmTcArgs& a, cudaStream_t st) {
     const size_t smem = (size_t)4 * GT_RAW + (size_t)2 * NT * 2 * GT_KC * 2 + 256;
     FIODE_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<LOAD, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const long long tiles = ((a.M + 127) / 128) * (a.N / NT);
+    const long long tiles = ((a.M + 127) / 128) * (a.N / NT) * (a.nbatch > 0 ? a.nbatch : 1);
     const int grid = (int)(tiles < sm_count() ? tiles : sm_count());       // one persistent CTA per SM
     gemm_tc_kernel<LOAD, NT><<<grid, GT_THREADS, smem, st>>>(a);
     FIODE_CUDA(cudaGetLastError());
@@ -366,6 +371,15 @@ int launch_linear_tc(const float* X, long long lda, const void* Wp, const float*
     GemmTcArgs a{};
     a.A = X; a.lda = lda; a.M = M; a.N = N; a.K = K; a.NT = gemm_tc_tile(N, gs);
     a.Wp = reinterpret_cast<const __half*>(Wp); a.bias = bias; a.group_sort = gs; a.out = y; a.ldo = ldy;
+    return launch_gemm_tc_t<kLoadRow>(a, st);
+}
+// nbatch independent products y_f (M, N) = X_f (M, K) . W_f^T (no bias): the per-frequency channel mixing of a CayleyConv
+int launch_linear_tc_batched(const float* X, long long lda, long long sA, const void* Wp, long long M, int N, int K, int nbatch,
+                             float* y, long long ldy, long long sO, cudaStream_t st) {
+    GemmTcArgs a{};
+    a.A = X; a.lda = lda; a.M = M; a.N = N; a.K = K; a.NT = gemm_tc_tile(N, 0);
+    a.Wp = reinterpret_cast<const __half*>(Wp); a.out = y; a.ldo = ldy;
+    a.nbatch = nbatch; a.sA = sA; a.sO = sO; a.sW = (long long)N * K * 2;
     return launch_gemm_tc_t<kLoadRow>(a, st);
 }
 // stride-2 CayleyConv as a 1x1 conv on the space-to-depth tensor: x (B, cin, n, n) -> y (B, cout, n/2, n/2)

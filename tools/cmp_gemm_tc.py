@@ -38,7 +38,7 @@ for (M, N, K, gs) in [(128, 64, 64, 0), (300, 512, 512, 1), (1000, 512, 4096, 1)
     e_tc = (out[0].double() - ref).abs().max().item(); e_ff = (out[1].double() - ref).abs().max().item()
     print(f'linear M={M:5d} N={N:4d} K={K:5d} gs={gs}: err tc {e_tc:.2e} ffma {e_ff:.2e} | tc {out[0, "t"]:8.1f} us  ffma {out[1, "t"]:8.1f} us '
           f'({2 * M * N * K / out[0, "t"] / 1e6:.1f} TFLOP/s)')
-    bad += e_tc > max(5e-6, 4 * e_ff)
+    bad += e_tc > 1e-5
 sd = fx.synth_state_dict()
 ivp = fx.build_b200_model(sd, device=dev)
 bw, keep = ivp.init_coordinates.param_map.backbone_weights()
