@@ -198,8 +198,87 @@ def certify_bench(ivp, device, pk, iters=3):
                 ms=ms, gpu_launches=launches,
                 roofline=dict(bound='tensor', achieved=tf, peak=pk['bf16'], unit='TFLOP/s', frac=tf / pk['bf16'],
                               traffic=None, peak_source=pk['source'],
-                              note='fp32 FFMA kernel: %.3f of the %.1f TFLOP/s fp32 FFMA pipe' % (tf / FFMA_PEAK_TFLOPS,
-                                                                                                  FFMA_PEAK_TFLOPS)))
+                              kernel='certify_tc_kernel',
+                              note='tcgen05, fp16x2-split FP32 emulation (3 MMAs per product: ceiling = peak / 3, i.e. frac %.3f '
+                                   'of that ceiling); %.2fx the 74.4 TFLOP/s FP32 FFMA pipe the reference formulation would '
+                                   'be bound by; ncu: issue-bound (profiles/)' % (3 * tf / pk['bf16'], tf / FFMA_PEAK_TFLOPS)))
+
+
+# per image: algorithmic HBM bytes (fp32 activations in + out; spectra complex64) and flops of each backbone stage
+#   name, kernel, bytes/img, flop/img
+STAGES = [
+    ('weight packing (per call)', 'pack_w_kernel x5 + mix_real_weights', 0, 0),
+    ('rfft2 32x32, 3 ch (+Normalize)', 'rfft2_kernel<32>', 3 * 1024 * 4 + 3 * 544 * 8, 0.12e6),
+    ('mix 3->32 + irfft2 32x32 + bias + GroupSort', 'irfft32_mix3_kernel', 3 * 544 * 8 + 32 * 1024 * 4, 0.42e6 + 1.1e6),
+    ('conv 128->32 @16x16 (s2d 1x1) + GroupSort', 'gemm_tc_kernel<s2d,32>', 32 * 1024 * 4 + 32 * 256 * 4, 2 * 128 * 32 * 256),
+    ('rfft2 16x16, 32 ch', 'rfft2_kernel<16,fm>', 32 * 256 * 4 + 32 * 144 * 8, 0.3e6),
+    ('mixing 144 x (64->128 real)', 'gemm_tc_kernel<row,128> batched', (32 + 64) * 144 * 8, 2 * 64 * 128 * 144),
+    ('irfft2 16x16, 64 ch + bias + GroupSort', 'irfft2_kernel<16,fm>', 64 * 144 * 8 + 64 * 256 * 4, 0.6e6),
+    ('conv 256->64 @8x8 (s2d 1x1) + GroupSort', 'gemm_tc_kernel<s2d,64>', 64 * 256 * 4 + 64 * 64 * 4, 2 * 256 * 64 * 64),
+    ('linear 4096->512 + GroupSort', 'gemm_tc_kernel<row,128>', 4096 * 4 + 512 * 4, 2 * 4096 * 512),
+    ('linear 512->512 + GroupSort', 'gemm_tc_kernel<row,128>', 512 * 4 * 2, 2 * 512 * 512),
+    ('fc 512->10', 'gemm_nt_kernel', 512 * 4 + 40, 2 * 512 * 10),
+]
+
+
+def stage_roofline(ivp, x_dev, G, ts, pk, iters=10):
+    """Device time of every kernel stage of one step (backbone over G*256 images, then the G-solve dopri5 launch),
+    CUDA events on the launching stream, averaged over ``iters`` runs on rotating (> L2) inputs; the `roofline`
+    object describes the stage with the longest launch."""
+    import ctypes
+    from fiode_b200 import ops
+    from fiode_b200._lib import lib
+    L = lib()
+    n_img = G * B
+    pm = ivp.init_coordinates.param_map
+    bw, keep = pm.backbone_weights()
+    xs = [x.reshape(n_img, 3, 32, 32) for x in x_dev]
+    acc = [0.0] * len(STAGES)
+    buf = (ctypes.c_float * 16)()
+    L.fiode_backbone_enable_stage_timing(1)
+    try:
+        for i in range(iters + 2):
+            s = ops.backbone_fwd(bw, xs[i % len(xs)])
+            rc = L.fiode_backbone_stage_times(buf, 16)
+            if rc == 0 and i >= 2:
+                for j in range(len(STAGES)):
+                    acc[j] += buf[j] / iters
+    finally:
+        L.fiode_backbone_enable_stage_timing(0)
+    dw = ivp.dyn_fun.dyn_weights()
+    h0 = torch.full((n_img, 10), 0.1, device=s.device)
+    t_dev = ts.to(device=s.device, dtype=torch.float64)
+    res = ops.dopri5_simplex_batched(dw, h0, s, G, t_dev, TOL, TOL)
+    st = res.stats()[0]
+    ms_solve = timed(lambda: ops.dopri5_simplex_batched(dw, h0, s, G, t_dev, TOL, TOL), iters) / iters
+    ridge = pk['bf16'] * 1e12 / 3 / (pk['hbm'] * 1e9)      # flop/byte above which the 3-MMA emulation is tensor-bound
+    stages = []
+    for (name, kern, by, fl), ms in zip(STAGES, acc):
+        d = dict(stage=name, kernel=kern, ms=ms)
+        if by:
+            d.update(gbs=by * n_img / (ms * 1e-3) / 1e9 if ms > 0 else None, tflops=fl * n_img / (ms * 1e-3) / 1e12 if ms > 0 else None,
+                     bound='tensor' if fl / by > ridge else 'hbm')
+            d['frac'] = (d['tflops'] / pk['bf16']) if d['bound'] == 'tensor' else (d['gbs'] / pk['hbm'])
+        stages.append(d)
+    solve_flop = sum(x.nfe for x in res.stats()) * RHS_FLOP * B
+    stages.append(dict(stage=f'dopri5, {G} solves x {B} rows (cluster per solve)', kernel='dopri5_simplex_batched_kernel',
+                       ms=ms_solve, tflops=solve_flop / (ms_solve * 1e-3) / 1e12, bound='latency',
+                       note='%d dependent RHS evaluations per solve, 32 rows per CTA: FP32 FFMA, latency-bound' % st.nfe))
+    ms_bb = sum(acc)
+    bb_bytes = sum(x[2] for x in STAGES) * n_img
+    top = max(stages, key=lambda d: d['ms'])
+    if top.get('bound') == 'hbm':
+        rf = dict(bound='hbm', achieved=top['gbs'], peak=pk['hbm'], unit='GB/s', frac=top['gbs'] / pk['hbm'])
+    else:
+        rf = dict(bound='tensor', achieved=top['tflops'], peak=pk['bf16'], unit='TFLOP/s', frac=top['tflops'] / pk['bf16'])
+    rf.update(traffic=None, kernel=top['kernel'], stage=top['stage'], ms_per_launch=top['ms'], peak_source=pk['source'],
+              note='algorithmic bytes / flops of SURVEY 8(d) over the CUDA-event time of that launch; tensor-core stages run the '
+                   'fp16x2-split FP32 emulation (3 MMAs per product), so their ceiling is peak / 3; see DESIGN.md section 4',
+              parts=dict(backbone_ms=ms_bb, backbone_images=n_img, backbone_algorithmic_gbs=bb_bytes / (ms_bb * 1e-3) / 1e9,
+                         backbone_hbm_frac=bb_bytes / (ms_bb * 1e-3) / 1e9 / pk['hbm'],
+                         backbone_tflops=BACKBONE_FLOP * n_img / (ms_bb * 1e-3) / 1e12, dopri5_ms=ms_solve,
+                         nfe=st.nfe, n_accept=st.n_accept, n_reject=st.n_reject, stages=stages))
+    return rf
 
 
 def run_b200(args):
@@ -262,19 +341,38 @@ def run_b200(args):
     value = world * G * args.steps / (ms_max * 1e-3)
 
     # ---- end to end through the public API with host buffers (e2e) ------------------------------
-    def e2e_step(i):
-        xd = x_dev[i % NBUF]
-        xd.copy_(x_host[i % len(x_host)], non_blocking=True)
-        step(xd, y_dev)
-        y_host.copy_(y_dev, non_blocking=True)
-        torch.cuda.synchronize()                       # the caller needs the result on the host
-    for i in range(max(1, args.warmup // 2)):
-        e2e_step(i)
+    # Every step copies its own inputs host -> device (pinned) and its result device -> host inside the timed region.
+    # The copy of step i+1 runs on a second stream while step i computes (two device buffers), which is how a
+    # caller feeding batches from a loader would drive the API; each step still ends with its result on the host.
+    copy_stream = torch.cuda.Stream(device=device)
+    main_stream = torch.cuda.current_stream(device)
+    xe = [torch.empty_like(x_dev[0]) for _ in range(2)]
+    ready = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
+
+    def prefetch(i):
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[i % 2])
+            xe[i % 2].copy_(x_host[i % len(x_host)], non_blocking=True)
+            ready[i % 2].record(copy_stream)
+
+    def e2e_run(n):
+        for k in range(2):
+            consumed[k].record(main_stream)
+        prefetch(0)
+        for i in range(n):
+            if i + 1 < n:
+                prefetch(i + 1)
+            main_stream.wait_event(ready[i % 2])
+            step(xe[i % 2], y_dev)
+            consumed[i % 2].record(main_stream)
+            y_host.copy_(y_dev, non_blocking=True)
+            main_stream.synchronize()                  # the caller needs this step's result on the host
+
+    e2e_run(max(2, args.warmup // 2))
     barrier()
-    t0 = time.perf_counter()
     e0.record()
-    for i in range(args.steps):
-        e2e_step(i)
+    e2e_run(args.steps)
     e1.record()
     torch.cuda.synchronize()
     e2e_ms = e0.elapsed_time(e1)
@@ -289,38 +387,8 @@ def run_b200(args):
             dist.destroy_process_group()
         return
 
-    # ---- per-kernel shares and the roofline of the dominant kernel (rank 0, same stream) ----------
-    x1 = x_dev[0][0]
-    s, state = ivp.init_coordinates(x1, ivp.dyn_fun)
-    ivp.dyn_fun.static_state = s
-    dw = ivp.dyn_fun.dyn_weights()
-    t_dev = ts.to(device=device, dtype=torch.float64)
-    res = ops.dopri5_simplex(dw, state[0], s, t_dev, TOL, TOL)
-    st = res.stats()
-    it = 50
-    ms_solve = timed(lambda: ops.dopri5_simplex(dw, state[0], s, t_dev, TOL, TOL), it) / it
-    pm = ivp.init_coordinates.param_map
-    bw, keep = pm.backbone_weights()
-    xs = [x_dev[i % NBUF][j] for i in range(NBUF) for j in range(G)]
-    cnt = [0]
-
-    def bb():
-        ops.backbone_fwd(bw, xs[cnt[0] % len(xs)]); cnt[0] += 1
-    bb(); bb()
-    ms_bb = timed(bb, it) / it
-    solve_flop = st.nfe * RHS_FLOP * B
-    bb_flop = BACKBONE_FLOP * B
-    tf_solve = solve_flop / (ms_solve * 1e-3) / 1e12
-    tf_bb = bb_flop / (ms_bb * 1e-3) / 1e12
-    dominant = 'dopri5_simplex_kernel' if ms_solve >= ms_bb else 'backbone (10 kernels; top: gemm_nt_kernel 4096->512)'
-    tf = tf_solve if ms_solve >= ms_bb else tf_bb
-    roofline = dict(bound='tensor', achieved=tf, peak=pk['bf16'], unit='TFLOP/s', frac=tf / pk['bf16'], traffic=None,
-                    kernel=dominant, peak_source=pk['source'],
-                    note='fp32 FFMA kernels (no tensor-core use yet): %.3f of the %.1f TFLOP/s fp32 FFMA pipe; the '
-                         'b=256 solve is latency-bound (%.0f dependent RHS evaluations)' % (
-                             tf / FFMA_PEAK_TFLOPS, FFMA_PEAK_TFLOPS, st.nfe),
-                    parts=dict(dopri5_ms=ms_solve, dopri5_tflops=tf_solve, backbone_ms=ms_bb, backbone_tflops=tf_bb,
-                               nfe=st.nfe, n_accept=st.n_accept, n_reject=st.n_reject))
+    # ---- per-kernel device times (CUDA events on the launching stream) and the roofline of the dominant kernel ----
+    roofline = stage_roofline(ivp, x_dev, G, ts, pk)
 
     # ---- CPU baseline beside it (bounded sample) ----------------------------------------------------
     cpu = None

@@ -53,6 +53,8 @@ SIGNATURES = {
     'fiode_cayley_conv': (I, [P, P, I, I, I, I, P, P, SZ, P]),
     'fiode_backbone_workspace_bytes': (SZ, [I]),
     'fiode_backbone_fwd': (I, [C.POINTER(BackboneWeights), P, I, P, P, SZ, P]),
+    'fiode_backbone_enable_stage_timing': (None, [I]),
+    'fiode_backbone_stage_times': (I, [P, I]),
     'fiode_cayley_conv_fwd_workspace_bytes': (SZ, [I, I, I, I]),
     'fiode_cayley_conv_fwd': (I, [P, P, P, I, I, I, I, I, P, P, SZ, P]),
     'fiode_linear_workspace_bytes': (SZ, [I, I, I]),

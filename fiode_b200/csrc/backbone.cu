@@ -35,6 +35,18 @@ static int slab_size() {
 }
 #define kSlab slab_size()
 
+// ---- optional per-stage device timing (bench.py's live roofline numbers): CUDA events on the launching stream ----
+constexpr int kStages = 11;
+static bool g_time_stages = false;
+static cudaEvent_t g_ev[kStages + 1];
+static bool g_ev_ready = false;
+static float g_stage_ms[kStages];
+static void mark(int i, cudaStream_t st) {
+    if (!g_time_stages) return;
+    if (!g_ev_ready) { for (auto& e : g_ev) cudaEventCreate(&e); g_ev_ready = true; }
+    cudaEventRecord(g_ev[i], st);
+}
+
 struct SlabLayout {
     size_t xf0, yf0, a0, a2, xf4, yf4, a4, a6, l9, l11, gws, p2, p6, p9, p11, w4, p4, qt0, total, gws_bytes;
 };
@@ -92,6 +104,7 @@ extern "C" int fiode_backbone_fwd(const fiode_backbone_weights* w, const float* 
     float* gws = (float*)(base + L.gws);
     int rc;
     const bool tcp = mlp_path() == 0;
+    mark(0, st);
     if (tcp) {
         if ((rc = launch_pack_w(w->Q2, 32, 128, gemm_tc_tile(32, 1), 1, base + L.p2, st))) return rc;
         if ((rc = launch_pack_w(w->Q6, 64, 256, gemm_tc_tile(64, 1), 1, base + L.p6, st))) return rc;
@@ -100,45 +113,70 @@ extern "C" int fiode_backbone_fwd(const fiode_backbone_weights* w, const float* 
         if ((rc = launch_mix_real_weights((const float2*)w->Qf4, 144, 64, 32, (float*)(base + L.w4), st))) return rc;
         if ((rc = launch_pack_w((const float*)(base + L.w4), 128, 64, 128, 0, base + L.p4, st, 144))) return rc;
     }
+    mark(1, st);
     for (int b0 = 0; b0 < B; b0 += S) {
         const int nb = (B - b0) < S ? (B - b0) : S;
         const float* xs = x + (size_t)b0 * 3 * 1024;
         // model.0: CayleyConv(3, 32, 3) @32x32 + GroupSort (Normalize fused into the FFT load)
         if ((rc = launch_rfft2(xs, nb * 3, 3, 32, w->mu, w->std, xf0, st))) return rc;
+        mark(2, st);
         if (tcp) {   // mixing fused into the inverse FFT: the 32-channel spectrum never reaches HBM
             if ((rc = launch_irfft32_mix3(xf0, (const float2*)w->Qf0, (float2*)(base + L.qt0), nb, 32, w->b0, 1, a0, st))) return rc;
         } else {
             if ((rc = launch_mix(xf0, (const float2*)w->Qf0, nb, 544, 32, 3, yf0, st))) return rc;
             if ((rc = launch_irfft2(yf0, nb, 32, 32, w->b0, 1, a0, st))) return rc;
         }
+        mark(3, st);
         // model.2: CayleyConv(32, 32, 3, stride=2) == orthogonal 1x1 on space-to-depth + GroupSort
         if ((rc = tcp ? launch_conv1x1_tc(a0, base + L.p2, w->b2, nb, 32, 32, 32, 1, a2, st)
                       : launch_conv1x1(a0, w->Q2, w->b2, nb, 32, 32, 32, 1, a2, st))) return rc;
+        mark(4, st);
         // model.4: CayleyConv(32, 64, 3) @16x16 + GroupSort
         if (tcp) {   // frequency-major spectra: the mixing of frequency phi is the row-major GEMM (nb x 64) . (128 x 64)^T
             if ((rc = launch_rfft2(a2, nb * 32, 32, 16, nullptr, nullptr, xf4, st, true))) return rc;
+            mark(5, st);
             if ((rc = launch_linear_tc_batched((const float*)xf4, 64, (long long)nb * 64, base + L.p4, nb, 128, 64, 144,
                                                (float*)yf4, 128, (long long)nb * 128, st))) return rc;
+            mark(6, st);
             if ((rc = launch_irfft2(yf4, nb, 64, 16, w->b4, 1, a4, st, true))) return rc;
         } else {
             if ((rc = launch_rfft2(a2, nb * 32, 32, 16, nullptr, nullptr, xf4, st))) return rc;
             if ((rc = launch_mix(xf4, (const float2*)w->Qf4, nb, 144, 64, 32, yf4, st))) return rc;
             if ((rc = launch_irfft2(yf4, nb, 64, 16, w->b4, 1, a4, st))) return rc;
         }
+        mark(7, st);
         // model.6: CayleyConv(64, 64, 3, stride=2) + GroupSort -> (nb, 64, 8, 8) == Flatten 4096
         if ((rc = tcp ? launch_conv1x1_tc(a4, base + L.p6, w->b6, nb, 64, 64, 16, 1, a6, st)
                       : launch_conv1x1(a4, w->Q6, w->b6, nb, 64, 64, 16, 1, a6, st))) return rc;
+        mark(8, st);
         // model.9 / model.11 / fc
         if (tcp) {
             if ((rc = launch_linear_tc(a6, 4096, base + L.p9, w->b9, nb, 512, 4096, 1, l9, 512, st))) return rc;
+            mark(9, st);
             if ((rc = launch_linear_tc(l9, 512, base + L.p11, w->b11, nb, 512, 512, 1, l11, 512, st))) return rc;
         } else {
             if ((rc = gemm_nt(a6, 4096, w->Q9, 4096, nb, 512, 4096, w->b9, 1.f, 1, l9, 512, gws, L.gws_bytes, st))) return rc;
             if ((rc = gemm_nt(l9, 512, w->Q11, 512, nb, 512, 512, w->b11, 1.f, 1, l11, 512, gws, L.gws_bytes, st))) return rc;
         }
+        mark(10, st);
         if ((rc = gemm_nt(l11, 512, w->Qfc, 512, nb, 10, 512, w->bfc, 1.f, 0, s_out + (size_t)b0 * 10, 10, gws,
                           L.gws_bytes, st))) return rc;
+        mark(11, st);
     }
     FIODE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+/* Stage timing for bench.py (tensor-core path, one slab): enable, run fiode_backbone_fwd once, then read.  Stages:
+ * 0 weight packing | 1 rfft 32x32 (3 ch) | 2 mix + irfft 32x32 (32 ch) | 3 conv 128->32 @16 (tcgen05) | 4 rfft 16x16 (32 ch)
+ * 5 mixing 144 x (64 -> 128) (tcgen05) | 6 irfft 16x16 (64 ch) | 7 conv 256->64 @8 (tcgen05) | 8 linear 4096->512 (tcgen05)
+ * 9 linear 512->512 (tcgen05) | 10 fc 512->10.  Synchronises the device.                                            */
+extern "C" void fiode_backbone_enable_stage_timing(int on) { fiode::g_time_stages = on != 0; }
+extern "C" int fiode_backbone_stage_times(float* ms_out, int n) {
+    if (!fiode::g_ev_ready) { set_error("fiode_backbone_stage_times: no timed run yet"); return -1; }
+    if (cudaDeviceSynchronize() != cudaSuccess) { set_error("fiode_backbone_stage_times: sync failed"); return -1; }
+    for (int i = 0; i < fiode::kStages && i < n; ++i)
+        if (cudaEventElapsedTime(&ms_out[i], fiode::g_ev[i], fiode::g_ev[i + 1]) != cudaSuccess) {
+            set_error("fiode_backbone_stage_times: events incomplete (tensor-core path, batch <= slab only)"); return -1; }
     return 0;
 }

@@ -84,6 +84,11 @@ FIODE_API size_t fiode_backbone_workspace_bytes(int B);
 FIODE_API int fiode_backbone_fwd(const fiode_backbone_weights* w, const float* x, int B, float* s_out,
                        void* ws, size_t ws_bytes, void* stream);
 
+/* Per-stage device times of the LAST fiode_backbone_fwd (CUDA events on its stream; measurement aid for the
+ * bench's roofline numbers, tensor-core path, batch <= one slab).  11 stages, see backbone.cu.  Synchronises. */
+FIODE_API void fiode_backbone_enable_stage_timing(int on);
+FIODE_API int fiode_backbone_stage_times(float* ms_out, int n);
+
 /* single layers (the reference's nn.Module.forward seams; used by the per-layer parity tests) */
 /* CayleyConv.forward, k=3 (layers.py:72-86): x (B,cin,n,n) -> y (B,cout,n,n), optional fused
  * GroupSort (layers.py:127-131).  n in {8,16,32}.                                             */
