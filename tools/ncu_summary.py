@@ -1,14 +1,80 @@
-"""Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list: per-kernel totals and shares."""
-import csv, collections, sys
-rows = [r for r in csv.reader(open(sys.argv[1])) if len(r) > 10]
-hdr = rows[0]; ki = hdr.index('Kernel Name'); vi = hdr.index('Metric Value'); ui = hdr.index('Metric Unit')
-agg = collections.OrderedDict()
-for r in rows[1:]:
-    v = float(r[vi].replace(',', '')); u = r[ui]
-    v = v / 1e3 if u in ('ns', 'nsecond') else v * 1e3 if u in ('ms', 'msecond') else v
-    a = agg.setdefault(r[ki][:70], [0, 0.0]); a[0] += 1; a[1] += v
-tot = sum(a[1] for a in agg.values())
-print('| kernel | launches | total us | share | avg us |\n|---|---|---|---|---|')
-for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1])[:int(sys.argv[2]) if len(sys.argv) > 2 else 20]:
-    print(f'| `{k}` | {a[0]} | {a[1]:.1f} | {a[1] / tot:.1%} | {a[1] / a[0]:.1f} |')
-print(f'\ntotal {tot:.1f} us over {sum(a[0] for a in agg.values())} launches')
+"""Turn ncu outputs into the markdown summaries kept under profiles/.
+
+    python tools/ncu_summary.py launches gpurun_out/<tag>/launches.csv  > profiles/rNN_launches_summary.md
+    python tools/ncu_summary.py full     gpurun_out/<tag>/full.ncu-rep  > profiles/rNN_ncu_full_summary.md
+"""
+import csv
+import io
+import subprocess
+import sys
+from collections import OrderedDict
+
+METRICS = [
+    'gpu__time_duration.sum', 'launch__grid_size', 'launch__block_size', 'launch__cluster_size', 'launch__registers_per_thread',
+    'launch__shared_mem_per_block_dynamic', 'launch__occupancy_limit_registers', 'launch__occupancy_limit_shared_mem',
+    'sm__warps_active.avg.pct_of_peak_sustained_active', 'sm__throughput.avg.pct_of_peak_sustained_elapsed',
+    'sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active', 'sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active',
+    'sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active',
+    'sm__inst_executed_pipe_tensor.sum', 'smsp__issue_active.avg.pct_of_peak_sustained_active',
+    'dram__bytes_read.sum', 'dram__bytes_write.sum', 'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed',
+    'lts__t_sector_hit_rate.pct', 'l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum',
+    'smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio',
+    'smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio',
+    'smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio',
+    'smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio',
+    'smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio',
+    'smsp__average_warps_issue_stalled_wait_per_issue_active.ratio',
+]
+
+
+def short(name, n=90):
+    name = name.replace('fiode::', '')
+    return name if len(name) <= n else name[:n] + '...'
+
+
+def launches(path):
+    rows = []
+    with open(path, newline='') as f:
+        lines = [l for l in f if l.startswith('"')]
+    rd = csv.DictReader(io.StringIO(''.join(lines)))
+    for r in rd:
+        if r.get('Metric Name') != 'gpu__time_duration.sum':
+            continue
+        v = float(r['Metric Value'].replace(',', ''))
+        unit = r.get('Metric Unit', 'ns')
+        v_us = v / 1e3 if unit in ('ns', 'nsecond') else v if unit in ('us', 'usecond') else v * 1e3 if unit in ('ms', 'msecond') else v
+        rows.append((r['Kernel Name'], v_us))
+    agg = OrderedDict()
+    for k, v in rows:
+        a = agg.setdefault(k, [0, 0.0])
+        a[0] += 1
+        a[1] += v
+    tot = sum(a[1] for a in agg.values())
+    print('| kernel | launches | total us | share | avg us |\n|---|---|---|---|---|')
+    for k, (n, t) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+        print(f'| `{short(k)}` | {n} | {t:.1f} | {100 * t / tot:.1f}% | {t / n:.1f} |')
+    print(f'\n{len(rows)} launches, {tot / 1e3:.2f} ms in total.')
+
+
+def full(path):
+    out = subprocess.run(['ncu', '-i', path, '--page', 'raw', '--csv'], capture_output=True, text=True, check=True).stdout
+    lines = [l for l in out.splitlines(True) if l.startswith('"')]
+    rd = list(csv.reader(io.StringIO(''.join(lines))))
+    head, units, data = rd[0], rd[1], rd[2:]
+    col = {h: i for i, h in enumerate(head)}
+    kn = col['Kernel Name']
+    seen = OrderedDict()
+    for r in data:
+        seen.setdefault(r[kn], []).append(r)
+    for k, rs in seen.items():
+        r = rs[-1]
+        print(f'## `{short(k, 140)}`  ({len(rs)} launch{"es" if len(rs) > 1 else ""} captured; last one shown)\n')
+        print('| metric | value | unit |\n|---|---|---|')
+        for m in METRICS:
+            if m in col:
+                print(f'| {m} | {r[col[m]]} | {units[col[m]]} |')
+        print()
+
+
+if __name__ == '__main__':
+    {'launches': launches, 'full': full}[sys.argv[1]](sys.argv[2])
