@@ -221,7 +221,7 @@ STAGES = [
 ]
 
 
-def stage_roofline(ivp, x_dev, G, ts, pk, iters=10):
+def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
     """Device time of every kernel stage of one step (backbone over G*256 images, then the G-solve dopri5 launch),
     CUDA events on the launching stream, averaged over ``iters`` runs on rotating (> L2) inputs; the `roofline`
     object describes the stage with the longest launch."""
@@ -248,9 +248,9 @@ def stage_roofline(ivp, x_dev, G, ts, pk, iters=10):
     dw = ivp.dyn_fun.dyn_weights()
     h0 = torch.full((n_img, 10), 0.1, device=s.device)
     t_dev = ts.to(device=s.device, dtype=torch.float64)
-    res = ops.dopri5_simplex_batched(dw, h0, s, G, t_dev, TOL, TOL)
+    res = ops.dopri5_simplex_batched(dw, h0, s, G, t_dev, TOL, TOL, cluster_size=cluster_size)
     st = res.stats()[0]
-    ms_solve = timed(lambda: ops.dopri5_simplex_batched(dw, h0, s, G, t_dev, TOL, TOL), iters) / iters
+    ms_solve = timed(lambda: ops.dopri5_simplex_batched(dw, h0, s, G, t_dev, TOL, TOL, cluster_size=cluster_size), iters) / iters
     ridge = pk['bf16'] * 1e12 / 3 / (pk['hbm'] * 1e9)      # flop/byte above which the 3-MMA emulation is tensor-bound
     stages = []
     for (name, kern, by, fl), ms in zip(STAGES, acc):
@@ -263,7 +263,7 @@ def stage_roofline(ivp, x_dev, G, ts, pk, iters=10):
     solve_flop = sum(x.nfe for x in res.stats()) * RHS_FLOP * B
     stages.append(dict(stage=f'dopri5, {G} solves x {B} rows (cluster per solve)', kernel='dopri5_simplex_batched_kernel',
                        ms=ms_solve, tflops=solve_flop / (ms_solve * 1e-3) / 1e12, bound='latency',
-                       note='%d dependent RHS evaluations per solve, 32 rows per CTA: FP32 FFMA, latency-bound' % st.nfe))
+                       note='%d dependent RHS evaluations per solve, %d rows per CTA: FP32 FFMA, latency-bound' % (st.nfe, B // max(cluster_size, 1) if cluster_size else 32)))
     ms_bb = sum(acc)
     bb_bytes = sum(x[2] for x in STAGES) * n_img
     top = max((d for d in stages if 'tflops' in d or 'gbs' in d), key=lambda d: d['ms'])
@@ -294,10 +294,15 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group('nccl', device_id=device)
     pk = peaks()
+    CS = args.cluster_size
     G = args.solves_per_step
+    if G <= 0:
+        # one wave of the cluster-per-solve launch: every solve beyond the co-resident count waits a full solve latency
+        G = ops.dopri5_max_concurrent_solves(B, CS)
+        G = G - G % 16 if G >= 16 else G          # whole backbone slabs (4096 images = 16 batches)
     ivp = build_model(device)
     ts = torch.linspace(0., T_MAX, 2)
-    int_params = dict(method='dopri5', rtol=TOL, atol=TOL, options=dict(check=False))
+    int_params = dict(method='dopri5', rtol=TOL, atol=TOL, options=dict(check=False, cluster_size=CS))
 
     # inputs: NBUF rotating device-resident sets, together larger than the 126 MB L2
     per_set = G * B * 3 * 32 * 32 * 4
@@ -388,7 +393,7 @@ def run_b200(args):
         return
 
     # ---- per-kernel device times (CUDA events on the launching stream) and the roofline of the dominant kernel ----
-    roofline = stage_roofline(ivp, x_dev, G, ts, pk)
+    roofline = stage_roofline(ivp, x_dev, G, ts, pk, cluster_size=CS)
 
     # ---- CPU baseline beside it (bounded sample) ----------------------------------------------------
     cpu = None
@@ -417,7 +422,7 @@ def run_b200(args):
                 ms_per_step=ms_max / args.steps, higher_is_better=True, scaling='weak', vs_baseline=None,
                 dtype='f32', data='synthetic',
                 config=dict(workload='cifar_cayley_node_inference_dopri5_b256_tol1e-3_tmax1', batch=B,
-                            solves_per_step=G, images_per_step=G * B, rtol=TOL, atol=TOL, t_max=T_MAX,
+                            solves_per_step=G, dopri5_cluster_size=CS, images_per_step=G * B, rtol=TOL, atol=TOL, t_max=T_MAX,
                             weights='random init, seed 0', l2='inputs rotate over %d device buffers (%.0f MB > L2)' % (
                                 NBUF, NBUF * per_set / 1e6), parallelism=f'independent batches x{world}'),
                 images_per_s=value * B,
@@ -435,7 +440,8 @@ def main():
     ap.add_argument('--steps', type=int, default=200)
     ap.add_argument('--warmup', type=int, default=10)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
-    ap.add_argument('--solves-per-step', type=int, default=16)
+    ap.add_argument('--solves-per-step', type=int, default=0, help='0 = as many as one dopri5 launch keeps co-resident')
+    ap.add_argument('--cluster-size', type=int, default=4, help='CTAs per solve in the cluster-per-solve dopri5 launch')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-certify', action='store_true')
     args = ap.parse_args()

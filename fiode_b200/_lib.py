@@ -62,6 +62,19 @@ SIGNATURES = {
     'fiode_conv1x1_s2d_fwd': (I, [P, P, P, I, I, I, I, I, P, P]),
     'fiode_space_to_depth': (I, [P, I, I, I, P, P]),
     'fiode_group_sort': (I, [P, I, I, I, P, P]),
+    'fiode_normalize': (I, [P, I, I, I, P, P, P, P]),
+    'fiode_group_sort_bwd': (I, [P, P, I, I, I, P, P]),
+    'fiode_bias_grad': (I, [P, I, I, I, P, P]),
+    'fiode_linear_bwd_workspace_bytes': (SZ, [I, I, I]),
+    'fiode_linear_bwd': (I, [P, P, P, I, I, I, P, P, P, P, SZ, P]),
+    'fiode_conv1x1_s2d_bwd_workspace_bytes': (SZ, [I, I, I, I]),
+    'fiode_conv1x1_s2d_bwd': (I, [P, P, P, I, I, I, I, P, P, P, P, SZ, P]),
+    'fiode_cayley_conv_layer_bwd_workspace_bytes': (SZ, [I, I, I, I]),
+    'fiode_cayley_conv_layer_bwd': (I, [P, P, P, I, I, I, I, P, P, P, P, SZ, P]),
+    'fiode_cayley_linear_bwd_workspace_bytes': (SZ, [I, I]),
+    'fiode_cayley_linear_bwd': (I, [P, P, I, I, P, P, P, P, SZ, P]),
+    'fiode_cayley_conv_bwd_workspace_bytes': (SZ, [I, I, I, I]),
+    'fiode_cayley_conv_bwd': (I, [P, P, I, I, I, I, P, P, P, P, SZ, P]),
     'fiode_rhs_workspace_bytes': (SZ, [LL]),
     'fiode_rhs_fwd': (I, [C.POINTER(DynWeights), P, P, LL, LL, LL, P, P, P, P, P, SZ, P]),
     'fiode_barrier_project_fwd': (I, [P, P, P, LL, I, F32, P, P, P, P, SZ, P]),
@@ -83,6 +96,7 @@ SIGNATURES = {
     'fiode_grid_enumerate': (I, [I, I, LL, LL, P, P, SZ, P]),
     'fiode_dopri5_workspace_bytes': (SZ, [I]),
     'fiode_dopri5_simplex': (I, [C.POINTER(DynWeights), P, P, I, I, P, I, F64, F64, LL, P, P, P, SZ, I, P]),
+    'fiode_dopri5_max_concurrent_solves': (I, [I, I]),
     'fiode_dopri5_simplex_batched': (I, [C.POINTER(DynWeights), P, P, I, I, I, P, I, F64, F64, LL, P, P, I, P]),
 }
 

@@ -1,0 +1,97 @@
+"""torch.autograd glue for the FI training step: every Function's forward AND backward is one C-ABI call
+into libfiode_b200.so (fiode_b200/csrc/train.cu, cayley.cu); autograd only chains them in the order the
+reference's graph does (pl_modules.py:504-506 `loss.backward()` through models_ortho.py:12-28 and
+libs/ortho_conv/layers.py:50-105).  No torch arithmetic on the path."""
+from __future__ import annotations
+
+import torch
+from torch.autograd import Function
+
+from . import ops
+
+
+class CayleyLinearQ(Function):
+    """Q = cayley(alpha * W / ||W||), layers.py:103-104."""
+    @staticmethod
+    def forward(ctx, weight, alpha):
+        ctx.save_for_backward(weight, alpha)
+        return ops.cayley_linear(weight, alpha)
+
+    @staticmethod
+    def backward(ctx, gQ):
+        weight, alpha = ctx.saved_tensors
+        gW, ga = ops.cayley_linear_bwd(weight, alpha, gQ)
+        return gW, ga.reshape(alpha.shape)
+
+
+class CayleyConvQ(Function):
+    """Per-frequency Q of a CayleyConv (layers.py:74-82); real (cout, cin) when k = 1."""
+    @staticmethod
+    def forward(ctx, weight, alpha, n):
+        ctx.save_for_backward(weight, alpha)
+        ctx.n = n
+        return ops.cayley_conv(weight, alpha, n)
+
+    @staticmethod
+    def backward(ctx, gQ):
+        weight, alpha = ctx.saved_tensors
+        gw, ga = ops.cayley_conv_bwd(weight, alpha, ctx.n, gQ)
+        return gw, ga.reshape(alpha.shape), None
+
+
+class Linear(Function):
+    """F.linear(X, Q, b), layers.py:105."""
+    @staticmethod
+    def forward(ctx, X, Q, bias):
+        ctx.save_for_backward(X, Q)
+        ctx.has_bias = bias is not None
+        return ops.linear_fwd(X, Q, bias, False)
+
+    @staticmethod
+    def backward(ctx, gY):
+        X, Q = ctx.saved_tensors
+        gX, gQ, gb = ops.linear_bwd(X, Q, gY, need_gx=ctx.needs_input_grad[0], need_gb=ctx.has_bias)
+        return gX, gQ, gb
+
+
+class Conv1x1S2d(Function):
+    """Emulated stride-2 CayleyConv: space-to-depth + real 1x1 mixing (layers.py:24-48)."""
+    @staticmethod
+    def forward(ctx, x, Q, bias):
+        ctx.save_for_backward(x, Q)
+        ctx.has_bias = bias is not None
+        return ops.conv1x1_s2d_fwd(x, Q, bias, False)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, Q = ctx.saved_tensors
+        gx, gQ, gb = ops.conv1x1_s2d_bwd(x, Q, gy, need_gx=ctx.needs_input_grad[0], need_gb=ctx.has_bias)
+        return gx, gQ, gb
+
+
+class CayleyConvLayer(Function):
+    """y = irfft2(Qf rfft2(x)) + b, layers.py:78-85."""
+    @staticmethod
+    def forward(ctx, x, Qf, bias):
+        ctx.save_for_backward(x, Qf)
+        ctx.has_bias = bias is not None
+        return ops.cayley_conv_fwd(x, Qf, bias, False)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, Qf = ctx.saved_tensors
+        gx, gQf, gb = ops.cayley_conv_layer_bwd(x, Qf, gy, need_gx=ctx.needs_input_grad[0], need_gb=ctx.has_bias)
+        return gx, gQf, gb
+
+
+class GroupSortFn(Function):
+    """layers.py:127-131."""
+    @staticmethod
+    def forward(ctx, x):
+        ctx.save_for_backward(x)
+        return ops.group_sort(x)
+
+    @staticmethod
+    def backward(ctx, gy):
+        (x,) = ctx.saved_tensors
+        return ops.group_sort_bwd(x, gy)

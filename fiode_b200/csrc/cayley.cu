@@ -320,6 +320,326 @@ __global__ void __launch_bounds__(256) cayley_conv_kernel(const float* __restric
     }
 }
 
+
+// ================================================================================================
+// Backward of the Cayley weight preparation (training: libs/ortho_conv/layers.py:50-60 under autograd,
+// reached from loss.backward() at pl_modules.py:504-506).  Forward intermediates are recomputed.
+//   Q = [2M - I ; -2 V M],  M = (I + A)^-1,  A = U - U^H + V^H V,  [U; V] = sc * W,  sc = alpha / (||W|| mult)
+//   gM = 2 G1 - 2 V^H G2 ;  gA = -M^H gM M^H ;  gU = gA - gA^H ;  gV = -2 G2 M^H + V (gA + gA^H)
+//   gW = sc (gWn - W <gWn, W> / ||W||^2) ;  galpha = <gWn, W> / (||W|| mult)
+// ================================================================================================
+// G (R x n) = tr ? gQ^T : gQ ; Gt2 (n x (R-n)) = transpose of G[n:]
+__global__ void cayley_bwd_prep_kernel(const float* __restrict__ gQ, int cout, int cin, int tr, float* __restrict__ G,
+                                       float* __restrict__ Gt2) {
+    const int R = tr ? cin : cout, n = tr ? cout : cin;
+    const size_t total = (size_t)R * n;
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const int r = (int)(e / n), c = (int)(e - (size_t)r * n);
+        const float v = tr ? gQ[(size_t)c * cin + r] : gQ[(size_t)r * cin + c];
+        G[e] = v;
+        if (r >= n) Gt2[(size_t)c * (R - n) + (r - n)] = v;
+    }
+}
+// gM = 2 G1 - 2 P
+__global__ void cayley_bwd_gm_kernel(const float* __restrict__ G1, const float* __restrict__ P, int nn, int has_v,
+                                     float* __restrict__ gM) {
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < nn; e += gridDim.x * blockDim.x)
+        gM[e] = 2.f * G1[e] - (has_v ? 2.f * P[e] : 0.f);
+}
+// from gAt (= gA^T): S = gA + gA^T, gU = gA - gA^T
+__global__ void cayley_bwd_sym_kernel(const float* __restrict__ gAt, int n, float* __restrict__ S, float* __restrict__ gU) {
+    const int total = n * n;
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < total; e += gridDim.x * blockDim.x) {
+        const int i = e / n, j = e - i * n;
+        const float a = gAt[j * n + i], at = gAt[e];
+        S[e] = a + at;
+        gU[e] = a - at;
+    }
+}
+// gWn (cout x cin) = un-transposed [gU ; gV1 + gV2], and per-block partial sums of <gWn, W>
+__global__ void __launch_bounds__(256) cayley_bwd_assemble_kernel(const float* __restrict__ gU, const float* __restrict__ gV1,
+                                                                  const float* __restrict__ gV2, const float* __restrict__ W,
+                                                                  int cout, int cin, int tr, float* __restrict__ gWn,
+                                                                  double* __restrict__ part) {
+    __shared__ double sh[8];
+    const int R = tr ? cin : cout, n = tr ? cout : cin;
+    const size_t total = (size_t)cout * cin;
+    double acc = 0;
+    for (size_t e = blockIdx.x * 256 + threadIdx.x; e < total; e += (size_t)gridDim.x * 256) {
+        const int o = (int)(e / cin), i = (int)(e - (size_t)o * cin);
+        const int r = tr ? i : o, c = tr ? o : i;       // position inside the R x n working matrix
+        float g;
+        if (r < n) g = gU[(size_t)r * n + c];
+        else { const size_t q = (size_t)(r - n) * n + c; g = gV1[q] + gV2[q]; }
+        gWn[e] = g;
+        acc += (double)g * (double)W[e];
+    }
+    (void)R;
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s = 0;
+        for (int i = 0; i < 8; ++i) s += sh[i];
+        part[blockIdx.x] = s;
+    }
+}
+// gW = sc (gWn - W dot / ||W||^2) ; galpha = dot / (||W|| mult)      scale[0] = alpha / (||W|| mult), scale[1] = ||W|| mult
+__global__ void cayley_bwd_finalize_kernel(const float* __restrict__ gWn, const float* __restrict__ W, size_t total,
+                                           const double* __restrict__ part, int np, const float* __restrict__ scale,
+                                           float mult, float* __restrict__ gW, float* __restrict__ galpha) {
+    double dot = 0;
+    for (int i = 0; i < np; ++i) dot += part[i];
+    const float sc = scale[0], nrm_m = scale[1], nrm = nrm_m / mult;
+    const float c2 = (float)(dot / ((double)nrm * nrm));
+    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x)
+        gW[e] = sc * (gWn[e] - W[e] * c2);
+    if (blockIdx.x == 0 && threadIdx.x == 0) galpha[0] = (float)(dot / nrm_m);
+}
+
+size_t cayley_linear_bwd_ws(int cout, int cin) {
+    const size_t R = cout > cin ? cout : cin, n = cout > cin ? cin : cout;
+    size_t b = cayley_linear_ws(cout, cin);
+    b += 2 * align256(R * n * 4);                         // G, gWn
+    b += align256(n * (R - n) * 4 + 4);                   // Gt2
+    b += 2 * align256((R - n) * n * 4 + 4);               // gV1, gV2
+    b += 8 * align256(n * n * 4);                         // P, gM, T1t, gAt, S, gU, Mt, spare
+    return b;
+}
+
+int cayley_linear_bwd_impl(const float* W, const float* alpha, int cout, int cin, float norm_mult, const float* gQ,
+                           float* gW, float* galpha, void* ws, size_t ws_bytes, cudaStream_t st) {
+    if (ws_bytes < cayley_linear_bwd_ws(cout, cin)) { set_error("cayley_linear_bwd: workspace too small"); return -1; }
+    const int tr = cin > cout;
+    const int R = tr ? cin : cout, n = tr ? cout : cin;
+    char* p = reinterpret_cast<char*>(ws);
+    auto take = [&](size_t bytes) { void* r = p; p += align256(bytes); return r; };
+    double* part = (double*)take(kNormBlocks * sizeof(double));
+    float* scale = (float*)take(256);
+    float* Ws = (float*)take((size_t)R * n * 4);
+    float* Vt = (float*)take((size_t)n * (R - n) * 4 + 4);
+    float* Gm = (float*)take((size_t)n * n * 4);          // V^T V
+    float* X = (float*)take((size_t)n * n * 4);
+    float* Y = (float*)take((size_t)n * n * 4);
+    float* ImAT = (float*)take((size_t)n * n * 4);
+    float* Mt = (float*)take((size_t)n * n * 4);
+    float* G = (float*)take((size_t)R * n * 4);
+    float* gWn = (float*)take((size_t)R * n * 4);
+    float* Gt2 = (float*)take((size_t)n * (R - n) * 4 + 4);
+    float* gV1 = (float*)take((size_t)(R - n) * n * 4 + 4);
+    float* gV2 = (float*)take((size_t)(R - n) * n * 4 + 4);
+    float* P = (float*)take((size_t)n * n * 4);
+    float* gM = (float*)take((size_t)n * n * 4);
+    float* T1t = (float*)take((size_t)n * n * 4);
+    float* gAt = (float*)take((size_t)n * n * 4);
+    float* S = (float*)take((size_t)n * n * 4);
+    float* gU = (float*)take((size_t)n * n * 4);
+    float* gws = (float*)p;
+    const size_t gws_bytes = ws_bytes - (size_t)(p - reinterpret_cast<char*>(ws));
+    if (gws_bytes < gemm_nt_workspace(R, n, R)) { set_error("cayley_linear_bwd: gemm workspace too small"); return -1; }
+
+    // ---- recompute the forward up to M -------------------------------------------------------------
+    const size_t total = (size_t)cout * cin;
+    sumsq_partial_kernel<<<kNormBlocks, 256, 0, st>>>(W, total, part);
+    norm_finalize_kernel<<<1, 32, 0, st>>>(part, kNormBlocks, alpha, norm_mult, scale);
+    const unsigned blocks = (unsigned)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
+    cayley_prep1_kernel<<<blocks, 256, 0, st>>>(W, cout, cin, tr, scale, Ws, Vt);
+    count_launch(3);
+    int rc;
+    const int has_v = R > n;
+    if (has_v && (rc = gemm_nt(Vt, R - n, Vt, R - n, n, n, R - n, nullptr, 1.f, 0, Gm, n, gws, gws_bytes, st))) return rc;
+    const int nb = (n * n + 255) / 256;
+    cayley_prep2_kernel<<<nb, 256, 0, st>>>(Ws, Gm, n, has_v, X, ImAT);
+    count_launch(1);
+    float* M = nullptr;
+    if ((rc = gj_inverse(X, Y, n, &M, st))) return rc;
+    transpose_kernel<<<dim3((n + 31) / 32, (n + 31) / 32), dim3(32, 8), 0, st>>>(M, n, n, Mt);
+    // ---- backward -----------------------------------------------------------------------------------
+    cayley_bwd_prep_kernel<<<blocks, 256, 0, st>>>(gQ, cout, cin, tr, G, Gt2);
+    count_launch(2);
+    const float* V = Ws + (size_t)n * n;
+    const float* G2 = G + (size_t)n * n;
+    if (has_v && (rc = gemm_nt(Vt, R - n, Gt2, R - n, n, n, R - n, nullptr, 1.f, 0, P, n, gws, gws_bytes, st))) return rc;
+    cayley_bwd_gm_kernel<<<nb, 256, 0, st>>>(G, P, n * n, has_v, gM);
+    count_launch(1);
+    if ((rc = gemm_nt(M, n, gM, n, n, n, n, nullptr, 1.f, 0, T1t, n, gws, gws_bytes, st))) return rc;       // (gM M^T)^T
+    if ((rc = gemm_nt(T1t, n, Mt, n, n, n, n, nullptr, -1.f, 0, gAt, n, gws, gws_bytes, st))) return rc;    // gA^T = -T1^T M
+    cayley_bwd_sym_kernel<<<nb, 256, 0, st>>>(gAt, n, S, gU);
+    count_launch(1);
+    if (has_v) {
+        if ((rc = gemm_nt(G2, n, M, n, R - n, n, n, nullptr, -2.f, 0, gV1, n, gws, gws_bytes, st))) return rc;   // -2 G2 M^T
+        if ((rc = gemm_nt(V, n, S, n, R - n, n, n, nullptr, 1.f, 0, gV2, n, gws, gws_bytes, st))) return rc;     // V (gA + gA^T)
+    }
+    cayley_bwd_assemble_kernel<<<kNormBlocks, 256, 0, st>>>(gU, gV1, gV2, W, cout, cin, tr, gWn, part);
+    cayley_bwd_finalize_kernel<<<blocks, 256, 0, st>>>(gWn, W, total, part, kNormBlocks, scale, norm_mult, gW, galpha);
+    count_launch(2);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return cuda_fail(e, "cayley_linear_bwd");
+    return 0;
+}
+
+// ---- convolution (k > 1): one CTA per frequency, everything in shared memory ---------------------------
+// Writes gWn[phi] (cout x cin complex, gradient w.r.t. the scaled spectrum sc * wfft) and dotp[phi] = Re <gWn[phi], wfft[phi]>.
+__global__ void __launch_bounds__(256) cayley_conv_bwd_kernel(const float* __restrict__ w, const float* __restrict__ alpha,
+                                                              const double* __restrict__ part, int F, int cout, int cin,
+                                                              int k, int n, const float2* __restrict__ gQf,
+                                                              float2* __restrict__ gWn, double* __restrict__ dotp) {
+    extern __shared__ float4 smem4[];
+    float2* Wf = reinterpret_cast<float2*>(smem4);       // [cout][cin] scaled spectrum
+    float2* X = Wf + cout * cin;
+    float2* Y = X + cin * cin;
+    float2* Gq = Y + cin * cin;                           // [cout][cin] incoming gradient
+    float2* gM = Gq + cout * cin;
+    float2* T = gM + cin * cin;
+    float2* gA = T + cin * cin;
+    __shared__ float sc_sh;
+    __shared__ double red[8];
+    const int t = threadIdx.x, phi = blockIdx.x, H = n / 2 + 1, u = phi / H, v = phi - u * H;
+    if (t == 0) {
+        double s = 0;
+        for (int i = 0; i < F; ++i) s += part[i];
+        sc_sh = alpha[0] / (float)sqrt(s);
+    }
+    __syncthreads();
+    const float sc = sc_sh;
+    const float2* gsrc = gQf + (size_t)phi * cout * cin;
+    for (int e = t; e < cout * cin; e += 256) {
+        const float2 z = conv_spectrum_at(w + (size_t)e * k * k, k, n, u, v);
+        Wf[e] = make_float2(sc * z.x, sc * z.y);
+        Gq[e] = gsrc[e];
+    }
+    __syncthreads();
+    const int nv = cout - cin;
+    for (int e = t; e < cin * cin; e += 256) {
+        const int i = e / cin, j = e - i * cin;
+        const float2 uij = Wf[i * cin + j], uji = Wf[j * cin + i];
+        float2 g = make_float2(0.f, 0.f);
+        for (int r = 0; r < nv; ++r) cfma(g, cconj(Wf[(cin + r) * cin + i]), Wf[(cin + r) * cin + j]);
+        X[e] = make_float2((i == j ? 1.f : 0.f) + uij.x - uji.x + g.x, uij.y + uji.y + g.y);
+    }
+    __syncthreads();
+    for (int kk = 0; kk < cin; ++kk) {
+        const float2* in = (kk & 1) ? Y : X;
+        float2* out = (kk & 1) ? X : Y;
+        const float2 pv = in[kk * cin + kk];
+        const float den = 1.f / (pv.x * pv.x + pv.y * pv.y);
+        const float2 ip = make_float2(pv.x * den, -pv.y * den);
+        for (int e = t; e < cin * cin; e += 256) {
+            const int i = e / cin, j = e - i * cin;
+            float2 r;
+            if (i == kk) r = (j == kk) ? ip : cmul(in[e], ip);
+            else {
+                const float2 f = in[i * cin + kk];
+                if (j == kk) { const float2 q = cmul(f, ip); r = make_float2(-q.x, -q.y); }
+                else { const float2 q = cmul(f, cmul(in[kk * cin + j], ip)); r = csub(in[e], q); }
+            }
+            out[e] = r;
+        }
+        __syncthreads();
+    }
+    const float2* M = (cin & 1) ? Y : X;
+    const float2* V = Wf + cin * cin;
+    const float2* G2 = Gq + cin * cin;
+    // gM = 2 G1 - 2 V^H G2
+    for (int e = t; e < cin * cin; e += 256) {
+        const int i = e / cin, j = e - i * cin;
+        float2 acc = make_float2(0.f, 0.f);
+        for (int r = 0; r < nv; ++r) cfma(acc, cconj(V[r * cin + i]), G2[r * cin + j]);
+        gM[e] = make_float2(2.f * (Gq[e].x - acc.x), 2.f * (Gq[e].y - acc.y));
+    }
+    __syncthreads();
+    // T = gM M^H
+    for (int e = t; e < cin * cin; e += 256) {
+        const int i = e / cin, j = e - i * cin;
+        float2 acc = make_float2(0.f, 0.f);
+        for (int r = 0; r < cin; ++r) cfma(acc, gM[i * cin + r], cconj(M[j * cin + r]));
+        T[e] = acc;
+    }
+    __syncthreads();
+    // gA = -M^H T
+    for (int e = t; e < cin * cin; e += 256) {
+        const int i = e / cin, j = e - i * cin;
+        float2 acc = make_float2(0.f, 0.f);
+        for (int r = 0; r < cin; ++r) cfma(acc, cconj(M[r * cin + i]), T[r * cin + j]);
+        gA[e] = make_float2(-acc.x, -acc.y);
+    }
+    __syncthreads();
+    // gU = gA - gA^H ; gV = -2 G2 M^H + V (gA + gA^H) ; dot with the unscaled spectrum
+    double dacc = 0;
+    float2* dst = gWn + (size_t)phi * cout * cin;
+    const float inv_sc = 1.f / sc;
+    for (int e = t; e < cout * cin; e += 256) {
+        const int i = e / cin, j = e - i * cin;
+        float2 g;
+        if (i < cin) {
+            const float2 a = gA[i * cin + j], b = gA[j * cin + i];
+            g = make_float2(a.x - b.x, a.y + b.y);
+        } else {
+            const int r = i - cin;
+            float2 a1 = make_float2(0.f, 0.f), a2 = make_float2(0.f, 0.f);
+            for (int q = 0; q < cin; ++q) {
+                cfma(a1, G2[r * cin + q], cconj(M[j * cin + q]));
+                const float2 x = gA[q * cin + j], y = gA[j * cin + q];
+                cfma(a2, V[r * cin + q], make_float2(x.x + y.x, x.y - y.y));
+            }
+            g = make_float2(a2.x - 2.f * a1.x, a2.y - 2.f * a1.y);
+        }
+        dst[e] = g;
+        dacc += ((double)g.x * Wf[e].x + (double)g.y * Wf[e].y) * inv_sc;
+    }
+    dacc = warp_sum(dacc);
+    if ((t & 31) == 0) red[t >> 5] = dacc;
+    __syncthreads();
+    if (t == 0) {
+        double s = 0;
+        for (int i = 0; i < 8; ++i) s += red[i];
+        dotp[phi] = s;
+    }
+}
+// gw[o,i,a,b] = sum_phi Re( conj(e^{i theta}) * sc (gWn - wfft D / ||wfft||^2) ) ; galpha = D / ||wfft||
+__global__ void __launch_bounds__(128) cayley_conv_bwd_taps_kernel(const float* __restrict__ w, const float* __restrict__ alpha,
+                                                                   const double* __restrict__ part,
+                                                                   const double* __restrict__ dotp, int F, int cout, int cin,
+                                                                   int k, int n, const float2* __restrict__ gWn,
+                                                                   float* __restrict__ gw, float* __restrict__ galpha) {
+    __shared__ double sh[2];
+    __shared__ double tap[4][9];
+    const int t = threadIdx.x, e = blockIdx.x, H = n / 2 + 1, s = (k - 1) / 2;   // e = o * cin + i
+    if (t < 2) {
+        double a = 0;
+        const double* src = t ? dotp : part;
+        for (int i = 0; i < F; ++i) a += src[i];
+        sh[t] = a;
+    }
+    __syncthreads();
+    const double nrm2 = sh[0], D = sh[1];
+    const float sc = alpha[0] / (float)sqrt(nrm2);
+    const float c2 = (float)(D / nrm2);
+    double acc[9];
+    for (int q = 0; q < 9; ++q) acc[q] = 0;
+    for (int phi = t; phi < F; phi += 128) {
+        const int u = phi / H, v = phi - u * H;
+        const float2 z = conv_spectrum_at(w + (size_t)e * k * k, k, n, u, v);
+        const float2 g0 = gWn[(size_t)phi * cout * cin + e];
+        const float gx = sc * (g0.x - z.x * c2), gy = sc * (g0.y - z.y * c2);
+        for (int a = 0; a < k; ++a)
+            for (int b = 0; b < k; ++b) {
+                int m = (u * (a - s) + v * (b - s)) % n;
+                if (m < 0) m += n;
+                float sn, cs;
+                sincospif(2.f * (float)m / (float)n, &sn, &cs);
+                acc[a * k + b] += (double)(gx * cs + gy * sn);
+            }
+    }
+    for (int q = 0; q < k * k; ++q) {
+        const double r = warp_sum(acc[q]);
+        if ((t & 31) == 0) tap[t >> 5][q] = r;
+    }
+    __syncthreads();
+    if (t < k * k) gw[(size_t)e * k * k + t] = (float)(tap[0][t] + tap[1][t] + tap[2][t] + tap[3][t]);
+    if (e == 0 && t == 0) galpha[0] = (float)(D / sqrt(nrm2));
+}
+
 }  // namespace fiode
 
 using namespace fiode;
@@ -372,5 +692,44 @@ extern "C" int fiode_cayley_conv(const float* w, const float* alpha, int cout, i
                                              reinterpret_cast<float2*>(Qf));
     FIODE_CUDA(cudaGetLastError());
     count_launch(2);
+    return 0;
+}
+
+// ---- backward of the weight preparation (training) ---------------------------------------------------
+extern "C" size_t fiode_cayley_linear_bwd_workspace_bytes(int cout, int cin) { return cayley_linear_bwd_ws(cout, cin); }
+
+extern "C" int fiode_cayley_linear_bwd(const float* W, const float* alpha, int cout, int cin, const float* gQ, float* gW,
+                                       float* galpha, void* ws, size_t ws_bytes, void* stream) {
+    if (!W || !alpha || !gQ || !gW || !galpha || !ws) { set_error("fiode_cayley_linear_bwd: null pointer"); return -1; }
+    if (cout <= 0 || cin <= 0) { set_error("fiode_cayley_linear_bwd: bad shape"); return -1; }
+    return cayley_linear_bwd_impl(W, alpha, cout, cin, 1.f, gQ, gW, galpha, ws, ws_bytes, (cudaStream_t)stream);
+}
+
+extern "C" size_t fiode_cayley_conv_bwd_workspace_bytes(int cout, int cin, int k, int n) {
+    if (k == 1) return cayley_linear_bwd_ws(cout, cin);
+    const size_t F = (size_t)n * (n / 2 + 1);
+    return 2 * conv_part_bytes(n) + align256(F * cout * cin * sizeof(float2));
+}
+
+extern "C" int fiode_cayley_conv_bwd(const float* w, const float* alpha, int cout, int cin, int k, int n, const float* gQf,
+                                     float* gw, float* galpha, void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    if (!w || !alpha || !gQf || !gw || !galpha || !ws) { set_error("fiode_cayley_conv_bwd: null pointer"); return -1; }
+    const int F = n * (n / 2 + 1);
+    if (k == 1) return cayley_linear_bwd_impl(w, alpha, cout, cin, sqrtf((float)F), gQf, gw, galpha, ws, ws_bytes, st);
+    if (cout < cin || k * k > 9) { set_error("fiode_cayley_conv_bwd: needs cout >= cin and k <= 3"); return -1; }
+    if (ws_bytes < fiode_cayley_conv_bwd_workspace_bytes(cout, cin, k, n)) { set_error("fiode_cayley_conv_bwd: workspace too small"); return -1; }
+    char* p = reinterpret_cast<char*>(ws);
+    double* part = (double*)p; p += conv_part_bytes(n);
+    double* dotp = (double*)p; p += conv_part_bytes(n);
+    float2* gWn = (float2*)p;
+    const size_t smem = (size_t)(2 * cout * cin + 5 * cin * cin) * sizeof(float2);
+    if (smem > 200 * 1024) { set_error("fiode_cayley_conv_bwd: layer too large for the in-smem solver"); return -1; }
+    FIODE_CUDA(cudaFuncSetAttribute(cayley_conv_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    conv_spectrum_sumsq_kernel<<<F, 256, 0, st>>>(w, cout, cin, k, n, part);
+    cayley_conv_bwd_kernel<<<F, 256, smem, st>>>(w, alpha, part, F, cout, cin, k, n, reinterpret_cast<const float2*>(gQf), gWn, dotp);
+    cayley_conv_bwd_taps_kernel<<<cout * cin, 128, 0, st>>>(w, alpha, part, dotp, F, cout, cin, k, n, gWn, gw, galpha);
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(3);
     return 0;
 }

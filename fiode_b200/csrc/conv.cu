@@ -10,6 +10,7 @@
 //
 // Spectra are kept in torch's rfft2 layout [b][c][u][v], v in [0, n/2], phi = u*(n/2+1)+v.
 #include "common.cuh"
+#include <cstdlib>
 #include "fft.cuh"
 
 namespace fiode {
@@ -277,15 +278,30 @@ __global__ void __launch_bounds__(160) irfft32_mix3_kernel(const float2* __restr
     }
 }
 // Qt: workspace of F * cout * 3 float2
-int launch_irfft32_mix3(const float2* Xf, const float2* Qf, float2* Qt, int B, int C, const float* bias, int gs, float* y,
-                        cudaStream_t st) {
-    constexpr int IM = 2, F = 544;
-    if (C % 8) { set_error("irfft32_mix3: C=%d", C); return -1; }
-    transpose_q_kernel<<<(F * C * 3 + 255) / 256, 256, 0, st>>>(Qf, F, C * 3, Qt);
+template <int IM>
+static int launch_irfft32_mix3_t(const float2* Xf, const float2* Qt, int B, int C, const float* bias, int gs, float* y,
+                                 cudaStream_t st) {
+    constexpr int F = 544;
     const size_t smem = (size_t)IM * 8 * (32 * 18 + 1) * sizeof(float2) + 16 + (size_t)IM * 3 * F * sizeof(float2);
     cudaError_t e = cudaFuncSetAttribute(irfft32_mix3_kernel<IM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return cuda_fail(e, "irfft32_mix3 smem attr");
     irfft32_mix3_kernel<IM><<<((B + IM - 1) / IM) * (C / 8), 160, smem, st>>>(Xf, Qt, B, C, bias, gs, y);
+    return 0;
+}
+// images per CTA: 2 reuses every Q value twice (2 CTAs / SM), 1 halves the footprint (4 CTAs / SM); FIODE_MIX3_IM overrides
+static int mix3_images_per_cta() {
+    static int v = [] { const char* e = getenv("FIODE_MIX3_IM"); const int x = e ? atoi(e) : 2; return x == 1 ? 1 : 2; }();
+    return v;
+}
+// Qt: workspace of F * cout * 3 float2
+int launch_irfft32_mix3(const float2* Xf, const float2* Qf, float2* Qt, int B, int C, const float* bias, int gs, float* y,
+                        cudaStream_t st) {
+    constexpr int F = 544;
+    if (C % 8) { set_error("irfft32_mix3: C=%d", C); return -1; }
+    transpose_q_kernel<<<(F * C * 3 + 255) / 256, 256, 0, st>>>(Qf, F, C * 3, Qt);
+    const int rc = mix3_images_per_cta() == 1 ? launch_irfft32_mix3_t<1>(Xf, Qt, B, C, bias, gs, y, st)
+                                              : launch_irfft32_mix3_t<2>(Xf, Qt, B, C, bias, gs, y, st);
+    if (rc) return rc;
     count_launch(2);
     return 0;
 }

@@ -532,3 +532,25 @@ extern "C" int fiode_dopri5_simplex_batched(const fiode_dyn_weights* w, const fl
     count_launch(1);
     return 0;
 }
+
+// How many solves of B rows one launch of fiode_dopri5_simplex_batched keeps co-resident (one cluster each).  A launch with
+// more solves than this runs in waves, each wave costing a full solve latency, so callers size G to a multiple of it.
+extern "C" int fiode_dopri5_max_concurrent_solves(int B, int cluster_size) {
+    int C = cluster_size;
+    if (C <= 0) { C = 8; while (C > 1 && (B + C - 1) / C < 8) C >>= 1; }
+    if (C != 1 && C != 2 && C != 4 && C != 8) { set_error("fiode_dopri5_max_concurrent_solves: cluster size must be 1, 2, 4 or 8"); return -1; }
+    const int R = (B + C - 1) / C;
+    if (B <= 0 || R > 64) { set_error("fiode_dopri5_max_concurrent_solves: B=%d does not fit a cluster of %d x 64 rows", B, C); return -2; }
+    int rc = ensure_smem_attr();
+    if (rc) return rc;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(C * 1024)); cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = solver_smem_bytes(R);
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = C; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    int n = 0;
+    FIODE_CUDA(cudaOccupancyMaxActiveClusters(&n, dopri5_simplex_kernel<true>, &cfg));
+    return n;
+}

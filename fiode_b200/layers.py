@@ -4,8 +4,10 @@
 Differences a maintainer should know about:
   * the Cayley matrices are cached per *weight version* (the reference recomputes the conv ones on
     every forward and never invalidates the linear ones in eval mode, layers.py:72-86, 103-105);
-  * forward only (inference / certification).  Training goes through the fused FI-loss op, which has
-    its own hand-written backward.
+  * in ``.eval()`` mode (inference / certification) the layers run forward only on the fused kernels;
+    in ``.train()`` mode with gradients enabled every layer goes through ``fiode_b200.autograd`` -- one C-ABI
+    call forward, one hand-written adjoint backward (csrc/train.cu, csrc/cayley.cu) -- so that
+    ``loss.backward()`` fills ``weight.grad / bias.grad / alpha.grad`` like the reference's autograd graph.
 """
 from __future__ import annotations
 
@@ -13,6 +15,13 @@ import torch
 from torch import nn
 
 from . import ops
+from . import autograd as ag
+
+
+def _differentiable(module, x):
+    """The reference's graph reaches the weights only in train mode (layers.py:103-105); mirror that."""
+    return module.training and torch.is_grad_enabled() and (
+        x.requires_grad or any(p.requires_grad for p in module.parameters(recurse=False)))
 
 
 def cayley(W):
@@ -24,6 +33,8 @@ def cayley(W):
 class GroupSort(nn.Module):
     """layers.py:127-131."""
     def forward(self, x):
+        if torch.is_grad_enabled() and x.requires_grad:
+            return ag.GroupSortFn.apply(x)
         return ops.group_sort(x)
 
 
@@ -53,7 +64,17 @@ class CayleyLinear(nn.Linear):
             self._q_key = key
         return self.Q
 
+    def orthogonal_weight_autograd(self):
+        """Q as a node of the autograd graph (its backward is fiode_cayley_linear_bwd); the detached value also
+        refreshes the cache that ``orthogonal_weight`` / ``dyn_weights`` read."""
+        Q = ag.CayleyLinearQ.apply(self.weight, self.alpha)
+        self.Q, self._q_key = Q.detach(), _version(self.weight, self.alpha)
+        return Q
+
     def forward(self, X, group_sort=False):
+        if _differentiable(self, X):
+            y = ag.Linear.apply(X, self.orthogonal_weight_autograd(), self.bias)
+            return ag.GroupSortFn.apply(y) if group_sort else y
         return ops.linear_fwd(X, self.orthogonal_weight(), self.bias, group_sort)
 
 
@@ -87,6 +108,12 @@ class CayleyConv(nn.Conv2d):
 
     def forward(self, x, group_sort=False):
         n = x.shape[-1] // (2 if self.striding else 1)
+        if _differentiable(self, x):
+            if self.alpha is None:
+                self.alpha = nn.Parameter(ops.conv_alpha_init(self.weight, n))
+            Qf = ag.CayleyConvQ.apply(self.weight, self.alpha, n)
+            y = (ag.Conv1x1S2d if self.striding else ag.CayleyConvLayer).apply(x, Qf, self.bias)
+            return ag.GroupSortFn.apply(y) if group_sort else y
         Qf = self.orthogonal_spectrum(n)
         if self.striding:
             assert self.kernel_size[0] == 1

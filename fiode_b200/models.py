@@ -74,6 +74,9 @@ class ParamMap(nn.Sequential):
         return bw, t
 
     def forward(self, x):
+        if self.training and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
+            # training: layer by layer through fiode_b200.autograd so that loss.backward() reaches every weight
+            return self[1](ops.normalize(x, self[0].mu, self[0].std))
         assert self[1].out_dim == 10
         bw, keep = self.backbone_weights()
         return ops.backbone_fwd(bw, x, keep)
@@ -121,7 +124,8 @@ class IVP(nn.Module):
         opts = p.get('options') or {}
         static_state, state = self.init_coordinates(x.reshape(G * B, *x.shape[2:]), self.dyn_fun)
         res = ops.dopri5_simplex_batched(self.dyn_fun.dyn_weights(), state[0], static_state, G, ts, p['rtol'], p['atol'],
-                                         max_num_steps=opts.get('max_num_steps', 2 ** 31 - 1))
+                                         max_num_steps=opts.get('max_num_steps', 2 ** 31 - 1),
+                                         cluster_size=opts.get('cluster_size', 0))
         if opts.get('check', True):
             res.raise_for_status()
         if return_result:

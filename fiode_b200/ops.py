@@ -330,3 +330,111 @@ def dopri5_simplex_batched(dw: DynWeights, h0, s, G, t, rtol, atol, max_num_step
                                              float(atol), int(max_num_steps), ptr(out), ptr(stats), int(cluster_size),
                                              stream_ptr()), 'fiode_dopri5_simplex_batched')
     return BatchedSolveResult(out, stats, G)
+
+
+def dopri5_max_concurrent_solves(B, cluster_size=0):
+    """Solves of B rows one ``dopri5_simplex_batched`` launch keeps co-resident (a cluster each); more run in waves."""
+    n = lib().fiode_dopri5_max_concurrent_solves(int(B), int(cluster_size))
+    if n < 0:
+        check(n, 'fiode_dopri5_max_concurrent_solves')
+    return n
+
+
+# ---- training: adjoints of the backbone layers and of the Cayley transform ------------------------
+def _opt(t):
+    return ptr(t) if t is not None else None
+
+
+def normalize(x, mu, std):
+    """Normalize.forward (models.py:23-26)."""
+    x = _f32(x)
+    B, Cc = x.shape[:2]
+    inner = x[0, 0].numel()
+    y = torch.empty_like(x)
+    check(lib().fiode_normalize(ptr(x), B, Cc, inner, ptr(_f32(mu).reshape(-1)), ptr(_f32(std).reshape(-1)), ptr(y),
+                                stream_ptr()), 'fiode_normalize')
+    return y
+
+
+def group_sort_bwd(x_pre, gy):
+    x_pre, gy = _f32(x_pre), _f32(gy)
+    B, Cc = x_pre.shape[:2]
+    inner = x_pre[0, 0].numel() if x_pre.dim() > 2 else 1
+    gx = torch.empty_like(x_pre)
+    check(lib().fiode_group_sort_bwd(ptr(x_pre), ptr(gy), B, Cc, inner, ptr(gx), stream_ptr()), 'fiode_group_sort_bwd')
+    return gx
+
+
+def linear_bwd(X, Q, gY, need_gx=True, need_gb=True):
+    """Adjoint of linear_fwd: returns (gX or None, gQ, gb or None)."""
+    X, Q, gY = _f32(X), _f32(Q), _f32(gY)
+    X2, g2 = X.reshape(-1, X.shape[-1]), gY.reshape(-1, gY.shape[-1])
+    M, K = X2.shape
+    N = Q.shape[0]
+    gX = torch.empty(M, K, dtype=torch.float32, device=X.device) if need_gx else None
+    gQ = torch.empty(N, K, dtype=torch.float32, device=X.device)
+    gb = torch.empty(N, dtype=torch.float32, device=X.device) if need_gb else None
+    nb = lib().fiode_linear_bwd_workspace_bytes(M, N, K)
+    ws = _ws(nb, X.device)
+    check(lib().fiode_linear_bwd(ptr(X2), ptr(Q), ptr(g2), M, N, K, _opt(gX), ptr(gQ), _opt(gb), ptr(ws), nb, stream_ptr()),
+          'fiode_linear_bwd')
+    return (gX.reshape(X.shape) if need_gx else None), gQ, gb
+
+
+def conv1x1_s2d_bwd(x, Q, gy, need_gx=True, need_gb=True):
+    x, Q, gy = _f32(x), _f32(Q), _f32(gy)
+    B, cin, n, _ = x.shape
+    cout = Q.shape[0]
+    gx = torch.empty_like(x) if need_gx else None
+    gQ = torch.empty_like(Q)
+    gb = torch.empty(cout, dtype=torch.float32, device=x.device) if need_gb else None
+    nb = lib().fiode_conv1x1_s2d_bwd_workspace_bytes(B, cin, cout, n)
+    ws = _ws(nb, x.device)
+    check(lib().fiode_conv1x1_s2d_bwd(ptr(x), ptr(Q), ptr(gy), B, cin, cout, n, _opt(gx), ptr(gQ), _opt(gb), ptr(ws), nb,
+                                      stream_ptr()), 'fiode_conv1x1_s2d_bwd')
+    return gx, gQ, gb
+
+
+def cayley_conv_layer_bwd(x, Qf, gy, need_gx=True, need_gb=True):
+    """Adjoint of cayley_conv_fwd: returns (gx or None, gQf complex (F,cout,cin), gb or None)."""
+    x, gy = _f32(x), _f32(gy)
+    B, cin, n, _ = x.shape
+    Qr = torch.view_as_real(Qf).contiguous()
+    F, cout = Qr.shape[:2]
+    gx = torch.empty_like(x) if need_gx else None
+    gQ = torch.empty_like(Qr)
+    gb = torch.empty(cout, dtype=torch.float32, device=x.device) if need_gb else None
+    nb = lib().fiode_cayley_conv_layer_bwd_workspace_bytes(B, cin, cout, n)
+    ws = _ws(nb, x.device)
+    check(lib().fiode_cayley_conv_layer_bwd(ptr(x), ptr(Qr), ptr(gy), B, cin, cout, n, _opt(gx), ptr(gQ), _opt(gb), ptr(ws),
+                                            nb, stream_ptr()), 'fiode_cayley_conv_layer_bwd')
+    return gx, torch.view_as_complex(gQ), gb
+
+
+def cayley_linear_bwd(weight, alpha, gQ):
+    """Adjoint of cayley_linear: (gW, galpha)."""
+    W, gQ = _f32(weight), _f32(gQ)
+    cout, cin = W.shape
+    a = _f32(alpha).reshape(1)
+    gW = torch.empty_like(W)
+    ga = torch.empty(1, dtype=torch.float32, device=W.device)
+    nb = lib().fiode_cayley_linear_bwd_workspace_bytes(cout, cin)
+    ws = _ws(nb, W.device)
+    check(lib().fiode_cayley_linear_bwd(ptr(W), ptr(a), cout, cin, ptr(gQ), ptr(gW), ptr(ga), ptr(ws), nb, stream_ptr()),
+          'fiode_cayley_linear_bwd')
+    return gW, ga
+
+
+def cayley_conv_bwd(weight, alpha, n, gQf):
+    """Adjoint of cayley_conv: (gw (cout,cin,k,k), galpha)."""
+    w = _f32(weight)
+    cout, cin, k, _ = w.shape
+    a = _f32(alpha).reshape(1)
+    g = (torch.view_as_real(gQf) if gQf.is_complex() else gQf).to(torch.float32).contiguous()
+    gw = torch.empty_like(w)
+    ga = torch.empty(1, dtype=torch.float32, device=w.device)
+    nb = lib().fiode_cayley_conv_bwd_workspace_bytes(cout, cin, k, n)
+    ws = _ws(nb, w.device)
+    check(lib().fiode_cayley_conv_bwd(ptr(w), ptr(a), cout, cin, k, n, ptr(g), ptr(gw), ptr(ga), ptr(ws), nb, stream_ptr()),
+          'fiode_cayley_conv_bwd')
+    return gw, ga

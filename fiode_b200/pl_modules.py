@@ -94,13 +94,21 @@ class LyapunovLearning(nn.Module):
         self.log('kappa', kappa)
         lay = (dyn.hidden_to_mlp, dyn.U_x, dyn.mlp_to_mlp, dyn.mlp_to_hidden)
         Qs = []
-        for l in lay:                                             # leaf proxies: dL/dQ lands in layer.Q.grad
-            q = l.orthogonal_weight()
+        for l in lay:
+            if dyn.training and torch.is_grad_enabled():
+                # train mode: Q is a graph node, dL/dQ continues through fiode_cayley_linear_bwd to weight / alpha
+                Qs.append(l.orthogonal_weight_autograd())
+                continue
+            q = l.orthogonal_weight()                             # eval mode: leaf proxies, dL/dQ lands in layer.Q.grad
             if not q.requires_grad:
                 q.requires_grad_(True)
             Qs.append(q)
         if not static_state.requires_grad:
             static_state = static_state.detach().requires_grad_(True)
+        if masks is None and dyn.training and dyn.dropout.p > 0:
+            # classification.py:97-101 dropout after each hidden activation; Bernoulli masks from torch's Philox stream
+            p, N = dyn.dropout.p, batch_size * S
+            masks = tuple((torch.rand(N, dyn.mlp_size, device=x.device) >= p).float() / (1 - p) for _ in range(2))
         self.last_static_state = static_state
         loss = _FiLoss.apply(dyn, h_sample_in[0], y, S, float(kappa), masks, static_state, *Qs,
                              lay[0].bias, lay[1].bias, lay[2].bias, lay[3].bias)

@@ -108,6 +108,41 @@ FIODE_API int fiode_conv1x1_s2d_fwd(const float* x, const float* Q, const float*
 FIODE_API int fiode_space_to_depth(const float* x, int B, int C, int n, float* y, void* stream);
 FIODE_API int fiode_group_sort(const float* x, int B, int C, int inner, float* y, void* stream);
 
+/* ---- training: adjoints of the backbone layers and of the Cayley transform ---------------------
+ * The reference differentiates these through autograd (loss.backward(), pl_modules.py:504-506).  Each
+ * entry point is the hand-written adjoint of the forward named beside it; optional outputs may be NULL.
+ * Batch sums are ordered (no float atomics): gradients are bit-reproducible.                         */
+/* Normalize.forward (models.py:23-26): y = (x - mu[c]) / std[c], x (B,C,inner).                      */
+FIODE_API int fiode_normalize(const float* x, int B, int C, int inner, const float* mu, const float* std, float* y,
+                    void* stream);
+/* adjoint of GroupSort (layers.py:127-131): x_pre is the layer's input; ties split evenly like torch.max/min. */
+FIODE_API int fiode_group_sort_bwd(const float* x_pre, const float* gy, int B, int C, int inner, float* gx, void* stream);
+/* gb[c] = sum over batch and inner of gy (B,C,inner): adjoint of the `+ bias` of every layer.          */
+FIODE_API int fiode_bias_grad(const float* gy, int B, int C, int inner, float* gb, void* stream);
+/* adjoint of F.linear(X, Q, b) (layers.py:105): gX = gY Q (M,K), gQ = gY^T X (N,K), gb = column sums.  */
+FIODE_API size_t fiode_linear_bwd_workspace_bytes(int M, int N, int K);
+FIODE_API int fiode_linear_bwd(const float* X, const float* Q, const float* gY, int M, int N, int K, float* gX, float* gQ,
+                     float* gb, void* ws, size_t ws_bytes, void* stream);
+/* adjoint of fiode_conv1x1_s2d_fwd: gx (B,cin,n,n), gQ (cout,4cin), gb (cout).                          */
+FIODE_API size_t fiode_conv1x1_s2d_bwd_workspace_bytes(int B, int cin, int cout, int n);
+FIODE_API int fiode_conv1x1_s2d_bwd(const float* x, const float* Q, const float* gy, int B, int cin, int cout, int n,
+                          float* gx, float* gQ, float* gb, void* ws, size_t ws_bytes, void* stream);
+/* adjoint of fiode_cayley_conv_fwd (CayleyConv.forward layers.py:78-85, k = 3): gx = irfft2(Q^H rfft2(gy)),
+ * gQf[phi] = c_phi / n^2 sum_b rfft2(gy)[b,:,phi] rfft2(x)[b,:,phi]^H  (F,cout,cin) complex64, gb (cout).   */
+FIODE_API size_t fiode_cayley_conv_layer_bwd_workspace_bytes(int B, int cin, int cout, int n);
+FIODE_API int fiode_cayley_conv_layer_bwd(const float* x, const float* Qf, const float* gy, int B, int cin, int cout, int n,
+                                float* gx, float* gQf, float* gb, void* ws, size_t ws_bytes, void* stream);
+/* adjoint of fiode_cayley_linear (cayley(alpha W / ||W||), layers.py:50-60, 103-104): gQ (cout,cin) ->
+ * gW (cout,cin), galpha (1).  Forward intermediates are recomputed.                                     */
+FIODE_API size_t fiode_cayley_linear_bwd_workspace_bytes(int cout, int cin);
+FIODE_API int fiode_cayley_linear_bwd(const float* W, const float* alpha, int cout, int cin, const float* gQ, float* gW,
+                            float* galpha, void* ws, size_t ws_bytes, void* stream);
+/* adjoint of fiode_cayley_conv (layers.py:74-82): gQf as produced by the layer adjoints above
+ * (k = 3: (F,cout,cin) complex64; k = 1: real (cout,cin)) -> gw (cout,cin,k,k), galpha (1).              */
+FIODE_API size_t fiode_cayley_conv_bwd_workspace_bytes(int cout, int cin, int k, int n);
+FIODE_API int fiode_cayley_conv_bwd(const float* w, const float* alpha, int cout, int cin, int k, int n, const float* gQf,
+                          float* gw, float* galpha, void* ws, size_t ws_bytes, void* stream);
+
 /* ---- ODE right-hand side -----------------------------------------------------------------------
  * replaces dynamics/classification.py:96-126 (_h_dot_raw, eval_dot, eval_dot_light) with
  * barrier_projection/barrier_projection.py:217-269 (FastBarrierProjectionNoUpper.forward).
@@ -271,6 +306,10 @@ FIODE_API int fiode_dopri5_simplex_batched(const fiode_dyn_weights* w, const flo
                                  long long max_num_steps, float* out, fiode_solve_stats* stats,
                                  int cluster_size, void* stream);
 
+/* Solves of B rows that one fiode_dopri5_simplex_batched launch keeps co-resident (one thread-block cluster per
+ * solve; cudaOccupancyMaxActiveClusters).  More solves than this run in waves of a full solve latency each:
+ * size G to a multiple of it.  cluster_size 0 = the launcher's default.  < 0 on error.                       */
+FIODE_API int fiode_dopri5_max_concurrent_solves(int B, int cluster_size);
 #ifdef __cplusplus
 }
 #endif
