@@ -204,6 +204,64 @@ def certify_bench(ivp, device, pk, iters=3):
                                    'be bound by; ncu: issue-bound (profiles/)' % (3 * tf / pk['bf16'], tf / FFMA_PEAK_TFLOPS)))
 
 
+def fi_step_bench(device, pk, world, iters=10, warm=3):
+    """Secondary metric (BASELINE config 3): one data-parallel FI training step = sampler + backbone forward (train
+    mode) + fused FI loss (B=128, S=h_sample_size=256 -> 32 768 rows, dropout 0.5) + loss.backward() through every
+    adjoint down to the 33 parameters + ONE flat-buffer gradient all-reduce (NCCL when world > 1).  No optimizer
+    step: Adam stays with the reference's Lightning loop (pl_modules.py:506-520)."""
+    import fiode_b200
+    from fiode_b200 import models, pl_modules, lya_cands
+    from fiode_b200.sampling import sampler as smp, sampler_schedulers as sch
+    from fiode_b200.dynamics.classification import OrthoClassDynProjectSimplexLips
+    from fiode_b200.dynamics.init_coordinates import UniformInitFun
+    from fiode_b200.dynamics.output_coordinates import DefaultOutputFun
+    from fiode_b200.distributed import FlatGradAllReduce
+    Bt, S = 128, 256
+    torch.manual_seed(0)
+    pm = models.make_ortho_KWLarge_Concat(3, 10, mu=MU, std=STD, out_dim=10, act='GroupSort')
+    dyn = OrthoClassDynProjectSimplexLips(n_hidden=10, activation='ReLU', mlp_size=128, alpha_1=100., alpha_2=20., sigma_1=0.02,
+                                          x_dim=10, cayley=True, dropout=0.5, scale_nominal=True, kappa=2.0, kappa_length=0)
+    mod = pl_modules.LyapunovLearning(
+        order=1, h_sample_size=S, h_dist_lim=15, lya_cand=lya_cands.DecisionBoundary(on_simplex=True),
+        sampler=smp.CompositeSampler((10,), [smp.UniformSimplexSampling((10,)), smp.CorrectConeSampling((10,))]),
+        sampler_scheduler=sch.CompositeSamplerScheduler([sch.ConstantScheduler(0.5), sch.ConstantScheduler(0.5)], [1., 1.]),
+        dynamics=dyn, output=DefaultOutputFun(), init_fun=UniformInitFun((10,), param_map=pm), t_max=T_MAX,
+        train_ode_tol=TOL, val_ode_tol=TOL, epoch_off_scale=10).to(device).train()
+    rank = int(os.environ.get('RANK', '0'))
+    g = torch.Generator().manual_seed(1234 + rank)
+    x = torch.rand(Bt, 3, 32, 32, generator=g).to(device)
+    y = torch.randint(0, 10, (Bt,), generator=torch.Generator().manual_seed(1235 + rank)).to(device)
+    mod.compute_loss(x, y, Bt, act='relu').backward()          # creates the lazily initialised conv alphas
+    reducer = FlatGradAllReduce(mod.parameters())
+
+    def step():
+        for p in reducer.params:
+            p.grad = None
+        loss = mod.compute_loss(x, y, Bt, act='relu')
+        loss.backward()
+        reducer.step()
+        return loss
+
+    for _ in range(warm):
+        step()
+    c0 = fiode_b200.launch_count()
+    ms = timed(step, iters) / iters
+    launches = (fiode_b200.launch_count() - c0) // iters
+    t = torch.tensor([ms], device=device)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    rows = Bt * S
+    flop = 3 * (rows * RHS_FLOP + Bt * BACKBONE_FLOP + 4.3e9)       # SURVEY 8(d): forward + ~2x backward
+    return dict(metric='FI training steps/s (B=128 x h_sample_size=256, data-parallel)', value=world / (ms * 1e-3),
+                unit='steps/s (whole job)', ms_per_step=ms, gpu_launches=launches, rows_per_step=rows,
+                grad_floats=reducer.numel, allreduce_bytes=4 * reducer.numel,
+                algorithmic_tflops=flop / (ms * 1e-3) / 1e12, loss=float(step().detach()),
+                note='forward + backward to all 33 parameters + one flat all-reduce; kernels are the first correct versions '
+                     '(FFMA GEMMs, per-layer launches), not yet tuned')
+
+
 # per image: algorithmic HBM bytes (fp32 activations in + out; spectra complex64) and flops of each backbone stage
 #   name, kernel, bytes/img, flop/img
 STAGES = [
@@ -386,6 +444,12 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_value = world * G * args.steps / (float(t.item()) * 1e-3)
 
+    fi = None
+    if not args.no_fi:
+        try:
+            fi = fi_step_bench(device, pk, world)
+        except Exception as e:           # secondary metric must not take the headline down
+            fi = dict(error=repr(e))
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -427,7 +491,7 @@ def run_b200(args):
                                 NBUF, NBUF * per_set / 1e6), parallelism=f'independent batches x{world}'),
                 images_per_s=value * B,
                 e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=per_set, d2h_bytes_per_step=G * B * 10 * 4),
-                gpu_launches=launches, clocks=clocks, roofline=roofline, cpu_baseline=cpu, certify=cert)
+                gpu_launches=launches, clocks=clocks, roofline=roofline, cpu_baseline=cpu, certify=cert, fi_step=fi)
     print(json.dumps(line))
     if world > 1:
         dist.barrier()
@@ -444,6 +508,7 @@ def main():
     ap.add_argument('--cluster-size', type=int, default=4, help='CTAs per solve in the cluster-per-solve dopri5 launch')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-certify', action='store_true')
+    ap.add_argument('--no-fi', action='store_true')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)

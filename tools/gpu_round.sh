@@ -13,7 +13,7 @@ timeout 600 python bench.py > $OUT/bench.json 2> $OUT/bench.err; echo "bench rc=
 timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > $OUT/bench_ref.json 2> $OUT/bench_ref.err; echo "ref rc=$?" | tee -a $OUT/rc.txt
 if [ -z "$SKIP_NCU" ]; then
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --csv --log-file $OUT/launches.csv \
-  python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-certify > $OUT/ncu_launch.log 2>&1; echo "ncu-list rc=$?" | tee -a $OUT/rc.txt
+  python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-certify --no-fi > $OUT/ncu_launch.log 2>&1; echo "ncu-list rc=$?" | tee -a $OUT/rc.txt
 timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off -c 40 -f -o $OUT/full \
   python tools/prof_kernels.py all > $OUT/ncu_full.log 2>&1; echo "ncu-full rc=$?" | tee -a $OUT/rc.txt
 fi
