@@ -133,7 +133,7 @@ struct Smem {
 // Follows classification.py:96-115 + barrier_projection.py:232-255.
 template <bool CLUSTER>
 __device__ __forceinline__ void eval_rhs(const SolveArgs& a, const Smem& S, int R, int Rp, const float (&q1)[NH],
-                                         const float4 (&q2)[16], const float (&q3)[16], float b2j, float b3o,
+                                         const float4 (&q2)[16], const float (&q3)[16], float b2j, float b2j1, float b3o,
                                          float* kout, Comm& comm) {
     const int t = threadIdx.x;
     // layer 1: z1[r][j] = relu(c[r][j] + Q1[j,:] . h[r,:])
@@ -151,51 +151,65 @@ __device__ __forceinline__ void eval_rhs(const SolveArgs& a, const Smem& S, int 
         }
     }
     __syncthreads();
-    // layer 2: thread (j, kh) owns Q2[j][kh*64 .. +64) in registers; 4 rows per pass for ILP
+    // layer 2: thread (jg, ks) owns Q2[4 jg .. 4 jg + 3][k], k = 32 m + 4 ks + c (m, c < 4), in registers: every LDS.128 of
+    // z1 feeds 16 FFMAs (4 outputs x 4 k) and the 8 ks-lanes of a row read 128 contiguous bytes (no bank conflicts);
+    // 4 rows per pass -> 16 independent accumulators, reduced over the 8 ks-lanes by a 3-step reduce-scatter
     {
-        const int j = t >> 1, kh = t & 1;
+        const int ks = t & 7, jg = t >> 3;
         for (int r = 0; r < Rp; r += 4) {
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-            const float4* z0 = reinterpret_cast<const float4*>(S.z1 + (r + 0) * NM + kh * 64);
-            const float4* z1 = reinterpret_cast<const float4*>(S.z1 + (r + 1) * NM + kh * 64);
-            const float4* z2 = reinterpret_cast<const float4*>(S.z1 + (r + 2) * NM + kh * 64);
-            const float4* z3 = reinterpret_cast<const float4*>(S.z1 + (r + 3) * NM + kh * 64);
+            float acc[16];
 #pragma unroll
-            for (int kk = 0; kk < 16; ++kk) {
-                const float4 q = q2[kk];
-                float4 v = z0[kk];
-                a0 = fmaf(q.x, v.x, a0); a0 = fmaf(q.y, v.y, a0); a0 = fmaf(q.z, v.z, a0); a0 = fmaf(q.w, v.w, a0);
-                v = z1[kk];
-                a1 = fmaf(q.x, v.x, a1); a1 = fmaf(q.y, v.y, a1); a1 = fmaf(q.z, v.z, a1); a1 = fmaf(q.w, v.w, a1);
-                v = z2[kk];
-                a2 = fmaf(q.x, v.x, a2); a2 = fmaf(q.y, v.y, a2); a2 = fmaf(q.z, v.z, a2); a2 = fmaf(q.w, v.w, a2);
-                v = z3[kk];
-                a3 = fmaf(q.x, v.x, a3); a3 = fmaf(q.y, v.y, a3); a3 = fmaf(q.z, v.z, a3); a3 = fmaf(q.w, v.w, a3);
+            for (int i = 0; i < 16; ++i) acc[i] = 0.f;
+#pragma unroll
+            for (int m = 0; m < 4; ++m) {
+#pragma unroll
+                for (int rr = 0; rr < 4; ++rr) {
+                    const float4 v = *reinterpret_cast<const float4*>(S.z1 + (r + rr) * NM + m * 32 + ks * 4);
+#pragma unroll
+                    for (int jj = 0; jj < 4; ++jj) {
+                        const float4 q = q2[jj * 4 + m];
+                        float a = acc[rr * 4 + jj];
+                        a = fmaf(q.x, v.x, a); a = fmaf(q.y, v.y, a); a = fmaf(q.z, v.z, a); a = fmaf(q.w, v.w, a);
+                        acc[rr * 4 + jj] = a;
+                    }
+                }
             }
-            a0 += __shfl_xor_sync(0xffffffffu, a0, 1);
-            a1 += __shfl_xor_sync(0xffffffffu, a1, 1);
-            a2 += __shfl_xor_sync(0xffffffffu, a2, 1);
-            a3 += __shfl_xor_sync(0xffffffffu, a3, 1);
-            if (kh == 0) {
-                S.z2[(r + 0) * NM + j] = fmaxf(a0 + b2j, 0.f);
-                S.z2[(r + 1) * NM + j] = fmaxf(a1 + b2j, 0.f);
-            } else {
-                S.z2[(r + 2) * NM + j] = fmaxf(a2 + b2j, 0.f);
-                S.z2[(r + 3) * NM + j] = fmaxf(a3 + b2j, 0.f);
+            float w8[8], w4[4], w2[2];
+            const bool h4 = ks & 4, h2 = ks & 2, h1 = ks & 1;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const float keep = h4 ? acc[i + 8] : acc[i], send = h4 ? acc[i] : acc[i + 8];
+                w8[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
             }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float keep = h2 ? w8[i + 4] : w8[i], send = h2 ? w8[i] : w8[i + 4];
+                w4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+            }
+#pragma unroll
+            for (int i = 0; i < 2; ++i) {
+                const float keep = h1 ? w4[i + 2] : w4[i], send = h1 ? w4[i] : w4[i + 2];
+                w2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+            }
+            // this lane now holds accumulator indices idx0, idx0 + 1 (idx = 4 row + output)
+            const int idx0 = (h4 ? 8 : 0) + (h2 ? 4 : 0) + (h1 ? 2 : 0);
+            const int rr = idx0 >> 2, jj = idx0 & 3;
+            *reinterpret_cast<float2*>(S.z2 + (r + rr) * NM + jg * 4 + jj) =
+                make_float2(fmaxf(w2[0] + b2j, 0.f), fmaxf(w2[1] + b2j1, 0.f));
         }
     }
     __syncthreads();
-    // layer 3: 8 threads per output, 3 rows x 10 outputs per pass (threads 240..255 shadow group 0)
+    // layer 3: 8 threads per output (k = 32 kk + 4 ks + c, conflict-free like layer 2), 3 rows x 10 outputs per pass
+    // (threads 240..255 shadow group 0)
     {
         const int g = (t >> 3) % 30, ks = t & 7, o = g % NH, rr = g / NH;
         for (int r0 = 0; r0 < R; r0 += 3) {
             const int r = min(r0 + rr, Rp - 1);
-            const float4* z = reinterpret_cast<const float4*>(S.z2 + r * NM + ks * 16);
+            const float* z = S.z2 + r * NM + ks * 4;
             float acc = 0.f;
 #pragma unroll
             for (int kk = 0; kk < 4; ++kk) {
-                const float4 v = z[kk];
+                const float4 v = *reinterpret_cast<const float4*>(z + kk * 32);
                 acc = fmaf(q3[4 * kk + 0], v.x, acc); acc = fmaf(q3[4 * kk + 1], v.y, acc);
                 acc = fmaf(q3[4 * kk + 2], v.z, acc); acc = fmaf(q3[4 * kk + 3], v.w, acc);
             }
@@ -270,19 +284,26 @@ __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const Solve
     comm.slots = reinterpret_cast<ClusterSlot*>(p); p += 2 * sizeof(ClusterSlot) / sizeof(float);
 
     // ---- one-time setup: weights to registers, c = b1 + bx + Qx s, y = h0 -----------------------
-    float q1[NH]; float4 q2[16]; float q3[16]; float b2j, b3o;
+    float q1[NH]; float4 q2[16]; float q3[16]; float b2j, b2j1, b3o;
     {
         const int j = t & 127;
 #pragma unroll
         for (int i = 0; i < NH; ++i) q1[i] = a.w.Q1[j * NH + i];
-        const int j2 = t >> 1, kh = t & 1;
-        const float4* src = reinterpret_cast<const float4*>(a.w.Q2 + j2 * NM + kh * 64);
+        {   // layer-2 slice: q2[jj * 4 + m] = Q2[4 jg + jj][32 m + 4 ks .. + 4]
+            const int ks2 = t & 7, jg = t >> 3;
 #pragma unroll
-        for (int kk = 0; kk < 16; ++kk) q2[kk] = src[kk];
-        b2j = a.w.b2[j2];
+            for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+                for (int m = 0; m < 4; ++m)
+                    q2[jj * 4 + m] = *reinterpret_cast<const float4*>(a.w.Q2 + (jg * 4 + jj) * NM + m * 32 + ks2 * 4);
+            const int j0 = jg * 4 + 2 * (ks2 & 1);          // the two outputs this lane stores after the reduce-scatter
+            b2j = a.w.b2[j0]; b2j1 = a.w.b2[j0 + 1];
+        }
         const int g = (t >> 3) % 30, ks = t & 7, o = g % NH;
 #pragma unroll
-        for (int kk = 0; kk < 16; ++kk) q3[kk] = a.w.Q3[o * NM + ks * 16 + kk];
+        for (int kk = 0; kk < 4; ++kk)
+#pragma unroll
+            for (int c = 0; c < 4; ++c) q3[4 * kk + c] = a.w.Q3[o * NM + kk * 32 + ks * 4 + c];
         b3o = a.w.b3[o];
         for (int e = t; e < Rp * NM; e += kThreads) { S.z1[e] = 0.f; S.z2[e] = 0.f; }
         float qx[NH];
@@ -323,7 +344,7 @@ __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const Solve
     double tcur = a.t[0], t_left = tcur, dt;
 
     // ---- f0 and the initial step (misc._select_initial_step) ------------------------------------
-    eval_rhs<CLUSTER>(a, S, R, Rp, q1, q2, q3, b2j, b3o, k0, comm); ++nfe;
+    eval_rhs<CLUSTER>(a, S, R, Rp, q1, q2, q3, b2j, b2j1, b3o, k0, comm); ++nfe;
     float h0s;
     {
         double s0 = 0, s1 = 0;
@@ -343,7 +364,7 @@ __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const Solve
             S.ys[r * SROW + i] = S.y[r * SROW + i] + h0s * k0[r * SROW + i];
         }
         __syncthreads();
-        eval_rhs<CLUSTER>(a, S, R, Rp, q1, q2, q3, b2j, b3o, kst(1), comm); ++nfe;
+        eval_rhs<CLUSTER>(a, S, R, Rp, q1, q2, q3, b2j, b2j1, b3o, kst(1), comm); ++nfe;
         double s2 = 0, dummy = 0;
         for (int e = t; e < R * NH; e += kThreads) {
             const int r = e / NH, i = e - r * NH;
@@ -375,7 +396,7 @@ __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const Solve
                     S.ys[o] = S.y[o] + acc;
                 }
                 __syncthreads();
-                eval_rhs<CLUSTER>(a, S, R, Rp, q1, q2, q3, b2j, b3o, kst(s + 1), comm); ++nfe;
+                eval_rhs<CLUSTER>(a, S, R, Rp, q1, q2, q3, b2j, b2j1, b3o, kst(s + 1), comm); ++nfe;
             }
             // error estimate + norm (+ count of non-finite entries of the step's start state)
             double se = 0, nonfin = 0;

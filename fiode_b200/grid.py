@@ -38,3 +38,36 @@ def get_grid_for_label(grid, label):
     if label != 0:
         g[:, [label, 0]] = g[:, [0, label]]
     return g
+
+
+# ---- grid file format ---------------------------------------------------------------
+def save_grid_pt(path, n=10, T=40, device='cuda'):
+    """Write the file ``robustness/sample_decision_boundary.py:37-42`` writes (``grid_T.pt``): a Python list of n
+    float32 CPU tensors (N, n), entry ``i`` being the label-0 grid with columns 0 and i swapped
+    (eval_utils.py:64-69, ``.float()`` of the float64 z / T).  The reference builds it with an O(N^2) numpy
+    recursion (minutes and > 10 GB at T = 40); here the numerators are enumerated on the device and each label's
+    tensor is produced by one column swap.  ``certify_lipschitz.py:57-58`` loads it with ``torch.load``."""
+    z = boundary_grid_numerators(n, T, device)
+    base = (z.double() / T).float()                     # same rounding as th.from_numpy(float64).float()
+    grids = [get_grid_for_label(base, i).cpu() for i in range(n)]
+    torch.save(grids, path)
+    return grids
+
+
+def numerators_from_grid_pt(path_or_list, T, label=0, device='cuda'):
+    """Read a reference ``grid_T.pt`` (or the list it holds) back into the uint8 numerators of the canonical
+    label-0 grid that ``fiode_certify_grid`` streams: z = round(T * eta), columns un-swapped.  Checks that every row
+    sums to T and lies on the decision boundary (z_0 = max_{i>=1} z_i, eval_utils.py:31-61)."""
+    grids = torch.load(path_or_list, map_location='cpu') if isinstance(path_or_list, (str, bytes)) or hasattr(path_or_list, '__fspath__') else path_or_list
+    g = grids[label].to(torch.float64)
+    if label != 0:
+        g = g.clone()
+        g[:, [label, 0]] = g[:, [0, label]]
+    z = torch.round(g * T).to(torch.int64)
+    if not bool((z.sum(1) == T).all()):
+        raise ValueError('grid rows do not sum to T')
+    if not bool((z[:, 0] == z[:, 1:].max(1).values).all()):
+        raise ValueError('grid rows are not on the label-0 decision boundary')
+    if int(z.max()) > 255:
+        raise ValueError('T too large for uint8 numerators')
+    return z.to(torch.uint8).to(device)

@@ -342,6 +342,26 @@ def test_grid_enumeration_full_size_properties(T):
     assert bool((g64[:, 3] == g64.max(1).values).all())
 
 
+def test_grid_pt_file_matches_reference_format(tmp_path):
+    """grid_T.pt as robustness/sample_decision_boundary.py:37-42 writes it: same container, dtype, shapes and -- as a set of
+    rows per label -- the same content as the reference's own generator (golden grid_10_10)."""
+    from fiode_b200 import grid
+    g = fx.load_golden('certify.pt')
+    f = tmp_path / 'grid_10.pt'
+    grid.save_grid_pt(str(f), n=10, T=10)
+    got = torch.load(str(f))
+    assert isinstance(got, list) and len(got) == 10
+    want0 = g['grid_10_10_sorted'].double() / 10
+    for label, t in enumerate(got):
+        assert t.dtype == torch.float32 and t.device.type == 'cpu' and t.shape == (g['counts'][(10, 10)], 10)
+        w = want0.clone()
+        if label:
+            w[:, [label, 0]] = w[:, [0, label]]
+        assert np.array_equal(np.unique(t.numpy(), axis=0), np.unique(w.float().numpy(), axis=0))
+    z = grid.numerators_from_grid_pt(str(f), 10, label=7)
+    assert torch.equal(z, grid.boundary_grid_numerators(10, 10))
+
+
 def test_certify_driver_matches_reference(sd):
     """The loop of certify_lipschitz.py:104-163 through fiode_b200.robustness.certify_lipschitz.certify."""
     from fiode_b200.robustness import certify_lipschitz as cl

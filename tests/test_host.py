@@ -56,3 +56,22 @@ def test_state_dict_keys_match_reference_layout(sd):
         k2 = k[len('model.'):]
         assert k2 in own and tuple(own[k2].shape) == tuple(v.shape), k
         assert torch.equal(own[k2], v), k
+
+
+def test_grid_pt_reader_round_trip(tmp_path):
+    """a reference-format grid file (list of 10 float32 (N,10) tensors, label i = columns 0 and i swapped,
+    sample_decision_boundary.py:37-42) read back into the canonical uint8 numerators; built here from the oracle grid."""
+    from fiode_b200 import grid
+    from oracle import certify as oc
+    T = 10
+    z = oc.boundary_grid_numerators(10, T)
+    grids = [oc.grid_for_label(z, T, i).float() for i in range(10)]
+    f = tmp_path / 'grid_10.pt'
+    torch.save(grids, f)
+    for label in (0, 3, 9):
+        back = grid.numerators_from_grid_pt(str(f), T, label=label, device='cpu')
+        assert back.dtype == torch.uint8 and torch.equal(back.long(), torch.as_tensor(z).long())
+    bad = [g.clone() for g in grids]
+    bad[0][5, 0] += 0.1
+    with pytest.raises(ValueError):
+        grid.numerators_from_grid_pt(bad, T, device='cpu')
