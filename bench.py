@@ -461,7 +461,7 @@ def run_b200(args):
 
     # ---- CPU baseline beside it (bounded sample) ----------------------------------------------------
     cpu = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:          # the contract asks for it on rank 0 at N=1 only
         threads = os.cpu_count() or 1
         n_cpu = 100                      # about 12 s of host work at ~8 solves/s
         rate, secs = cpu_solve_rate(cpu_state_dict(ivp), n_cpu, threads)

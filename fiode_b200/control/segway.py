@@ -90,3 +90,39 @@ def simulate(ctrl_sd, x0, ts, rtol=1e-6, atol=1e-6, device='cuda'):
         raise AssertionError({1: 'underflow in dt', 2: 'non-finite values in state `y`', 3: 'max_num_steps exceeded'}[st[0]])
     simulate.last_stats = dict(n_accept=st[1], n_reject=st[2], nfe=st[3])
     return xs, us
+
+
+def slab(total, rank, world):
+    """Contiguous slab [first, first + count) of the flattened grid for ``rank`` (phi is the slowest axis, so a slab is
+    a range of phi planes plus a partial one: SURVEY 8e "slab the phi axis")."""
+    per = (total + world - 1) // world
+    first = min(total, rank * per)
+    return first, min(per, total - first)
+
+
+def certify_grid_sharded(ctrl_sd, P, sizes, r, level=0.15, device='cuda', levels=None, evaluate=None):
+    """control/certify_segway.py:55-59 across the ranks of the default process group: every rank evaluates one slab of
+    the grid (grid points are independent), then ONE all-reduce carries (max barrier derivative, shell-point count).
+    Returns (eta_local, val_local, global max val, global shell count).  ``evaluate(first, count) -> (eta, val, vmax)``
+    can be injected (CPU tests of the sharding); default is ``certify_grid`` on this rank's device."""
+    import torch.distributed as dist
+    from .. import distributed as fdist
+    rank, world = fdist.world()
+    total = 1
+    for a in grid_axes(sizes, r):
+        total *= len(a)
+    first, count = slab(total, rank, world)
+    if evaluate is None:
+        evaluate = lambda f, c: certify_grid(ctrl_sd, P, sizes, r, level=level, device=device, levels=levels, first=f, count=c)
+    if count > 0:
+        eta, val, vmax = evaluate(first, count)
+    else:
+        eta, val, vmax = torch.empty(0, 3), torch.empty(0, 1), float('-inf')
+    m = eta.shape[0]
+    red_dev = eta.device if eta.is_cuda else 'cpu'
+    vm = torch.tensor([vmax if m else float('-inf')], dtype=torch.float32, device=red_dev)
+    cnt = torch.tensor([m], dtype=torch.int64, device=red_dev)
+    if world > 1:
+        dist.all_reduce(vm, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
+    return eta, val, float(vm.item()), int(cnt.item())

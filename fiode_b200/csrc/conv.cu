@@ -208,28 +208,32 @@ __global__ void __launch_bounds__(160) irfft32_mix3_kernel(const float2* __restr
         Xs[e] = (b0 + im < B) ? __ldg(Xf + (size_t)b0 * 3 * F + e) : make_float2(0.f, 0.f);
     }
     __syncthreads();
-    // step 1: mix + columns (inverse along u).  task = (channel, v), v fastest
-    for (int task = threadIdx.x; task < CH * H; task += THREADS) {
-        const int ci = task / H, v = task - ci * H;
-        const float2* q = Qt + (size_t)chan(ci) * 3 * F + v;
-        float2 z[IM][n];
-#pragma unroll
-        for (int u = 0; u < n; ++u) {
-            const float2 q0 = __ldg(q + u * H), q1 = __ldg(q + F + u * H), q2 = __ldg(q + 2 * F + u * H);
-#pragma unroll
-            for (int im = 0; im < IM; ++im) {
-                const float2* xs = Xs + im * 3 * F + u * H + v;
-                float2 acc = make_float2(0.f, 0.f);
-                cfma(acc, q0, xs[0]); cfma(acc, q1, xs[F]); cfma(acc, q2, xs[2 * F]);
-                z[im][u] = acc;
-            }
-        }
+    // step 1a: mix.  Yf[im][ci][phi] = sum_c Q[chan(ci)][c][phi] Xs[im][c][phi], lanes along phi: the Q reads are coalesced,
+    // independent of each other (the loop carries no FFT registers, so the compiler keeps many in flight) and each Q
+    // value is read once per CTA.  Results land in T at the place the column pass reads them.
+    for (int e = threadIdx.x; e < CH * F; e += THREADS) {
+        const int ci = e / F, phi = e - ci * F, u = phi / H, v = phi - u * H;
+        const float2* q = Qt + (size_t)chan(ci) * 3 * F + phi;
+        const float2 q0 = __ldg(q), q1 = __ldg(q + F), q2 = __ldg(q + 2 * F);
 #pragma unroll
         for (int im = 0; im < IM; ++im) {
-            fft_dif<n, true>(z[im]);
-#pragma unroll
-            for (int a = 0; a < n; ++a) T[(im * CH + ci) * RSI + a * RS + v] = z[im][bitrev<n>(a)];
+            const float2* xs = Xs + im * 3 * F + phi;
+            float2 acc = make_float2(0.f, 0.f);
+            cfma(acc, q0, xs[0]); cfma(acc, q1, xs[F]); cfma(acc, q2, xs[2 * F]);
+            T[(im * CH + ci) * RSI + u * RS + v] = acc;
         }
+    }
+    __syncthreads();
+    // step 1b: columns (inverse along u), in place.  task = (image, channel, v), v fastest
+    for (int task = threadIdx.x; task < IM * CH * H; task += THREADS) {
+        const int ic = task / H, v = task - ic * H;
+        float2* col = T + ic * RSI + v;
+        float2 z[n];
+#pragma unroll
+        for (int u = 0; u < n; ++u) z[u] = col[u * RS];
+        fft_dif<n, true>(z);
+#pragma unroll
+        for (int a = 0; a < n; ++a) col[a * RS] = z[bitrev<n>(a)];
     }
     __syncthreads();
     // step 2: rows, two at a time; the 2 x 32 real outputs replace the two complex rows they were computed from

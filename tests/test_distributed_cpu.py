@@ -98,3 +98,48 @@ def test_flat_gradient_allreduce():
         p.join(timeout=60)
         assert p.exitcode == 0
     assert ok and alias and numel == 7 * 5 + 5 + 5 * 3 + 3 and shard == [0, 2, 4, 6]
+
+
+def _segway_worker(rank, world, port, out_q):
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    from fiode_b200.control import segway
+    from oracle import segway as oseg
+    g = fx.load_golden('segway.pt')
+    sizes, r = g['sizes'].tolist(), [g['r']] * 3
+    grid = oseg.grid_uniform_3d(sizes, r)
+
+    def evaluate(first, count):           # the oracle as the per-slab evaluator: what is under test is the sharding
+        pts = grid[first:first + count]
+        V = ((pts @ g['P'].T) ** 2).sum(1)
+        keep = (V >= g['lb']) & (V <= g['ub'])
+        eta = pts[keep]
+        val = oseg.barrier_hdot(eta, g['ctrl'], g['P'])
+        return eta, val.reshape(-1, 1), float(val.max()) if eta.shape[0] else float('-inf')
+
+    eta, val, vmax, count = segway.certify_grid_sharded(g['ctrl'], g['P'], sizes, r, level=g['level'],
+                                                        levels=(g['lb'], g['ub']), evaluate=evaluate)
+    out_q.put((rank, eta.shape[0], vmax, count))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_segway_grid_sharding_and_max_reduction():
+    """slabs of the grid per rank, one max / count reduction; equals the reference's one-shot result."""
+    g = fx.load_golden('segway.pt')
+    ctx = mp.get_context('spawn')
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_segway_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert sum(m for _, m, _, _ in res) == res[0][3]
+    assert abs(res[0][3] - g['mask_count']) <= 2
+    for _, _, vmax, _ in res:
+        assert abs(vmax - g['val_max']) <= 1e-5 * max(1.0, abs(g['val_max']))
+    from fiode_b200.control import segway
+    assert segway.slab(10, 0, 3) == (0, 4) and segway.slab(10, 2, 3) == (8, 2) and segway.slab(2, 2, 3) == (2, 0)
