@@ -236,52 +236,50 @@ __global__ void __launch_bounds__(160) irfft32_mix3_kernel(const float2* __restr
         for (int a = 0; a < n; ++a) col[a * RS] = z[bitrev<n>(a)];
     }
     __syncthreads();
-    // step 2: rows, two at a time; the 2 x 32 real outputs replace the two complex rows they were computed from
+    // step 2: rows.  task = (image, channel pair (ci, ci + CH/2), row pair p): two real rows per complex FFT (rows 2p, 2p+1 packed
+    // as re / im), both channels of a GroupSort pair in the same thread, so bias + (max, min) happen in registers and the
+    // four finished rows go straight to global memory as float4 (no smem round trip, no separate store pass).
     const float scale = 1.0f / (float)(n * n);
-    for (int task = threadIdx.x; task < IM * CH * (n / 2); task += THREADS) {
-        const int ic = task / (n / 2), p = task - ic * (n / 2), im = ic / CH, ci = ic - im * CH;
+    for (int task = threadIdx.x; task < IM * (CH / 2) * (n / 2); task += THREADS) {
+        const int ic = task / (n / 2), p = task - ic * (n / 2), im = ic / (CH / 2), ci = ic - im * (CH / 2);
         if (b0 + im >= B) continue;
-        float2* ta = T + ic * RSI + 2 * p * RS;
-        float2* tb = ta + RS;
-        float2 z[n];
+        float2 za[n], zb[n];
+        auto load_rows = [&](int c, float2 (&z)[n]) {
+            const float2* ta = T + (im * CH + c) * RSI + 2 * p * RS;
+            const float2* tb = ta + RS;
 #pragma unroll
-        for (int k = 0; k <= n / 2; ++k) {
-            float2 A = ta[k], Bq = tb[k];
-            if (k == 0 || k == n / 2) { A.y = 0.f; Bq.y = 0.f; }
-            z[k] = make_float2(A.x - Bq.y, A.y + Bq.x);
-            if (k > 0 && k < n / 2) z[n - k] = make_float2(A.x + Bq.y, -A.y + Bq.x);
-        }
-        fft_dif<n, true>(z);
-        const float bs = bias ? bias[chan(ci)] : 0.f;
-        float* oa = reinterpret_cast<float*>(ta);
-        float* ob = reinterpret_cast<float*>(tb);
+            for (int k = 0; k <= n / 2; ++k) {
+                float2 A = ta[k], Bq = tb[k];
+                if (k == 0 || k == n / 2) { A.y = 0.f; Bq.y = 0.f; }
+                z[k] = make_float2(A.x - Bq.y, A.y + Bq.x);
+                if (k > 0 && k < n / 2) z[n - k] = make_float2(A.x + Bq.y, -A.y + Bq.x);
+            }
+            fft_dif<n, true>(z);
+        };
+        load_rows(ci, za);
+        load_rows(ci + CH / 2, zb);
+        const int ca = chan(ci), cb = chan(ci + CH / 2);
+        const float bsa = bias ? bias[ca] : 0.f, bsb = bias ? bias[cb] : 0.f;
+        float* ya = y + (((size_t)(b0 + im) * C + ca) * n + 2 * p) * n;     // rows 2p, 2p+1 of channel a
+        float* yb = y + (((size_t)(b0 + im) * C + cb) * n + 2 * p) * n;
 #pragma unroll
-        for (int k = 0; k < n; ++k) {
-            const float2 r = z[bitrev<n>(k)];
-            oa[k] = r.x * scale + bs;
-            ob[k] = r.y * scale + bs;
-        }
-    }
-    __syncthreads();
-    auto outp = [&](int ic, int a, int k) { return reinterpret_cast<const float*>(T + ic * RSI + a * RS)[k]; };
-    if (group_sort) {
-        for (int e = threadIdx.x; e < IM * (CH / 2) * n * n; e += THREADS) {
-            const int im = e / ((CH / 2) * n * n), r = e - im * ((CH / 2) * n * n);
-            const int ci = r / (n * n), px = r - ci * (n * n), a = px / n, k = px - a * n;
-            if (b0 + im >= B) continue;
-            const float u = outp(im * CH + ci, a, k), w = outp(im * CH + ci + CH / 2, a, k);
-            y[((size_t)(b0 + im) * C + chan(ci)) * n * n + px] = fmaxf(u, w);
-            y[((size_t)(b0 + im) * C + chan(ci + CH / 2)) * n * n + px] = fminf(u, w);
-        }
-    } else {
-        for (int e = threadIdx.x; e < IM * CH * n * n; e += THREADS) {
-            const int ic = e / (n * n), px = e - ic * (n * n), a = px / n, k = px - a * n, im = ic / CH;
-            if (b0 + im >= B) continue;
-            y[((size_t)(b0 + im) * C + chan(ic - im * CH)) * n * n + px] = outp(ic, a, k);
+        for (int k = 0; k < n; k += 4) {
+            float a0[4], a1[4], c0[4], c1[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float2 ra = za[bitrev<n>(k + q)], rb = zb[bitrev<n>(k + q)];
+                const float u0 = ra.x * scale + bsa, u1 = ra.y * scale + bsa;       // channel a: row 2p, row 2p+1
+                const float w0 = rb.x * scale + bsb, w1 = rb.y * scale + bsb;       // channel b
+                a0[q] = group_sort ? fmaxf(u0, w0) : u0; c0[q] = group_sort ? fminf(u0, w0) : w0;
+                a1[q] = group_sort ? fmaxf(u1, w1) : u1; c1[q] = group_sort ? fminf(u1, w1) : w1;
+            }
+            *reinterpret_cast<float4*>(ya + k) = make_float4(a0[0], a0[1], a0[2], a0[3]);
+            *reinterpret_cast<float4*>(ya + n + k) = make_float4(a1[0], a1[1], a1[2], a1[3]);
+            *reinterpret_cast<float4*>(yb + k) = make_float4(c0[0], c0[1], c0[2], c0[3]);
+            *reinterpret_cast<float4*>(yb + n + k) = make_float4(c1[0], c1[1], c1[2], c1[3]);
         }
     }
 }
-// Qt: workspace of F * cout * 3 float2
 template <int IM>
 static int launch_irfft32_mix3_t(const float2* Xf, const float2* Qt, int B, int C, const float* bias, int gs, float* y,
                                  cudaStream_t st) {

@@ -97,7 +97,10 @@ class LyapunovLearning(nn.Module):
         for l in lay:
             if dyn.training and torch.is_grad_enabled():
                 # train mode: Q is a graph node, dL/dQ continues through fiode_cayley_linear_bwd to weight / alpha
-                Qs.append(l.orthogonal_weight_autograd())
+                q = l.orthogonal_weight_autograd()
+                q.retain_grad()                                   # dL/dQ stays observable in layer.Q.grad, as in eval mode
+                l.Q = q
+                Qs.append(q)
                 continue
             q = l.orthogonal_weight()                             # eval mode: leaf proxies, dL/dQ lands in layer.Q.grad
             if not q.requires_grad:
