@@ -120,7 +120,141 @@ __global__ void __launch_bounds__(256) gj_inverse_kernel(float* X, float* Y, int
     }
 }
 
+// n <= 128: the whole ping-pong elimination in ONE CTA's shared memory (block barriers instead of n grid barriers).
+__global__ void __launch_bounds__(1024) gj_inverse_smem_kernel(const float* __restrict__ Xin, float* __restrict__ out, int n) {
+    extern __shared__ float4 smem4[];
+    float* A = reinterpret_cast<float*>(smem4);
+    float* Bf = A + n * n;
+    const int total = n * n, t = threadIdx.x;
+    for (int e = t; e < total; e += 1024) A[e] = Xin[e];
+    __syncthreads();
+    for (int k = 0; k < n; ++k) {
+        const float* in = (k & 1) ? Bf : A;
+        float* o = (k & 1) ? A : Bf;
+        const float ip = 1.f / in[k * n + k];
+        for (int e = t; e < total; e += 1024) {
+            const int i = e / n, j = e - i * n;
+            float v;
+            if (i == k) v = (j == k) ? ip : in[e] * ip;
+            else {
+                const float f = in[i * n + k];
+                v = (j == k) ? -f * ip : fmaf(-f, in[k * n + j] * ip, in[e]);
+            }
+            o[e] = v;
+        }
+        __syncthreads();
+    }
+    const float* res = (n & 1) ? Bf : A;
+    for (int e = t; e < total; e += 1024) out[e] = res[e];
+}
+
+// n a multiple of 64: blocked Gauss-Jordan, one pivot block (64 x 64) per step, out of place X -> Y:
+//   Y_kk = D^-1, Y_kj = D^-1 X_kj, Y_ik = -X_ik D^-1, Y_ij = X_ij - X_ik D^-1 X_kj      (D = X_kk)
+// panel kernel: CTA j inverts D in shared memory (redundantly, 64 block barriers) and writes block row k of Y;
+// update kernel: CTA (i, j), i != k, applies the rank-64 update with Y's block row k.  2 plain launches per step.
+constexpr int GB = 64;
+__global__ void __launch_bounds__(256) gj_block_panel_kernel(const float* __restrict__ X, float* __restrict__ Y, int n, int kb) {
+    __shared__ float D0[GB * GB];
+    __shared__ float D1[GB * GB];
+    __shared__ float P[GB * GB];
+    const int t = threadIdx.x, jb = blockIdx.x;
+    for (int e = t; e < GB * GB; e += 256) {
+        const int i = e / GB, j = e - i * GB;
+        D0[e] = X[(size_t)(kb * GB + i) * n + kb * GB + j];
+        P[e] = X[(size_t)(kb * GB + i) * n + jb * GB + j];
+    }
+    __syncthreads();
+    for (int k = 0; k < GB; ++k) {
+        const float* in = (k & 1) ? D1 : D0;
+        float* o = (k & 1) ? D0 : D1;
+        const float ip = 1.f / in[k * GB + k];
+        for (int e = t; e < GB * GB; e += 256) {
+            const int i = e / GB, j = e - i * GB;
+            float v;
+            if (i == k) v = (j == k) ? ip : in[e] * ip;
+            else {
+                const float f = in[i * GB + k];
+                v = (j == k) ? -f * ip : fmaf(-f, in[k * GB + j] * ip, in[e]);
+            }
+            o[e] = v;
+        }
+        __syncthreads();
+    }
+    const float* Dinv = D0;                            // GB is even: the inverse ends in D0
+    for (int e = t; e < GB * GB; e += 256) {
+        const int i = e / GB, j = e - i * GB;
+        float acc;
+        if (jb == kb) acc = Dinv[e];
+        else {
+            acc = 0.f;
+#pragma unroll 8
+            for (int r = 0; r < GB; ++r) acc = fmaf(Dinv[i * GB + r], P[r * GB + j], acc);
+        }
+        Y[(size_t)(kb * GB + i) * n + jb * GB + j] = acc;
+    }
+}
+__global__ void __launch_bounds__(256) gj_block_update_kernel(const float* __restrict__ X, float* __restrict__ Y, int n, int kb) {
+    __shared__ float Ls[GB * (GB + 1)];               // X_ik
+    __shared__ float Rs[GB * GB];                      // Y_kj
+    const int t = threadIdx.x, jb = blockIdx.x;
+    const int ib = blockIdx.y + (blockIdx.y >= kb ? 1 : 0);          // skip the pivot block row
+    for (int e = t; e < GB * GB; e += 256) {
+        const int i = e / GB, j = e - i * GB;
+        Ls[i * (GB + 1) + j] = X[(size_t)(ib * GB + i) * n + kb * GB + j];
+        Rs[e] = Y[(size_t)(kb * GB + i) * n + jb * GB + j];
+    }
+    __syncthreads();
+    const int tx = t & 15, ty = t >> 4;                // thread tile 4 x 4: rows ty + 16 a, columns tx + 16 b
+    float acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+#pragma unroll 4
+    for (int r = 0; r < GB; ++r) {
+        float l[4], q[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) { l[a] = Ls[(ty + 16 * a) * (GB + 1) + r]; q[a] = Rs[r * GB + tx + 16 * a]; }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(l[a], q[b], acc[a][b]);
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const size_t o = (size_t)(ib * GB + ty + 16 * a) * n + jb * GB + tx + 16 * b;
+            Y[o] = (jb == kb ? 0.f : X[o]) - acc[a][b];
+        }
+}
+
 static int gj_inverse(float* X, float* Y, int n, float** result, cudaStream_t st) {
+    if (n <= 128) {
+        const size_t smem = (size_t)2 * n * n * sizeof(float);
+        static bool attr = false;
+        if (!attr) {
+            cudaError_t e = cudaFuncSetAttribute(gj_inverse_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 128 * 128 * 4);
+            if (e != cudaSuccess) return cuda_fail(e, "gj_inverse smem attr");
+            attr = true;
+        }
+        gj_inverse_smem_kernel<<<1, 1024, smem, st>>>(X, Y, n);
+        count_launch(1);
+        *result = Y;
+        return 0;
+    }
+    if (n % GB == 0) {
+        const int nb = n / GB;
+        float *in = X, *out = Y;
+        for (int kb = 0; kb < nb; ++kb) {
+            gj_block_panel_kernel<<<nb, 256, 0, st>>>(in, out, n, kb);
+            gj_block_update_kernel<<<dim3(nb, nb - 1), 256, 0, st>>>(in, out, n, kb);
+            float* tmp = in; in = out; out = tmp;
+        }
+        count_launch(2 * nb);
+        *result = in;
+        return 0;
+    }
     int grid = (n * n + 256 * 4 - 1) / (256 * 4);
     const int cap = sm_count() * 2;
     if (grid > cap) grid = cap;

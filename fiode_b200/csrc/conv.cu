@@ -191,7 +191,9 @@ template <int IM>
 __global__ void __launch_bounds__(160) irfft32_mix3_kernel(const float2* __restrict__ Xf, const float2* __restrict__ Qt,
                                                            int B, int C, const float* __restrict__ bias, int group_sort,
                                                            float* __restrict__ y) {
-    constexpr int n = 32, CH = 8, H = 17, RS = 18, RSI = n * RS + 1, F = n * H, THREADS = 160;   // CH * H = 136 column tasks: one round
+    // RS = H (no row padding): phi = u * RS + v, so the mixing writes consecutive words, the column pass reads consecutive
+    // words across lanes, and the row pass (lane = row pair, stride 2 RS float2 = 68 words) is 2-way instead of 4-way conflicted
+    constexpr int n = 32, CH = 8, H = 17, RS = 17, RSI = n * RS + 1, F = n * H, THREADS = 160, OS = n + 4;
     extern __shared__ float4 smem4[];
     float2* T = reinterpret_cast<float2*>(smem4);                 // [IM][CH] images of [n][RS] (+1)
     const int groups_per_b = C / CH;
@@ -208,19 +210,41 @@ __global__ void __launch_bounds__(160) irfft32_mix3_kernel(const float2* __restr
         Xs[e] = (b0 + im < B) ? __ldg(Xf + (size_t)b0 * 3 * F + e) : make_float2(0.f, 0.f);
     }
     __syncthreads();
-    // step 1a: mix.  Yf[im][ci][phi] = sum_c Q[chan(ci)][c][phi] Xs[im][c][phi], lanes along phi: the Q reads are coalesced,
-    // independent of each other (the loop carries no FFT registers, so the compiler keeps many in flight) and each Q
-    // value is read once per CTA.  Results land in T at the place the column pass reads them.
-    for (int e = threadIdx.x; e < CH * F; e += THREADS) {
-        const int ci = e / F, phi = e - ci * F, u = phi / H, v = phi - u * H;
-        const float2* q = Qt + (size_t)chan(ci) * 3 * F + phi;
-        const float2 q0 = __ldg(q), q1 = __ldg(q + F), q2 = __ldg(q + 2 * F);
+    // step 1a: mix.  Yf[im][ci][phi] = sum_c Q[chan(ci)][c][phi] Xs[im][c][phi].  Lanes run along phi (coalesced Q reads, each
+    // Q value read once per CTA); a thread does channels cp and cp + CH/2 of one phi, so every Xs value it reads from shared
+    // memory feeds two outputs; the Q loads of UB iterations are issued together (they would otherwise serialise on L2 latency).
+    {
+        constexpr int UB = 5, ITERS = ((CH / 2) * F + THREADS - 1) / THREADS;      // 14 (phi, channel-pair) items per thread
+        for (int it0 = 0; it0 < ITERS; it0 += UB) {
+            float2 qa[UB][3], qb[UB][3];
 #pragma unroll
-        for (int im = 0; im < IM; ++im) {
-            const float2* xs = Xs + im * 3 * F + phi;
-            float2 acc = make_float2(0.f, 0.f);
-            cfma(acc, q0, xs[0]); cfma(acc, q1, xs[F]); cfma(acc, q2, xs[2 * F]);
-            T[(im * CH + ci) * RSI + u * RS + v] = acc;
+            for (int j = 0; j < UB; ++j) {
+                const int e = threadIdx.x + (it0 + j) * THREADS;
+                if (it0 + j < ITERS && e < (CH / 2) * F) {
+                    const int cp = e / F, phi = e - cp * F;
+                    const float2* q = Qt + (size_t)chan(cp) * 3 * F + phi;
+                    const float2* r = Qt + (size_t)chan(cp + CH / 2) * 3 * F + phi;
+                    qa[j][0] = __ldg(q); qa[j][1] = __ldg(q + F); qa[j][2] = __ldg(q + 2 * F);
+                    qb[j][0] = __ldg(r); qb[j][1] = __ldg(r + F); qb[j][2] = __ldg(r + 2 * F);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < UB; ++j) {
+                const int e = threadIdx.x + (it0 + j) * THREADS;
+                if (it0 + j < ITERS && e < (CH / 2) * F) {
+                    const int cp = e / F, phi = e - cp * F;
+#pragma unroll
+                    for (int im = 0; im < IM; ++im) {
+                        const float2* xs = Xs + im * 3 * F + phi;
+                        const float2 x0 = xs[0], x1 = xs[F], x2 = xs[2 * F];
+                        float2 acc = make_float2(0.f, 0.f), bcc = make_float2(0.f, 0.f);
+                        cfma(acc, qa[j][0], x0); cfma(acc, qa[j][1], x1); cfma(acc, qa[j][2], x2);
+                        cfma(bcc, qb[j][0], x0); cfma(bcc, qb[j][1], x1); cfma(bcc, qb[j][2], x2);
+                        T[(im * CH + cp) * RSI + phi] = acc;
+                        T[(im * CH + cp + CH / 2) * RSI + phi] = bcc;
+                    }
+                }
+            }
         }
     }
     __syncthreads();
@@ -237,13 +261,14 @@ __global__ void __launch_bounds__(160) irfft32_mix3_kernel(const float2* __restr
     }
     __syncthreads();
     // step 2: rows.  task = (image, channel pair (ci, ci + CH/2), row pair p): two real rows per complex FFT (rows 2p, 2p+1 packed
-    // as re / im), both channels of a GroupSort pair in the same thread, so bias + (max, min) happen in registers and the
-    // four finished rows go straight to global memory as float4 (no smem round trip, no separate store pass).
+    // as re / im), both channels of a GroupSort pair in the same thread, so bias + (max, min) happen in registers.  The four
+    // finished rows are staged in shared memory (over T / Xs, which are dead by then) and leave as coalesced float4 rows.
     const float scale = 1.0f / (float)(n * n);
-    for (int task = threadIdx.x; task < IM * (CH / 2) * (n / 2); task += THREADS) {
-        const int ic = task / (n / 2), p = task - ic * (n / 2), im = ic / (CH / 2), ci = ic - im * (CH / 2);
-        if (b0 + im >= B) continue;
-        float2 za[n], zb[n];
+    const int task = threadIdx.x;
+    const bool has_task = task < IM * (CH / 2) * (n / 2);
+    const int ic2 = task / (n / 2), p = task - ic2 * (n / 2), im = ic2 / (CH / 2), ci = ic2 - im * (CH / 2);
+    float2 za[n], zb[n];
+    if (has_task) {
         auto load_rows = [&](int c, float2 (&z)[n]) {
             const float2* ta = T + (im * CH + c) * RSI + 2 * p * RS;
             const float2* tb = ta + RS;
@@ -258,10 +283,13 @@ __global__ void __launch_bounds__(160) irfft32_mix3_kernel(const float2* __restr
         };
         load_rows(ci, za);
         load_rows(ci + CH / 2, zb);
-        const int ca = chan(ci), cb = chan(ci + CH / 2);
-        const float bsa = bias ? bias[ca] : 0.f, bsb = bias ? bias[cb] : 0.f;
-        float* ya = y + (((size_t)(b0 + im) * C + ca) * n + 2 * p) * n;     // rows 2p, 2p+1 of channel a
-        float* yb = y + (((size_t)(b0 + im) * C + cb) * n + 2 * p) * n;
+    }
+    __syncthreads();                                   // every read of T is done: reuse the buffer as the output stage
+    float* O = reinterpret_cast<float*>(smem4);        // [IM * CH][n rows][OS] floats (OS = n + 4: conflict-free float4 rows)
+    if (has_task) {
+        const float bsa = bias ? bias[chan(ci)] : 0.f, bsb = bias ? bias[chan(ci + CH / 2)] : 0.f;
+        float* oa = O + ((im * CH + ci) * n + 2 * p) * OS;
+        float* ob = O + ((im * CH + ci + CH / 2) * n + 2 * p) * OS;
 #pragma unroll
         for (int k = 0; k < n; k += 4) {
             float a0[4], a1[4], c0[4], c1[4];
@@ -273,18 +301,29 @@ __global__ void __launch_bounds__(160) irfft32_mix3_kernel(const float2* __restr
                 a0[q] = group_sort ? fmaxf(u0, w0) : u0; c0[q] = group_sort ? fminf(u0, w0) : w0;
                 a1[q] = group_sort ? fmaxf(u1, w1) : u1; c1[q] = group_sort ? fminf(u1, w1) : w1;
             }
-            *reinterpret_cast<float4*>(ya + k) = make_float4(a0[0], a0[1], a0[2], a0[3]);
-            *reinterpret_cast<float4*>(ya + n + k) = make_float4(a1[0], a1[1], a1[2], a1[3]);
-            *reinterpret_cast<float4*>(yb + k) = make_float4(c0[0], c0[1], c0[2], c0[3]);
-            *reinterpret_cast<float4*>(yb + n + k) = make_float4(c1[0], c1[1], c1[2], c1[3]);
+            *reinterpret_cast<float4*>(oa + k) = make_float4(a0[0], a0[1], a0[2], a0[3]);
+            *reinterpret_cast<float4*>(oa + OS + k) = make_float4(a1[0], a1[1], a1[2], a1[3]);
+            *reinterpret_cast<float4*>(ob + k) = make_float4(c0[0], c0[1], c0[2], c0[3]);
+            *reinterpret_cast<float4*>(ob + OS + k) = make_float4(c1[0], c1[1], c1[2], c1[3]);
         }
+    }
+    __syncthreads();
+    // step 3: coalesced copy-out, one float4 per lane, a channel-image (4 KB) per 256 consecutive items
+    for (int e = threadIdx.x; e < IM * CH * n * (n / 4); e += THREADS) {
+        const int ic = e / (n * (n / 4)), rem = e - ic * (n * (n / 4)), row = rem / (n / 4), k4 = rem - row * (n / 4);
+        const int im3 = ic / CH, c3 = ic - im3 * CH;
+        if (b0 + im3 >= B) continue;
+        const float4 v4 = *reinterpret_cast<const float4*>(O + (ic * n + row) * OS + k4 * 4);
+        *reinterpret_cast<float4*>(y + ((size_t)(b0 + im3) * C + chan(c3)) * n * n + rem * 4) = v4;
     }
 }
 template <int IM>
 static int launch_irfft32_mix3_t(const float2* Xf, const float2* Qt, int B, int C, const float* bias, int gs, float* y,
                                  cudaStream_t st) {
     constexpr int F = 544;
-    const size_t smem = (size_t)IM * 8 * (32 * 18 + 1) * sizeof(float2) + 16 + (size_t)IM * 3 * F * sizeof(float2);
+    const size_t stage = (size_t)IM * 8 * (32 * 17 + 1) * sizeof(float2) + 16 + (size_t)IM * 3 * F * sizeof(float2);
+    const size_t outb = (size_t)IM * 8 * 32 * 36 * sizeof(float);      // output stage reuses the same buffer
+    const size_t smem = stage > outb ? stage : outb;
     cudaError_t e = cudaFuncSetAttribute(irfft32_mix3_kernel<IM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return cuda_fail(e, "irfft32_mix3 smem attr");
     irfft32_mix3_kernel<IM><<<((B + IM - 1) / IM) * (C / 8), 160, smem, st>>>(Xf, Qt, B, C, bias, gs, y);
