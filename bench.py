@@ -279,6 +279,19 @@ STAGES = [
 ]
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of one 4096-image slab
+# (profiles/r01c_ncu_full_summary.md; re-measure when a kernel changes).  Keyed by the kernel named in STAGES / the solver.
+NCU_TRAFFIC_BYTES = {
+    'rfft2_kernel<32>': 50.41e6 + 3.33e6,
+    'irfft32_mix3_kernel': 54.27e6 + 477.67e6,
+    'gemm_tc_kernel<s2d,32>': 536.93e6 + 114.61e6,
+    'rfft2_kernel<16,fm>': 134.24e6 + 101.42e6,
+    'irfft2_kernel<16,fm>': 302.01e6 + 227.90e6,
+    'gemm_tc_kernel<s2d,64>': 268.55e6 + 45.70e6,
+    'dopri5_simplex_batched_kernel': 0.60e6,
+}
+
+
 def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
     """Device time of every kernel stage of one step (backbone over G*256 images, then the G-solve dopri5 launch),
     CUDA events on the launching stream, averaged over ``iters`` runs on rotating (> L2) inputs; the `roofline`
@@ -290,19 +303,21 @@ def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
     n_img = G * B
     pm = ivp.init_coordinates.param_map
     bw, keep = pm.backbone_weights()
-    xs = [x.reshape(n_img, 3, 32, 32) for x in x_dev]
+    n_stage = min(n_img, 4096)                 # the stage events describe ONE slab (4096 images) of the backbone
+    xs = [x.reshape(n_img, 3, 32, 32)[:n_stage] for x in x_dev]
     acc = [0.0] * len(STAGES)
     buf = (ctypes.c_float * 16)()
     L.fiode_backbone_enable_stage_timing(1)
     try:
         for i in range(iters + 2):
-            s = ops.backbone_fwd(bw, xs[i % len(xs)])
+            ops.backbone_fwd(bw, xs[i % len(xs)])
             rc = L.fiode_backbone_stage_times(buf, 16)
             if rc == 0 and i >= 2:
                 for j in range(len(STAGES)):
                     acc[j] += buf[j] / iters
     finally:
         L.fiode_backbone_enable_stage_timing(0)
+    s = ops.backbone_fwd(bw, x_dev[0].reshape(n_img, 3, 32, 32))
     dw = ivp.dyn_fun.dyn_weights()
     h0 = torch.full((n_img, 10), 0.1, device=s.device)
     t_dev = ts.to(device=s.device, dtype=torch.float64)
@@ -314,7 +329,7 @@ def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
     for (name, kern, by, fl), ms in zip(STAGES, acc):
         d = dict(stage=name, kernel=kern, ms=ms)
         if by:
-            d.update(gbs=by * n_img / (ms * 1e-3) / 1e9 if ms > 0 else None, tflops=fl * n_img / (ms * 1e-3) / 1e12 if ms > 0 else None,
+            d.update(gbs=by * n_stage / (ms * 1e-3) / 1e9 if ms > 0 else None, tflops=fl * n_stage / (ms * 1e-3) / 1e12 if ms > 0 else None,
                      bound='tensor' if fl / by > ridge else 'hbm')
             d['frac'] = (d['tflops'] / pk['bf16']) if d['bound'] == 'tensor' else (d['gbs'] / pk['hbm'])
         stages.append(d)
@@ -323,18 +338,19 @@ def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
                        ms=ms_solve, tflops=solve_flop / (ms_solve * 1e-3) / 1e12, bound='latency',
                        note='%d dependent RHS evaluations per solve, %d rows per CTA: FP32 FFMA, latency-bound' % (st.nfe, B // max(cluster_size, 1) if cluster_size else 32)))
     ms_bb = sum(acc)
-    bb_bytes = sum(x[2] for x in STAGES) * n_img
+    bb_bytes = sum(x[2] for x in STAGES) * n_stage
     top = max((d for d in stages if 'tflops' in d or 'gbs' in d), key=lambda d: d['ms'])
     if top.get('bound') == 'hbm':
         rf = dict(bound='hbm', achieved=top['gbs'], peak=pk['hbm'], unit='GB/s', frac=top['gbs'] / pk['hbm'])
     else:
         rf = dict(bound='tensor', achieved=top['tflops'], peak=pk['bf16'], unit='TFLOP/s', frac=top['tflops'] / pk['bf16'])
-    rf.update(traffic=None, kernel=top['kernel'], stage=top['stage'], ms_per_launch=top['ms'], peak_source=pk['source'],
+    rf.update(traffic=NCU_TRAFFIC_BYTES.get(top['kernel']), traffic_source='profiles/r01c_ncu_full_summary.md (one 4096-image slab)',
+              kernel=top['kernel'], stage=top['stage'], ms_per_launch=top['ms'], peak_source=pk['source'],
               note='algorithmic bytes / flops of SURVEY 8(d) over the CUDA-event time of that launch; tensor-core stages run the '
                    'fp16x2-split FP32 emulation (3 MMAs per product), so their ceiling is peak / 3; see DESIGN.md section 4',
-              parts=dict(backbone_ms=ms_bb, backbone_images=n_img, backbone_algorithmic_gbs=bb_bytes / (ms_bb * 1e-3) / 1e9,
+              parts=dict(backbone_ms=ms_bb, backbone_images=n_stage, backbone_algorithmic_gbs=bb_bytes / (ms_bb * 1e-3) / 1e9,
                          backbone_hbm_frac=bb_bytes / (ms_bb * 1e-3) / 1e9 / pk['hbm'],
-                         backbone_tflops=BACKBONE_FLOP * n_img / (ms_bb * 1e-3) / 1e12, dopri5_ms=ms_solve,
+                         backbone_tflops=BACKBONE_FLOP * n_stage / (ms_bb * 1e-3) / 1e12, dopri5_ms=ms_solve,
                          nfe=st.nfe, n_accept=st.n_accept, n_reject=st.n_reject, stages=stages))
     return rf
 
