@@ -10,6 +10,7 @@
 //
 // Spectra are kept in torch's rfft2 layout [b][c][u][v], v in [0, n/2], phi = u*(n/2+1)+v.
 #include "common.cuh"
+#include <cuda_pipeline.h>
 #include <cstdlib>
 #include "fft.cuh"
 
@@ -204,12 +205,14 @@ __global__ void __launch_bounds__(160) irfft32_mix3_kernel(const float2* __restr
         return g * CH + ci;
     };
     // the IM input spectra (3 channels each) are staged once; every thread then reuses each Q value for all IM images
-    float2* Xs = T + IM * CH * RSI + 1;                           // [IM][3][F]
-    for (int e = threadIdx.x; e < IM * 3 * F; e += THREADS) {
-        const int im = e / (3 * F);
-        Xs[e] = (b0 + im < B) ? __ldg(Xf + (size_t)b0 * 3 * F + e) : make_float2(0.f, 0.f);
+    float2* Xs = T + IM * CH * RSI + ((IM * CH * RSI) & 1);       // [IM][3][F], 16-byte aligned
+    // asynchronous 16-byte copies (LDGSTS): all in flight at once, and they overlap the first batch of Q loads below
+    for (int e = threadIdx.x; e < IM * 3 * F / 2; e += THREADS) {
+        const int im = e / (3 * F / 2);
+        if (b0 + im < B) __pipeline_memcpy_async(Xs + 2 * e, Xf + (size_t)b0 * 3 * F + 2 * e, 16);
+        else *reinterpret_cast<float4*>(Xs + 2 * e) = make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    __syncthreads();
+    __pipeline_commit();
     // step 1a: mix.  Yf[im][ci][phi] = sum_c Q[chan(ci)][c][phi] Xs[im][c][phi].  Lanes run along phi (coalesced Q reads, each
     // Q value read once per CTA); a thread does channels cp and cp + CH/2 of one phi, so every Xs value it reads from shared
     // memory feeds two outputs; the Q loads of UB iterations are issued together (they would otherwise serialise on L2 latency).
@@ -227,6 +230,10 @@ __global__ void __launch_bounds__(160) irfft32_mix3_kernel(const float2* __restr
                     qa[j][0] = __ldg(q); qa[j][1] = __ldg(q + F); qa[j][2] = __ldg(q + 2 * F);
                     qb[j][0] = __ldg(r); qb[j][1] = __ldg(r + F); qb[j][2] = __ldg(r + 2 * F);
                 }
+            }
+            if (it0 == 0) {                          // uniform: the staged spectra are needed from here on
+                __pipeline_wait_prior(0);
+                __syncthreads();
             }
 #pragma unroll
             for (int j = 0; j < UB; ++j) {
