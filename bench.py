@@ -252,8 +252,19 @@ def fi_step_bench(device, pk, world, iters=10, warm=3):
     for _ in range(warm):
         step()
     c0 = fiode_b200.launch_count()
-    ms = timed(step, iters) / iters
+    ms_eager = timed(step, iters) / iters
     launches = (fiode_b200.launch_count() - c0) // iters
+    # the step is launch-bound on the host: capture it once in a CUDA graph and replay (fiode_b200/graphs.py)
+    ms, graphed = ms_eager, False
+    if world == 1 or os.environ.get('FIODE_GRAPH_NCCL') == '1':
+        try:
+            from fiode_b200.graphs import GraphedStep
+            gstep = GraphedStep(step, warmup=1)
+            gstep(); gstep()
+            ms, graphed = timed(gstep, iters) / iters, True
+            step = gstep
+        except Exception as e:           # keep the eager number
+            graph_error = repr(e)
     t = torch.tensor([ms], device=device)
     if world > 1:
         import torch.distributed as dist
@@ -262,9 +273,10 @@ def fi_step_bench(device, pk, world, iters=10, warm=3):
     rows = Bt * S
     flop = 3 * (rows * RHS_FLOP + Bt * BACKBONE_FLOP + 4.3e9)       # forward + ~2x backward
     return dict(metric='FI training steps/s (B=128 x h_sample_size=256, data-parallel)', value=world / (ms * 1e-3),
-                unit='steps/s (whole job)', ms_per_step=ms, gpu_launches=launches, rows_per_step=rows,
+                unit='steps/s (whole job)', ms_per_step=ms, ms_per_step_eager=ms_eager, cuda_graph=graphed, gpu_launches=launches, rows_per_step=rows,
                 grad_floats=reducer.numel, allreduce_bytes=4 * reducer.numel,
                 algorithmic_tflops=flop / (ms * 1e-3) / 1e12, loss=float(step().detach()),
+                **({} if graphed or world > 1 else {'graph_error': locals().get('graph_error')}),
                 note='forward + backward to all 33 parameters + one flat all-reduce; kernels are the first correct versions '
                      '(FFMA GEMMs, per-layer launches), not yet tuned')
 

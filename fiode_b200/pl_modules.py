@@ -51,6 +51,7 @@ class LyapunovLearning(nn.Module):
         self.train_ode_solver, self.train_ode_tol = train_ode_solver, train_ode_tol
         self.val_ode_solver, self.val_ode_tol = val_ode_solver, val_ode_tol
         self.use_adjoint = False
+        self.keep_graph_tensors = False        # tests: expose dL/dQ and dL/ds of the last step (layer.Q.grad, last_static_state.grad)
         self.current_epoch, self.global_step = 0, 10 ** 9
         self.logged = {}
         self.model = IVP(n_input=n_input, n_output=n_output, init_coordinates=init_fun, ts=torch.linspace(0, t_max, 2),
@@ -98,8 +99,9 @@ class LyapunovLearning(nn.Module):
             if dyn.training and torch.is_grad_enabled():
                 # train mode: Q is a graph node, dL/dQ continues through fiode_cayley_linear_bwd to weight / alpha
                 q = l.orthogonal_weight_autograd()
-                q.retain_grad()                                   # dL/dQ stays observable in layer.Q.grad, as in eval mode
-                l.Q = q
+                if self.keep_graph_tensors:                       # dL/dQ observable in layer.Q.grad, as in eval mode
+                    q.retain_grad()
+                    l.Q = q
                 Qs.append(q)
                 continue
             q = l.orthogonal_weight()                             # eval mode: leaf proxies, dL/dQ lands in layer.Q.grad
@@ -112,7 +114,9 @@ class LyapunovLearning(nn.Module):
             # classification.py:97-101 dropout after each hidden activation; Bernoulli masks from torch's Philox stream
             p, N = dyn.dropout.p, batch_size * S
             masks = tuple((torch.rand(N, dyn.mlp_size, device=x.device) >= p).float() / (1 - p) for _ in range(2))
-        self.last_static_state = static_state
+        # holding graph-attached tensors on the module keeps last step's autograd graph (and its AccumulateGrad nodes)
+        # alive, which breaks CUDA-graph capture of the next step: only on request
+        self.last_static_state = static_state if (self.keep_graph_tensors or not static_state.grad_fn) else None
         loss = _FiLoss.apply(dyn, h_sample_in[0], y, S, float(kappa), masks, static_state, *Qs,
                              lay[0].bias, lay[1].bias, lay[2].bias, lay[3].bias)
         out4 = dyn.last_fi.out4

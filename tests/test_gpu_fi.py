@@ -33,6 +33,7 @@ def build_learning(sd, c, samplers=None):
     # exact coefficients, as the golden generator pins them (the scheduler's 1e-12 regulariser would turn
     # floor(32 * 0.5) into 15)
     mod.sampler_scheduler.get_mixer_coefficients = lambda epoch: list(c['mix'])
+    mod.keep_graph_tensors = True
     return mod.to(DEV)
 
 

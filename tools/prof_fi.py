@@ -56,3 +56,16 @@ torch.cuda.profiler.start()
 step()
 torch.cuda.synchronize()
 torch.cuda.profiler.stop()
+
+if len(sys.argv) > 1 and sys.argv[1] == 'graph':
+    import traceback
+    del loss                     # a live loss keeps last step's autograd graph (default-stream AccumulateGrad nodes) alive
+    from fiode_b200.graphs import GraphedStep
+    try:
+        g = GraphedStep(step, warmup=2)
+        g(); g()
+        torch.cuda.synchronize()
+        print('graphed step:', bench.timed(g, 20) / 20, 'ms; loss', float(g().detach()))
+        print('eager step  :', bench.timed(step, 20) / 20, 'ms')
+    except Exception:
+        traceback.print_exc()
