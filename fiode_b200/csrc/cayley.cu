@@ -128,19 +128,28 @@ __global__ void __launch_bounds__(1024) gj_inverse_smem_kernel(const float* __re
     const int total = n * n, t = threadIdx.x;
     for (int e = t; e < total; e += 1024) A[e] = Xin[e];
     __syncthreads();
+    // warp w owns rows w, w + 32, ...; lane l owns columns l, l + 32, ... : no index arithmetic inside the pivot loop, the
+    // pivot row is read once per lane and reused for every row of the warp
+    const int w = t >> 5, l = t & 31;
     for (int k = 0; k < n; ++k) {
         const float* in = (k & 1) ? Bf : A;
         float* o = (k & 1) ? A : Bf;
         const float ip = 1.f / in[k * n + k];
-        for (int e = t; e < total; e += 1024) {
-            const int i = e / n, j = e - i * n;
-            float v;
-            if (i == k) v = (j == k) ? ip : in[e] * ip;
-            else {
-                const float f = in[i * n + k];
-                v = (j == k) ? -f * ip : fmaf(-f, in[k * n + j] * ip, in[e]);
+        float pk[4];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) { const int j = l + 32 * c; pk[c] = j < n ? in[k * n + j] * ip : 0.f; }
+        for (int i = w; i < n; i += 32) {
+            const float f = in[i * n + k];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const int j = l + 32 * c;
+                if (j < n) {
+                    float v;
+                    if (i == k) v = (j == k) ? ip : pk[c];
+                    else v = (j == k) ? -f * ip : fmaf(-f, pk[c], in[i * n + j]);
+                    o[i * n + j] = v;
+                }
             }
-            o[e] = v;
         }
         __syncthreads();
     }
@@ -164,19 +173,24 @@ __global__ void __launch_bounds__(256) gj_block_panel_kernel(const float* __rest
         P[e] = X[(size_t)(kb * GB + i) * n + jb * GB + j];
     }
     __syncthreads();
+    const int w = t >> 5, l = t & 31;                  // warp w: rows w, w + 8, ...; lane l: columns l, l + 32
     for (int k = 0; k < GB; ++k) {
         const float* in = (k & 1) ? D1 : D0;
         float* o = (k & 1) ? D0 : D1;
         const float ip = 1.f / in[k * GB + k];
-        for (int e = t; e < GB * GB; e += 256) {
-            const int i = e / GB, j = e - i * GB;
-            float v;
-            if (i == k) v = (j == k) ? ip : in[e] * ip;
+        const float pk0 = in[k * GB + l] * ip, pk1 = in[k * GB + l + 32] * ip;
+#pragma unroll
+        for (int a = 0; a < GB / 8; ++a) {
+            const int i = w + 8 * a;
+            const float f = in[i * GB + k];
+            float v0, v1;
+            if (i == k) { v0 = (l == k) ? ip : pk0; v1 = (l + 32 == k) ? ip : pk1; }
             else {
-                const float f = in[i * GB + k];
-                v = (j == k) ? -f * ip : fmaf(-f, in[k * GB + j] * ip, in[e]);
+                v0 = (l == k) ? -f * ip : fmaf(-f, pk0, in[i * GB + l]);
+                v1 = (l + 32 == k) ? -f * ip : fmaf(-f, pk1, in[i * GB + l + 32]);
             }
-            o[e] = v;
+            o[i * GB + l] = v0;
+            o[i * GB + l + 32] = v1;
         }
         __syncthreads();
     }

@@ -65,10 +65,19 @@ __global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict_
     __shared__ double sh[8];
     const int c = blockIdx.x;
     double acc = 0;
-    const size_t per = (size_t)B * inner;
-    for (size_t e = threadIdx.x; e < per; e += 256) {
-        const size_t b = e / inner, r = e - b * inner;
-        acc += (double)gy[(b * C + c) * inner + r];
+    if (inner >= 32) {           // warp per image, lanes along the (contiguous) inner axis: no index division
+        for (int b = threadIdx.x >> 5; b < B; b += 8) {
+            const float* g = gy + ((size_t)b * C + c) * inner;
+            float a = 0.f;
+            for (int r = threadIdx.x & 31; r < inner; r += 32) a += g[r];
+            acc += (double)a;
+        }
+    } else {
+        const size_t per = (size_t)B * inner;
+        for (size_t e = threadIdx.x; e < per; e += 256) {
+            const size_t b = e / inner, r = e - b * inner;
+            acc += (double)gy[(b * C + c) * inner + r];
+        }
     }
     acc = warp_sum(acc);
     if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
