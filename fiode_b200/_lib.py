@@ -97,6 +97,11 @@ SIGNATURES = {
     'fiode_dopri5_workspace_bytes': (SZ, [I]),
     'fiode_dopri5_simplex': (I, [C.POINTER(DynWeights), P, P, I, I, P, I, F64, F64, LL, P, P, P, SZ, I, P]),
     'fiode_dopri5_max_concurrent_solves': (I, [I, I]),
+    'fiode_ibp_workspace_bytes': (SZ, []),
+    'fiode_ibp_sigmoid': (I, [P, P, P, LL, F32, F32, F32, F32, P, P, P]),
+    'fiode_ibp_cbf_qp': (I, [P, P, P, LL, F32, F32, F32, I, F32, P, P, P, P, SZ, P]),
+    'fiode_runner_up_mask': (I, [P, LL, I, F32, P, P]),
+    'fiode_perturbed_vdot': (I, [P, P, P, I, P, LL, P, P, P, SZ, P]),
     'fiode_dopri5_simplex_batched': (I, [C.POINTER(DynWeights), P, P, I, I, I, P, I, F64, F64, LL, P, P, I, P]),
 }
 

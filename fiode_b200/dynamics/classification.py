@@ -69,3 +69,22 @@ class OrthoClassDynProjectSimplexLips(nn.Module):
     def ode_forward(self, t, h_tuple):
         assert self.static_state is not None, '[ERROR] You forgot to set static state before calling forward.'
         return self.eval_dot(t, h_tuple, self.static_state)
+
+
+    # ---- interval step after the CROWN bound (CrownOrthoClassDynProjectSimplexLips, classification.py:175-242) ----
+    def ibp_sigmoid(self, f_lb, f_ub, h_lb, h_ub):
+        """classification.py:175-181.  The reference passes (eta - eps, eta + eps); the box is recovered from them."""
+        h = (h_lb + h_ub) * 0.5
+        eps = float(((h_ub - h_lb) * 0.5).flatten()[0])
+        return ops.ibp_sigmoid(f_lb, f_ub, h, eps, self.alpha_1, self.alpha_2, self.sigma_1)
+
+    def ibp_cbf_qp(self, h, eps, lb, ub, upper=False):
+        """classification.py:208-242 with upper=False (the call at certify_crown.py:143)."""
+        assert not upper, 'upper=True needs the three-argument solver the reference class does not construct either'
+        return ops.ibp_cbf_qp(h, eps, lb, ub, self.alpha_1, self.sigma_1, self.max_iter, self.tol)
+
+
+class CrownOrthoClassDynProjectSimplexLips(OrthoClassDynProjectSimplexLips):
+    """Name the CROWN certification config instantiates (configs/certify); the plain nn.Linear re-parametrisation the
+    reference needs for auto_LiRPA (convert_cayley, classification.py:281-295) is not needed here: the Cayley matrices
+    are cached, and CROWN itself stays on the reference."""

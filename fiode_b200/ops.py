@@ -438,3 +438,45 @@ def cayley_conv_bwd(weight, alpha, n, gQf):
     check(lib().fiode_cayley_conv_bwd(ptr(w), ptr(a), cout, cin, k, n, ptr(g), ptr(gw), ptr(ga), ptr(ws), nb, stream_ptr()),
           'fiode_cayley_conv_bwd')
     return gw, ga
+
+
+# ---- interval step after the CROWN bound (certify_crown.py:139-150) ----------------------------------
+def ibp_sigmoid(lb, ub, h, eps, alpha_1, alpha_2, sigma_1):
+    lb, ub, h = _f32(lb), _f32(ub), _f32(h)
+    N = h.shape[0]
+    o_lb, o_ub = torch.empty_like(lb), torch.empty_like(ub)
+    check(lib().fiode_ibp_sigmoid(ptr(lb), ptr(ub), ptr(h), N, float(eps), float(alpha_1), float(alpha_2), float(sigma_1),
+                                  ptr(o_lb), ptr(o_ub), stream_ptr()), 'fiode_ibp_sigmoid')
+    return o_lb, o_ub
+
+
+def ibp_cbf_qp(h, eps, lb, ub, alpha_1, sigma_1, max_iter=30, tol=1e-4, return_iters=False):
+    h, lb, ub = _f32(h), _f32(lb), _f32(ub)
+    N = h.shape[0]
+    f_lb, f_ub = torch.empty_like(h), torch.empty_like(h)
+    it = torch.zeros(2, dtype=torch.int32, device=h.device)
+    ws = _ws(lib().fiode_ibp_workspace_bytes(), h.device)
+    check(lib().fiode_ibp_cbf_qp(ptr(h), ptr(lb), ptr(ub), N, float(eps), float(alpha_1), float(sigma_1), int(max_iter),
+                                 float(tol), ptr(f_lb), ptr(f_ub), ptr(it), ptr(ws), ws.numel(), stream_ptr()), 'fiode_ibp_cbf_qp')
+    return (f_lb, f_ub, it) if return_iters else (f_lb, f_ub)
+
+
+def perturbed_vdot(f_lb, f_ub, label, runner_up, return_max=False):
+    f_lb, f_ub = _f32(f_lb), _f32(f_ub)
+    N = f_lb.shape[0]
+    lab = label.detach().to(device=f_lb.device, dtype=torch.int32).reshape(-1).contiguous()
+    ru = runner_up.detach().to(device=f_lb.device, dtype=torch.uint8).contiguous()
+    vdot = torch.empty(N, dtype=torch.float32, device=f_lb.device)
+    vmax = torch.empty(1, dtype=torch.float32, device=f_lb.device) if return_max else None
+    ws = _ws(256, f_lb.device)
+    check(lib().fiode_perturbed_vdot(ptr(f_lb), ptr(f_ub), ptr(lab), lab.numel(), ptr(ru), N, ptr(vdot), _opt(vmax), ptr(ws),
+                                     ws.numel(), stream_ptr()), 'fiode_perturbed_vdot')
+    return (vdot, vmax) if return_max else vdot
+
+
+def runner_up_mask(eta, label, margin):
+    eta = _f32(eta)
+    N = eta.shape[0]
+    mask = torch.empty(N, NH, dtype=torch.uint8, device=eta.device)
+    check(lib().fiode_runner_up_mask(ptr(eta), N, int(label), float(margin), ptr(mask), stream_ptr()), 'fiode_runner_up_mask')
+    return mask

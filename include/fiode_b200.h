@@ -306,6 +306,24 @@ FIODE_API int fiode_dopri5_simplex_batched(const fiode_dyn_weights* w, const flo
                                  long long max_num_steps, float* out, fiode_solve_stats* stats,
                                  int cluster_size, void* stream);
 
+/* ---- interval step after the CROWN bound (robustness/certify_crown.py:139-150) ------------------
+ * CROWN itself (auto_LiRPA) stays on the reference; lb <= ftilde <= ub (N,10) are its outputs over [eta-eps, eta+eps].
+ * fiode_ibp_sigmoid   : CrownOrthoClassDynProjectSimplexLips.ibp_sigmoid (dynamics/classification.py:175-181)
+ * fiode_ibp_cbf_qp    : ....ibp_cbf_qp(h, eps, lb, ub, upper=False) (:208-242): 10 N projection problems, one batch-global
+ *                       stop iteration per call (lower / upper), coordinate i of problem (n, i) kept.  iters2 (2 ints,
+ *                       optional) returns the iterations each call ran.
+ * fiode_perturbed_vdot: certify_crown.py:29-34; label (1 or N ints), runner_up (N,10) uint8 mask; vmax optional.          */
+FIODE_API size_t fiode_ibp_workspace_bytes(void);
+FIODE_API int fiode_ibp_sigmoid(const float* lb, const float* ub, const float* h, long long N, float eps, float alpha_1,
+                      float alpha_2, float sigma_1, float* out_lb, float* out_ub, void* stream);
+FIODE_API int fiode_ibp_cbf_qp(const float* h, const float* lb, const float* ub, long long N, float eps, float alpha_1,
+                     float sigma_1, int max_iter, float tol, float* f_lb, float* f_ub, int* iters2, void* ws,
+                     size_t ws_bytes, void* stream);
+/* certify_crown.py:146-148: mask[n][j] = (j != label) && eta[n][j] >= max_j eta[n][j] - margin.                          */
+FIODE_API int fiode_runner_up_mask(const float* eta, long long N, int label, float margin, uint8_t* mask, void* stream);
+FIODE_API int fiode_perturbed_vdot(const float* f_lb, const float* f_ub, const int* label, int label_rows,
+                         const uint8_t* runner_up, long long N, float* vdot, float* vmax, void* ws, size_t ws_bytes,
+                         void* stream);
 /* Solves of B rows that one fiode_dopri5_simplex_batched launch keeps co-resident (one thread-block cluster per
  * solve; cudaOccupancyMaxActiveClusters).  More solves than this run in waves of a full solve latency each:
  * size G to a multiple of it.  cluster_size 0 = the launcher's default.  < 0 on error.                       */

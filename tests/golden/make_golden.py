@@ -353,8 +353,42 @@ def gen_segway():
     save('segway.pt', res)
 
 
+def gen_crown():
+    """Post-CROWN interval step of robustness/certify_crown.py:139-150 with the reference's own functions:
+    CrownOrthoClassDynProjectSimplexLips.ibp_sigmoid / ibp_cbf_qp (dynamics/classification.py:175-242) and
+    perturbed_vdot (certify_crown.py:29-34).  The CROWN bounds themselves (auto_LiRPA) stay on the reference: lb / ub are
+    synthetic intervals around a random nominal."""
+    print('[crown]')
+    import importlib
+    cls = importlib.import_module('dynamics.classification')
+    g = torch.Generator().manual_seed(77)
+    res = {}
+    for name, N, eps, a1, a2, sn, width in [('a1_100', 600, 0.0125, 100., 20., False, 0.3), ('a1_5_sn', 400, 0.025, 5., 5., True, 1.0)]:
+        dyn = cls.CrownOrthoClassDynProjectSimplexLips(alpha_1=a1, alpha_2=a2, sigma_1=0.02, scale_nominal=sn)
+        e = -torch.log1p(-torch.rand(N, 10, generator=g))
+        eta = e / e.sum(1, keepdim=True)
+        mid = torch.randn(N, 10, generator=g) * 2.0
+        half = torch.rand(N, 10, generator=g) * width
+        lb, ub = mid - half, mid + half
+        label = 3
+        with torch.no_grad():
+            lb2, ub2 = (dyn.ibp_sigmoid(lb, ub, eta - eps, eta + eps) if sn else (lb, ub))
+            f_lb, f_ub = dyn.ibp_cbf_qp(eta, eps, lb2.clone(), ub2.clone())
+            max_wrong = torch.max(eta, dim=-1, keepdim=True).values
+            ind_wrong = eta >= (max_wrong - 2 * eps)
+            ind_wrong[:, label] = False
+            y = torch.ones(N, dtype=torch.long) * label
+            f_y = f_lb[list(range(N)), y]
+            f_wrong = torch.max(f_ub.masked_fill(~ind_wrong, -float('inf')), dim=-1).values
+            vdot = -f_y + f_wrong                                  # perturbed_vdot, certify_crown.py:29-34
+        res[name] = dict(eta=eta, eps=eps, alpha_1=a1, alpha_2=a2, sigma_1=0.02, scale_nominal=sn, lb=lb, ub=ub, lb_sig=lb2, ub_sig=ub2,
+                         f_lb=f_lb, f_ub=f_ub, label=label, ind_wrong=ind_wrong, vdot=vdot)
+        print(f'  {name}: f_lb [{float(f_lb.min()):.3f}, {float(f_lb.max()):.3f}]  vdot max {float(vdot.max()):.4f}')
+    save('crown.pt', res)
+
+
 GROUPS = dict(weights=gen_weights, layers=gen_layers, rhs=gen_rhs, ivp=gen_ivp, fi=gen_fi,
-              certify=gen_certify, segway=gen_segway)
+              certify=gen_certify, segway=gen_segway, crown=gen_crown)
 
 if __name__ == '__main__':
     assert rh.available(), 'reference checkout not found: golden vectors can only be regenerated in the build container'

@@ -497,3 +497,26 @@ def test_forward_batches_equals_per_batch_forward(sd):
         torch.testing.assert_close(got[g], want, rtol=1e-5, atol=1e-6)
         a, b = res.stats()[g], one.stats()
         assert (a.n_accept, a.n_reject, a.nfe) == (b.n_accept, b.n_reject, b.nfe)
+
+
+def test_max_concurrent_solves_is_the_wave_size(sd):
+    """fiode_dopri5_max_concurrent_solves: one launch keeps that many solve clusters co-resident; results do not depend on
+    how many solves share a launch (a second wave only costs time)."""
+    from fiode_b200 import ops
+    for cs in (4, 8):
+        n = ops.dopri5_max_concurrent_solves(256, cs)
+        assert 1 <= n <= 148 // cs
+    with pytest.raises(Exception):
+        ops.dopri5_max_concurrent_solves(256, 3)
+    ivp = fx.build_b200_model(sd)
+    dw = ivp.dyn_fun.dyn_weights()
+    n = ops.dopri5_max_concurrent_solves(64, 4)
+    G = n + 3                                             # forces a second wave
+    g = torch.Generator().manual_seed(5)
+    s = (torch.randn(G * 64, 10, generator=g) * 0.5).cuda()
+    h0 = torch.full((G * 64, 10), 0.1, device='cuda')
+    t = torch.tensor([0., 1.], dtype=torch.float64)
+    a = ops.dopri5_simplex_batched(dw, h0, s, G, t, 1e-3, 1e-3, cluster_size=4)
+    b = ops.dopri5_simplex_batched(dw, h0[:3 * 64], s[:3 * 64], 3, t, 1e-3, 1e-3, cluster_size=4)
+    assert torch.equal(a.out[:, :3 * 64], b.out)
+    assert [(x.n_accept, x.n_reject, x.nfe) for x in a.stats()[:3]] == [(x.n_accept, x.n_reject, x.nfe) for x in b.stats()]

@@ -165,3 +165,32 @@ def test_fi_step_gradients_reach_every_parameter(sd, name):
             assert abs(got - want_norm) <= 1e-3 * want_norm + 1e-9, (k, got, want_norm)
         elif named[k].numel() > 1:
             assert abs(got - want_norm) <= 0.2 * want_norm, (k, got, want_norm)
+
+
+def test_graphed_fi_step_equals_eager(sd):
+    """fiode_b200.graphs.GraphedStep: the captured compute_loss -> backward step replays to the same loss and gradients
+    as the eager step on the same inputs (dropout off, fixed variates)."""
+    from tests.test_gpu_fi import build_learning, dev
+    from fiode_b200.graphs import GraphedStep
+    c = fx.load_golden('fi.pt')['uniform_sn1']
+    mod = build_learning(sd, c).train()
+    mod.keep_graph_tensors = False
+    x, y = dev(c['x']), dev(c['y'])
+    var = [dev(v) if v is not None else None for v in c['variates']]
+
+    def step():
+        for p in mod.parameters():
+            p.grad = None
+        loss = mod.compute_loss(x, y, c['B'], act='relu', variates=var)
+        loss.backward()
+        return loss.detach()
+
+    eager_loss = step().clone()
+    eager = {k: p.grad.clone() for k, p in mod.named_parameters()}
+    g = GraphedStep(step, warmup=2)
+    for _ in range(2):
+        out = g()
+    torch.cuda.synchronize()
+    assert torch.equal(out, eager_loss)
+    for k, p in mod.named_parameters():
+        assert torch.equal(p.grad, eager[k]), k
