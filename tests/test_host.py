@@ -75,3 +75,28 @@ def test_grid_pt_reader_round_trip(tmp_path):
     bad[0][5, 0] += 0.1
     with pytest.raises(ValueError):
         grid.numerators_from_grid_pt(bad, T, device='cpu')
+
+
+def test_lightning_checkpoint_loads(sd, tmp_path):
+    """a Lightning-style model.ckpt ({'state_dict': {'model.*': ...}, plus trainer keys and tensors the hot path does
+    not own}) loads into the mirrored IVP and into LyapunovLearning with strict=False, like eval_utils.py:92-107."""
+    from fiode_b200 import checkpoint, pl_modules, lya_cands
+    from fiode_b200.sampling import sampler as smp, sampler_schedulers as sch
+    from fiode_b200.dynamics.output_coordinates import DefaultOutputFun
+    extra = {'some_callback.buffer': torch.zeros(3)}
+    f = tmp_path / 'model.ckpt'
+    torch.save({'epoch': 7, 'global_step': 1234, 'state_dict': {**sd, **extra}, 'optimizer_states': []}, f)
+    ivp = fx.build_b200_model({k: torch.zeros_like(v) for k, v in sd.items()}, device='cpu')
+    missing, unexpected = checkpoint.load_reference_checkpoint(ivp, str(f))
+    assert all('static_state' in m for m in missing) and not unexpected
+    for k, v in sd.items():
+        assert torch.equal(ivp.state_dict()[k[len('model.'):]], v), k
+    ivp2 = fx.build_b200_model({k: torch.zeros_like(v) for k, v in sd.items()}, device='cpu')
+    mod = pl_modules.LyapunovLearning(
+        order=1, h_sample_size=8, h_dist_lim=15, lya_cand=lya_cands.DecisionBoundary(on_simplex=True),
+        sampler=smp.CompositeSampler((10,), [smp.UniformSimplexSampling((10,))]),
+        sampler_scheduler=sch.CompositeSamplerScheduler([sch.ConstantScheduler(1.0)], [1.]),
+        dynamics=ivp2.dyn_fun, output=DefaultOutputFun(), init_fun=ivp2.init_coordinates, t_max=1.0)
+    missing, unexpected = checkpoint.load_reference_checkpoint(mod, str(f))
+    assert unexpected == ['some_callback.buffer']
+    assert torch.equal(mod.model.dyn_fun.mlp_to_mlp.weight, sd['model.dyn_fun.mlp_to_mlp.weight'])
