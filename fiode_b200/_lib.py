@@ -97,6 +97,13 @@ SIGNATURES = {
     'fiode_dopri5_workspace_bytes': (SZ, [I]),
     'fiode_dopri5_simplex': (I, [C.POINTER(DynWeights), P, P, I, I, P, I, F64, F64, LL, P, P, P, SZ, I, P]),
     'fiode_dopri5_max_concurrent_solves': (I, [I, I]),
+    'fiode_rhs_train_workspace_bytes': (SZ, [LL]),
+    'fiode_rhs_fwd_train': (I, [C.POINTER(DynWeights), P, P, LL, P, P, P, P, P, P, SZ, P]),
+    'fiode_dyn_transposes': (I, [C.POINTER(DynWeights), P, P, P, P, P]),
+    'fiode_rhs_bwd_data': (I, [C.POINTER(DynWeights), P, LL, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, P, SZ, P]),
+    'fiode_rhs_bwd_params_workspace_bytes': (SZ, [LL]),
+    'fiode_rhs_bwd_params': (I, [P, P, P, P, P, P, P, LL, P, P, P, P, P, P, P, P, SZ, P]),
+    'fiode_lincomb': (I, [P, LL, I, P, P, P]),
     'fiode_ibp_workspace_bytes': (SZ, []),
     'fiode_ibp_sigmoid': (I, [P, P, P, LL, F32, F32, F32, F32, P, P, P]),
     'fiode_ibp_cbf_qp': (I, [P, P, P, LL, F32, F32, F32, I, F32, P, P, P, P, SZ, P]),

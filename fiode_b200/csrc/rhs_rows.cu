@@ -428,6 +428,16 @@ int launch_rows_store(const fiode_dyn_weights* w, const float* h, const float* s
 }
 }  // namespace fiode
 
+namespace fiode {
+int launch_rhs_finish(const float* ft, const float* h, long long N, const fiode_dyn_weights* w, const unsigned* notconv,
+                      float* f, float* mu, int* n_iter, cudaStream_t st) {
+    rhs_finish_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(ft, h, N, *w, notconv, f, mu, n_iter);
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(1);
+    return 0;
+}
+}  // namespace fiode
+
 extern "C" int fiode_rhs_fwd(const fiode_dyn_weights* w, const float* h, const float* s, long long N,
                              long long s_rows, long long s_group, float* f, float* ftilde, float* mu, int* n_iter,
                              void* ws, size_t ws_bytes, void* stream) {

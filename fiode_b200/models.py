@@ -139,5 +139,18 @@ class IVP(nn.Module):
         if int_params is None:
             int_params = dict(rtol=self.ode_tol, atol=self.ode_tol)
         static_state, state = self.init_coordinates(x, self.dyn_fun)
-        self.dyn_fun.static_state = static_state
+        dyn = self.dyn_fun
+        if torch.is_grad_enabled() and (static_state.requires_grad or (
+                dyn.training and any(p.requires_grad for p in dyn.parameters()))):
+            # differentiable solve (train_ode pl_modules.py:490-500, PGD :189-199): backward replays the accepted steps
+            from .ode_autograd import OdeSolve
+            p = dict(int_params)
+            assert p.pop('method', 'dopri5') == 'dopri5'
+            lay = (dyn.hidden_to_mlp, dyn.U_x, dyn.mlp_to_mlp, dyn.mlp_to_hidden)
+            Qs = [l.orthogonal_weight_autograd() if dyn.training else l.orthogonal_weight() for l in lay]
+            dyn.static_state = static_state.detach()
+            out = OdeSolve.apply(dyn, state[0], static_state, ts, p['rtol'], p['atol'], p.get('options') or {}, *Qs,
+                                 *[l.bias for l in lay])
+            return (out,)
+        dyn.static_state = static_state
         return odeint(self.h_dot, state, ts, **int_params)

@@ -480,3 +480,76 @@ def runner_up_mask(eta, label, margin):
     mask = torch.empty(N, NH, dtype=torch.uint8, device=eta.device)
     check(lib().fiode_runner_up_mask(ptr(eta), N, int(label), float(margin), ptr(mask), stream_ptr()), 'fiode_runner_up_mask')
     return mask
+
+
+# ---- differentiable solve: right-hand-side VJPs (csrc/ode_bwd.cu) ---------------------------------------
+class RhsEval:
+    """One evaluation of f(h, s) with what its adjoint needs."""
+    __slots__ = ('h', 'f', 'ft', 'mu', 'z1', 'z2', 'dft', 'd2', 'd1')
+
+
+def rhs_fwd_train(dw: DynWeights, h, s):
+    h, s = _f32(h), _f32(s)
+    N = h.shape[0]
+    assert s.shape[0] == N, 'one static-feature row per state row'
+    ev = RhsEval()
+    ev.h = h
+    ev.f, ev.ft = torch.empty_like(h), torch.empty_like(h)
+    ev.mu = torch.empty(N, dtype=torch.float32, device=h.device)
+    ev.z1 = torch.empty(N, 128, dtype=torch.float32, device=h.device)
+    ev.z2 = torch.empty(N, 128, dtype=torch.float32, device=h.device)
+    nb = lib().fiode_rhs_train_workspace_bytes(N)
+    ws = _ws(nb, h.device)
+    check(lib().fiode_rhs_fwd_train(C.byref(dw), ptr(h), ptr(s), N, ptr(ev.f), ptr(ev.ft), ptr(ev.mu), ptr(ev.z1), ptr(ev.z2),
+                                    ptr(ws), nb, stream_ptr()), 'fiode_rhs_fwd_train')
+    return ev
+
+
+def dyn_transposes(dw: DynWeights, device):
+    t = [torch.empty(10, 128, device=device), torch.empty(10, 128, device=device), torch.empty(128, 128, device=device),
+         torch.empty(128, 10, device=device)]
+    check(lib().fiode_dyn_transposes(C.byref(dw), *[ptr(x) for x in t], stream_ptr()), 'fiode_dyn_transposes')
+    return t
+
+
+def rhs_bwd_data(dw: DynWeights, ev: RhsEval, g_f, QT):
+    """g_f -> (g_h, g_s); the layer deltas are stored on ``ev`` for the stacked weight-gradient GEMMs."""
+    g_f = _f32(g_f)
+    N = ev.h.shape[0]
+    dev = ev.h.device
+    ev.dft = torch.empty(N, 10, dtype=torch.float32, device=dev)
+    ev.d2 = torch.empty(N, 128, dtype=torch.float32, device=dev)
+    ev.d1 = torch.empty(N, 128, dtype=torch.float32, device=dev)
+    g_h, g_s = torch.empty(N, 10, dtype=torch.float32, device=dev), torch.empty(N, 10, dtype=torch.float32, device=dev)
+    nb = lib().fiode_rhs_train_workspace_bytes(N)
+    ws = _ws(nb, dev)
+    check(lib().fiode_rhs_bwd_data(C.byref(dw), ptr(ev.h), N, ptr(g_f), ptr(ev.f), ptr(ev.ft), ptr(ev.mu), ptr(ev.z1), ptr(ev.z2),
+                                   ptr(QT[0]), ptr(QT[1]), ptr(QT[2]), ptr(QT[3]), ptr(ev.dft), ptr(ev.d2), ptr(ev.d1),
+                                   ptr(g_h), ptr(g_s), ptr(ws), nb, stream_ptr()), 'fiode_rhs_bwd_data')
+    return g_h, g_s
+
+
+def rhs_bwd_params(h, s, z1, z2, dft, d2, d1):
+    M = h.shape[0]
+    dev = h.device
+    o = dict(Q1=torch.empty(128, 10, device=dev), Qx=torch.empty(128, 10, device=dev), Q2=torch.empty(128, 128, device=dev),
+             Q3=torch.empty(10, 128, device=dev), b1=torch.empty(128, device=dev), b2=torch.empty(128, device=dev),
+             b3=torch.empty(10, device=dev))
+    nb = lib().fiode_rhs_bwd_params_workspace_bytes(M)
+    ws = _ws(nb, dev)
+    check(lib().fiode_rhs_bwd_params(ptr(h), ptr(s), ptr(z1), ptr(z2), ptr(dft), ptr(d2), ptr(d1), M, ptr(o['Q1']), ptr(o['Qx']),
+                                     ptr(o['Q2']), ptr(o['Q3']), ptr(o['b1']), ptr(o['b2']), ptr(o['b3']), ptr(ws), nb,
+                                     stream_ptr()), 'fiode_rhs_bwd_params')
+    return o
+
+
+def lincomb(out, terms):
+    """out = sum c_i x_i for ``terms`` = [(c, x), ...] (at most 8; out may be one of the x)."""
+    n = len(terms)
+    assert 1 <= n <= 8
+    xs = (C.c_void_p * n)(*[t[1].data_ptr() for t in terms])
+    cs = (C.c_float * n)(*[float(t[0]) for t in terms])
+    for _, x in terms:
+        assert x.is_cuda and x.is_contiguous() and x.dtype == torch.float32 and x.numel() == out.numel()
+    check(lib().fiode_lincomb(ptr(out), out.numel(), n, xs, cs, stream_ptr()), 'fiode_lincomb')
+    return out

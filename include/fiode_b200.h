@@ -306,6 +306,25 @@ FIODE_API int fiode_dopri5_simplex_batched(const fiode_dyn_weights* w, const flo
                                  long long max_num_steps, float* out, fiode_solve_stats* stats,
                                  int cluster_size, void* stream);
 
+/* ---- differentiable solve: vector-Jacobian products of the right-hand side -------------------------
+ * The reference back-propagates through torchdiffeq's dopri5 (use_adjoint=False, pl_modules.py:303; train_ode :490-500,
+ * PGD :189-199).  fiode_b200/odeint.py replays the accepted steps the device solver logged and walks them backwards
+ * with these calls (one stage each); the weight gradients of all stages are formed at the end from the stacked deltas.  */
+FIODE_API size_t fiode_rhs_train_workspace_bytes(long long N);
+FIODE_API int fiode_rhs_fwd_train(const fiode_dyn_weights* w, const float* h, const float* s, long long N, float* f,
+                        float* ftilde, float* mu, float* z1, float* z2, void* ws, size_t ws_bytes, void* stream);
+FIODE_API int fiode_dyn_transposes(const fiode_dyn_weights* w, float* Q1T, float* QxT, float* Q2T, float* Q3T, void* stream);
+FIODE_API int fiode_rhs_bwd_data(const fiode_dyn_weights* w, const float* h, long long N, const float* g_f, const float* f,
+                       const float* ftilde, const float* mu, const float* z1, const float* z2, const float* Q1T,
+                       const float* QxT, const float* Q2T, const float* Q3T, float* dft, float* d2, float* d1,
+                       float* g_h, float* g_s, void* ws, size_t ws_bytes, void* stream);
+FIODE_API size_t fiode_rhs_bwd_params_workspace_bytes(long long M);
+FIODE_API int fiode_rhs_bwd_params(const float* h, const float* s, const float* z1, const float* z2, const float* dft,
+                         const float* d2, const float* d1, long long M, float* dQ1, float* dQx, float* dQ2,
+                         float* dQ3, float* db1, float* db2, float* db3, void* ws, size_t ws_bytes, void* stream);
+/* out = sum_i c[i] x[i], n_terms <= 8 (the Runge-Kutta combinations of the replay and of its adjoint). */
+FIODE_API int fiode_lincomb(float* out, long long n, int n_terms, const float* const* x, const float* c, void* stream);
+
 /* ---- interval step after the CROWN bound (robustness/certify_crown.py:139-150) ------------------
  * CROWN itself (auto_LiRPA) stays on the reference; lb <= ftilde <= ub (N,10) are its outputs over [eta-eps, eta+eps].
  * fiode_ibp_sigmoid   : CrownOrthoClassDynProjectSimplexLips.ibp_sigmoid (dynamics/classification.py:175-181)

@@ -148,8 +148,13 @@ def _next_dt(dt, ratio):
     return dt * factor
 
 
-@torch.no_grad()
-def odeint_dopri5(func, y0, t, rtol, atol, max_num_steps=2 ** 31 - 1, return_stats=False):
+def odeint_dopri5(func, y0, t, rtol, atol, max_num_steps=2 ** 31 - 1, return_stats=False, differentiable=False):
+    """``differentiable=True`` keeps the autograd graph of the accepted stages (torchdiffeq's use_adjoint=False behaviour)."""
+    with torch.set_grad_enabled(bool(differentiable) and torch.is_grad_enabled()):
+        return _odeint_dopri5(func, y0, t, rtol, atol, max_num_steps, return_stats)
+
+
+def _odeint_dopri5(func, y0, t, rtol, atol, max_num_steps=2 ** 31 - 1, return_stats=False):
     """func(t, y) -> dy/dt with y a Tensor or a tuple of Tensors (then func returns a
     Tensor/tuple of the same total size).  Returns (len(t), *y0.shape) (tuple-wrapped
     if y0 was a tuple).  Raises AssertionError exactly where torchdiffeq does."""
@@ -180,7 +185,9 @@ def odeint_dopri5(func, y0, t, rtol, atol, max_num_steps=2 ** 31 - 1, return_sta
     y, tcur = flat0, t[0]
     fcur = f(tcur, y)
     stats.nfe += 1
-    dt = _initial_step(f, tcur, y, fcur, rtol_t, atol_t, stats)
+    # torchdiffeq's step-size heuristics run under torch.no_grad (misc._select_initial_step / _optimal_step_size): the
+    # step sizes are constants of the autograd graph, gradients flow through the accepted stages only
+    dt = _initial_step(f, tcur, y.detach(), fcur.detach(), rtol_t, atol_t, stats).detach()
     t_left = tcur
     coef = [y] * 5
     sol = [flat0]
@@ -200,7 +207,7 @@ def odeint_dopri5(func, y0, t, rtol, atol, max_num_steps=2 ** 31 - 1, return_sta
                 stats.n_accept += 1
             else:
                 stats.n_reject += 1
-            dt = _next_dt(dt, ratio)
+            dt = _next_dt(dt, ratio.detach())
             nsteps += 1
         sol.append(_interp_eval(coef, t_left, tcur, t[i]))
     stats.t_final = float(tcur)
