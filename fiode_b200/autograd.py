@@ -95,3 +95,16 @@ class GroupSortFn(Function):
     def backward(ctx, gy):
         (x,) = ctx.saved_tensors
         return ops.group_sort_bwd(x, gy)
+
+
+class NormalizeFn(Function):
+    """Normalize.forward (models.py:23-26); backward g / std (the PGD attack of validation_step differentiates w.r.t. x)."""
+    @staticmethod
+    def forward(ctx, x, mu, std):
+        ctx.save_for_backward(std)
+        return ops.normalize(x, mu, std)
+
+    @staticmethod
+    def backward(ctx, g):
+        (std,) = ctx.saved_tensors
+        return ops.normalize(g, torch.zeros_like(std), std), None, None

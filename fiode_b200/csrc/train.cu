@@ -311,7 +311,15 @@ extern "C" int fiode_cayley_conv_layer_bwd(const float* x, const float* Qf, cons
     if (gx) {
         conv_bwd_data_kernel<<<nblocks((size_t)B * cin * F), 256, 0, st>>>(reinterpret_cast<const float2*>(Qf), GYf, B, cin, cout, F, GXf);
         count_launch(1);
-        if ((rc = launch_irfft2(GXf, B, cin, n, nullptr, 0, gx, st, false))) return rc;
+        // no bias, no GroupSort: the channel index is irrelevant to the inverse FFT, so a channel count the kernel does not
+        // tile (the 3-channel input layer) is regrouped as (B * cin / CH) images of CH channels
+        const int CH = n == 32 ? 8 : 16;
+        int Bv = B, Cv = cin;
+        if (cin % CH) {
+            if (((long long)B * cin) % CH) { set_error("fiode_cayley_conv_layer_bwd: B * cin = %d * %d is not a multiple of %d", B, cin, CH); return -1; }
+            Bv = B * cin / CH; Cv = CH;
+        }
+        if ((rc = launch_irfft2(GXf, Bv, Cv, n, nullptr, 0, gx, st, false))) return rc;
     }
     if (gb) {
         bias_grad_kernel<<<cout, 256, 0, st>>>(gy, B, cout, n * n, gb);

@@ -19,9 +19,11 @@ from . import autograd as ag
 
 
 def _differentiable(module, x):
-    """The reference's graph reaches the weights only in train mode (layers.py:103-105); mirror that."""
-    return module.training and torch.is_grad_enabled() and (
-        x.requires_grad or any(p.requires_grad for p in module.parameters(recurse=False)))
+    """The reference's graph reaches the weights only in train mode (layers.py:103-105: eval uses Q.detach()); the input
+    gradient (PGD in validation_step, pl_modules.py:189-199) flows in either mode."""
+    if not torch.is_grad_enabled():
+        return False
+    return x.requires_grad or (module.training and any(p.requires_grad for p in module.parameters(recurse=False)))
 
 
 def cayley(W):
@@ -73,7 +75,8 @@ class CayleyLinear(nn.Linear):
 
     def forward(self, X, group_sort=False):
         if _differentiable(self, X):
-            y = ag.Linear.apply(X, self.orthogonal_weight_autograd(), self.bias)
+            Q = self.orthogonal_weight_autograd() if self.training else self.orthogonal_weight()
+            y = ag.Linear.apply(X, Q, self.bias)
             return ag.GroupSortFn.apply(y) if group_sort else y
         return ops.linear_fwd(X, self.orthogonal_weight(), self.bias, group_sort)
 
@@ -111,7 +114,7 @@ class CayleyConv(nn.Conv2d):
         if _differentiable(self, x):
             if self.alpha is None:
                 self.alpha = nn.Parameter(ops.conv_alpha_init(self.weight, n))
-            Qf = ag.CayleyConvQ.apply(self.weight, self.alpha, n)
+            Qf = ag.CayleyConvQ.apply(self.weight, self.alpha, n) if self.training else self.orthogonal_spectrum(n)
             y = (ag.Conv1x1S2d if self.striding else ag.CayleyConvLayer).apply(x, Qf, self.bias)
             return ag.GroupSortFn.apply(y) if group_sort else y
         Qf = self.orthogonal_spectrum(n)

@@ -74,9 +74,12 @@ class ParamMap(nn.Sequential):
         return bw, t
 
     def forward(self, x):
-        if self.training and torch.is_grad_enabled() and any(p.requires_grad for p in self.parameters()):
-            # training: layer by layer through fiode_b200.autograd so that loss.backward() reaches every weight
-            return self[1](ops.normalize(x, self[0].mu, self[0].std))
+        if torch.is_grad_enabled() and (x.requires_grad or (self.training and any(p.requires_grad for p in self.parameters()))):
+            # layer by layer through fiode_b200.autograd: loss.backward() reaches every weight (train mode) and / or the input
+            from .autograd import NormalizeFn
+            xn = NormalizeFn.apply(x, self[0].mu.reshape(-1), self[0].std.reshape(-1)) if x.requires_grad else \
+                ops.normalize(x, self[0].mu, self[0].std)
+            return self[1](xn)
         assert self[1].out_dim == 10
         bw, keep = self.backbone_weights()
         return ops.backbone_fwd(bw, x, keep)

@@ -88,7 +88,7 @@ def test_conv1x1_s2d_bwd(cin, cout, n):
 @pytest.mark.parametrize('cin,cout,n', [(3, 32, 32), (32, 64, 16)])
 def test_cayley_conv_layer_bwd(cin, cout, n):
     from fiode_b200 import ops
-    B = 5
+    B = 8
     F = n * (n // 2 + 1)
     w = randn(cout, cin, 3, 3, seed=5, scale=(cin * 9) ** -0.5)
     Qf = ol.cayley_conv_Q(w, torch.tensor(ol.conv_alpha_init(w, n)), n).detach()
@@ -99,7 +99,7 @@ def test_cayley_conv_layer_bwd(cin, cout, n):
     yf = (torch.complex(Qr, Qi) @ xf).reshape(n, n // 2 + 1, cout, B)
     y = torch.fft.irfft2(yf.permute(3, 2, 0, 1)) + bc[:, None, None]
     (y * gy).sum().backward()
-    need_gx = cin != 3                                         # the 3-channel input layer has no data gradient path (C % 16)
+    need_gx = True                                             # cin = 3: regrouped as (B * 3 / 8) x 8 channel-images
     gx, gQ, gb = ops.cayley_conv_layer_bwd(x.to(DEV), Qf.to(DEV), gy.to(DEV), need_gx=need_gx)
     assert rel(gQ.real, Qr.grad) < 1e-4 and rel(gQ.imag, Qi.grad) < 1e-4 and rel(gb, bc.grad) < 1e-4
     if need_gx:
@@ -245,3 +245,57 @@ def test_differentiable_solve_matches_autograd_through_oracle_solver(sd, scale_n
         elif a.numel() > 1:
             cos = float(torch.nn.functional.cosine_similarity(a, b, dim=0))
             assert cos > 0.95 and 0.7 < float(a.norm() / b.norm()) < 1.4, (k, cos, float(a.norm() / b.norm()))
+
+
+def test_train_ode_loss_backward_end_to_end(sd):
+    """train_ode (pl_modules.py:490-500): nll_loss(log(IVP(x)), y).backward() in train mode reaches all 33 parameters through the
+    differentiable solve and the backbone adjoints; compared with autograd through the oracle (backbone + restated solver)."""
+    from oracle import dynamics as od, dopri5 as odp
+    B, tol = 8, 1e-3
+    x, y = fx.synth_images(B), fx.synth_labels(B)
+    ts = torch.linspace(0., 1., 2)
+    cfg = fx.dyn_cfg(scale_nominal=True)
+    sdc = {k: (v.clone().requires_grad_(True) if v.is_floating_point() and v.dim() <= 4 and any(t in k for t in ('weight', 'bias', 'alpha'))
+               else v) for k, v in sd.items()}
+    s_ref = ol.backbone_forward(x, sdc, PM)
+    f = lambda t, hh: od.eval_dot(hh, s_ref, sdc, cfg, None, fx.DYN, differentiable=True)
+    sol = odp.odeint_dopri5(f, torch.full((B, 10), 0.1), ts, tol, tol, differentiable=True)
+    loss_ref = torch.nn.functional.nll_loss(torch.log(sol[-1]), y)
+    loss_ref.backward()
+
+    ivp = fx.build_b200_model(sd, scale_nominal=True, dropout=0.0).train()
+    out = ivp(x.cuda(), ts=ts, int_params=dict(method='dopri5', rtol=tol, atol=tol))
+    loss = torch.nn.functional.nll_loss(torch.log(out), y.cuda())
+    assert abs(float(loss.detach()) - float(loss_ref.detach())) < 1e-4
+    loss.backward()
+    named = dict(ivp.named_parameters())
+    assert len(named) == 33 and all(p.grad is not None for p in named.values())
+    bad = {}
+    for k, p in named.items():
+        want = sdc['model.' + k].grad
+        r = rel(p.grad.reshape(want.shape), want)
+        if r > 1e-2:
+            bad[k] = r
+    assert not bad, bad
+
+
+def test_input_gradient_for_pgd(sd):
+    """validation_step's PGD (pl_modules.py:189-199) differentiates the eval-mode network w.r.t. the input image: backbone data
+    adjoints (incl. the 3-channel first layer and Normalize) + differentiable solve, no weight gradients."""
+    from oracle import dynamics as od, dopri5 as odp
+    B, tol = 8, 1e-3
+    x, y = fx.synth_images(B), fx.synth_labels(B)
+    ts = torch.linspace(0., 1., 2)
+    cfg = fx.dyn_cfg(scale_nominal=True)
+    xr = x.clone().requires_grad_(True)
+    s_ref = ol.backbone_forward(xr, sd, PM)
+    f = lambda t, hh: od.eval_dot(hh, s_ref, sd, cfg, None, fx.DYN, differentiable=True)
+    sol = odp.odeint_dopri5(f, torch.full((B, 10), 0.1), ts, tol, tol, differentiable=True)
+    torch.nn.functional.nll_loss(torch.log(sol[-1]), y).backward()
+    ivp = fx.build_b200_model(sd, scale_nominal=True).eval()
+    xd = x.cuda().requires_grad_(True)
+    out = ivp(xd, ts=ts, int_params=dict(method='dopri5', rtol=tol, atol=tol))
+    torch.nn.functional.nll_loss(torch.log(out), y.cuda()).backward()
+    # (eval mode detaches the cached Q only, layers.py:105; biases still receive gradients there as here)
+    assert ivp.dyn_fun.mlp_to_mlp.weight.grad is None
+    assert rel(xd.grad, xr.grad) < 1e-2, rel(xd.grad, xr.grad)
