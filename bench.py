@@ -301,12 +301,12 @@ STAGES = [
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of one 4096-image slab
 # (profiles/r01c_ncu_full_summary.md; re-measure when a kernel changes).  Keyed by the kernel named in STAGES / the solver.
 NCU_TRAFFIC_BYTES = {
-    'rfft2_kernel<32>': 50.41e6 + 3.33e6,
-    'irfft32_mix3_kernel': 54.27e6 + 477.67e6,
-    'gemm_tc_kernel<s2d,32>': 536.93e6 + 114.61e6,
-    'rfft2_kernel<16,fm>': 134.24e6 + 101.42e6,
-    'irfft2_kernel<16,fm>': 302.01e6 + 227.90e6,
-    'gemm_tc_kernel<s2d,64>': 268.55e6 + 45.70e6,
+    'rfft2_kernel<32>': 50.42e6 + 4.57e6,
+    'irfft32_mix3_kernel': 54.04e6 + 478.27e6,
+    'gemm_tc_kernel<s2d,32>': 536.93e6 + 116.05e6,
+    'rfft2_kernel<16,fm>': 134.24e6 + 100.99e6,
+    'irfft2_kernel<16,fm>': 302.11e6 + 228.70e6,
+    'gemm_tc_kernel<s2d,64>': 268.59e6 + 45.88e6,
     'dopri5_simplex_batched_kernel': 0.60e6,
 }
 
@@ -363,7 +363,7 @@ def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
         rf = dict(bound='hbm', achieved=top['gbs'], peak=pk['hbm'], unit='GB/s', frac=top['gbs'] / pk['hbm'])
     else:
         rf = dict(bound='tensor', achieved=top['tflops'], peak=pk['bf16'], unit='TFLOP/s', frac=top['tflops'] / pk['bf16'])
-    rf.update(traffic=NCU_TRAFFIC_BYTES.get(top['kernel']), traffic_source='profiles/r01c_ncu_full_summary.md (one 4096-image slab)',
+    rf.update(traffic=NCU_TRAFFIC_BYTES.get(top['kernel']), traffic_source='profiles/r01d_ncu_full_summary.md (one 4096-image slab; dopri5 at 16 solves)',
               kernel=top['kernel'], stage=top['stage'], ms_per_launch=top['ms'], peak_source=pk['source'],
               note='algorithmic bytes / flops of SURVEY 8(d) over the CUDA-event time of that launch; tensor-core stages run the '
                    'fp16x2-split FP32 emulation (3 MMAs per product), so their ceiling is peak / 3; see DESIGN.md section 4',
