@@ -314,7 +314,7 @@ NCU_TRAFFIC_BYTES = {
 def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
     """Device time of every kernel stage of one step (backbone over G*256 images, then the G-solve dopri5 launch),
     CUDA events on the launching stream, averaged over ``iters`` runs on rotating (> L2) inputs; the `roofline`
-    object describes the stage with the longest launch."""
+    object describes the kernel with the largest share of the step (launch time x launches per step)."""
     import ctypes
     from fiode_b200 import ops
     from fiode_b200._lib import lib
@@ -322,7 +322,7 @@ def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
     n_img = G * B
     pm = ivp.init_coordinates.param_map
     bw, keep = pm.backbone_weights()
-    n_stage = min(n_img, 4096)                 # the stage events describe ONE slab (4096 images) of the backbone
+    n_stage = min(n_img, L.fiode_backbone_slab_images())   # the stage events describe ONE slab of the backbone
     xs = [x.reshape(n_img, 3, 32, 32)[:n_stage] for x in x_dev]
     acc = [0.0] * len(STAGES)
     buf = (ctypes.c_float * 16)()
@@ -343,10 +343,11 @@ def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
     res = ops.dopri5_simplex_batched(dw, h0, s, G, t_dev, TOL, TOL, cluster_size=cluster_size)
     st = res.stats()[0]
     ms_solve = timed(lambda: ops.dopri5_simplex_batched(dw, h0, s, G, t_dev, TOL, TOL, cluster_size=cluster_size), iters) / iters
+    n_slabs = -(-n_img // n_stage)              # backbone launches per step (one per slab)
     ridge = pk['bf16'] * 1e12 / 3 / (pk['hbm'] * 1e9)      # flop/byte above which the 3-MMA emulation is tensor-bound
     stages = []
     for (name, kern, by, fl), ms in zip(STAGES, acc):
-        d = dict(stage=name, kernel=kern, ms=ms)
+        d = dict(stage=name, kernel=kern, ms=ms, launches_per_step=n_slabs, ms_per_step=ms * n_slabs)
         if by:
             d.update(gbs=by * n_stage / (ms * 1e-3) / 1e9 if ms > 0 else None, tflops=fl * n_stage / (ms * 1e-3) / 1e12 if ms > 0 else None,
                      bound='tensor' if fl / by > ridge else 'hbm')
@@ -354,17 +355,20 @@ def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
         stages.append(d)
     solve_flop = sum(x.nfe for x in res.stats()) * RHS_FLOP * B
     stages.append(dict(stage=f'dopri5, {G} solves x {B} rows (cluster per solve)', kernel='dopri5_simplex_batched_kernel',
-                       ms=ms_solve, tflops=solve_flop / (ms_solve * 1e-3) / 1e12, bound='latency',
+                       ms=ms_solve, launches_per_step=1, ms_per_step=ms_solve, tflops=solve_flop / (ms_solve * 1e-3) / 1e12, bound='latency',
                        note='%d dependent RHS evaluations per solve, %d rows per CTA: FP32 FFMA, latency-bound' % (st.nfe, B // max(cluster_size, 1) if cluster_size else 32)))
     ms_bb = sum(acc)
     bb_bytes = sum(x[2] for x in STAGES) * n_stage
-    top = max((d for d in stages if 'tflops' in d or 'gbs' in d), key=lambda d: d['ms'])
+    top = max((d for d in stages if 'tflops' in d or 'gbs' in d), key=lambda d: d['ms_per_step'])    # dominant = largest share of the step
     if top.get('bound') == 'hbm':
         rf = dict(bound='hbm', achieved=top['gbs'], peak=pk['hbm'], unit='GB/s', frac=top['gbs'] / pk['hbm'])
     else:
         rf = dict(bound='tensor', achieved=top['tflops'], peak=pk['bf16'], unit='TFLOP/s', frac=top['tflops'] / pk['bf16'])
-    rf.update(traffic=NCU_TRAFFIC_BYTES.get(top['kernel']), traffic_source='profiles/r01d_ncu_full_summary.md (one 4096-image slab; dopri5 at 16 solves)',
-              kernel=top['kernel'], stage=top['stage'], ms_per_launch=top['ms'], peak_source=pk['source'],
+    traffic = NCU_TRAFFIC_BYTES.get(top['kernel'])
+    if traffic and top['kernel'] != 'dopri5_simplex_batched_kernel':
+        traffic *= n_stage / 4096.             # the capture ran one 4096-image launch; these kernels stream, bytes scale with images
+    rf.update(traffic=traffic, traffic_source='profiles/r01d_ncu_full_summary.md (4096-image launch, scaled to the %d images of this launch)' % n_stage,
+              kernel=top['kernel'], stage=top['stage'], ms_per_launch=top['ms'], launches_per_step=top['launches_per_step'], peak_source=pk['source'],
               note='algorithmic bytes / flops of SURVEY 8(d) over the CUDA-event time of that launch; tensor-core stages run the '
                    'fp16x2-split FP32 emulation (3 MMAs per product), so their ceiling is peak / 3; see DESIGN.md section 4',
               parts=dict(backbone_ms=ms_bb, backbone_images=n_stage, backbone_algorithmic_gbs=bb_bytes / (ms_bb * 1e-3) / 1e9,
@@ -386,13 +390,25 @@ def run_b200(args):
     device = torch.device('cuda', local)
     if world > 1:
         dist.init_process_group('nccl', device_id=device)
+    # pinned host buffers on the GPU's own NUMA node: bind this process to the device's CPU set while they are
+    # allocated and while the GPU is driven; the CPU baseline later gets all cores back
+    all_cpus = os.sched_getaffinity(0)
+    numa = None
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByUUID('GPU-' + str(torch.cuda.get_device_properties(local).uuid))
+        pynvml.nvmlDeviceSetCpuAffinity(h)
+        numa = len(os.sched_getaffinity(0))
+    except Exception as e:           # affinity is an optimisation only
+        numa = repr(e)
     pk = peaks()
     CS = args.cluster_size
     G = args.solves_per_step
     if G <= 0:
         # one wave of the cluster-per-solve launch: every solve beyond the co-resident count waits a full solve latency
         G = ops.dopri5_max_concurrent_solves(B, CS)
-        G = G - G % 16 if G >= 16 else G          # whole backbone slabs (4096 images = 16 batches)
+        G = G - G % 16 if G >= 16 else G          # a multiple of 16 batches (4096 images)
     ivp = build_model(device)
     ts = torch.linspace(0., T_MAX, 2)
     int_params = dict(method='dopri5', rtol=TOL, atol=TOL, options=dict(check=False, cluster_size=CS))
@@ -444,40 +460,47 @@ def run_b200(args):
     # caller feeding batches from a loader would drive the API; each step still ends with its result on the host.
     copy_stream = torch.cuda.Stream(device=device)
     main_stream = torch.cuda.current_stream(device)
-    xe = [torch.empty_like(x_dev[0]) for _ in range(2)]
     ready = [torch.cuda.Event() for _ in range(2)]
     consumed = [torch.cuda.Event() for _ in range(2)]
 
-    def prefetch(i):
-        with torch.cuda.stream(copy_stream):
-            copy_stream.wait_event(consumed[i % 2])
-            xe[i % 2].copy_(x_host[i % len(x_host)], non_blocking=True)
-            ready[i % 2].record(copy_stream)
+    def e2e_measure(hosts):
+        """whole-job solves/s with `hosts` (pinned host tensors) as each step's input"""
+        xe = [torch.empty(hosts[0].shape, dtype=hosts[0].dtype, device=device) for _ in range(2)]
 
-    def e2e_run(n):
-        for k in range(2):
-            consumed[k].record(main_stream)
-        prefetch(0)
-        for i in range(n):
-            if i + 1 < n:
-                prefetch(i + 1)
-            main_stream.wait_event(ready[i % 2])
-            step(xe[i % 2], y_dev)
-            consumed[i % 2].record(main_stream)
-            y_host.copy_(y_dev, non_blocking=True)
-            main_stream.synchronize()                  # the caller needs this step's result on the host
+        def prefetch(i):
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(consumed[i % 2])
+                xe[i % 2].copy_(hosts[i % len(hosts)], non_blocking=True)
+                ready[i % 2].record(copy_stream)
 
-    e2e_run(max(2, args.warmup // 2))
-    barrier()
-    e0.record()
-    e2e_run(args.steps)
-    e1.record()
-    torch.cuda.synchronize()
-    e2e_ms = e0.elapsed_time(e1)
-    t = torch.tensor([e2e_ms], device=device)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = world * G * args.steps / (float(t.item()) * 1e-3)
+        def e2e_run(n):
+            for k in range(2):
+                consumed[k].record(main_stream)
+            prefetch(0)
+            for i in range(n):
+                if i + 1 < n:
+                    prefetch(i + 1)
+                main_stream.wait_event(ready[i % 2])
+                step(xe[i % 2], y_dev)
+                consumed[i % 2].record(main_stream)
+                y_host.copy_(y_dev, non_blocking=True)
+                main_stream.synchronize()                  # the caller needs this step's result on the host
+
+        e2e_run(max(2, args.warmup // 2))
+        barrier()
+        e0.record()
+        e2e_run(args.steps)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device=device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return world * G * args.steps / (float(t.item()) * 1e-3)
+
+    e2e_value = e2e_measure(x_host)
+    # the same call on the dataset's own 8-bit pixels (ToTensor's / 255 runs inside the first kernel): a quarter of the bytes
+    x_host_u8 = [torch.randint(0, 256, (G, B, 3, 32, 32), dtype=torch.uint8, generator=gen).pin_memory() for _ in range(2)]
+    e2e_u8_value = e2e_measure(x_host_u8)
 
     cert = None
     if not args.no_certify:
@@ -497,6 +520,7 @@ def run_b200(args):
             dist.destroy_process_group()
         return
 
+    os.sched_setaffinity(0, all_cpus)
     # ---- per-kernel device times (CUDA events on the launching stream) and the roofline of the dominant kernel ----
     roofline = stage_roofline(ivp, x_dev, G, ts, pk, cluster_size=CS)
 
@@ -522,9 +546,12 @@ def run_b200(args):
                 config=dict(workload='cifar_cayley_node_inference_dopri5_b256_tol1e-3_tmax1', batch=B,
                             solves_per_step=G, dopri5_cluster_size=CS, images_per_step=G * B, rtol=TOL, atol=TOL, t_max=T_MAX,
                             weights='random init, seed 0', l2='inputs rotate over %d device buffers (%.0f MB > L2)' % (
-                                NBUF, NBUF * per_set / 1e6), parallelism=f'independent batches x{world}'),
+                                NBUF, NBUF * per_set / 1e6), parallelism=f'independent batches x{world}', host_cpus_bound_to_gpu_numa=numa),
                 images_per_s=value * B,
-                e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=per_set, d2h_bytes_per_step=G * B * 10 * 4),
+                e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=per_set, d2h_bytes_per_step=G * B * 10 * 4,
+                         input='float32 images in pinned host memory (the argument of model.forward)'),
+                e2e_u8_pixels=dict(value=e2e_u8_value, unit=UNIT, h2d_bytes_per_step=per_set // 4, d2h_bytes_per_step=G * B * 10 * 4,
+                                   input='uint8 pixels in pinned host memory; ToTensor (/255) fused into the first kernel, same bits'),
                 gpu_launches=launches, clocks=clocks, roofline=roofline, cpu_baseline=cpu, certify=cert, fi_step=fi)
     print(json.dumps(line))
     if world > 1:

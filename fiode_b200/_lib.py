@@ -27,7 +27,7 @@ class DynWeights(C.Structure):
 
 class BackboneWeights(C.Structure):
     _fields_ = [(n, P) for n in ('mu', 'std', 'Qf0', 'b0', 'Q2', 'b2', 'Qf4', 'b4', 'Q6', 'b6',
-                                 'Q9', 'b9', 'Q11', 'b11', 'Qfc', 'bfc')]
+                                 'Q9', 'b9', 'Q11', 'b11', 'Qfc', 'bfc', 'packed')]
 
 
 class SolveStats(C.Structure):
@@ -52,7 +52,11 @@ SIGNATURES = {
     'fiode_cayley_conv_workspace_bytes': (SZ, [I, I, I, I]),
     'fiode_cayley_conv': (I, [P, P, I, I, I, I, P, P, SZ, P]),
     'fiode_backbone_workspace_bytes': (SZ, [I]),
+    'fiode_backbone_slab_images': (I, []),
+    'fiode_backbone_packed_bytes': (SZ, []),
+    'fiode_backbone_pack': (I, [C.POINTER(BackboneWeights), P, SZ, P]),
     'fiode_backbone_fwd': (I, [C.POINTER(BackboneWeights), P, I, P, P, SZ, P]),
+    'fiode_backbone_fwd_u8': (I, [C.POINTER(BackboneWeights), P, I, P, P, SZ, P]),
     'fiode_backbone_enable_stage_timing': (None, [I]),
     'fiode_backbone_stage_times': (I, [P, I]),
     'fiode_cayley_conv_fwd_workspace_bytes': (SZ, [I, I, I, I]),

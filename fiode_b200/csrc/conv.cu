@@ -28,7 +28,8 @@ template <int n> struct FftCfg {
 
 // FM ("frequency-major"): the spectrum is written as Xt[phi][b][c] instead of torch's [b][c][phi], so that the channel
 // mixing of one frequency is a plain row-major (batch x 2C) GEMM operand for the tensor-core kernel (gemm_tc.cu).
-template <int n, bool FM>
+// U8: x holds 8-bit pixels; the load applies torchvision's ToTensor (float(p) / 255, IEEE division) before Normalize.
+template <int n, bool FM, bool U8 = false>
 __global__ void __launch_bounds__(128) rfft2_kernel(const float* __restrict__ x, int n_img, int C,
                                                     const float* __restrict__ mu, const float* __restrict__ sd,
                                                     float2* __restrict__ Xf) {
@@ -44,10 +45,16 @@ __global__ void __launch_bounds__(128) rfft2_kernel(const float* __restrict__ x,
         float m = 0.f, inv = 1.f;
         if (mu) { const int c = img % C; m = mu[c]; inv = sd[c]; }
         const float4* src = reinterpret_cast<const float4*>(x + ((size_t)img * n + 2 * p) * n);
+        const uchar4* src8 = reinterpret_cast<const uchar4*>(reinterpret_cast<const unsigned char*>(x) + ((size_t)img * n + 2 * p) * n);
         float2 z[n];
 #pragma unroll
         for (int q = 0; q < n / 4; ++q) {
-            const float4 a = src[q], b = src[n / 4 + q];
+            float4 a, b;
+            if (U8) {
+                const uchar4 ua = src8[q], ub = src8[n / 4 + q];
+                a = make_float4(__fdiv_rn((float)ua.x, 255.f), __fdiv_rn((float)ua.y, 255.f), __fdiv_rn((float)ua.z, 255.f), __fdiv_rn((float)ua.w, 255.f));
+                b = make_float4(__fdiv_rn((float)ub.x, 255.f), __fdiv_rn((float)ub.y, 255.f), __fdiv_rn((float)ub.z, 255.f), __fdiv_rn((float)ub.w, 255.f));
+            } else { a = src[q]; b = src[n / 4 + q]; }
             if (mu) {   // models.py:23-26 Normalize: (x - mu) / std
                 z[4 * q + 0] = make_float2((a.x - m) / inv, (b.x - m) / inv);
                 z[4 * q + 1] = make_float2((a.y - m) / inv, (b.y - m) / inv);
@@ -341,16 +348,22 @@ static int mix3_images_per_cta() {
     static int v = [] { const char* e = getenv("FIODE_MIX3_IM"); const int x = e ? atoi(e) : 2; return x == 1 ? 1 : 2; }();
     return v;
 }
-// Qt: workspace of F * cout * 3 float2
+int launch_transpose_q(const float2* Qf, int F, int CC, float2* Qt, cudaStream_t st) {
+    transpose_q_kernel<<<(F * CC + 255) / 256, 256, 0, st>>>(Qf, F, CC, Qt);
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(1);
+    return 0;
+}
+// Qt: F * cout * 3 float2, filled here from Qf; Qf == nullptr means Qt already holds the transposed spectrum
 int launch_irfft32_mix3(const float2* Xf, const float2* Qf, float2* Qt, int B, int C, const float* bias, int gs, float* y,
                         cudaStream_t st) {
     constexpr int F = 544;
     if (C % 8) { set_error("irfft32_mix3: C=%d", C); return -1; }
-    transpose_q_kernel<<<(F * C * 3 + 255) / 256, 256, 0, st>>>(Qf, F, C * 3, Qt);
+    if (Qf) transpose_q_kernel<<<(F * C * 3 + 255) / 256, 256, 0, st>>>(Qf, F, C * 3, Qt);
     const int rc = mix3_images_per_cta() == 1 ? launch_irfft32_mix3_t<1>(Xf, Qt, B, C, bias, gs, y, st)
                                               : launch_irfft32_mix3_t<2>(Xf, Qt, B, C, bias, gs, y, st);
     if (rc) return rc;
-    count_launch(2);
+    count_launch(Qf ? 2 : 1);
     return 0;
 }
 
@@ -518,8 +531,10 @@ __global__ void group_sort_kernel(const float* __restrict__ x, int B, int C, int
 
 // host-side dispatch helpers used by backbone.cu too
 int launch_rfft2(const float* x, int n_img, int C, int n, const float* mu, const float* sd, float2* Xf, cudaStream_t st,
-                 bool freq_major) {
-    if (n == 32 && !freq_major) rfft2_kernel<32, false><<<(n_img + FftCfg<32>::CH - 1) / FftCfg<32>::CH, 128, 0, st>>>(x, n_img, C, mu, sd, Xf);
+                 bool freq_major, bool x_u8 = false) {
+    if (x_u8 && !(n == 32 && !freq_major)) { set_error("rfft2: 8-bit input only for the 32x32 image layer"); return -1; }
+    if (x_u8) rfft2_kernel<32, false, true><<<(n_img + FftCfg<32>::CH - 1) / FftCfg<32>::CH, 128, 0, st>>>(x, n_img, C, mu, sd, Xf);
+    else if (n == 32 && !freq_major) rfft2_kernel<32, false><<<(n_img + FftCfg<32>::CH - 1) / FftCfg<32>::CH, 128, 0, st>>>(x, n_img, C, mu, sd, Xf);
     else if (n == 16 && !freq_major) rfft2_kernel<16, false><<<(n_img + FftCfg<16>::CH - 1) / FftCfg<16>::CH, 128, 0, st>>>(x, n_img, C, mu, sd, Xf);
     else if (n == 16 && C % FftCfg<16>::CH == 0) rfft2_kernel<16, true><<<(n_img + FftCfg<16>::CH - 1) / FftCfg<16>::CH, 128, 0, st>>>(x, n_img, C, mu, sd, Xf);
     else { set_error("rfft2: unsupported n=%d (16 or 32), freq_major=%d", n, (int)freq_major); return -1; }

@@ -71,6 +71,14 @@ class ParamMap(nn.Sequential):
                  Qfc=net.fc.orthogonal_weight(), bfc=net.fc.bias)
         t = {k: v.detach().float().contiguous() for k, v in t.items()}
         bw = BackboneWeights(**{k: ptr(v) for k, v in t.items()})
+        # kernel-ready copies (tensor-core tiles, transposed spectrum) live as long as the cached Q's they were made
+        # from -- the reference's eval-mode `self.Q` reuse (layers.py:77-83, 95-103) carried one step further
+        key = tuple(m[i]._q_key for i in (0, 2, 4, 6, 9, 11)) + tuple(t[k].data_ptr() for k in ('Qf0', 'Q2', 'Qf4', 'Q6', 'Q9', 'Q11'))
+        if getattr(self, '_packed_key', None) != key:
+            self._packed = ops.backbone_pack(bw, t['Q9'].device)
+            self._packed_key = key
+        bw.packed = ptr(self._packed)
+        t['packed'] = self._packed
         return bw, t
 
     def forward(self, x):

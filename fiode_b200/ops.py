@@ -117,15 +117,26 @@ def group_sort(x):
     return y
 
 
+def backbone_pack(bw: BackboneWeights, device):
+    """Kernel-ready copies of the prepared backbone matrices (fiode_backbone_pack); pass the block as ``bw.packed``."""
+    nb = lib().fiode_backbone_packed_bytes()
+    blk = torch.empty(nb, dtype=torch.uint8, device=device)
+    check(lib().fiode_backbone_pack(C.byref(bw), ptr(blk), nb, stream_ptr()), 'fiode_backbone_pack')
+    return blk
+
+
 def backbone_fwd(bw: BackboneWeights, x, keep=()):
     """s = param_map(x) for the CIFAR KWLarge_Concat backbone.  ``keep`` holds the tensors the struct
-    points into (so they outlive the asynchronous launch)."""
-    x = _f32(x)
+    points into (so they outlive the asynchronous launch).  x: float32 in [0, 1], or the dataset's uint8 pixels
+    (ToTensor's / 255 then happens inside the first kernel; same bits as the float call on x / 255)."""
+    u8 = x.dtype == torch.uint8
+    x = x.contiguous() if u8 else _f32(x)
     B = x.shape[0]
     s = torch.empty(B, NH, dtype=torch.float32, device=x.device)
     nb = lib().fiode_backbone_workspace_bytes(B)
     ws = _ws(nb, x.device)
-    check(lib().fiode_backbone_fwd(C.byref(bw), ptr(x), B, ptr(s), ptr(ws), nb, stream_ptr()), 'fiode_backbone_fwd')
+    fn = lib().fiode_backbone_fwd_u8 if u8 else lib().fiode_backbone_fwd
+    check(fn(C.byref(bw), ptr(x), B, ptr(s), ptr(ws), nb, stream_ptr()), 'fiode_backbone_fwd')
     return s
 
 

@@ -78,11 +78,25 @@ typedef struct fiode_backbone_weights {
     const float* b11;  /* (512) */
     const float* Qfc;  /* (10, 512) */
     const float* bfc;  /* (10) */
+    const void* packed; /* NULL, or a block filled by fiode_backbone_pack for THESE weights: skips the per-call packing */
 } fiode_backbone_weights;
 FIODE_API size_t fiode_backbone_workspace_bytes(int B);
+/* Kernel-ready copies of the prepared matrices (fp16x2-split tensor-core tiles, model.4's spectrum as real matrices,
+ * model.0's transposed spectrum).  The reference caches Q per weight version in eval mode (layers.py:77-83,
+ * 95-103: `self.Q` reused while not training); a caller that does the same keeps one block per weight version and
+ * sets `packed`, so that a forward pass launches no weight preparation at all.                                   */
+/* images per internal slab of fiode_backbone_fwd (each kernel of the chain is launched once per slab) */
+FIODE_API int fiode_backbone_slab_images(void);
+FIODE_API size_t fiode_backbone_packed_bytes(void);
+FIODE_API int fiode_backbone_pack(const fiode_backbone_weights* w, void* packed, size_t packed_bytes, void* stream);
 /* x: (B,3,32,32) in [0,1]; s_out: (B,10) */
 FIODE_API int fiode_backbone_fwd(const fiode_backbone_weights* w, const float* x, int B, float* s_out,
                        void* ws, size_t ws_bytes, void* stream);
+/* Same, on the dataset's own 8-bit pixels: x (B,3,32,32) uint8.  The first kernel applies torchvision's ToTensor
+ * (float(p) / 255, dataset_loaders.py:76-78, the CIFAR-10 test transform) while loading, so the result is bit-identical to
+ * fiode_backbone_fwd on x / 255 and the host -> device copy is a quarter of the float one.                        */
+FIODE_API int fiode_backbone_fwd_u8(const fiode_backbone_weights* w, const unsigned char* x, int B, float* s_out,
+                          void* ws, size_t ws_bytes, void* stream);
 
 /* Per-stage device times of the LAST fiode_backbone_fwd (CUDA events on its stream; measurement aid for the
  * bench's roofline numbers, tensor-core path, batch <= one slab).  11 stages, see backbone.cu.  Synchronises. */

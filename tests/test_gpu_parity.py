@@ -482,6 +482,49 @@ def test_backbone_tensor_core_path_matches_ffma_path(ops, sd):
     assert (got - want).abs().max().item() < 1e-5
 
 
+def test_backbone_u8_pixels_equal_totensor_floats(ops, sd):
+    """fiode_backbone_fwd_u8 on the dataset's 8-bit pixels == fiode_backbone_fwd on ToTensor's floats (p / 255,
+    dataset_loaders.py:76-78), bit for bit, through the module call and through forward_batches; and the packed-weight
+    block kept per weight version gives the same bits as per-call packing."""
+    ivp = fx.build_b200_model(sd, device='cuda:0')
+    pm = ivp.init_coordinates.param_map
+    g = torch.Generator().manual_seed(11)
+    for B in (1, 37, 300):
+        p8 = torch.randint(0, 256, (B, 3, 32, 32), dtype=torch.uint8, generator=g)
+        xf = dev(p8.to(torch.float32).div(255))            # torchvision ToTensor
+        bw, keep = pm.backbone_weights()
+        assert bw.packed
+        want = ops.backbone_fwd(bw, xf)
+        got = ops.backbone_fwd(bw, dev(p8))
+        assert torch.equal(got, want)
+        bw.packed = None                                    # per-call packing inside the workspace
+        assert torch.equal(ops.backbone_fwd(bw, xf), want)
+        assert torch.equal(pm(dev(p8)), want)
+    G, B = 2, 64
+    p8 = torch.randint(0, 256, (G, B, 3, 32, 32), dtype=torch.uint8, generator=g)
+    ts = torch.linspace(0., 1., 2)
+    p = dict(method='dopri5', rtol=1e-3, atol=1e-3)
+    assert torch.equal(ivp.forward_batches(dev(p8), ts=ts, int_params=p),
+                       ivp.forward_batches(dev(p8.float().div(255)), ts=ts, int_params=p))
+
+
+def test_packed_weights_follow_weight_updates(sd):
+    """The cached kernel-ready block is rebuilt when a weight changes in place (optimizer step) and reused otherwise."""
+    ivp = fx.build_b200_model(sd, device='cuda:0')
+    pm = ivp.init_coordinates.param_map
+    x = dev(fx.synth_images(40))
+    a = pm(x)
+    blk = pm._packed
+    assert torch.equal(pm(x), a) and pm._packed is blk
+    with torch.no_grad():
+        pm[1].model[9].weight.mul_(1.5).add_(0.01)          # Cayley is scale-invariant, the shift is not
+    b = pm(x)
+    assert pm._packed is not blk
+    assert (a - b).abs().max().item() > 1e-4
+    fresh = fx.build_b200_model({'model.' + k: v.clone() for k, v in ivp.state_dict().items()}, device='cuda:0')
+    torch.testing.assert_close(fresh.init_coordinates.param_map(x), b, rtol=0, atol=0)
+
+
 def test_forward_batches_equals_per_batch_forward(sd):
     """IVP.forward_batches (backbone once over G*B images, one cluster-per-solve launch) == G calls of forward()."""
     ivp = fx.build_b200_model(sd, device='cuda:0')
