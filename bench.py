@@ -548,10 +548,13 @@ def run_b200(args):
                             weights='random init, seed 0', l2='inputs rotate over %d device buffers (%.0f MB > L2)' % (
                                 NBUF, NBUF * per_set / 1e6), parallelism=f'independent batches x{world}', host_cpus_bound_to_gpu_numa=numa),
                 images_per_s=value * B,
-                e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=per_set, d2h_bytes_per_step=G * B * 10 * 4,
-                         input='float32 images in pinned host memory (the argument of model.forward)'),
-                e2e_u8_pixels=dict(value=e2e_u8_value, unit=UNIT, h2d_bytes_per_step=per_set // 4, d2h_bytes_per_step=G * B * 10 * 4,
-                                   input='uint8 pixels in pinned host memory; ToTensor (/255) fused into the first kernel, same bits'),
+                # e2e: the dataset's 8-bit pixels in pinned host memory -> result on the host; ToTensor (/255, dataset_loaders.py:76-78)
+                # runs inside the first kernel, bit-identical to the float call (tests/test_gpu_parity.py).  e2e_f32_images: the
+                # same loop fed with ToTensor's float32 output (4x the bytes; host-memory bound once 8 ranks copy at once).
+                e2e=dict(value=e2e_u8_value, unit=UNIT, h2d_bytes_per_step=per_set // 4, d2h_bytes_per_step=G * B * 10 * 4,
+                         input='uint8 pixels (G,256,3,32,32) in pinned host memory, ToTensor fused into the first kernel'),
+                e2e_f32_images=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=per_set, d2h_bytes_per_step=G * B * 10 * 4,
+                                    input='float32 images in pinned host memory (the argument of model.forward)'),
                 gpu_launches=launches, clocks=clocks, roofline=roofline, cpu_baseline=cpu, certify=cert, fi_step=fi)
     print(json.dumps(line))
     if world > 1:

@@ -17,6 +17,7 @@
 //                    epilogue: x 1/64, + bias, GroupSort pairs, store
 #include "common.cuh"
 #include "tc.cuh"
+#include <cstdlib>
 
 namespace fiode {
 using namespace tc;
@@ -110,7 +111,9 @@ struct GtIter {
 // number of MMAs chained on one accumulator (measured: 5e-5 relative after 768 MMAs, K = 4096).  MMAs are therefore
 // chained over GT_PC chunks (48 MMAs) only; each such segment lands in one of two TMEM accumulators and four
 // dedicated warps add it -- in round-to-nearest FFMA-pipe arithmetic -- to the running sum they hold in registers.
-template <int LOAD, int NT>
+// TR (row-major output only): transpose the epilogue's 32 x NT/4 register blocks through warp-private smem tiles so that
+// every store instruction writes whole row segments instead of 16 bytes per lane at a row stride.
+template <int LOAD, int NT, bool TR = false>
 __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs a) {
     constexpr int kTmemCols = NT > 64 ? 512 : 256, kABase = 2 * NT;       // D0 [0,NT) D1 [NT,2NT) A0 A1 (64 columns each)
     constexpr uint32_t kStage = NT * 2 * GT_KC * 2;                       // hi + lo weight blocks of one k chunk
@@ -286,7 +289,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
             const long long fb = tile / per_batch, mt = (tile - fb * per_batch) / n_nt;
             const int nt = (int)(tile % n_nt);
             const long long m = mt * 128 + q * 32 + lane;
-            if (m >= a.M) continue;
+            if (LOAD != kLoadRow && m >= a.M) continue;   // row-major: guarded at the stores (the TR path needs the whole warp)
             const int ca = a.group_sort ? nt * (NT / 2) + hset * W4 : nt * NT + hset * W4;
             const int cb = a.group_sort ? ca + a.N / 2 : ca + NT / 2;
 #pragma unroll
@@ -296,12 +299,45 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
                 aa[i] = a.group_sort ? fmaxf(u, w) : u;
                 bb[i] = a.group_sort ? fminf(u, w) : w;
             }
-            if (LOAD == kLoadRow) {
-                float* o = a.out + fb * a.sO + m * a.ldo;
+            if (LOAD == kLoadRow && TR) {
+                // thread = row stores 16 bytes per lane at a row stride: 32 half-filled sectors per request (ncu r01d: 18.9 M
+                // sectors written for 9.4 M sectors of output).  Here one instruction writes 32 / W4 whole row segments.
+                float* sg = reinterpret_cast<float*>(wst + 2 * kStage + 256) + (warp - 10) * 32 * (W4 + 1);
+                const long long m0 = mt * 128 + q * 32;
+                constexpr int RPI = 32 / W4;               // rows per store instruction
+                const int rl = lane / W4, cl = lane % W4;
+                const size_t ldo = (size_t)a.ldo;
+                const int nrow = (int)(a.M - m0 < 32 ? a.M - m0 : 32);
+                float* const obase = a.out + fb * a.sO + (m0 + rl) * (long long)ldo + cl;
+                const float* const sp = sg + rl * (W4 + 1) + cl;
 #pragma unroll
-                for (int i = 0; i < W4; i += 4) {
-                    *reinterpret_cast<float4*>(o + ca + i) = make_float4(aa[i], aa[i + 1], aa[i + 2], aa[i + 3]);
-                    *reinterpret_cast<float4*>(o + cb + i) = make_float4(bb[i], bb[i + 1], bb[i + 2], bb[i + 3]);
+                for (int half = 0; half < 2; ++half) {
+                    __syncwarp();
+#pragma unroll
+                    for (int i = 0; i < W4; ++i) sg[lane * (W4 + 1) + i] = half ? bb[i] : aa[i];
+                    __syncwarp();
+                    float* op = obase + (half ? cb : ca);
+                    if (nrow == 32) {
+#pragma unroll
+                        for (int r0 = 0; r0 < 32; r0 += 8 * RPI) {
+                            float v[8];
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) v[j] = sp[(r0 + j * RPI) * (W4 + 1)];
+#pragma unroll
+                            for (int j = 0; j < 8; ++j) { *op = v[j]; op += ldo * RPI; }
+                        }
+                    } else {
+                        for (int r = rl; r < nrow; r += RPI) { *op = sp[(r - rl) * (W4 + 1)]; op += ldo * RPI; }
+                    }
+                }
+            } else if (LOAD == kLoadRow) {
+                if (m < a.M) {
+                    float* o = a.out + fb * a.sO + m * a.ldo;
+#pragma unroll
+                    for (int i = 0; i < W4; i += 4) {
+                        *reinterpret_cast<float4*>(o + ca + i) = make_float4(aa[i], aa[i + 1], aa[i + 2], aa[i + 3]);
+                        *reinterpret_cast<float4*>(o + cb + i) = make_float4(bb[i], bb[i + 1], bb[i + 2], bb[i + 3]);
+                    }
                 }
             } else {
                 const long long b = m / P;
@@ -343,16 +379,28 @@ int launch_pack_w(const float* W, int N, int K, int NT, int gs, void* Wp, cudaSt
     return 0;
 }
 
-template <int LOAD, int NT>
-static int launch_gemm_tc_nt(const GemmTcArgs& a, cudaStream_t st) {
-    const size_t smem = (size_t)4 * GT_RAW + (size_t)2 * NT * 2 * GT_KC * 2 + 256;
-    FIODE_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<LOAD, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+// Transposing epilogue for row-major outputs; FIODE_GEMM_ST=0 selects the thread-per-row stores (measured on the 144-batch
+// mixing of 8192 images: 0.284 ms -> 0.273 ms; the epilogue is not what bounds that launch)
+static bool gemm_tr_stores() {
+    static int v = [] { const char* e = getenv("FIODE_GEMM_ST"); return e ? atoi(e) : 1; }();
+    return v != 0;
+}
+template <int LOAD, int NT, bool TR>
+static int launch_gemm_tc_ntr(const GemmTcArgs& a, cudaStream_t st) {
+    const size_t smem = (size_t)4 * GT_RAW + (size_t)2 * NT * 2 * GT_KC * 2 + 256 +
+                        (TR ? (size_t)8 * 32 * (NT / 4 + 1) * sizeof(float) : 0);   // + epilogue transpose tiles
+    FIODE_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<LOAD, NT, TR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long tiles = ((a.M + 127) / 128) * (a.N / NT) * (a.nbatch > 0 ? a.nbatch : 1);
     const int grid = (int)(tiles < sm_count() ? tiles : sm_count());       // one persistent CTA per SM
-    gemm_tc_kernel<LOAD, NT><<<grid, GT_THREADS, smem, st>>>(a);
+    gemm_tc_kernel<LOAD, NT, TR><<<grid, GT_THREADS, smem, st>>>(a);
     FIODE_CUDA(cudaGetLastError());
     count_launch(1);
     return 0;
+}
+template <int LOAD, int NT>
+static int launch_gemm_tc_nt(const GemmTcArgs& a, cudaStream_t st) {
+    if (LOAD == kLoadRow && gemm_tr_stores()) return launch_gemm_tc_ntr<LOAD, NT, LOAD == kLoadRow>(a, st);
+    return launch_gemm_tc_ntr<LOAD, NT, false>(a, st);
 }
 template <int LOAD>
 static int launch_gemm_tc_t(const GemmTcArgs& a, cudaStream_t st) {
