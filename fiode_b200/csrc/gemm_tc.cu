@@ -74,6 +74,11 @@ __device__ __forceinline__ void tmem_ld8(uint32_t addr, uint32_t* v) {
                  : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
                  : "r"(addr) : "memory");
 }
+__device__ __forceinline__ void tmem_ld8f(uint32_t addr, float* v) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+                 : "r"(addr) : "memory");
+}
 __device__ __forceinline__ void tmem_st32(uint32_t addr, const uint32_t* v) {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
                  "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
@@ -103,7 +108,7 @@ constexpr int GT_PC = 4;             // chunks per accumulation segment (see "pr
 constexpr int GT_RAW = 128 * 256;    // one raw fp32 A chunk: 128 rows x 64 floats
 // flattened (tile, chunk) sequence of a persistent CTA; every role walks the same sequence
 struct GtIter {
-    long long tile, g; int c;
+    int tile; unsigned g; int c;       // 32-bit on purpose: the tile -> (batch, m tile, n tile) divisions sit on the epilogue's critical path
     __device__ __forceinline__ void next(int kcn, int stride) { ++g; if (++c == kcn) { c = 0; tile += stride; } }
 };
 
@@ -141,7 +146,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
     fence_after_sync();
     const uint32_t tmem = *tmem_slot;
     const int n_nt = a.N / NT, kcn = a.K / GT_KC;
-    const long long per_batch = ((a.M + 127) / 128) * n_nt, tiles = per_batch * (a.nbatch > 0 ? a.nbatch : 1);
+    const int per_batch = (int)((a.M + 127) / 128) * n_nt, tiles = per_batch * (a.nbatch > 0 ? a.nbatch : 1);
     const int half_n = a.n / 2, P = half_n * half_n;                      // kLoadS2d geometry
 
     if (warp < 8) {
@@ -153,7 +158,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
         // issue the copies of chunk `it` (if it exists) into own stage `st`
         auto issue = [&](const GtIter& it, int st) {
             if (it.tile < tiles) {
-                const long long fb = it.tile / per_batch, mt = (it.tile - fb * per_batch) / n_nt;
+                const int fb = it.tile / per_batch;
+                const long long mt = (it.tile - fb * per_batch) / n_nt;
                 const uint32_t dst = raw0 + st * GT_RAW;
                 if (LOAD == kLoadRow) {       // 16 lanes cover the 256 contiguous bytes of one row
 #pragma unroll
@@ -180,7 +186,7 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
             }
             cp_async_commit();
         };
-        GtIter cur{(long long)blockIdx.x, 0, 0};
+        GtIter cur{(int)blockIdx.x, 0u, 0};
         if (par == 1) cur.next(kcn, gridDim.x);            // warpgroup p owns the chunks with g = p (mod 2)
         GtIter nxt = cur;
         nxt.next(kcn, gridDim.x); nxt.next(kcn, gridDim.x);
@@ -228,8 +234,8 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
             const uint32_t sw = smem_u32(wst);
             const uint32_t idesc = idesc_f16(128, NT);
             constexpr uint64_t step = (uint64_t)(2 * NT * 16) >> 4;        // descriptor units per 16-wide k slab
-            long long sg = 0;                                              // segment counter
-            for (GtIter it{(long long)blockIdx.x, 0, 0}; it.tile < tiles; it.next(kcn, gridDim.x)) {
+            unsigned sg = 0;                                               // segment counter
+            for (GtIter it{(int)blockIdx.x, 0u, 0}; it.tile < tiles; it.next(kcn, gridDim.x)) {
                 const int b = (int)(it.g & 1), cs = it.c % GT_PC, db = (int)(sg & 1);
                 const uint32_t ph = (uint32_t)((it.g >> 1) & 1);
                 mbar_wait(&a_full[b], ph);
@@ -249,11 +255,11 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
     } else if (warp == 9) {
         // ================= weight-chunk copies (cp.async.bulk) ============================================
         if (lane == 0) {
-            for (GtIter it{(long long)blockIdx.x, 0, 0}; it.tile < tiles; it.next(kcn, gridDim.x)) {
-                const int b = (int)(it.g & 1), nt = (int)(it.tile % n_nt);
+            for (GtIter it{(int)blockIdx.x, 0u, 0}; it.tile < tiles; it.next(kcn, gridDim.x)) {
+                const int b = (int)(it.g & 1), nt = it.tile % n_nt;
                 mbar_wait(&empty[b], (uint32_t)((it.g >> 1) & 1) ^ 1u);
                 mbar_expect_tx(&b_full[b], kStage);
-                bulk_g2s(wst + b * kStage, a.Wp + (it.tile / per_batch) * a.sW + ((size_t)nt * kcn + it.c) * (size_t)(2 * NT * GT_KC), kStage,
+                bulk_g2s(wst + b * kStage, a.Wp + (long long)(it.tile / per_batch) * a.sW + ((size_t)nt * kcn + it.c) * (size_t)(2 * NT * GT_KC), kStage,
                          &b_full[b]);
             }
         }
@@ -263,13 +269,21 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
         const int q = warp & 3, hset = (warp - 10) >> 2;
         const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
         const int nseg = (kcn + GT_PC - 1) / GT_PC;
-        long long sg = 0;
-        for (long long tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        unsigned sg = 0;
+        for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
             float aa[W4], bb[W4];     // local columns hset*W4 + i  and  NT/2 + hset*W4 + i  (GroupSort partners)
             for (int s_ = 0; s_ < nseg; ++s_, ++sg) {
                 const int db = (int)(sg & 1);
                 mbar_wait(&seg_full[db], (uint32_t)((sg >> 1) & 1));
                 fence_after_sync();
+                if (s_ == 0) {        // first segment: straight into the sums, ONE TMEM round trip for all NT/2 columns
+#pragma unroll
+                    for (int i = 0; i < W4; i += 8) {
+                        tmem_ld8f(lane_base + db * NT + hset * W4 + i, aa + i);
+                        tmem_ld8f(lane_base + db * NT + NT / 2 + hset * W4 + i, bb + i);
+                    }
+                    tmem_wait_ld();
+                } else
 #pragma unroll
                 for (int i = 0; i < W4; i += 8) {
                     uint32_t ua[8], ub[8];
@@ -278,16 +292,16 @@ __global__ void __launch_bounds__(GT_THREADS, 1) gemm_tc_kernel(const GemmTcArgs
                     tmem_wait_ld();
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
-                        aa[i + j] = s_ == 0 ? __uint_as_float(ua[j]) : aa[i + j] + __uint_as_float(ua[j]);
-                        bb[i + j] = s_ == 0 ? __uint_as_float(ub[j]) : bb[i + j] + __uint_as_float(ub[j]);
+                        aa[i + j] += __uint_as_float(ua[j]);
+                        bb[i + j] += __uint_as_float(ub[j]);
                     }
                 }
                 fence_before_sync();
                 mbar_arrive(&seg_empty[db]);
             }
             // ---- epilogue: / 64, + bias, GroupSort (layers.py:127-131), store ------------------------------
-            const long long fb = tile / per_batch, mt = (tile - fb * per_batch) / n_nt;
-            const int nt = (int)(tile % n_nt);
+            const int fb = tile / per_batch, rem = tile - fb * per_batch, mti = rem / n_nt, nt = rem - mti * n_nt;
+            const long long mt = mti;
             const long long m = mt * 128 + q * 32 + lane;
             if (LOAD != kLoadRow && m >= a.M) continue;   // row-major: guarded at the stores (the TR path needs the whole warp)
             const int ca = a.group_sort ? nt * (NT / 2) + hset * W4 : nt * NT + hset * W4;
