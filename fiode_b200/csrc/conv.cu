@@ -331,6 +331,143 @@ __global__ void __launch_bounds__(160) irfft32_mix3_kernel(const float2* __restr
         *reinterpret_cast<float4*>(y + ((size_t)(b0 + im3) * C + chan(c3)) * n * n + rem * 4) = v4;
     }
 }
+// Wide variant: 288 threads, so that the 272 column tasks and the 256 row tasks (ONE channel-image row pair each) are a single
+// round, 18 warps per SM instead of 10 (ncu r01f: 160-thread CTAs leave 2.5 warps per scheduler, 'wait' + 'selected' are the top
+// stall reasons, issue 52 %).  One FFT per thread keeps it under 112 registers; GroupSort moves to the copy-out.
+template <int IM>
+__global__ void __launch_bounds__(288, 2) irfft32_mix3_wide_kernel(const float2* __restrict__ Xf, const float2* __restrict__ Qt,
+                                                           int B, int C, const float* __restrict__ bias, int group_sort,
+                                                           float* __restrict__ y) {
+    // RS = H (no row padding): phi = u * RS + v, so the mixing writes consecutive words, the column pass reads consecutive
+    // words across lanes, and the row pass (lane = row pair, stride 2 RS float2 = 68 words) is 2-way instead of 4-way conflicted
+    constexpr int n = 32, CH = 8, H = 17, RS = 17, RSI = n * RS + 1, F = n * H, THREADS = 288, OS = n + 4;
+    extern __shared__ float4 smem4[];
+    float2* T = reinterpret_cast<float2*>(smem4);                 // [IM][CH] images of [n][RS] (+1)
+    const int groups_per_b = C / CH;
+    const int bg = blockIdx.x / groups_per_b, g = blockIdx.x - bg * groups_per_b;
+    const int b0 = bg * IM;
+    auto chan = [&](int ci) {
+        if (group_sort) return (ci < CH / 2) ? g * (CH / 2) + ci : C / 2 + g * (CH / 2) + (ci - CH / 2);
+        return g * CH + ci;
+    };
+    // the IM input spectra (3 channels each) are staged once; every thread then reuses each Q value for all IM images
+    float2* Xs = T + IM * CH * RSI + ((IM * CH * RSI) & 1);       // [IM][3][F], 16-byte aligned
+    // asynchronous 16-byte copies (LDGSTS): all in flight at once, and they overlap the first batch of Q loads below
+    for (int e = threadIdx.x; e < IM * 3 * F / 2; e += THREADS) {
+        const int im = e / (3 * F / 2);
+        if (b0 + im < B) __pipeline_memcpy_async(Xs + 2 * e, Xf + (size_t)b0 * 3 * F + 2 * e, 16);
+        else *reinterpret_cast<float4*>(Xs + 2 * e) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    __pipeline_commit();
+    // step 1a: mix.  Yf[im][ci][phi] = sum_c Q[chan(ci)][c][phi] Xs[im][c][phi].  Lanes run along phi (coalesced Q reads, each
+    // Q value read once per CTA); a thread does channels cp and cp + CH/2 of one phi, so every Xs value it reads from shared
+    // memory feeds two outputs; the Q loads of UB iterations are issued together (they would otherwise serialise on L2 latency).
+    {
+        constexpr int UB = 4, ITERS = ((CH / 2) * F + THREADS - 1) / THREADS;      // 8 (phi, channel-pair) items per thread
+        for (int it0 = 0; it0 < ITERS; it0 += UB) {
+            float2 qa[UB][3], qb[UB][3];
+#pragma unroll
+            for (int j = 0; j < UB; ++j) {
+                const int e = threadIdx.x + (it0 + j) * THREADS;
+                if (it0 + j < ITERS && e < (CH / 2) * F) {
+                    const int cp = e / F, phi = e - cp * F;
+                    const float2* q = Qt + (size_t)chan(cp) * 3 * F + phi;
+                    const float2* r = Qt + (size_t)chan(cp + CH / 2) * 3 * F + phi;
+                    qa[j][0] = __ldg(q); qa[j][1] = __ldg(q + F); qa[j][2] = __ldg(q + 2 * F);
+                    qb[j][0] = __ldg(r); qb[j][1] = __ldg(r + F); qb[j][2] = __ldg(r + 2 * F);
+                }
+            }
+            if (it0 == 0) {                          // uniform: the staged spectra are needed from here on
+                __pipeline_wait_prior(0);
+                __syncthreads();
+            }
+#pragma unroll
+            for (int j = 0; j < UB; ++j) {
+                const int e = threadIdx.x + (it0 + j) * THREADS;
+                if (it0 + j < ITERS && e < (CH / 2) * F) {
+                    const int cp = e / F, phi = e - cp * F;
+#pragma unroll
+                    for (int im = 0; im < IM; ++im) {
+                        const float2* xs = Xs + im * 3 * F + phi;
+                        const float2 x0 = xs[0], x1 = xs[F], x2 = xs[2 * F];
+                        float2 acc = make_float2(0.f, 0.f), bcc = make_float2(0.f, 0.f);
+                        cfma(acc, qa[j][0], x0); cfma(acc, qa[j][1], x1); cfma(acc, qa[j][2], x2);
+                        cfma(bcc, qb[j][0], x0); cfma(bcc, qb[j][1], x1); cfma(bcc, qb[j][2], x2);
+                        T[(im * CH + cp) * RSI + phi] = acc;
+                        T[(im * CH + cp + CH / 2) * RSI + phi] = bcc;
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();
+    // step 1b: columns (inverse along u), in place.  task = (image, channel, v), v fastest
+    for (int task = threadIdx.x; task < IM * CH * H; task += THREADS) {
+        const int ic = task / H, v = task - ic * H;
+        float2* col = T + ic * RSI + v;
+        float2 z[n];
+#pragma unroll
+        for (int u = 0; u < n; ++u) z[u] = col[u * RS];
+        fft_dif<n, true>(z);
+#pragma unroll
+        for (int a = 0; a < n; ++a) col[a * RS] = z[bitrev<n>(a)];
+    }
+    __syncthreads();
+    // step 2: rows.  task = (image, channel, row pair p): two real rows per complex FFT (rows 2p, 2p+1 packed as re / im).  The two
+    // finished rows (+ bias) are staged in shared memory (over T / Xs, which are dead by then).
+    const float scale = 1.0f / (float)(n * n);
+    const int task = threadIdx.x;
+    const bool has_task = task < IM * CH * (n / 2);
+    const int ic2 = task / (n / 2), p = task - ic2 * (n / 2), ci = ic2 % CH;
+    float2 za[n];
+    if (has_task) {
+        const float2* ta = T + ic2 * RSI + 2 * p * RS;
+        const float2* tb = ta + RS;
+#pragma unroll
+        for (int k = 0; k <= n / 2; ++k) {
+            float2 A = ta[k], Bq = tb[k];
+            if (k == 0 || k == n / 2) { A.y = 0.f; Bq.y = 0.f; }
+            za[k] = make_float2(A.x - Bq.y, A.y + Bq.x);
+            if (k > 0 && k < n / 2) za[n - k] = make_float2(A.x + Bq.y, -A.y + Bq.x);
+        }
+        fft_dif<n, true>(za);
+    }
+    __syncthreads();                                   // every read of T is done: reuse the buffer as the output stage
+    float* O = reinterpret_cast<float*>(smem4);        // [IM * CH][n rows][OS] floats (OS = n + 4: conflict-free float4 rows)
+    if (has_task) {
+        const float bsa = bias ? bias[chan(ci)] : 0.f;
+        float* oa = O + (ic2 * n + 2 * p) * OS;
+#pragma unroll
+        for (int k = 0; k < n; k += 4) {
+            float a0[4], a1[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float2 ra = za[bitrev<n>(k + q)];
+                a0[q] = ra.x * scale + bsa; a1[q] = ra.y * scale + bsa;             // row 2p, row 2p+1
+            }
+            *reinterpret_cast<float4*>(oa + k) = make_float4(a0[0], a0[1], a0[2], a0[3]);
+            *reinterpret_cast<float4*>(oa + OS + k) = make_float4(a1[0], a1[1], a1[2], a1[3]);
+        }
+    }
+    __syncthreads();
+    // step 3: GroupSort of the (ci, ci + CH/2) pair (layers.py:127-131) + coalesced copy-out, one float4 of each partner per lane
+    for (int e = threadIdx.x; e < IM * (CH / 2) * n * (n / 4); e += THREADS) {
+        const int ip = e / (n * (n / 4)), rem = e - ip * (n * (n / 4)), row = rem / (n / 4), k4 = rem - row * (n / 4);
+        const int im3 = ip / (CH / 2), c3 = ip - im3 * (CH / 2);
+        if (b0 + im3 >= B) continue;
+        const float4 u = *reinterpret_cast<const float4*>(O + ((im3 * CH + c3) * n + row) * OS + k4 * 4);
+        const float4 w = *reinterpret_cast<const float4*>(O + ((im3 * CH + c3 + CH / 2) * n + row) * OS + k4 * 4);
+        const float4 hi = group_sort ? make_float4(fmaxf(u.x, w.x), fmaxf(u.y, w.y), fmaxf(u.z, w.z), fmaxf(u.w, w.w)) : u;
+        const float4 lo = group_sort ? make_float4(fminf(u.x, w.x), fminf(u.y, w.y), fminf(u.z, w.z), fminf(u.w, w.w)) : w;
+        *reinterpret_cast<float4*>(y + ((size_t)(b0 + im3) * C + chan(c3)) * n * n + rem * 4) = hi;
+        *reinterpret_cast<float4*>(y + ((size_t)(b0 + im3) * C + chan(c3 + CH / 2)) * n * n + rem * 4) = lo;
+    }
+}
+// FIODE_MIX3_T=160 selects the 160-thread kernel (two FFTs per row task), default the 288-thread one
+static bool mix3_wide() {
+    static int v = [] { const char* e = getenv("FIODE_MIX3_T"); return e ? atoi(e) : 288; }();
+    return v != 160;
+}
 template <int IM>
 static int launch_irfft32_mix3_t(const float2* Xf, const float2* Qt, int B, int C, const float* bias, int gs, float* y,
                                  cudaStream_t st) {
@@ -340,7 +477,13 @@ static int launch_irfft32_mix3_t(const float2* Xf, const float2* Qt, int B, int 
     const size_t smem = stage > outb ? stage : outb;
     cudaError_t e = cudaFuncSetAttribute(irfft32_mix3_kernel<IM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return cuda_fail(e, "irfft32_mix3 smem attr");
-    irfft32_mix3_kernel<IM><<<((B + IM - 1) / IM) * (C / 8), 160, smem, st>>>(Xf, Qt, B, C, bias, gs, y);
+    if (mix3_wide()) {
+        e = cudaFuncSetAttribute(irfft32_mix3_wide_kernel<IM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return cuda_fail(e, "irfft32_mix3 smem attr");
+        irfft32_mix3_wide_kernel<IM><<<((B + IM - 1) / IM) * (C / 8), 288, smem, st>>>(Xf, Qt, B, C, bias, gs, y);
+    } else {
+        irfft32_mix3_kernel<IM><<<((B + IM - 1) / IM) * (C / 8), 160, smem, st>>>(Xf, Qt, B, C, bias, gs, y);
+    }
     return 0;
 }
 // images per CTA: 2 reuses every Q value twice (2 CTAs / SM), 1 halves the footprint (4 CTAs / SM); FIODE_MIX3_IM overrides
