@@ -23,14 +23,15 @@ template <int n> struct FftCfg {
     static constexpr int H = n / 2 + 1;          // half-spectrum width
     static constexpr int RS = H + 1;             // padded smem row stride (complex)
     static constexpr int CH = (n == 32) ? 8 : 16;  // channel-images per CTA
-    static constexpr int THREADS = 128;
+    // 160 threads: the CH * H column tasks (136 at n = 32, 144 at n = 16) are one round instead of 128 + a nearly empty second one
+    static constexpr int THREADS = 160;
 };
 
 // FM ("frequency-major"): the spectrum is written as Xt[phi][b][c] instead of torch's [b][c][phi], so that the channel
 // mixing of one frequency is a plain row-major (batch x 2C) GEMM operand for the tensor-core kernel (gemm_tc.cu).
 // U8: x holds 8-bit pixels; the load applies torchvision's ToTensor (float(p) / 255, IEEE division) before Normalize.
 template <int n, bool FM, bool U8 = false>
-__global__ void __launch_bounds__(128) rfft2_kernel(const float* __restrict__ x, int n_img, int C,
+__global__ void __launch_bounds__(FftCfg<n>::THREADS) rfft2_kernel(const float* __restrict__ x, int n_img, int C,
                                                     const float* __restrict__ mu, const float* __restrict__ sd,
                                                     float2* __restrict__ Xf) {
     using Cf = FftCfg<n>;
@@ -104,7 +105,7 @@ __global__ void __launch_bounds__(128) rfft2_kernel(const float* __restrict__ x,
 // CTA handles CH channel-images: with GroupSort they are CH/2 (c, c + C/2) pairs of one batch item.
 // ------------------------------------------------------------------------------------------------
 template <int n, bool FM>
-__global__ void __launch_bounds__(128) irfft2_kernel(const float2* __restrict__ Yf, int B, int C,
+__global__ void __launch_bounds__(FftCfg<n>::THREADS) irfft2_kernel(const float2* __restrict__ Yf, int B, int C,
                                                      const float* __restrict__ bias, int group_sort,
                                                      float* __restrict__ y) {
     using Cf = FftCfg<n>;
@@ -676,10 +677,10 @@ __global__ void group_sort_kernel(const float* __restrict__ x, int B, int C, int
 int launch_rfft2(const float* x, int n_img, int C, int n, const float* mu, const float* sd, float2* Xf, cudaStream_t st,
                  bool freq_major, bool x_u8 = false) {
     if (x_u8 && !(n == 32 && !freq_major)) { set_error("rfft2: 8-bit input only for the 32x32 image layer"); return -1; }
-    if (x_u8) rfft2_kernel<32, false, true><<<(n_img + FftCfg<32>::CH - 1) / FftCfg<32>::CH, 128, 0, st>>>(x, n_img, C, mu, sd, Xf);
-    else if (n == 32 && !freq_major) rfft2_kernel<32, false><<<(n_img + FftCfg<32>::CH - 1) / FftCfg<32>::CH, 128, 0, st>>>(x, n_img, C, mu, sd, Xf);
-    else if (n == 16 && !freq_major) rfft2_kernel<16, false><<<(n_img + FftCfg<16>::CH - 1) / FftCfg<16>::CH, 128, 0, st>>>(x, n_img, C, mu, sd, Xf);
-    else if (n == 16 && C % FftCfg<16>::CH == 0) rfft2_kernel<16, true><<<(n_img + FftCfg<16>::CH - 1) / FftCfg<16>::CH, 128, 0, st>>>(x, n_img, C, mu, sd, Xf);
+    if (x_u8) rfft2_kernel<32, false, true><<<(n_img + FftCfg<32>::CH - 1) / FftCfg<32>::CH, FftCfg<32>::THREADS, 0, st>>>(x, n_img, C, mu, sd, Xf);
+    else if (n == 32 && !freq_major) rfft2_kernel<32, false><<<(n_img + FftCfg<32>::CH - 1) / FftCfg<32>::CH, FftCfg<32>::THREADS, 0, st>>>(x, n_img, C, mu, sd, Xf);
+    else if (n == 16 && !freq_major) rfft2_kernel<16, false><<<(n_img + FftCfg<16>::CH - 1) / FftCfg<16>::CH, FftCfg<16>::THREADS, 0, st>>>(x, n_img, C, mu, sd, Xf);
+    else if (n == 16 && C % FftCfg<16>::CH == 0) rfft2_kernel<16, true><<<(n_img + FftCfg<16>::CH - 1) / FftCfg<16>::CH, FftCfg<16>::THREADS, 0, st>>>(x, n_img, C, mu, sd, Xf);
     else { set_error("rfft2: unsupported n=%d (16 or 32), freq_major=%d", n, (int)freq_major); return -1; }
     count_launch(1);
     return 0;
@@ -691,12 +692,12 @@ int launch_irfft2(const float2* Yf, int B, int C, int n, const float* bias, int 
         const size_t smem = (size_t)Cf::CH * 32 * (Cf::RS * sizeof(float2) + 33 * sizeof(float)) + (Cf::CH + 2) * sizeof(float2);
         cudaError_t e = cudaFuncSetAttribute(irfft2_kernel<32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return cuda_fail(e, "irfft2 smem attr");
-        irfft2_kernel<32, false><<<B * (C / Cf::CH), 128, smem, st>>>(Yf, B, C, bias, gs, y);
+        irfft2_kernel<32, false><<<B * (C / Cf::CH), FftCfg<32>::THREADS, smem, st>>>(Yf, B, C, bias, gs, y);
     } else if (n == 16 && C % FftCfg<16>::CH == 0) {
         using Cf = FftCfg<16>;
         const size_t smem = (size_t)Cf::CH * 16 * (Cf::RS * sizeof(float2) + 17 * sizeof(float)) + (Cf::CH + 2) * sizeof(float2);
-        if (freq_major) irfft2_kernel<16, true><<<B * (C / Cf::CH), 128, smem, st>>>(Yf, B, C, bias, gs, y);
-        else irfft2_kernel<16, false><<<B * (C / Cf::CH), 128, smem, st>>>(Yf, B, C, bias, gs, y);
+        if (freq_major) irfft2_kernel<16, true><<<B * (C / Cf::CH), FftCfg<16>::THREADS, smem, st>>>(Yf, B, C, bias, gs, y);
+        else irfft2_kernel<16, false><<<B * (C / Cf::CH), FftCfg<16>::THREADS, smem, st>>>(Yf, B, C, bias, gs, y);
     } else { set_error("irfft2: unsupported n=%d C=%d", n, C); return -1; }
     count_launch(1);
     return 0;
