@@ -286,7 +286,7 @@ def fi_step_bench(device, pk, world, iters=10, warm=3):
 STAGES = [
     ('weight packing (per call)', 'pack_w_kernel x5 + mix_real_weights', 0, 0),
     ('rfft2 32x32, 3 ch (+Normalize)', 'rfft2_kernel<32>', 3 * 1024 * 4 + 3 * 544 * 8, 0.12e6),
-    ('mix 3->32 + irfft2 32x32 + bias + GroupSort', 'irfft32_mix3_kernel', 3 * 544 * 8 + 32 * 1024 * 4, 0.42e6 + 1.1e6),
+    ('mix 3->32 + irfft2 32x32 + bias + GroupSort', 'irfft32_mix3_wide_kernel', 3 * 544 * 8 + 32 * 1024 * 4, 0.42e6 + 1.1e6),
     ('conv 128->32 @16x16 (s2d 1x1) + GroupSort', 'gemm_tc_kernel<s2d,32>', 32 * 1024 * 4 + 32 * 256 * 4, 2 * 128 * 32 * 256),
     ('rfft2 16x16, 32 ch', 'rfft2_kernel<16,fm>', 32 * 256 * 4 + 32 * 144 * 8, 0.3e6),
     ('mixing 144 x (64->128 real)', 'gemm_tc_kernel<row,128> batched', (32 + 64) * 144 * 8, 2 * 64 * 128 * 144),
@@ -298,15 +298,16 @@ STAGES = [
 ]
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture of one 4096-image slab
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture (profiles/r01g_ncu_full_summary.md, one 4096-image launch)
 # (profiles/r01c_ncu_full_summary.md; re-measure when a kernel changes).  Keyed by the kernel named in STAGES / the solver.
 NCU_TRAFFIC_BYTES = {
-    'rfft2_kernel<32>': 50.42e6 + 4.57e6,
-    'irfft32_mix3_kernel': 54.04e6 + 478.27e6,
-    'gemm_tc_kernel<s2d,32>': 536.93e6 + 116.05e6,
-    'rfft2_kernel<16,fm>': 134.24e6 + 100.99e6,
-    'irfft2_kernel<16,fm>': 302.11e6 + 228.70e6,
-    'gemm_tc_kernel<s2d,64>': 268.59e6 + 45.88e6,
+    'rfft2_kernel<32>': 50.37e6 + 4.19e6,
+    'irfft32_mix3_wide_kernel': 53.93e6 + 477.15e6,
+    'gemm_tc_kernel<s2d,32>': 536.93e6 + 114.70e6,
+    'rfft2_kernel<16,fm>': 134.24e6 + 100.31e6,
+    'gemm_tc_kernel<row,128> batched': 156.84e6 + 245.81e6,
+    'irfft2_kernel<16,fm>': 302.02e6 + 229.64e6,
+    'gemm_tc_kernel<s2d,64>': 268.54e6 + 46.07e6,
     'dopri5_simplex_batched_kernel': 0.60e6,
 }
 
@@ -367,7 +368,7 @@ def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
     traffic = NCU_TRAFFIC_BYTES.get(top['kernel'])
     if traffic and top['kernel'] != 'dopri5_simplex_batched_kernel':
         traffic *= n_stage / 4096.             # the capture ran one 4096-image launch; these kernels stream, bytes scale with images
-    rf.update(traffic=traffic, traffic_source='profiles/r01d_ncu_full_summary.md (4096-image launch, scaled to the %d images of this launch)' % n_stage,
+    rf.update(traffic=traffic, traffic_source='profiles/r01g_ncu_full_summary.md (4096-image launch, scaled to the %d images of this launch)' % n_stage,
               kernel=top['kernel'], stage=top['stage'], ms_per_launch=top['ms'], launches_per_step=top['launches_per_step'], peak_source=pk['source'],
               note='algorithmic bytes / flops of SURVEY 8(d) over the CUDA-event time of that launch; tensor-core stages run the '
                    'fp16x2-split FP32 emulation (3 MMAs per product), so their ceiling is peak / 3; see DESIGN.md section 4',
