@@ -16,7 +16,7 @@ namespace fiode {
 int launch_rfft2(const float* x, int n_img, int C, int n, const float* mu, const float* sd, float2* Xf, cudaStream_t st,
                  bool freq_major = false, bool x_u8 = false);
 int launch_irfft2(const float2* Yf, int B, int C, int n, const float* bias, int gs, float* y, cudaStream_t st,
-                  bool freq_major = false);
+                  int freq_major = 0);
 int launch_irfft32_mix3(const float2* Xf, const float2* Qf, float2* Qt, int B, int C, const float* bias, int gs, float* y,
                         cudaStream_t st);
 int launch_mix_real_weights(const float2* Qf, int F, int cout, int cin, float* W, cudaStream_t st);
@@ -164,10 +164,13 @@ static int backbone_fwd(const fiode_backbone_weights* w, const float* x, bool x_
         if (tcp) {   // frequency-major spectra: the mixing of frequency phi is the row-major GEMM (nb x 64) . (128 x 64)^T
             if ((rc = launch_rfft2(a2, nb * 32, 32, 16, nullptr, nullptr, xf4, st, true))) return rc;
             mark(5, st);
+            // mixed spectrum as [b][phi][co] (row stride 144 x 128 floats, one frequency = 128 floats further): scattered 512-byte
+            // row writes for the GEMM, one contiguous 74 KB block per image for the inverse FFT.  FIODE_YF4=1: [phi][b][co].
+            static const bool ifm = [] { const char* e = getenv("FIODE_YF4"); return !(e && atoi(e) == 1); }();
             if ((rc = launch_linear_tc_batched((const float*)xf4, 64, (long long)nb * 64, pk + P.p4, nb, 128, 64, 144,
-                                               (float*)yf4, 128, (long long)nb * 128, st))) return rc;
+                                               (float*)yf4, ifm ? 144 * 128 : 128, ifm ? 128 : (long long)nb * 128, st))) return rc;
             mark(6, st);
-            if ((rc = launch_irfft2(yf4, nb, 64, 16, w->b4, 1, a4, st, true))) return rc;
+            if ((rc = launch_irfft2(yf4, nb, 64, 16, w->b4, 1, a4, st, ifm ? 2 : 1))) return rc;
         } else {
             if ((rc = launch_rfft2(a2, nb * 32, 32, 16, nullptr, nullptr, xf4, st))) return rc;
             if ((rc = launch_mix(xf4, (const float2*)w->Qf4, nb, 144, 64, 32, yf4, st))) return rc;

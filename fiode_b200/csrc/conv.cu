@@ -104,7 +104,9 @@ __global__ void __launch_bounds__(FftCfg<n>::THREADS) rfft2_kernel(const float* 
 // inverse: Yf [img][n][H] -> y [img][n][n] (+bias[c]), optional GroupSort over channel halves
 // CTA handles CH channel-images: with GroupSort they are CH/2 (c, c + C/2) pairs of one batch item.
 // ------------------------------------------------------------------------------------------------
-template <int n, bool FM>
+// FM: 0 torch layout [b][c][phi]; 1 frequency-major [phi][b][c]; 2 image-major, channels innermost [b][phi][c] (what the
+// batched mixing GEMM writes with ldo = F * C: the 144 pieces a CTA gathers then sit in ONE 74 KB block per image)
+template <int n, int FM>
 __global__ void __launch_bounds__(FftCfg<n>::THREADS) irfft2_kernel(const float2* __restrict__ Yf, int B, int C,
                                                      const float* __restrict__ bias, int group_sort,
                                                      float* __restrict__ y) {
@@ -126,10 +128,14 @@ __global__ void __launch_bounds__(FftCfg<n>::THREADS) irfft2_kernel(const float2
     for (int task = threadIdx.x; task < CH * Cf::H; task += Cf::THREADS) {
         const int ci = FM ? task % CH : task / Cf::H, v = FM ? task / CH : task - ci * Cf::H;
         float2 z[n];
-        if (FM) {                                  // Yt[(u H + v)][b][co]: lanes read consecutive channels
+        if (FM == 1) {                             // Yt[(u H + v)][b][co]: lanes read consecutive channels
             const float2* src = Yf + ((size_t)v * B + b) * C + chan(ci);
 #pragma unroll
             for (int u = 0; u < n; ++u) z[u] = src[(size_t)u * Cf::H * B * C];
+        } else if (FM == 2) {                      // Yi[b][(u H + v)][co]
+            const float2* src = Yf + ((size_t)b * n * Cf::H + v) * C + chan(ci);
+#pragma unroll
+            for (int u = 0; u < n; ++u) z[u] = src[(size_t)u * Cf::H * C];
         } else {
             const float2* src = Yf + ((size_t)b * C + chan(ci)) * n * Cf::H + v;
 #pragma unroll
@@ -686,18 +692,19 @@ int launch_rfft2(const float* x, int n_img, int C, int n, const float* mu, const
     return 0;
 }
 int launch_irfft2(const float2* Yf, int B, int C, int n, const float* bias, int gs, float* y, cudaStream_t st,
-                  bool freq_major) {
+                  int freq_major) {
     if (n == 32 && C % FftCfg<32>::CH == 0 && !freq_major) {
         using Cf = FftCfg<32>;
         const size_t smem = (size_t)Cf::CH * 32 * (Cf::RS * sizeof(float2) + 33 * sizeof(float)) + (Cf::CH + 2) * sizeof(float2);
-        cudaError_t e = cudaFuncSetAttribute(irfft2_kernel<32, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(irfft2_kernel<32, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return cuda_fail(e, "irfft2 smem attr");
-        irfft2_kernel<32, false><<<B * (C / Cf::CH), FftCfg<32>::THREADS, smem, st>>>(Yf, B, C, bias, gs, y);
+        irfft2_kernel<32, 0><<<B * (C / Cf::CH), FftCfg<32>::THREADS, smem, st>>>(Yf, B, C, bias, gs, y);
     } else if (n == 16 && C % FftCfg<16>::CH == 0) {
         using Cf = FftCfg<16>;
         const size_t smem = (size_t)Cf::CH * 16 * (Cf::RS * sizeof(float2) + 17 * sizeof(float)) + (Cf::CH + 2) * sizeof(float2);
-        if (freq_major) irfft2_kernel<16, true><<<B * (C / Cf::CH), FftCfg<16>::THREADS, smem, st>>>(Yf, B, C, bias, gs, y);
-        else irfft2_kernel<16, false><<<B * (C / Cf::CH), FftCfg<16>::THREADS, smem, st>>>(Yf, B, C, bias, gs, y);
+        if (freq_major == 2) irfft2_kernel<16, 2><<<B * (C / Cf::CH), FftCfg<16>::THREADS, smem, st>>>(Yf, B, C, bias, gs, y);
+        else if (freq_major) irfft2_kernel<16, 1><<<B * (C / Cf::CH), FftCfg<16>::THREADS, smem, st>>>(Yf, B, C, bias, gs, y);
+        else irfft2_kernel<16, 0><<<B * (C / Cf::CH), FftCfg<16>::THREADS, smem, st>>>(Yf, B, C, bias, gs, y);
     } else { set_error("irfft2: unsupported n=%d C=%d", n, C); return -1; }
     count_launch(1);
     return 0;

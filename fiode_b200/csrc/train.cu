@@ -24,7 +24,7 @@ size_t gemm_tn_workspace(int M, int N, long long K);
 int launch_rfft2(const float* x, int n_img, int C, int n, const float* mu, const float* sd, float2* Xf, cudaStream_t st,
                  bool freq_major, bool x_u8 = false);
 int launch_irfft2(const float2* Yf, int B, int C, int n, const float* bias, int gs, float* y, cudaStream_t st,
-                  bool freq_major);
+                  int freq_major);
 
 static size_t al256(size_t x) { return (x + 255) & ~(size_t)255; }
 static unsigned nblocks(size_t total, unsigned cap = 65535) {
