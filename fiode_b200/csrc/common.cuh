@@ -112,6 +112,31 @@ __device__ __forceinline__ unsigned bisect_all(const float (&ft)[NH], const floa
     }
     return notconv;
 }
+// Same bisection for a caller where ONE warp runs it while the rest of the CTA waits (the dopri5 kernel: ncu r01g, 21 % of all
+// warp samples sit at the barrier behind it).  The dependent chain per midpoint is cut from ~16 to 8 operations: the ten terms are
+// summed as a tree (the reference's torch.sum fixes no order either), and the next midpoint is computed for either sign of e while
+// e is still being summed -- (hi - mu) / 2 + mu and (mu - lw) / 2 + lw are exactly what the sequential form evaluates next.
+__device__ __forceinline__ unsigned bisect_all_ilp(const float (&ft)[NH], const float (&lo)[NH], int max_iter,
+                                                   float tol, float* mus, int mu_stride) {
+    static_assert(NH == 10, "tree sum written for 10 terms");
+    float hi = ft[0] - lo[0], lw = ft[0];
+#pragma unroll
+    for (int j = 1; j < NH; ++j) { hi = fmaxf(hi, ft[j] - lo[j]); lw = fminf(lw, ft[j]); }
+    unsigned notconv = 0;
+    float mu = (hi - lw) / 2.f + lw;
+    for (int k = 0; k < max_iter; ++k) {
+        float t[NH];
+#pragma unroll
+        for (int j = 0; j < NH; ++j) t[j] = fmaxf(ft[j] - mu, lo[j]);
+        const float mu_pos = (hi - mu) / 2.f + mu, mu_neg = (mu - lw) / 2.f + lw;
+        const float e = (((t[0] + t[1]) + (t[2] + t[3])) + ((t[4] + t[5]) + (t[6] + t[7]))) + (t[8] + t[9]);
+        mus[k * mu_stride] = mu;
+        if (!(fabsf(e) < tol)) notconv |= (1u << k);
+        if (e > 0.f) { lw = mu; mu = mu_pos; }
+        else if (e < 0.f) { hi = mu; mu = mu_neg; }
+    }
+    return notconv;
+}
 // stop iteration from the OR of the not-converged words: first k whose bit is clear, else the last
 __device__ __forceinline__ int stop_iter(unsigned notconv_or, int max_iter) {
     unsigned conv = ~notconv_or & (max_iter >= 32 ? 0xffffffffu : ((1u << max_iter) - 1u));

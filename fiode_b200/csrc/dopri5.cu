@@ -236,7 +236,7 @@ __device__ __forceinline__ void eval_rhs(const SolveArgs& a, const Smem& S, int 
             ft[i] = f;
             S.lo[t * SROW + i] = lo[i];
         }
-        nc = bisect_all(ft, lo, a.w.max_iter, a.w.tol, S.mus + t, Rp);
+        nc = bisect_all_ilp(ft, lo, a.w.max_iter, a.w.tol, S.mus + t, Rp);
     }
     if (t < 64) {  // R <= 64 -> rows live in warps 0 and 1
         nc = __reduce_or_sync(0xffffffffu, nc);
