@@ -158,5 +158,11 @@ __device__ __forceinline__ float scale_nominal_f(float alpha_2, float h, float l
     const float up = alpha_2 * (1.f - h);
     return __fadd_rn(__fmul_rn(up - lo, sigmoidf_(f)), lo);
 }
+// every rounding spelled out (`up - lo` cannot be contracted into an FMA whatever the calling context): the solver's accept / reject
+// sequence on the stress fixtures follows the reference only with the reference's separate roundings
+__device__ __forceinline__ float scale_nominal_strict(float alpha_2, float h, float lo, float f) {
+    const float up = __fmul_rn(alpha_2, __fsub_rn(1.f, h));
+    return __fadd_rn(__fmul_rn(__fsub_rn(up, lo), sigmoidf_(f)), lo);
+}
 
 }  // namespace fiode

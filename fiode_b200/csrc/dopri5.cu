@@ -220,22 +220,22 @@ __device__ __forceinline__ void eval_rhs(const SolveArgs& a, const Smem& S, int 
         }
     }
     __syncthreads();
-    // barrier projection, pass A: one row per thread, all max_iter midpoints, record mu_k + mask
+    // barrier projection.  The element-wise part first, spread over the whole CTA (one correctly rounded exp through fp64 per
+    // element: ten per row on the one or two row warps was a quarter of pass A, with every other warp waiting at the barrier)
+    for (int e = t; e < R * NH; e += kThreads) {
+        const int r = e / NH, i = e - r * NH;
+        const float h = S.ys[r * SROW + i];
+        const float lo = barrier_lower(a.w.alpha_1, a.w.sigma_1, h);
+        if (a.w.scale_nominal) S.ft[r * SROW + i] = scale_nominal_strict(a.w.alpha_2, h, lo, S.ft[r * SROW + i]);
+        S.lo[r * SROW + i] = lo;
+    }
+    __syncthreads();
+    // pass A: one row per thread, all max_iter midpoints, record mu_k + mask
     unsigned nc = 0;
     if (t < R) {
         float ft[NH], lo[NH];
 #pragma unroll
-        for (int i = 0; i < NH; ++i) {
-            const float h = S.ys[t * SROW + i];
-            lo[i] = barrier_lower(a.w.alpha_1, a.w.sigma_1, h);
-            float f = S.ft[t * SROW + i];
-            if (a.w.scale_nominal) {
-                f = scale_nominal_f(a.w.alpha_2, h, lo[i], f);
-                S.ft[t * SROW + i] = f;
-            }
-            ft[i] = f;
-            S.lo[t * SROW + i] = lo[i];
-        }
+        for (int i = 0; i < NH; ++i) { ft[i] = S.ft[t * SROW + i]; lo[i] = S.lo[t * SROW + i]; }
         nc = bisect_all_ilp(ft, lo, a.w.max_iter, a.w.tol, S.mus + t, Rp);
     }
     if (t < 64) {  // R <= 64 -> rows live in warps 0 and 1
