@@ -139,15 +139,24 @@ __device__ __forceinline__ void eval_rhs(const SolveArgs& a, const Smem& S, int 
     // layer 1: z1[r][j] = relu(c[r][j] + Q1[j,:] . h[r,:])
     {
         const int j = t & 127;
-        for (int r = t >> 7; r < R; r += 2) {
-            const float4 h0 = *reinterpret_cast<const float4*>(S.ys + r * SROW);
-            const float4 h1 = *reinterpret_cast<const float4*>(S.ys + r * SROW + 4);
-            const float2 h2 = *reinterpret_cast<const float2*>(S.ys + r * SROW + 8);
-            float z = S.c[r * NM + j];
-            z = fmaf(q1[0], h0.x, z); z = fmaf(q1[1], h0.y, z); z = fmaf(q1[2], h0.z, z); z = fmaf(q1[3], h0.w, z);
-            z = fmaf(q1[4], h1.x, z); z = fmaf(q1[5], h1.y, z); z = fmaf(q1[6], h1.z, z); z = fmaf(q1[7], h1.w, z);
-            z = fmaf(q1[8], h2.x, z); z = fmaf(q1[9], h2.y, z);
-            S.z1[r * NM + j] = fmaxf(z, 0.f);
+        // four rows per pass: the ten dependent FMAs of a row are the latency, independent rows hide it (same order per row)
+        for (int r0 = t >> 7; r0 < R; r0 += 8) {
+            float z[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int r = min(r0 + 2 * u, Rp - 1);
+                const float4 h0 = *reinterpret_cast<const float4*>(S.ys + r * SROW);
+                const float4 h1 = *reinterpret_cast<const float4*>(S.ys + r * SROW + 4);
+                const float2 h2 = *reinterpret_cast<const float2*>(S.ys + r * SROW + 8);
+                float zz = S.c[r * NM + j];
+                zz = fmaf(q1[0], h0.x, zz); zz = fmaf(q1[1], h0.y, zz); zz = fmaf(q1[2], h0.z, zz); zz = fmaf(q1[3], h0.w, zz);
+                zz = fmaf(q1[4], h1.x, zz); zz = fmaf(q1[5], h1.y, zz); zz = fmaf(q1[6], h1.z, zz); zz = fmaf(q1[7], h1.w, zz);
+                zz = fmaf(q1[8], h2.x, zz); zz = fmaf(q1[9], h2.y, zz);
+                z[u] = zz;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (r0 + 2 * u < R) S.z1[(r0 + 2 * u) * NM + j] = fmaxf(z[u], 0.f);
         }
     }
     __syncthreads();
@@ -203,20 +212,31 @@ __device__ __forceinline__ void eval_rhs(const SolveArgs& a, const Smem& S, int 
     // (threads 240..255 shadow group 0)
     {
         const int g = (t >> 3) % 30, ks = t & 7, o = g % NH, rr = g / NH;
-        for (int r0 = 0; r0 < R; r0 += 3) {
-            const int r = min(r0 + rr, Rp - 1);
-            const float* z = S.z2 + r * NM + ks * 4;
-            float acc = 0.f;
+        // four passes of 3 rows in flight per thread: independent 16-FMA + 3-shuffle chains, same order per output as before
+        for (int r0 = 0; r0 < R; r0 += 12) {
+            float acc[4];
 #pragma unroll
-            for (int kk = 0; kk < 4; ++kk) {
-                const float4 v = *reinterpret_cast<const float4*>(z + kk * 32);
-                acc = fmaf(q3[4 * kk + 0], v.x, acc); acc = fmaf(q3[4 * kk + 1], v.y, acc);
-                acc = fmaf(q3[4 * kk + 2], v.z, acc); acc = fmaf(q3[4 * kk + 3], v.w, acc);
+            for (int u = 0; u < 4; ++u) {
+                const int r = min(r0 + 3 * u + rr, Rp - 1);
+                const float* z = S.z2 + r * NM + ks * 4;
+                float a_ = 0.f;
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) {
+                    const float4 v = *reinterpret_cast<const float4*>(z + kk * 32);
+                    a_ = fmaf(q3[4 * kk + 0], v.x, a_); a_ = fmaf(q3[4 * kk + 1], v.y, a_);
+                    a_ = fmaf(q3[4 * kk + 2], v.z, a_); a_ = fmaf(q3[4 * kk + 3], v.w, a_);
+                }
+                acc[u] = a_;
             }
-            acc += __shfl_xor_sync(0xffffffffu, acc, 1);
-            acc += __shfl_xor_sync(0xffffffffu, acc, 2);
-            acc += __shfl_xor_sync(0xffffffffu, acc, 4);
-            if (ks == 0 && t < 240 && r0 + rr < R) S.ft[(r0 + rr) * SROW + o] = acc + b3o;
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                acc[u] += __shfl_xor_sync(0xffffffffu, acc[u], 1);
+                acc[u] += __shfl_xor_sync(0xffffffffu, acc[u], 2);
+                acc[u] += __shfl_xor_sync(0xffffffffu, acc[u], 4);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ks == 0 && t < 240 && r0 + 3 * u + rr < R) S.ft[(r0 + 3 * u + rr) * SROW + o] = acc[u] + b3o;
         }
     }
     __syncthreads();
