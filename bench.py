@@ -298,17 +298,17 @@ STAGES = [
 ]
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture (profiles/r01g_ncu_full_summary.md, one 4096-image launch)
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture (profiles/r01h_ncu_full_summary.md, one 4096-image launch)
 # (profiles/r01c_ncu_full_summary.md; re-measure when a kernel changes).  Keyed by the kernel named in STAGES / the solver.
 NCU_TRAFFIC_BYTES = {
-    'rfft2_kernel<32>': 50.37e6 + 4.19e6,
-    'irfft32_mix3_wide_kernel': 53.93e6 + 477.15e6,
-    'gemm_tc_kernel<s2d,32>': 536.93e6 + 114.70e6,
-    'rfft2_kernel<16,fm>': 134.24e6 + 100.31e6,
+    'rfft2_kernel<32>': 50.37e6 + 4.59e6,
+    'irfft32_mix3_wide_kernel': 53.95e6 + 476.89e6,
+    'gemm_tc_kernel<s2d,32>': 536.93e6 + 114.31e6,
+    'rfft2_kernel<16,fm>': 134.24e6 + 100.68e6,
     'gemm_tc_kernel<row,128> batched': 156.84e6 + 245.81e6,
-    'irfft2_kernel<16,fm>': 302.02e6 + 229.64e6,
-    'gemm_tc_kernel<s2d,64>': 268.54e6 + 46.07e6,
-    'dopri5_simplex_batched_kernel': 0.60e6,
+    'irfft2_kernel<16,fm>': 302.05e6 + 228.97e6,
+    'gemm_tc_kernel<s2d,64>': 268.56e6 + 46.21e6,
+    'dopri5_simplex_batched_kernel': 0.55e6,
 }
 
 
@@ -368,7 +368,7 @@ def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
     traffic = NCU_TRAFFIC_BYTES.get(top['kernel'])
     if traffic and top['kernel'] != 'dopri5_simplex_batched_kernel':
         traffic *= n_stage / 4096.             # the capture ran one 4096-image launch; these kernels stream, bytes scale with images
-    rf.update(traffic=traffic, traffic_source='profiles/r01g_ncu_full_summary.md (4096-image launch, scaled to the %d images of this launch)' % n_stage,
+    rf.update(traffic=traffic, traffic_source='profiles/r01h_ncu_full_summary.md (4096-image launch, scaled to the %d images of this launch)' % n_stage,
               kernel=top['kernel'], stage=top['stage'], ms_per_launch=top['ms'], launches_per_step=top['launches_per_step'], peak_source=pk['source'],
               note='algorithmic bytes / flops of SURVEY 8(d) over the CUDA-event time of that launch; tensor-core stages run the '
                    'fp16x2-split FP32 emulation (3 MMAs per product), so their ceiling is peak / 3; see DESIGN.md section 4',
