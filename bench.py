@@ -211,7 +211,7 @@ def certify_bench(ivp, device, pk, world=1, iters=2):
                                    'be bound by; ncu: issue-bound (profiles/)' % (3 * tf / pk['bf16'], tf / FFMA_PEAK_TFLOPS)))
 
 
-def fi_step_bench(device, pk, world, iters=10, warm=3):
+def fi_step_bench(device, pk, world, iters=10, warm=8):
     """Secondary metric (BASELINE config 3): one data-parallel FI training step = sampler + backbone forward (train
     mode) + fused FI loss (B=128, S=h_sample_size=256 -> 32 768 rows, dropout 0.5) + loss.backward() through every
     adjoint down to the 33 parameters + ONE flat-buffer gradient all-reduce (NCCL when world > 1).  No optimizer

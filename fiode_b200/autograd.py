@@ -4,23 +4,32 @@ reference's graph does (pl_modules.py:504-506 `loss.backward()` through models_o
 libs/ortho_conv/layers.py:50-105).  No torch arithmetic on the path."""
 from __future__ import annotations
 
+import os
+
 import torch
 from torch.autograd import Function
 
 from . import ops
 
 
+_SAVE_MINV = os.environ.get('FIODE_SAVE_MINV', '1') != '0'     # A/B switch: 0 = the adjoint inverts (I + A) again
+
+
 class CayleyLinearQ(Function):
     """Q = cayley(alpha * W / ||W||), layers.py:103-104."""
     @staticmethod
     def forward(ctx, weight, alpha):
-        ctx.save_for_backward(weight, alpha)
-        return ops.cayley_linear(weight, alpha)
+        if not _SAVE_MINV:
+            ctx.save_for_backward(weight, alpha)
+            return ops.cayley_linear(weight, alpha)
+        Q, minv = ops.cayley_linear(weight, alpha, save_minv=True)
+        ctx.save_for_backward(weight, alpha, minv)       # (I + A)^-1: the adjoint does not invert again
+        return Q
 
     @staticmethod
     def backward(ctx, gQ):
-        weight, alpha = ctx.saved_tensors
-        gW, ga = ops.cayley_linear_bwd(weight, alpha, gQ)
+        weight, alpha, *rest = ctx.saved_tensors
+        gW, ga = ops.cayley_linear_bwd(weight, alpha, gQ, minv=rest[0] if rest else None)
         return gW, ga.reshape(alpha.shape)
 
 

@@ -297,7 +297,7 @@ size_t cayley_linear_ws(int cout, int cin) {
 
 // Q = cayley(alpha * W / (||W||_F * norm_mult))
 int cayley_linear_impl(const float* W, const float* alpha, int cout, int cin, float norm_mult, float* Q, void* ws,
-                       size_t ws_bytes, cudaStream_t st) {
+                       size_t ws_bytes, cudaStream_t st, float* M_save) {
     if (ws_bytes < cayley_linear_ws(cout, cin)) { set_error("cayley_linear: workspace too small"); return -1; }
     const int tr = cin > cout;
     const int R = tr ? cin : cout, n = tr ? cout : cin;
@@ -330,6 +330,7 @@ int cayley_linear_impl(const float* W, const float* alpha, int cout, int cin, fl
     count_launch(1);
     float* M = nullptr;
     if ((rc = gj_inverse(X, Y, n, &M, st))) return rc;
+    if (M_save) FIODE_CUDA(cudaMemcpyAsync(M_save, M, (size_t)n * n * sizeof(float), cudaMemcpyDeviceToDevice, st));   // for the adjoint
     float* out_top = tr ? Qfull : Q;
     if ((rc = gemm_nt(M, n, ImAT, n, n, n, n, nullptr, 1.f, 0, out_top, n, gws, gws_bytes, st))) return rc;
     if (has_v) {
@@ -556,7 +557,7 @@ size_t cayley_linear_bwd_ws(int cout, int cin) {
 }
 
 int cayley_linear_bwd_impl(const float* W, const float* alpha, int cout, int cin, float norm_mult, const float* gQ,
-                           float* gW, float* galpha, void* ws, size_t ws_bytes, cudaStream_t st) {
+                           float* gW, float* galpha, void* ws, size_t ws_bytes, cudaStream_t st, const float* M_saved) {
     if (ws_bytes < cayley_linear_bwd_ws(cout, cin)) { set_error("cayley_linear_bwd: workspace too small"); return -1; }
     const int tr = cin > cout;
     const int R = tr ? cin : cout, n = tr ? cout : cin;
@@ -599,8 +600,12 @@ int cayley_linear_bwd_impl(const float* W, const float* alpha, int cout, int cin
     const int nb = (n * n + 255) / 256;
     cayley_prep2_kernel<<<nb, 256, 0, st>>>(Ws, Gm, n, has_v, X, ImAT);
     count_launch(1);
-    float* M = nullptr;
-    if ((rc = gj_inverse(X, Y, n, &M, st))) return rc;
+    const float* M = M_saved;                  // (I + A)^-1 kept by the forward call, else inverted again here
+    if (!M) {
+        float* Minv = nullptr;
+        if ((rc = gj_inverse(X, Y, n, &Minv, st))) return rc;
+        M = Minv;
+    }
     transpose_kernel<<<dim3((n + 31) / 32, (n + 31) / 32), dim3(32, 8), 0, st>>>(M, n, n, Mt);
     // ---- backward -----------------------------------------------------------------------------------
     cayley_bwd_prep_kernel<<<blocks, 256, 0, st>>>(gQ, cout, cin, tr, G, Gt2);
@@ -798,7 +803,13 @@ extern "C" int fiode_cayley_linear(const float* W, const float* alpha, int cout,
                                    size_t ws_bytes, void* stream) {
     if (!W || !alpha || !Q || !ws) { set_error("fiode_cayley_linear: null pointer"); return -1; }
     if (cout <= 0 || cin <= 0) { set_error("fiode_cayley_linear: bad shape"); return -1; }
-    return cayley_linear_impl(W, alpha, cout, cin, 1.f, Q, ws, ws_bytes, (cudaStream_t)stream);
+    return cayley_linear_impl(W, alpha, cout, cin, 1.f, Q, ws, ws_bytes, (cudaStream_t)stream, nullptr);
+}
+extern "C" int fiode_cayley_linear_save(const float* W, const float* alpha, int cout, int cin, float* Q, float* Minv,
+                                        void* ws, size_t ws_bytes, void* stream) {
+    if (!W || !alpha || !Q || !Minv || !ws) { set_error("fiode_cayley_linear_save: null pointer"); return -1; }
+    if (cout <= 0 || cin <= 0) { set_error("fiode_cayley_linear_save: bad shape"); return -1; }
+    return cayley_linear_impl(W, alpha, cout, cin, 1.f, Q, ws, ws_bytes, (cudaStream_t)stream, Minv);
 }
 
 static size_t conv_part_bytes(int n) { return align256((size_t)n * (n / 2 + 1) * sizeof(double)); }
@@ -828,7 +839,7 @@ extern "C" int fiode_cayley_conv(const float* w, const float* alpha, int cout, i
     const int F = n * (n / 2 + 1);
     if (k == 1) {
         // wfft[phi] = w[:, :, 0, 0] for every phi  =>  ||wfft||_F = sqrt(F) ||w||_F, one real Q (App. C-1)
-        return cayley_linear_impl(w, alpha, cout, cin, sqrtf((float)F), Qf, ws, ws_bytes, st);
+        return cayley_linear_impl(w, alpha, cout, cin, sqrtf((float)F), Qf, ws, ws_bytes, st, nullptr);
     }
     if (cout < cin) { set_error("fiode_cayley_conv: k>1 needs cout >= cin (got %d < %d)", cout, cin); return -1; }
     if (ws_bytes < conv_part_bytes(n)) { set_error("fiode_cayley_conv: workspace too small"); return -1; }
@@ -850,7 +861,14 @@ extern "C" int fiode_cayley_linear_bwd(const float* W, const float* alpha, int c
                                        float* galpha, void* ws, size_t ws_bytes, void* stream) {
     if (!W || !alpha || !gQ || !gW || !galpha || !ws) { set_error("fiode_cayley_linear_bwd: null pointer"); return -1; }
     if (cout <= 0 || cin <= 0) { set_error("fiode_cayley_linear_bwd: bad shape"); return -1; }
-    return cayley_linear_bwd_impl(W, alpha, cout, cin, 1.f, gQ, gW, galpha, ws, ws_bytes, (cudaStream_t)stream);
+    return cayley_linear_bwd_impl(W, alpha, cout, cin, 1.f, gQ, gW, galpha, ws, ws_bytes, (cudaStream_t)stream, nullptr);
+}
+extern "C" int fiode_cayley_linear_bwd_saved(const float* W, const float* alpha, int cout, int cin, const float* gQ,
+                                             const float* Minv, float* gW, float* galpha, void* ws, size_t ws_bytes,
+                                             void* stream) {
+    if (!W || !alpha || !gQ || !Minv || !gW || !galpha || !ws) { set_error("fiode_cayley_linear_bwd_saved: null pointer"); return -1; }
+    if (cout <= 0 || cin <= 0) { set_error("fiode_cayley_linear_bwd_saved: bad shape"); return -1; }
+    return cayley_linear_bwd_impl(W, alpha, cout, cin, 1.f, gQ, gW, galpha, ws, ws_bytes, (cudaStream_t)stream, Minv);
 }
 
 extern "C" size_t fiode_cayley_conv_bwd_workspace_bytes(int cout, int cin, int k, int n) {
@@ -864,7 +882,7 @@ extern "C" int fiode_cayley_conv_bwd(const float* w, const float* alpha, int cou
     cudaStream_t st = (cudaStream_t)stream;
     if (!w || !alpha || !gQf || !gw || !galpha || !ws) { set_error("fiode_cayley_conv_bwd: null pointer"); return -1; }
     const int F = n * (n / 2 + 1);
-    if (k == 1) return cayley_linear_bwd_impl(w, alpha, cout, cin, sqrtf((float)F), gQf, gw, galpha, ws, ws_bytes, st);
+    if (k == 1) return cayley_linear_bwd_impl(w, alpha, cout, cin, sqrtf((float)F), gQf, gw, galpha, ws, ws_bytes, st, nullptr);
     if (cout < cin || k * k > 9) { set_error("fiode_cayley_conv_bwd: needs cout >= cin and k <= 3"); return -1; }
     if (ws_bytes < fiode_cayley_conv_bwd_workspace_bytes(cout, cin, k, n)) { set_error("fiode_cayley_conv_bwd: workspace too small"); return -1; }
     char* p = reinterpret_cast<char*>(ws);

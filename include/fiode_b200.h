@@ -151,6 +151,13 @@ FIODE_API int fiode_cayley_conv_layer_bwd(const float* x, const float* Qf, const
 FIODE_API size_t fiode_cayley_linear_bwd_workspace_bytes(int cout, int cin);
 FIODE_API int fiode_cayley_linear_bwd(const float* W, const float* alpha, int cout, int cin, const float* gQ, float* gW,
                             float* galpha, void* ws, size_t ws_bytes, void* stream);
+/* Same pair with (I + A)^-1 handed from the forward call to its adjoint: Minv (n, n), n = min(cout, cin).  The reference's
+ * autograd keeps the forward's intermediates for backward (layers.py:50-60 under loss.backward()); without it the adjoint
+ * inverts again (n = 512: ~0.5 ms per layer per step).                                                              */
+FIODE_API int fiode_cayley_linear_save(const float* W, const float* alpha, int cout, int cin, float* Q, float* Minv,
+                             void* ws, size_t ws_bytes, void* stream);
+FIODE_API int fiode_cayley_linear_bwd_saved(const float* W, const float* alpha, int cout, int cin, const float* gQ,
+                                  const float* Minv, float* gW, float* galpha, void* ws, size_t ws_bytes, void* stream);
 /* adjoint of fiode_cayley_conv (layers.py:74-82): gQf as produced by the layer adjoints above
  * (k = 3: (F,cout,cin) complex64; k = 1: real (cout,cin)) -> gw (cout,cin,k,k), galpha (1).              */
 FIODE_API size_t fiode_cayley_conv_bwd_workspace_bytes(int cout, int cin, int k, int n);

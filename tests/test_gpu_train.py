@@ -34,6 +34,11 @@ def test_cayley_linear_bwd(cout, cin):
     gW, ga = ops.cayley_linear_bwd(W.to(DEV), alpha.to(DEV), gQ.to(DEV))
     assert rel(gW, Wc.grad) < 2e-4
     assert abs(float(ga) - float(ac.grad)) <= 2e-4 * max(1.0, abs(float(ac.grad)))
+    # the forward call's (I + A)^-1 handed to the adjoint (fiode_cayley_linear_save / _bwd_saved): same bits, no second inversion
+    Qd, minv = ops.cayley_linear(W.to(DEV), alpha.to(DEV), save_minv=True)
+    assert torch.equal(Qd, ops.cayley_linear(W.to(DEV), alpha.to(DEV))) and minv.shape == (min(cout, cin),) * 2
+    gW2, ga2 = ops.cayley_linear_bwd(W.to(DEV), alpha.to(DEV), gQ.to(DEV), minv=minv)
+    assert torch.equal(gW2, gW) and torch.equal(ga2, ga)
 
 
 @pytest.mark.parametrize('cout,cin,k,n', [(32, 3, 3, 32), (64, 32, 3, 16), (32, 128, 1, 16), (64, 256, 1, 8)])
