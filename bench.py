@@ -241,11 +241,15 @@ def fi_step_bench(device, pk, world, iters=10, warm=8):
     mod.compute_loss(x, y, Bt, act='relu').backward()          # creates the lazily initialised conv alphas
     reducer = FlatGradAllReduce(mod.parameters())
 
-    def step():
+    def compute():
         for p in reducer.params:
             p.grad = None
         loss = mod.compute_loss(x, y, Bt, act='relu')
         loss.backward()
+        return loss
+
+    def step():
+        loss = compute()
         reducer.step()
         return loss
 
@@ -256,10 +260,18 @@ def fi_step_bench(device, pk, world, iters=10, warm=8):
     launches = (fiode_b200.launch_count() - c0) // iters
     # the step is launch-bound on the host: capture it once in a CUDA graph and replay (fiode_b200/graphs.py)
     ms, graphed = ms_eager, False
-    if world == 1 or os.environ.get('FIODE_GRAPH_NCCL') == '1':
+    if True:
         try:
             from fiode_b200.graphs import GraphedStep
-            gstep = GraphedStep(step, warmup=1)
+            if world == 1 or os.environ.get('FIODE_GRAPH_NCCL') == '1':
+                gstep = GraphedStep(step, warmup=1)
+            else:       # N > 1: forward + backward replayed from the graph, the flat NCCL all-reduce launched eagerly after it
+                gcompute = GraphedStep(compute, warmup=1)
+
+                def gstep():
+                    loss = gcompute()
+                    reducer.step()
+                    return loss
             gstep(); gstep()
             ms, graphed = timed(gstep, iters) / iters, True
             step = gstep
@@ -276,7 +288,7 @@ def fi_step_bench(device, pk, world, iters=10, warm=8):
                 unit='steps/s (whole job)', ms_per_step=ms, ms_per_step_eager=ms_eager, cuda_graph=graphed, gpu_launches=launches, rows_per_step=rows,
                 grad_floats=reducer.numel, allreduce_bytes=4 * reducer.numel,
                 algorithmic_tflops=flop / (ms * 1e-3) / 1e12, loss=float(step().detach()),
-                **({} if graphed or world > 1 else {'graph_error': locals().get('graph_error')}),
+                **({} if graphed else {'graph_error': locals().get('graph_error')}),
                 note='forward + backward to all 33 parameters + one flat all-reduce; kernels are the first correct versions '
                      '(FFMA GEMMs, per-layer launches), not yet tuned')
 
