@@ -102,6 +102,7 @@ SIGNATURES = {
     'fiode_grid_enumerate': (I, [I, I, LL, LL, P, P, SZ, P]),
     'fiode_dopri5_workspace_bytes': (SZ, [I]),
     'fiode_dopri5_simplex': (I, [C.POINTER(DynWeights), P, P, I, I, P, I, F64, F64, LL, P, P, P, SZ, I, P]),
+    'fiode_dopri5_simplex_logged': (I, [C.POINTER(DynWeights), P, P, I, I, P, I, F64, F64, LL, P, P, P, SZ, I, P, P, LL, P]),
     'fiode_dopri5_max_concurrent_solves': (I, [I, I]),
     'fiode_rhs_train_workspace_bytes': (SZ, [LL]),
     'fiode_rhs_fwd_train': (I, [C.POINTER(DynWeights), P, P, LL, P, P, P, P, P, P, SZ, P]),

@@ -34,6 +34,7 @@ struct SolveArgs {
     const double* t; int nt; float rtol, atol; long long max_steps;
     float* out; fiode_solve_stats* stats; SolveCtl* ctl;
     int G, C;                     // cluster mode: G independent solves of B rows each, C CTAs (one cluster) per solve
+    double* xlog_dt; float* xlog_ratio; long long xlog_cap;   // optional caller-owned attempt log (per solve: xlog_cap entries)
 };
 
 struct ClusterSlot { double s0, s1; unsigned orw; unsigned pad; };
@@ -439,6 +440,10 @@ __global__ void __launch_bounds__(kThreads, 1) dopri5_simplex_kernel(const Solve
                 stats->dts[n_logged] = dt; stats->ratios[n_logged] = ratio;
             }
             if (n_logged < FIODE_LOG_STEPS) ++n_logged;
+            if (a.xlog_dt && comm.rank == 0 && t == 0 && nsteps_total < a.xlog_cap) {
+                a.xlog_dt[(size_t)solve * a.xlog_cap + nsteps_total] = dt;
+                a.xlog_ratio[(size_t)solve * a.xlog_cap + nsteps_total] = ratio;
+            }
             if (ratio <= 1.f) {
                 // accept: fit the quartic interpolant (interp._interp_fit), advance, FSAL
                 for (int e = t; e < R * NH; e += kThreads) {
@@ -511,7 +516,22 @@ extern "C" int fiode_dopri5_simplex(const fiode_dyn_weights* w, const float* h0,
                                     int B, const double* t, int nt, double rtol, double atol,
                                     long long max_num_steps, float* out, fiode_solve_stats* stats, void* ws,
                                     size_t ws_bytes, int rows_per_cta, void* stream) {
+    return fiode_dopri5_simplex_logged(w, h0, s, s_rows, B, t, nt, rtol, atol, max_num_steps, out, stats, ws, ws_bytes,
+                                       rows_per_cta, nullptr, nullptr, 0, stream);
+}
+
+// Same solve with a caller-owned log of EVERY step attempt (dt as the controller held it in fp64, error ratio in fp32):
+// the differentiable solve replays the accepted ones.  Attempts beyond log_capacity are not recorded; the attempt count is
+// stats->n_accept + stats->n_reject, so a caller that sees more attempts than capacity re-runs with a larger log.
+extern "C" int fiode_dopri5_simplex_logged(const fiode_dyn_weights* w, const float* h0, const float* s, int s_rows,
+                                           int B, const double* t, int nt, double rtol, double atol,
+                                           long long max_num_steps, float* out, fiode_solve_stats* stats, void* ws,
+                                           size_t ws_bytes, int rows_per_cta, double* log_dts, float* log_ratios,
+                                           long long log_capacity, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
+    if ((log_dts == nullptr) != (log_ratios == nullptr) || log_capacity < 0 || (log_dts && log_capacity == 0)) {
+        set_error("fiode_dopri5_simplex_logged: log_dts / log_ratios / log_capacity must be given together"); return -1;
+    }
     if (!w || !h0 || !s || !t || !out || !stats || !ws) { set_error("fiode_dopri5_simplex: null pointer"); return -1; }
     if (B <= 0 || nt < 1) { set_error("fiode_dopri5_simplex: B=%d nt=%d", B, nt); return -1; }
     if (s_rows != 1 && s_rows != B) { set_error("fiode_dopri5_simplex: s_rows must be 1 or B"); return -1; }
@@ -534,6 +554,7 @@ extern "C" int fiode_dopri5_simplex(const fiode_dyn_weights* w, const float* h0,
     a.w = *w; a.h0 = h0; a.s = s; a.s_rows = s_rows; a.B = B; a.R = R; a.t = t; a.nt = nt;
     a.rtol = (float)rtol; a.atol = (float)atol; a.max_steps = max_num_steps; a.out = out; a.stats = stats;
     a.ctl = reinterpret_cast<SolveCtl*>(ws); a.G = 1; a.C = G;
+    a.xlog_dt = log_dts; a.xlog_ratio = log_ratios; a.xlog_cap = log_capacity;
     void* args[] = {&a};
     FIODE_CUDA(cudaLaunchCooperativeKernel((void*)dopri5_simplex_kernel<false>, dim3(G), dim3(kThreads), args, smem, st));
     count_launch(1);
@@ -562,6 +583,7 @@ extern "C" int fiode_dopri5_simplex_batched(const fiode_dyn_weights* w, const fl
     a.w = *w; a.h0 = h0; a.s = s; a.s_rows = s_rows; a.B = B; a.R = R; a.t = t; a.nt = nt;
     a.rtol = (float)rtol; a.atol = (float)atol; a.max_steps = max_num_steps; a.out = out; a.stats = stats;
     a.ctl = nullptr; a.G = G; a.C = C;
+    a.xlog_dt = nullptr; a.xlog_ratio = nullptr; a.xlog_cap = 0;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(G * C)); cfg.blockDim = dim3(kThreads);
     cfg.dynamicSmemBytes = solver_smem_bytes(R); cfg.stream = st;

@@ -23,7 +23,7 @@ BETA = [[1 / 5], [3 / 40, 9 / 40], [44 / 45, -56 / 15, 32 / 9], [19372 / 6561, -
         [35 / 384, 0., 500 / 1113, 125 / 192, -2187 / 6784, 11 / 84]]
 C_MID = [6025192743 / 30085553152 / 2, 0., 51252292925 / 65400821598 / 2, -2691868925 / 45128329728 / 2,
          187940372067 / 1594534317056 / 2, -1776094331 / 19743644256 / 2, 11237099 / 235043384 / 2]
-MAX_LOGGED = 64        # FIODE_LOG_STEPS
+LOG_CAPACITY = 1024    # first size of the device attempt log; a solve with more attempts is re-run with a log that fits
 
 
 def _f32c(v):
@@ -39,17 +39,30 @@ def _axpy(dst, c, x):
     return ops.lincomb(dst, [(1.0, dst), (c, x)])
 
 
-def accepted_steps(stats, t0):
-    """[(t_left, dt)] of the accepted attempts, time in float64 like the device controller."""
-    n = stats.n_accept + stats.n_reject
-    if n > MAX_LOGGED or stats.n_logged < n:
-        raise NotImplementedError(f'differentiable solve: {n} step attempts exceed the {MAX_LOGGED}-entry device log')
+def accepted_steps(log, t0):
+    """[(t_left, dt)] of the accepted attempts of an attempt log [(dt, ratio)], time in float64 like the device controller."""
     steps, t = [], float(t0)
-    for i in range(n):
-        if stats.ratios[i] <= 1.0:
-            steps.append((t, float(stats.dts[i])))
-            t = t + float(stats.dts[i])
+    for dt, ratio in log:
+        if ratio <= 1.0:
+            steps.append((t, float(dt)))
+            t = t + float(dt)
     return steps
+
+
+def solve_with_log(dw, h0, s, t, rtol, atol, opts):
+    """Forward solve that keeps EVERY step attempt: the log lives in a caller-owned device buffer
+    (fiode_dopri5_simplex_logged); if a stiff solve outgrows it the solve -- deterministic -- is repeated with a log that
+    fits.  Trained dynamics need hundreds of attempts (profiles/: 272 for stress B at tol 1e-3)."""
+    cap = int(opts.get('log_capacity', LOG_CAPACITY))
+    while True:
+        res = ops.dopri5_simplex(dw, h0, s, t, rtol, atol, max_num_steps=opts.get('max_num_steps', 2 ** 31 - 1),
+                                 rows_per_cta=opts.get('rows_per_cta', 0), log_capacity=cap)
+        res.raise_for_status()
+        log = res.attempt_log()
+        if log is not None:
+            return res, log
+        st = res.stats()
+        cap = st.n_accept + st.n_reject
 
 
 class OdeSolve(Function):
@@ -58,10 +71,9 @@ class OdeSolve(Function):
     @staticmethod
     def forward(ctx, dyn, h0, s, t, rtol, atol, opts, Q1, Qx, Q2, Q3, b1, bx, b2, b3):
         dw = dyn.dyn_weights()
-        res = ops.dopri5_simplex(dw, h0, s, t, rtol, atol, max_num_steps=opts.get('max_num_steps', 2 ** 31 - 1),
-                                 rows_per_cta=opts.get('rows_per_cta', 0))
-        res.raise_for_status()
-        ctx.dyn, ctx.stats, ctx.t = dyn, res.stats(), [float(x) for x in t.detach().cpu().double()]
+        res, log = solve_with_log(dw, h0, s, t, rtol, atol, opts)
+        ctx.dyn, ctx.log, ctx.t = dyn, log, [float(x) for x in t.detach().cpu().double()]
+        ctx.stats = res.stats()
         ctx.save_for_backward(h0.detach(), s.detach())
         return res.out
 
@@ -71,7 +83,7 @@ class OdeSolve(Function):
         dyn, t = ctx.dyn, ctx.t
         dw = dyn.dyn_weights()
         QT = ops.dyn_transposes(dw, h0.device)
-        steps = accepted_steps(ctx.stats, t[0])
+        steps = accepted_steps(ctx.log, t[0])
         g_out = g_out.contiguous().float()
         # ---- replay ----------------------------------------------------------------------------------------
         y = h0.contiguous().float().clone()

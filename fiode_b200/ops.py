@@ -217,10 +217,22 @@ class SolveResult:
     """Device-resident result of one dopri5 solve.  ``stats()`` is the only host sync."""
     ERRORS = {1: 'underflow in dt {}', 2: 'non-finite values in state `y`', 3: 'max_num_steps exceeded'}
 
-    def __init__(self, out, stats_buf):
+    def __init__(self, out, stats_buf, log=None):
         self.out = out
         self._buf = stats_buf
         self._stats = None
+        self._log = log            # (dts fp64, ratios fp32, capacity) device buffers of fiode_dopri5_simplex_logged
+
+    def attempt_log(self):
+        """[(dt, ratio)] of every step attempt, or None if the caller-owned log was too small (re-run larger)."""
+        st = self.stats()
+        n = st.n_accept + st.n_reject
+        if self._log is None:
+            return [(float(st.dts[i]), float(st.ratios[i])) for i in range(n)] if n <= st.n_logged else None
+        dts, ratios, cap = self._log
+        if n > cap:
+            return None
+        return list(zip(dts[:n].cpu().tolist(), ratios[:n].cpu().tolist()))
 
     def stats(self) -> SolveStats:
         if self._stats is None:
@@ -235,10 +247,11 @@ class SolveResult:
         return self
 
 
-def dopri5_simplex(dw: DynWeights, h0, s, t, rtol, atol, max_num_steps=2 ** 31 - 1, rows_per_cta=0):
+def dopri5_simplex(dw: DynWeights, h0, s, t, rtol, atol, max_num_steps=2 ** 31 - 1, rows_per_cta=0, log_capacity=0):
     """Device-resident adaptive dopri5 over the simplex dynamics (replaces torchdiffeq.odeint at
     models.py:236-241).  h0 (B,10); s (1|B,10); t 1-D fp64 (device).  Returns SolveResult with
-    out (len(t), B, 10)."""
+    out (len(t), B, 10).  ``log_capacity`` > 0 keeps a device log of that many step attempts
+    (``SolveResult.attempt_log``); the stats struct alone holds the first 64."""
     h0, s = _f32(h0), _f32(s)
     B = h0.shape[0]
     t = t.detach().to(device=h0.device, dtype=torch.float64).contiguous()
@@ -247,10 +260,15 @@ def dopri5_simplex(dw: DynWeights, h0, s, t, rtol, atol, max_num_steps=2 ** 31 -
     stats = torch.zeros(C.sizeof(SolveStats), dtype=torch.uint8, device=h0.device)
     nb = lib().fiode_dopri5_workspace_bytes(B)
     ws = _ws(nb, h0.device)
-    check(lib().fiode_dopri5_simplex(C.byref(dw), ptr(h0), ptr(s), s.shape[0], B, ptr(t), nt, float(rtol), float(atol),
-                                     int(max_num_steps), ptr(out), ptr(stats), ptr(ws), nb, int(rows_per_cta),
-                                     stream_ptr()), 'fiode_dopri5_simplex')
-    return SolveResult(out, stats)
+    log = None
+    if log_capacity > 0:
+        log = (torch.zeros(log_capacity, dtype=torch.float64, device=h0.device),
+               torch.zeros(log_capacity, dtype=torch.float32, device=h0.device), int(log_capacity))
+    check(lib().fiode_dopri5_simplex_logged(C.byref(dw), ptr(h0), ptr(s), s.shape[0], B, ptr(t), nt, float(rtol), float(atol),
+                                            int(max_num_steps), ptr(out), ptr(stats), ptr(ws), nb, int(rows_per_cta),
+                                            ptr(log[0]) if log else None, ptr(log[1]) if log else None,
+                                            int(log_capacity), stream_ptr()), 'fiode_dopri5_simplex_logged')
+    return SolveResult(out, stats, log)
 
 
 # ---- forward-invariance training workload ---------------------------------------------------------------

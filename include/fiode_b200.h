@@ -317,6 +317,16 @@ FIODE_API int fiode_dopri5_simplex(const fiode_dyn_weights* w, const float* h0, 
                          float* out, fiode_solve_stats* stats, void* ws, size_t ws_bytes,
                          int rows_per_cta, void* stream);
 
+/* The same solve with a caller-owned device log of EVERY step attempt (fiode_solve_stats keeps the first
+ * FIODE_LOG_STEPS only): log_dts[i] = dt of attempt i as the fp64 controller held it, log_ratios[i] = its fp32 error
+ * ratio (accepted iff <= 1).  Trained FI-ODE dynamics take hundreds of attempts; the differentiable solve
+ * (train_ode pl_modules.py:490-500, PGD :189-199) replays the accepted ones.  Attempts beyond log_capacity are dropped;
+ * the attempt count is n_accept + n_reject, so the caller re-runs with a larger log if it overflowed.          */
+FIODE_API int fiode_dopri5_simplex_logged(const fiode_dyn_weights* w, const float* h0, const float* s, int s_rows, int B,
+                                const double* t, int nt, double rtol, double atol, long long max_num_steps,
+                                float* out, fiode_solve_stats* stats, void* ws, size_t ws_bytes, int rows_per_cta,
+                                double* log_dts, float* log_ratios, long long log_capacity, void* stream);
+
 /* G independent solves of B rows each (row g*B+r belongs to solve g) in one launch: one thread-block
  * cluster per solve, so every solve keeps ITS OWN batch-wide RMS norm and projection stop rule -- the
  * result of solve g equals fiode_dopri5_simplex on rows [g*B, (g+1)*B).  This is how whole batches

@@ -148,13 +148,17 @@ def _next_dt(dt, ratio):
     return dt * factor
 
 
-def odeint_dopri5(func, y0, t, rtol, atol, max_num_steps=2 ** 31 - 1, return_stats=False, differentiable=False):
-    """``differentiable=True`` keeps the autograd graph of the accepted stages (torchdiffeq's use_adjoint=False behaviour)."""
+def odeint_dopri5(func, y0, t, rtol, atol, max_num_steps=2 ** 31 - 1, return_stats=False, differentiable=False,
+                  forced_dts=None):
+    """``differentiable=True`` keeps the autograd graph of the accepted stages (torchdiffeq's use_adjoint=False behaviour).
+    ``forced_dts`` (test aid, not torchdiffeq): a list of ACCEPTED step sizes to take instead of running the controller --
+    step sizes are constants of torchdiffeq's graph, so two solvers fed the same sizes compute the same function of
+    (y0, parameters) and their gradients can be compared even where the controller's own sequence is chaotic."""
     with torch.set_grad_enabled(bool(differentiable) and torch.is_grad_enabled()):
-        return _odeint_dopri5(func, y0, t, rtol, atol, max_num_steps, return_stats)
+        return _odeint_dopri5(func, y0, t, rtol, atol, max_num_steps, return_stats, forced_dts)
 
 
-def _odeint_dopri5(func, y0, t, rtol, atol, max_num_steps=2 ** 31 - 1, return_stats=False):
+def _odeint_dopri5(func, y0, t, rtol, atol, max_num_steps=2 ** 31 - 1, return_stats=False, forced_dts=None):
     """func(t, y) -> dy/dt with y a Tensor or a tuple of Tensors (then func returns a
     Tensor/tuple of the same total size).  Returns (len(t), *y0.shape) (tuple-wrapped
     if y0 was a tuple).  Raises AssertionError exactly where torchdiffeq does."""
@@ -187,7 +191,11 @@ def _odeint_dopri5(func, y0, t, rtol, atol, max_num_steps=2 ** 31 - 1, return_st
     stats.nfe += 1
     # torchdiffeq's step-size heuristics run under torch.no_grad (misc._select_initial_step / _optimal_step_size): the
     # step sizes are constants of the autograd graph, gradients flow through the accepted stages only
-    dt = _initial_step(f, tcur, y.detach(), fcur.detach(), rtol_t, atol_t, stats).detach()
+    if forced_dts is None:
+        dt = _initial_step(f, tcur, y.detach(), fcur.detach(), rtol_t, atol_t, stats).detach()
+    else:
+        forced = [torch.as_tensor(float(d), dtype=torch.float64) for d in forced_dts]
+        dt = forced[0]
     t_left = tcur
     coef = [y] * 5
     sol = [flat0]
@@ -201,13 +209,16 @@ def _odeint_dopri5(func, y0, t, rtol, atol, max_num_steps=2 ** 31 - 1, return_st
             tol = atol_t + rtol_t * torch.max(y.abs(), y1.abs())
             ratio = _rms(err / tol).abs()
             stats.dts.append(float(dt)); stats.ratios.append(float(ratio))
-            if ratio <= 1:
+            if ratio <= 1 or forced_dts is not None:
                 coef = _interp_fit(y, y1, k, dt)
                 t_left, tcur, y, fcur = tcur, tcur + dt, y1, f1
                 stats.n_accept += 1
             else:
                 stats.n_reject += 1
-            dt = _next_dt(dt, ratio.detach())
+            if forced_dts is None:
+                dt = _next_dt(dt, ratio.detach())
+            elif stats.n_accept < len(forced):
+                dt = forced[stats.n_accept]
             nsteps += 1
         sol.append(_interp_eval(coef, t_left, tcur, t[i]))
     stats.t_final = float(tcur)

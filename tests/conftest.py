@@ -30,3 +30,9 @@ def pytest_collection_modifyitems(config, items):
 def sd():
     from tests import fixtures as fx
     return fx.synth_state_dict()
+
+
+@pytest.fixture(scope='session')
+def ops():
+    from fiode_b200 import ops as _ops
+    return _ops

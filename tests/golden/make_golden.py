@@ -244,6 +244,106 @@ def gen_fi():
     save('fi.pt', res)
 
 
+def gen_fi_state():
+    """Forward state the reference itself saves in compute_loss (pl_modules.py:390-466) and the gradients its own
+    loss.backward() produces *at the Cayley matrices* -- so that the CUDA backward (fiode_fi_loss_bwd,
+    fiode_barrier_project_bwd) can be fed the reference's bits (v, mu, nominal from BarrierProjectionFn's
+    ctx.save_for_backward, barrier_projection.py:270; post-activation z1, z2; V, Vdot returned by jvp, pl_modules.py:411-414)
+    and must then reproduce the reference's gradients to round-off, independent of the round-off active set
+    (v - nominal + mu > 0, barrier_projection.py:288-289) that separates two forward passes."""
+    print('[fi_state]')
+    import pl_modules
+    sd = fx.synth_state_dict()
+    res = {}
+    B, S = 16, 32
+    x = fx.synth_images(B)
+    y = fx.synth_labels(B)
+    y[0] = 9
+    from sampling.sampler import CompositeSampler, DecisionBoundarySampling
+    for name, sn, mix, samplers in (
+            ('uniform_sn1', True, [1.0, 0.0], None),
+            ('mixed_sn0', False, [0.5, 0.5], None),
+            ('boundary_sn0', False, [0.5, 0.5], 'db')):
+        mod = build_module(scale_nominal=sn, dropout=0.0, h_sample_size=S, sd=sd)
+        mod.train()
+        if samplers == 'db':
+            mod.sampler = CompositeSampler((10,), [DecisionBoundarySampling((10,)), DecisionBoundarySampling((10,))])
+        mod.sampler.device_initialize(torch.device('cpu'))
+        mod.sampler_scheduler.get_mixer_coefficients = lambda epoch, m=mix: list(m)
+        mod.epoch_off_scale = -1
+        dyn = mod.model.dyn_fun
+        cap = dict(act=[], Q={}, proj=[])
+        orig_qp = dyn.fast_qp_solver
+
+        def qp(lower, nominal, _o=orig_qp, _c=cap):
+            v = _o(lower, nominal)
+            if v.grad_fn is not None:
+                _c['proj'].append(tuple(t.detach().clone() for t in v.grad_fn.saved_tensors))
+            return v
+        dyn.fast_qp_solver = qp
+        orig_jvp = pl_modules.jvp
+
+        def jvp_cap(*a, _c=cap, **k):
+            out = orig_jvp(*a, **k)
+            _c['V'], _c['Vdot'] = out[0].detach().clone(), out[1].detach().clone()
+            return out
+        pl_modules.jvp = jvp_cap
+        hooks = [dyn.activation.register_forward_hook(lambda m, i, o, _c=cap: _c['act'].append(o.detach().clone()))]
+        for ln in ('hidden_to_mlp', 'U_x', 'mlp_to_mlp', 'mlp_to_hidden'):
+            def hk(m, i, o, _c=cap, _n=ln):
+                if _n not in _c['Q'] and m.Q.requires_grad:
+                    m.Q.retain_grad()
+                    _c['Q'][_n] = m.Q
+            hooks.append(getattr(dyn, ln).register_forward_hook(hk))
+
+        def pm_hook(m, i, o, _c=cap):
+            if 's' not in _c:
+                o.retain_grad()
+                _c['s'] = o
+        hooks.append(mod.model.init_coordinates.param_map.register_forward_hook(pm_hook))
+        torch.manual_seed(4242)
+        _, hs = mod.sampler(x, y, mod, S, B, mix)
+        h = hs[0].clone()
+        torch.manual_seed(4242)
+        mod.zero_grad()
+        try:
+            loss = mod.compute_loss(x, y, B, 'relu')
+            loss.backward()
+        finally:
+            pl_modules.jvp = orig_jvp
+            for hh in hooks:
+                hh.remove()
+        v, mu, lower, nominal = cap['proj'][0]
+        p = dict(mod.named_parameters())
+        pre = 'model.dyn_fun.'
+        res[name] = dict(
+            B=B, S=S, y=y, scale_nominal=sn, kappa=float(mod.logged['kappa']), h=h, s=cap['s'].detach().clone(),
+            f=v, mu=mu[:, 0].clone(), ft=nominal, lower=lower, z1=cap['act'][0], z2=cap['act'][1], V=cap['V'], Vdot=cap['Vdot'],
+            loss=loss.detach().clone(),
+            dQ1=cap['Q']['hidden_to_mlp'].grad.clone(), dQx=cap['Q']['U_x'].grad.clone(),
+            dQ2=cap['Q']['mlp_to_mlp'].grad.clone(), dQ3=cap['Q']['mlp_to_hidden'].grad.clone(),
+            db1=p[pre + 'hidden_to_mlp.bias'].grad.clone(), dbx=p[pre + 'U_x.bias'].grad.clone(),
+            db2=p[pre + 'mlp_to_mlp.bias'].grad.clone(), db3=p[pre + 'mlp_to_hidden.bias'].grad.clone(),
+            ds=cap['s'].grad.clone())
+        free = ~((v - nominal + mu) > 0)
+        print(f'  {name}: loss={float(loss):.6f} rows={v.shape[0]} free entries={int(free.sum())} '
+              f'rows with no free entry={int((free.sum(1) == 0).sum())} |dQ2|={float(res[name]["dQ2"].norm()):.4e}')
+    # stand-alone projection with the state BarrierProjectionFn saved (adds mu to the 'proj' entry of rhs.pt)
+    from barrier_projection.barrier_projection import FastBarrierProjectionNoUpper
+    g = torch.Generator().manual_seed(9)
+    nominal = torch.randn(300, 10, generator=g) * 3
+    lower = -torch.rand(300, 10, generator=g) * 2
+    _ = torch.rand(300, 10, generator=g)
+    gout = torch.randn(300, 10, generator=g)
+    lo_r, no_r = lower.clone().requires_grad_(True), nominal.clone().requires_grad_(True)
+    v = FastBarrierProjectionNoUpper(max_iter=30, tol=1e-4, verbose=False)(lo_r, no_r)
+    sv_v, sv_mu, _, _ = [t.detach().clone() for t in v.grad_fn.saved_tensors]
+    v.backward(gout)
+    res['proj'] = dict(nominal=nominal, lower=lower, v=sv_v, mu=sv_mu[:, 0].clone(), gout=gout, d_lower=lo_r.grad.clone(),
+                       d_nominal=no_r.grad.clone())
+    save('fi_state.pt', res)
+
+
 def gen_certify():
     """Grid functions of robustness/eval_utils.py and the certify loop body (restated around the
     reference's own h_vdot / eval_dot_light) on the T=10 grid."""
@@ -311,6 +411,70 @@ def gen_certify():
                                                out=torch.tensor(outs, dtype=torch.float64))
         print(f'  T={T} sn={sn} shift={shift}:', [f'{a:.4f}' for a, _ in outs])
     save('certify.pt', res)
+
+
+def gen_certify40(stride=1, shift=2.1, M=8, eps=0.141, save_it=True):
+    """BASELINE config 4 at full size: the reference's own h_vdot (robustness/certify_lipschitz.py:37-42) driven over
+    ALL 41 320 837 rows of grid_40 in the chunks of certify_lipschitz.py:104-121 (batches = 10 -> ten chunks of
+    4 132 083 rows + a 7-row tail) for M = 8 images, loop body restated from :122-143.  Rows come from the oracle's
+    C enumerator (oracle/grid_enum.c) in canonical order -- the reference's O(N^2) numpy generator would need minutes
+    and > 10 GB here; the set is the same (every consumer is a max over rows) and the chunk composition, which fixes the
+    batch-global bisection stop, is then the one the CUDA enumerator produces too.  'planted' dynamics: label-3 images
+    pushed by shift * (e_3 - 1/10) on mlp_to_hidden.bias so that both verdicts occur."""
+    print('[certify40]')
+    import certify_lipschitz as cl
+    from oracle import certify as oc
+    T, batches = 40, 10
+    sd = fx.synth_state_dict()
+    z = oc.boundary_grid_numerators_c(10, T)
+    res = dict(T=T, eps=eps, batches=batches, shift=shift, scale_nominal=False, rows=z.shape[0],
+               row_hash=oc.grid_row_hash(z), stride=stride)
+    if stride > 1:
+        z = z[::stride]
+    mod = build_module(scale_nominal=False, sd=sd)
+    dyn = mod.model.dyn_fun
+    with torch.no_grad():
+        e = torch.zeros(10); e[3] = 1.0
+        dyn.mlp_to_hidden.bias.add_(shift * (e - 0.1))
+    x = fx.synth_images(M, seed=1236)
+    labels = fx.synth_labels(M, seed=1237)
+    labels[:M // 2] = 3
+    std_min = min(mod.model.init_coordinates.param_map[0].std).item()
+    kappa = math.sqrt(2) * (1.0 / std_min) * eps
+    dist = math.sqrt(10) / T
+    eps_g = 1 / T
+    n = z.shape[0]
+    ebs = n // batches
+    nb = batches + (1 if n % batches else 0)
+    per_chunk = torch.zeros(M, nb, 2, dtype=torch.float64)
+    t0 = time.time()
+    with torch.no_grad():
+        s_all = mod.model.init_coordinates(x, dyn)[0]
+        for bi in range(nb):
+            zc = z[bi * ebs:(bi + 1) * ebs] if (bi + 1) * ebs < n else z[bi * ebs:]
+            for label in sorted(set(labels.tolist())):
+                eta = oc.grid_for_label(zc, T, label)          # eval_utils.py:64-69, float64 z/T -> .float()
+                eta_ub = eta.amax(dim=1) + eps_g
+                Lf = math.sqrt(10) * (dyn.sigma_1 * dyn.alpha_1 * torch.exp(dyn.sigma_1 * eta_ub)) + 1
+                perturb = (math.sqrt(2) * Lf) * dist
+                ind = eta == eta.max(dim=-1, keepdim=True).values
+                ind[:, label] = False
+                yv = torch.ones(eta.shape[0], dtype=torch.long) * label
+                for m in range(M):
+                    if int(labels[m]) != label:
+                        continue
+                    hx = cl.h_vdot(dyn, eta, s_all[m:m + 1], yv, ind)
+                    per_chunk[m, bi, 1] = (hx + kappa).max().item()
+                    per_chunk[m, bi, 0] = (hx + perturb + kappa).max().item()
+            print(f'  chunk {bi + 1}/{nb} ({zc.shape[0]} rows) done at {time.time() - t0:.0f} s', flush=True)
+    out = per_chunk.max(dim=1).values
+    near_zero = [(m, float(out[m, 0])) for m in range(M) if abs(float(out[m, 0])) < 3e-4]
+    res.update(x=x, labels=labels, s=s_all, kappa=kappa, out=out, per_chunk=per_chunk, near_zero=near_zero,
+               cpu_seconds=time.time() - t0, cpu_threads=torch.get_num_threads())
+    print('  out:', [f'{a:.4f}' for a in out[:, 0].tolist()], 'labels', labels.tolist(), 'near_zero', near_zero)
+    if save_it:
+        save('certify40.pt', res)
+    return res
 
 
 def gen_segway():
@@ -387,7 +551,8 @@ def gen_crown():
     save('crown.pt', res)
 
 
-GROUPS = dict(weights=gen_weights, layers=gen_layers, rhs=gen_rhs, ivp=gen_ivp, fi=gen_fi,
+GROUPS = dict(weights=gen_weights, layers=gen_layers, rhs=gen_rhs, ivp=gen_ivp, fi=gen_fi, fi_state=gen_fi_state,
+              certify40=gen_certify40,
               certify=gen_certify, segway=gen_segway, crown=gen_crown)
 
 if __name__ == '__main__':

@@ -311,6 +311,43 @@ def test_certify_matches_reference(ops, sd, key):
         assert abs(float(out[m, 0]) - v1) < 2e-4 + 1e-4 * abs(v1) and abs(float(out[m, 1]) - v2) < 2e-4 + 1e-4 * abs(v2)
 
 
+def _row_hash_torch(z):
+    """oracle.certify.grid_row_hash on the device (int64 arithmetic wraps like uint64)."""
+    key = torch.zeros(z.shape[0], dtype=torch.int64, device=z.device)
+    for j in range(8):
+        key = key * 256 + z[:, j].long()
+    for j in range(8, z.shape[1]):
+        key = key ^ (z[:, j].long() << (8 * (j - 8) + 5))
+    idx = torch.arange(1, z.shape[0] + 1, dtype=torch.int64, device=z.device)
+    return int((key * idx).sum().item()) & 0xFFFFFFFFFFFFFFFF
+
+
+def test_certify_grid_40_matches_reference(ops, sd):
+    """BASELINE config 4 at its real size: fiode_certify_grid over ALL 41 320 837 rows of grid_40 (batches = 10: ten chunks
+    of 4 132 083 rows + the 7-row tail) for 8 images, against the reference's own h_vdot driven over the same rows in
+    the same chunks (tests/golden/certify40.pt, generated by make_golden.py certify40 in ~11 CPU-minutes).  The planted
+    dynamics put the label-3 images on both sides of the threshold (|violation| 0.006 .. 0.06)."""
+    from fiode_b200 import grid as fgrid
+    c = fx.load_golden('certify40.pt')
+    e = torch.zeros(10); e[3] = 1.0
+    sd2 = dict(sd)
+    sd2[DYN + 'mlp_to_hidden.bias'] = sd[DYN + 'mlp_to_hidden.bias'] + c['shift'] * (e - 0.1)
+    dyn = fx.build_b200_model(sd2, scale_nominal=c['scale_nominal']).dyn_fun
+    gz = fgrid.boundary_grid_numerators(10, c['T'])
+    assert gz.shape[0] == c['rows'] == 41320837
+    assert _row_hash_torch(gz) == c['row_hash'], 'CUDA enumerator and the oracle enumerator disagree on rows or row order'
+    out, iters = ops.certify_grid(dyn.dyn_weights(), gz, c['T'], dev(c['s']), dev(c['labels']), c['kappa'],
+                                  batches=c['batches'], return_iters=True)
+    out = out.cpu().double()
+    want = c['out']
+    assert iters.shape == (8, 11) and bool((iters > 0).all()) and bool((iters <= 30).all())
+    assert (out - want).abs().max().item() < 1e-4 + 1e-5 * want.abs().max().item(), (out, want)
+    near = want[:, 0].abs() <= 3e-4                        # the stated margin; this fixture has none inside it
+    assert [m for m, _ in c['near_zero']] == near.nonzero()[:, 0].tolist()
+    assert torch.equal((out[:, 0] < 0)[~near], (want[:, 0] < 0)[~near])
+    assert bool((out[:, 0] < 0).any()) and bool((out[:, 0] > 0).any())     # both verdicts occur
+
+
 # ---- decision-boundary grid ------------------------------------------------------------------------------
 def test_grid_enumeration_small_sets():
     from fiode_b200 import grid

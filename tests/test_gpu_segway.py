@@ -15,15 +15,25 @@ def test_segway_grid_matches_reference():
     r = [g['r']] * 3
     eta, val, vmax = segway.certify_grid(g['ctrl'], g['P'], g['sizes'].tolist(), r, level=g['level'],
                                          levels=(g['lb'], g['ub']))
-    # the shell test compares an fp32 sum of three squares with the level: a point within one ulp of the
-    # level can fall either side; everything else must be the same point, in the same (grid) order
-    assert abs(eta.shape[0] - g['mask_count']) <= 2
-    if eta.shape[0] == g['mask_count']:
-        axes = oseg.grid_axes(g['sizes'].tolist(), r)
-        grid = oseg.grid_uniform_3d(g['sizes'].tolist(), r)
-        assert torch.equal(eta.cpu(), grid[g['mask_idx'].long()])
-        torch.testing.assert_close(val.cpu(), g['val'], rtol=1e-5, atol=1e-5)
+    # the shell test compares an fp32 sum of three squares with the level: a point within one ulp of the level can
+    # fall either side (at most 2 such points tolerated); every other point must be the same grid point, in grid
+    # order, with the same barrier derivative -- compared on the intersection of the two index sets, never skipped
+    grid = oseg.grid_uniform_3d(g['sizes'].tolist(), r)
+    where = {tuple(row): i for i, row in enumerate(grid.tolist())}
+    got_idx = torch.tensor([where[tuple(row)] for row in eta.cpu().tolist()], dtype=torch.long)   # KeyError = not a grid point
+    assert bool((got_idx[1:] > got_idx[:-1]).all()), 'compaction must keep grid order'
+    want_idx = g['mask_idx'].long()
+    common = np.intersect1d(got_idx.numpy(), want_idx.numpy())
+    assert (len(got_idx) - len(common)) + (len(want_idx) - len(common)) <= 2, (len(got_idx), len(want_idx), len(common))
+    assert len(common) >= g['mask_count'] - 2 and len(common) > 900
+    gi = torch.from_numpy(np.searchsorted(got_idx.numpy(), common))
+    wi = torch.from_numpy(np.searchsorted(want_idx.numpy(), common))
+    torch.testing.assert_close(val.cpu()[gi], g['val'][wi], rtol=1e-5, atol=1e-5)
+    want_max = float(g['val'][wi].max())
+    if len(common) == len(want_idx) == len(got_idx):
         assert abs(vmax - g['val_max']) <= 1e-5 * max(1.0, abs(g['val_max']))
+    else:
+        assert vmax >= want_max - 1e-5 * max(1.0, abs(want_max))
     lb2, ub2 = segway.shell_levels(g['P'], g['level'], g['r'])
     assert abs(lb2 - g['lb']) < 1e-6 and abs(ub2 - g['ub']) < 1e-6
 

@@ -306,3 +306,70 @@ def test_input_gradient_for_pgd(sd):
     # (eval mode detaches the cached Q only, layers.py:105; biases still receive gradients there as here)
     assert ivp.dyn_fun.mlp_to_mlp.weight.grad is None
     assert rel(xd.grad, xr.grad) < 1e-2, rel(xd.grad, xr.grad)
+
+
+def test_differentiable_solve_beyond_64_attempts(sd):
+    """A stiff solve (the sweep's stress-B dynamics: alpha_1 = 1000, alpha_2 = 200, scale_nominal, t_max = 5 -> a few hundred
+    attempts, some rejected) through OdeSolve: the attempt log is a caller-owned device buffer now (fiode_dopri5_simplex_logged),
+    not the 64-entry stats array.  Checked: (a) a log that overflows (capacity 32) is re-run and gives bit-identical gradients
+    to a log that fits; (b) the gradients agree with torch autograd through the oracle's restated dopri5 taking the SAME
+    accepted step sizes (step sizes are constants of torchdiffeq's graph; the controller's own sequence is chaotic here)."""
+    from oracle import dynamics as od, dopri5 as odp
+    from fiode_b200.ode_autograd import OdeSolve, accepted_steps
+    B, tol, t_max = 8, 1e-3, 5.0
+    g = torch.Generator().manual_seed(33)
+    s0 = torch.randn(B, 10, generator=g) * 0.5
+    h0 = fx.simplex_rows(B, seed=6)
+    ts = torch.tensor([0., 0.5 * t_max, t_max])
+    R = torch.randn(3, B, 10, generator=g)
+    kw = dict(scale_nominal=True, alpha_1=1000., alpha_2=200.)
+    ivp = fx.build_b200_model(sd, dropout=0.0, **kw).train()
+    dyn = ivp.dyn_fun
+    names = ['hidden_to_mlp', 'U_x', 'mlp_to_mlp', 'mlp_to_hidden']
+    lay = [getattr(dyn, n) for n in names]
+
+    def run(opts):
+        for p in dyn.parameters():
+            p.grad = None
+        s_dev, h_dev = s0.cuda().requires_grad_(True), h0.cuda().requires_grad_(True)
+        Qs = [l.orthogonal_weight_autograd() for l in lay]
+        out = OdeSolve.apply(dyn, h_dev, s_dev, ts, tol, tol, dict(opts), *Qs, *[l.bias for l in lay])
+        (out * R.cuda()).sum().backward()
+        grads = {'s': s_dev.grad.clone(), 'h0': h_dev.grad.clone()}
+        for n, l in zip(names, lay):
+            for kind in ('weight', 'bias', 'alpha'):
+                grads[f'{n}.{kind}'] = getattr(l, kind).grad.clone()
+        return out.detach(), grads, out.grad_fn
+
+    out_a, ga, fn_a = run({})
+    log = fn_a.log
+    n_att = len(log)
+    assert n_att > 64, f'fixture must exceed the old 64-entry log, got {n_att} attempts'
+    assert any(r > 1.0 for _, r in log), 'fixture must contain rejected attempts'
+    out_b, gb, fn_b = run(dict(log_capacity=32))             # overflows -> solve repeated with a log that fits
+    assert fn_b.log == log and torch.equal(out_a, out_b)
+    for k in ga:
+        assert torch.equal(ga[k], gb[k]), k
+
+    # oracle with the same accepted step sizes
+    steps = accepted_steps(log, 0.0)
+    cfg = fx.dyn_cfg(**kw)
+    sdc = dict(sd)
+    leaves = {}
+    for n in names:
+        for kind in ('weight', 'bias', 'alpha'):
+            k = f'{fx.DYN}{n}.{kind}'
+            sdc[k] = sd[k].clone().requires_grad_(True)
+            leaves[f'{n}.{kind}'] = sdc[k]
+    s_ref, h_ref = s0.clone().requires_grad_(True), h0.clone().requires_grad_(True)
+    f = lambda t, hh: od.eval_dot(hh, s_ref, sdc, cfg, None, fx.DYN, differentiable=True)
+    sol = odp.odeint_dopri5(f, h_ref, ts, tol, tol, differentiable=True, forced_dts=[dt for _, dt in steps])
+    (sol * R).sum().backward()
+    torch.testing.assert_close(out_a.cpu(), sol.detach(), rtol=2e-3, atol=2e-4)
+    want = {'s': s_ref.grad, 'h0': h_ref.grad}
+    want.update({k: v.grad for k, v in leaves.items()})
+    for k in want:
+        a, b = ga[k].detach().cpu().reshape(-1).double(), want[k].reshape(-1).double()
+        if a.numel() > 1:
+            cos = float(torch.nn.functional.cosine_similarity(a, b, dim=0))
+            assert cos > 0.95 and 0.7 < float(a.norm() / b.norm()) < 1.4, (k, cos, float(a.norm() / b.norm()))

@@ -193,3 +193,46 @@ def test_segway_matches_reference():
     xs, us = oseg.simulate(g['x0'], g['ctrl'], g['ts'])
     torch.testing.assert_close(xs, g['xs'], rtol=1e-6, atol=1e-7)
     torch.testing.assert_close(us, g['us'], rtol=1e-6, atol=1e-7)
+
+
+def test_c_grid_enumerator_matches_python_recursion_and_reference_rows():
+    """oracle/grid_enum.c against its specification (the Python recursion), the reference generator's own rows
+    (golden grid_4_8 / grid_10_10 from robustness/eval_utils.py:31-61) and count_samples_decision_boundary."""
+    g = fx.load_golden('certify.pt')
+    for n, T in ((4, 8), (10, 10), (5, 12), (3, 6), (4, 7)):
+        a, b = oc.boundary_grid_numerators(n, T), oc.boundary_grid_numerators_c(n, T)
+        assert np.array_equal(a, b), (n, T)
+        assert a.shape[0] == g['counts'].get((n, T), a.shape[0])
+    assert sorted(map(tuple, oc.boundary_grid_numerators_c(4, 8).tolist())) == sorted(map(tuple, g['grid_4_8'].tolist()))
+    assert np.array_equal(np.unique(oc.boundary_grid_numerators_c(10, 10), axis=0), g['grid_10_10_sorted'].numpy())
+    z40 = oc.boundary_grid_numerators_c(10, 40)
+    c40 = fx.load_golden('certify40.pt')
+    assert z40.shape[0] == g['counts'][(10, 40)] == c40['rows'] == 41320837
+    assert oc.grid_row_hash(z40) == c40['row_hash']
+
+
+def test_oracle_certify_grid_40_chunks_match_reference():
+    """The oracle's certify loop against the reference-generated grid_40 golden on the chunks that are affordable here:
+    the 7-row tail chunk for all 8 images and the first full chunk (4 132 083 rows) for the image closest to the
+    threshold.  (All 11 chunks x 8 images took 635 s of the reference's own h_vdot when the golden was made.)"""
+    c = fx.load_golden('certify40.pt')
+    sd = fx.synth_state_dict()
+    e = torch.zeros(10); e[3] = 1.0
+    sd2 = dict(sd)
+    sd2[DYN + 'mlp_to_hidden.bias'] = sd[DYN + 'mlp_to_hidden.bias'] + c['shift'] * (e - 0.1)
+    cfg = fx.dyn_cfg(scale_nominal=False)
+    Q = od.dyn_Q(sd2, DYN)
+    z = oc.boundary_grid_numerators_c(10, 40)
+    ebs = z.shape[0] // 10
+    tail = z[10 * ebs:]
+    assert tail.shape[0] == 7
+    for m in range(8):
+        label = int(c['labels'][m])
+        v1, v2 = oc.certify_image(oc.grid_for_label(tail, 40, label), c['s'][m:m + 1], label, sd2, cfg, eps=c['eps'], T=40,
+                                  batches=1, prefix=DYN, Q=Q)
+        assert abs(v1 - float(c['per_chunk'][m, 10, 0])) < 1e-5 and abs(v2 - float(c['per_chunk'][m, 10, 1])) < 1e-5
+    m = int(c['out'][:, 0].abs().argmin())
+    label = int(c['labels'][m])
+    v1, v2 = oc.certify_image(oc.grid_for_label(z[:ebs], 40, label), c['s'][m:m + 1], label, sd2, cfg, eps=c['eps'], T=40,
+                              batches=1, prefix=DYN, Q=Q)
+    assert abs(v1 - float(c['per_chunk'][m, 0, 0])) < 1e-5 and abs(v2 - float(c['per_chunk'][m, 0, 1])) < 1e-5
