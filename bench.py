@@ -234,6 +234,7 @@ def fi_step_bench(device, pk, world, iters=10, warm=8):
         sampler_scheduler=sch.CompositeSamplerScheduler([sch.ConstantScheduler(0.5), sch.ConstantScheduler(0.5)], [1., 1.]),
         dynamics=dyn, output=DefaultOutputFun(), init_fun=UniformInitFun((10,), param_map=pm), t_max=T_MAX,
         train_ode_tol=TOL, val_ode_tol=TOL, epoch_off_scale=10).to(device).train()
+    mod.current_epoch, mod.global_step = 0, 10 ** 9              # epoch 0 (scale_nominal on), kappa ramp finished (kappa_length=0)
     rank = int(os.environ.get('RANK', '0'))
     g = torch.Generator().manual_seed(1234 + rank)
     x = torch.rand(Bt, 3, 32, 32, generator=g).to(device)
@@ -242,8 +243,7 @@ def fi_step_bench(device, pk, world, iters=10, warm=8):
     reducer = FlatGradAllReduce(mod.parameters())
 
     def compute():
-        for p in reducer.params:
-            p.grad = None
+        reducer.prepare()              # one memset; the backward accumulates straight into the flat all-reduce buffer
         loss = mod.compute_loss(x, y, Bt, act='relu')
         loss.backward()
         return loss

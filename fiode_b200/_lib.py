@@ -25,6 +25,10 @@ class DynWeights(C.Structure):
                 ('scale_nominal', I), ('max_iter', I), ('tol', F32)]
 
 
+class FiOptions(C.Structure):
+    _fields_ = [('kappa_dev', P), ('dropout_p', F32), ('seed', C.c_ulonglong), ('step_dev', P)]
+
+
 class BackboneWeights(C.Structure):
     _fields_ = [(n, P) for n in ('mu', 'std', 'Qf0', 'b0', 'Q2', 'b2', 'Qf4', 'b4', 'Q6', 'b6',
                                  'Q9', 'b9', 'Q11', 'b11', 'Qfc', 'bfc', 'packed')]
@@ -92,6 +96,10 @@ SIGNATURES = {
     'fiode_sampler_fill': (I, [I, P, P, I, I, I, I, P, P]),
     'fiode_fi_loss_workspace_bytes': (SZ, [LL, I]),
     'fiode_fi_loss_fwd': (I, [C.POINTER(DynWeights), P, P, P, I, I, F32, P, P, P, P, P, P, P, P, P, P, P, SZ, P]),
+    'fiode_fi_loss_fwd_opt': (I, [C.POINTER(DynWeights), P, P, P, I, I, F32, P, P, C.POINTER(FiOptions), P, P, P, P, P, P, P, P, P, SZ, P]),
+    'fiode_fi_loss_bwd_opt': (I, [C.POINTER(DynWeights), P, P, P, I, I, F32, F32, P, P, C.POINTER(FiOptions), P, P, P, P, P, P, P, P, P, P, P, P, P, P, P,
+                                  P, SZ, P]),
+    'fiode_dropout_mask': (I, [F32, C.c_ulonglong, P, I, LL, P, P]),
     'fiode_fi_loss_bwd': (I, [C.POINTER(DynWeights), P, P, P, I, I, F32, F32, P, P, P, P, P, P, P, P, P,
                               P, P, P, P, P, P, P, P, P, SZ, P]),
     'fiode_segway_grid_workspace_bytes': (SZ, []),

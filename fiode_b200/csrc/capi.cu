@@ -16,14 +16,25 @@ int cuda_fail(cudaError_t e, const char* what) {
     set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
     return -100 - (int)e;
 }
+// Per-device caches: one process may drive several GPUs (cudaFuncSetAttribute and the SM count are per device).
+int current_device() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kMaxDevices) return 0;
+    return dev;
+}
 int sm_count() {
-    static int n = 0;
-    if (n == 0) {
-        int dev = 0;
-        if (cudaGetDevice(&dev) != cudaSuccess) return 148;
-        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    static std::atomic<int> n[kMaxDevices];
+    const int dev = current_device();
+    int v = n[dev].load(std::memory_order_relaxed);
+    if (v == 0) {
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+        n[dev].store(v, std::memory_order_relaxed);
     }
-    return n;
+    return v;
+}
+// true exactly once per (flag array, device): the caller then sets its per-device function attributes
+bool first_use_on_device(std::atomic<bool>* flags) {
+    return !flags[current_device()].exchange(true, std::memory_order_acq_rel);
 }
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 }  // namespace fiode

@@ -246,11 +246,10 @@ __global__ void __launch_bounds__(256) gj_block_update_kernel(const float* __res
 static int gj_inverse(float* X, float* Y, int n, float** result, cudaStream_t st) {
     if (n <= 128) {
         const size_t smem = (size_t)2 * n * n * sizeof(float);
-        static bool attr = false;
-        if (!attr) {
+        static std::atomic<bool> attr[kMaxDevices];
+        if (first_use_on_device(attr)) {
             cudaError_t e = cudaFuncSetAttribute(gj_inverse_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 128 * 128 * 4);
             if (e != cudaSuccess) return cuda_fail(e, "gj_inverse smem attr");
-            attr = true;
         }
         gj_inverse_smem_kernel<<<1, 1024, smem, st>>>(X, Y, n);
         count_launch(1);

@@ -1,5 +1,6 @@
 // fiode_b200/csrc/common.cuh -- shared device helpers for the FI-ODE hot path (sm_100a).
 #pragma once
+#include <atomic>
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
@@ -16,7 +17,10 @@ void set_error(const char* fmt, ...);
 int cuda_fail(cudaError_t e, const char* what);
 #define FIODE_CUDA(x) do { cudaError_t e__ = (x); if (e__ != cudaSuccess) return ::fiode::cuda_fail(e__, #x); } while (0)
 
-int sm_count();
+constexpr int kMaxDevices = 64;
+int current_device();
+int sm_count();                 // of the current device (cached per device)
+bool first_use_on_device(std::atomic<bool>* flags /*[kMaxDevices]*/);
 void count_launch(int n);
 
 // ---- Dormand-Prince(5,4) tableau (torchdiffeq 0.2.2 dopri5.py) -------------
@@ -165,4 +169,30 @@ __device__ __forceinline__ float scale_nominal_strict(float alpha_2, float h, fl
     return __fadd_rn(__fmul_rn(__fsub_rn(up, lo), sigmoidf_(f)), lo);
 }
 
+
+// ---- counter-based dropout masks (Philox4x32-10, Salmon et al. 2011; the generator family torch's CUDA dropout uses) ----
+// One call yields the four mask decisions of four consecutive hidden units of one row: element (row, k) of layer l at
+// step `step` is lane k & 3 of philox(counter = (row lo, row hi, (k >> 2) | l << 8, step lo), key = seed ^ step hi).
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const unsigned hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        const unsigned hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        k.x += 0x9E3779B9u; k.y += 0xBB67AE85u;
+    }
+    return c;
+}
+struct DropCfg {            // in-kernel dropout of the dynamics MLP (classification.py:96-102); thresh == 0 -> off
+    unsigned thresh;        // drop iff u32 < thresh  (thresh = p * 2^32)
+    float scale;            // 1 / (1 - p)
+    unsigned long long seed, step;
+};
+__device__ __forceinline__ float4 dropout_mask4(const DropCfg& d, long long row, int k4, int layer) {
+    const uint4 r = philox4x32_10(make_uint4((unsigned)row, (unsigned)((unsigned long long)row >> 32),
+                                             (unsigned)k4 | ((unsigned)layer << 8), (unsigned)d.step),
+                                  make_uint2((unsigned)d.seed ^ (unsigned)(d.step >> 32), (unsigned)(d.seed >> 32)));
+    return make_float4(r.x >= d.thresh ? d.scale : 0.f, r.y >= d.thresh ? d.scale : 0.f,
+                       r.z >= d.thresh ? d.scale : 0.f, r.w >= d.thresh ? d.scale : 0.f);
+}
 }  // namespace fiode

@@ -500,12 +500,11 @@ static size_t solver_smem_bytes(int R) {
 using namespace fiode;
 
 static int ensure_smem_attr() {
-    static bool done = false;
-    if (!done) {
+    static std::atomic<bool> done[kMaxDevices];
+    if (first_use_on_device(done)) {
         const int mx = (int)solver_smem_bytes(64);
         FIODE_CUDA(cudaFuncSetAttribute(dopri5_simplex_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
         FIODE_CUDA(cudaFuncSetAttribute(dopri5_simplex_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
-        done = true;
     }
     return 0;
 }

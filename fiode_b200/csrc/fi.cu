@@ -11,12 +11,10 @@
 //   * the autograd graph behind loss.backward() down to the Cayley matrices, the biases and the static
 //     feature s (barrier_projection.py:272-311, classification.py:96-115).
 #include "common.cuh"
+#include "rows.cuh"
 
 namespace fiode {
 
-int launch_rows_store(const fiode_dyn_weights* w, const float* h, const float* s, long long N, long long s_rows,
-                      long long s_group, float* ft, unsigned* notconv, const float* m1, const float* m2, float* z1,
-                      float* z2, cudaStream_t st);
 int gemm_nt(const float* A, int lda, const float* Bm, int ldb, int M, int N, int K, const float* bias, float alpha,
             int group_sort, float* y, int ldy, float* ws, size_t ws_bytes, cudaStream_t st);
 size_t gemm_nt_workspace(int M, int N, int K);
@@ -98,13 +96,15 @@ struct FiPart { double loss; unsigned long long eff; unsigned long long mac; };
 
 __global__ void __launch_bounds__(256) fi_finish_kernel(const float* __restrict__ ft, const float* __restrict__ h,
                                                         const int* __restrict__ y, long long N, int S,
-                                                        fiode_dyn_weights w, float kappa,
+                                                        fiode_dyn_weights w, float kappa_h,
+                                                        const float* __restrict__ kappa_d,
                                                         const unsigned* __restrict__ notconv, float* __restrict__ f,
                                                         float* __restrict__ mu_out, float* __restrict__ V,
                                                         float* __restrict__ Vdot, FiPart* __restrict__ part) {
     __shared__ double sl[8];
     __shared__ unsigned long long se[8], sm[8];
     const int K = stop_iter(*notconv, w.max_iter);
+    const float kappa = kappa_d ? *kappa_d : kappa_h;
     double loss = 0; unsigned long long eff = 0, mac = 0;
     for (long long r = blockIdx.x * 256ll + threadIdx.x; r < N; r += (long long)gridDim.x * 256) {
         float v[NH], lo[NH], hh[NH];
@@ -158,8 +158,9 @@ __global__ void __launch_bounds__(256) fi_finish_kernel(const float* __restrict_
 }
 // out[0] = loss (mean), out[1] = effective_batch_size, out[2] = mean_active_constraints, out[3] = bisection iterations
 __global__ void fi_reduce_kernel(const FiPart* __restrict__ part, int np, long long N, const unsigned* __restrict__ notconv,
-                                 int max_iter, float* __restrict__ out) {
+                                 int max_iter, float* __restrict__ out, unsigned long long* __restrict__ drop_step) {
     if (threadIdx.x == 0 && blockIdx.x == 0) {
+        if (drop_step) *drop_step += 1ull;      // next call (or next replay of a captured graph) draws fresh dropout masks
         double loss = 0; unsigned long long eff = 0, mac = 0;
         for (int i = 0; i < np; ++i) { loss += part[i].loss; eff += part[i].eff; mac += part[i].mac; }
         out[0] = (float)(loss / (double)N);
@@ -172,11 +173,13 @@ __global__ void fi_reduce_kernel(const FiPart* __restrict__ part, int np, long l
 // ---- backward ---------------------------------------------------------------------------------------------
 // d loss / d ftilde_raw for every row (App. C-4, C-5): loss seed -> projection Jacobian -> sigmoid rescale
 __global__ void __launch_bounds__(256) fi_seed_kernel(const float* __restrict__ h, const int* __restrict__ y,
-                                                      long long N, int S, fiode_dyn_weights w, float kappa,
+                                                      long long N, int S, fiode_dyn_weights w, float kappa_h,
+                                                      const float* __restrict__ kappa_d,
                                                       float gscale, const float* __restrict__ f,
                                                       const float* __restrict__ ft, const float* __restrict__ mu,
                                                       const float* __restrict__ V, const float* __restrict__ Vdot,
                                                       float* __restrict__ dft, float* __restrict__ ones) {
+    const float kappa = kappa_d ? *kappa_d : kappa_h;
     for (long long r = blockIdx.x * 256ll + threadIdx.x; r < N; r += (long long)gridDim.x * 256) {
         ones[r] = 1.f;
         const bool on = (Vdot[r] + kappa * V[r]) > 0.f;
@@ -207,10 +210,11 @@ __global__ void __launch_bounds__(256) fi_seed_kernel(const float* __restrict__ 
     }
 }
 // da = dz * 1[z > 0] * mask (in place on dz)
+// (in-kernel dropout: z > 0 implies the unit was kept, so its mask value is the constant 1 / (1 - p) = `scale`)
 __global__ void __launch_bounds__(256) relu_mask_bwd_kernel(float* __restrict__ dz, const float* __restrict__ z,
-                                                            const float* __restrict__ mask, size_t n) {
+                                                            const float* __restrict__ mask, float scale, size_t n) {
     for (size_t e = blockIdx.x * 256ull + threadIdx.x; e < n; e += (size_t)gridDim.x * 256) {
-        float d = z[e] > 0.f ? dz[e] : 0.f;
+        float d = z[e] > 0.f ? dz[e] * scale : 0.f;
         if (mask) d *= mask[e];
         dz[e] = d;
     }
@@ -269,19 +273,37 @@ extern "C" int fiode_fi_loss_fwd(const fiode_dyn_weights* w, const float* h, con
                                  float kappa, const float* m1, const float* m2, float* f, float* ftilde, float* mu,
                                  float* z1, float* z2, float* V, float* Vdot, float* out4, void* ws, size_t ws_bytes,
                                  void* stream) {
+    return fiode_fi_loss_fwd_opt(w, h, s, y, B, S, kappa, m1, m2, nullptr, f, ftilde, mu, z1, z2, V, Vdot, out4, ws, ws_bytes, stream);
+}
+
+static int check_fi_options(const char* who, const fiode_fi_options* o, const float* m1, const float* m2) {
+    if (!o) return 0;
+    if (!(o->dropout_p >= 0.f) || o->dropout_p >= 1.f) { set_error("%s: dropout_p must be in [0, 1)", who); return -1; }
+    if (o->dropout_p > 0.f && (m1 || m2)) { set_error("%s: pass either dropout masks or dropout_p, not both", who); return -1; }
+    return 0;
+}
+
+extern "C" int fiode_fi_loss_fwd_opt(const fiode_dyn_weights* w, const float* h, const float* s, const int* y, int B, int S,
+                                     float kappa, const float* m1, const float* m2, const fiode_fi_options* opt, float* f,
+                                     float* ftilde, float* mu, float* z1, float* z2, float* V, float* Vdot, float* out4,
+                                     void* ws, size_t ws_bytes, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
+    if (check_fi_options("fiode_fi_loss_fwd_opt", opt, m1, m2)) return -1;
+    const float* kappa_d = opt ? opt->kappa_dev : nullptr;
+    const float drop_p = opt ? opt->dropout_p : 0.f;
+    unsigned long long* step = (opt && drop_p > 0.f) ? opt->step_dev : nullptr;
     if (!w || !h || !s || !y || !f || !ftilde || !mu || !V || !Vdot || !out4 || !ws) { set_error("fiode_fi_loss_fwd: null pointer"); return -1; }
     if (B <= 0 || S <= 0) { set_error("fiode_fi_loss_fwd: B=%d S=%d", B, S); return -1; }
     const long long N = (long long)B * S;
     if (ws_bytes < fiode_fi_loss_workspace_bytes(N, B)) { set_error("fiode_fi_loss_fwd: workspace too small"); return -1; }
     unsigned* notconv = reinterpret_cast<unsigned*>(ws);
     FiPart* part = reinterpret_cast<FiPart*>(reinterpret_cast<char*>(ws) + 256);
-    int rc = launch_rows_store(w, h, s, N, B, S, ftilde, notconv, m1, m2, z1, z2, st);
+    int rc = launch_rows_store(w, h, s, N, B, S, ftilde, notconv, m1, m2, z1, z2, st, drop_p, opt ? opt->seed : 0ull, step);
     if (rc) return rc;
     const long long want = (N + 255) / 256;
     const int grid = (int)(want < kFiBlocks ? want : kFiBlocks);
-    fi_finish_kernel<<<grid, 256, 0, st>>>(ftilde, h, y, N, S, *w, kappa, notconv, f, mu, V, Vdot, part);
-    fi_reduce_kernel<<<1, 32, 0, st>>>(part, grid, N, notconv, w->max_iter, out4);
+    fi_finish_kernel<<<grid, 256, 0, st>>>(ftilde, h, y, N, S, *w, kappa, kappa_d, notconv, f, mu, V, Vdot, part);
+    fi_reduce_kernel<<<1, 32, 0, st>>>(part, grid, N, notconv, w->max_iter, out4, step);
     FIODE_CUDA(cudaGetLastError());
     count_launch(2);
     return 0;
@@ -292,7 +314,20 @@ extern "C" int fiode_fi_loss_bwd(const fiode_dyn_weights* w, const float* h, con
                                  const float* ftilde, const float* mu, const float* z1, const float* z2, const float* V,
                                  const float* Vdot, float* dQ1, float* dQx, float* dQ2, float* dQ3, float* db1, float* db2,
                                  float* db3, float* ds, void* ws, size_t ws_bytes, void* stream) {
+    return fiode_fi_loss_bwd_opt(w, h, s, y, B, S, kappa, grad_loss, m1, m2, nullptr, f, ftilde, mu, z1, z2, V, Vdot, dQ1, dQx,
+                                 dQ2, dQ3, db1, db2, db3, ds, ws, ws_bytes, stream);
+}
+
+extern "C" int fiode_fi_loss_bwd_opt(const fiode_dyn_weights* w, const float* h, const float* s, const int* y, int B, int S,
+                                     float kappa, float grad_loss, const float* m1, const float* m2,
+                                     const fiode_fi_options* opt, const float* f, const float* ftilde, const float* mu,
+                                     const float* z1, const float* z2, const float* V, const float* Vdot, float* dQ1,
+                                     float* dQx, float* dQ2, float* dQ3, float* db1, float* db2, float* db3, float* ds,
+                                     void* ws, size_t ws_bytes, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
+    if (check_fi_options("fiode_fi_loss_bwd_opt", opt, m1, m2)) return -1;
+    const float* kappa_d = opt ? opt->kappa_dev : nullptr;
+    const float dscale = (opt && opt->dropout_p > 0.f) ? 1.f / (1.f - opt->dropout_p) : 1.f;
     if (!w || !h || !s || !y || !f || !ftilde || !mu || !z1 || !z2 || !V || !Vdot || !dQ1 || !dQx || !dQ2 || !dQ3 || !db1 ||
         !db2 || !db3 || !ds || !ws) { set_error("fiode_fi_loss_bwd: null pointer"); return -1; }
     const long long N = (long long)B * S;
@@ -314,7 +349,7 @@ extern "C" int fiode_fi_loss_bwd(const fiode_dyn_weights* w, const float* h, con
     const long long want = (N + 255) / 256;
     const int grid = (int)(want < 4096 ? want : 4096);
     int rc;
-    fi_seed_kernel<<<grid, 256, 0, st>>>(h, y, N, S, *w, kappa, grad_loss, f, ftilde, mu, V, Vdot, dft, ones);
+    fi_seed_kernel<<<grid, 256, 0, st>>>(h, y, N, S, *w, kappa, kappa_d, grad_loss, f, ftilde, mu, V, Vdot, dft, ones);
     small_transpose_kernel<<<8, 256, 0, st>>>(w->Q3, NH, NM, Q3T);     // (10,128) -> (128,10)
     small_transpose_kernel<<<64, 256, 0, st>>>(w->Q2, NM, NM, Q2T);
     small_transpose_kernel<<<8, 256, 0, st>>>(w->Qx, NM, NH, QxT);     // (128,10) -> (10,128)
@@ -323,12 +358,12 @@ extern "C" int fiode_fi_loss_bwd(const fiode_dyn_weights* w, const float* h, con
     if ((rc = gemm_tn(dft, NH, ones, 1, NH, 1, N, 1.f, db3, 1, gws, gwb, st))) return rc;
     if ((rc = gemm_tn(dft, NH, z2, NM, NH, NM, N, 1.f, dQ3, NM, gws, gwb, st))) return rc;
     if ((rc = gemm_nt(dft, NH, Q3T, NH, Ni, NM, NH, nullptr, 1.f, 0, d2, NM, gws, gwb, st))) return rc;
-    relu_mask_bwd_kernel<<<4096, 256, 0, st>>>(d2, z2, m2, (size_t)N * NM);
+    relu_mask_bwd_kernel<<<4096, 256, 0, st>>>(d2, z2, m2, dscale, (size_t)N * NM);
     // layer 2
     if ((rc = gemm_tn(d2, NM, ones, 1, NM, 1, N, 1.f, db2, 1, gws, gwb, st))) return rc;
     if ((rc = gemm_tn(d2, NM, z1, NM, NM, NM, N, 1.f, dQ2, NM, gws, gwb, st))) return rc;
     if ((rc = gemm_nt(d2, NM, Q2T, NM, Ni, NM, NM, nullptr, 1.f, 0, d1, NM, gws, gwb, st))) return rc;
-    relu_mask_bwd_kernel<<<4096, 256, 0, st>>>(d1, z1, m1, (size_t)N * NM);
+    relu_mask_bwd_kernel<<<4096, 256, 0, st>>>(d1, z1, m1, dscale, (size_t)N * NM);
     // layer 1: z = Q1 h + b1 + Qx s + bx
     if ((rc = gemm_tn(d1, NM, h, NH, NM, NH, N, 1.f, dQ1, NH, gws, gwb, st))) return rc;
     segment_sum_kernel<<<B, NM, 0, st>>>(d1, B, S, D);
@@ -337,5 +372,31 @@ extern "C" int fiode_fi_loss_bwd(const fiode_dyn_weights* w, const float* h, con
     if ((rc = gemm_tn(D, NM, s, NH, NM, NH, B, 1.f, dQx, NH, gws, gwb, st))) return rc;
     if ((rc = gemm_nt(D, NM, QxT, NM, B, NH, NM, nullptr, 1.f, 0, ds, NH, gws, gwb, st))) return rc;
     FIODE_CUDA(cudaGetLastError());
+    return 0;
+}
+
+
+// The masks the forward draws for (seed, step): mask (N,128) of layer 0 (after hidden_to_mlp + U_x) or 1 (after mlp_to_mlp),
+// values 0 or 1 / (1 - p).  Lets a caller (and the parity tests) replay an in-kernel-dropout step with explicit masks.
+namespace fiode {
+__global__ void __launch_bounds__(256) dropout_mask_kernel(DropCfg d, int layer, long long N, float* __restrict__ out) {
+    for (long long e = blockIdx.x * 256ll + threadIdx.x; e < N * (NM / 4); e += (long long)gridDim.x * 256) {
+        const long long row = e / (NM / 4); const int k4 = (int)(e - row * (NM / 4));
+        *reinterpret_cast<float4*>(out + row * NM + k4 * 4) = dropout_mask4(d, row, k4, layer);
+    }
+}
+}  // namespace fiode
+extern "C" int fiode_dropout_mask(float dropout_p, unsigned long long seed, const unsigned long long* step_dev, int layer,
+                                  long long N, float* mask, void* stream) {
+    if (!mask || !step_dev || N <= 0 || (layer != 0 && layer != 1) || !(dropout_p > 0.f) || dropout_p >= 1.f) {
+        set_error("fiode_dropout_mask: bad arguments"); return -1; }
+    unsigned long long step = 0;
+    FIODE_CUDA(cudaMemcpyAsync(&step, step_dev, sizeof(step), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+    FIODE_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+    fiode::DropCfg d{(unsigned)fminf(dropout_p * 4294967296.f, 4294967040.f), 1.f / (1.f - dropout_p), seed, step};
+    const long long want = (N * (NM / 4) + 255) / 256;
+    fiode::dropout_mask_kernel<<<(unsigned)(want < 4096 ? want : 4096), 256, 0, (cudaStream_t)stream>>>(d, layer, N, mask);
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(1);
     return 0;
 }

@@ -10,6 +10,7 @@
 //   fiode_rhs_bwd_params  all evaluations stacked: dQ1, dQx, dQ2, dQ3, db1 (= dbx), db2, db3 in one set of GEMMs
 // following dynamics/classification.py:96-115 and the NoUpper projection adjoint barrier_projection.py:288-311.
 #include "common.cuh"
+#include "rows.cuh"
 
 namespace fiode {
 
@@ -19,9 +20,6 @@ size_t gemm_nt_workspace(int M, int N, int K);
 int gemm_tn(const float* A, int lda, const float* Bm, int ldb, int M, int N, long long K, float alpha, float* y, int ldy,
             float* ws, size_t ws_bytes, cudaStream_t st);
 size_t gemm_tn_workspace(int M, int N, long long K);
-int launch_rows_store(const fiode_dyn_weights* w, const float* h, const float* s, long long N, long long s_rows,
-                      long long s_group, float* ft, unsigned* notconv, const float* m1, const float* m2, float* z1,
-                      float* z2, cudaStream_t st);
 int launch_rhs_finish(const float* ft, const float* h, long long N, const fiode_dyn_weights* w, const unsigned* notconv,
                       float* f, float* mu, int* n_iter, cudaStream_t st);
 

@@ -77,8 +77,10 @@ __device__ __forceinline__ void set_static_feature(const fiode_dyn_weights& w, c
 // MLP over the tile whose h rows are in S.hs; result ftilde in S.ft ([TR][10]).
 struct TileAux {   // kStore extras (all optional): dropout masks in, activations out
     const float* m1; const float* m2; float* z1_out; float* z2_out; long long row0; int rows;
+    DropCfg drop;   // thresh > 0: masks drawn in the kernel (m1 / m2 NULL)
 };
-__device__ __forceinline__ void tile_mlp(const RowsSmem& S, const TileAux aux = TileAux{nullptr, nullptr, nullptr, nullptr, 0, 0}) {
+__device__ __forceinline__ void tile_mlp(const RowsSmem& S, const TileAux aux = TileAux{nullptr, nullptr, nullptr, nullptr, 0, 0,
+                                                                                         DropCfg{0u, 1.f, 0ull, 0ull}}) {
     const int t = threadIdx.x;
     // ---- L1: thread = (row pair rp / rp+32, k quarter) --------------------------------------
     {
@@ -90,6 +92,7 @@ __device__ __forceinline__ void tile_mlp(const RowsSmem& S, const TileAux aux = 
             const float2 b = *reinterpret_cast<const float2*>(S.hs + (rp + 32) * NH + i);
             ha[i] = a.x; ha[i + 1] = a.y; hb[i] = b.x; hb[i + 1] = b.y;
         }
+        float4 dma = make_float4(1.f, 1.f, 1.f, 1.f), dmb = dma;
 #pragma unroll 4
         for (int k = kq * 32; k < kq * 32 + 32; ++k) {
             const float4 q0 = *reinterpret_cast<const float4*>(S.Q1s + k * Q1S);
@@ -109,6 +112,14 @@ __device__ __forceinline__ void tile_mlp(const RowsSmem& S, const TileAux aux = 
             if (aux.m1) {   // classification.py:98: act(dropout(z))
                 if (rp < aux.rows) za *= aux.m1[(aux.row0 + rp) * NM + k];
                 if (rp + 32 < aux.rows) zb *= aux.m1[(aux.row0 + rp + 32) * NM + k];
+            } else if (aux.drop.thresh) {   // the same, masks drawn here: one Philox call per four units of a row
+                if ((k & 3) == 0) {
+                    dma = dropout_mask4(aux.drop, aux.row0 + rp, k >> 2, 0);
+                    dmb = dropout_mask4(aux.drop, aux.row0 + rp + 32, k >> 2, 0);
+                }
+                const int l = k & 3;
+                za *= l == 0 ? dma.x : l == 1 ? dma.y : l == 2 ? dma.z : dma.w;
+                zb *= l == 0 ? dmb.x : l == 1 ? dmb.y : l == 2 ? dmb.z : dmb.w;
             }
             S.z1T[k * TR + rp] = fmaxf(za, 0.f);
             S.z1T[k * TR + rp + 32] = fmaxf(zb, 0.f);
@@ -154,6 +165,8 @@ __device__ __forceinline__ void tile_mlp(const RowsSmem& S, const TileAux aux = 
             const int row = rg * 4 + r;
             if (aux.m2 && row < aux.rows)
                 mk = *reinterpret_cast<const float4*>(aux.m2 + (aux.row0 + row) * NM + q * 32 + cg * 4);
+            else if (aux.drop.thresh)
+                mk = dropout_mask4(aux.drop, aux.row0 + row, q * 8 + cg, 1);
             acc[r][q * 4 + 0] = fmaxf((acc[r][q * 4 + 0] + b.x) * mk.x, 0.f);
             acc[r][q * 4 + 1] = fmaxf((acc[r][q * 4 + 1] + b.y) * mk.y, 0.f);
             acc[r][q * 4 + 2] = fmaxf((acc[r][q * 4 + 2] + b.z) * mk.z, 0.f);
@@ -212,6 +225,12 @@ __global__ void __launch_bounds__(RT, 2) rhs_rows_kernel(const RowsArgs a) {
         const long long n_tiles = n_groups * blocks_per_group;
         long long cur_group = -1;
         unsigned notconv = 0;
+        DropCfg drop{0u, 1.f, 0ull, 0ull};
+        if (a.drop_p > 0.f && !a.m1 && !a.m2) {
+            drop.thresh = (unsigned)fminf(a.drop_p * 4294967296.f, 4294967040.f);
+            drop.scale = 1.f / (1.f - a.drop_p);
+            drop.seed = a.drop_seed; drop.step = a.drop_step ? *a.drop_step : 0ull;
+        }
         for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
             const long long gi = tile / blocks_per_group, bi = tile - gi * blocks_per_group;
             const long long row0 = gi * group + bi * TR;
@@ -224,7 +243,7 @@ __global__ void __launch_bounds__(RT, 2) rhs_rows_kernel(const RowsArgs a) {
             for (int e = t; e < TR * NH; e += RT)
                 S.hs[e] = e < rows * NH ? a.h[row0 * NH + e] : 0.f;
             __syncthreads();
-            tile_mlp(S, TileAux{a.m1, a.m2, a.z1_out, a.z2_out, row0, rows});
+            tile_mlp(S, TileAux{a.m1, a.m2, a.z1_out, a.z2_out, row0, rows, drop});
             if (t < rows) {
                 float ft[NH], lo[NH];
 #pragma unroll
@@ -408,7 +427,8 @@ namespace fiode {
 // ftilde (N,10) [post scale_nominal] + OR of the not-converged words of every row; optional dropout masks / activations
 int launch_rows_store(const fiode_dyn_weights* w, const float* h, const float* s, long long N, long long s_rows,
                       long long s_group, float* ft, unsigned* notconv, const float* m1, const float* m2, float* z1,
-                      float* z2, cudaStream_t st) {
+                      float* z2, cudaStream_t st, float drop_p, unsigned long long drop_seed,
+                      const unsigned long long* drop_step) {
     if (s_rows != 1 && (s_group <= 0 || s_rows * s_group < N)) {
         set_error("rhs: s_rows=%lld s_group=%lld do not cover N=%lld", s_rows, s_group, N); return -1; }
     if (w->max_iter < 1 || w->max_iter > kIt) { set_error("rhs: max_iter must be in [1,32]"); return -1; }
@@ -418,6 +438,7 @@ int launch_rows_store(const fiode_dyn_weights* w, const float* h, const float* s
     RowsArgs a{};
     a.w = *w; a.h = h; a.s = s; a.N = N; a.s_rows = s_rows; a.s_group = s_group; a.ft_out = ft; a.notconv = notconv;
     a.m1 = m1; a.m2 = m2; a.z1_out = z1; a.z2_out = z2;
+    a.drop_p = drop_p; a.drop_seed = drop_seed; a.drop_step = drop_step;
     const long long group = s_rows == 1 ? N : s_group;
     const long long n_tiles = ((N + group - 1) / group) * ((group + TR - 1) / TR);
     const int grid = (int)min((long long)2 * sm_count(), n_tiles);

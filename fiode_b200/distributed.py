@@ -41,9 +41,17 @@ def gather_by_index(n, local_idx, local_vals):
 
 
 class FlatGradAllReduce:
-    """One contiguous fp32 buffer holding every trainable parameter's gradient; ``step()`` averages it
-    over the ranks with a single all-reduce and scatters the views back (payload 2 426 043 floats = 9.7 MB
-    for the CIFAR model: latency-bound, so one message rather than DDP's buckets)."""
+    """One contiguous fp32 buffer holding every trainable parameter's gradient; ``step()`` averages it over the ranks
+    with a single all-reduce (payload 2 426 047 floats = 9.7 MB for the CIFAR model: latency-bound, so one message
+    rather than DDP's buckets).
+
+    ``prepare()`` (call it where a training loop calls ``zero_grad``) zeroes the buffer with one memset and points every
+    ``p.grad`` at its slice, so the backward accumulates straight into the flat buffer -- no per-parameter copies.
+    A parameter that receives no gradient therefore holds zeros rather than ``None`` (DDP leaves ``None``): an optimiser
+    with weight decay would still move it.  The only such parameters in this model are none -- every one of the 33
+    receives a gradient in the FI step; the lazily created conv ``alpha`` of the reference is not a registered parameter at
+    optimiser-construction time there and is a normal parameter here.  ``step()`` also accepts gradients
+    that were produced the usual way (``p.grad`` not aliasing the buffer): those are copied in first."""
 
     def __init__(self, params):
         self.params = [p for p in params if p.requires_grad]
@@ -55,16 +63,22 @@ class FlatGradAllReduce:
             self.views.append(self.flat[o:o + p.numel()].view_as(p))
             o += p.numel()
 
+    def prepare(self):
+        self.flat.zero_()
+        for p, v in zip(self.params, self.views):
+            p.grad = v
+        return self
+
     def step(self):
         _, w = world()
         for p, v in zip(self.params, self.views):
             if p.grad is None:
                 v.zero_()
-            else:
+            elif p.grad.data_ptr() != v.data_ptr():
                 v.copy_(p.grad)
         if w > 1:
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM)
             self.flat.div_(w)
         for p, v in zip(self.params, self.views):
-            p.grad = v            # gradients now alias the flat buffer: no copy back
+            p.grad = v            # gradients alias the flat buffer
         return self.flat

@@ -9,9 +9,19 @@ import torch
 
 
 class GraphedStep:
-    def __init__(self, fn, warmup=3):
+    def __init__(self, fn, warmup=3, key_fn=None):
         """``fn()`` must read its inputs from fixed device tensors, do no host synchronisation (no .item() / .cpu())
-        and return tensors (or None).  It is run ``warmup`` times on a side stream, then captured once."""
+        and return tensors (or None).  It is run ``warmup`` times on a side stream, then captured once.
+        ``key_fn()`` (optional) runs on the host before every replay -- it is where schedule values are written into
+        device scalars (``LyapunovLearning.prepare_step``) -- and returns a hashable key of whatever the capture has
+        baked in as Python constants (sampler counts, scale_nominal, dropout p): a changed key re-captures."""
+        self.fn, self.warmup, self.key_fn = fn, warmup, key_fn
+        self.key = key_fn() if key_fn else None
+        self.captures = 0
+        self._capture()
+
+    def _capture(self):
+        fn, warmup = self.fn, self.warmup
         cur = torch.cuda.current_stream()
         side = torch.cuda.Stream()
         side.wait_stream(cur)
@@ -23,7 +33,13 @@ class GraphedStep:
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
             self.out = fn()
+        self.captures += 1
 
     def __call__(self):
+        if self.key_fn is not None:
+            key = self.key_fn()
+            if key != self.key:
+                self.key = key
+                self._capture()
         self.graph.replay()
         return self.out

@@ -113,6 +113,14 @@ class IVP(nn.Module):
     def h_dot(self, t, h):
         return self.dyn_fun.ode_forward(t, h)
 
+    def _no_dropout_in_solve(self):
+        """The reference applies nn.Dropout inside every RHS evaluation of a train-mode solve (classification.py:96-101).
+        The fused solver has no dropout; rather than return eval-mode results silently, refuse (as eval_dot_light does)."""
+        d = self.dyn_fun
+        if d.training and getattr(d, 'dropout', None) is not None and d.dropout.p > 0:
+            raise NotImplementedError('IVP solve with the dynamics in .train() mode and dropout p > 0: the device-resident '
+                                      'solver evaluates the RHS without dropout; call dyn_fun.eval() or set dropout p = 0')
+
     def forward(self, x, ts=None, int_params=None, use_adjoint=False, return_traj=False):
         solution = self.integrate(x, ts=ts, int_params=int_params, use_adjoint=use_adjoint)
         return self.output_fun(solution) if return_traj else self.output_fun(solution)[-1]
@@ -126,6 +134,7 @@ class IVP(nn.Module):
         solves sharing one launch (a thread-block cluster per solve).  This is the unit that shards across
         SMs and, one level up, across GPUs."""
         from . import ops
+        self._no_dropout_in_solve()
         G, B = x.shape[:2]
         if ts is None:
             ts = self.ts
@@ -145,6 +154,7 @@ class IVP(nn.Module):
 
     def integrate(self, x, ts=None, int_params=None, use_adjoint=False):
         assert not use_adjoint, 'the adjoint solve stays on the reference (unused by the FI-ODE configs)'
+        self._no_dropout_in_solve()
         if ts is None:
             ts = self.ts
         if int_params is None:

@@ -287,10 +287,37 @@ def sampler_fill(kind, e, y, h, s0):
 
 class FiSaved:
     """Device tensors the FI-loss forward keeps for its backward."""
-    __slots__ = ('h', 's', 'y', 'B', 'S', 'kappa', 'm1', 'm2', 'f', 'ft', 'mu', 'z1', 'z2', 'V', 'Vdot', 'out4', 'dw')
+    __slots__ = ('h', 's', 'y', 'B', 'S', 'kappa', 'm1', 'm2', 'f', 'ft', 'mu', 'z1', 'z2', 'V', 'Vdot', 'out4', 'dw', 'opt')
+
+    def __init__(self):
+        self.opt = None
 
 
-def fi_loss_fwd(dw, h, s, y, S, kappa, m1=None, m2=None):
+class FiOpt:
+    """fiode_fi_options: kappa as a device scalar (schedules under CUDA-graph replay) and in-kernel Philox dropout."""
+
+    def __init__(self, kappa_dev=None, dropout_p=0.0, seed=0, step_dev=None):
+        from ._lib import FiOptions
+        self.kappa_dev, self.step_dev = kappa_dev, step_dev            # keep the tensors alive
+        assert kappa_dev is None or (kappa_dev.dtype == torch.float32 and kappa_dev.numel() == 1)
+        assert step_dev is None or (step_dev.dtype == torch.int64 and step_dev.numel() == 1)
+        assert dropout_p == 0.0 or step_dev is not None, 'in-kernel dropout needs a device step counter'
+        self.c = FiOptions(ptr(kappa_dev), float(dropout_p), int(seed) & (2 ** 64 - 1), ptr(step_dev))
+
+    @property
+    def dropout_p(self):
+        return self.c.dropout_p
+
+
+def dropout_mask(opt: 'FiOpt', layer, N):
+    """The (N,128) mask the next forward call draws for ``layer`` (0 | 1) with these options (host sync)."""
+    out = torch.empty(N, 128, dtype=torch.float32, device=opt.step_dev.device)
+    check(lib().fiode_dropout_mask(opt.c.dropout_p, opt.c.seed, ptr(opt.step_dev), int(layer), N, ptr(out), stream_ptr()),
+          'fiode_dropout_mask')
+    return out
+
+
+def fi_loss_fwd(dw, h, s, y, S, kappa, m1=None, m2=None, opt: 'FiOpt' = None):
     """loss = mean relu(Vdot + kappa V) over the B*S samples (pl_modules.py:435-466).  Returns FiSaved;
     ``out4`` = [loss, effective_batch_size, mean_active_constraints, bisection iterations] on the device."""
     h, s = _f32(h), _f32(s)
@@ -307,9 +334,11 @@ def fi_loss_fwd(dw, h, s, y, S, kappa, m1=None, m2=None):
     sv.out4 = new(4)
     nb = lib().fiode_fi_loss_workspace_bytes(N, B)
     ws = _ws(nb, dev)
-    check(lib().fiode_fi_loss_fwd(C.byref(dw), ptr(h), ptr(s), ptr(sv.y), B, S, sv.kappa, ptr(sv.m1), ptr(sv.m2), ptr(sv.f),
-                                  ptr(sv.ft), ptr(sv.mu), ptr(sv.z1), ptr(sv.z2), ptr(sv.V), ptr(sv.Vdot), ptr(sv.out4),
-                                  ptr(ws), nb, stream_ptr()), 'fiode_fi_loss_fwd')
+    sv.opt = opt
+    check(lib().fiode_fi_loss_fwd_opt(C.byref(dw), ptr(h), ptr(s), ptr(sv.y), B, S, sv.kappa, ptr(sv.m1), ptr(sv.m2),
+                                      C.byref(opt.c) if opt else None, ptr(sv.f),
+                                      ptr(sv.ft), ptr(sv.mu), ptr(sv.z1), ptr(sv.z2), ptr(sv.V), ptr(sv.Vdot), ptr(sv.out4),
+                                      ptr(ws), nb, stream_ptr()), 'fiode_fi_loss_fwd_opt')
     return sv
 
 
@@ -322,11 +351,13 @@ def fi_loss_bwd(sv: FiSaved, grad_loss=1.0):
     N = sv.B * sv.S
     nb = lib().fiode_fi_loss_workspace_bytes(N, sv.B)
     ws = _ws(nb, dev)
-    check(lib().fiode_fi_loss_bwd(C.byref(sv.dw), ptr(sv.h), ptr(sv.s), ptr(sv.y), sv.B, sv.S, sv.kappa, float(grad_loss),
-                                  ptr(sv.m1), ptr(sv.m2), ptr(sv.f), ptr(sv.ft), ptr(sv.mu), ptr(sv.z1), ptr(sv.z2),
-                                  ptr(sv.V), ptr(sv.Vdot), ptr(g['Q1']), ptr(g['Qx']), ptr(g['Q2']), ptr(g['Q3']),
-                                  ptr(g['b1']), ptr(g['b2']), ptr(g['b3']), ptr(g['s']), ptr(ws), nb, stream_ptr()),
-          'fiode_fi_loss_bwd')
+    opt = getattr(sv, 'opt', None)
+    check(lib().fiode_fi_loss_bwd_opt(C.byref(sv.dw), ptr(sv.h), ptr(sv.s), ptr(sv.y), sv.B, sv.S, sv.kappa, float(grad_loss),
+                                      ptr(sv.m1), ptr(sv.m2), C.byref(opt.c) if opt else None, ptr(sv.f), ptr(sv.ft), ptr(sv.mu),
+                                      ptr(sv.z1), ptr(sv.z2),
+                                      ptr(sv.V), ptr(sv.Vdot), ptr(g['Q1']), ptr(g['Qx']), ptr(g['Q2']), ptr(g['Q3']),
+                                      ptr(g['b1']), ptr(g['b2']), ptr(g['b3']), ptr(g['s']), ptr(ws), nb, stream_ptr()),
+          'fiode_fi_loss_bwd_opt')
     return g
 
 
@@ -593,3 +624,40 @@ def lincomb(out, terms):
         assert x.is_cuda and x.is_contiguous() and x.dtype == torch.float32 and x.numel() == out.numel()
     check(lib().fiode_lincomb(ptr(out), out.numel(), n, xs, cs, stream_ptr()), 'fiode_lincomb')
     return out
+
+
+# ---- every op runs on the device of its tensors --------------------------------------------------------------------
+# The C ABI launches on the CURRENT CUDA device (per-device function attributes, SM counts, the current stream); a
+# process that drives several GPUs must therefore make the tensors' device current around each call.
+def _first_cuda_device(args, kwargs):
+    for a in list(args) + list(kwargs.values()):
+        if isinstance(a, torch.Tensor) and a.is_cuda:
+            return a.device
+        for name in ('h', 'out', 'step_dev', 'kappa_dev', '_keep'):
+            t = getattr(a, name, None)
+            if isinstance(t, torch.Tensor) and t.is_cuda:
+                return t.device
+            if isinstance(t, dict):
+                for v in t.values():
+                    if isinstance(v, torch.Tensor) and v.is_cuda:
+                        return v.device
+    return None
+
+
+def _on_tensor_device(fn):
+    import functools
+
+    @functools.wraps(fn)
+    def wrapped(*args, **kwargs):
+        dev = _first_cuda_device(args, kwargs)
+        if dev is None or dev.index == torch.cuda.current_device():
+            return fn(*args, **kwargs)
+        with torch.cuda.device(dev):
+            return fn(*args, **kwargs)
+    return wrapped
+
+
+for _name, _obj in list(globals().items()):
+    if callable(_obj) and getattr(_obj, '__module__', None) == __name__ and not _name.startswith('_') \
+            and not isinstance(_obj, type):
+        globals()[_name] = _on_tensor_device(_obj)

@@ -27,7 +27,8 @@ def certify_constants(dyn, std_min, eps, T, n_class=10):
 
 @torch.no_grad()
 def certify(model, images, labels, T=40, eps=0.141, batches=10, gridz=None, images_per_launch=296,
-            with_accuracy=True, ode_tol=1e-3, t_max=5.0, margin_tol=3e-4, evaluate=None, backbone=None):
+            with_accuracy=True, ode_tol=1e-3, t_max=5.0, margin_tol=3e-4, evaluate=None, backbone=None, std_min=None,
+            solve=None):
     """The loop of certify_lipschitz.py:104-163 for ``images`` (n,3,32,32) / ``labels`` (n,).
 
     Images are sharded round-robin over the ranks of the default process group; each rank holds the
@@ -36,13 +37,16 @@ def certify(model, images, labels, T=40, eps=0.141, batches=10, gridz=None, imag
     certified_idx, violations_store (list of per-image max violations, what the reference torch.saves) and
     ``near_zero``: images whose margin lies within ``margin_tol`` of 0 (verdict not guaranteed to match a
     run with a different summation order).
-    ``evaluate(s, labels) -> (m,2)`` and ``backbone(x) -> s`` can be injected (CPU tests of the sharding)."""
+    ``std_min``: min of the model's Normalize.std (certify_lipschitz.py:66); read from the model when None.
+    ``evaluate(s, labels) -> (m,2)``, ``backbone(x) -> s`` and ``solve(x) -> (m,10)`` can be injected (CPU tests of the
+    sharding)."""
     dyn = model.dyn_fun
     n = images.shape[0]
     rank, world = fdist.world()
     mine = fdist.shard_indices(n, rank, world)
     dev = images.device
-    std_min = float(model.init_coordinates.param_map[0].std.min()) if backbone is None else 0.225
+    if std_min is None:
+        std_min = float(torch.as_tensor(model.init_coordinates.param_map[0].std).min())
     c = certify_constants(dyn, std_min, eps, T)
     if evaluate is None:
         if gridz is None:
@@ -58,11 +62,16 @@ def certify(model, images, labels, T=40, eps=0.141, batches=10, gridz=None, imag
         x, lab = images[sel].contiguous(), labels[sel]
         s = backbone(x)
         viol[o:o + sel.numel()] = evaluate(s, lab)
-        if with_accuracy:                      # net_out = module(image): a batch-1 solve per image (:111-112)
-            ts = torch.linspace(0., t_max, 2)
-            for j in range(sel.numel()):
-                y = model(x[j:j + 1], ts=ts, int_params=dict(method='dopri5', rtol=ode_tol, atol=ode_tol))
-                correct[o + j] = float(int(y.argmax(-1)) == int(lab[j]))
+        if with_accuracy:
+            # net_out = module(image) (:111-112) is a batch-1 solve per image: all of this launch's images go through ONE
+            # forward_batches call as G = m independent solves of B = 1 row (each keeps its own error norm and projection
+            # stop rule, exactly like the per-image calls), one status read, no per-image host sync
+            if solve is not None:
+                y = solve(x)
+            else:
+                y = model.forward_batches(x[:, None], ts=torch.linspace(0., t_max, 2),
+                                          int_params=dict(method='dopri5', rtol=ode_tol, atol=ode_tol))[:, 0]
+            correct[o:o + sel.numel()] = (y.argmax(-1) == lab).float()
     if bool(torch.isnan(viol).any()):
         from .._lib import FiodeError
         raise FiodeError('certify: an activation left the fp16x2 range of the tensor-core path (|x| >= 1023); '

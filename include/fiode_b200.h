@@ -253,6 +253,31 @@ FIODE_API int fiode_fi_loss_bwd(const fiode_dyn_weights* w, const float* h, cons
                       const float* Vdot, float* dQ1, float* dQx, float* dQ2, float* dQ3, float* db1, float* db2,
                       float* db3, float* ds, void* ws, size_t ws_bytes, void* stream);
 
+/* Options for the _opt variants of the two calls above.  kappa_dev: device scalar read instead of the by-value kappa, so that the
+ * kappa warm-up (pl_modules.py:447-450, kappa_length = 30 000 steps in cifar_train.yaml) survives CUDA-graph replay.
+ * dropout_p > 0 (with m1 == m2 == NULL): the nn.Dropout of classification.py:96-102 is drawn INSIDE the kernel
+ * (Philox4x32-10 keyed by seed, offset *step_dev), masks never touch HBM; the forward increments *step_dev so every call /
+ * graph replay draws fresh masks; the backward needs only dropout_p (a kept unit's mask value is 1 / (1 - p)).        */
+typedef struct fiode_fi_options {
+    const float* kappa_dev;
+    float dropout_p;
+    unsigned long long seed;
+    unsigned long long* step_dev;
+} fiode_fi_options;
+FIODE_API int fiode_fi_loss_fwd_opt(const fiode_dyn_weights* w, const float* h, const float* s, const int* y, int B, int S,
+                          float kappa, const float* m1, const float* m2, const fiode_fi_options* opt, float* f,
+                          float* ftilde, float* mu, float* z1, float* z2, float* V, float* Vdot, float* out4, void* ws,
+                          size_t ws_bytes, void* stream);
+FIODE_API int fiode_fi_loss_bwd_opt(const fiode_dyn_weights* w, const float* h, const float* s, const int* y, int B, int S,
+                          float kappa, float grad_loss, const float* m1, const float* m2, const fiode_fi_options* opt,
+                          const float* f, const float* ftilde, const float* mu, const float* z1, const float* z2,
+                          const float* V, const float* Vdot, float* dQ1, float* dQx, float* dQ2, float* dQ3, float* db1,
+                          float* db2, float* db3, float* ds, void* ws, size_t ws_bytes, void* stream);
+/* The (N,128) mask (0 or 1/(1-p)) the forward draws for layer 0 (after hidden_to_mlp + U_x) / 1 (after mlp_to_mlp) at the
+ * CURRENT value of *step_dev: replaying a step with explicit masks (parity tests).  Synchronises the stream.        */
+FIODE_API int fiode_dropout_mask(float dropout_p, unsigned long long seed, const unsigned long long* step_dev, int layer,
+                       long long N, float* mask, void* stream);
+
 /* ---- decision-boundary grid -----------------------------------------------------------------------
  * replaces robustness/eval_utils.py:31-61 sample_decision_boundary and :72-89
  * count_samples_decision_boundary: the set { z in Z^n_{>=0} : sum z = T, z_0 = max_{i>=1} z_i } in a

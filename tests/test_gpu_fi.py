@@ -34,6 +34,7 @@ def build_learning(sd, c, samplers=None):
     # floor(32 * 0.5) into 15)
     mod.sampler_scheduler.get_mixer_coefficients = lambda epoch: list(c['mix'])
     mod.keep_graph_tensors = True
+    mod.current_epoch, mod.global_step = 0, 10 ** 9           # what the golden generator's Lightning stand-in reports
     return mod.to(DEV)
 
 
@@ -209,3 +210,86 @@ def test_fi_loss_backward_on_reference_forward_state(ops, sd, name):
         want = c[theirs]
         err = (g[ours].cpu() - want).abs().max().item()
         assert err <= 1e-5 * float(want.abs().max()), (name, ours, err, float(want.abs().max()))
+
+
+def test_in_kernel_dropout_equals_explicit_masks(sd):
+    """classification.py:96-102 dropout drawn INSIDE the FI-loss kernel (Philox4x32-10, fiode_fi_options): the forward
+    equals -- bit for bit -- the forward fed the masks fiode_dropout_mask reports for the same (seed, step); masks are
+    Bernoulli(1 - p) / (1 - p), differ between the two layers and between steps; the backward (which only knows p)
+    equals the explicit-mask backward."""
+    from fiode_b200 import ops
+    c = fx.load_golden('fi.pt')['mixed_sn0']
+    dyn = fx.build_b200_model(sd).dyn_fun
+    S, B = c['S'], c['B']
+    N = B * S
+    g = torch.Generator().manual_seed(78)
+    s = dev(torch.randn(B, 10, generator=g) * 0.5)
+    step = torch.zeros(1, dtype=torch.int64, device=DEV)
+    kd = torch.full((1,), 2.0, device=DEV)
+    p = 0.5
+    opt = ops.FiOpt(kappa_dev=kd, dropout_p=p, seed=1234567, step_dev=step)
+    m1, m2 = ops.dropout_mask(opt, 0, N), ops.dropout_mask(opt, 1, N)
+    for m in (m1, m2):
+        assert set(m.unique().tolist()) == {0.0, 2.0}
+        assert abs(float((m > 0).float().mean()) - (1 - p)) < 0.01
+    assert float((m1 != m2).float().mean()) > 0.4
+    sv_in = ops.fi_loss_fwd(dyn.dyn_weights(), dev(c['h']), s, dev(c['y']), S, -1.0, opt=opt)     # by-value kappa ignored
+    assert int(step.item()) == 1
+    sv_ex = ops.fi_loss_fwd(dyn.dyn_weights(), dev(c['h']), s, dev(c['y']), S, 2.0, m1, m2)
+    for name in ('f', 'ft', 'mu', 'z1', 'z2', 'V', 'Vdot'):
+        assert torch.equal(getattr(sv_in, name), getattr(sv_ex, name)), name
+    assert torch.equal(sv_in.out4, sv_ex.out4)
+    g_in, g_ex = ops.fi_loss_bwd(sv_in), ops.fi_loss_bwd(sv_ex)
+    for k in g_in:
+        assert (g_in[k] - g_ex[k]).abs().max().item() <= 1e-6 * max(1e-9, g_ex[k].abs().max().item()), k
+    m1b = ops.dropout_mask(opt, 0, N)                        # the forward advanced the step: fresh masks
+    assert float((m1b != m1).float().mean()) > 0.4
+    # other p
+    opt3 = ops.FiOpt(dropout_p=0.3, seed=5, step_dev=step)
+    m = ops.dropout_mask(opt3, 0, 4096)
+    assert abs(float((m > 0).float().mean()) - 0.7) < 0.01 and abs(float(m.max()) - 1 / 0.7) < 1e-6
+
+
+def test_schedules_reach_the_kernels_and_survive_graph_replay(sd):
+    """kappa warm-up (pl_modules.py:447-450) and the epoch-driven sampler mix / scale_nominal switch are read from
+    the trainer seam every step; under CUDA-graph replay kappa travels in a device scalar and a change of the baked-in
+    sampler counts re-captures."""
+    from fiode_b200.graphs import GraphedStep
+    c = fx.load_golden('fi.pt')['uniform_sn1']
+    mod = build_learning(sd, c)
+    mod.keep_graph_tensors = False
+    dyn = mod.model.dyn_fun
+    dyn.kappa_length = 30000
+    x, y = dev(c['x']), dev(c['y'])
+    var = [dev(v) if v is not None else None for v in c['variates']]
+
+    class Trainer:
+        global_step, current_epoch = 15000, 0
+    mod.current_epoch = mod.global_step = None
+    with pytest.raises(RuntimeError, match='attach_trainer'):
+        mod.compute_loss(x, y, c['B'], act='relu', variates=var)
+    mod.attach_trainer(Trainer)
+    l_half = float(mod.compute_loss(x, y, c['B'], act='relu', variates=var))
+    assert mod.logged['kappa'] == pytest.approx(1.0)
+    Trainer.global_step = 10 ** 9
+    l_full = float(mod.compute_loss(x, y, c['B'], act='relu', variates=var))
+    assert mod.logged['kappa'] == 2.0 and l_full > l_half
+    torch.testing.assert_close(torch.tensor(l_full), c['loss'], rtol=2e-4, atol=1e-5)
+    # graph replay follows the schedule
+    mod.train()
+
+    def step():
+        for p in mod.parameters():
+            p.grad = None
+        loss = mod.compute_loss(x, y, c['B'], act='relu', variates=var)
+        loss.backward()
+        return loss.detach()
+    Trainer.global_step = 15000
+    gs = GraphedStep(step, warmup=2, key_fn=lambda: mod.prepare_step(x.device))
+    a = float(gs())
+    Trainer.global_step = 10 ** 9
+    b = float(gs())
+    assert gs.captures == 1 and a == pytest.approx(l_half, rel=1e-5) and b == pytest.approx(l_full, rel=1e-5)
+    Trainer.current_epoch = mod.epoch_off_scale = 3              # scale_nominal switches off -> key changes -> re-capture
+    cval = float(gs())
+    assert gs.captures == 2 and dyn.scale_nominal is False and cval != b
