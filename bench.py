@@ -294,34 +294,30 @@ def fi_step_bench(device, pk, world, iters=10, warm=8):
 
 
 # per image: algorithmic HBM bytes (fp32 activations in + out; spectra complex64) and flops of each backbone stage
-#   name, kernel, bytes/img, flop/img
+#   name, kernel, bytes/img, flop/img, (kernel key, launch index) in profiles/ncu_traffic.json
 STAGES = [
-    ('weight packing (per call)', 'pack_w_kernel x5 + mix_real_weights', 0, 0),
-    ('rfft2 32x32, 3 ch (+Normalize)', 'rfft2_kernel<32>', 3 * 1024 * 4 + 3 * 544 * 8, 0.12e6),
-    ('mix 3->32 + irfft2 32x32 + bias + GroupSort', 'irfft32_mix3_wide_kernel', 3 * 544 * 8 + 32 * 1024 * 4, 0.42e6 + 1.1e6),
-    ('conv 128->32 @16x16 (s2d 1x1) + GroupSort', 'gemm_tc_kernel<s2d,32>', 32 * 1024 * 4 + 32 * 256 * 4, 2 * 128 * 32 * 256),
-    ('rfft2 16x16, 32 ch', 'rfft2_kernel<16,fm>', 32 * 256 * 4 + 32 * 144 * 8, 0.3e6),
-    ('mixing 144 x (64->128 real)', 'gemm_tc_kernel<row,128> batched', (32 + 64) * 144 * 8, 2 * 64 * 128 * 144),
-    ('irfft2 16x16, 64 ch + bias + GroupSort', 'irfft2_kernel<16,fm>', 64 * 144 * 8 + 64 * 256 * 4, 0.6e6),
-    ('conv 256->64 @8x8 (s2d 1x1) + GroupSort', 'gemm_tc_kernel<s2d,64>', 64 * 256 * 4 + 64 * 64 * 4, 2 * 256 * 64 * 64),
-    ('linear 4096->512 + GroupSort', 'gemm_tc_kernel<row,128>', 4096 * 4 + 512 * 4, 2 * 4096 * 512),
-    ('linear 512->512 + GroupSort', 'gemm_tc_kernel<row,128>', 512 * 4 * 2, 2 * 512 * 512),
-    ('fc 512->10', 'gemm_nt_kernel', 512 * 4 + 40, 2 * 512 * 10),
+    ('weight packing (per call)', 'pack_w_kernel x5 + mix_real_weights', 0, 0, None),
+    ('rfft2 32x32, 3 ch (+Normalize)', 'rfft2_kernel<32>', 3 * 1024 * 4 + 3 * 544 * 8, 0.12e6, ('rfft2_kernel<32, 0, 0>', 0)),
+    ('mix 3->32 + irfft2 32x32 + bias + GroupSort', 'irfft32_mix3_wide_kernel', 3 * 544 * 8 + 32 * 1024 * 4, 0.42e6 + 1.1e6, ('irfft32_mix3_wide_kernel<2>', 0)),
+    ('conv 128->32 @16x16 (s2d 1x1) + GroupSort', 'gemm_tc_kernel<s2d,32>', 32 * 1024 * 4 + 32 * 256 * 4, 2 * 128 * 32 * 256, ('gemm_tc_kernel<1, 32, 0>', 0)),
+    ('rfft2 16x16, 32 ch', 'rfft2_kernel<16,fm>', 32 * 256 * 4 + 32 * 144 * 8, 0.3e6, ('rfft2_kernel<16, 1, 0>', 0)),
+    ('mixing 144 x (64->128 real)', 'gemm_tc_kernel<row,128> batched', (32 + 64) * 144 * 8, 2 * 64 * 128 * 144, ('gemm_tc_kernel<0, 128, 1>', 0)),
+    ('irfft2 16x16, 64 ch + bias + GroupSort', 'irfft2_kernel<16,fm>', 64 * 144 * 8 + 64 * 256 * 4, 0.6e6, ('irfft2_kernel<16, 2>', 0)),
+    ('conv 256->64 @8x8 (s2d 1x1) + GroupSort', 'gemm_tc_kernel<s2d,64>', 64 * 256 * 4 + 64 * 64 * 4, 2 * 256 * 64 * 64, ('gemm_tc_kernel<1, 64, 0>', 0)),
+    ('linear 4096->512 + GroupSort', 'gemm_tc_kernel<row,128>', 4096 * 4 + 512 * 4, 2 * 4096 * 512, ('gemm_tc_kernel<0, 128, 1>', 1)),
+    ('linear 512->512 + GroupSort', 'gemm_tc_kernel<row,128>', 512 * 4 * 2, 2 * 512 * 512, ('gemm_tc_kernel<0, 128, 1>', 2)),
+    ('fc 512->10', 'gemm_nt_kernel', 512 * 4 + 40, 2 * 512 * 10, ('gemm_nt_kernel', 0)),
 ]
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed `ncu --set full` capture (profiles/r01h_ncu_full_summary.md, one 4096-image launch)
-# (profiles/r01c_ncu_full_summary.md; re-measure when a kernel changes).  Keyed by the kernel named in STAGES / the solver.
-NCU_TRAFFIC_BYTES = {
-    'rfft2_kernel<32>': 50.37e6 + 4.59e6,
-    'irfft32_mix3_wide_kernel': 53.95e6 + 476.89e6,
-    'gemm_tc_kernel<s2d,32>': 536.93e6 + 114.31e6,
-    'rfft2_kernel<16,fm>': 134.24e6 + 100.68e6,
-    'gemm_tc_kernel<row,128> batched': 156.84e6 + 245.81e6,
-    'irfft2_kernel<16,fm>': 302.05e6 + 228.97e6,
-    'gemm_tc_kernel<s2d,64>': 268.56e6 + 46.21e6,
-    'dopri5_simplex_batched_kernel': 0.55e6,
-}
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed `ncu --set full` capture of this code
+    (profiles/ncu_traffic.json, written by `tools/ncu_summary.py traffic <capture>`; re-generated whenever a kernel changes --
+    a number measured under the profiler cannot be taken inside this run)."""
+    p = os.path.join(ROOT, 'profiles', 'ncu_traffic.json')
+    if not os.path.exists(p):
+        return None
+    return json.load(open(p))
 
 
 def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
@@ -359,8 +355,14 @@ def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
     n_slabs = -(-n_img // n_stage)              # backbone launches per step (one per slab)
     ridge = pk['bf16'] * 1e12 / 3 / (pk['hbm'] * 1e9)      # flop/byte above which the 3-MMA emulation is tensor-bound
     stages = []
-    for (name, kern, by, fl), ms in zip(STAGES, acc):
+    nt = ncu_traffic()
+    for (name, kern, by, fl, nkey), ms in zip(STAGES, acc):
         d = dict(stage=name, kernel=kern, ms=ms, launches_per_step=n_slabs, ms_per_step=ms * n_slabs)
+        if nt and nkey and nkey[0] in nt['kernels'] and len(nt['kernels'][nkey[0]]) > nkey[1]:
+            # the capture ran one backbone pass over nt['backbone_images'] images; these kernels stream, bytes scale with images
+            d['traffic'] = nt['kernels'][nkey[0]][nkey[1]]['dram_bytes'] * n_stage / nt['backbone_images']
+            if by:
+                d['traffic_over_algorithmic'] = d['traffic'] / (by * n_stage)
         if by:
             d.update(gbs=by * n_stage / (ms * 1e-3) / 1e9 if ms > 0 else None, tflops=fl * n_stage / (ms * 1e-3) / 1e12 if ms > 0 else None,
                      bound='tensor' if fl / by > ridge else 'hbm')
@@ -372,23 +374,128 @@ def stage_roofline(ivp, x_dev, G, ts, pk, iters=10, cluster_size=0):
                        note='%d dependent RHS evaluations per solve, %d rows per CTA: FP32 FFMA, latency-bound' % (st.nfe, B // max(cluster_size, 1) if cluster_size else 32)))
     ms_bb = sum(acc)
     bb_bytes = sum(x[2] for x in STAGES) * n_stage
+    bb_traffic = sum(d.get('traffic', 0.0) for d in stages[:len(STAGES)])
     top = max((d for d in stages if 'tflops' in d or 'gbs' in d), key=lambda d: d['ms_per_step'])    # dominant = largest share of the step
     if top.get('bound') == 'hbm':
         rf = dict(bound='hbm', achieved=top['gbs'], peak=pk['hbm'], unit='GB/s', frac=top['gbs'] / pk['hbm'])
     else:
         rf = dict(bound='tensor', achieved=top['tflops'], peak=pk['bf16'], unit='TFLOP/s', frac=top['tflops'] / pk['bf16'])
-    traffic = NCU_TRAFFIC_BYTES.get(top['kernel'])
-    if traffic and top['kernel'] != 'dopri5_simplex_batched_kernel':
-        traffic *= n_stage / 4096.             # the capture ran one 4096-image launch; these kernels stream, bytes scale with images
-    rf.update(traffic=traffic, traffic_source='profiles/r01h_ncu_full_summary.md (4096-image launch, scaled to the %d images of this launch)' % n_stage,
+    traffic = top.get('traffic')
+    if top['kernel'] == 'dopri5_simplex_batched_kernel' and nt and 'dopri5_simplex_kernel<1>' in nt['kernels']:
+        traffic = nt['kernels']['dopri5_simplex_kernel<1>'][0]['dram_bytes']
+    rf.update(traffic=traffic, traffic_source=('profiles/ncu_traffic.json <- %s (%d-image pass, scaled to the %d images of this launch)' % (
+                  nt['source'], nt['backbone_images'], n_stage)) if nt else None,
               kernel=top['kernel'], stage=top['stage'], ms_per_launch=top['ms'], launches_per_step=top['launches_per_step'], peak_source=pk['source'],
               note='algorithmic bytes / flops of SURVEY 8(d) over the CUDA-event time of that launch; tensor-core stages run the '
                    'fp16x2-split FP32 emulation (3 MMAs per product), so their ceiling is peak / 3; see DESIGN.md section 4',
               parts=dict(backbone_ms=ms_bb, backbone_images=n_stage, backbone_algorithmic_gbs=bb_bytes / (ms_bb * 1e-3) / 1e9,
                          backbone_hbm_frac=bb_bytes / (ms_bb * 1e-3) / 1e9 / pk['hbm'],
+                         backbone_ncu_traffic_bytes=bb_traffic, backbone_minimal_bytes_per_image=61e3,
                          backbone_tflops=BACKBONE_FLOP * n_stage / (ms_bb * 1e-3) / 1e12, dopri5_ms=ms_solve,
                          nfe=st.nfe, n_accept=st.n_accept, n_reject=st.n_reject, stages=stages))
     return rf
+
+
+def segway_bench(device, pk, world, iters=10):
+    """BASELINE config 1: Segway NN-controller forward-invariance grid check (control/certify_segway.py:35-59): the
+    300 x 53 x 300 = 4.77 M-point grid (r = 0.01) generated from its index, shell mask V in [lb, ub], barrier derivative
+    of the closed loop at the shell points, ordered compaction.  Grid slabs shard across ranks (weak scaling would need
+    a finer grid; here every rank evaluates the WHOLE grid, N replicas)."""
+    from fiode_b200.control import segway
+    torch.manual_seed(0)
+    ctrl = torch.nn.Sequential(torch.nn.Linear(3, 32), torch.nn.ReLU(), torch.nn.Linear(32, 32), torch.nn.ReLU(), torch.nn.Linear(32, 1))
+    sd = {'model.' + k: v.detach() for k, v in ctrl.state_dict().items()}
+    P = torch.eye(3) + 0.1 * torch.randn(3, 3, generator=torch.Generator().manual_seed(2))
+    sizes, r = [math.pi / 12, 1.5, 1.5], [0.01] * 3
+    n = 1
+    for a in segway.grid_axes(sizes, r):
+        n *= len(a)
+    fn = lambda: segway.certify_grid(sd, P, sizes, r, level=0.15, device=device)
+    eta, val, vmax = fn()
+    ms = timed(fn, iters) / iters
+    t = torch.tensor([ms], device=device)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    flop = 2 * (3 * 32 + 32 * 32 + 32) + 60                  # SURVEY 8(d): controller MLP at a shell point + closed-form dynamics
+    out = dict(metric='Segway grid pts/s (certify_segway shell + barrier derivative)', value=world * n / (ms * 1e-3), unit='grid pts/s (whole job)',
+               workload=f'grid {n} pts (r=0.01), NNController(3,1,32) seed 0, P = I + 0.1 randn seed 2, level 0.15; every rank the whole grid',
+               ms_per_call=ms, shell_points=int(eta.shape[0]), max_barrier_derivative=vmax,
+               note='public call segway.certify_grid: allocation of the (n, 3) candidate buffer, ONE kernel (index -> point -> shell test -> '
+                    'controller + dynamics at shell points -> ordered compaction) and the 8-byte status read; the grid is generated, never read: '
+                    '0 B in, 16 B out per shell point',
+               roofline=dict(bound='issue', achieved=n * 12 / (ms * 1e-3) / 1e9, unit='G lane-instr/s (about 12 FP32 instr per grid point for the shell test)',
+                             shell_tflops=eta.shape[0] * flop / (ms * 1e-3) / 1e12, ffma_peak_tflops=FFMA_PEAK_TFLOPS))
+    return out, (sd, P, sizes, r)
+
+
+def cpu_legs(ivp, device, seg_cfg, threads):
+    """CPU baselines beside the secondary metrics (SURVEY 8d 'CPU baseline beside it'), oracle ports on the host cores,
+    each a bounded sample: certify = 1 image x 1 of the 10 chunks of grid_40 (extrapolated, labelled), FI step = the oracle's
+    backbone + fi_loss forward and autograd backward on B=128 x S=256, Segway = the whole 4.77 M-point grid."""
+    from oracle import certify as oc, dynamics as od, layers as ol, segway as oseg, sampler as osm
+    from tests import fixtures as fx
+    from fiode_b200 import grid as fgrid
+    torch.set_num_threads(threads)
+    sd = cpu_state_dict(ivp)
+    out = {}
+    # certify_lipschitz, one image, one chunk (certify_lipschitz.py:104-143)
+    try:
+        T = 40
+        gz = fgrid.boundary_grid_numerators(10, T, device=device)
+        n_all = gz.shape[0]
+        chunk = n_all // 10
+        z = gz[:chunk].cpu().numpy()
+        label = 3
+        grid = oc.grid_for_label(z, T, label)
+        cfg = dict(alpha_1=100., alpha_2=20., sigma_1=0.02, scale_nominal=False)
+        s = torch.randn(1, 10, generator=torch.Generator().manual_seed(1236)) * 0.5
+        Q = od.dyn_Q(sd, 'model.dyn_fun.')
+        t0 = time.perf_counter()
+        oc.certify_image(grid, s, label, sd, cfg, eps=0.141, T=T, batches=1, Q=Q)
+        dt = time.perf_counter() - t0
+        out['certify'] = dict(value=chunk / dt, unit='grid pts/s', cores=threads, kind='port',
+                              sample=f'1 image x 1 chunk of {chunk} grid_40 points in {dt:.1f} s (oracle certify_image); full config '
+                                     f'(10 000 images x {n_all} points) extrapolates to {10000 * n_all / (chunk / dt) / 3600:.0f} h')
+    except Exception as e:
+        out['certify'] = dict(error=repr(e))
+    # FI training step (pl_modules.py:390-506): forward + backward to the 33 parameters
+    try:
+        Bt, S = 128, 256
+        cfg = dict(alpha_1=100., alpha_2=20., sigma_1=0.02, scale_nominal=True)
+        x = fx.synth_images(Bt, seed=1234)
+        y = fx.synth_labels(Bt, seed=1235)
+        e = torch.empty(S, 10).exponential_(generator=torch.Generator().manual_seed(5))
+        h = osm.uniform_simplex(e).repeat(Bt, 1)
+        params = {k: v.clone().requires_grad_(v.is_floating_point() and ('weight' in k or 'bias' in k or 'alpha' in k)) for k, v in sd.items()}
+
+        def fi_step():
+            s_ = ol.backbone_forward(x, params, 'model.init_coordinates.param_map.')
+            loss = od.fi_loss(h, s_.repeat_interleave(S, 0), y.repeat_interleave(S), params, cfg, 2.0, prefix='model.dyn_fun.')[0]
+            loss.backward()
+            return float(loss.detach())
+        fi_step()
+        ts_ = []
+        for _ in range(2):
+            t0 = time.perf_counter()
+            fi_step()
+            ts_.append(time.perf_counter() - t0)
+        dt = sorted(ts_)[0]
+        out['fi_step'] = dict(value=1.0 / dt, unit='steps/s', cores=threads, kind='port',
+                              sample=f'B=128 x S=256 oracle backbone + fi_loss forward + autograd backward, best of 2 after a warm-up: {dt:.2f} s per step')
+    except Exception as e:
+        out['fi_step'] = dict(error=repr(e))
+    try:
+        sdc, P, sizes, r = seg_cfg
+        t0 = time.perf_counter()
+        eta, val, mask = oseg.certify_grid(sdc, P, sizes, r, level=0.15)
+        dt = time.perf_counter() - t0
+        out['segway'] = dict(value=mask.numel() / dt, unit='grid pts/s', cores=threads, kind='port',
+                             sample=f'whole {mask.numel()}-point grid once (numpy meshgrid + torch shell mask + controller at {eta.shape[0]} shell points): {dt:.2f} s')
+    except Exception as e:
+        out['segway'] = dict(error=repr(e))
+    return out
 
 
 def run_b200(args):
@@ -424,7 +531,9 @@ def run_b200(args):
         G = G - G % 16 if G >= 16 else G          # a multiple of 16 batches (4096 images)
     ivp = build_model(device)
     ts = torch.linspace(0., T_MAX, 2)
-    int_params = dict(method='dopri5', rtol=TOL, atol=TOL, options=dict(check=False, cluster_size=CS))
+    # the public call with its DEFAULT options: the end-of-solve status read (torchdiffeq's assertions) is on
+    int_params = dict(method='dopri5', rtol=TOL, atol=TOL, options=dict(cluster_size=CS))
+    int_params_nocheck = dict(method='dopri5', rtol=TOL, atol=TOL, options=dict(check=False, cluster_size=CS))
 
     # inputs: NBUF rotating device-resident sets, together larger than the 126 MB L2
     per_set = G * B * 3 * 32 * 32 * 4
@@ -435,37 +544,52 @@ def run_b200(args):
     y_dev = torch.empty(G, B, 10, device=device)
     y_host = torch.empty(G, B, 10).pin_memory()
 
-    def step(xs, out):
+    def step(xs, out, ip=int_params):
         # G independent batch-256 solves: backbone once over G*256 images, one cluster-per-solve dopri5 launch
-        out.copy_(ivp.forward_batches(xs, ts=ts, int_params=int_params))
+        out.copy_(ivp.forward_batches(xs, ts=ts, int_params=ip))
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def timed_blocks(run_k_steps, min_seconds=args.min_seconds, max_blocks=40):
+        """Blocks of EXACTLY args.steps steps, each bracketed by barrier + synchronize and timed with CUDA events (max over
+        ranks), repeated until >= min_seconds have been timed; returns the per-block times in ms."""
+        blocks = []
+        while True:
+            barrier()
+            e0.record()
+            run_k_steps(args.steps)
+            e1.record()
+            torch.cuda.synchronize()
+            t = torch.tensor([e0.elapsed_time(e1)], device=device)
+            if world > 1:
+                dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            blocks.append(float(t.item()))
+            if sum(blocks) >= min_seconds * 1e3 or len(blocks) >= max_blocks:
+                return blocks
+
+    def rate(blocks):
+        med = sorted(blocks)[len(blocks) // 2]
+        return world * G * args.steps / (med * 1e-3), med
+
     # ---- device-resident timing (value) ------------------------------------------------------------
-    for i in range(args.warmup):
+    for i in range(max(args.warmup, 3)):
         step(x_dev[i % NBUF], y_dev)
     barrier()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     fiode_b200.reset_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(args.steps):
-        step(x_dev[i % NBUF], y_dev)
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1)
-    launches = fiode_b200.launch_count()
+    blocks = timed_blocks(lambda n: [step(x_dev[i % NBUF], y_dev) for i in range(n)])
+    launches = fiode_b200.launch_count() // len(blocks)
     clocks = sampler.stop() if rank == 0 else None
-    t = torch.tensor([ms], device=device)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_max = float(t.item())
-    value = world * G * args.steps / (ms_max * 1e-3)
+    value, ms_block = rate(blocks)
+    blocks_nc = timed_blocks(lambda n: [step(x_dev[i % NBUF], y_dev, int_params_nocheck) for i in range(n)])
+    value_nc, ms_block_nc = rate(blocks_nc)
 
     # ---- end to end through the public API with host buffers (e2e) ------------------------------
     # Every step copies its own inputs host -> device (pinned) and its result device -> host inside the timed region.
@@ -476,7 +600,7 @@ def run_b200(args):
     ready = [torch.cuda.Event() for _ in range(2)]
     consumed = [torch.cuda.Event() for _ in range(2)]
 
-    def e2e_measure(hosts, depth=1):
+    def e2e_measure(hosts, depth=1, ip=int_params):
         """whole-job solves/s with `hosts` (pinned host tensors) as each step's input.  depth 1: the caller blocks on every
         step's result before submitting the next step; depth 2: it submits step i + 1, then collects the result of step i
         (what a loader-fed inference loop does), so the GPU does not idle while the host turns around."""
@@ -499,7 +623,7 @@ def run_b200(args):
                 if i + 1 < n:
                     prefetch(i + 1)
                 main_stream.wait_event(ready[i % 2])
-                step(xe[i % 2], yd[i % 2])
+                step(xe[i % 2], yd[i % 2], ip)
                 consumed[i % 2].record(main_stream)
                 yh[i % 2].copy_(yd[i % 2], non_blocking=True)
                 done[i % 2].record(main_stream)
@@ -510,21 +634,49 @@ def run_b200(args):
             done[(n - 1) % 2].synchronize()
 
         e2e_run(max(2, args.warmup // 2))
-        barrier()
-        e0.record()
-        e2e_run(args.steps)
-        e1.record()
-        torch.cuda.synchronize()
-        t = torch.tensor([e0.elapsed_time(e1)], device=device)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return world * G * args.steps / (float(t.item()) * 1e-3)
+        return rate(timed_blocks(e2e_run))[0]
 
+    # e2e: float32 images (the argument of the reference's model.forward), default options (status check on)
     e2e_value = e2e_measure(x_host, depth=2)
+    e2e_blocking = e2e_measure(x_host, depth=1)
+    e2e_nocheck = e2e_measure(x_host, depth=2, ip=int_params_nocheck)
     # the same call on the dataset's own 8-bit pixels (ToTensor's / 255 runs inside the first kernel): a quarter of the bytes
     x_host_u8 = [torch.randint(0, 256, (G, B, 3, 32, 32), dtype=torch.uint8, generator=gen).pin_memory() for _ in range(2)]
     e2e_u8_value = e2e_measure(x_host_u8, depth=2)
-    e2e_u8_blocking = e2e_measure(x_host_u8, depth=1)
+    e2e_u8_nocheck = e2e_measure(x_host_u8, depth=2, ip=int_params_nocheck)
+
+    # ---- the literal drop-in seam: module(x) on ONE batch of 256 (models.py:203-242), default options, host buffers ----
+    def single_call():
+        xh = x_host[0][0]
+        xd = torch.empty(B, 3, 32, 32, device=device)
+        yh = torch.empty(B, 10).pin_memory()
+        n = max(50, args.steps)
+
+        def run(k):
+            for _ in range(k):
+                xd.copy_(xh, non_blocking=True)
+                yh.copy_(ivp(xd, ts=ts, int_params=dict(method='dopri5', rtol=TOL, atol=TOL)), non_blocking=True)
+                torch.cuda.synchronize()
+        run(10)
+        barrier()
+        t0 = time.perf_counter()
+        e0.record()
+        run(n)
+        e1.record()
+        torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        t = torch.tensor([max(e0.elapsed_time(e1), wall * 1e3)], device=device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item()) / n
+        return dict(value=world / (ms * 1e-3), unit=UNIT, ms_per_call=ms, calls=n, h2d_bytes_per_call=B * 3 * 32 * 32 * 4, d2h_bytes_per_call=B * 40,
+                    note='IVP.forward(x) on one float32 batch of 256 from pinned host memory, default int_params (status check on), result copied '
+                         'to the host and waited for before the next call: one solve in flight, latency-bound (backbone on 256 images + one '
+                         'cooperative dopri5 launch); forward_batches is the same arithmetic with G solves in flight')
+    try:
+        e2e_single = single_call()
+    except Exception as e:
+        e2e_single = dict(error=repr(e))
 
     cert = None
     if not args.no_certify:
@@ -538,6 +690,12 @@ def run_b200(args):
             fi = fi_step_bench(device, pk, world)
         except Exception as e:           # secondary metric must not take the headline down
             fi = dict(error=repr(e))
+    seg, seg_cfg = None, None
+    if not args.no_segway:
+        try:
+            seg, seg_cfg = segway_bench(device, pk, world)
+        except Exception as e:
+            seg = dict(error=repr(e))
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -548,13 +706,26 @@ def run_b200(args):
     # ---- per-kernel device times (CUDA events on the launching stream) and the roofline of the dominant kernel ----
     roofline = stage_roofline(ivp, x_dev, G, ts, pk, cluster_size=CS)
 
+    # ---- BASELINE config 5: dopri5 batch / tolerance sweep with the oracle's step counts beside the GPU's (summary; the
+    #      table is tools/sweep.py -> profiles/) ------------------------------------------------------------------
+    sweep = None
+    if not args.no_sweep and world == 1:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, 'tools'))
+            import sweep as sweep_tool
+            rows = sweep_tool.sweep(iters=3, oracle_path=os.path.join(ROOT, 'profiles', 'r02_sweep_oracle.json'), dev=device)
+            sweep = sweep_tool.summary(rows)
+            sweep['table'] = 'tools/sweep.py (B 64..8192 x tol 1e-2..1e-5 x 3 dynamics x cooperative / cluster launches); profiles/r02_sweep_dopri5.md'
+        except Exception as e:
+            sweep = dict(error=repr(e))
+
     # ---- CPU baseline beside it (bounded sample) ----------------------------------------------------
     cpu = None
     if not args.no_cpu_baseline and world == 1:          # the contract asks for it on rank 0 at N=1 only
         threads = os.cpu_count() or 1
         n_cpu = 100                      # about 12 s of host work at ~8 solves/s
-        rate, secs = cpu_solve_rate(cpu_state_dict(ivp), n_cpu, threads)
-        cpu = dict(value=rate, unit=UNIT, cores=threads, kind='port',
+        rate_cpu, secs = cpu_solve_rate(cpu_state_dict(ivp), n_cpu, threads)
+        cpu = dict(value=rate_cpu, unit=UNIT, cores=threads, kind='port',
                    sample=f'{n_cpu} batch-256 solves (backbone + dopri5) in {secs:.1f} s on the same weights')
         # and the answer check that makes the timing meaningful
         from oracle import dynamics as od
@@ -563,27 +734,38 @@ def run_b200(args):
                               t_max=T_MAX, tol=TOL)
         got = ivp(xc.to(device), ts=ts, int_params=int_params).cpu()
         cpu['max_abs_diff_vs_cuda'] = float((got - want).abs().max())
+        legs = cpu_legs(ivp, device, seg_cfg, threads) if seg_cfg is not None else {}
+        for name, obj in (('certify', cert), ('fi_step', fi), ('segway', seg)):
+            if isinstance(obj, dict) and name in legs:
+                obj['cpu_baseline'] = legs[name]
 
-    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=args.warmup,
-                ms_per_step=ms_max / args.steps, higher_is_better=True, scaling='weak', vs_baseline=None,
+    d2h = G * B * 10 * 4
+    line = dict(metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
+                ms_per_step=ms_block / args.steps, higher_is_better=True, scaling='weak', vs_baseline=None,
                 dtype='f32', data='synthetic',
                 config=dict(workload='cifar_cayley_node_inference_dopri5_b256_tol1e-3_tmax1', batch=B,
                             solves_per_step=G, dopri5_cluster_size=CS, images_per_step=G * B, rtol=TOL, atol=TOL, t_max=T_MAX,
                             weights='random init, seed 0', l2='inputs rotate over %d device buffers (%.0f MB > L2)' % (
-                                NBUF, NBUF * per_set / 1e6), parallelism=f'independent batches x{world}', host_cpus_bound_to_gpu_numa=numa),
+                                NBUF, NBUF * per_set / 1e6), parallelism=f'independent batches x{world}', host_cpus_bound_to_gpu_numa=numa,
+                            options='public call defaults: end-of-solve status check on (one 96-byte-per-solve read + sync per step)'),
+                timing=dict(blocks=len(blocks), steps_per_block=args.steps, timed_seconds=sum(blocks) / 1e3, block_ms_median=ms_block,
+                            block_ms_min=min(blocks), block_ms_max=max(blocks),
+                            note='value = the median block of EXACTLY --steps steps; blocks repeat until >= 0.5 s have been timed'),
+                value_no_check=value_nc, ms_per_step_no_check=ms_block_nc / args.steps,
                 images_per_s=value * B,
-                # e2e: the dataset's 8-bit pixels in pinned host memory -> result on the host; ToTensor (/255, dataset_loaders.py:76-78)
-                # runs inside the first kernel, bit-identical to the float call (tests/test_gpu_parity.py).  e2e_f32_images: the
-                # same loop fed with ToTensor's float32 output (4x the bytes; host-memory bound once 8 ranks copy at once).
-                e2e=dict(value=e2e_u8_value, unit=UNIT, h2d_bytes_per_step=per_set // 4, d2h_bytes_per_step=G * B * 10 * 4,
-                         input='uint8 pixels (G,256,3,32,32) in pinned host memory, ToTensor fused into the first kernel',
-                         results_in_flight=2, blocking_value=e2e_u8_blocking,
+                # e2e: float32 images (the reference's argument) in pinned host memory -> result on the host, default options
+                e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=per_set, d2h_bytes_per_step=d2h,
+                         input='float32 images (G,256,3,32,32) in pinned host memory (the argument of model.forward), default options (status check on)',
+                         results_in_flight=2, blocking_value=e2e_blocking, value_no_check=e2e_nocheck,
                          note='every step: H2D copy of its inputs, the public forward_batches call, D2H copy of its result; the host '
                               'collects the result of step i after submitting step i + 1 (blocking_value: it waits for each result '
                               'before submitting the next step)'),
-                e2e_f32_images=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=per_set, d2h_bytes_per_step=G * B * 10 * 4,
-                                    input='float32 images in pinned host memory (the argument of model.forward)', results_in_flight=2),
-                gpu_launches=launches, clocks=clocks, roofline=roofline, cpu_baseline=cpu, certify=cert, fi_step=fi)
+                # the dataset's 8-bit pixels: ToTensor (/255, dataset_loaders.py:76-78) runs inside the first kernel, bit-identical to the float
+                # call (tests/test_gpu_parity.py), a quarter of the H2D bytes
+                e2e_u8_pixels=dict(value=e2e_u8_value, unit=UNIT, h2d_bytes_per_step=per_set // 4, d2h_bytes_per_step=d2h, value_no_check=e2e_u8_nocheck,
+                                   input='uint8 pixels in pinned host memory, ToTensor fused into the first kernel', results_in_flight=2),
+                e2e_single_call=e2e_single,
+                gpu_launches=launches, clocks=clocks, roofline=roofline, cpu_baseline=cpu, certify=cert, fi_step=fi, segway=seg, sweep=sweep)
     print(json.dumps(line))
     if world > 1:
         dist.barrier()
@@ -593,7 +775,7 @@ def run_b200(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=200)
+    ap.add_argument('--steps', type=int, default=50)
     ap.add_argument('--warmup', type=int, default=10)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
     ap.add_argument('--solves-per-step', type=int, default=0, help='0 = as many as one dopri5 launch keeps co-resident')
@@ -601,6 +783,9 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-certify', action='store_true')
     ap.add_argument('--no-fi', action='store_true')
+    ap.add_argument('--no-segway', action='store_true')
+    ap.add_argument('--no-sweep', action='store_true')
+    ap.add_argument('--min-seconds', type=float, default=0.5, help='repeat the K-step block until this much has been timed')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)

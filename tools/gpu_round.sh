@@ -10,10 +10,11 @@ python -c "import torchdiffeq; print(torchdiffeq.__version__)" > $OUT/torchdiffe
 timeout 900 python -m pytest tests -m gpu -x -q > $OUT/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a $OUT/rc.txt
 timeout 300 python __graft_entry__.py smoke > $OUT/smoke.log 2>&1; echo "smoke rc=$?" | tee -a $OUT/rc.txt
 timeout 600 python bench.py > $OUT/bench.json 2> $OUT/bench.err; echo "bench rc=$?" | tee -a $OUT/rc.txt
+if [ -n "$SWEEP" ]; then timeout 600 python tools/sweep.py --out $OUT/sweep_dopri5.md > $OUT/sweep.log 2>&1; echo "sweep rc=$?" | tee -a $OUT/rc.txt; fi
 timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > $OUT/bench_ref.json 2> $OUT/bench_ref.err; echo "ref rc=$?" | tee -a $OUT/rc.txt
 if [ -z "$SKIP_NCU" ]; then
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --csv --log-file $OUT/launches.csv \
-  python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-certify --no-fi > $OUT/ncu_launch.log 2>&1; echo "ncu-list rc=$?" | tee -a $OUT/rc.txt
+  python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-certify --no-fi --no-segway --no-sweep --min-seconds 0 > $OUT/ncu_launch.log 2>&1; echo "ncu-list rc=$?" | tee -a $OUT/rc.txt
 timeout 900 ncu --set full --clock-control none --import-source on --profile-from-start off -c 40 -f -o $OUT/full \
   python tools/prof_kernels.py all > $OUT/ncu_full.log 2>&1; echo "ncu-full rc=$?" | tee -a $OUT/rc.txt
 fi

@@ -2,9 +2,11 @@
 
     python tools/ncu_summary.py launches gpurun_out/<tag>/launches.csv  > profiles/rNN_launches_summary.md
     python tools/ncu_summary.py full     gpurun_out/<tag>/full.ncu-rep  > profiles/rNN_ncu_full_summary.md
+    python tools/ncu_summary.py traffic  gpurun_out/<tag>/full.ncu-rep  > profiles/ncu_traffic.json   (what bench.py's roofline.traffic reads)
 """
 import csv
 import io
+import re
 import subprocess
 import sys
 from collections import OrderedDict
@@ -76,5 +78,32 @@ def full(path):
         print()
 
 
+def traffic(path):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of every fiode kernel in the capture (tools/prof_kernels.py:
+    one 4096-image backbone pass + the 16-solve dopri5 launch + one certify call), as JSON keyed by the kernel name (a list per kernel, in launch order)."""
+    import json
+    import os
+    out = subprocess.run(['ncu', '-i', path, '--page', 'raw', '--csv'], capture_output=True, text=True, check=True).stdout
+    lines = [l for l in out.splitlines(True) if l.startswith('"')]
+    rd = list(csv.reader(io.StringIO(''.join(lines))))
+    head, units, data = rd[0], rd[1], rd[2:]
+    col = {h: i for i, h in enumerate(head)}
+    scale = {'byte': 1.0, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
+    tab = OrderedDict()
+    for r in data:
+        name = r[col['Kernel Name']]
+        if name.startswith('void at::') or name.startswith('at::'):
+            continue
+        by = sum(float(r[col[m]].replace(',', '')) * scale[units[col[m]]] for m in ('dram__bytes_read.sum', 'dram__bytes_write.sum'))
+        t = float(r[col['gpu__time_duration.sum']].replace(',', ''))
+        tu = units[col['gpu__time_duration.sum']]
+        t_us = t * {'ns': 1e-3, 'nsecond': 1e-3, 'us': 1.0, 'usecond': 1.0, 'ms': 1e3, 'msecond': 1e3}.get(tu, 1.0)
+        key = re.sub(r'\(.*$', '', name.replace('fiode::', '').replace('void ', ''))
+        tab.setdefault(key, []).append(dict(dram_bytes=by, us_under_ncu=t_us, grid=int(r[col['launch__grid_size']].replace(',', ''))))
+    print(json.dumps(dict(source=os.path.basename(os.path.dirname(os.path.abspath(path))) + '/' + os.path.basename(path),
+                          capture='tools/prof_kernels.py all: certify grid_20 x 296 images; one step of 16 batch-256 solves (4096 images)',
+                          backbone_images=4096, kernels=tab), indent=1))
+
+
 if __name__ == '__main__':
-    {'launches': launches, 'full': full}[sys.argv[1]](sys.argv[2])
+    {'launches': launches, 'full': full, 'traffic': traffic}[sys.argv[1]](sys.argv[2])
