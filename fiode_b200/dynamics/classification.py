@@ -7,7 +7,7 @@ from torch import nn
 
 from .. import ops
 from .._lib import DynWeights, ptr
-from ..layers import CayleyLinear
+from ..layers import CayleyLinear, _version
 from ..barrier_projection import FastBarrierProjectionNoUpper
 
 
@@ -34,7 +34,14 @@ class OrthoClassDynProjectSimplexLips(nn.Module):
     # ---- weights for the C ABI -------------------------------------------------------------------
     def dyn_weights(self):
         """(fiode_dyn_weights struct, tensors it points into).  Reads alpha_1 / alpha_2 / sigma_1 /
-        scale_nominal at call time because the training loop mutates them (pl_modules.py:392-393)."""
+        scale_nominal at call time because the training loop mutates them (pl_modules.py:392-393).  Cached per weight
+        version and hyper-parameter tuple."""
+        lays = (self.hidden_to_mlp, self.U_x, self.mlp_to_mlp, self.mlp_to_hidden)
+        key = tuple(_version(l.weight, l.alpha, l.bias) for l in lays) + (
+            float(self.alpha_1), float(self.alpha_2), float(self.sigma_1), bool(self.scale_nominal), self.max_iter, self.tol)
+        hit = getattr(self, '_dw_cache', None)
+        if hit is not None and hit[0] == key:
+            return hit[1]
         t = dict(Q1=self.hidden_to_mlp.orthogonal_weight(), b1=self.hidden_to_mlp.bias,
                  Qx=self.U_x.orthogonal_weight(), bx=self.U_x.bias,
                  Q2=self.mlp_to_mlp.orthogonal_weight(), b2=self.mlp_to_mlp.bias,
@@ -44,6 +51,7 @@ class OrthoClassDynProjectSimplexLips(nn.Module):
                         sigma_1=float(self.sigma_1), scale_nominal=int(bool(self.scale_nominal)),
                         max_iter=self.max_iter, tol=self.tol)
         dw._keep = t
+        self._dw_cache = (key, dw)
         return dw
 
     # ---- the reference's methods --------------------------------------------------------------------

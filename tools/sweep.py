@@ -49,7 +49,10 @@ def verdict(gpu, row):
 
 def sweep(iters=5, oracle_path=None, batches=BATCHES, tols=TOLS, dev=None):
     dev = dev or torch.device('cuda', 0)
-    ivp = bench.build_model(dev)
+    # the SAME weights and images as tools/sweep_oracle.py (tests/fixtures.py: reference-layout state_dict + seed-1234 images):
+    # the step controller is sensitive to the static features, so counts are only comparable on identical inputs
+    from tests import fixtures as fx
+    ivp = fx.build_b200_model(fx.synth_state_dict(), device=dev)
     dyn = ivp.dyn_fun
     pm = ivp.init_coordinates.param_map
     orc = {}
@@ -57,7 +60,7 @@ def sweep(iters=5, oracle_path=None, batches=BATCHES, tols=TOLS, dev=None):
         for r in json.load(open(oracle_path))['rows']:
             orc[(r['case'], r['B'], r['tol'])] = r
     nmax = max(batches)
-    x = torch.rand(nmax, 3, 32, 32, generator=torch.Generator().manual_seed(1234)).to(dev)
+    x = torch.cat([fx.synth_images(256, seed=1234), torch.rand(max(nmax - 256, 0), 3, 32, 32, generator=torch.Generator().manual_seed(4321))])[:nmax].to(dev)
     s_all = torch.cat([pm(x[i:i + 4096]) for i in range(0, nmax, 4096)])
     h_all = torch.full((nmax, 10), 0.1, device=dev)
     rows = []
