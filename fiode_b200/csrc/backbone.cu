@@ -19,6 +19,10 @@ int launch_irfft2(const float2* Yf, int B, int C, int n, const float* bias, int 
                   int freq_major = 0);
 int launch_irfft32_mix3(const float2* Xf, const float2* Qf, float2* Qt, int B, int C, const float* bias, int gs, float* y,
                         cudaStream_t st);
+size_t dft32_consts_bytes();
+int launch_dft32_consts(void* out, cudaStream_t st);
+int launch_irfft32_mix3_tc(const float2* Xf, const float2* Qt, const void* consts, int B, const float* bias, int gs, float* y,
+                           cudaStream_t st);
 int launch_mix_real_weights(const float2* Qf, int F, int cout, int cin, float* W, cudaStream_t st);
 int launch_transpose_q(const float2* Qf, int F, int CC, float2* Qt, cudaStream_t st);
 int launch_mix(const float2* Xf, const float2* Qf, int B, int F, int cout, int cin, float2* Yf, cudaStream_t st);
@@ -56,7 +60,7 @@ struct SlabLayout {
 };
 // Kernel-ready copies of the prepared weights (one block, filled by pack_weights): fp16x2-split MMA tiles of the four
 // real matrices, model.4's mixing as 144 real (128 x 64) matrices (fp32 staging + tiles), model.0's transposed spectrum.
-struct PackedLayout { size_t p2, p6, p9, p11, w4, p4, qt0, total; };
+struct PackedLayout { size_t p2, p6, p9, p11, w4, p4, qt0, dft0, total; };
 static size_t al(size_t x) { return (x + 255) & ~(size_t)255; }
 static PackedLayout packed_layout() {
     PackedLayout L; size_t o = 0;
@@ -65,6 +69,7 @@ static PackedLayout packed_layout() {
     L.p9 = take(gemm_tc_packed_bytes(512, 4096)); L.p11 = take(gemm_tc_packed_bytes(512, 512));
     L.w4 = take((size_t)144 * 128 * 64 * 4); L.p4 = take((size_t)144 * gemm_tc_packed_bytes(128, 64));
     L.qt0 = take((size_t)544 * 32 * 3 * 8);
+    L.dft0 = take(dft32_consts_bytes());         // fp16 hi / lo DFT matrices of the tensor-core inverse transform (dft_tc.cu)
     L.total = o;
     return L;
 }
@@ -103,10 +108,20 @@ static int pack_weights(const fiode_backbone_weights* w, char* pk, cudaStream_t 
     if ((rc = launch_pack_w(w->Q11, 512, 512, gemm_tc_tile(512, 1), 1, pk + P.p11, st))) return rc;
     if ((rc = launch_mix_real_weights((const float2*)w->Qf4, 144, 64, 32, (float*)(pk + P.w4), st))) return rc;
     if ((rc = launch_pack_w((const float*)(pk + P.w4), 128, 64, 128, 0, pk + P.p4, st, 144))) return rc;
-    return launch_transpose_q((const float2*)w->Qf0, 544, 32 * 3, (float2*)(pk + P.qt0), st);
+    if ((rc = launch_transpose_q((const float2*)w->Qf0, 544, 32 * 3, (float2*)(pk + P.qt0), st))) return rc;
+    return launch_dft32_consts(pk + P.dft0, st);
+}
+// model.0's inverse transform: 0 (default) = CUDA-core FFT kernel, 1 = two DFT GEMMs on tcgen05 (dft_tc.cu; FIODE_CONV0=tc or
+// fiode_backbone_set_conv0_path(1)).  Measured equal in time on 8192 images (0.584 vs 0.592 ms, profiles/r02_dft_tc_*.md): the
+// tensor-core version is bound by the shared-memory pipe and by latency at 12 warps per SM, see DESIGN.md section 7.
+static int g_conv0_path = -1;
+static bool conv0_tc() {
+    if (g_conv0_path < 0) { const char* e = getenv("FIODE_CONV0"); g_conv0_path = (e && e[0] == 't') ? 1 : 0; }
+    return g_conv0_path == 1;
 }
 
 extern "C" int fiode_backbone_slab_images(void) { return kSlab; }
+extern "C" void fiode_backbone_set_conv0_path(int path) { g_conv0_path = path == 1 ? 1 : 0; }
 extern "C" size_t fiode_backbone_packed_bytes(void) { return packed_layout().total; }
 extern "C" int fiode_backbone_pack(const fiode_backbone_weights* w, void* packed, size_t packed_bytes, void* stream) {
     if (!w || !packed) { set_error("fiode_backbone_pack: null pointer"); return -1; }
@@ -150,7 +165,9 @@ static int backbone_fwd(const fiode_backbone_weights* w, const float* x, bool x_
         if ((rc = launch_rfft2(xs, nb * 3, 3, 32, w->mu, w->std, xf0, st, false, x_u8))) return rc;
         mark(2, st);
         if (tcp) {   // mixing fused into the inverse FFT: the 32-channel spectrum never reaches HBM
-            if ((rc = launch_irfft32_mix3(xf0, nullptr, (float2*)(pk + P.qt0), nb, 32, w->b0, 1, a0, st))) return rc;
+            if (conv0_tc()) {
+                if ((rc = launch_irfft32_mix3_tc(xf0, (const float2*)(pk + P.qt0), pk + P.dft0, nb, w->b0, 1, a0, st))) return rc;
+            } else if ((rc = launch_irfft32_mix3(xf0, nullptr, (float2*)(pk + P.qt0), nb, 32, w->b0, 1, a0, st))) return rc;
         } else {
             if ((rc = launch_mix(xf0, (const float2*)w->Qf0, nb, 544, 32, 3, yf0, st))) return rc;
             if ((rc = launch_irfft2(yf0, nb, 32, 32, w->b0, 1, a0, st))) return rc;

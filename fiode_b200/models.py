@@ -69,6 +69,7 @@ class ParamMap(nn.Sequential):
             (norm.mu.data_ptr(), norm.std.data_ptr())
         hit = getattr(self, '_bw_cache', None)
         if hit is not None and hit[0] == vkey and all(l.alpha is not None for l in lays):
+            hit[1].packed = ptr(self._packed)            # callers may clear it to force per-call packing
             return hit[1], hit[2]
         t = dict(mu=norm.mu.reshape(-1), std=norm.std.reshape(-1),
                  Qf0=torch.view_as_real(m[0].orthogonal_spectrum(32)), b0=m[0].bias,

@@ -519,6 +519,28 @@ def test_backbone_tensor_core_path_matches_ffma_path(ops, sd):
     assert (got - want).abs().max().item() < 1e-5
 
 
+def test_backbone_conv0_dft_tensor_core_path(ops, sd):
+    """model.0 with the inverse transform as two DFT GEMMs on tcgen05 (csrc/dft_tc.cu, packed Nyquist column) against the FFT
+    kernel on the same spectra, and against the oracle backbone; ragged batch sizes exercise the image slicing."""
+    from fiode_b200._lib import lib
+    from oracle import layers as ol
+    ivp = fx.build_b200_model(sd, device='cuda:0')
+    bw, keep = ivp.init_coordinates.param_map.backbone_weights()
+    for B in (1, 5, 37, 200, 515):
+        x = dev(fx.synth_images(B, seed=100 + B))
+        try:
+            lib().fiode_backbone_set_conv0_path(0)
+            want = ops.backbone_fwd(bw, x)
+            lib().fiode_backbone_set_conv0_path(1)
+            got = ops.backbone_fwd(bw, x)
+        finally:
+            lib().fiode_backbone_set_conv0_path(0)
+        assert (got - want).abs().max().item() < 5e-6, B
+        if B == 37:
+            ref = ol.backbone_forward(x.cpu(), sd, fx.PM)
+            torch.testing.assert_close(got.cpu(), ref, rtol=1e-4, atol=2e-5)
+
+
 def test_backbone_u8_pixels_equal_totensor_floats(ops, sd):
     """fiode_backbone_fwd_u8 on the dataset's 8-bit pixels == fiode_backbone_fwd on ToTensor's floats (p / 255,
     dataset_loaders.py:76-78), bit for bit, through the module call and through forward_batches; and the packed-weight
