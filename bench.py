@@ -532,7 +532,10 @@ def run_b200(args):
     ivp = build_model(device)
     ts = torch.linspace(0., T_MAX, 2)
     # the public call with its DEFAULT options: the end-of-solve status read (torchdiffeq's assertions) is on
-    int_params = dict(method='dopri5', rtol=TOL, atol=TOL, options=dict(cluster_size=CS))
+    # graph=True: the pass is replayed from a CUDA graph (fiode_b200/models.py), so the host turn-around after the status read is one
+    # graph launch instead of ~15 kernel launches; value_eager is the same call without it
+    int_params = dict(method='dopri5', rtol=TOL, atol=TOL, options=dict(cluster_size=CS, graph=not args.no_graph))
+    int_params_eager = dict(method='dopri5', rtol=TOL, atol=TOL, options=dict(cluster_size=CS))
     int_params_nocheck = dict(method='dopri5', rtol=TOL, atol=TOL, options=dict(check=False, cluster_size=CS))
 
     # inputs: NBUF rotating device-resident sets, together larger than the 126 MB L2
@@ -584,12 +587,15 @@ def run_b200(args):
     if rank == 0:
         sampler.start()
     fiode_b200.reset_launch_count()
+    step(x_dev[0], y_dev, int_params_eager)          # the pass's own kernels, counted on one eager pass (graph replays launch the same nodes)
+    launches_per_step = fiode_b200.launch_count()
     blocks = timed_blocks(lambda n: [step(x_dev[i % NBUF], y_dev) for i in range(n)])
-    launches = fiode_b200.launch_count() // len(blocks)
+    launches = launches_per_step * args.steps
     clocks = sampler.stop() if rank == 0 else None
     value, ms_block = rate(blocks)
     blocks_nc = timed_blocks(lambda n: [step(x_dev[i % NBUF], y_dev, int_params_nocheck) for i in range(n)])
     value_nc, ms_block_nc = rate(blocks_nc)
+    value_eager = rate(timed_blocks(lambda n: [step(x_dev[i % NBUF], y_dev, int_params_eager) for i in range(n)]))[0]
 
     # ---- end to end through the public API with host buffers (e2e) ------------------------------
     # Every step copies its own inputs host -> device (pinned) and its result device -> host inside the timed region.
@@ -747,11 +753,11 @@ def run_b200(args):
                             solves_per_step=G, dopri5_cluster_size=CS, images_per_step=G * B, rtol=TOL, atol=TOL, t_max=T_MAX,
                             weights='random init, seed 0', l2='inputs rotate over %d device buffers (%.0f MB > L2)' % (
                                 NBUF, NBUF * per_set / 1e6), parallelism=f'independent batches x{world}', host_cpus_bound_to_gpu_numa=numa,
-                            options='public call defaults: end-of-solve status check on (one 96-byte-per-solve read + sync per step)'),
+                            options='end-of-solve status check on (the default: one 4-byte read + sync per step), options.graph=%s (CUDA-graph replay of the pass)' % (not args.no_graph)),
                 timing=dict(blocks=len(blocks), steps_per_block=args.steps, timed_seconds=sum(blocks) / 1e3, block_ms_median=ms_block,
                             block_ms_min=min(blocks), block_ms_max=max(blocks),
                             note='value = the median block of EXACTLY --steps steps; blocks repeat until >= 0.5 s have been timed'),
-                value_no_check=value_nc, ms_per_step_no_check=ms_block_nc / args.steps,
+                value_no_check=value_nc, ms_per_step_no_check=ms_block_nc / args.steps, value_eager_launches=value_eager,
                 images_per_s=value * B,
                 # e2e: float32 images (the reference's argument) in pinned host memory -> result on the host, default options
                 e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=per_set, d2h_bytes_per_step=d2h,
@@ -765,7 +771,7 @@ def run_b200(args):
                 e2e_u8_pixels=dict(value=e2e_u8_value, unit=UNIT, h2d_bytes_per_step=per_set // 4, d2h_bytes_per_step=d2h, value_no_check=e2e_u8_nocheck,
                                    input='uint8 pixels in pinned host memory, ToTensor fused into the first kernel', results_in_flight=2),
                 e2e_single_call=e2e_single,
-                gpu_launches=launches, clocks=clocks, roofline=roofline, cpu_baseline=cpu, certify=cert, fi_step=fi, segway=seg, sweep=sweep)
+                gpu_launches=launches, gpu_launches_per_step=launches_per_step, clocks=clocks, roofline=roofline, cpu_baseline=cpu, certify=cert, fi_step=fi, segway=seg, sweep=sweep)
     print(json.dumps(line))
     if world > 1:
         dist.barrier()
@@ -785,6 +791,7 @@ def main():
     ap.add_argument('--no-fi', action='store_true')
     ap.add_argument('--no-segway', action='store_true')
     ap.add_argument('--no-sweep', action='store_true')
+    ap.add_argument('--no-graph', action='store_true', help='eager launches in the headline loop instead of options.graph=True')
     ap.add_argument('--min-seconds', type=float, default=0.5, help='repeat the K-step block until this much has been timed')
     args = ap.parse_args()
     if args.impl == 'reference':

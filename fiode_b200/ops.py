@@ -376,12 +376,15 @@ class BatchedSolveResult:
             self._stats = [SolveStats.from_buffer_copy(raw[g * n:(g + 1) * n]) for g in range(self.G)]
         return self._stats
 
+    def status_max(self):
+        """Largest status word of the G solves, on the device (0 = every solve finished)."""
+        return self._buf.view(torch.int32).view(self.G, -1)[:, 3].max()             # SolveStats.status
+
     def raise_for_status(self):
         """The end-of-solve check (torchdiffeq's assertions): ONE 4-byte read -- the largest status word of the G solves --
         and the full statistics only when it is non-zero."""
         if self._stats is None:
-            words = self._buf.view(torch.int32).view(self.G, -1)[:, 3]          # SolveStats.status
-            if int(words.max()) == 0:
+            if int(self.status_max()) == 0:
                 return self
         for st in self.stats():
             if st.status:

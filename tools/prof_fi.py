@@ -29,6 +29,7 @@ mod = pl_modules.LyapunovLearning(
     sampler_scheduler=sch.CompositeSamplerScheduler([sch.ConstantScheduler(0.5), sch.ConstantScheduler(0.5)], [1., 1.]),
     dynamics=dyn, output=DefaultOutputFun(), init_fun=UniformInitFun((10,), param_map=pm), t_max=1.0,
     train_ode_tol=1e-3, val_ode_tol=1e-3, epoch_off_scale=10).to(dev).train()
+mod.current_epoch, mod.global_step = 0, 10 ** 9
 x = torch.rand(Bt, 3, 32, 32, generator=torch.Generator().manual_seed(1234)).to(dev)
 y = torch.randint(0, 10, (Bt,), generator=torch.Generator().manual_seed(1235)).to(dev)
 
