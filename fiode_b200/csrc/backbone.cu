@@ -23,6 +23,8 @@ size_t dft32_consts_bytes();
 int launch_dft32_consts(void* out, cudaStream_t st);
 int launch_irfft32_mix3_tc(const float2* Xf, const float2* Qt, const void* consts, int B, const float* bias, int gs, float* y,
                            cudaStream_t st);
+int launch_irfft32_mix3_tc2(const float2* Xf, const float2* Qt, const void* consts, int B, const float* bias, int gs, float* y,
+                            cudaStream_t st);
 int launch_mix_real_weights(const float2* Qf, int F, int cout, int cin, float* W, cudaStream_t st);
 int launch_transpose_q(const float2* Qf, int F, int CC, float2* Qt, cudaStream_t st);
 int launch_mix(const float2* Xf, const float2* Qf, int B, int F, int cout, int cin, float2* Yf, cudaStream_t st);
@@ -115,13 +117,13 @@ static int pack_weights(const fiode_backbone_weights* w, char* pk, cudaStream_t 
 // fiode_backbone_set_conv0_path(1)).  Measured equal in time on 8192 images (0.584 vs 0.592 ms, profiles/r02_dft_tc_*.md): the
 // tensor-core version is bound by the shared-memory pipe and by latency at 12 warps per SM, see DESIGN.md section 7.
 static int g_conv0_path = -1;
-static bool conv0_tc() {
-    if (g_conv0_path < 0) { const char* e = getenv("FIODE_CONV0"); g_conv0_path = (e && e[0] == 't') ? 1 : 0; }
-    return g_conv0_path == 1;
+static int conv0_path() {
+    if (g_conv0_path < 0) { const char* e = getenv("FIODE_CONV0"); g_conv0_path = (e && e[0] == 't') ? ((e[1] == 'c' && e[2] == '2') ? 2 : 1) : 0; }
+    return g_conv0_path;
 }
 
 extern "C" int fiode_backbone_slab_images(void) { return kSlab; }
-extern "C" void fiode_backbone_set_conv0_path(int path) { g_conv0_path = path == 1 ? 1 : 0; }
+extern "C" void fiode_backbone_set_conv0_path(int path) { g_conv0_path = (path == 1 || path == 2) ? path : 0; }
 extern "C" size_t fiode_backbone_packed_bytes(void) { return packed_layout().total; }
 extern "C" int fiode_backbone_pack(const fiode_backbone_weights* w, void* packed, size_t packed_bytes, void* stream) {
     if (!w || !packed) { set_error("fiode_backbone_pack: null pointer"); return -1; }
@@ -165,7 +167,9 @@ static int backbone_fwd(const fiode_backbone_weights* w, const float* x, bool x_
         if ((rc = launch_rfft2(xs, nb * 3, 3, 32, w->mu, w->std, xf0, st, false, x_u8))) return rc;
         mark(2, st);
         if (tcp) {   // mixing fused into the inverse FFT: the 32-channel spectrum never reaches HBM
-            if (conv0_tc()) {
+            if (conv0_path() == 2) {
+                if ((rc = launch_irfft32_mix3_tc2(xf0, (const float2*)(pk + P.qt0), pk + P.dft0, nb, w->b0, 1, a0, st))) return rc;
+            } else if (conv0_path() == 1) {
                 if ((rc = launch_irfft32_mix3_tc(xf0, (const float2*)(pk + P.qt0), pk + P.dft0, nb, w->b0, 1, a0, st))) return rc;
             } else if ((rc = launch_irfft32_mix3(xf0, nullptr, (float2*)(pk + P.qt0), nb, 32, w->b0, 1, a0, st))) return rc;
         } else {
@@ -214,6 +218,23 @@ static int backbone_fwd(const fiode_backbone_weights* w, const float* x, bool x_
     }
     FIODE_CUDA(cudaGetLastError());
     return 0;
+}
+
+// model.0 alone (debug / tests): x (B,3,32,32) -> a0 (B,32,32,32) through conv0 path 0 | 1 | 2; ws as for fiode_backbone_fwd, B <= slab
+extern "C" __attribute__((visibility("default"))) int fiode_debug_conv0(const fiode_backbone_weights* w, const float* x, int B, int path,
+                                                                        float* a0_out, void* ws, size_t ws_bytes, void* stream) {
+    cudaStream_t st = (cudaStream_t)stream;
+    const SlabLayout L = slab_layout(B);
+    if (!w || !w->packed || ws_bytes < L.total || B > kSlab) { set_error("fiode_debug_conv0: bad arguments"); return -1; }
+    char* base = reinterpret_cast<char*>(ws);
+    float2* xf0 = (float2*)(base + L.xf0);
+    const PackedLayout P = packed_layout();
+    char* pk = reinterpret_cast<char*>(const_cast<void*>(w->packed));
+    int rc;
+    if ((rc = launch_rfft2(x, B * 3, 3, 32, w->mu, w->std, xf0, st, false, false))) return rc;
+    if (path == 2) return launch_irfft32_mix3_tc2(xf0, (const float2*)(pk + P.qt0), pk + P.dft0, B, w->b0, 1, a0_out, st);
+    if (path == 1) return launch_irfft32_mix3_tc(xf0, (const float2*)(pk + P.qt0), pk + P.dft0, B, w->b0, 1, a0_out, st);
+    return launch_irfft32_mix3(xf0, nullptr, (float2*)(pk + P.qt0), B, 32, w->b0, 1, a0_out, st);
 }
 
 extern "C" int fiode_backbone_fwd(const fiode_backbone_weights* w, const float* x, int B, float* s_out, void* ws,

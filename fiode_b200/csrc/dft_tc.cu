@@ -316,6 +316,342 @@ irfft32_mix3_tc_kernel(const float2* __restrict__ Xf, const float2* __restrict__
     if (warp == 0) tmem_dealloc(tmem, 512);
 }
 
+
+// =====================================================================================================================
+// Version 2: warp-specialised.  The first kernel above delivers every mixing operand through shared memory (2 x 96 complex
+// values per lane and unit: 1 536 of its 2 900 shared-memory wavefronts per unit, profiles/r02_dft_tc_ncu.md) and runs one
+// serial pipeline per warpgroup.  Here
+//   8 mixer warps   thread = two (u, v') frequency pairs over ALL 8 channels of the CTA: its 2 x 24 complex entries of Q
+//                   never move (pair A in registers, pair B in 48 TMEM columns of its own lane); per image it loads 6
+//                   complex X values, forms the 16 mixed values, splits them and writes the A operand of the column pass
+//                   into a shared-memory ring in the tcgen05 K-major core-matrix layout (conflict-free 4-byte stores)
+//   2 Nyquist warps the v = 16 column (32 frequencies x 8 channels), handed to the lanes that own v' = 0
+//   8 tail warps    two warpgroups alternating images: D1 (TMEM) -> transposition -> A2 (TMEM) -> D2 -> GroupSort -> stores
+//   1 MMA thread    both GEMMs of both tail warpgroups, issued as their operands become ready (non-blocking polling)
+//   1 copy thread   TMA bulk copies of the 3-channel input spectra into a 3-deep ring
+// connected by mbarrier rings only (no CTA-wide barrier in the loop); setmaxnreg moves registers to the mixers.
+// =====================================================================================================================
+namespace {
+constexpr int V_THREADS = 640;
+constexpr int V_NX = 3, V_NA = 2;
+constexpr int kRegsTail = 88, kRegsMix = 128, kRegsAux = 48;
+static_assert(256 * kRegsTail + 256 * kRegsMix + 128 * kRegsAux <= 96 * V_THREADS, "setmaxnreg.inc would block");
+constexpr uint32_t kA1Bytes = 2 * 128 * 64 * 2;                 // hi + lo blocks of one A1 tile: 32 768
+constexpr uint32_t kS2Words = 2 * 32 * 32 + 16;                 // [j 2][a 32][k 32] floats, j = 1 block shifted by 16 words
+constexpr uint32_t kS2Bytes = 8320;
+static_assert(kS2Words * 4 <= kS2Bytes, "S tile");
+constexpr uint32_t V_OFF_CONST = 0;
+constexpr uint32_t V_OFF_A1 = V_OFF_CONST + kConstBytes;                       //  20 480
+constexpr uint32_t V_OFF_XS = V_OFF_A1 + V_NA * kA1Bytes;                      //  86 016
+constexpr uint32_t V_OFF_Y16 = V_OFF_XS + V_NX * kXsBytes;                     // 125 184
+constexpr uint32_t V_OFF_Q16 = V_OFF_Y16 + 2 * 2048;                           // 129 280
+constexpr uint32_t V_OFF_S = V_OFF_Q16 + 8 * 3 * 32 * 8;                       // 135 424
+constexpr uint32_t V_OFF_BARS = V_OFF_S + 8 * kS2Bytes;                        // 201 984
+constexpr uint32_t V_SMEM = V_OFF_BARS + 32 * 8 + 16;
+enum { BX_FULL = 0, BX_EMPTY = 3, BA_FULL = 6, BA_EMPTY = 8, BY_FULL = 10, BY_EMPTY = 12, BD1_FULL = 14, BD1_FREE = 16,
+       BA2_FULL = 18, BD2_FULL = 20, B_COUNT = 22 };
+
+__device__ __forceinline__ void tmem_ld16f(uint32_t addr, float* v) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                 : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7]),
+                   "=f"(v[8]), "=f"(v[9]), "=f"(v[10]), "=f"(v[11]), "=f"(v[12]), "=f"(v[13]), "=f"(v[14]), "=f"(v[15])
+                 : "r"(addr) : "memory");
+}
+// mbarrier.arrive that releases a buffer this thread has READ: the arrive must not be issued before the loads have returned.
+// Issue is in order, so it is enough that instructions consuming the loaded values precede it; the (unused) operands tie the
+// arrive to their results, which keeps the compiler from hoisting it above them.
+__device__ __forceinline__ void mbar_arrive_after(uint64_t* bar, float d0, float d1, float d2, float d3) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)), "f"(d0), "f"(d1), "f"(d2), "f"(d3) : "memory");
+}
+__device__ __forceinline__ void cmac(float2& acc, float2 q, float2 x) {
+    acc.x = fmaf(q.x, x.x, acc.x); acc.x = fmaf(-q.y, x.y, acc.x);
+    acc.y = fmaf(q.x, x.y, acc.y); acc.y = fmaf(q.y, x.x, acc.y);
+}
+}  // namespace
+
+__global__ void __launch_bounds__(V_THREADS, 1)
+irfft32_mix3_tc2_kernel(const float2* __restrict__ Xf, const float2* __restrict__ Qt, const __half* __restrict__ consts, int B,
+                        const float* __restrict__ bias, int group_sort, float* __restrict__ y) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + V_OFF_BARS);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 32);
+    const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+    const int cg = blockIdx.x & 3, slice = blockIdx.x >> 2, nslices = gridDim.x >> 2;
+    const int N = slice < B ? (B - slice + nslices - 1) / nslices : 0;       // units (images) of this CTA: img = slice + nslices * n
+    auto chan = [&](int slot) { return 4 * cg + (slot >> 1) + 16 * (slot & 1); };   // slot = 2 q + j: GroupSort pairs (c, c + 16)
+
+    if (warp == 16) tmem_alloc(tmem_slot, 512);
+    if (t == 0) {
+        for (int k = 0; k < V_NX; ++k) { mbar_init(&bars[BX_FULL + k], 1); mbar_init(&bars[BX_EMPTY + k], 256 + 64); }
+        for (int k = 0; k < 2; ++k) {
+            mbar_init(&bars[BA_FULL + k], 256); mbar_init(&bars[BA_EMPTY + k], 1);
+            mbar_init(&bars[BY_FULL + k], 64); mbar_init(&bars[BY_EMPTY + k], 32);
+            mbar_init(&bars[BD1_FULL + k], 1); mbar_init(&bars[BD1_FREE + k], 128);
+            mbar_init(&bars[BA2_FULL + k], 128); mbar_init(&bars[BD2_FULL + k], 1);
+        }
+        mbar_init_fence();
+    }
+    for (int e = t; e < (int)(kConstBytes / 16); e += V_THREADS)
+        reinterpret_cast<float4*>(smem + V_OFF_CONST)[e] = __ldg(reinterpret_cast<const float4*>(consts) + e);
+    for (int e = t; e < 8 * 3 * 32; e += V_THREADS) {           // Nyquist column of the CTA's Q slice: [slot][c][u]
+        const int slot = e / 96, c = (e / 32) % 3, u = e & 31;
+        reinterpret_cast<float2*>(smem + V_OFF_Q16)[e] = __ldg(Qt + ((size_t)chan(slot) * 3 + c) * D_F + u * D_H + 16);
+    }
+    fence_proxy_async();
+    fence_before_sync();
+    __syncthreads();
+    fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+
+    if (warp < 8) {
+        // ============================ tails: two warpgroups alternating units ======================================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsTail));
+        const int tw = warp >> 2, q = warp & 3, j = lane >> 4, i = lane & 15;
+        const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16) + tw * 192;    // A2 [0,64) D1 [64,128) D2 [128,192)
+        float* S = reinterpret_cast<float*>(smem + V_OFF_S + warp * kS2Bytes);
+        const uint32_t sj = j * (1024 + 16);
+        const float bs0 = bias ? __ldg(bias + chan(2 * q)) : 0.f, bs1 = bias ? __ldg(bias + chan(2 * q + 1)) : 0.f;
+        uint64_t* d1_full = &bars[BD1_FULL + tw], *d1_free = &bars[BD1_FREE + tw], *a2_full = &bars[BA2_FULL + tw], *d2_full = &bars[BD2_FULL + tw];
+        for (int n = tw, k = 0; n < N; n += 2, ++k) {
+            const uint32_t ph = k & 1;
+            const int img = slice + nslices * n;
+            mbar_wait(d1_full, ph);
+            fence_after_sync();
+            // D1 row (slot 2q + j, v' = i): columns n = 32 h + 2 a' + (re | im), a = 16 h + a'  ->  S[j][a][k], k = v' | 16 + v'
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                float d[32];
+                tmem_ld32f(lane_base + 64 + h * 32, d);
+                tmem_wait_ld();
+                if (h == 1) { fence_before_sync(); mbar_arrive(d1_free); }      // D1 is in registers: the next column pass may overwrite it
+#pragma unroll
+                for (int a = 0; a < 16; ++a) {
+                    float* row = S + sj + (16 * h + a) * 32;
+                    row[i ^ ((a & 7) << 2)] = d[2 * a] * kS1;
+                    row[(16 + i) ^ ((a & 7) << 2)] = d[2 * a + 1] * kS1;
+                }
+            }
+            __syncwarp();
+            // rows (channel j', a = lane) of the row pass: tile A = channel slot 2q, tile B = its GroupSort partner 2q + 1
+#pragma unroll
+            for (int jj = 0; jj < 2; ++jj) {
+                const float* row = S + jj * (1024 + 16) + lane * 32;
+                const int xi = (lane & 7) << 2;
+                uint32_t hi[16], lo[16];
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const float4 w = *reinterpret_cast<const float4*>(row + ((c << 2) ^ xi));
+                    split_pair(w.x, w.y, hi[2 * c], lo[2 * c]);
+                    split_pair(w.z, w.w, hi[2 * c + 1], lo[2 * c + 1]);
+                }
+                tmem_st16(lane_base + jj * 32, hi);
+                tmem_st16(lane_base + jj * 32 + 16, lo);
+            }
+            tmem_wait_st();
+            fence_before_sync();
+            mbar_arrive(a2_full);
+            __syncwarp();                         // every lane has read its S rows: the tile is free for the output staging
+            mbar_wait(d2_full, ph);
+            fence_after_sync();
+            // epilogue: / 64, + bias, GroupSort of (tile A, tile B) in registers, smem, coalesced stores
+            {
+                float* ra = S + lane * 32;
+                float* rb = S + (1024 + 16) + lane * 32;
+                const int xi = (lane & 7) << 2;
+#pragma unroll
+                for (int cc = 0; cc < 2; ++cc) {
+                    float da[16], db[16];
+                    tmem_ld16f(lane_base + 128 + cc * 16, da);
+                    tmem_ld16f(lane_base + 160 + cc * 16, db);
+                    tmem_wait_ld();
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        float hi4[4], lo4[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const float u = fmaf(da[4 * c + e], kWSInv, bs0), w = fmaf(db[4 * c + e], kWSInv, bs1);
+                            hi4[e] = group_sort ? fmaxf(u, w) : u;
+                            lo4[e] = group_sort ? fminf(u, w) : w;
+                        }
+                        const int pc = (((cc * 4 + c) << 2) ^ xi);
+                        *reinterpret_cast<float4*>(ra + pc) = make_float4(hi4[0], hi4[1], hi4[2], hi4[3]);
+                        *reinterpret_cast<float4*>(rb + pc) = make_float4(lo4[0], lo4[1], lo4[2], lo4[3]);
+                    }
+                }
+            }
+            fence_before_sync();
+            __syncwarp();
+#pragma unroll
+            for (int s = 0; s < 16; ++s) {
+                const int R = 4 * s + (lane >> 3), jj = R >> 5, a = R & 31, c = lane & 7;
+                const float4 w = *reinterpret_cast<const float4*>(S + jj * (1024 + 16) + a * 32 + ((c ^ (a & 7)) << 2));
+                *reinterpret_cast<float4*>(y + (((size_t)img * 32 + chan(2 * q + jj)) * 32 + a) * 32 + 4 * c) = w;
+            }
+            __syncwarp();
+        }
+    } else if (warp < 16) {
+        // ============================ mixers ==================================================================
+        asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(kRegsMix));
+        const int mw = warp - 8, mg = mw >> 2, ul = lane & 3, vl = lane >> 2;
+        const int u = 4 * mw + ul;
+        const uint32_t tq = tmem + ((uint32_t)((warp & 3) * 32) << 16) + 384 + mg * 48;     // pair B's Q: column c * 16 + slot * 2 + (re | im)
+        float2 qa[3][8];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            uint32_t qb[16];
+#pragma unroll
+            for (int slot = 0; slot < 8; ++slot) {
+                const float2* src = Qt + ((size_t)chan(slot) * 3 + c) * D_F + u * D_H;
+                qa[c][slot] = __ldg(src + vl);
+                const float2 b = __ldg(src + 8 + vl);
+                qb[2 * slot] = __float_as_uint(b.x); qb[2 * slot + 1] = __float_as_uint(b.y);
+            }
+            tmem_st16(tq + c * 16, qb);
+        }
+        tmem_wait_st();
+        // word offset of this lane's (re, im) pair inside an A1 block: core matrix (u >> 2, row >> 3), row & 7, k & 7 = 2 (u & 3)
+        const uint32_t wofs = (uint32_t)(u >> 2) * 512 + (uint32_t)vl * 4 + (uint32_t)(u & 3);      // + row0 * 4, row0 = 16 slot (+ 8 for pair B)
+        for (int n = 0; n < N; ++n) {
+            const int xb = n % V_NX, ab = n & 1;
+            mbar_wait(&bars[BX_FULL + xb], (uint32_t)((n / V_NX) & 1));
+            const float2* Xs = reinterpret_cast<const float2*>(smem + V_OFF_XS + xb * kXsBytes);
+            float2 xa[3], xbv[3];
+#pragma unroll
+            for (int c = 0; c < 3; ++c) { xa[c] = Xs[c * D_F + u * D_H + vl]; xbv[c] = Xs[c * D_F + u * D_H + 8 + vl]; }
+            float2 acc[8];
+#pragma unroll
+            for (int slot = 0; slot < 8; ++slot) {
+                acc[slot] = make_float2(0.f, 0.f);
+#pragma unroll
+                for (int c = 0; c < 3; ++c) cmac(acc[slot], qa[c][slot], xa[c]);
+            }
+            if (vl == 0) {                         // packed column: P[u] = Y[u][0] + i Y[u][16]
+                mbar_wait(&bars[BY_FULL + ab], (uint32_t)((n >> 1) & 1));
+                const float2* Y16 = reinterpret_cast<const float2*>(smem + V_OFF_Y16 + ab * 2048);
+#pragma unroll
+                for (int slot = 0; slot < 8; ++slot) { const float2 w = Y16[slot * 32 + u]; acc[slot].x -= w.y; acc[slot].y += w.x; }
+                mbar_arrive_after(&bars[BY_EMPTY + ab], acc[0].x + acc[1].x, acc[2].x + acc[3].x, acc[4].x + acc[5].x, acc[6].x + acc[7].x);
+            }
+            mbar_wait(&bars[BA_EMPTY + ab], (uint32_t)(((n >> 1) & 1) ^ 1));
+            uint32_t* A1 = reinterpret_cast<uint32_t*>(smem + V_OFF_A1 + ab * kA1Bytes);
+#pragma unroll
+            for (int slot = 0; slot < 8; ++slot) {
+                uint32_t hi, lo;
+                split_pair(acc[slot].x, acc[slot].y, hi, lo);
+                A1[wofs + slot * 64] = hi;
+                A1[4096 + wofs + slot * 64] = lo;
+            }
+#pragma unroll
+            for (int slot = 0; slot < 8; ++slot) acc[slot] = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                float qb[16];
+                tmem_ld16f(tq + c * 16, qb);
+                tmem_wait_ld();
+#pragma unroll
+                for (int slot = 0; slot < 8; ++slot) cmac(acc[slot], make_float2(qb[2 * slot], qb[2 * slot + 1]), xbv[c]);
+            }
+            mbar_arrive_after(&bars[BX_EMPTY + xb], acc[0].x, acc[0].y, acc[7].x, acc[7].y);     // xa / xbv of all three channels went into these
+#pragma unroll
+            for (int slot = 0; slot < 8; ++slot) {
+                uint32_t hi, lo;
+                split_pair(acc[slot].x, acc[slot].y, hi, lo);
+                A1[wofs + slot * 64 + 32] = hi;
+                A1[4096 + wofs + slot * 64 + 32] = lo;
+            }
+            fence_proxy_async();                   // generic stores -> the tensor core's (async proxy) operand reads
+            mbar_arrive(&bars[BA_FULL + ab]);
+        }
+    } else {
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(kRegsAux));
+        if (warp == 16) {
+            // ============================ MMA issuer ==========================================================
+            if (lane == 0) {
+                const uint32_t sb = smem_u32(smem);
+                const uint32_t m1 = sb + V_OFF_CONST, m2 = m1 + 4 * kM1Halves;
+                constexpr uint32_t id64 = idesc_f16(128, 64), id32 = idesc_f16(128, 32);
+                int n1 = 0, n2 = 0;
+                while (n2 < N) {
+                    if (n1 < N) {
+                        const int tw = n1 & 1, ab = n1 & 1, k = n1 >> 1;
+                        if (mbar_test_wait(&bars[BA_FULL + ab], (uint32_t)(k & 1)) && mbar_test_wait(&bars[BD1_FREE + tw], (uint32_t)((k & 1) ^ 1))) {
+                            fence_after_sync();
+                            const uint32_t tD = tmem + tw * 192 + 64;
+                            const uint32_t a1 = sb + V_OFF_A1 + ab * kA1Bytes;
+#pragma unroll
+                            for (int pass = 0; pass < 3; ++pass) {          // hi . hi, lo . hi, hi . lo
+                                const uint32_t ablk = a1 + (pass == 1 ? 16384 : 0), bblk = m1 + (pass == 2 ? 2 * kM1Halves : 0);
+#pragma unroll
+                                for (int sl = 0; sl < 4; ++sl)
+                                    mma_ss_f16(tD, smem_desc(ablk + sl * 4096, 128 * 16, 128), smem_desc(bblk + sl * 2048, 64 * 16, 128), id64,
+                                               (pass | sl) != 0);
+                            }
+                            mma_commit(&bars[BA_EMPTY + ab]);
+                            mma_commit(&bars[BD1_FULL + tw]);
+                            ++n1;
+                        }
+                    }
+                    if (n2 < n1) {
+                        const int tw = n2 & 1, k = n2 >> 1;
+                        if (mbar_test_wait(&bars[BA2_FULL + tw], (uint32_t)(k & 1))) {
+                            fence_after_sync();
+                            const uint64_t bh = smem_desc(m2, 32 * 16, 128), bl = smem_desc(m2 + 2 * kM2Halves, 32 * 16, 128);
+                            constexpr uint64_t step = (uint64_t)(2 * 32 * 16) >> 4;
+#pragma unroll
+                            for (int jj = 0; jj < 2; ++jj) {
+                                const uint32_t tD = tmem + tw * 192 + 128 + jj * 32, tA = tmem + tw * 192 + jj * 32;
+                                mma_ts_f16(tD, tA, bh, id32, 0);             mma_ts_f16(tD, tA + 8, bh + step, id32, 1);
+                                mma_ts_f16(tD, tA + 16, bh, id32, 1);        mma_ts_f16(tD, tA + 24, bh + step, id32, 1);
+                                mma_ts_f16(tD, tA, bl, id32, 1);             mma_ts_f16(tD, tA + 8, bl + step, id32, 1);
+                            }
+                            mma_commit(&bars[BD2_FULL + tw]);
+                            ++n2;
+                        }
+                    }
+                }
+            }
+        } else if (warp == 17) {
+            // ============================ input spectra: TMA bulk copies ======================================
+            if (lane == 0) {
+                for (int n = 0; n < N; ++n) {
+                    const int xb = n % V_NX;
+                    mbar_wait(&bars[BX_EMPTY + xb], (uint32_t)(((n / V_NX) & 1) ^ 1));
+                    mbar_expect_tx_(&bars[BX_FULL + xb], kXsBytes);
+                    bulk_g2s_(smem + V_OFF_XS + xb * kXsBytes, Xf + (size_t)(slice + nslices * n) * 3 * D_F, kXsBytes, &bars[BX_FULL + xb]);
+                }
+            }
+        } else {
+            // ============================ Nyquist column v = 16: thread = (u, 4 channels) =========================
+            const int nt = (warp - 18) * 32 + lane, u = nt & 31, half = nt >> 5;
+            const float2* Q16 = reinterpret_cast<const float2*>(smem + V_OFF_Q16);
+            for (int n = 0; n < N; ++n) {
+                const int xb = n % V_NX, yb = n & 1;
+                mbar_wait(&bars[BX_FULL + xb], (uint32_t)((n / V_NX) & 1));
+                const float2* Xs = reinterpret_cast<const float2*>(smem + V_OFF_XS + xb * kXsBytes);
+                float2 x16[3];
+#pragma unroll
+                for (int c = 0; c < 3; ++c) x16[c] = Xs[c * D_F + u * D_H + 16];
+                float2 acc[4];
+#pragma unroll
+                for (int s4 = 0; s4 < 4; ++s4) {
+                    acc[s4] = make_float2(0.f, 0.f);
+#pragma unroll
+                    for (int c = 0; c < 3; ++c) cmac(acc[s4], Q16[((4 * half + s4) * 3 + c) * 32 + u], x16[c]);
+                }
+                mbar_arrive_after(&bars[BX_EMPTY + xb], acc[0].x, acc[0].y, acc[3].x, acc[3].y);
+                mbar_wait(&bars[BY_EMPTY + yb], (uint32_t)(((n >> 1) & 1) ^ 1));
+                float2* Y16 = reinterpret_cast<float2*>(smem + V_OFF_Y16 + yb * 2048);
+#pragma unroll
+                for (int s4 = 0; s4 < 4; ++s4) Y16[(4 * half + s4) * 32 + u] = acc[s4];
+                mbar_arrive(&bars[BY_FULL + yb]);
+            }
+        }
+    }
+    fence_before_sync();
+    __syncthreads();
+    if (warp == 16) tmem_dealloc(tmem, 512);
+}
+
 size_t dft32_consts_bytes() { return kConstBytes; }
 int launch_dft32_consts(void* out, cudaStream_t st) {
     dft32_consts_kernel<<<(64 * 64 + 32 * 32 + 255) / 256, 256, 0, st>>>(reinterpret_cast<__half*>(out));
@@ -333,6 +669,19 @@ int launch_irfft32_mix3_tc(const float2* Xf, const float2* Qt, const void* const
     if (slices > B) slices = B;
     if (slices < 1) slices = 1;
     irfft32_mix3_tc_kernel<<<4 * slices, D_THREADS, kSmemBytes, st>>>(Xf, Qt, reinterpret_cast<const __half*>(consts), B, bias, gs, y);
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(1);
+    return 0;
+}
+int launch_irfft32_mix3_tc2(const float2* Xf, const float2* Qt, const void* consts, int B, const float* bias, int gs, float* y,
+                            cudaStream_t st) {
+    static std::atomic<bool> done[kMaxDevices];
+    if (first_use_on_device(done))
+        FIODE_CUDA(cudaFuncSetAttribute(irfft32_mix3_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)V_SMEM));
+    int slices = sm_count() / 4;
+    if (slices > B) slices = B;
+    if (slices < 1) slices = 1;
+    irfft32_mix3_tc2_kernel<<<4 * slices, V_THREADS, V_SMEM, st>>>(Xf, Qt, reinterpret_cast<const __half*>(consts), B, bias, gs, y);
     FIODE_CUDA(cudaGetLastError());
     count_launch(1);
     return 0;

@@ -194,6 +194,7 @@ class IVP(nn.Module):
             if hit[0] != wkey:
                 hit = None
         if hit is None:
+            ts = ts.detach().to(device=x.device, dtype=torch.float64).contiguous()      # outside the capture: no H2D copy in the graph
             run()                                             # eager once: lazy initialisations, weight preparation, allocator warm-up
             torch.cuda.synchronize()
             wkey = (pm._bw_cache[0], pm._packed.data_ptr(), self.dyn_fun._dw_cache[0])
@@ -203,8 +204,8 @@ class IVP(nn.Module):
             pool = self.__dict__.setdefault('_graph_pool', torch.cuda.graph_pool_handle())
             with torch.cuda.graph(g, pool=pool):
                 res, out, smax = run()
-            hit = cache[key] = (wkey, g, res, out, smax)
-        _, g, res, out, smax = hit
+            hit = cache[key] = (wkey, g, res, out, smax, ts)
+        _, g, res, out, smax, _ts = hit
         g.replay()
         res._stats = None
         if opts.get('check', True) and int(smax) != 0:
