@@ -298,7 +298,7 @@ def fi_step_bench(device, pk, world, iters=10, warm=8):
 STAGES = [
     ('weight packing (per call)', 'pack_w_kernel x5 + mix_real_weights', 0, 0, None),
     ('rfft2 32x32, 3 ch (+Normalize)', 'rfft2_kernel<32>', 3 * 1024 * 4 + 3 * 544 * 8, 0.12e6, ('rfft2_kernel<32, 0, 0>', 0)),
-    ('mix 3->32 + irfft2 32x32 + bias + GroupSort', 'irfft32_mix3_wide_kernel', 3 * 544 * 8 + 32 * 1024 * 4, 0.42e6 + 1.1e6, ('irfft32_mix3_wide_kernel<2>', 0)),
+    ('mix 3->32 + inverse DFT 32x32 (tcgen05) + bias + GroupSort', 'irfft32_mix3_tc2_kernel', 3 * 544 * 8 + 32 * 1024 * 4, 0.42e6 + 6.7e6, ('irfft32_mix3_tc2_kernel', 0)),
     ('conv 128->32 @16x16 (s2d 1x1) + GroupSort', 'gemm_tc_kernel<s2d,32>', 32 * 1024 * 4 + 32 * 256 * 4, 2 * 128 * 32 * 256, ('gemm_tc_kernel<1, 32, 0>', 0)),
     ('rfft2 16x16, 32 ch', 'rfft2_kernel<16,fm>', 32 * 256 * 4 + 32 * 144 * 8, 0.3e6, ('rfft2_kernel<16, 1, 0>', 0)),
     ('mixing 144 x (64->128 real)', 'gemm_tc_kernel<row,128> batched', (32 + 64) * 144 * 8, 2 * 64 * 128 * 144, ('gemm_tc_kernel<0, 128, 1>', 0)),

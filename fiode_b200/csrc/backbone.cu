@@ -113,17 +113,20 @@ static int pack_weights(const fiode_backbone_weights* w, char* pk, cudaStream_t 
     if ((rc = launch_transpose_q((const float2*)w->Qf0, 544, 32 * 3, (float2*)(pk + P.qt0), st))) return rc;
     return launch_dft32_consts(pk + P.dft0, st);
 }
-// model.0's inverse transform: 0 (default) = CUDA-core FFT kernel, 1 = two DFT GEMMs on tcgen05 (dft_tc.cu; FIODE_CONV0=tc or
-// fiode_backbone_set_conv0_path(1)).  Measured equal in time on 8192 images (0.584 vs 0.592 ms, profiles/r02_dft_tc_*.md): the
-// tensor-core version is bound by the shared-memory pipe and by latency at 12 warps per SM, see DESIGN.md section 7.
+// model.0's inverse transform: 2 (default) = two DFT GEMMs on tcgen05, warp-specialised (dft_tc.cu, irfft32_mix3_tc2_kernel);
+// 1 = the first tcgen05 version (one serial pipeline per warpgroup); 0 = mixing + inverse FFT on the CUDA cores.
+// FIODE_CONV0 = tc2 | tc | fft, or fiode_backbone_set_conv0_path.  Per 8192 images: 0.441 / 0.584 / 0.592 ms.
 static int g_conv0_path = -1;
 static int conv0_path() {
-    if (g_conv0_path < 0) { const char* e = getenv("FIODE_CONV0"); g_conv0_path = (e && e[0] == 't') ? ((e[1] == 'c' && e[2] == '2') ? 2 : 1) : 0; }
+    if (g_conv0_path < 0) {
+        const char* e = getenv("FIODE_CONV0");
+        g_conv0_path = !e ? 2 : (e[0] == 'f' ? 0 : ((e[0] == 't' && e[1] == 'c' && e[2] == '\0') ? 1 : 2));
+    }
     return g_conv0_path;
 }
 
 extern "C" int fiode_backbone_slab_images(void) { return kSlab; }
-extern "C" void fiode_backbone_set_conv0_path(int path) { g_conv0_path = (path == 1 || path == 2) ? path : 0; }
+extern "C" void fiode_backbone_set_conv0_path(int path) { g_conv0_path = (path == 0 || path == 1) ? path : 2; }
 extern "C" size_t fiode_backbone_packed_bytes(void) { return packed_layout().total; }
 extern "C" int fiode_backbone_pack(const fiode_backbone_weights* w, void* packed, size_t packed_bytes, void* stream) {
     if (!w || !packed) { set_error("fiode_backbone_pack: null pointer"); return -1; }

@@ -87,8 +87,9 @@ FIODE_API size_t fiode_backbone_workspace_bytes(int B);
  * sets `packed`, so that a forward pass launches no weight preparation at all.                                   */
 /* images per internal slab of fiode_backbone_fwd (each kernel of the chain is launched once per slab) */
 FIODE_API int fiode_backbone_slab_images(void);
-/* model.0 (libs/ortho_conv/layers.py:72-86 at 3 -> 32 channels): 0 = mixing + inverse FFT on the CUDA cores (default),
- * 1 = mixing + the inverse transform as two DFT GEMMs on tcgen05 (csrc/dft_tc.cu); same results to fp32 round-off */
+/* model.0 (libs/ortho_conv/layers.py:72-86 at 3 -> 32 channels): 2 (default) = mixing + the inverse transform as two DFT
+ * GEMMs on tcgen05, warp-specialised (csrc/dft_tc.cu); 1 = its first, single-role version; 0 = mixing + inverse FFT on the
+ * CUDA cores; same results to fp32 round-off */
 FIODE_API void fiode_backbone_set_conv0_path(int path);
 FIODE_API size_t fiode_backbone_packed_bytes(void);
 FIODE_API int fiode_backbone_pack(const fiode_backbone_weights* w, void* packed, size_t packed_bytes, void* stream);

@@ -526,19 +526,21 @@ def test_backbone_conv0_dft_tensor_core_path(ops, sd):
     from oracle import layers as ol
     ivp = fx.build_b200_model(sd, device='cuda:0')
     bw, keep = ivp.init_coordinates.param_map.backbone_weights()
-    for B in (1, 5, 37, 200, 515):
+    for B in (1, 5, 37, 200, 515, 3000):
         x = dev(fx.synth_images(B, seed=100 + B))
         try:
             lib().fiode_backbone_set_conv0_path(0)
             want = ops.backbone_fwd(bw, x)
-            lib().fiode_backbone_set_conv0_path(1)
-            got = ops.backbone_fwd(bw, x)
+            for path in (1, 2):
+                lib().fiode_backbone_set_conv0_path(path)
+                got = ops.backbone_fwd(bw, x)
+                assert (got - want).abs().max().item() < 5e-6, (B, path)
+                assert torch.equal(ops.backbone_fwd(bw, x), got), 'the kernel is deterministic (no atomics, fixed summation order)'
+                if B == 37:
+                    ref = ol.backbone_forward(x.cpu(), sd, fx.PM)
+                    torch.testing.assert_close(got.cpu(), ref, rtol=1e-4, atol=2e-5)
         finally:
-            lib().fiode_backbone_set_conv0_path(0)
-        assert (got - want).abs().max().item() < 5e-6, B
-        if B == 37:
-            ref = ol.backbone_forward(x.cpu(), sd, fx.PM)
-            torch.testing.assert_close(got.cpu(), ref, rtol=1e-4, atol=2e-5)
+            lib().fiode_backbone_set_conv0_path(2)
 
 
 def test_backbone_u8_pixels_equal_totensor_floats(ops, sd):
