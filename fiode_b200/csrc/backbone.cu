@@ -14,12 +14,13 @@
 
 namespace fiode {
 int launch_rfft2(const float* x, int n_img, int C, int n, const float* mu, const float* sd, float2* Xf, cudaStream_t st,
-                 bool freq_major = false, bool x_u8 = false);
+                 bool freq_major = false, bool x_u8 = false, int xrow = 0);
 int launch_irfft2(const float2* Yf, int B, int C, int n, const float* bias, int gs, float* y, cudaStream_t st,
                   int freq_major = 0);
 int launch_irfft32_mix3(const float2* Xf, const float2* Qf, float2* Qt, int B, int C, const float* bias, int gs, float* y,
                         cudaStream_t st);
 size_t dft32_consts_bytes();
+int dft32_tc2_xrow();
 int launch_dft32_consts(void* out, cudaStream_t st);
 int launch_irfft32_mix3_tc(const float2* Xf, const float2* Qt, const void* consts, int B, const float* bias, int gs, float* y,
                            cudaStream_t st);
@@ -78,7 +79,7 @@ static PackedLayout packed_layout() {
 static SlabLayout slab_layout(int S) {
     SlabLayout L; size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o += al(bytes); return r; };
-    L.xf0 = take((size_t)S * 3 * 544 * 8);
+    L.xf0 = take((size_t)S * 3 * 32 * 20 * 8);          // rows of 17, or padded to 20 for the tcgen05 DFT kernel
     L.yf0 = take((size_t)S * 32 * 544 * 8);
     L.a0 = take((size_t)S * 32 * 1024 * 4);
     L.a2 = take((size_t)S * 32 * 256 * 4);
@@ -167,7 +168,7 @@ static int backbone_fwd(const fiode_backbone_weights* w, const float* x, bool x_
         const float* xs = x_u8 ? reinterpret_cast<const float*>(reinterpret_cast<const unsigned char*>(x) + (size_t)b0 * 3 * 1024)
                                : x + (size_t)b0 * 3 * 1024;
         // model.0: CayleyConv(3, 32, 3) @32x32 + GroupSort (ToTensor of 8-bit pixels and Normalize fused into the FFT load)
-        if ((rc = launch_rfft2(xs, nb * 3, 3, 32, w->mu, w->std, xf0, st, false, x_u8))) return rc;
+        if ((rc = launch_rfft2(xs, nb * 3, 3, 32, w->mu, w->std, xf0, st, false, x_u8, tcp && conv0_path() == 2 ? dft32_tc2_xrow() : 0))) return rc;
         mark(2, st);
         if (tcp) {   // mixing fused into the inverse FFT: the 32-channel spectrum never reaches HBM
             if (conv0_path() == 2) {
@@ -234,7 +235,7 @@ extern "C" __attribute__((visibility("default"))) int fiode_debug_conv0(const fi
     const PackedLayout P = packed_layout();
     char* pk = reinterpret_cast<char*>(const_cast<void*>(w->packed));
     int rc;
-    if ((rc = launch_rfft2(x, B * 3, 3, 32, w->mu, w->std, xf0, st, false, false))) return rc;
+    if ((rc = launch_rfft2(x, B * 3, 3, 32, w->mu, w->std, xf0, st, false, false, path == 2 ? dft32_tc2_xrow() : 0))) return rc;
     if (path == 2) return launch_irfft32_mix3_tc2(xf0, (const float2*)(pk + P.qt0), pk + P.dft0, B, w->b0, 1, a0_out, st);
     if (path == 1) return launch_irfft32_mix3_tc(xf0, (const float2*)(pk + P.qt0), pk + P.dft0, B, w->b0, 1, a0_out, st);
     return launch_irfft32_mix3(xf0, nullptr, (float2*)(pk + P.qt0), B, 32, w->b0, 1, a0_out, st);

@@ -33,7 +33,7 @@ template <int n> struct FftCfg {
 template <int n, bool FM, bool U8 = false>
 __global__ void __launch_bounds__(FftCfg<n>::THREADS) rfft2_kernel(const float* __restrict__ x, int n_img, int C,
                                                     const float* __restrict__ mu, const float* __restrict__ sd,
-                                                    float2* __restrict__ Xf) {
+                                                    float2* __restrict__ Xf, int xrow) {   // xrow: row stride of the [b][c][u][v] output (>= n/2 + 1)
     using Cf = FftCfg<n>;
     constexpr int RSI = n * Cf::RS + 1;           // per-image stride, odd: lanes may run along the image index
     __shared__ float2 R[Cf::CH * RSI];
@@ -93,9 +93,9 @@ __global__ void __launch_bounds__(FftCfg<n>::THREADS) rfft2_kernel(const float* 
 #pragma unroll
             for (int u = 0; u < n; ++u) dst[(size_t)u * Cf::H * n_img] = z[bitrev<n>(u)];
         } else {
-            float2* dst = Xf + (size_t)img * n * Cf::H + v;
+            float2* dst = Xf + (size_t)img * n * xrow + v;
 #pragma unroll
-            for (int u = 0; u < n; ++u) dst[u * Cf::H] = z[bitrev<n>(u)];
+            for (int u = 0; u < n; ++u) dst[u * xrow] = z[bitrev<n>(u)];
         }
     }
 }
@@ -681,12 +681,13 @@ __global__ void group_sort_kernel(const float* __restrict__ x, int B, int C, int
 
 // host-side dispatch helpers used by backbone.cu too
 int launch_rfft2(const float* x, int n_img, int C, int n, const float* mu, const float* sd, float2* Xf, cudaStream_t st,
-                 bool freq_major, bool x_u8 = false) {
+                 bool freq_major, bool x_u8 = false, int xrow = 0) {
+    if (xrow <= 0) xrow = n / 2 + 1;
     if (x_u8 && !(n == 32 && !freq_major)) { set_error("rfft2: 8-bit input only for the 32x32 image layer"); return -1; }
-    if (x_u8) rfft2_kernel<32, false, true><<<(n_img + FftCfg<32>::CH - 1) / FftCfg<32>::CH, FftCfg<32>::THREADS, 0, st>>>(x, n_img, C, mu, sd, Xf);
-    else if (n == 32 && !freq_major) rfft2_kernel<32, false><<<(n_img + FftCfg<32>::CH - 1) / FftCfg<32>::CH, FftCfg<32>::THREADS, 0, st>>>(x, n_img, C, mu, sd, Xf);
-    else if (n == 16 && !freq_major) rfft2_kernel<16, false><<<(n_img + FftCfg<16>::CH - 1) / FftCfg<16>::CH, FftCfg<16>::THREADS, 0, st>>>(x, n_img, C, mu, sd, Xf);
-    else if (n == 16 && C % FftCfg<16>::CH == 0) rfft2_kernel<16, true><<<(n_img + FftCfg<16>::CH - 1) / FftCfg<16>::CH, FftCfg<16>::THREADS, 0, st>>>(x, n_img, C, mu, sd, Xf);
+    if (x_u8) rfft2_kernel<32, false, true><<<(n_img + FftCfg<32>::CH - 1) / FftCfg<32>::CH, FftCfg<32>::THREADS, 0, st>>>(x, n_img, C, mu, sd, Xf, xrow);
+    else if (n == 32 && !freq_major) rfft2_kernel<32, false><<<(n_img + FftCfg<32>::CH - 1) / FftCfg<32>::CH, FftCfg<32>::THREADS, 0, st>>>(x, n_img, C, mu, sd, Xf, xrow);
+    else if (n == 16 && !freq_major) rfft2_kernel<16, false><<<(n_img + FftCfg<16>::CH - 1) / FftCfg<16>::CH, FftCfg<16>::THREADS, 0, st>>>(x, n_img, C, mu, sd, Xf, xrow);
+    else if (n == 16 && C % FftCfg<16>::CH == 0) rfft2_kernel<16, true><<<(n_img + FftCfg<16>::CH - 1) / FftCfg<16>::CH, FftCfg<16>::THREADS, 0, st>>>(x, n_img, C, mu, sd, Xf, xrow);
     else { set_error("rfft2: unsupported n=%d (16 or 32), freq_major=%d", n, (int)freq_major); return -1; }
     count_launch(1);
     return 0;

@@ -333,7 +333,9 @@ irfft32_mix3_tc_kernel(const float2* __restrict__ Xf, const float2* __restrict__
 // =====================================================================================================================
 namespace {
 constexpr int V_THREADS = 640;
-constexpr int V_NX = 3, V_NA = 2;
+constexpr int V_NX = 2, V_NA = 2;
+constexpr int V_XR = 20;                                        // row stride of the input spectrum [c][u][V_XR]: 4 u x 4 v' lanes of a half-warp hit 16 different 8-byte banks
+constexpr uint32_t kXs2Bytes = 3 * 32 * V_XR * 8;               // 15 360
 constexpr int kRegsTail = 88, kRegsMix = 128, kRegsAux = 48;
 static_assert(256 * kRegsTail + 256 * kRegsMix + 128 * kRegsAux <= 96 * V_THREADS, "setmaxnreg.inc would block");
 constexpr uint32_t kA1Bytes = 2 * 128 * 64 * 2;                 // hi + lo blocks of one A1 tile: 32 768
@@ -343,11 +345,13 @@ static_assert(kS2Words * 4 <= kS2Bytes, "S tile");
 constexpr uint32_t V_OFF_CONST = 0;
 constexpr uint32_t V_OFF_A1 = V_OFF_CONST + kConstBytes;                       //  20 480
 constexpr uint32_t V_OFF_XS = V_OFF_A1 + V_NA * kA1Bytes;                      //  86 016
-constexpr uint32_t V_OFF_Y16 = V_OFF_XS + V_NX * kXsBytes;                     // 125 184
+constexpr uint32_t V_OFF_Y16 = V_OFF_XS + V_NX * kXs2Bytes;                     // 125 184
 constexpr uint32_t V_OFF_Q16 = V_OFF_Y16 + 2 * 2048;                           // 129 280
 constexpr uint32_t V_OFF_S = V_OFF_Q16 + 8 * 3 * 32 * 8;                       // 135 424
-constexpr uint32_t V_OFF_BARS = V_OFF_S + 8 * kS2Bytes;                        // 201 984
+constexpr uint32_t V_OFF_O = V_OFF_S + 8 * kS2Bytes;                           // output staging tiles, 4 KB per tail warp
+constexpr uint32_t V_OFF_BARS = V_OFF_O + 8 * 4096;
 constexpr uint32_t V_SMEM = V_OFF_BARS + 32 * 8 + 16;
+static_assert(V_NX <= 3, "barrier map below reserves three X slots");
 enum { BX_FULL = 0, BX_EMPTY = 3, BA_FULL = 6, BA_EMPTY = 8, BY_FULL = 10, BY_EMPTY = 12, BD1_FULL = 14, BD1_FREE = 16,
        BA2_FULL = 18, BD2_FULL = 20, B_COUNT = 22 };
 
@@ -412,12 +416,11 @@ irfft32_mix3_tc2_kernel(const float2* __restrict__ Xf, const float2* __restrict_
         const uint32_t sj = j * (1024 + 16);
         const float bs0 = bias ? __ldg(bias + chan(2 * q)) : 0.f, bs1 = bias ? __ldg(bias + chan(2 * q + 1)) : 0.f;
         uint64_t* d1_full = &bars[BD1_FULL + tw], *d1_free = &bars[BD1_FREE + tw], *a2_full = &bars[BA2_FULL + tw], *d2_full = &bars[BD2_FULL + tw];
-        for (int n = tw, k = 0; n < N; n += 2, ++k) {
-            const uint32_t ph = k & 1;
-            const int img = slice + nslices * n;
+        float* O = reinterpret_cast<float*>(smem + V_OFF_O + warp * 4096);       // output staging: [j 2][a 32][16 floats], 16-byte chunks swizzled
+        // part A of a unit: D1 row (slot 2q + j, v' = i), columns 32 h + 2 a' + (re | im), a = 16 h + a'  ->  S[j][a][k], k = v' | 16 + v'
+        auto part_a = [&](uint32_t ph) {
             mbar_wait(d1_full, ph);
             fence_after_sync();
-            // D1 row (slot 2q + j, v' = i): columns n = 32 h + 2 a' + (re | im), a = 16 h + a'  ->  S[j][a][k], k = v' | 16 + v'
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 float d[32];
@@ -432,7 +435,12 @@ irfft32_mix3_tc2_kernel(const float2* __restrict__ Xf, const float2* __restrict_
                 }
             }
             __syncwarp();
-            // rows (channel j', a = lane) of the row pass: tile A = channel slot 2q, tile B = its GroupSort partner 2q + 1
+        };
+        if (tw < N) part_a(0);
+        for (int n = tw, k = 0; n < N; n += 2, ++k) {
+            const uint32_t ph = k & 1;
+            const int img = slice + nslices * n;
+            // part B: rows (channel j', a = lane) of the row pass: tile A = channel slot 2q, tile B = its GroupSort partner 2q + 1
 #pragma unroll
             for (int jj = 0; jj < 2; ++jj) {
                 const float* row = S + jj * (1024 + 16) + lane * 32;
@@ -450,44 +458,40 @@ irfft32_mix3_tc2_kernel(const float2* __restrict__ Xf, const float2* __restrict_
             tmem_wait_st();
             fence_before_sync();
             mbar_arrive(a2_full);
-            __syncwarp();                         // every lane has read its S rows: the tile is free for the output staging
+            __syncwarp();                         // every lane has read its S rows
+            if (n + 2 < N) part_a((uint32_t)((k + 1) & 1));       // the next unit's column pass goes to S while this unit's row pass runs
             mbar_wait(d2_full, ph);
             fence_after_sync();
-            // epilogue: / 64, + bias, GroupSort of (tile A, tile B) in registers, smem, coalesced stores
-            {
-                float* ra = S + lane * 32;
-                float* rb = S + (1024 + 16) + lane * 32;
-                const int xi = (lane & 7) << 2;
+            // epilogue: / 64, + bias, GroupSort of (tile A, tile B) in registers; 16 columns at a time through O, 64-byte row pieces out
 #pragma unroll
-                for (int cc = 0; cc < 2; ++cc) {
-                    float da[16], db[16];
-                    tmem_ld16f(lane_base + 128 + cc * 16, da);
-                    tmem_ld16f(lane_base + 160 + cc * 16, db);
-                    tmem_wait_ld();
+            for (int cc = 0; cc < 2; ++cc) {
+                float da[16], db[16];
+                tmem_ld16f(lane_base + 128 + cc * 16, da);
+                tmem_ld16f(lane_base + 160 + cc * 16, db);
+                tmem_wait_ld();
+                const int sw = (lane >> 1) & 3;
 #pragma unroll
-                    for (int c = 0; c < 4; ++c) {
-                        float hi4[4], lo4[4];
+                for (int c = 0; c < 4; ++c) {
+                    float hi4[4], lo4[4];
 #pragma unroll
-                        for (int e = 0; e < 4; ++e) {
-                            const float u = fmaf(da[4 * c + e], kWSInv, bs0), w = fmaf(db[4 * c + e], kWSInv, bs1);
-                            hi4[e] = group_sort ? fmaxf(u, w) : u;
-                            lo4[e] = group_sort ? fminf(u, w) : w;
-                        }
-                        const int pc = (((cc * 4 + c) << 2) ^ xi);
-                        *reinterpret_cast<float4*>(ra + pc) = make_float4(hi4[0], hi4[1], hi4[2], hi4[3]);
-                        *reinterpret_cast<float4*>(rb + pc) = make_float4(lo4[0], lo4[1], lo4[2], lo4[3]);
+                    for (int e = 0; e < 4; ++e) {
+                        const float u = fmaf(da[4 * c + e], kWSInv, bs0), w = fmaf(db[4 * c + e], kWSInv, bs1);
+                        hi4[e] = group_sort ? fmaxf(u, w) : u;
+                        lo4[e] = group_sort ? fminf(u, w) : w;
                     }
+                    *reinterpret_cast<float4*>(O + lane * 16 + ((c ^ sw) << 2)) = make_float4(hi4[0], hi4[1], hi4[2], hi4[3]);
+                    *reinterpret_cast<float4*>(O + 512 + lane * 16 + ((c ^ sw) << 2)) = make_float4(lo4[0], lo4[1], lo4[2], lo4[3]);
                 }
+                __syncwarp();
+#pragma unroll
+                for (int s_ = 0; s_ < 8; ++s_) {
+                    const int R = 8 * s_ + (lane >> 2), jj = R >> 5, a = R & 31, c = lane & 3;
+                    const float4 w = *reinterpret_cast<const float4*>(O + jj * 512 + a * 16 + ((c ^ ((a >> 1) & 3)) << 2));
+                    *reinterpret_cast<float4*>(y + (((size_t)img * 32 + chan(2 * q + jj)) * 32 + a) * 32 + 16 * cc + 4 * c) = w;
+                }
+                __syncwarp();
             }
             fence_before_sync();
-            __syncwarp();
-#pragma unroll
-            for (int s = 0; s < 16; ++s) {
-                const int R = 4 * s + (lane >> 3), jj = R >> 5, a = R & 31, c = lane & 7;
-                const float4 w = *reinterpret_cast<const float4*>(S + jj * (1024 + 16) + a * 32 + ((c ^ (a & 7)) << 2));
-                *reinterpret_cast<float4*>(y + (((size_t)img * 32 + chan(2 * q + jj)) * 32 + a) * 32 + 4 * c) = w;
-            }
-            __syncwarp();
         }
     } else if (warp < 16) {
         // ============================ mixers ==================================================================
@@ -514,10 +518,10 @@ irfft32_mix3_tc2_kernel(const float2* __restrict__ Xf, const float2* __restrict_
         for (int n = 0; n < N; ++n) {
             const int xb = n % V_NX, ab = n & 1;
             mbar_wait(&bars[BX_FULL + xb], (uint32_t)((n / V_NX) & 1));
-            const float2* Xs = reinterpret_cast<const float2*>(smem + V_OFF_XS + xb * kXsBytes);
+            const float2* Xs = reinterpret_cast<const float2*>(smem + V_OFF_XS + xb * kXs2Bytes);
             float2 xa[3], xbv[3];
 #pragma unroll
-            for (int c = 0; c < 3; ++c) { xa[c] = Xs[c * D_F + u * D_H + vl]; xbv[c] = Xs[c * D_F + u * D_H + 8 + vl]; }
+            for (int c = 0; c < 3; ++c) { xa[c] = Xs[(c * 32 + u) * V_XR + vl]; xbv[c] = Xs[(c * 32 + u) * V_XR + 8 + vl]; }
             float2 acc[8];
 #pragma unroll
             for (int slot = 0; slot < 8; ++slot) {
@@ -616,8 +620,8 @@ irfft32_mix3_tc2_kernel(const float2* __restrict__ Xf, const float2* __restrict_
                 for (int n = 0; n < N; ++n) {
                     const int xb = n % V_NX;
                     mbar_wait(&bars[BX_EMPTY + xb], (uint32_t)(((n / V_NX) & 1) ^ 1));
-                    mbar_expect_tx_(&bars[BX_FULL + xb], kXsBytes);
-                    bulk_g2s_(smem + V_OFF_XS + xb * kXsBytes, Xf + (size_t)(slice + nslices * n) * 3 * D_F, kXsBytes, &bars[BX_FULL + xb]);
+                    mbar_expect_tx_(&bars[BX_FULL + xb], kXs2Bytes);
+                    bulk_g2s_(smem + V_OFF_XS + xb * kXs2Bytes, Xf + (size_t)(slice + nslices * n) * 3 * 32 * V_XR, kXs2Bytes, &bars[BX_FULL + xb]);
                 }
             }
         } else {
@@ -627,10 +631,10 @@ irfft32_mix3_tc2_kernel(const float2* __restrict__ Xf, const float2* __restrict_
             for (int n = 0; n < N; ++n) {
                 const int xb = n % V_NX, yb = n & 1;
                 mbar_wait(&bars[BX_FULL + xb], (uint32_t)((n / V_NX) & 1));
-                const float2* Xs = reinterpret_cast<const float2*>(smem + V_OFF_XS + xb * kXsBytes);
+                const float2* Xs = reinterpret_cast<const float2*>(smem + V_OFF_XS + xb * kXs2Bytes);
                 float2 x16[3];
 #pragma unroll
-                for (int c = 0; c < 3; ++c) x16[c] = Xs[c * D_F + u * D_H + 16];
+                for (int c = 0; c < 3; ++c) x16[c] = Xs[(c * 32 + u) * V_XR + 16];
                 float2 acc[4];
 #pragma unroll
                 for (int s4 = 0; s4 < 4; ++s4) {
@@ -653,13 +657,14 @@ irfft32_mix3_tc2_kernel(const float2* __restrict__ Xf, const float2* __restrict_
 }
 
 size_t dft32_consts_bytes() { return kConstBytes; }
+int dft32_tc2_xrow() { return V_XR; }
 int launch_dft32_consts(void* out, cudaStream_t st) {
     dft32_consts_kernel<<<(64 * 64 + 32 * 32 + 255) / 256, 256, 0, st>>>(reinterpret_cast<__half*>(out));
     FIODE_CUDA(cudaGetLastError());
     count_launch(1);
     return 0;
 }
-// Xf [b][3][544] (torch rfft2 layout), Qt [32][3][544] (transposed spectrum), consts from launch_dft32_consts, y [b][32][32][32]
+// Xf [b][3][544] (torch rfft2 layout; the warp-specialised kernel takes rows padded to dft32_tc2_xrow() = 20), Qt [32][3][544] (transposed spectrum), consts from launch_dft32_consts, y [b][32][32][32]
 int launch_irfft32_mix3_tc(const float2* Xf, const float2* Qt, const void* consts, int B, const float* bias, int gs, float* y,
                            cudaStream_t st) {
     static std::atomic<bool> done[kMaxDevices];

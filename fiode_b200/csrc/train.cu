@@ -22,7 +22,7 @@ int gemm_tn(const float* A, int lda, const float* Bm, int ldb, int M, int N, lon
             float* ws, size_t ws_bytes, cudaStream_t st);
 size_t gemm_tn_workspace(int M, int N, long long K);
 int launch_rfft2(const float* x, int n_img, int C, int n, const float* mu, const float* sd, float2* Xf, cudaStream_t st,
-                 bool freq_major, bool x_u8 = false);
+                 bool freq_major, bool x_u8 = false, int xrow = 0);
 int launch_irfft2(const float2* Yf, int B, int C, int n, const float* bias, int gs, float* y, cudaStream_t st,
                   int freq_major);
 
