@@ -80,14 +80,21 @@ __global__ void __launch_bounds__(FftCfg<n>::THREADS) rfft2_kernel(const float* 
     }
     __syncthreads();
     // step 2: columns.  task = (ci, v)
-    for (int task = threadIdx.x; task < Cf::CH * Cf::H; task += Cf::THREADS) {
-        const int ci = FM ? task % Cf::CH : task / Cf::H, v = FM ? task / Cf::CH : task - ci * Cf::H;
+    // (rows padded to xrow > H: the pad columns are written too, as zeros, so that whole sectors leave the SM)
+    const int vcols = FM ? Cf::H : xrow;
+    for (int task = threadIdx.x; task < Cf::CH * vcols; task += Cf::THREADS) {
+        const int ci = FM ? task % Cf::CH : task / vcols, v = FM ? task / Cf::CH : task - ci * vcols;
         const int img = img0 + ci;
         if (img >= n_img) continue;
         float2 z[n];
+        if (v < Cf::H) {
 #pragma unroll
-        for (int a = 0; a < n; ++a) z[a] = R[ci * RSI + a * Cf::RS + v];
-        fft_dif<n, false>(z);
+            for (int a = 0; a < n; ++a) z[a] = R[ci * RSI + a * Cf::RS + v];
+            fft_dif<n, false>(z);
+        } else {
+#pragma unroll
+            for (int a = 0; a < n; ++a) z[a] = make_float2(0.f, 0.f);
+        }
         if (FM) {                                  // lanes = consecutive channels of one image: contiguous runs
             float2* dst = Xf + (size_t)v * n_img + img;        // [(u H + v)][b][c], b C + c == img
 #pragma unroll
