@@ -17,9 +17,12 @@ namespace fiode {
 
 constexpr int GT = 64, GK = 32, GS = GK + 4, GTHREADS = 128;
 
+// DIRECT (one split, no GroupSort): the tile goes straight to y with alpha and bias applied -- no partials, no second launch
+template <bool DIRECT>
 __global__ void __launch_bounds__(GTHREADS) gemm_nt_kernel(const float* __restrict__ A, int lda,
                                                            const float* __restrict__ Bm, int ldb, int M, int N, int K,
-                                                           int k_per_split, int vec_ok, float* __restrict__ part /*[splits][M][N]*/) {
+                                                           int k_per_split, int vec_ok, float* __restrict__ part /*[splits][M][N]*/,
+                                                           const float* __restrict__ bias = nullptr, float alpha = 1.f, int ldy = 0) {
     __shared__ __align__(16) float As[2][GT * GS];
     __shared__ __align__(16) float Bs[2][GT * GS];
     const int t = threadIdx.x;
@@ -88,7 +91,10 @@ __global__ void __launch_bounds__(GTHREADS) gemm_nt_kernel(const float* __restri
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int n = n0 + tn + 16 * j;
-            if (n < N) dst[(size_t)m * N + n] = acc[i][j];
+            if (n < N) {
+                if (DIRECT) part[(size_t)m * ldy + n] = alpha * acc[i][j] + (bias ? bias[n] : 0.f);
+                else dst[(size_t)m * N + n] = acc[i][j];
+            }
         }
     }
 }
@@ -143,7 +149,14 @@ int gemm_nt(const float* A, int lda, const float* Bm, int ldb, int M, int N, int
     // 16-byte cp.async needs 16-byte aligned rows on both operands; otherwise scalar loads
     const int vec_ok = ((lda & 3) == 0) && ((ldb & 3) == 0) && ((reinterpret_cast<uintptr_t>(A) & 15) == 0) &&
                        ((reinterpret_cast<uintptr_t>(Bm) & 15) == 0);
-    gemm_nt_kernel<<<grid, GTHREADS, 0, st>>>(A, lda, Bm, ldb, M, N, K, kps, vec_ok, ws);
+    if (splits == 1 && !group_sort) {
+        gemm_nt_kernel<true><<<grid, GTHREADS, 0, st>>>(A, lda, Bm, ldb, M, N, K, kps, vec_ok, y, bias, alpha, ldy);
+        cudaError_t e1 = cudaGetLastError();
+        if (e1 != cudaSuccess) return cuda_fail(e1, "gemm_nt launch");
+        count_launch(1);
+        return 0;
+    }
+    gemm_nt_kernel<false><<<grid, GTHREADS, 0, st>>>(A, lda, Bm, ldb, M, N, K, kps, vec_ok, ws);
     const size_t total = group_sort ? (size_t)M * (N / 2) : (size_t)M * N;
     gemm_epilogue_kernel<<<(unsigned)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096), 256, 0, st>>>(
         ws, splits, M, N, bias, alpha, group_sort, y, ldy);
