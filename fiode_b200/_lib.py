@@ -90,6 +90,7 @@ SIGNATURES = {
     'fiode_rhs_fwd': (I, [C.POINTER(DynWeights), P, P, LL, LL, LL, P, P, P, P, P, SZ, P]),
     'fiode_barrier_project_fwd': (I, [P, P, P, LL, I, F32, P, P, P, P, SZ, P]),
     'fiode_barrier_project_bwd': (I, [P, P, P, P, LL, P, P, P]),
+    'fiode_barrier_project_bwd_upper': (I, [P, P, P, P, LL, P, P, P, P]),
     'fiode_certify_workspace_bytes': (SZ, [I, I]),
     'fiode_set_mlp_path': (None, [I]),
     'fiode_get_mlp_path': (I, []),

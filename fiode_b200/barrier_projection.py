@@ -1,6 +1,6 @@
 """barrier_projection/barrier_projection.py of the reference: autograd.Function factories
 ``FastBarrierProjectionNoUpper(max_iter, tol, verbose) -> apply(lower, nominal)`` (:217-313) and
-``FastBarrierProjection(...) -> apply(lower, upper, nominal)`` (:108-214, forward only)."""
+``FastBarrierProjection(...) -> apply(lower, upper, nominal)`` (:108-214), forward and backward."""
 import torch
 
 from . import ops
@@ -24,6 +24,16 @@ def FastBarrierProjectionNoUpper(max_iter=100, tol=1e-8, verbose=False):
 
 
 def FastBarrierProjection(max_iter=100, tol=1e-8, verbose=False):
-    def apply(lower, upper, nominal):
-        return ops.barrier_project_fwd(lower, nominal, upper, max_iter, tol)[0]
-    return apply
+    class BarrierProjectionFn(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, lower, upper, nominal):
+            v, mu, _ = ops.barrier_project_fwd(lower, nominal, upper, max_iter, tol)
+            ctx.save_for_backward(v, mu, nominal.detach())
+            return v
+
+        @staticmethod
+        def backward(ctx, grad_v):
+            v, mu, nominal = ctx.saved_tensors
+            return ops.barrier_project_bwd_upper(grad_v, v, mu, nominal)
+
+    return BarrierProjectionFn.apply

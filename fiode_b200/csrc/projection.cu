@@ -119,9 +119,54 @@ __global__ void __launch_bounds__(256) project_bwd_kernel(const float* __restric
     }
 }
 
+// backward of the upper-bounded projection, barrier_projection.py:164-214, as written there: lambda = v - nominal + mu,
+// L = {lambda > 0}, U = {lambda < 0}, F = neither;  d_nominal_j = g_j - mean_F g (j in F),  d_lower_j = g_j - mean_{not L} g
+// (j in L),  d_upper_j = g_j - mean_{not U} g (j in U)  -- the two bound Jacobians average over the COMPLEMENT of their own
+// active set (which contains the other bound's active entries), not over F; an empty complement leaves d = g.
+__global__ void __launch_bounds__(256) project_bwd_upper_kernel(const float* __restrict__ g, const float* __restrict__ v,
+                                                                const float* __restrict__ mu, const float* __restrict__ nominal,
+                                                                long long N, float* __restrict__ d_lower, float* __restrict__ d_upper,
+                                                                float* __restrict__ d_nominal) {
+    for (long long r = blockIdx.x * 256ll + threadIdx.x; r < N; r += (long long)gridDim.x * 256) {
+        const float m = mu[r];
+        float gj[NH]; bool lo[NH], up[NH];
+        float s_free = 0.f, s_notl = 0.f, s_notu = 0.f; int n_free = 0, n_notl = 0, n_notu = 0;
+#pragma unroll
+        for (int j = 0; j < NH; ++j) {
+            gj[j] = g[r * NH + j];
+            const float lam = v[r * NH + j] - nominal[r * NH + j] + m;
+            lo[j] = lam > 0.f; up[j] = lam < 0.f;
+            if (!lo[j]) { s_notl += gj[j]; ++n_notl; }
+            if (!up[j]) { s_notu += gj[j]; ++n_notu; }
+            if (!lo[j] && !up[j]) { s_free += gj[j]; ++n_free; }
+        }
+        const float mf = n_free > 0 ? s_free / (float)n_free : 0.f;
+        const float ml = n_notl > 0 ? s_notl / (float)n_notl : 0.f;
+        const float mu_ = n_notu > 0 ? s_notu / (float)n_notu : 0.f;
+#pragma unroll
+        for (int j = 0; j < NH; ++j) {
+            d_lower[r * NH + j] = lo[j] ? gj[j] - ml : 0.f;
+            d_upper[r * NH + j] = up[j] ? gj[j] - mu_ : 0.f;
+            d_nominal[r * NH + j] = (!lo[j] && !up[j]) ? gj[j] - mf : 0.f;
+        }
+    }
+}
+
 }  // namespace fiode
 
 using namespace fiode;
+
+extern "C" int fiode_barrier_project_bwd_upper(const float* grad_v, const float* v, const float* mu, const float* nominal,
+                                               long long N, float* d_lower, float* d_upper, float* d_nominal, void* stream) {
+    if (!grad_v || !v || !mu || !nominal || !d_lower || !d_upper || !d_nominal) { set_error("fiode_barrier_project_bwd_upper: null pointer"); return -1; }
+    if (N <= 0) { set_error("fiode_barrier_project_bwd_upper: N=%lld", N); return -1; }
+    const long long want = (N + 255) / 256;
+    const int grid = (int)(want < 8ll * sm_count() ? want : 8ll * sm_count());
+    project_bwd_upper_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(grad_v, v, mu, nominal, N, d_lower, d_upper, d_nominal);
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(1);
+    return 0;
+}
 
 extern "C" int fiode_barrier_project_fwd(const float* lower, const float* upper, const float* nominal, long long N,
                                          int max_iter, float tol, float* v, float* mu, int* n_iter, void* ws,

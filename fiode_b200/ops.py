@@ -194,6 +194,15 @@ def barrier_project_bwd(grad_v, v, mu, nominal):
     return dl, dn
 
 
+def barrier_project_bwd_upper(grad_v, v, mu, nominal):
+    """(d_lower, d_upper, d_nominal) of FastBarrierProjection (barrier_projection.py:164-214) from its saved forward state."""
+    grad_v, v, mu, nominal = _f32(grad_v), _f32(v), _f32(mu), _f32(nominal)
+    dl, du, dn = torch.empty_like(v), torch.empty_like(v), torch.empty_like(v)
+    check(lib().fiode_barrier_project_bwd_upper(ptr(grad_v), ptr(v), ptr(mu), ptr(nominal), v.shape[0], ptr(dl), ptr(du), ptr(dn),
+                                                stream_ptr()), 'fiode_barrier_project_bwd_upper')
+    return dl, du, dn
+
+
 def certify_grid(dw: DynWeights, gridz, T, s, labels, kappa, batches=10, return_iters=False):
     """Per-image maxima of the Lipschitz grid check (robustness/certify_lipschitz.py:104-143).
     gridz: (Ng,10) uint8 numerators of the canonical label-0 grid; returns (M,2)."""

@@ -204,6 +204,10 @@ FIODE_API int fiode_barrier_project_fwd(const float* lower, const float* upper /
                               float* mu, int* n_iter, void* ws, size_t ws_bytes, void* stream);
 FIODE_API int fiode_barrier_project_bwd(const float* grad_v, const float* v, const float* mu, const float* nominal,
                               long long N, float* d_lower, float* d_nominal, void* stream);
+/* backward of the upper-bounded projection (barrier_projection.py:164-214: FastBarrierProjection.backward) from the saved
+ * forward state (v, mu, nominal) -> d_lower, d_upper, d_nominal, each (N,10) */
+FIODE_API int fiode_barrier_project_bwd_upper(const float* grad_v, const float* v, const float* mu, const float* nominal,
+                                              long long N, float* d_lower, float* d_upper, float* d_nominal, void* stream);
 
 /* ---- Lipschitz grid certification ----------------------------------------------------------------
  * replaces the per-image body of robustness/certify_lipschitz.py:104-143 (h_vdot :37-42, Lf_eta /

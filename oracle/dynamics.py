@@ -96,6 +96,22 @@ def project_no_upper_backward(g, v, mu, lower, nominal):
     return d_low, d_nom
 
 
+def project_with_upper_backward(g, v, mu, nominal):
+    """barrier_projection.py:164-214 in closed form.  lambda = v - nominal + mu; L = {lambda > 0}, U = {lambda < 0},
+    F = neither.  The three Jacobians of the reference average over DIFFERENT sets: d_nominal over F, d_lower over the
+    complement of L, d_upper over the complement of U (`recp_card(not_lower_active)`, `recp_card(not_upper_active)`).
+    Returns (d_lower, d_upper, d_nominal)."""
+    lam = v - nominal + mu
+    up, lo = lam < 0, lam > 0
+    free = ~(up | lo)
+
+    def centred(mask_out, mask_avg):
+        m = mask_avg.sum(dim=-1, keepdim=True).to(g.dtype)
+        mean = torch.where(m > 0, (g * mask_avg).sum(dim=-1, keepdim=True) / m.clamp(min=1), torch.zeros_like(m))
+        return torch.where(mask_out, g - mean, torch.zeros_like(g))
+    return centred(lo, ~lo), centred(up, ~up), centred(free, free)
+
+
 class _ProjFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, lower, nominal):

@@ -131,6 +131,37 @@ def gen_rhs():
     save('rhs.pt', out)
 
 
+def gen_proj_upper():
+    """FastBarrierProjection (lower AND upper bound, barrier_projection.py:108-214) forward + backward of the reference on
+    seeded rows; the bounds are tight enough that all three sets (lower-active, upper-active, free) occur in most rows."""
+    print('[proj_upper]')
+    from barrier_projection.barrier_projection import FastBarrierProjection
+    g = torch.Generator().manual_seed(19)
+    n = 400
+    nominal = torch.randn(n, 10, generator=g) * 3
+    lower = -torch.rand(n, 10, generator=g) * 2
+    upper = lower + torch.rand(n, 10, generator=g) * 1.5 + 0.1
+    # feasibility of sum v = 0 inside the box: shift rows whose box excludes it
+    bad = (lower.sum(1) > -0.05) | (upper.sum(1) < 0.05)
+    lower[bad] -= 1.0
+    upper[bad] += 1.0
+    gout = torch.randn(n, 10, generator=g)
+    lo_r, up_r, no_r = (t.clone().requires_grad_(True) for t in (lower, upper, nominal))
+    captured = {}
+    import torch.autograd.function as _f
+    v = FastBarrierProjection(max_iter=30, tol=1e-4, verbose=False)(lo_r, up_r, no_r)
+    # the saved forward state (v, mu): re-derive mu exactly as the forward does (it is not returned)
+    from oracle import dynamics as od
+    v2, mu, n_iter = od.project_with_upper(lower, upper, nominal, 30, 1e-4)
+    assert torch.equal(v2, v.detach()), 'oracle forward must reproduce the reference bit for bit on this CPU'
+    v.backward(gout)
+    lam = v.detach() - nominal + mu
+    print(f'  rows {n}, iterations {n_iter}, lower-active {int((lam > 0).sum())}, upper-active {int((lam < 0).sum())}, '
+          f'free {int((lam == 0).sum())}')
+    save('proj_upper.pt', dict(nominal=nominal, lower=lower, upper=upper, gout=gout, v=v.detach(), mu=mu, n_iter=n_iter,
+                               d_lower=lo_r.grad.clone(), d_upper=up_r.grad.clone(), d_nominal=no_r.grad.clone()))
+
+
 def _solve_with_stats(mod, x, t_max, tol):
     """The reference's IVP.forward with the restated solver, plus the step log."""
     model = mod.model
@@ -553,7 +584,7 @@ def gen_crown():
 
 GROUPS = dict(weights=gen_weights, layers=gen_layers, rhs=gen_rhs, ivp=gen_ivp, fi=gen_fi, fi_state=gen_fi_state,
               certify40=gen_certify40,
-              certify=gen_certify, segway=gen_segway, crown=gen_crown)
+              certify=gen_certify, segway=gen_segway, crown=gen_crown, proj_upper=gen_proj_upper)
 
 if __name__ == '__main__':
     assert rh.available(), 'reference checkout not found: golden vectors can only be regenerated in the build container'

@@ -176,6 +176,26 @@ def test_projection_forward_backward(ops):
     torch.testing.assert_close(v_up.cpu(), g['v_upper'], rtol=0, atol=5e-5)
 
 
+def test_projection_with_upper_forward_backward(ops):
+    """FastBarrierProjection (lower and upper bound, barrier_projection.py:108-214) through the autograd Function: forward
+    against the reference's v, backward (a) on the reference's own saved forward state -- same bits in, 1e-6 out -- and
+    (b) end to end, where rows whose multiplier sits within round-off of a bound may classify differently."""
+    g = fx.load_golden('proj_upper.pt')
+    from fiode_b200.barrier_projection import FastBarrierProjection
+    dl, du, dn = ops.barrier_project_bwd_upper(dev(g['gout']), dev(g['v']), dev(g['mu'][:, 0]), dev(g['nominal']))
+    torch.testing.assert_close(dl.cpu(), g['d_lower'], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(du.cpu(), g['d_upper'], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(dn.cpu(), g['d_nominal'], rtol=1e-5, atol=1e-6)
+    lo, up, no = (dev(g[k]).requires_grad_(True) for k in ('lower', 'upper', 'nominal'))
+    v = FastBarrierProjection(max_iter=30, tol=1e-4)(lo, up, no)
+    torch.testing.assert_close(v.detach().cpu(), g['v'], rtol=0, atol=5e-5)
+    assert float(v.detach().sum(1).abs().max()) < 1e-4
+    v.backward(dev(g['gout']))
+    bad = ((lo.grad.cpu() - g['d_lower']).abs().amax(1) > 1e-5) | ((up.grad.cpu() - g['d_upper']).abs().amax(1) > 1e-5) | \
+        ((no.grad.cpu() - g['d_nominal']).abs().amax(1) > 1e-5)
+    assert bad.float().mean() <= 0.02, bad.sum()
+
+
 # ---- dopri5 --------------------------------------------------------------------------------------------
 @pytest.mark.parametrize('case', ['c2_b256_tol1e-3', 'c5_b64_tol1e-5', 'c5_b64_tol1e-2', 'stress_a', 'stress_b'])
 def test_ivp_matches_reference(sd, case):

@@ -71,6 +71,19 @@ def test_projection_forward_backward():
     assert torch.equal(v_up, g['v_upper'])
 
 
+def test_projection_with_upper_backward():
+    """FastBarrierProjection (barrier_projection.py:108-214): forward bit-exact, the three closed-form Jacobian products
+    against the reference's dense-Jacobian backward."""
+    g = fx.load_golden('proj_upper.pt')
+    v, mu, n_iter = od.project_with_upper(g['lower'], g['upper'], g['nominal'])
+    assert torch.equal(v, g['v']) and torch.equal(mu, g['mu']) and n_iter == g['n_iter']
+    d_low, d_up, d_nom = od.project_with_upper_backward(g['gout'], v, mu, g['nominal'])
+    torch.testing.assert_close(d_low, g['d_lower'], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(d_up, g['d_upper'], rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(d_nom, g['d_nominal'], rtol=1e-5, atol=1e-6)
+    assert (g['d_lower'] != 0).any() and (g['d_upper'] != 0).any() and (g['d_nominal'] != 0).any()
+
+
 @pytest.mark.parametrize('case', ['c2_b256_tol1e-3', 'c5_b64_tol1e-5', 'c5_b64_tol1e-2', 'stress_a'])
 def test_ivp_matches_reference(sd, case):
     c = fx.load_golden('ivp.pt')[case]
