@@ -107,6 +107,11 @@ SIGNATURES = {
     'fiode_segway_grid_workspace_bytes': (SZ, []),
     'fiode_segway_grid': (I, [C.POINTER(SegwayWeights), P, I, P, I, P, I, F32, F32, LL, LL, LL, P, P, P, P, SZ, P]),
     'fiode_segway_simulate': (I, [C.POINTER(SegwayWeights), P, I, P, I, F64, F64, P, P, P, P]),
+    'fiode_segway_param_count': (I, []),
+    'fiode_segway_hdot_bwd_workspace_bytes': (SZ, [LL]),
+    'fiode_segway_hdot': (I, [P, P, LL, P, P]),
+    'fiode_segway_hdot_bwd': (I, [P, P, LL, P, P, P, P, SZ, P]),
+    'fiode_segway_pgd_step': (I, [P, P, P, LL, F32, F32, F32, F32, P]),
     'fiode_grid_count': (LL, [I, I]),
     'fiode_grid_workspace_bytes': (SZ, [I, I]),
     'fiode_grid_enumerate': (I, [I, I, LL, LL, P, P, SZ, P]),

@@ -126,3 +126,119 @@ def certify_grid_sharded(ctrl_sd, P, sizes, r, level=0.15, device='cuda', levels
         dist.all_reduce(vm, op=dist.ReduceOp.MAX)
         dist.all_reduce(cnt, op=dist.ReduceOp.SUM)
     return eta, val, float(vm.item()), int(cnt.item())
+
+
+# ---- adversarial training of the controller and the Lyapunov matrix (control/train_segway.py:119-158) -------------------
+class NNController(torch.nn.Module):
+    """libs/core/core/controllers/nn_controller.py:6-34: 3 -> 32 -> 32 -> 1, ReLU, weights ~ N(0, 6 / fan_in), zero biases; same
+    state_dict keys (``model.{0,2,4}.{weight,bias}``)."""
+    def __init__(self, dynamics=None, in_channels=3, out_channels=1, hidden_channels=32):
+        super().__init__()
+        assert (in_channels, out_channels, hidden_channels) == (3, 1, 32), 'the fused Segway kernels cover NNController(system, 3, 1, 32)'
+        nn = torch.nn
+        self.model = nn.Sequential(nn.Linear(3, 32), nn.ReLU(), nn.Linear(32, 32), nn.ReLU(), nn.Linear(32, 1))
+        for m in self.model.modules():
+            if isinstance(m, nn.Linear):
+                m.weight.data.normal_(0, math.sqrt(6. / m.in_features))
+                m.bias.data.zero_()
+
+
+class LyaQuadratic(torch.nn.Module):
+    """control/control_utils.py:215-234: V = ||P x||^2 with ``P.weight`` trainable (goal = 0)."""
+    def __init__(self, P, goal=None):
+        super().__init__()
+        self.P = torch.nn.Linear(3, 3, bias=False)
+        self.P.weight.data = P.detach().clone().float()
+
+
+class _SegwayHdot(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, W0, b0, W1, b1, W2, b2, P):
+        w = SegwayWeights(W0=ptr(W0), b0=ptr(b0), W1=ptr(W1), b1=ptr(b1), W2=ptr(W2), b2=ptr(b2), P=ptr(P))
+        x = x.detach().float().contiguous()
+        N = x.shape[0]
+        val = torch.empty(N, dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            check(lib().fiode_segway_hdot(C.byref(w), ptr(x), N, ptr(val), stream_ptr()), 'fiode_segway_hdot')
+        ctx.save_for_backward(x, W0, b0, W1, b1, W2, b2, P)
+        return val[:, None]
+
+    @staticmethod
+    def backward(ctx, gout):
+        x, W0, b0, W1, b1, W2, b2, P = ctx.saved_tensors
+        w = SegwayWeights(W0=ptr(W0), b0=ptr(b0), W1=ptr(W1), b1=ptr(b1), W2=ptr(W2), b2=ptr(b2), P=ptr(P))
+        N = x.shape[0]
+        g = gout.detach().float().reshape(N).contiguous()
+        need_x, need_p = ctx.needs_input_grad[0], any(ctx.needs_input_grad[1:])
+        gx = torch.empty(N, 3, dtype=torch.float32, device=x.device) if need_x else None
+        gp = torch.empty(lib().fiode_segway_param_count(), dtype=torch.float32, device=x.device) if need_p else None
+        nb = lib().fiode_segway_hdot_bwd_workspace_bytes(N)
+        ws = torch.empty(nb, dtype=torch.uint8, device=x.device)
+        with torch.cuda.device(x.device):
+            check(lib().fiode_segway_hdot_bwd(C.byref(w), ptr(x), N, ptr(g), ptr(gx), ptr(gp), ptr(ws), nb, stream_ptr()),
+                  'fiode_segway_hdot_bwd')
+        if gp is None:
+            return (gx,) + (None,) * 7
+        parts = torch.split(gp, [96, 32, 1024, 32, 32, 1, 9])
+        return gx, parts[0].view(32, 3), parts[1], parts[2].view(32, 32), parts[3], parts[4].view(1, 32), parts[5], parts[6].view(3, 3)
+
+
+class SegwaySingleBarrierModel(torch.nn.Module):
+    """control/control_utils.py:97-111 over AutoLirpaModel(Segway(), controller) (:21-28) and LyaQuadratic: forward(x) (N,3) ->
+    (N,1) barrier derivative sum(P^T (P f(x, u(x))) * x), differentiable w.r.t. x, the controller weights and P."""
+    def __init__(self, controller, lya):
+        super().__init__()
+        self.controller, self.barrier = controller, lya
+
+    def _params(self):
+        m = self.controller.model
+        return [t.float().contiguous() for t in (m[0].weight, m[0].bias, m[2].weight, m[2].bias, m[4].weight, m[4].bias,
+                                                 self.barrier.P.weight)]
+
+    def forward(self, x):
+        return _SegwayHdot.apply(x, *self._params())
+
+    forward_adv = forward
+
+    def input_gradient(self, x):
+        """d mean(val) / d x without building a graph (what LinfPGDAttack's loss_fn = mean needs)."""
+        ps = [p.detach() for p in self._params()]
+        w = SegwayWeights(**{k: ptr(v) for k, v in zip(('W0', 'b0', 'W1', 'b1', 'W2', 'b2', 'P'), ps)})
+        x = x.detach().float().contiguous()
+        N = x.shape[0]
+        gx = torch.empty(N, 3, dtype=torch.float32, device=x.device)
+        with torch.cuda.device(x.device):
+            check(lib().fiode_segway_hdot_bwd(C.byref(w), ptr(x), N, None, ptr(gx), None, None, 0, stream_ptr()), 'fiode_segway_hdot_bwd')
+        return gx                     # gradient of sum(val); sign(.) is what the attack uses, the 1/N of the mean drops out
+
+
+def linf_pgd(model, x, eps=0.02, nb_iter=7, eps_iter=None, clip_min=-2 * math.pi, clip_max=2 * math.pi, rand_init=True,
+             delta0=None, generator=None):
+    """advertorch.attacks.LinfPGDAttack(model.forward_adv, loss_fn=mean, eps, nb_iter, eps_iter, rand_init, clip_min, clip_max,
+    targeted=False).perturb(x) as train_segway.py:119-123 configures it (perturb_iterative, ord = inf: maximise the mean barrier
+    derivative).  ``delta0`` replaces the uniform(-eps, eps) start (parity runs)."""
+    eps_iter = 2.5 * eps / nb_iter if eps_iter is None else eps_iter
+    x = x.detach().float().contiguous()
+    if delta0 is None:
+        delta0 = (torch.rand(x.shape, device=x.device, generator=generator) * 2 - 1) * eps if rand_init else torch.zeros_like(x)
+    x_adv = torch.clamp(x + delta0.to(x), clip_min, clip_max).contiguous()
+    for _ in range(nb_iter):
+        g = model.input_gradient(x_adv)
+        with torch.cuda.device(x.device):
+            check(lib().fiode_segway_pgd_step(ptr(x_adv), ptr(x), ptr(g), x.numel(), float(eps), float(eps_iter), float(clip_min),
+                                              float(clip_max), stream_ptr()), 'fiode_segway_pgd_step')
+    return x_adv
+
+
+def train_step(model, eta, optimizer, adv_train=True, eps=0.02, margin=0.01, delta0=None):
+    """One epoch body of train_segway.py:138-152: PGD on the shell points (model in eval / no parameter gradients), then
+    loss = sum(relu(model(eta_adv) + margin)) (or sum(relu(model(eta))) without the attack), backward, optimizer step."""
+    optimizer.zero_grad()
+    if adv_train:
+        eta_adv = linf_pgd(model, eta, eps=eps, delta0=delta0)
+        loss = torch.relu(model(eta_adv) + margin).sum()
+    else:
+        loss = torch.relu(model(eta)).sum()
+    loss.backward()
+    optimizer.step()
+    return loss.detach()

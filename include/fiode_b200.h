@@ -325,6 +325,24 @@ FIODE_API int fiode_segway_grid(const fiode_segway_weights* w, const float* d0, 
 FIODE_API int fiode_segway_simulate(const fiode_segway_weights* w, const float* x0, int B, const float* ts, int N,
                           double rtol, double atol, float* xs, float* us, int* stats4, void* stream);
 
+/* ---- Segway adversarial training (control/train_segway.py:119-158) ----------------------------------------------------
+ * The barrier model at arbitrary points and its gradients: val_r = sum(P^T (P f(x_r, u(x_r))) * x_r)
+ * (control_utils.py:97-111 SegwaySingleBarrierModel.forward / forward_adv).
+ *   fiode_segway_hdot      x (N,3) -> val (N)
+ *   fiode_segway_hdot_bwd  gradients of sum_r gout_r val_r (gout NULL = all ones): grad_x (N,3) and / or grad_params
+ *                          (fiode_segway_param_count() = 1226 floats: W0 96 | b0 32 | W1 1024 | b1 32 | W2 32 | b2 1 | P 9),
+ *                          deterministic two-stage reduction through ws.  P's gradient is the reference graph's: through the inner
+ *                          self.P(f) only, g (P x) f^T -- LyaQuadratic.h_dot refreshes P_t through .data (control_utils.py:230)
+ *   fiode_segway_pgd_step  advertorch perturb_iterative (ord = inf), one iteration, in place on x_adv:
+ *                          delta = clamp(x_adv - x0 + eps_iter sign(grad), -eps, eps); x_adv = clamp(x0 + delta, clip_min, clip_max) */
+FIODE_API int fiode_segway_param_count(void);
+FIODE_API size_t fiode_segway_hdot_bwd_workspace_bytes(long long N);
+FIODE_API int fiode_segway_hdot(const fiode_segway_weights* w, const float* x, long long N, float* val, void* stream);
+FIODE_API int fiode_segway_hdot_bwd(const fiode_segway_weights* w, const float* x, long long N, const float* gout, float* grad_x,
+                                    float* grad_params, void* ws, size_t ws_bytes, void* stream);
+FIODE_API int fiode_segway_pgd_step(float* x_adv, const float* x0, const float* grad, long long n, float eps, float eps_iter,
+                                    float clip_min, float clip_max, void* stream);
+
 /* ---- device-resident adaptive dopri5 -----------------------------------------------------------
  * replaces torchdiffeq==0.2.2 odeint(func, y0, t, rtol, atol, method='dopri5') as called at
  * models.py:236-241 with func = IVP.h_dot -> dyn_fun.ode_forward (classification.py:128-132).

@@ -48,10 +48,12 @@ def lya_V(x, P):
     return (Px * Px).sum(dim=1, keepdim=True)
 
 
-def barrier_hdot(x, ctrl, P):
-    """SegwaySingleBarrierModel.forward: h_dot(f, x) = sum(P^T (P f) * x)."""
+def barrier_hdot(x, ctrl, P, pt_detached=False):
+    """SegwaySingleBarrierModel.forward: h_dot(f, x) = sum(P^T (P f) * x).  ``pt_detached``: the autograd graph of the
+    reference -- LyaQuadratic.h_dot refreshes its transposed copy through ``.data`` (control_utils.py:230), so the gradient
+    w.r.t. P flows through the inner ``self.P(.)`` only (App. B-6: it is applied to f because the call swaps the arguments)."""
     f = closed_loop(x, ctrl)
-    return (F.linear(F.linear(f, P), P.t()) * x).sum(dim=1, keepdim=True)
+    return (F.linear(F.linear(f, P), P.t().detach() if pt_detached else P.t()) * x).sum(dim=1, keepdim=True)
 
 
 def grid_axes(sizes, r):
@@ -109,3 +111,27 @@ def simulate(x0, ctrl, ts, rtol=1e-6, atol=1e-6):
         sol = odeint_dopri5(lambda t, xx: segway_f(xx, u), x, torch.tensor([ts[j], ts[j + 1]]), rtol, atol)
         xs.append(sol[-1])
     return torch.stack(xs, dim=1), torch.stack(us, dim=1)
+
+
+# ---- adversarial training (control/train_segway.py:119-158) ---------------------------------------------------------
+def pgd_linf(x, hdot_fn, eps=0.02, nb_iter=7, eps_iter=None, clip_min=-2 * math.pi, clip_max=2 * math.pi, delta0=None):
+    """advertorch 0.2.x ``perturb_iterative`` (ord = inf, minimize = False) as ``LinfPGDAttack(model.forward_adv,
+    loss_fn=mean, eps, nb_iter, eps_iter, rand_init, clip_min, clip_max, targeted=False).perturb(x)`` runs it
+    (train_segway.py:119-123; advertorch is not in this image: restated from its published source).  ``delta0``: the
+    rand_init draw, uniform(-eps, eps) in advertorch; ``hdot_fn(x) -> (N,1)`` differentiable w.r.t. x."""
+    eps_iter = 2.5 * eps / nb_iter if eps_iter is None else eps_iter
+    delta = torch.zeros_like(x) if delta0 is None else delta0.clone()
+    delta = torch.clamp(x + delta, clip_min, clip_max) - x
+    for _ in range(nb_iter):
+        d = delta.clone().requires_grad_(True)
+        loss = hdot_fn(x + d).mean()
+        g, = torch.autograd.grad(loss, d)
+        delta = delta + eps_iter * g.sign()
+        delta = torch.clamp(delta, -eps, eps)
+        delta = torch.clamp(x + delta, clip_min, clip_max) - x
+    return torch.clamp(x + delta, clip_min, clip_max)
+
+
+def train_loss(x, ctrl, P, margin=0.01):
+    """train_segway.py:147 / :150: sum(relu(model(x) + margin)); differentiable w.r.t. ctrl tensors and P."""
+    return torch.relu(barrier_hdot(x, ctrl, P, pt_detached=True) + margin).sum()

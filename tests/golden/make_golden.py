@@ -548,6 +548,46 @@ def gen_segway():
     save('segway.pt', res)
 
 
+def gen_segway_train():
+    """The adversarial-training pieces of control/train_segway.py:119-158 on the reference's own modules: barrier values at
+    arbitrary points, the input gradient the PGD attack uses, one PGD run (perturb_iterative restated, fixed rand_init draw)
+    and the gradients of sum(relu(model(x_adv) + 0.01)) w.r.t. the controller weights and P."""
+    print('[segway_train]')
+    import control_utils as cu
+    from core.systems.segway_system import Segway
+    from core.controllers.nn_controller import NNController
+    from oracle import segway as oseg
+    torch.set_default_dtype(torch.float32)
+    torch.manual_seed(3)
+    system = Segway()
+    ctrl = NNController(system, 3, 1, 32)
+    with torch.no_grad():
+        ctrl.model[4].weight.mul_(0.2)
+        for m in (ctrl.model[0], ctrl.model[2], ctrl.model[4]):
+            m.bias.normal_(0, 0.1)
+    P = torch.eye(3) + 0.1 * torch.randn(3, 3, generator=torch.Generator().manual_seed(4))
+    lya = cu.LyaQuadratic(P.clone(), torch.zeros(1, 3))
+    model = cu.SegwaySingleBarrierModel(cu.AutoLirpaModel(system, ctrl), lya)
+    g = torch.Generator().manual_seed(5)
+    n = 777
+    x = (torch.rand(n, 3, generator=g) * 2 - 1) * torch.tensor([math.pi / 12, 1.5, 1.5])
+    delta0 = (torch.rand(n, 3, generator=g) * 2 - 1) * 0.02
+    xr = x.clone().requires_grad_(True)
+    val = model(xr)
+    gx, = torch.autograd.grad(val.mean(), xr)
+    x_adv = oseg.pgd_linf(x, lambda z: model.forward_adv(z), eps=0.02, nb_iter=7, delta0=delta0)
+    for p in list(ctrl.parameters()) + list(lya.P.parameters()):
+        p.grad = None
+    loss = torch.relu(model(x_adv) + 0.01).sum()
+    loss.backward()
+    grads = {k: v.grad.clone() for k, v in ctrl.named_parameters()}
+    res = dict(ctrl={k: v.detach().clone() for k, v in ctrl.state_dict().items()}, P=P, x=x, delta0=delta0, val=val.detach(),
+               grad_x_of_mean=gx, x_adv=x_adv, loss=float(loss), grads=grads, grad_P=lya.P.weight.grad.clone(),
+               active=int((model(x_adv) + 0.01 > 0).sum()))
+    print(f'  {n} points, loss {float(loss):.4f}, active {res["active"]}, max |x_adv - x| {float((x_adv - x).abs().max()):.4f}')
+    save('segway_train.pt', res)
+
+
 def gen_crown():
     """Post-CROWN interval step of robustness/certify_crown.py:139-150 with the reference's own functions:
     CrownOrthoClassDynProjectSimplexLips.ibp_sigmoid / ibp_cbf_qp (dynamics/classification.py:175-242) and
@@ -584,7 +624,7 @@ def gen_crown():
 
 GROUPS = dict(weights=gen_weights, layers=gen_layers, rhs=gen_rhs, ivp=gen_ivp, fi=gen_fi, fi_state=gen_fi_state,
               certify40=gen_certify40,
-              certify=gen_certify, segway=gen_segway, crown=gen_crown, proj_upper=gen_proj_upper)
+              certify=gen_certify, segway=gen_segway, crown=gen_crown, proj_upper=gen_proj_upper, segway_train=gen_segway_train)
 
 if __name__ == '__main__':
     assert rh.available(), 'reference checkout not found: golden vectors can only be regenerated in the build container'

@@ -69,3 +69,41 @@ def test_segway_simulate_matches_reference():
     torch.testing.assert_close(xs.cpu(), g['xs'], rtol=1e-4, atol=1e-5)
     st = segway.simulate.last_stats
     assert st['nfe'] == 2 * (len(g['ts']) - 1) + 6 * (st['n_accept'] + st['n_reject'])
+
+
+def test_segway_adversarial_training_step_matches_reference():
+    """control/train_segway.py:119-158 on the device: barrier values at arbitrary points, the PGD attack's input gradient, the
+    whole 7-iteration attack from the same rand_init draw, and loss.backward() to the controller weights and P -- against the
+    reference's own modules under autograd (tests/golden/segway_train.pt), then one Adam step through train_step."""
+    from fiode_b200.control import segway
+    g = fx.load_golden('segway_train.pt')
+    dev = torch.device('cuda', 0)
+    ctrl = segway.NNController().to(dev)
+    ctrl.load_state_dict(g['ctrl'])
+    lya = segway.LyaQuadratic(g['P']).to(dev)
+    model = segway.SegwaySingleBarrierModel(ctrl, lya)
+    x = g['x'].to(dev)
+    val = model(x)
+    torch.testing.assert_close(val.detach().cpu(), g['val'], rtol=1e-5, atol=2e-5)
+    gx = model.input_gradient(x) / x.shape[0]
+    torch.testing.assert_close(gx.cpu(), g['grad_x_of_mean'], rtol=2e-4, atol=1e-6)
+    xr = x.clone().requires_grad_(True)
+    gx2, = torch.autograd.grad(model(xr).mean(), xr)               # the autograd.Function route gives the same numbers
+    torch.testing.assert_close(gx2, gx, rtol=1e-6, atol=1e-9)
+    x_adv = segway.linf_pgd(model, x, eps=0.02, nb_iter=7, delta0=g['delta0'].to(dev))
+    # a sign flip of a ~0 gradient component moves one coordinate by eps_iter: allow a handful, none beyond the eps ball
+    diff = (x_adv.cpu() - g['x_adv']).abs()
+    assert (diff > 1e-6).float().mean() < 0.002 and float((x_adv - x).abs().max()) <= 0.02 + 1e-6
+    loss = torch.relu(model(g['x_adv'].to(dev)) + 0.01).sum()
+    assert abs(float(loss.detach()) - g['loss']) < 1e-3 * abs(g['loss'])
+    loss.backward()
+    for k, want in g['grads'].items():
+        got = dict(ctrl.named_parameters())[k].grad.cpu()
+        torch.testing.assert_close(got, want, rtol=5e-4, atol=1e-3 * float(want.abs().max()))
+    torch.testing.assert_close(lya.P.weight.grad.cpu(), g['grad_P'], rtol=5e-4, atol=1e-3 * float(g['grad_P'].abs().max()))
+    # one epoch body: attack + loss + backward + Adam
+    opt = torch.optim.Adam([{'params': list(ctrl.parameters())}, {'params': list(lya.P.parameters()), 'lr': 0.02}], lr=0.01)
+    before = [p.detach().clone() for p in list(ctrl.parameters()) + list(lya.P.parameters())]
+    l0 = float(segway.train_step(model, x, opt, adv_train=True, delta0=g['delta0'].to(dev)))
+    assert abs(l0 - g['loss']) < 2e-3 * abs(g['loss'])
+    assert all(not torch.equal(a, b.detach()) for a, b in zip(before, list(ctrl.parameters()) + list(lya.P.parameters())))

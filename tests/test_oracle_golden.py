@@ -249,3 +249,25 @@ def test_oracle_certify_grid_40_chunks_match_reference():
     v1, v2 = oc.certify_image(oc.grid_for_label(z[:ebs], 40, label), c['s'][m:m + 1], label, sd2, cfg, eps=c['eps'], T=40,
                               batches=1, prefix=DYN, Q=Q)
     assert abs(v1 - float(c['per_chunk'][m, 0, 0])) < 1e-5 and abs(v2 - float(c['per_chunk'][m, 0, 1])) < 1e-5
+
+
+def test_segway_training_pieces_match_reference():
+    """oracle/segway.py (barrier derivative, restated PGD, training loss) against the reference's own Segway / NNController /
+    LyaQuadratic / SegwaySingleBarrierModel under autograd (tests/golden/segway_train.pt)."""
+    from oracle import segway as oseg
+    g = fx.load_golden('segway_train.pt')
+    ctrl = {k: v.clone().requires_grad_(True) for k, v in g['ctrl'].items()}
+    P = g['P'].clone().requires_grad_(True)
+    x = g['x'].clone().requires_grad_(True)
+    val = oseg.barrier_hdot(x, ctrl, P)
+    torch.testing.assert_close(val.detach(), g['val'], rtol=1e-5, atol=1e-5)
+    gx, = torch.autograd.grad(val.mean(), x)
+    torch.testing.assert_close(gx, g['grad_x_of_mean'], rtol=1e-4, atol=1e-7)
+    x_adv = oseg.pgd_linf(g['x'], lambda z: oseg.barrier_hdot(z, ctrl, P), eps=0.02, nb_iter=7, delta0=g['delta0'])
+    assert (x_adv - g['x_adv']).abs().max() < 1e-6
+    loss = oseg.train_loss(g['x_adv'], ctrl, P, margin=0.01)
+    assert abs(float(loss.detach()) - g['loss']) < 1e-3 * abs(g['loss'])
+    loss.backward()
+    for k, want in g['grads'].items():
+        torch.testing.assert_close(ctrl[k].grad, want, rtol=2e-4, atol=1e-3 * float(want.abs().max()))
+    torch.testing.assert_close(P.grad, g['grad_P'], rtol=2e-4, atol=1e-3 * float(g['grad_P'].abs().max()))
