@@ -226,17 +226,31 @@ __global__ void __launch_bounds__(256) gj_block_panel_kernel(const float* __rest
     for (int a = 0; a < GB / 8; ++a) { D0[(w + 8 * a) * GB + l] = v0[a]; D0[(w + 8 * a) * GB + l + 32] = v1[a]; }
     __syncthreads();
     const float* Dinv = D0;
-    for (int e = t; e < GB * GB; e += 256) {
-        const int i = e / GB, j = e - i * GB;
-        float acc;
-        if (jb == kb) acc = Dinv[e];
-        else {
-            acc = 0.f;
-#pragma unroll 8
-            for (int r = 0; r < GB; ++r) acc = fmaf(Dinv[i * GB + r], P[r * GB + j], acc);
-        }
-        Y[(size_t)(kb * GB + i) * n + jb * GB + j] = acc;
+    if (jb == kb) {
+        for (int e = t; e < GB * GB; e += 256) Y[(size_t)(kb * GB + e / GB) * n + jb * GB + e % GB] = Dinv[e];
+        return;
     }
+    // Y_kj = D^-1 X_kj: thread tile 4 x 4 (rows ty + 16 a, columns tx + 16 b) like the update kernel -- 8 loads per 16 FMAs
+    const int tx = t & 15, ty = t >> 4;
+    float acc[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+#pragma unroll 4
+    for (int r = 0; r < GB; ++r) {
+        float dl[4], pq[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) { dl[a] = Dinv[(ty + 16 * a) * GB + r]; pq[a] = P[r * GB + tx + 16 * a]; }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(dl[a], pq[b], acc[a][b]);
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) Y[(size_t)(kb * GB + ty + 16 * a) * n + jb * GB + tx + 16 * b] = acc[a][b];
 }
 __global__ void __launch_bounds__(256) gj_block_update_kernel(const float* __restrict__ X, float* __restrict__ Y, int n, int kb) {
     __shared__ float Ls[GB * (GB + 1)];               // X_ik
