@@ -58,6 +58,7 @@ SIGNATURES = {
     'fiode_backbone_workspace_bytes': (SZ, [I]),
     'fiode_backbone_slab_images': (I, []),
     'fiode_backbone_set_conv0_path': (None, [I]),
+    'fiode_debug_conv0': (I, [C.POINTER(BackboneWeights), P, I, I, P, P, SZ, P]),
     'fiode_backbone_packed_bytes': (SZ, []),
     'fiode_backbone_pack': (I, [C.POINTER(BackboneWeights), P, SZ, P]),
     'fiode_backbone_fwd': (I, [C.POINTER(BackboneWeights), P, I, P, P, SZ, P]),

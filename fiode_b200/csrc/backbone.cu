@@ -225,8 +225,8 @@ static int backbone_fwd(const fiode_backbone_weights* w, const float* x, bool x_
 }
 
 // model.0 alone (debug / tests): x (B,3,32,32) -> a0 (B,32,32,32) through conv0 path 0 | 1 | 2; ws as for fiode_backbone_fwd, B <= slab
-extern "C" __attribute__((visibility("default"))) int fiode_debug_conv0(const fiode_backbone_weights* w, const float* x, int B, int path,
-                                                                        float* a0_out, void* ws, size_t ws_bytes, void* stream) {
+extern "C" int fiode_debug_conv0(const fiode_backbone_weights* w, const float* x, int B, int path, float* a0_out, void* ws,
+                                 size_t ws_bytes, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     const SlabLayout L = slab_layout(B);
     if (!w || !w->packed || ws_bytes < L.total || B > kSlab) { set_error("fiode_debug_conv0: bad arguments"); return -1; }

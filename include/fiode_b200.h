@@ -91,6 +91,10 @@ FIODE_API int fiode_backbone_slab_images(void);
  * GEMMs on tcgen05, warp-specialised (csrc/dft_tc.cu); 1 = its first, single-role version; 0 = mixing + inverse FFT on the
  * CUDA cores; same results to fp32 round-off */
 FIODE_API void fiode_backbone_set_conv0_path(int path);
+/* model.0 alone through one of the three paths (tests / tools/debug_conv0.py): x (B,3,32,32) -> a0 (B,32,32,32) after bias and
+ * GroupSort; w->packed must be set; ws as for fiode_backbone_fwd, B <= fiode_backbone_slab_images() */
+FIODE_API int fiode_debug_conv0(const fiode_backbone_weights* w, const float* x, int B, int path, float* a0_out, void* ws,
+                                size_t ws_bytes, void* stream);
 FIODE_API size_t fiode_backbone_packed_bytes(void);
 FIODE_API int fiode_backbone_pack(const fiode_backbone_weights* w, void* packed, size_t packed_bytes, void* stream);
 /* x: (B,3,32,32) in [0,1]; s_out: (B,10) */

@@ -623,6 +623,30 @@ def test_forward_batches_equals_per_batch_forward(sd):
         assert (a.n_accept, a.n_reject, a.nfe) == (b.n_accept, b.n_reject, b.nfe)
 
 
+def test_forward_batches_graph_option(sd):
+    """options.graph=True: the pass replayed from a CUDA graph gives the bits of the eager pass; new input contents in the same
+    buffer are picked up by a replay, a weight update re-captures, the status check still raises."""
+    ivp = fx.build_b200_model(sd, device='cuda:0')
+    G, B = 2, 64
+    ts = torch.linspace(0., 1., 2)
+    p = dict(method='dopri5', rtol=1e-3, atol=1e-3)
+    pg = dict(p, options=dict(graph=True))
+    x = dev(fx.synth_images(G * B, seed=31)).reshape(G, B, 3, 32, 32)
+    want = ivp.forward_batches(x, ts=ts, int_params=p).clone()
+    got = ivp.forward_batches(x, ts=ts, int_params=pg)
+    assert torch.equal(got, want)
+    assert torch.equal(ivp.forward_batches(x, ts=ts, int_params=pg), want) and len(ivp._graphs) == 1
+    x.copy_(dev(fx.synth_images(G * B, seed=32)).reshape(G, B, 3, 32, 32))          # same buffer, new images
+    want2 = ivp.forward_batches(x, ts=ts, int_params=p).clone()
+    assert torch.equal(ivp.forward_batches(x, ts=ts, int_params=pg), want2) and not torch.equal(want2, want)
+    with torch.no_grad():                                                           # weight update -> new capture
+        ivp.dyn_fun.mlp_to_hidden.bias.add_(0.05)
+    want3 = ivp.forward_batches(x, ts=ts, int_params=p).clone()
+    assert torch.equal(ivp.forward_batches(x, ts=ts, int_params=pg), want3) and not torch.equal(want3, want2)
+    with pytest.raises(AssertionError):                                             # torchdiffeq's message after the replay
+        ivp.forward_batches(x, ts=ts, int_params=dict(p, options=dict(graph=True, max_num_steps=1)))
+
+
 def test_max_concurrent_solves_is_the_wave_size(sd):
     """fiode_dopri5_max_concurrent_solves: one launch keeps that many solve clusters co-resident; results do not depend on
     how many solves share a launch (a second wave only costs time)."""

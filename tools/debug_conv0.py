@@ -9,7 +9,6 @@ B = int(sys.argv[1]) if len(sys.argv) > 1 else 5
 x = torch.rand(B, 3, 32, 32, generator=torch.Generator().manual_seed(7)).to(dev)
 bw, keep = pm.backbone_weights()
 L = lib()
-L.fiode_debug_conv0.restype = C.c_int
 nb = L.fiode_backbone_workspace_bytes(B)
 ws = torch.empty(nb, dtype=torch.uint8, device=dev)
 outs = []
