@@ -97,6 +97,7 @@ SIGNATURES = {
     'fiode_get_mlp_path': (I, []),
     'fiode_certify_grid': (I, [C.POINTER(DynWeights), P, LL, I, P, P, P, I, I, F32, P, P, P, SZ, P]),
     'fiode_sampler_fill': (I, [I, P, P, I, I, I, I, P, P]),
+    'fiode_decision_boundary': (I, [P, P, LL, I, I, P, P]),
     'fiode_fi_loss_workspace_bytes': (SZ, [LL, I]),
     'fiode_fi_loss_fwd': (I, [C.POINTER(DynWeights), P, P, P, I, I, F32, P, P, P, P, P, P, P, P, P, P, P, SZ, P]),
     'fiode_fi_loss_fwd_opt': (I, [C.POINTER(DynWeights), P, P, P, I, I, F32, P, P, C.POINTER(FiOptions), P, P, P, P, P, P, P, P, P, SZ, P]),

@@ -576,6 +576,7 @@ irfft32_mix3_tc2_kernel(const float2* __restrict__ Xf, const float2* __restrict_
                 constexpr uint32_t id64 = idesc_f16(128, 64), id32 = idesc_f16(128, 32);
                 int n1 = 0, n2 = 0;
                 while (n2 < N) {
+                    bool progressed = false;
                     if (n1 < N) {
                         const int tw = n1 & 1, ab = n1 & 1, k = n1 >> 1;
                         if (mbar_test_wait(&bars[BA_FULL + ab], (uint32_t)(k & 1)) && mbar_test_wait(&bars[BD1_FREE + tw], (uint32_t)((k & 1) ^ 1))) {
@@ -593,6 +594,7 @@ irfft32_mix3_tc2_kernel(const float2* __restrict__ Xf, const float2* __restrict_
                             mma_commit(&bars[BA_EMPTY + ab]);
                             mma_commit(&bars[BD1_FULL + tw]);
                             ++n1;
+                            progressed = true;
                         }
                     }
                     if (n2 < n1) {
@@ -610,8 +612,10 @@ irfft32_mix3_tc2_kernel(const float2* __restrict__ Xf, const float2* __restrict_
                             }
                             mma_commit(&bars[BD2_FULL + tw]);
                             ++n2;
+                            progressed = true;
                         }
                     }
+                    if (!progressed) __nanosleep(40);      // the polling loop shares a scheduler with two mixer and two tail warps
                 }
             }
         } else if (warp == 17) {

@@ -241,7 +241,37 @@ __global__ void small_transpose_kernel(const float* __restrict__ x, int rows, in
 static size_t al(size_t x) { return (x + 255) & ~(size_t)255; }
 constexpr int kFiBlocks = 592;
 
+// lya_cands.py:72-94 DecisionBoundary.forward stand-alone: V = 1 + max_{j != y} p_j - p_y (log_mode: log of it), p = the state
+// itself (on_simplex) or its softmax
+__global__ void __launch_bounds__(256) decision_boundary_kernel(const float* __restrict__ h, const int* __restrict__ y, long long N,
+                                                                int on_simplex, int log_mode, float* __restrict__ V) {
+    for (long long r = blockIdx.x * 256ll + threadIdx.x; r < N; r += (long long)gridDim.x * 256) {
+        float p[NH];
+#pragma unroll
+        for (int j = 0; j < NH; ++j) p[j] = h[r * NH + j];
+        if (!on_simplex) {
+            float mx = p[0];
+#pragma unroll
+            for (int j = 1; j < NH; ++j) mx = fmaxf(mx, p[j]);
+            float sum = 0.f;
+#pragma unroll
+            for (int j = 0; j < NH; ++j) { p[j] = expf(p[j] - mx); sum += p[j]; }
+#pragma unroll
+            for (int j = 0; j < NH; ++j) p[j] = p[j] / sum;
+        }
+        const int yy = y[r];
+        float py = 0.f, mw = -INFINITY;
+#pragma unroll
+        for (int j = 0; j < NH; ++j) {
+            if (j == yy) py = p[j];
+            else mw = fmaxf(mw, p[j]);
+        }
+        const float v = 1.f + mw - py;
+        V[r] = log_mode ? logf(v) : v;
+    }
+}
 }  // namespace fiode
+
 
 using namespace fiode;
 
@@ -396,6 +426,17 @@ extern "C" int fiode_dropout_mask(float dropout_p, unsigned long long seed, cons
     fiode::DropCfg d{(unsigned)fminf(dropout_p * 4294967296.f, 4294967040.f), 1.f / (1.f - dropout_p), seed, step};
     const long long want = (N * (NM / 4) + 255) / 256;
     fiode::dropout_mask_kernel<<<(unsigned)(want < 4096 ? want : 4096), 256, 0, (cudaStream_t)stream>>>(d, layer, N, mask);
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(1);
+    return 0;
+}
+
+extern "C" int fiode_decision_boundary(const float* h, const int* y, long long N, int on_simplex, int log_mode, float* V,
+                                       void* stream) {
+    if (!h || !y || !V) { set_error("fiode_decision_boundary: null pointer"); return -1; }
+    if (N <= 0) { set_error("fiode_decision_boundary: N=%lld", N); return -1; }
+    const long long want = (N + 255) / 256;
+    decision_boundary_kernel<<<(int)(want < 4096 ? want : 4096), 256, 0, (cudaStream_t)stream>>>(h, y, N, on_simplex, log_mode, V);
     FIODE_CUDA(cudaGetLastError());
     count_launch(1);
     return 0;

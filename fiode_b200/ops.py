@@ -296,6 +296,16 @@ def sampler_fill(kind, e, y, h, s0):
           'fiode_sampler_fill')
 
 
+def decision_boundary(h, y, on_simplex=True, log_mode=False):
+    """lya_cands.py:72-94: V = 1 + max_{j != y} p_j - p_y per row (its log in log_mode)."""
+    h = _f32(h)
+    yy = y.to(torch.int32).contiguous()
+    V = torch.empty(h.shape[0], dtype=torch.float32, device=h.device)
+    check(lib().fiode_decision_boundary(ptr(h), ptr(yy), h.shape[0], int(bool(on_simplex)), int(bool(log_mode)), ptr(V), stream_ptr()),
+          'fiode_decision_boundary')
+    return V
+
+
 class FiSaved:
     """Device tensors the FI-loss forward keeps for its backward."""
     __slots__ = ('h', 's', 'y', 'B', 'S', 'kappa', 'm1', 'm2', 'f', 'ft', 'mu', 'z1', 'z2', 'V', 'Vdot', 'out4', 'dw', 'opt')

@@ -65,7 +65,6 @@ class LyapunovLearning(nn.Module):
         self.logged = {}
         self.model = IVP(n_input=n_input, n_output=n_output, init_coordinates=init_fun, ts=torch.linspace(0, t_max, 2),
                          ode_tol=train_ode_tol, dyn_fun=dynamics, output_fun=output)
-        object.__setattr__(lya_cand, '_dyn_for_v', dynamics)
 
     def log(self, name, value, **kw):
         self.logged[name] = value
@@ -153,7 +152,8 @@ class LyapunovLearning(nn.Module):
     def compute_loss(self, x, y, batch_size, act='identity', variates=None, masks=None, static_state=None,
                      global_step=None, current_epoch=None):
         assert act == 'relu', "act='relu' (README configuration)"
-        assert not getattr(self.lya_cand, 'log_mode', False), 'the fused FI loss implements log_mode=False (README configuration)'
+        assert not getattr(self.lya_cand, 'log_mode', False) and getattr(self.lya_cand, 'on_simplex', True), \
+            'the fused FI loss implements on_simplex=True, log_mode=False (README configuration)'
         dyn = self.model.dyn_fun
         capturing = x.is_cuda and torch.cuda.is_current_stream_capturing()
         if not capturing:     # under capture the caller has run prepare_step() before replay (kappa lives in a device scalar)

@@ -244,6 +244,10 @@ FIODE_API int fiode_certify_grid(const fiode_dyn_weights* w, const uint8_t* grid
  * (CompositeSampler.forward :195-216: cat on the sample axis, flatten to (B*S,10)).            */
 FIODE_API int fiode_sampler_fill(int kind, const float* e, const int* y, int B, int n, int S, int s0, float* h,
                        void* stream);
+/* lya_cands.py:72-94 DecisionBoundary.forward: h (N,10), y (N) -> V (N) = 1 + max_{j != y} p_j - p_y (log_mode: its log);
+ * p = h (on_simplex) or softmax(h) */
+FIODE_API int fiode_decision_boundary(const float* h, const int* y, long long N, int on_simplex, int log_mode, float* V,
+                                      void* stream);
 
 /* LyapunovLearning.compute_loss, order 1, act 'relu' (pl_modules.py:390-484) with the DecisionBoundary
  * candidate (lya_cands.py:79-94): h (B*S,10) samples, s (B,10) static features (row r uses s[r/S],

@@ -174,6 +174,20 @@ def test_decision_boundary_candidate(sd):
     y_rows = c['y'][:, None].expand(-1, c['S']).flatten(0, 1)
     V = mod.lya_cand(dev(c['h']), dev(y_rows))
     torch.testing.assert_close(V.cpu(), od.decision_boundary_V(c['h'], y_rows), rtol=1e-6, atol=1e-6)
+    # the other three modes of lya_cands.py:72-94 (softmax input, log_mode), written out with torch ops as the reference does
+    from fiode_b200.lya_cands import DecisionBoundary
+    import torch.nn.functional as F
+    x = torch.randn(513, 10, generator=torch.Generator().manual_seed(3)) * 2
+    yy = torch.randint(0, 10, (513,), generator=torch.Generator().manual_seed(4))
+    for on_simplex in (True, False):
+        for log_mode in (False, True):
+            prob = x.abs() / x.abs().sum(1, keepdim=True) if on_simplex else x
+            p = prob if on_simplex else F.softmax(prob, dim=1)
+            py = p.gather(1, yy[:, None])[:, 0]
+            mw = p.masked_fill(F.one_hot(yy, 10).bool(), -float('inf')).max(1).values
+            want = torch.log(1 + mw - py) if log_mode else 1 + mw - py
+            got = DecisionBoundary(on_simplex=on_simplex, log_mode=log_mode)(dev(prob), dev(yy))
+            torch.testing.assert_close(got.cpu(), want, rtol=2e-6, atol=2e-6)
 
 
 # ---- the reference's own saved forward state in -> CUDA backward out --------------------------------------
