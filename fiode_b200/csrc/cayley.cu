@@ -14,6 +14,7 @@
 // n = 512, one CTA for n <= 128).  Complex path: one CTA per frequency, everything in shared
 // memory; the weight spectrum is the direct 9-tap sum of SURVEY App. C-1 (no FFT of the weights).
 #include "common.cuh"
+#include <cstdlib>
 #include "fft.cuh"
 #include <cooperative_groups.h>
 namespace cg = cooperative_groups;
@@ -319,6 +320,245 @@ static int gj_inverse(float* X, float* Y, int n, float** result, cudaStream_t st
     return 0;
 }
 
+// ---- small layers, fused: n = min(cout, cin) <= 64 and R n <= 16384 (R = max): ONE CTA does the whole transform ------------
+// (the dynamics' 128x10 / 10x128 layers, fc 10x512, the stride-2 convs' 32x128 and 64x256 matrices).  The staged version above
+// costs such a layer ~12 launches forward and ~25 backward, each a few microseconds of latency on an otherwise idle GPU: 7 of
+// the FI step's 11 layers are this size.  Same formulas as the staged path (libs/ortho_conv/layers.py:50-60 and its adjoint).
+constexpr int kSmallThreads = 1024;
+__device__ __forceinline__ bool cayley_small_ok(int R, int n) { return n <= 64 && (size_t)R * n <= 16384; }
+static bool cayley_small_host_ok(int cout, int cin) {
+    const int R = cout > cin ? cout : cin, n = cout > cin ? cin : cout;
+    static const bool off = [] { const char* e = getenv("FIODE_CAYLEY_FUSED"); return e && e[0] == '0'; }();
+    return !off && n <= 64 && (size_t)R * n <= 16384;
+}
+struct SmallSm { float* Ws; float* Gs; float* A0; float* A1; float* A2; float* A3; float* Mi; float* prow; double* red; float* sc; };
+__device__ __forceinline__ SmallSm small_carve(float* base, int R, int n, bool with_g) {
+    SmallSm s; float* p = base;
+    const int ld = n + 1;                           // odd-ish leading dimension: column walks (stride ld) hit different banks
+    s.Ws = p; p += (size_t)R * ld;
+    s.Gs = p; if (with_g) p += (size_t)R * ld;
+    s.A0 = p; p += n * ld; s.A1 = p; p += n * ld; s.A2 = p; p += n * ld; s.A3 = p; p += n * ld; s.Mi = p; p += n * ld;
+    s.prow = p; p += 256;
+    s.red = reinterpret_cast<double*>(p + (((size_t)(p - base)) & 1)); p += 2 * 34;
+    s.sc = p;
+    return s;
+}
+static size_t small_smem_bytes(int R, int n, bool with_g) { return ((size_t)R * (n + 1) * (with_g ? 2 : 1) + 5 * (size_t)n * (n + 1) + 256 + 72 + 8) * sizeof(float); }
+
+// ||W||_F (double accumulation), scale -> sc[0] = alpha / (||W|| mult), sc[1] = ||W|| mult
+__device__ __forceinline__ void small_norm(const float* __restrict__ W, size_t total, const float* alpha, float mult, const SmallSm& S) {
+    double acc = 0;
+    for (size_t e = threadIdx.x; e < total; e += kSmallThreads) { const double v = W[e]; acc += v * v; }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) S.red[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0;
+        for (int i = 0; i < kSmallThreads / 32; ++i) t += S.red[i];
+        const float nrm = (float)sqrt(t) * mult;
+        S.sc[1] = nrm;
+        S.sc[0] = alpha ? alpha[0] / nrm : 1.f / nrm;
+    }
+    __syncthreads();
+}
+// Ws, X = I + A (A0), I - A (A1); A = U - U^T + V^T V
+__device__ __forceinline__ void small_build(const float* __restrict__ W, int cout, int cin, int tr, int R, int n, const SmallSm& S) {
+    const int t = threadIdx.x, ld = n + 1;
+    const float sc = S.sc[0];
+    for (int e = t; e < cout * cin; e += kSmallThreads) {   // global order (coalesced); (r, c) = position in the R x n working matrix
+        const int o = e / cin, i2 = e - o * cin;
+        const int r = tr ? i2 : o, c = tr ? o : i2;
+        S.Ws[r * ld + c] = sc * W[e];
+    }
+    __syncthreads();
+    for (int e = t; e < n * n; e += kSmallThreads) {
+        const int i = e / n, j = e - i * n;
+        float g = 0.f;
+        for (int r = n; r < R; ++r) g = fmaf(S.Ws[r * ld + i], S.Ws[r * ld + j], g);
+        const float a = (S.Ws[i * ld + j] - S.Ws[j * ld + i]) + g;
+        const float d = (i == j) ? 1.f : 0.f;
+        S.A0[i * ld + j] = d + a;
+        S.A1[i * ld + j] = d - a;
+    }
+    __syncthreads();
+}
+// out (smem) = X^-1 for n <= 64 ... 128: Gauss-Jordan without pivoting in registers (see gj_inverse_smem_kernel)
+__device__ __forceinline__ void small_inverse(const float* X, float* out, int n, int ld, float* prow2) {
+    const int t = threadIdx.x, w = t >> 5, l = t & 31;
+    float v[4][4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int i = w + 32 * a, j = l + 32 * c;
+            v[a][c] = (i < n && j < n) ? X[i * ld + j] : 0.f;
+        }
+#pragma unroll
+    for (int ka = 0; ka < 4; ++ka) {
+        for (int kk = 0; kk < 32; ++kk) {
+            const int k = 32 * ka + kk;
+            if (k >= n) break;
+            float* pr = prow2 + (k & 1) * 128;
+            if (w == kk) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) pr[l + 32 * c] = v[ka][c];
+            }
+            __syncthreads();
+            const float ip = 1.f / pr[k];
+            float pk[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) pk[c] = pr[l + 32 * c] * ip;
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                const int i = w + 32 * a;
+                const float f = __shfl_sync(0xffffffffu, v[a][ka], kk);
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int j = l + 32 * c;
+                    float r;
+                    if (i == k) r = (j == k) ? ip : pk[c];
+                    else r = (j == k) ? -f * ip : fmaf(-f, pk[c], v[a][c]);
+                    v[a][c] = r;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int i = w + 32 * a, j = l + 32 * c;
+            if (i < n && j < n) out[i * ld + j] = v[a][c];
+        }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(kSmallThreads) cayley_small_fwd_kernel(const float* __restrict__ W, const float* __restrict__ alpha,
+                                                                         int cout, int cin, float mult, float* __restrict__ Q,
+                                                                         float* __restrict__ M_save) {
+    extern __shared__ __align__(16) float sm_small[];
+    const int tr = cin > cout, R = tr ? cin : cout, n = tr ? cout : cin, t = threadIdx.x, ld = n + 1;
+    const SmallSm S = small_carve(sm_small, R, n, false);
+    small_norm(W, (size_t)cout * cin, alpha, mult, S);
+    small_build(W, cout, cin, tr, R, n, S);
+    small_inverse(S.A0, S.Mi, n, ld, S.prow);
+    if (M_save) for (int e = t; e < n * n; e += kSmallThreads) M_save[e] = S.Mi[(e / n) * ld + e % n];
+    // Q_top = M (I - A), Q_bottom = -2 V M; Q = tr ? Qfull^T : Qfull
+    for (int e = t; e < cout * cin; e += kSmallThreads) {   // global order: coalesced stores
+        const int o = e / cin, i2 = e - o * cin;
+        const int r = tr ? i2 : o, j = tr ? o : i2;
+        float acc = 0.f;
+        if (r < n) { for (int k = 0; k < n; ++k) acc = fmaf(S.Mi[r * ld + k], S.A1[k * ld + j], acc); }
+        else { for (int k = 0; k < n; ++k) acc = fmaf(S.Ws[r * ld + k], S.Mi[k * ld + j], acc); acc *= -2.f; }
+        Q[e] = acc;
+    }
+}
+
+__global__ void __launch_bounds__(kSmallThreads) cayley_small_bwd_kernel(const float* __restrict__ W, const float* __restrict__ alpha,
+                                                                         int cout, int cin, float mult, const float* __restrict__ gQ,
+                                                                         const float* __restrict__ M_saved, float* __restrict__ gW,
+                                                                         float* __restrict__ galpha) {
+    extern __shared__ __align__(16) float sm_small[];
+    const int tr = cin > cout, R = tr ? cin : cout, n = tr ? cout : cin, t = threadIdx.x, ld = n + 1;
+    const SmallSm S = small_carve(sm_small, R, n, true);
+    for (int e = t; e < cout * cin; e += kSmallThreads) {   // incoming gradient in the working orientation (R x n), staged once
+        const int o = e / cin, i2 = e - o * cin;
+        S.Gs[(tr ? i2 : o) * ld + (tr ? o : i2)] = gQ[e];
+    }
+    auto gq = [&](int r, int c) { return S.Gs[r * ld + c]; };
+    small_norm(W, (size_t)cout * cin, alpha, mult, S);
+    small_build(W, cout, cin, tr, R, n, S);
+    if (M_saved) { for (int e = t; e < n * n; e += kSmallThreads) S.Mi[(e / n) * ld + e % n] = M_saved[e]; __syncthreads(); }
+    else small_inverse(S.A0, S.Mi, n, ld, S.prow);
+    // gM = 2 G1 - 2 V^T G2   (A0)
+    for (int e = t; e < n * n; e += kSmallThreads) {
+        const int i = e / n, j = e - i * n;
+        float pacc = 0.f;
+        for (int r = n; r < R; ++r) pacc = fmaf(S.Ws[r * ld + i], gq(r, j), pacc);
+        S.A0[i * ld + j] = 2.f * gq(i, j) - 2.f * pacc;
+    }
+    __syncthreads();
+    // T1t = M gM^T   (A1)
+    for (int e = t; e < n * n; e += kSmallThreads) {
+        const int i = e / n, j = e - i * n;
+        float acc = 0.f;
+        for (int k = 0; k < n; ++k) acc = fmaf(S.Mi[i * ld + k], S.A0[j * ld + k], acc);
+        S.A1[i * ld + j] = acc;
+    }
+    __syncthreads();
+    // gA^T = -T1t M   (A2)
+    for (int e = t; e < n * n; e += kSmallThreads) {
+        const int i = e / n, j = e - i * n;
+        float acc = 0.f;
+        for (int k = 0; k < n; ++k) acc = fmaf(S.A1[i * ld + k], S.Mi[k * ld + j], acc);
+        S.A2[i * ld + j] = -acc;
+    }
+    __syncthreads();
+    // S = gA + gA^T (A3), gU = gA - gA^T (A0)
+    for (int e = t; e < n * n; e += kSmallThreads) {
+        const int i = e / n, j = e - i * n;
+        const float a = S.A2[j * ld + i], at = S.A2[i * ld + j];
+        S.A3[i * ld + j] = a + at;
+        S.A0[i * ld + j] = a - at;
+    }
+    __syncthreads();
+    // gWn = un-transposed [gU ; -2 G2 M^T + V S] -> gW (temporarily), dot = <gWn, W>
+    double dacc = 0;
+    for (int e = t; e < cout * cin; e += kSmallThreads) {   // global order
+        const int o_ = e / cin, i2 = e - o_ * cin;
+        const int r = tr ? i2 : o_, c = tr ? o_ : i2;
+        float g;
+        if (r < n) g = S.A0[r * ld + c];
+        else {
+            float a1 = 0.f, a2 = 0.f;
+            for (int k = 0; k < n; ++k) { a1 = fmaf(gq(r, k), S.Mi[c * ld + k], a1); a2 = fmaf(S.Ws[r * ld + k], S.A3[c * ld + k], a2); }
+            g = -2.f * a1 + a2;
+        }
+        gW[e] = g;
+        dacc += (double)g * (double)W[e];
+    }
+    dacc = warp_sum(dacc);
+    __syncthreads();
+    if ((t & 31) == 0) S.red[t >> 5] = dacc;
+    __syncthreads();
+    if (t == 0) {
+        double d = 0;
+        for (int i = 0; i < kSmallThreads / 32; ++i) d += S.red[i];
+        S.red[33] = d;
+    }
+    __syncthreads();
+    const double dot = S.red[33];
+    const float sc = S.sc[0], nrm_m = S.sc[1], nrm = nrm_m / mult;
+    const float c2 = (float)(dot / ((double)nrm * nrm));
+    for (size_t e = t; e < (size_t)cout * cin; e += kSmallThreads) gW[e] = sc * (gW[e] - W[e] * c2);
+    if (t == 0) galpha[0] = (float)(dot / nrm_m);
+}
+
+static int launch_cayley_small_fwd(const float* W, const float* alpha, int cout, int cin, float mult, float* Q, float* M_save,
+                                   cudaStream_t st) {
+    const int R = cout > cin ? cout : cin, n = cout > cin ? cin : cout;
+    const size_t smem = small_smem_bytes(R, n, false);
+    static std::atomic<bool> attr[kMaxDevices];
+    if (first_use_on_device(attr))
+        FIODE_CUDA(cudaFuncSetAttribute(cayley_small_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)small_smem_bytes(256, 64, false)));
+    cayley_small_fwd_kernel<<<1, kSmallThreads, smem, st>>>(W, alpha, cout, cin, mult, Q, M_save);
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(1);
+    return 0;
+}
+static int launch_cayley_small_bwd(const float* W, const float* alpha, int cout, int cin, float mult, const float* gQ,
+                                   const float* M_saved, float* gW, float* galpha, cudaStream_t st) {
+    const int R = cout > cin ? cout : cin, n = cout > cin ? cin : cout;
+    const size_t smem = small_smem_bytes(R, n, true);
+    static std::atomic<bool> attr[kMaxDevices];
+    if (first_use_on_device(attr))
+        FIODE_CUDA(cudaFuncSetAttribute(cayley_small_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)small_smem_bytes(256, 64, true)));
+    cayley_small_bwd_kernel<<<1, kSmallThreads, smem, st>>>(W, alpha, cout, cin, mult, gQ, M_saved, gW, galpha);
+    FIODE_CUDA(cudaGetLastError());
+    count_launch(1);
+    return 0;
+}
+
 static size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 size_t cayley_linear_ws(int cout, int cin) {
@@ -337,6 +577,7 @@ size_t cayley_linear_ws(int cout, int cin) {
 int cayley_linear_impl(const float* W, const float* alpha, int cout, int cin, float norm_mult, float* Q, void* ws,
                        size_t ws_bytes, cudaStream_t st, float* M_save) {
     if (ws_bytes < cayley_linear_ws(cout, cin)) { set_error("cayley_linear: workspace too small"); return -1; }
+    if (cayley_small_host_ok(cout, cin)) return launch_cayley_small_fwd(W, alpha, cout, cin, norm_mult, Q, M_save, st);
     const int tr = cin > cout;
     const int R = tr ? cin : cout, n = tr ? cout : cin;
     char* p = reinterpret_cast<char*>(ws);
@@ -597,6 +838,7 @@ size_t cayley_linear_bwd_ws(int cout, int cin) {
 int cayley_linear_bwd_impl(const float* W, const float* alpha, int cout, int cin, float norm_mult, const float* gQ,
                            float* gW, float* galpha, void* ws, size_t ws_bytes, cudaStream_t st, const float* M_saved) {
     if (ws_bytes < cayley_linear_bwd_ws(cout, cin)) { set_error("cayley_linear_bwd: workspace too small"); return -1; }
+    if (cayley_small_host_ok(cout, cin)) return launch_cayley_small_bwd(W, alpha, cout, cin, norm_mult, gQ, M_saved, gW, galpha, st);
     const int tr = cin > cout;
     const int R = tr ? cin : cout, n = tr ? cout : cin;
     char* p = reinterpret_cast<char*>(ws);
