@@ -100,3 +100,39 @@ def test_lightning_checkpoint_loads(sd, tmp_path):
     missing, unexpected = checkpoint.load_reference_checkpoint(mod, str(f))
     assert unexpected == ['some_callback.buffer']
     assert torch.equal(mod.model.dyn_fun.mlp_to_mlp.weight, sd['model.dyn_fun.mlp_to_mlp.weight'])
+
+
+def test_segway_training_mirrors_have_reference_keys():
+    """NNController / LyaQuadratic mirrors (fiode_b200/control/segway.py) carry the reference's state_dict keys, so the files
+    train_segway.py saves and certify_segway.py loads are interchangeable."""
+    from fiode_b200.control import segway
+    from tests import fixtures as fx
+    g = fx.load_golden('segway_train.pt')
+    ctrl = segway.NNController(None, 3, 1, 32)
+    assert set(ctrl.state_dict().keys()) == set(g['ctrl'].keys())
+    ctrl.load_state_dict(g['ctrl'])
+    lya = segway.LyaQuadratic(g['P'])
+    assert list(lya.state_dict().keys()) == ['P.weight'] and torch.equal(lya.P.weight, g['P'])
+    with pytest.raises(AssertionError):
+        segway.NNController(None, 4, 1, 32)
+
+
+def test_sweep_verdict_logic():
+    """tools/sweep.py: equal / noise / different against an oracle row and its 1e-6-noise band."""
+    import importlib.util
+    import os
+    spec = importlib.util.spec_from_file_location('sweep_tool', os.path.join(os.path.dirname(os.path.dirname(__file__)), 'tools', 'sweep.py'))
+    # the module imports bench + fiode_b200.ops at import time (no GPU needed for that)
+    sw = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(sw)
+    row = dict(oracle=[52, 0, 314], oracle_noise_1e6=[[52, 0, 314], [53, 1, 326]])
+    assert sw.verdict((52, 0, 314), row) == 'equal'
+    assert sw.verdict((53, 1, 326), row) == 'noise'
+    assert sw.verdict((54, 2, 338), row) == 'noise'          # band (1 step) doubled plus one step
+    assert sw.verdict((60, 0, 362), row) == 'different'
+    assert sw.verdict((52, 0, 314), None) == ''
+    rows = [dict(case='README', launch='cooperative', B=64, tol=1e-3, n_accept=3, n_reject=0, nfe=20, oracle=[3, 0, 20], verdict='equal',
+                 rows_per_s=1.0, tflops=0.1, hbm_gbs=0.1),
+            dict(case='README', launch='cooperative', B=64, tol=1e-2, status=1)]
+    s = sw.summary(rows)
+    assert s['equal'] == 1 and s['failed'] == 1 and s['cells'] == 2 and s['worst']['gpu'] == [3, 0, 20]
