@@ -652,16 +652,17 @@ def run_b200(args):
     e2e_u8_nocheck = e2e_measure(x_host_u8, depth=2, ip=int_params_nocheck)
 
     # ---- the literal drop-in seam: module(x) on ONE batch of 256 (models.py:203-242), default options, host buffers ----
-    def single_call():
+    def single_call(graph=False):
         xh = x_host[0][0]
         xd = torch.empty(B, 3, 32, 32, device=device)
         yh = torch.empty(B, 10).pin_memory()
         n = max(50, args.steps)
+        ip = dict(method='dopri5', rtol=TOL, atol=TOL, options=dict(graph=True)) if graph else dict(method='dopri5', rtol=TOL, atol=TOL)
 
         def run(k):
             for _ in range(k):
                 xd.copy_(xh, non_blocking=True)
-                yh.copy_(ivp(xd, ts=ts, int_params=dict(method='dopri5', rtol=TOL, atol=TOL)), non_blocking=True)
+                yh.copy_(ivp(xd, ts=ts, int_params=ip), non_blocking=True)
                 torch.cuda.synchronize()
         run(10)
         barrier()
@@ -681,6 +682,9 @@ def run_b200(args):
                          'cooperative dopri5 launch); forward_batches is the same arithmetic with G solves in flight')
     try:
         e2e_single = single_call()
+        g1 = single_call(graph=True)
+        e2e_single['with_options_graph'] = dict(value=g1['value'], ms_per_call=g1['ms_per_call'],
+                                                note='the same call with options=dict(graph=True): backbone + cooperative solve replayed from a CUDA graph')
     except Exception as e:
         e2e_single = dict(error=repr(e))
 

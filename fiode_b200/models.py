@@ -133,6 +133,14 @@ class IVP(nn.Module):
                                       'solver evaluates the RHS without dropout; call dyn_fun.eval() or set dropout p = 0')
 
     def forward(self, x, ts=None, int_params=None, use_adjoint=False, return_traj=False):
+        opts = (int_params or {}).get('options') or {}
+        if opts.get('graph', False) and not return_traj and not use_adjoint and not self.training and \
+                not (torch.is_grad_enabled() and x.requires_grad):
+            self._no_dropout_in_solve()
+            p = dict(rtol=self.ode_tol, atol=self.ode_tol)
+            p.update(int_params or {})
+            assert p.get('method', 'dopri5') == 'dopri5'
+            return self._forward_batches_graphed(x, self.ts if ts is None else ts, p, opts, single=True)
         solution = self.integrate(x, ts=ts, int_params=int_params, use_adjoint=use_adjoint)
         return self.output_fun(solution) if return_traj else self.output_fun(solution)[-1]
 
@@ -165,20 +173,26 @@ class IVP(nn.Module):
             return res
         return self.output_fun((res.out,))[-1].reshape(G, B, -1)
 
-    def _forward_batches_graphed(self, x, ts, p, opts):
+    def _forward_batches_graphed(self, x, ts, p, opts, single=False):
         """``options=dict(graph=True)``: the pass (backbone launches + the solve + the status reduction) is captured once per
         (input buffer, shapes, tolerances, weight versions) in a CUDA graph and replayed, so a caller that reads the solver
         status after every call (the default ``check``) does not leave the GPU idle while the host re-issues ~15 launches.
-        The returned tensor is the graph's static output: consume it before the next call on the same input buffer."""
+        The returned tensor is the graph's static output: consume it before the next call on the same input buffer.
+        ``single``: x is ONE batch (B, C, H, W) -- ``IVP.forward`` -- solved by the cooperative single-solve launch."""
         from . import ops
-        G, B = x.shape[:2]
+        G, B = (1, x.shape[0]) if single else x.shape[:2]
         pm = self.init_coordinates.param_map
         ts_key = tuple(float(v) for v in ts.detach().cpu().tolist()) if ts.device.type == 'cpu' else (ts.data_ptr(), ts._version)
         cache = self.__dict__.setdefault('_graphs', {})
         key = (x.data_ptr(), tuple(x.shape), x.dtype, ts_key, float(p['rtol']), float(p['atol']), opts.get('cluster_size', 0),
-               opts.get('max_num_steps', 2 ** 31 - 1))
+               opts.get('max_num_steps', 2 ** 31 - 1), single, opts.get('rows_per_cta', 0))
 
         def run():
+            if single:
+                static_state, state = self.init_coordinates(x, self.dyn_fun)
+                res = ops.dopri5_simplex(self.dyn_fun.dyn_weights(), state[0], static_state, ts, p['rtol'], p['atol'],
+                                         max_num_steps=opts.get('max_num_steps', 2 ** 31 - 1), rows_per_cta=opts.get('rows_per_cta', 0))
+                return res, self.output_fun((res.out,))[-1], res._buf.view(torch.int32)[3]
             static_state, state = self.init_coordinates(x.reshape(G * B, *x.shape[2:]), self.dyn_fun)
             res = ops.dopri5_simplex_batched(self.dyn_fun.dyn_weights(), state[0], static_state, G, ts, p['rtol'], p['atol'],
                                              max_num_steps=opts.get('max_num_steps', 2 ** 31 - 1),

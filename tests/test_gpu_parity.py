@@ -645,6 +645,13 @@ def test_forward_batches_graph_option(sd):
     assert torch.equal(ivp.forward_batches(x, ts=ts, int_params=pg), want3) and not torch.equal(want3, want2)
     with pytest.raises(AssertionError):                                             # torchdiffeq's message after the replay
         ivp.forward_batches(x, ts=ts, int_params=dict(p, options=dict(graph=True, max_num_steps=1)))
+    # the single-batch seam: IVP.forward(x) with the cooperative solve launch inside the graph
+    x1 = x[0].clone()
+    want1 = ivp(x1, ts=ts, int_params=p).clone()
+    for _ in range(2):
+        assert torch.equal(ivp(x1, ts=ts, int_params=pg), want1)
+    with pytest.raises(AssertionError):
+        ivp(x1, ts=ts, int_params=dict(p, options=dict(graph=True, max_num_steps=1)))
 
 
 def test_max_concurrent_solves_is_the_wave_size(sd):
