@@ -85,6 +85,9 @@ SIGNATURES = {
     'fiode_cayley_linear_bwd': (I, [P, P, I, I, P, P, P, P, SZ, P]),
     'fiode_cayley_linear_save': (I, [P, P, I, I, P, P, P, SZ, P]),
     'fiode_cayley_linear_bwd_saved': (I, [P, P, I, I, P, P, P, P, P, SZ, P]),
+    'fiode_cayley_small_ok': (I, [I, I]),
+    'fiode_cayley_small_batch_fwd': (I, [I, P, P, P, P, P, P, P, P]),
+    'fiode_cayley_small_batch_bwd': (I, [I, P, P, P, P, P, P, P, P, P, P]),
     'fiode_cayley_conv_bwd_workspace_bytes': (SZ, [I, I, I, I]),
     'fiode_cayley_conv_bwd': (I, [P, P, I, I, I, I, P, P, P, P, SZ, P]),
     'fiode_rhs_workspace_bytes': (SZ, [LL]),

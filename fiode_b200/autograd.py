@@ -48,6 +48,33 @@ class CayleyConvQ(Function):
         return gw, ga.reshape(alpha.shape), None
 
 
+class CayleySmallBatchQ(Function):
+    """Q of several small Cayley layers (``ops.cayley_small_ok``) as ONE node: forward is one launch with a CTA per layer,
+    backward -- which autograd runs once every layer's dL/dQ has arrived, i.e. at the end of the step's backward pass -- is one
+    launch too.  ``mults``: 1 for a CayleyLinear, sqrt(n (n/2+1)) for a k = 1 CayleyConv; tensors = w0, a0, w1, a1, ..."""
+    @staticmethod
+    def forward(ctx, mults, *wa):
+        ws, als = wa[0::2], wa[1::2]
+        Qs, Ms = ops.cayley_small_batch(ws, als, mults)
+        ctx.mults, ctx.k = tuple(mults), len(ws)
+        ctx.save_for_backward(*ws, *als, *Ms)
+        return tuple(Qs)
+
+    @staticmethod
+    def backward(ctx, *gQs):
+        k = ctx.k
+        sv = ctx.saved_tensors
+        ws, als, Ms = sv[:k], sv[k:2 * k], sv[2 * k:]
+        live = [i for i in range(k) if gQs[i] is not None]
+        out = [None] * (2 * k)
+        if live:
+            gWs, gas = ops.cayley_small_batch_bwd([ws[i] for i in live], [als[i] for i in live], [ctx.mults[i] for i in live],
+                                                  [gQs[i] for i in live], [Ms[i] for i in live])
+            for j, i in enumerate(live):
+                out[2 * i], out[2 * i + 1] = gWs[j], gas[j].reshape(als[i].shape)
+        return (None, *out)
+
+
 class Linear(Function):
     """F.linear(X, Q, b), layers.py:105."""
     @staticmethod

@@ -433,10 +433,9 @@ __device__ __forceinline__ void small_inverse(const float* X, float* out, int n,
     __syncthreads();
 }
 
-__global__ void __launch_bounds__(kSmallThreads) cayley_small_fwd_kernel(const float* __restrict__ W, const float* __restrict__ alpha,
-                                                                         int cout, int cin, float mult, float* __restrict__ Q,
-                                                                         float* __restrict__ M_save) {
-    extern __shared__ __align__(16) float sm_small[];
+extern __shared__ __align__(16) float sm_small[];
+__device__ __forceinline__ void cayley_small_fwd_body(const float* __restrict__ W, const float* __restrict__ alpha, int cout, int cin,
+                                                      float mult, float* __restrict__ Q, float* __restrict__ M_save) {
     const int tr = cin > cout, R = tr ? cin : cout, n = tr ? cout : cin, t = threadIdx.x, ld = n + 1;
     const SmallSm S = small_carve(sm_small, R, n, false);
     small_norm(W, (size_t)cout * cin, alpha, mult, S);
@@ -454,11 +453,15 @@ __global__ void __launch_bounds__(kSmallThreads) cayley_small_fwd_kernel(const f
     }
 }
 
-__global__ void __launch_bounds__(kSmallThreads) cayley_small_bwd_kernel(const float* __restrict__ W, const float* __restrict__ alpha,
-                                                                         int cout, int cin, float mult, const float* __restrict__ gQ,
-                                                                         const float* __restrict__ M_saved, float* __restrict__ gW,
-                                                                         float* __restrict__ galpha) {
-    extern __shared__ __align__(16) float sm_small[];
+__global__ void __launch_bounds__(kSmallThreads) cayley_small_fwd_kernel(const float* __restrict__ W, const float* __restrict__ alpha,
+                                                                         int cout, int cin, float mult, float* __restrict__ Q,
+                                                                         float* __restrict__ M_save) {
+    cayley_small_fwd_body(W, alpha, cout, cin, mult, Q, M_save);
+}
+
+__device__ __forceinline__ void cayley_small_bwd_body(const float* __restrict__ W, const float* __restrict__ alpha, int cout, int cin,
+                                                      float mult, const float* __restrict__ gQ, const float* __restrict__ M_saved,
+                                                      float* __restrict__ gW, float* __restrict__ galpha) {
     const int tr = cin > cout, R = tr ? cin : cout, n = tr ? cout : cin, t = threadIdx.x, ld = n + 1;
     const SmallSm S = small_carve(sm_small, R, n, true);
     for (int e = t; e < cout * cin; e += kSmallThreads) {   // incoming gradient in the working orientation (R x n), staged once
@@ -532,6 +535,32 @@ __global__ void __launch_bounds__(kSmallThreads) cayley_small_bwd_kernel(const f
     const float c2 = (float)(dot / ((double)nrm * nrm));
     for (size_t e = t; e < (size_t)cout * cin; e += kSmallThreads) gW[e] = sc * (gW[e] - W[e] * c2);
     if (t == 0) galpha[0] = (float)(dot / nrm_m);
+}
+
+__global__ void __launch_bounds__(kSmallThreads) cayley_small_bwd_kernel(const float* __restrict__ W, const float* __restrict__ alpha,
+                                                                         int cout, int cin, float mult, const float* __restrict__ gQ,
+                                                                         const float* __restrict__ M_saved, float* __restrict__ gW,
+                                                                         float* __restrict__ galpha) {
+    cayley_small_bwd_body(W, alpha, cout, cin, mult, gQ, M_saved, gW, galpha);
+}
+
+// Several small layers in ONE launch, one CTA per layer: the transforms of a step's layers do not depend on each other (forward:
+// weights only; adjoint: each layer's dL/dQ), so a training step prepares all of them up front and differentiates all of them at
+// the end instead of paying each single-CTA kernel's latency in sequence.
+constexpr int kSmallBatchMax = 16;
+struct SmallDesc {
+    const float* W; const float* alpha; float* Q; float* M_save;          // forward
+    const float* gQ; const float* M_saved; float* gW; float* galpha;      // adjoint
+    int cout, cin; float mult;
+};
+struct SmallBatch { SmallDesc d[kSmallBatchMax]; };
+__global__ void __launch_bounds__(kSmallThreads) cayley_small_fwd_batch_kernel(const __grid_constant__ SmallBatch b) {
+    const SmallDesc& d = b.d[blockIdx.x];
+    cayley_small_fwd_body(d.W, d.alpha, d.cout, d.cin, d.mult, d.Q, d.M_save);
+}
+__global__ void __launch_bounds__(kSmallThreads) cayley_small_bwd_batch_kernel(const __grid_constant__ SmallBatch b) {
+    const SmallDesc& d = b.d[blockIdx.x];
+    cayley_small_bwd_body(d.W, d.alpha, d.cout, d.cin, d.mult, d.gQ, d.M_saved, d.gW, d.galpha);
 }
 
 static int launch_cayley_small_fwd(const float* W, const float* alpha, int cout, int cin, float mult, float* Q, float* M_save,
@@ -1177,5 +1206,81 @@ extern "C" int fiode_cayley_conv_bwd(const float* w, const float* alpha, int cou
     cayley_conv_bwd_taps_kernel<<<cout * cin, 128, 0, st>>>(w, alpha, part, dotp, F, cout, cin, k, n, gWn, gw, galpha);
     FIODE_CUDA(cudaGetLastError());
     count_launch(3);
+    return 0;
+}
+
+// ---- batched small layers (one launch for all of a step's small Cayley transforms / adjoints) -----------------------------
+extern "C" int fiode_cayley_small_ok(int cout, int cin) { return cayley_small_host_ok(cout, cin) ? 1 : 0; }
+
+static int small_batch_check(const char* who, int count, const float* const* W, const int* cout, const int* cin) {
+    if (count <= 0 || !W || !cout || !cin) { set_error("%s: bad arguments", who); return -1; }
+    for (int i = 0; i < count; ++i)
+        if (!W[i] || cout[i] <= 0 || cin[i] <= 0 || !cayley_small_host_ok(cout[i], cin[i])) {
+            set_error("%s: layer %d is not a small layer (min(cout, cin) <= 64, max * min <= 16384)", who, i);
+            return -1;
+        }
+    return 0;
+}
+
+extern "C" int fiode_cayley_small_batch_fwd(int count, const float* const* W, const float* const* alpha, const int* cout,
+                                            const int* cin, const float* mult, float* const* Q, float* const* Minv,
+                                            void* stream) {
+    if (small_batch_check("fiode_cayley_small_batch_fwd", count, W, cout, cin)) return -1;
+    if (!Q) { set_error("fiode_cayley_small_batch_fwd: null output list"); return -1; }
+    cudaStream_t st = (cudaStream_t)stream;
+    static std::atomic<bool> attr[kMaxDevices];
+    if (first_use_on_device(attr))
+        FIODE_CUDA(cudaFuncSetAttribute(cayley_small_fwd_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)small_smem_bytes(256, 64, false)));
+    for (int base = 0; base < count; base += kSmallBatchMax) {
+        const int m = count - base < kSmallBatchMax ? count - base : kSmallBatchMax;
+        SmallBatch b{};
+        size_t smem = 0;
+        for (int i = 0; i < m; ++i) {
+            const int j = base + i;
+            if (!Q[j]) { set_error("fiode_cayley_small_batch_fwd: null output"); return -1; }
+            SmallDesc& d = b.d[i];
+            d.W = W[j]; d.alpha = alpha ? alpha[j] : nullptr; d.Q = Q[j]; d.M_save = Minv ? Minv[j] : nullptr;
+            d.cout = cout[j]; d.cin = cin[j]; d.mult = mult ? mult[j] : 1.f;
+            const int R = d.cout > d.cin ? d.cout : d.cin, n = d.cout > d.cin ? d.cin : d.cout;
+            const size_t s = small_smem_bytes(R, n, false);
+            if (s > smem) smem = s;
+        }
+        cayley_small_fwd_batch_kernel<<<m, kSmallThreads, smem, st>>>(b);
+        FIODE_CUDA(cudaGetLastError());
+        count_launch(1);
+    }
+    return 0;
+}
+
+extern "C" int fiode_cayley_small_batch_bwd(int count, const float* const* W, const float* const* alpha, const int* cout,
+                                            const int* cin, const float* mult, const float* const* gQ,
+                                            const float* const* Minv, float* const* gW, float* const* galpha, void* stream) {
+    if (small_batch_check("fiode_cayley_small_batch_bwd", count, W, cout, cin)) return -1;
+    if (!gQ || !gW || !galpha) { set_error("fiode_cayley_small_batch_bwd: null list"); return -1; }
+    cudaStream_t st = (cudaStream_t)stream;
+    static std::atomic<bool> attr[kMaxDevices];
+    if (first_use_on_device(attr))
+        FIODE_CUDA(cudaFuncSetAttribute(cayley_small_bwd_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        (int)small_smem_bytes(256, 64, true)));
+    for (int base = 0; base < count; base += kSmallBatchMax) {
+        const int m = count - base < kSmallBatchMax ? count - base : kSmallBatchMax;
+        SmallBatch b{};
+        size_t smem = 0;
+        for (int i = 0; i < m; ++i) {
+            const int j = base + i;
+            if (!gQ[j] || !gW[j] || !galpha[j]) { set_error("fiode_cayley_small_batch_bwd: null pointer"); return -1; }
+            SmallDesc& d = b.d[i];
+            d.W = W[j]; d.alpha = alpha ? alpha[j] : nullptr; d.gQ = gQ[j]; d.M_saved = Minv ? Minv[j] : nullptr;
+            d.gW = gW[j]; d.galpha = galpha[j];
+            d.cout = cout[j]; d.cin = cin[j]; d.mult = mult ? mult[j] : 1.f;
+            const int R = d.cout > d.cin ? d.cout : d.cin, n = d.cout > d.cin ? d.cin : d.cout;
+            const size_t s = small_smem_bytes(R, n, true);
+            if (s > smem) smem = s;
+        }
+        cayley_small_bwd_batch_kernel<<<m, kSmallThreads, smem, st>>>(b);
+        FIODE_CUDA(cudaGetLastError());
+        count_launch(1);
+    }
     return 0;
 }

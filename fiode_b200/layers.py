@@ -11,6 +11,8 @@ Differences a maintainer should know about:
 """
 from __future__ import annotations
 
+import os
+
 import torch
 from torch import nn
 
@@ -44,6 +46,83 @@ def _version(*ts):
     return tuple((t.data_ptr(), t._version) for t in ts)
 
 
+def _take_prefetch(module, n=None):
+    """The Q that ``prefetch_orthogonal`` prepared for this forward, if it is still the Q of the current parameters."""
+    pf, module._q_prefetch = module._q_prefetch, None
+    if pf is None:
+        return None
+    key, pn, Q = pf
+    if key != _version(module.weight, module.alpha) or pn != n:
+        return None
+    return Q
+
+
+_PREFETCH = os.environ.get('FIODE_PREFETCH', '1') != '0'
+_side_streams = {}
+
+
+def _side_stream(device, i):
+    key = (torch.device(device).index, i)
+    if key not in _side_streams:
+        _side_streams[key] = torch.cuda.Stream(device=device)
+    return _side_streams[key]
+
+
+def prefetch_orthogonal(*roots):
+    """Every Cayley transform of a training step up front.  The reference evaluates ``cayley(alpha W / ||W||)`` inside each
+    layer's forward (libs/ortho_conv/layers.py:74-82, :103-104); the transforms depend on the weights only, so here the small
+    layers' go out as ONE launch (``CayleySmallBatchQ``, one CTA per layer, one more launch for all their adjoints at the end of
+    backward) and each large layer's launch chain (Gauss-Jordan on a 512 x 512 matrix is ~16 dependent launches) runs on its
+    own side stream next to the others; autograd runs each node's backward on the stream of its forward, so the adjoints
+    overlap the activation backward the same way.  Values and gradients are those of the per-layer path, bit for bit.
+    Each layer's forward picks its Q up (``_take_prefetch``); a layer not reached this step drops it at the next prefetch.
+    ``FIODE_PREFETCH=0`` turns this off.  Returns the number of layers prepared."""
+    if not _PREFETCH or not torch.is_grad_enabled():
+        return 0
+    small, big = [], []
+    for root in roots:
+        for m in root.modules():
+            if not isinstance(m, (CayleyLinear, CayleyConv)) or not m.training:
+                continue
+            m._q_prefetch = None
+            if not (m.weight.is_cuda and m.weight.requires_grad):
+                continue
+            if isinstance(m, CayleyConv):
+                if m.alpha is None or m._last_n is None:
+                    continue                     # first step: alpha and the spatial size appear in the layer's own forward
+                n = m._last_n
+                if m.kernel_size[0] == 1 and ops.cayley_small_ok(m.weight.shape[0], m.weight.shape[1]):
+                    small.append((m, n, float(n * (n // 2 + 1)) ** 0.5))
+                else:
+                    big.append((m, n))
+            elif ops.cayley_small_ok(*m.weight.shape):
+                small.append((m, None, 1.0))
+            else:
+                big.append((m, None))
+    if not small and not big:
+        return 0
+    cur = torch.cuda.current_stream()
+    big.sort(key=lambda e: -e[0].weight.numel())
+    streams = []
+    for i, (m, n) in enumerate(big):
+        st = _side_stream(m.weight.device, i)
+        st.wait_stream(cur)
+        with torch.cuda.stream(st):
+            Q = ag.CayleyLinearQ.apply(m.weight, m.alpha) if n is None else ag.CayleyConvQ.apply(m.weight, m.alpha, n)
+        m._q_prefetch = (_version(m.weight, m.alpha), n, Q)
+        streams.append(st)
+    if small:
+        flat = []
+        for m, _, _ in small:
+            flat += [m.weight, m.alpha]
+        Qs = ag.CayleySmallBatchQ.apply(tuple(mu for _, _, mu in small), *flat)
+        for (m, n, _), Q in zip(small, Qs):
+            m._q_prefetch = (_version(m.weight, m.alpha), n, Q)
+    for st in streams:
+        cur.wait_stream(st)
+    return len(small) + len(big)
+
+
 class CayleyLinear(nn.Linear):
     """layers.py:88-105.  ``Q`` holds the cached orthogonal matrix like the reference attribute."""
     def __init__(self, in_features, out_features, bias=True):
@@ -51,6 +130,7 @@ class CayleyLinear(nn.Linear):
         self.alpha = nn.Parameter(torch.ones(1, dtype=torch.float32))
         self.alpha.data = self.weight.norm()
         self._q_key = None
+        self._q_prefetch = None
 
     def reset_parameters(self):
         std = 1 / self.weight.shape[1] ** 0.5
@@ -69,7 +149,9 @@ class CayleyLinear(nn.Linear):
     def orthogonal_weight_autograd(self):
         """Q as a node of the autograd graph (its backward is fiode_cayley_linear_bwd); the detached value also
         refreshes the cache that ``orthogonal_weight`` / ``dyn_weights`` read."""
-        Q = ag.CayleyLinearQ.apply(self.weight, self.alpha)
+        Q = _take_prefetch(self)
+        if Q is None:
+            Q = ag.CayleyLinearQ.apply(self.weight, self.alpha)
         self.Q, self._q_key = Q.detach(), _version(self.weight, self.alpha)
         return Q
 
@@ -93,6 +175,8 @@ class CayleyConv(nn.Conv2d):
         self.register_parameter('alpha', None)
         self.Qf = None
         self._q_key = None
+        self._q_prefetch = None
+        self._last_n = None            # spatial size of the last training forward: what prefetch_orthogonal prepares for
 
     def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
         k = prefix + 'alpha'
@@ -114,7 +198,13 @@ class CayleyConv(nn.Conv2d):
         if _differentiable(self, x):
             if self.alpha is None:
                 self.alpha = nn.Parameter(ops.conv_alpha_init(self.weight, n))
-            Qf = ag.CayleyConvQ.apply(self.weight, self.alpha, n) if self.training else self.orthogonal_spectrum(n)
+            if self.training:
+                Qf = _take_prefetch(self, n)
+                if Qf is None:
+                    Qf = ag.CayleyConvQ.apply(self.weight, self.alpha, n)
+                self._last_n = n
+            else:
+                Qf = self.orthogonal_spectrum(n)
             y = (ag.Conv1x1S2d if self.striding else ag.CayleyConvLayer).apply(x, Qf, self.bias)
             return ag.GroupSortFn.apply(y) if group_sort else y
         Qf = self.orthogonal_spectrum(n)

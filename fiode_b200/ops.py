@@ -526,6 +526,51 @@ def cayley_linear_bwd(weight, alpha, gQ, minv=None):
     return gW, ga
 
 
+def cayley_small_ok(cout, cin):
+    """True when the layer's Cayley transform runs as one CTA (and so can ride in a cayley_small_batch launch)."""
+    return bool(lib().fiode_cayley_small_ok(int(cout), int(cin)))
+
+
+def _ptr_list(ts):
+    arr = (C.c_void_p * len(ts))()
+    for i, t in enumerate(ts):
+        arr[i] = None if t is None else ptr(t).value
+    return arr
+
+
+def _small_batch_args(weights, alphas, mults):
+    Ws = [_f32(w).reshape(w.shape[0], w.shape[1]) for w in weights]          # (cout, cin[, 1, 1]) -> (cout, cin)
+    As = [_f32(a).reshape(1) for a in alphas]
+    k = len(Ws)
+    couts = (C.c_int * k)(*[w.shape[0] for w in Ws])
+    cins = (C.c_int * k)(*[w.shape[1] for w in Ws])
+    mu = (C.c_float * k)(*[float(m) for m in mults])
+    return Ws, As, k, couts, cins, mu
+
+
+def cayley_small_batch(weights, alphas, mults):
+    """Q_i = cayley(alpha_i W_i / (||W_i|| mult_i)) for several small layers in ONE launch (one CTA per layer).  Returns
+    ([Q_i], [Minv_i]); bit-identical with ``cayley_linear`` / ``cayley_conv`` (k = 1, mult = sqrt(F)) of each layer."""
+    Ws, As, k, couts, cins, mu = _small_batch_args(weights, alphas, mults)
+    Qs = [torch.empty_like(w) for w in Ws]
+    Ms = [torch.empty(min(w.shape), min(w.shape), dtype=torch.float32, device=w.device) for w in Ws]
+    check(lib().fiode_cayley_small_batch_fwd(k, _ptr_list(Ws), _ptr_list(As), couts, cins, mu, _ptr_list(Qs), _ptr_list(Ms),
+                                             stream_ptr()), 'fiode_cayley_small_batch_fwd')
+    return Qs, Ms
+
+
+def cayley_small_batch_bwd(weights, alphas, mults, gQs, minvs):
+    """Adjoint of ``cayley_small_batch``: ([gW_i] shaped like W_i, [galpha_i] (1,)), one launch."""
+    Ws, As, k, couts, cins, mu = _small_batch_args(weights, alphas, mults)
+    Gs = [_f32(g).reshape(w.shape) for g, w in zip(gQs, Ws)]
+    Ms = [None if m is None else _f32(m) for m in minvs]
+    gWs = [torch.empty_like(w) for w in Ws]
+    gas = [torch.empty(1, dtype=torch.float32, device=w.device) for w in Ws]
+    check(lib().fiode_cayley_small_batch_bwd(k, _ptr_list(Ws), _ptr_list(As), couts, cins, mu, _ptr_list(Gs), _ptr_list(Ms),
+                                             _ptr_list(gWs), _ptr_list(gas), stream_ptr()), 'fiode_cayley_small_batch_bwd')
+    return [g.reshape(w.shape) for g, w in zip(gWs, weights)], gas
+
+
 def cayley_conv_bwd(weight, alpha, n, gQf):
     """Adjoint of cayley_conv: (gw (cout,cin,k,k), galpha)."""
     w = _f32(weight)

@@ -8,6 +8,7 @@ import torch
 from torch import nn
 
 from . import ops
+from .layers import prefetch_orthogonal
 from .models import IVP
 
 ADAPTIVE_SOLVERS = ['dopri8', 'dopri5', 'bosh3', 'adaptive_heun']
@@ -159,6 +160,10 @@ class LyapunovLearning(nn.Module):
         if not capturing:     # under capture the caller has run prepare_step() before replay (kappa lives in a device scalar)
             self.prepare_step(x.device, global_step, current_epoch)
         kappa_dev, drop_step = self._device_scalars(x.device)
+        if dyn.training and torch.is_grad_enabled() and x.is_cuda:
+            # all of the step's Cayley transforms first: the small layers in one launch, the large ones side by side
+            init = self.model.init_coordinates
+            prefetch_orthogonal(dyn, *([init] if static_state is None and isinstance(init, nn.Module) else []))
         if static_state is None:
             static_state, _ = self.model.init_coordinates(x, dyn)
         S = self.h_sample_size

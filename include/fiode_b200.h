@@ -166,6 +166,18 @@ FIODE_API int fiode_cayley_linear_save(const float* W, const float* alpha, int c
                              void* ws, size_t ws_bytes, void* stream);
 FIODE_API int fiode_cayley_linear_bwd_saved(const float* W, const float* alpha, int cout, int cin, const float* gQ,
                                   const float* Minv, float* gW, float* galpha, void* ws, size_t ws_bytes, void* stream);
+/* Several small layers (fiode_cayley_small_ok: min(cout,cin) <= 64 and max*min <= 16384 -- the dynamics' 128x10 / 10x128
+ * layers, fc 10x512, the stride-2 convs' 1x1 matrices) in ONE launch, one CTA per layer: the Cayley transforms of a training
+ * step's layers are independent (libs/ortho_conv/layers.py:103-104 / :74-82 evaluate them layer by layer).  The lists are HOST
+ * arrays of device pointers; mult[i] = 1 for a CayleyLinear, sqrt(n (n/2+1)) for a k = 1 CayleyConv (layers.py:80-81), NULL =
+ * all 1.  Minv[i] (n x n, n = min(cout,cin)) is written by fwd when non-NULL and read by bwd when non-NULL (else recomputed).
+ * Results are bit-identical with fiode_cayley_linear(_save) / fiode_cayley_linear_bwd(_saved) of the same layer.        */
+FIODE_API int fiode_cayley_small_ok(int cout, int cin);
+FIODE_API int fiode_cayley_small_batch_fwd(int count, const float* const* W, const float* const* alpha, const int* cout,
+                                 const int* cin, const float* mult, float* const* Q, float* const* Minv, void* stream);
+FIODE_API int fiode_cayley_small_batch_bwd(int count, const float* const* W, const float* const* alpha, const int* cout,
+                                 const int* cin, const float* mult, const float* const* gQ, const float* const* Minv,
+                                 float* const* gW, float* const* galpha, void* stream);
 /* adjoint of fiode_cayley_conv (layers.py:74-82): gQf as produced by the layer adjoints above
  * (k = 3: (F,cout,cin) complex64; k = 1: real (cout,cin)) -> gw (cout,cin,k,k), galpha (1).              */
 FIODE_API size_t fiode_cayley_conv_bwd_workspace_bytes(int cout, int cin, int k, int n);

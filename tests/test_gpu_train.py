@@ -374,3 +374,72 @@ def test_differentiable_solve_beyond_64_attempts(sd):
         if a.numel() > 1:
             cos = float(torch.nn.functional.cosine_similarity(a, b, dim=0))
             assert cos > 0.95 and 0.7 < float(a.norm() / b.norm()) < 1.4, (k, cos, float(a.norm() / b.norm()))
+
+
+def test_cayley_small_batch_equals_per_layer():
+    """fiode_cayley_small_batch_fwd / _bwd (one CTA per layer, one launch): Q, Minv-based adjoint and galpha are bit-identical
+    with the per-layer calls, for the step's small layers incl. the k = 1 conv matrices (mult = sqrt(F))."""
+    from fiode_b200 import ops
+    shapes = [(128, 10, 1.0), (10, 128, 1.0), (10, 512, 1.0), (32, 128, (16 * 9) ** 0.5), (64, 256, (8 * 5) ** 0.5)]
+    Ws = [randn(co, ci, seed=10 + i).to(DEV) for i, (co, ci, _) in enumerate(shapes)]
+    als = [W.norm() * (0.7 + 0.1 * i) for i, W in enumerate(Ws)]
+    gQs = [randn(co, ci, seed=30 + i).to(DEV) for i, (co, ci, _) in enumerate(shapes)]
+    mults = [m for _, _, m in shapes]
+    assert all(ops.cayley_small_ok(co, ci) for co, ci, _ in shapes) and not ops.cayley_small_ok(128, 128)
+    Qs, Ms = ops.cayley_small_batch(Ws, als, mults)
+    gWs, gas = ops.cayley_small_batch_bwd(Ws, als, mults, gQs, Ms)
+    for i, (co, ci, m) in enumerate(shapes):
+        if m == 1.0:
+            Q1, M1 = ops.cayley_linear(Ws[i], als[i], save_minv=True)
+            gW1, ga1 = ops.cayley_linear_bwd(Ws[i], als[i], gQs[i], minv=M1)
+            assert torch.equal(Ms[i], M1)
+        else:
+            n = 16 if co == 32 else 8
+            w4 = Ws[i].reshape(co, ci, 1, 1)
+            Q1 = ops.cayley_conv(w4, als[i], n)
+            gW1, ga1 = ops.cayley_conv_bwd(w4, als[i], n, gQs[i])
+            gW1 = gW1.reshape(co, ci)
+        assert torch.equal(Qs[i], Q1), i
+        assert torch.equal(gWs[i], gW1), i
+        assert torch.equal(gas[i], ga1.reshape(1)), i
+    with pytest.raises(Exception):
+        ops.cayley_small_batch([randn(128, 128).to(DEV)], [torch.ones((), device=DEV)], [1.0])
+
+
+def test_prefetched_cayley_transforms_leave_the_fi_step_unchanged(sd):
+    """layers.prefetch_orthogonal (small layers in one launch, large ones on side streams, adjoints likewise): loss and all 33
+    gradients equal the per-layer step's bit for bit, eager and over repeated steps."""
+    from tests.test_gpu_fi import build_learning, dev
+    from fiode_b200 import layers
+    c = fx.load_golden('fi.pt')['uniform_sn1']
+    x, y = dev(c['x']), dev(c['y'])
+    var = [dev(v) if v is not None else None for v in c['variates']]
+
+    def run(prefetch):
+        old, layers._PREFETCH = layers._PREFETCH, prefetch
+        try:
+            mod = build_learning(sd, c).train()
+            mod.keep_graph_tensors = False
+            outs = []
+            for _ in range(3):
+                for p in mod.parameters():
+                    p.grad = None
+                loss = mod.compute_loss(x, y, c['B'], act='relu', variates=var)
+                loss.backward()
+                torch.cuda.synchronize()
+                outs.append((loss.detach().clone(), {k: p.grad.clone() for k, p in mod.named_parameters()}))
+            n = layers.prefetch_orthogonal(mod.model.dyn_fun, mod.model.init_coordinates)
+            for m in mod.modules():
+                if hasattr(m, '_q_prefetch'):
+                    m._q_prefetch = None
+            return outs, n
+        finally:
+            layers._PREFETCH = old
+
+    ref, n0 = run(False)
+    got, n1 = run(True)
+    assert n0 == 0 and n1 == 11
+    for (l0, g0), (l1, g1) in zip(ref, got):
+        assert torch.equal(l0, l1)
+        for k in g0:
+            assert torch.equal(g0[k], g1[k]), k
