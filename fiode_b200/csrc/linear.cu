@@ -110,7 +110,15 @@ __global__ void gemm_epilogue_kernel(const float* __restrict__ part, int splits,
         for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
             const size_t m = e / half; const int n = (int)(e - m * half);
             float u = 0.f, w = 0.f;
-            for (int s = 0; s < splits; ++s) { u += part[s * MN + m * N + n]; w += part[s * MN + m * N + n + half]; }
+            int s = 0;
+            for (; s + 4 <= splits; s += 4) {      // loads in flight together, added in split order
+                float a[4], b[4];
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { a[i] = part[(s + i) * MN + m * N + n]; b[i] = part[(s + i) * MN + m * N + n + half]; }
+#pragma unroll
+                for (int i = 0; i < 4; ++i) { u += a[i]; w += b[i]; }
+            }
+            for (; s < splits; ++s) { u += part[s * MN + m * N + n]; w += part[s * MN + m * N + n + half]; }
             u = alpha * u + (bias ? bias[n] : 0.f);
             w = alpha * w + (bias ? bias[n + half] : 0.f);
             y[m * ldy + n] = fmaxf(u, w);
@@ -120,7 +128,15 @@ __global__ void gemm_epilogue_kernel(const float* __restrict__ part, int splits,
         for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < MN; e += (size_t)gridDim.x * blockDim.x) {
             const size_t m = e / N; const int n = (int)(e - m * N);
             float u = 0.f;
-            for (int s = 0; s < splits; ++s) u += part[s * MN + e];
+            int s = 0;
+            for (; s + 8 <= splits; s += 8) {
+                float a[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) a[i] = part[(s + i) * MN + e];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) u += a[i];
+            }
+            for (; s < splits; ++s) u += part[s * MN + e];
             y[m * ldy + n] = alpha * u + (bias ? bias[n] : 0.f);
         }
     }

@@ -112,14 +112,23 @@ __device__ __forceinline__ size_t s2d_src(int b, int ci, int p, int cin, int n) 
 // gx (un-space-to-depth'd) = Q^T gy
 __global__ void conv1x1_bwd_data_kernel(const float* __restrict__ Q, const float* __restrict__ gy, int B, int cin, int cout,
                                         int n, float* __restrict__ gx) {
-    const int P = (n / 2) * (n / 2), cin4 = 4 * cin;
-    const size_t total = (size_t)B * cin4 * P;
+    // one thread = the 2 x 2 input pixels of one (image, channel, output position): one gy load and one float4 of Q per output
+    // channel feed four sums, and the results leave as two float2 rows (the scalar version was bound by its two loads per FMA)
+    const int n2 = n / 2, P = n2 * n2, cin4 = 4 * cin;
+    const size_t total = (size_t)B * cin * P;
     for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
-        const int p = (int)(e % P), ci = (int)((e / P) % cin4), b = (int)(e / ((size_t)P * cin4));
+        const int p = (int)(e % P), c = (int)((e / P) % cin), b = (int)(e / ((size_t)P * cin));
         const float* g = gy + (size_t)b * cout * P + p;
-        float acc = 0.f;
-        for (int co = 0; co < cout; ++co) acc = fmaf(__ldg(Q + (size_t)co * cin4 + ci), g[(size_t)co * P], acc);
-        gx[s2d_src(b, ci, p, cin, n)] = acc;
+        float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        for (int co = 0; co < cout; ++co) {
+            const float4 q = __ldg(reinterpret_cast<const float4*>(Q + (size_t)co * cin4 + 4 * c));
+            const float gv = g[(size_t)co * P];
+            a0 = fmaf(q.x, gv, a0); a1 = fmaf(q.y, gv, a1); a2 = fmaf(q.z, gv, a2); a3 = fmaf(q.w, gv, a3);
+        }
+        const int w = p / n2, h = p - w * n2;                       // ci = 4c + 2 k1 + k2 -> pixel (2w + k1, 2h + k2), as s2d_src
+        float* o = gx + (((size_t)b * cin + c) * n + 2 * w) * n + 2 * h;
+        *reinterpret_cast<float2*>(o) = make_float2(a0, a1);
+        *reinterpret_cast<float2*>(o + n) = make_float2(a2, a3);
     }
 }
 // part[split][co][ci] = sum_{b in split} sum_p gy[b][co][p] xs[b][ci][p] ; CTA tile 32 co x 32 ci, thread 2 x 2
@@ -166,7 +175,15 @@ __global__ void __launch_bounds__(256) conv1x1_bwd_weight_kernel(const float* __
 __global__ void sum_partials_kernel(const float* __restrict__ part, int splits, size_t total, float* __restrict__ out) {
     for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
         float s = 0.f;
-        for (int k = 0; k < splits; ++k) s += part[(size_t)k * total + e];
+        int k = 0;
+        for (; k + 8 <= splits; k += 8) {          // eight loads in flight, added in split order (same sum as the plain loop)
+            float v[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = part[(size_t)(k + i) * total + e];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) s += v[i];
+        }
+        for (; k < splits; ++k) s += part[(size_t)k * total + e];
         out[e] = s;
     }
 }
@@ -174,31 +191,66 @@ __global__ void sum_partials_kernel(const float* __restrict__ part, int splits, 
 // ---- Fourier-domain conv adjoints ---------------------------------------------------------------------
 // gQf[phi][co][ci] = (c_phi / n^2) sum_b GYf[b][co][phi] conj(Xf[b][ci][phi]),  c_phi = 1 on the self-conjugate columns
 // v = 0, n/2 of the half spectrum and 2 elsewhere (adjoint of irfft2, which reads each interior bin twice)
-__global__ void conv_bwd_weight_kernel(const float2* __restrict__ GYf, const float2* __restrict__ Xf, int B, int cin,
-                                       int cout, int n, float2* __restrict__ gQf) {
-    const int H = n / 2 + 1, F = n * H;
-    const size_t total = (size_t)cout * cin * F;
+__global__ void __launch_bounds__(256) conv_bwd_weight_kernel(const float2* __restrict__ GYf, const float2* __restrict__ Xf, int B,
+                                                              int cin, int cout, int n, float2* __restrict__ gQf) {
+    // one thread = 2 output x 2 input channels of one frequency: four loads feed four complex FMAs per image (the one-entry
+    // version re-read every spectrum value cin resp. cout times through L2 and was bound by that); each sum still runs over
+    // the images in order
+    const int H = n / 2 + 1, F = n * H, cin2 = (cin + 1) / 2, cout2 = (cout + 1) / 2;
+    const size_t total = (size_t)cout2 * cin2 * F;
     const float inv = 1.f / (float)(n * n);
     for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
-        const int phi = (int)(e % F), ci = (int)((e / F) % cin), co = (int)(e / ((size_t)F * cin));
-        float2 acc = make_float2(0.f, 0.f);
-        for (int b = 0; b < B; ++b)
-            cfma(acc, GYf[((size_t)b * cout + co) * F + phi], cconj(Xf[((size_t)b * cin + ci) * F + phi]));
+        const int phi = (int)(e % F), ci = 2 * (int)((e / F) % cin2), co = 2 * (int)(e / ((size_t)F * cin2));
+        const bool i1 = ci + 1 < cin, o1 = co + 1 < cout;
+        const float2* gp0 = GYf + (size_t)co * F + phi;
+        const float2* gp1 = GYf + (size_t)(o1 ? co + 1 : co) * F + phi;
+        const float2* xp0 = Xf + (size_t)ci * F + phi;
+        const float2* xp1 = Xf + (size_t)(i1 ? ci + 1 : ci) * F + phi;
+        const size_t gs = (size_t)cout * F, xs = (size_t)cin * F;
+        float2 a00 = make_float2(0.f, 0.f), a01 = a00, a10 = a00, a11 = a00;
+#pragma unroll 8
+        for (int b = 0; b < B; ++b) {
+            const float2 g0 = gp0[b * gs], g1 = gp1[b * gs], x0 = cconj(xp0[b * xs]), x1 = cconj(xp1[b * xs]);
+            cfma(a00, g0, x0); cfma(a01, g0, x1); cfma(a10, g1, x0); cfma(a11, g1, x1);
+        }
         const int v = phi % H;
         const float c = ((v == 0 || v == n / 2) ? 1.f : 2.f) * inv;
-        gQf[((size_t)phi * cout + co) * cin + ci] = make_float2(acc.x * c, acc.y * c);
+        float2* o = gQf + ((size_t)phi * cout + co) * cin + ci;
+        o[0] = make_float2(a00.x * c, a00.y * c);
+        if (i1) o[1] = make_float2(a01.x * c, a01.y * c);
+        if (o1) {
+            o[cin] = make_float2(a10.x * c, a10.y * c);
+            if (i1) o[cin + 1] = make_float2(a11.x * c, a11.y * c);
+        }
     }
 }
 // GXf[b][ci][phi] = sum_co conj(Qf[phi][co][ci]) GYf[b][co][phi]
-__global__ void conv_bwd_data_kernel(const float2* __restrict__ Qf, const float2* __restrict__ GYf, int B, int cin, int cout,
-                                     int F, float2* __restrict__ GXf) {
-    const size_t total = (size_t)B * cin * F;
+// consecutive threads = consecutive ci (Qf is (phi, co, ci): coalesced; the GYf value is one broadcast per warp), four images
+// per thread so that each Qf entry is loaded once for four sums
+constexpr int kBwdDataImgs = 4;
+__global__ void __launch_bounds__(256) conv_bwd_data_kernel(const float2* __restrict__ Qf, const float2* __restrict__ GYf, int B,
+                                                            int cin, int cout, int F, float2* __restrict__ GXf) {
+    const int Bg = (B + kBwdDataImgs - 1) / kBwdDataImgs;
+    const size_t total = (size_t)Bg * cin * F;
     for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
-        const int phi = (int)(e % F), ci = (int)((e / F) % cin), b = (int)(e / ((size_t)F * cin));
-        float2 acc = make_float2(0.f, 0.f);
-        for (int co = 0; co < cout; ++co)
-            cfma(acc, cconj(__ldg(Qf + ((size_t)phi * cout + co) * cin + ci)), GYf[((size_t)b * cout + co) * F + phi]);
-        GXf[e] = acc;
+        const int ci = (int)(e % cin), phi = (int)((e / cin) % F), b0 = kBwdDataImgs * (int)(e / ((size_t)F * cin));
+        float2 acc[kBwdDataImgs];
+        const float2* gp[kBwdDataImgs];
+#pragma unroll
+        for (int i = 0; i < kBwdDataImgs; ++i) {
+            acc[i] = make_float2(0.f, 0.f);
+            gp[i] = GYf + (size_t)(b0 + i < B ? b0 + i : b0) * cout * F + phi;
+        }
+        const float2* qp = Qf + (size_t)phi * cout * cin + ci;
+#pragma unroll 4
+        for (int co = 0; co < cout; ++co) {
+            const float2 q = cconj(__ldg(qp + (size_t)co * cin));
+#pragma unroll
+            for (int i = 0; i < kBwdDataImgs; ++i) cfma(acc[i], q, gp[i][(size_t)co * F]);
+        }
+#pragma unroll
+        for (int i = 0; i < kBwdDataImgs; ++i)
+            if (b0 + i < B) GXf[((size_t)(b0 + i) * cin + ci) * F + phi] = acc[i];
     }
 }
 
@@ -261,7 +313,9 @@ extern "C" int fiode_linear_bwd(const float* X, const float* Q, const float* gY,
     return 0;
 }
 
-static int conv1x1_splits(int B) { return B < 16 ? B : 16; }
+// one split per image up to 128: the weight gradient's grid is (4cin/32) x (cout/32) x splits CTAs, and at 16 splits the 32 x 128
+// matrix of the first stride-2 conv was 64 CTAs doing eight images each (0.27 ms on an otherwise idle GPU)
+static int conv1x1_splits(int B) { return B < 128 ? B : 128; }
 
 extern "C" size_t fiode_conv1x1_s2d_bwd_workspace_bytes(int B, int cin, int cout, int n) {
     (void)n;
@@ -276,7 +330,7 @@ extern "C" int fiode_conv1x1_s2d_bwd(const float* x, const float* Q, const float
     if (ws_bytes < fiode_conv1x1_s2d_bwd_workspace_bytes(B, cin, cout, n)) { set_error("fiode_conv1x1_s2d_bwd: workspace too small"); return -1; }
     const int P = (n / 2) * (n / 2), cin4 = 4 * cin;
     if (gx) {
-        conv1x1_bwd_data_kernel<<<nblocks((size_t)B * cin4 * P), 256, 0, st>>>(Q, gy, B, cin, cout, n, gx);
+        conv1x1_bwd_data_kernel<<<nblocks((size_t)B * cin * P), 256, 0, st>>>(Q, gy, B, cin, cout, n, gx);
         count_launch(1);
     }
     const int splits = conv1x1_splits(B), bps = (B + splits - 1) / splits;
@@ -310,10 +364,12 @@ extern "C" int fiode_cayley_conv_layer_bwd(const float* x, const float* Qf, cons
     int rc;
     if ((rc = launch_rfft2(x, B * cin, cin, n, nullptr, nullptr, Xf, st, false))) return rc;
     if ((rc = launch_rfft2(gy, B * cout, cout, n, nullptr, nullptr, GYf, st, false))) return rc;
-    conv_bwd_weight_kernel<<<nblocks((size_t)cout * cin * F), 256, 0, st>>>(GYf, Xf, B, cin, cout, n, reinterpret_cast<float2*>(gQf));
+    conv_bwd_weight_kernel<<<nblocks((size_t)((cout + 1) / 2) * ((cin + 1) / 2) * F), 256, 0, st>>>(GYf, Xf, B, cin, cout, n,
+                                                                                                 reinterpret_cast<float2*>(gQf));
     count_launch(1);
     if (gx) {
-        conv_bwd_data_kernel<<<nblocks((size_t)B * cin * F), 256, 0, st>>>(reinterpret_cast<const float2*>(Qf), GYf, B, cin, cout, F, GXf);
+        conv_bwd_data_kernel<<<nblocks((size_t)((B + kBwdDataImgs - 1) / kBwdDataImgs) * cin * F), 256, 0, st>>>(
+            reinterpret_cast<const float2*>(Qf), GYf, B, cin, cout, F, GXf);
         count_launch(1);
         // no bias, no GroupSort: the channel index is irrelevant to the inverse FFT, so a channel count the kernel does not
         // tile (the 3-channel input layer) is regrouped as (B * cin / CH) images of CH channels

@@ -51,10 +51,23 @@ def _take_prefetch(module, n=None):
     pf, module._q_prefetch = module._q_prefetch, None
     if pf is None:
         return None
-    key, pn, Q = pf
+    key, pn, Q, st = pf
+    if st is not None:                 # prepared on a side stream: the consumer joins it here, not the whole step up front
+        torch.cuda.current_stream().wait_stream(st)
     if key != _version(module.weight, module.alpha) or pn != n:
         return None
     return Q
+
+
+def finish_prefetch(*roots):
+    """Join the side streams of prepared layers that no forward has picked up yet (a stream forked inside a CUDA-graph
+    capture has to come back to the capturing stream; eager code loses nothing by it)."""
+    for root in roots:
+        for m in root.modules():
+            pf = getattr(m, '_q_prefetch', None)
+            if pf is not None and pf[3] is not None:
+                torch.cuda.current_stream().wait_stream(pf[3])
+                m._q_prefetch = pf[:3] + (None,)
 
 
 _PREFETCH = os.environ.get('FIODE_PREFETCH', '1') != '0'
@@ -75,7 +88,8 @@ def prefetch_orthogonal(*roots):
     backward) and each large layer's launch chain (Gauss-Jordan on a 512 x 512 matrix is ~16 dependent launches) runs on its
     own side stream next to the others; autograd runs each node's backward on the stream of its forward, so the adjoints
     overlap the activation backward the same way.  Values and gradients are those of the per-layer path, bit for bit.
-    Each layer's forward picks its Q up (``_take_prefetch``); a layer not reached this step drops it at the next prefetch.
+    Each layer's forward picks its Q up and joins that layer's stream there (``_take_prefetch``), so the first layers' activations
+    run while the last layers' matrices are still being inverted; ``finish_prefetch`` joins what no forward reached.
     ``FIODE_PREFETCH=0`` turns this off.  Returns the number of layers prepared."""
     if not _PREFETCH or not torch.is_grad_enabled():
         return 0
@@ -103,23 +117,25 @@ def prefetch_orthogonal(*roots):
         return 0
     cur = torch.cuda.current_stream()
     big.sort(key=lambda e: -e[0].weight.numel())
-    streams = []
     for i, (m, n) in enumerate(big):
         st = _side_stream(m.weight.device, i)
         st.wait_stream(cur)
         with torch.cuda.stream(st):
             Q = ag.CayleyLinearQ.apply(m.weight, m.alpha) if n is None else ag.CayleyConvQ.apply(m.weight, m.alpha, n)
-        m._q_prefetch = (_version(m.weight, m.alpha), n, Q)
-        streams.append(st)
-    if small:
+        m._q_prefetch = (_version(m.weight, m.alpha), n, Q, st)
+    # small layers: the linear ones (dynamics, fc -- their dL/dQ all arrive early in backward) as one node, each stride-2 conv's
+    # matrix as its own (its dL/dQ arrives late; sharing a node would hold every small adjoint back to the end of the step)
+    groups = [[e for e in small if e[1] is None]] + [[e] for e in small if e[1] is not None]
+    for j, grp in enumerate(g for g in groups if g):
+        st = _side_stream(grp[0][0].weight.device, len(big) + j)
+        st.wait_stream(cur)
         flat = []
-        for m, _, _ in small:
+        for m, _, _ in grp:
             flat += [m.weight, m.alpha]
-        Qs = ag.CayleySmallBatchQ.apply(tuple(mu for _, _, mu in small), *flat)
-        for (m, n, _), Q in zip(small, Qs):
-            m._q_prefetch = (_version(m.weight, m.alpha), n, Q)
-    for st in streams:
-        cur.wait_stream(st)
+        with torch.cuda.stream(st):
+            Qs = ag.CayleySmallBatchQ.apply(tuple(mu for _, _, mu in grp), *flat)
+        for (m, n, _), Q in zip(grp, Qs):
+            m._q_prefetch = (_version(m.weight, m.alpha), n, Q, st)
     return len(small) + len(big)
 
 

@@ -8,7 +8,7 @@ import torch
 from torch import nn
 
 from . import ops
-from .layers import prefetch_orthogonal
+from .layers import finish_prefetch, prefetch_orthogonal
 from .models import IVP
 
 ADAPTIVE_SOLVERS = ['dopri8', 'dopri5', 'bosh3', 'adaptive_heun']
@@ -163,7 +163,8 @@ class LyapunovLearning(nn.Module):
         if dyn.training and torch.is_grad_enabled() and x.is_cuda:
             # all of the step's Cayley transforms first: the small layers in one launch, the large ones side by side
             init = self.model.init_coordinates
-            prefetch_orthogonal(dyn, *([init] if static_state is None and isinstance(init, nn.Module) else []))
+            pf_roots = (dyn, init) if static_state is None and isinstance(init, nn.Module) else (dyn,)
+            prefetch_orthogonal(*pf_roots)
         if static_state is None:
             static_state, _ = self.model.init_coordinates(x, dyn)
         S = self.h_sample_size
@@ -192,6 +193,8 @@ class LyapunovLearning(nn.Module):
                 q = q.clone().requires_grad_(True)
                 l.Q_grad_proxy = q
             Qs.append(q)
+        if dyn.training and torch.is_grad_enabled() and x.is_cuda:
+            finish_prefetch(*pf_roots)
         if not static_state.requires_grad:
             static_state = static_state.detach().requires_grad_(True)
         drop_p = 0.0

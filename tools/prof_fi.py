@@ -70,3 +70,22 @@ if len(sys.argv) > 1 and sys.argv[1] == 'graph':
         print('eager step  :', bench.timed(step, 20) / 20, 'ms')
     except Exception:
         traceback.print_exc()
+
+if len(sys.argv) > 2 and sys.argv[2] == 'trace':
+    # kernel timeline of one graph replay (kineto): per-stream start / duration, for the critical path
+    import json
+    from torch.profiler import profile, ProfilerActivity
+    with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
+        g()
+        torch.cuda.synchronize()
+    os.makedirs('gpurun_out', exist_ok=True)
+    prof.export_chrome_trace('gpurun_out/fi_trace_raw.json')
+    ev = json.load(open('gpurun_out/fi_trace_raw.json'))['traceEvents']
+    ks = [e for e in ev if e.get('cat') in ('kernel', 'gpu_memcpy', 'gpu_memset')]
+    ks.sort(key=lambda e: e['ts'])
+    t0 = ks[0]['ts']
+    with open('gpurun_out/fi_trace.txt', 'w') as f:
+        for e in ks:
+            f.write(f"{e['ts'] - t0:9.1f} {e['dur']:8.1f} s{e['args'].get('stream', '?'):<4} {e['name'][:100]}\n")
+    os.remove('gpurun_out/fi_trace_raw.json')
+    print('trace:', len(ks), 'kernels, span', ks[-1]['ts'] + ks[-1]['dur'] - t0, 'us')
