@@ -70,6 +70,35 @@ __global__ void cayley_prep1_kernel(const float* __restrict__ W, int cout, int c
         if (r >= n) Vt[(size_t)c * (R - n) + (r - n)] = v;
     }
 }
+// The same two outputs through a 32 x 32 shared-memory tile (block 32 x 8): out1 (R x n) = f * (tr ? S^T : S), out2 (n x (R-n)) = the
+// transpose of out1's rows n.. -- every global access runs along a contiguous axis (the element-per-thread kernels above and
+// below read or write one of the three arrays with a stride of a whole row).  f = scale[0] when scale is given, else 1.
+__global__ void __launch_bounds__(256) cayley_tile_prep_kernel(const float* __restrict__ S, int cout, int cin, int tr,
+                                                               const float* __restrict__ scale, float* __restrict__ out1,
+                                                               float* __restrict__ out2) {
+    __shared__ float tile[32][33];
+    const int R = tr ? cin : cout, n = tr ? cout : cin;
+    const float f = scale ? scale[0] : 1.f;
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32, x = threadIdx.x;
+    // tile[rl][cl] = f * value at (r0 + rl, c0 + cl)
+    if (tr) {
+        for (int cl = threadIdx.y; cl < 32; cl += 8)
+            if (c0 + cl < n && r0 + x < R) tile[x][cl] = f * S[(size_t)(c0 + cl) * cin + r0 + x];
+    } else {
+        for (int rl = threadIdx.y; rl < 32; rl += 8)
+            if (r0 + rl < R && c0 + x < n) tile[rl][x] = f * S[(size_t)(r0 + rl) * cin + c0 + x];
+    }
+    __syncthreads();
+    for (int rl = threadIdx.y; rl < 32; rl += 8)
+        if (r0 + rl < R && c0 + x < n) out1[(size_t)(r0 + rl) * n + c0 + x] = tile[rl][x];
+    for (int cl = threadIdx.y; cl < 32; cl += 8)
+        if (c0 + cl < n && r0 + x < R && r0 + x >= n) out2[(size_t)(c0 + cl) * (R - n) + (r0 + x - n)] = tile[x][cl];
+}
+static void launch_tile_prep(const float* S, int cout, int cin, int tr, const float* scale, float* out1, float* out2,
+                             cudaStream_t st) {
+    const int R = tr ? cin : cout, n = tr ? cout : cin;
+    cayley_tile_prep_kernel<<<dim3((n + 31) / 32, (R + 31) / 32), dim3(32, 8), 0, st>>>(S, cout, cin, tr, scale, out1, out2);
+}
 // IpA = I + U - U^T + G ; ImAT = (I - A)^T = I - (U^T - U + G^T)
 __global__ void cayley_prep2_kernel(const float* __restrict__ Ws, const float* __restrict__ G, int n, int has_v,
                                     float* __restrict__ IpA, float* __restrict__ ImAT) {
@@ -629,7 +658,7 @@ int cayley_linear_impl(const float* W, const float* alpha, int cout, int cin, fl
     sumsq_partial_kernel<<<kNormBlocks, 256, 0, st>>>(W, total, part);
     norm_finalize_kernel<<<1, 32, 0, st>>>(part, kNormBlocks, alpha, norm_mult, scale);
     const unsigned blocks = (unsigned)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
-    cayley_prep1_kernel<<<blocks, 256, 0, st>>>(W, cout, cin, tr, scale, Ws, Vt);
+    launch_tile_prep(W, cout, cin, tr, scale, Ws, Vt, st);
     count_launch(3);
     int rc;
     const int has_v = R > n;
@@ -713,10 +742,11 @@ __global__ void __launch_bounds__(256) cayley_conv_kernel(const float* __restric
     float2* A = Y + cin * cin;
     __shared__ float sc_sh;
     const int t = threadIdx.x, phi = blockIdx.x, H = n / 2 + 1, u = phi / H, v = phi - u * H;
-    if (t == 0) {
-        double s = 0;
-        for (int i = 0; i < F; ++i) s += part[i];
-        sc_sh = alpha[0] / (float)sqrt(s);
+    if (t < 32) {                               // the F per-frequency partials, by one warp (a single thread walking them
+        double s = 0;                           // cost every CTA ~8 us before it could start)
+        for (int i = t; i < F; i += 32) s += part[i];
+        s = warp_sum(s);
+        if (t == 0) sc_sh = alpha[0] / (float)sqrt(s);
     }
     __syncthreads();
     const float sc = sc_sh;
@@ -841,6 +871,48 @@ __global__ void __launch_bounds__(256) cayley_bwd_assemble_kernel(const float* _
         part[blockIdx.x] = s;
     }
 }
+// the same for a transposed layer (cin > cout: gWn = [gU ; gV1 + gV2]^T) through 32 x 32 tiles, so that the reads of gU / gV and the
+// writes of gWn both run along contiguous rows; CTA b takes tiles b, b + gridDim.x, ... and leaves one partial of <gWn, W>
+__global__ void __launch_bounds__(256) cayley_bwd_assemble_tr_kernel(const float* __restrict__ gU, const float* __restrict__ gV1,
+                                                                     const float* __restrict__ gV2, const float* __restrict__ W,
+                                                                     int R, int n, float* __restrict__ gWn,
+                                                                     double* __restrict__ part) {
+    __shared__ float tile[32][33];
+    __shared__ double sh[8];
+    const int tc = (n + 31) / 32, tr_ = (R + 31) / 32, x = threadIdx.x & 31, y = threadIdx.x >> 5;
+    double acc = 0;
+    for (int tI = blockIdx.x; tI < tc * tr_; tI += gridDim.x) {
+        const int r0 = (tI / tc) * 32, c0 = (tI % tc) * 32;
+        for (int rl = y; rl < 32; rl += 8) {
+            const int r = r0 + rl, c = c0 + x;
+            if (r < R && c < n) {
+                float g;
+                if (r < n) g = gU[(size_t)r * n + c];
+                else { const size_t q = (size_t)(r - n) * n + c; g = gV1[q] + gV2[q]; }
+                tile[rl][x] = g;
+            }
+        }
+        __syncthreads();
+        for (int cl = y; cl < 32; cl += 8) {
+            const int c = c0 + cl, r = r0 + x;             // gWn is (cout = n) x (cin = R): row c, column r
+            if (c < n && r < R) {
+                const float g = tile[x][cl];
+                const size_t e = (size_t)c * R + r;
+                gWn[e] = g;
+                acc += (double)g * (double)W[e];
+            }
+        }
+        __syncthreads();
+    }
+    acc = warp_sum(acc);
+    if (x == 0) sh[y] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double s2 = 0;
+        for (int i = 0; i < 8; ++i) s2 += sh[i];
+        part[blockIdx.x] = s2;
+    }
+}
 // gW = sc (gWn - W dot / ||W||^2) ; galpha = dot / (||W|| mult)      scale[0] = alpha / (||W|| mult), scale[1] = ||W|| mult
 __global__ void cayley_bwd_finalize_kernel(const float* __restrict__ gWn, const float* __restrict__ W, size_t total,
                                            const double* __restrict__ part, int np, const float* __restrict__ scale,
@@ -901,23 +973,23 @@ int cayley_linear_bwd_impl(const float* W, const float* alpha, int cout, int cin
     sumsq_partial_kernel<<<kNormBlocks, 256, 0, st>>>(W, total, part);
     norm_finalize_kernel<<<1, 32, 0, st>>>(part, kNormBlocks, alpha, norm_mult, scale);
     const unsigned blocks = (unsigned)((total + 255) / 256 < 2048 ? (total + 255) / 256 : 2048);
-    cayley_prep1_kernel<<<blocks, 256, 0, st>>>(W, cout, cin, tr, scale, Ws, Vt);
+    launch_tile_prep(W, cout, cin, tr, scale, Ws, Vt, st);
     count_launch(3);
     int rc;
     const int has_v = R > n;
-    if (has_v && (rc = gemm_nt(Vt, R - n, Vt, R - n, n, n, R - n, nullptr, 1.f, 0, Gm, n, gws, gws_bytes, st))) return rc;
     const int nb = (n * n + 255) / 256;
-    cayley_prep2_kernel<<<nb, 256, 0, st>>>(Ws, Gm, n, has_v, X, ImAT);
-    count_launch(1);
     const float* M = M_saved;                  // (I + A)^-1 kept by the forward call, else inverted again here
-    if (!M) {
+    if (!M) {                                  // (A = U - U^T + V^T V is needed for that only)
+        if (has_v && (rc = gemm_nt(Vt, R - n, Vt, R - n, n, n, R - n, nullptr, 1.f, 0, Gm, n, gws, gws_bytes, st))) return rc;
+        cayley_prep2_kernel<<<nb, 256, 0, st>>>(Ws, Gm, n, has_v, X, ImAT);
+        count_launch(1);
         float* Minv = nullptr;
         if ((rc = gj_inverse(X, Y, n, &Minv, st))) return rc;
         M = Minv;
     }
     transpose_kernel<<<dim3((n + 31) / 32, (n + 31) / 32), dim3(32, 8), 0, st>>>(M, n, n, Mt);
     // ---- backward -----------------------------------------------------------------------------------
-    cayley_bwd_prep_kernel<<<blocks, 256, 0, st>>>(gQ, cout, cin, tr, G, Gt2);
+    launch_tile_prep(gQ, cout, cin, tr, nullptr, G, Gt2, st);
     count_launch(2);
     const float* V = Ws + (size_t)n * n;
     const float* G2 = G + (size_t)n * n;
@@ -932,7 +1004,8 @@ int cayley_linear_bwd_impl(const float* W, const float* alpha, int cout, int cin
         if ((rc = gemm_nt(G2, n, M, n, R - n, n, n, nullptr, -2.f, 0, gV1, n, gws, gws_bytes, st))) return rc;   // -2 G2 M^T
         if ((rc = gemm_nt(V, n, S, n, R - n, n, n, nullptr, 1.f, 0, gV2, n, gws, gws_bytes, st))) return rc;     // V (gA + gA^T)
     }
-    cayley_bwd_assemble_kernel<<<kNormBlocks, 256, 0, st>>>(gU, gV1, gV2, W, cout, cin, tr, gWn, part);
+    if (tr) cayley_bwd_assemble_tr_kernel<<<kNormBlocks, 256, 0, st>>>(gU, gV1, gV2, W, R, n, gWn, part);
+    else cayley_bwd_assemble_kernel<<<kNormBlocks, 256, 0, st>>>(gU, gV1, gV2, W, cout, cin, tr, gWn, part);
     cayley_bwd_finalize_kernel<<<blocks, 256, 0, st>>>(gWn, W, total, part, kNormBlocks, scale, norm_mult, gW, galpha);
     count_launch(2);
     cudaError_t e = cudaGetLastError();
@@ -957,10 +1030,11 @@ __global__ void __launch_bounds__(256) cayley_conv_bwd_kernel(const float* __res
     __shared__ float sc_sh;
     __shared__ double red[8];
     const int t = threadIdx.x, phi = blockIdx.x, H = n / 2 + 1, u = phi / H, v = phi - u * H;
-    if (t == 0) {
-        double s = 0;
-        for (int i = 0; i < F; ++i) s += part[i];
-        sc_sh = alpha[0] / (float)sqrt(s);
+    if (t < 32) {                               // the F per-frequency partials, by one warp (a single thread walking them
+        double s = 0;                           // cost every CTA ~8 us before it could start)
+        for (int i = t; i < F; i += 32) s += part[i];
+        s = warp_sum(s);
+        if (t == 0) sc_sh = alpha[0] / (float)sqrt(s);
     }
     __syncthreads();
     const float sc = sc_sh;

@@ -60,31 +60,40 @@ __global__ void group_sort_bwd_kernel(const float* __restrict__ x, const float* 
 }
 
 // ---- bias gradient: gb[c] = sum_{b, r} gy[b][c][r], one CTA per channel, ordered --------------------------
-__global__ void __launch_bounds__(256) bias_grad_kernel(const float* __restrict__ gy, int B, int C, int inner,
-                                                        float* __restrict__ gb) {
-    __shared__ double sh[8];
-    const int c = blockIdx.x;
+// 32 warps, a warp per image with the lanes along the contiguous inner axis (float4 when it divides): the channel count is
+// far below the SM count (32 / 64 CTAs), so each CTA has to keep many loads in flight on its own
+constexpr int kBiasThreads = 1024;
+__global__ void __launch_bounds__(kBiasThreads) bias_grad_kernel(const float* __restrict__ gy, int B, int C, int inner,
+                                                                 float* __restrict__ gb) {
+    __shared__ double sh[kBiasThreads / 32];
+    const int c = blockIdx.x, w = threadIdx.x >> 5, l = threadIdx.x & 31;
     double acc = 0;
-    if (inner >= 32) {           // warp per image, lanes along the (contiguous) inner axis: no index division
-        for (int b = threadIdx.x >> 5; b < B; b += 8) {
+    if (inner >= 32) {
+        for (int b = w; b < B; b += kBiasThreads / 32) {
             const float* g = gy + ((size_t)b * C + c) * inner;
             float a = 0.f;
-            for (int r = threadIdx.x & 31; r < inner; r += 32) a += g[r];
+            if ((inner & 127) == 0) {
+                const float4* g4 = reinterpret_cast<const float4*>(g);
+#pragma unroll 4
+                for (int r = l; r < inner / 4; r += 32) { const float4 v = g4[r]; a += (v.x + v.y) + (v.z + v.w); }
+            } else {
+                for (int r = l; r < inner; r += 32) a += g[r];
+            }
             acc += (double)a;
         }
     } else {
         const size_t per = (size_t)B * inner;
-        for (size_t e = threadIdx.x; e < per; e += 256) {
+        for (size_t e = threadIdx.x; e < per; e += kBiasThreads) {
             const size_t b = e / inner, r = e - b * inner;
             acc += (double)gy[(b * C + c) * inner + r];
         }
     }
     acc = warp_sum(acc);
-    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    if (l == 0) sh[w] = acc;
     __syncthreads();
     if (threadIdx.x == 0) {
         double s = 0;
-        for (int i = 0; i < 8; ++i) s += sh[i];
+        for (int i = 0; i < kBiasThreads / 32; ++i) s += sh[i];
         gb[c] = (float)s;
     }
 }
@@ -172,19 +181,37 @@ __global__ void __launch_bounds__(256) conv1x1_bwd_weight_kernel(const float* __
             if (co < cout && ci < cin4) dst[(size_t)co * cin4 + ci] = acc[i][j];
         }
 }
-__global__ void sum_partials_kernel(const float* __restrict__ part, int splits, size_t total, float* __restrict__ out) {
-    for (size_t e = blockIdx.x * (size_t)blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+// out[e] = sum_k part[k][e]: a CTA takes 32 consecutive outputs, its eight warps an eighth of the splits each (loads of a whole
+// chunk in flight, added in split order), then the eight sub-sums are added in warp order -- deterministic, and the 128 splits
+// of the stride-2 conv's weight gradient no longer sit in one thread's dependent chain
+__global__ void __launch_bounds__(256) sum_partials_kernel(const float* __restrict__ part, int splits, size_t total,
+                                                           float* __restrict__ out) {
+    __shared__ float sh[8][32];
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    const int chunk = (splits + 7) / 8, k0 = w * chunk, k1 = min(splits, k0 + chunk);
+    for (size_t base = (size_t)blockIdx.x * 32; base < total; base += (size_t)gridDim.x * 32) {
+        const size_t e = base + l;
         float s = 0.f;
-        int k = 0;
-        for (; k + 8 <= splits; k += 8) {          // eight loads in flight, added in split order (same sum as the plain loop)
-            float v[8];
+        if (e < total) {
+            int k = k0;
+            for (; k + 8 <= k1; k += 8) {
+                float v[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = part[(size_t)(k + i) * total + e];
+                for (int i = 0; i < 8; ++i) v[i] = part[(size_t)(k + i) * total + e];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) s += v[i];
+                for (int i = 0; i < 8; ++i) s += v[i];
+            }
+            for (; k < k1; ++k) s += part[(size_t)k * total + e];
         }
-        for (; k < splits; ++k) s += part[(size_t)k * total + e];
-        out[e] = s;
+        sh[w][l] = s;
+        __syncthreads();
+        if (w == 0 && e < total) {
+            float r = sh[0][l];
+#pragma unroll
+            for (int i = 1; i < 8; ++i) r += sh[i][l];
+            out[e] = r;
+        }
+        __syncthreads();
     }
 }
 
@@ -278,7 +305,7 @@ extern "C" int fiode_group_sort_bwd(const float* x_pre, const float* gy, int B, 
 
 extern "C" int fiode_bias_grad(const float* gy, int B, int C, int inner, float* gb, void* stream) {
     if (!gy || !gb || B <= 0 || C <= 0 || inner <= 0) { set_error("fiode_bias_grad: bad args"); return -1; }
-    bias_grad_kernel<<<C, 256, 0, (cudaStream_t)stream>>>(gy, B, C, inner, gb);
+    bias_grad_kernel<<<C, kBiasThreads, 0, (cudaStream_t)stream>>>(gy, B, C, inner, gb);
     FIODE_CUDA(cudaGetLastError());
     count_launch(1);
     return 0;
@@ -306,7 +333,7 @@ extern "C" int fiode_linear_bwd(const float* X, const float* Q, const float* gY,
     }
     if ((rc = gemm_tn(gY, N, X, K, N, K, M, 1.f, gQ, K, gws, gws_bytes, st))) return rc;
     if (gb) {
-        bias_grad_kernel<<<N, 256, 0, st>>>(gY, M, N, 1, gb);
+        bias_grad_kernel<<<N, kBiasThreads, 0, st>>>(gY, M, N, 1, gb);
         count_launch(1);
     }
     FIODE_CUDA(cudaGetLastError());
@@ -336,10 +363,10 @@ extern "C" int fiode_conv1x1_s2d_bwd(const float* x, const float* Q, const float
     const int splits = conv1x1_splits(B), bps = (B + splits - 1) / splits;
     float* part = reinterpret_cast<float*>(ws);
     conv1x1_bwd_weight_kernel<<<dim3((cin4 + 31) / 32, (cout + 31) / 32, splits), 256, 0, st>>>(x, gy, B, cin, cout, n, bps, part);
-    sum_partials_kernel<<<nblocks((size_t)cout * cin4), 256, 0, st>>>(part, splits, (size_t)cout * cin4, gQ);
+    sum_partials_kernel<<<nblocks(((size_t)cout * cin4 + 31) / 32 * 256), 256, 0, st>>>(part, splits, (size_t)cout * cin4, gQ);
     count_launch(2);
     if (gb) {
-        bias_grad_kernel<<<cout, 256, 0, st>>>(gy, B, cout, P, gb);
+        bias_grad_kernel<<<cout, kBiasThreads, 0, st>>>(gy, B, cout, P, gb);
         count_launch(1);
     }
     FIODE_CUDA(cudaGetLastError());
@@ -382,7 +409,7 @@ extern "C" int fiode_cayley_conv_layer_bwd(const float* x, const float* Qf, cons
         if ((rc = launch_irfft2(GXf, Bv, Cv, n, nullptr, 0, gx, st, false))) return rc;
     }
     if (gb) {
-        bias_grad_kernel<<<cout, 256, 0, st>>>(gy, B, cout, n * n, gb);
+        bias_grad_kernel<<<cout, kBiasThreads, 0, st>>>(gy, B, cout, n * n, gb);
         count_launch(1);
     }
     FIODE_CUDA(cudaGetLastError());
