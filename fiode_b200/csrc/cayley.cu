@@ -318,11 +318,102 @@ __global__ void __launch_bounds__(256) gj_block_update_kernel(const float* __res
         }
 }
 
+// The same blocked Gauss-Jordan with 32 x 32 pivot blocks and ONE launch per block step.  A 32 x 32 block is inverted by a single
+// warp in registers (lane = column, the 32 pivots fully unrolled: the pivot row is the lane's own register, the multipliers come
+// by shuffle -- no shared memory, no barrier), so every CTA (ib, jb) simply inverts D = X_kk itself, forms
+// T = D^-1 X_kj (or D^-1 when jb = k) and writes its own block: Y_kj = T for the pivot row, Y_ij = X_ij - X_ik T elsewhere
+// (X_ij read as 0 when jb = k).  n = 512: 16 launches of ~15 us instead of 8 x (27 us panel + 10 us update).
+constexpr int GB2 = 32;
+__global__ void __launch_bounds__(256) gj_block32_step_kernel(const float* __restrict__ X, float* __restrict__ Y, int n, int kb) {
+    __shared__ float Ds[GB2][GB2 + 1];
+    __shared__ float Ps[GB2][GB2 + 1];
+    __shared__ float Ls[GB2][GB2 + 1];
+    __shared__ float Ts[GB2][GB2 + 1];
+    const int t = threadIdx.x, jb = blockIdx.x, ib = blockIdx.y, w = t >> 5, l = t & 31;
+    for (int e = t; e < GB2 * GB2; e += 256) {
+        const int i = e >> 5, j = e & 31;
+        Ds[i][j] = X[(size_t)(kb * GB2 + i) * n + kb * GB2 + j];
+        Ps[i][j] = X[(size_t)(kb * GB2 + i) * n + jb * GB2 + j];
+        if (ib != kb) Ls[i][j] = X[(size_t)(ib * GB2 + i) * n + kb * GB2 + j];
+    }
+    __syncthreads();
+    if (w == 0) {
+        float v[GB2];
+#pragma unroll
+        for (int i = 0; i < GB2; ++i) v[i] = Ds[i][l];
+#pragma unroll
+        for (int k = 0; k < GB2; ++k) {
+            const float ip = 1.f / __shfl_sync(0xffffffffu, v[k], k);
+            const float pk = v[k] * ip;
+            float f[GB2];                                  // column k (M[i][k] before this pivot touches it): all 31 shuffles first,
+#pragma unroll                                             // so that their latencies overlap instead of chaining through one register
+            for (int i = 0; i < GB2; ++i) f[i] = (i == k) ? 0.f : __shfl_sync(0xffffffffu, v[i], k);
+#pragma unroll
+            for (int i = 0; i < GB2; ++i) {
+                if (i == k) continue;
+                v[i] = (l == k) ? -f[i] * ip : fmaf(-f[i], pk, v[i]);
+            }
+            v[k] = (l == k) ? ip : pk;
+        }
+#pragma unroll
+        for (int i = 0; i < GB2; ++i) Ds[i][l] = v[i];
+    }
+    __syncthreads();
+    const int r = t >> 3, c0 = 4 * (t & 7);              // thread = one row, four consecutive columns of the 32 x 32 block
+    float acc[4];
+    if (jb == kb) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[q] = Ds[r][c0 + q];
+    } else {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[q] = 0.f;
+#pragma unroll 8
+        for (int m = 0; m < GB2; ++m) {
+            const float d = Ds[r][m];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) acc[q] = fmaf(d, Ps[m][c0 + q], acc[q]);
+        }
+    }
+    if (ib == kb) {
+        *reinterpret_cast<float4*>(Y + (size_t)(kb * GB2 + r) * n + jb * GB2 + c0) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        return;
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) Ts[r][c0 + q] = acc[q];
+    __syncthreads();
+    float a2[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 8
+    for (int m = 0; m < GB2; ++m) {
+        const float lv = Ls[r][m];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) a2[q] = fmaf(lv, Ts[m][c0 + q], a2[q]);
+    }
+    const size_t o = (size_t)(ib * GB2 + r) * n + jb * GB2 + c0;
+    float4 x4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (jb != kb) x4 = *reinterpret_cast<const float4*>(X + o);
+    *reinterpret_cast<float4*>(Y + o) = make_float4(x4.x - a2[0], x4.y - a2[1], x4.z - a2[2], x4.w - a2[3]);
+}
+static int gj_block_size() {
+    static const int v = [] { const char* e = getenv("FIODE_GJ_BLOCK"); return (e && atoi(e) == 64) ? 64 : 32; }();
+    return v;
+}
+
 static int gj_inverse(float* X, float* Y, int n, float** result, cudaStream_t st) {
     if (n <= 128) {
         gj_inverse_smem_kernel<<<1, 1024, 0, st>>>(X, Y, n);
         count_launch(1);
         *result = Y;
+        return 0;
+    }
+    if (n % GB2 == 0 && gj_block_size() == 32) {
+        const int nb = n / GB2;
+        float *in = X, *out = Y;
+        for (int kb = 0; kb < nb; ++kb) {
+            gj_block32_step_kernel<<<dim3(nb, nb), 256, 0, st>>>(in, out, n, kb);
+            float* tmp = in; in = out; out = tmp;
+        }
+        count_launch(nb);
+        *result = in;
         return 0;
     }
     if (n % GB == 0) {
