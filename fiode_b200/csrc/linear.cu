@@ -273,7 +273,9 @@ extern "C" int fiode_linear_fwd(const float* X, const float* Q, const float* bia
     if (M <= 0 || N <= 0 || K <= 0) { set_error("fiode_linear_fwd: bad sizes"); return -1; }
     if (group_sort && (N & 1)) { set_error("fiode_linear_fwd: GroupSort needs an even width"); return -1; }
     cudaStream_t st = (cudaStream_t)stream;
-    if (mlp_path() == 0 && gemm_tc_supported(N, K, group_sort) && ws_bytes >= gemm_tc_packed_bytes(N, K)) {
+    // the tensor-core kernel tiles M by 128 rows per CTA and walks all of K in each: at a training batch (M = 128) it is 4 CTAs
+    // deep in a latency chain plus a weight re-pack per call, where the split-K FFMA product fills the GPU -- rows >= 1024 only
+    if (mlp_path() == 0 && M >= 1024 && gemm_tc_supported(N, K, group_sort) && ws_bytes >= gemm_tc_packed_bytes(N, K)) {
         // tensor cores (fp16x2 split): split + tile the weights into the workspace, then one persistent GEMM
         int rc = launch_pack_w(Q, N, K, gemm_tc_tile(N, group_sort), group_sort, ws, st);
         if (rc) return rc;
