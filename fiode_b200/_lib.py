@@ -69,6 +69,8 @@ SIGNATURES = {
     'fiode_cayley_conv_fwd': (I, [P, P, P, I, I, I, I, I, P, P, SZ, P]),
     'fiode_linear_workspace_bytes': (SZ, [I, I, I]),
     'fiode_linear_fwd': (I, [P, P, P, I, I, I, I, P, P, SZ, P]),
+    'fiode_linear_static_max_bytes': (SZ, []),
+    'fiode_linear_fwd_static': (I, [P, P, P, I, I, I, I, P, P]),
     'fiode_conv1x1_s2d_fwd': (I, [P, P, P, I, I, I, I, I, P, P]),
     'fiode_space_to_depth': (I, [P, I, I, I, P, P]),
     'fiode_group_sort': (I, [P, I, I, I, P, P]),

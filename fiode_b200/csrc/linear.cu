@@ -283,3 +283,57 @@ extern "C" int fiode_linear_fwd(const float* X, const float* Q, const float* bia
     }
     return gemm_nt(X, K, Q, K, M, N, K, bias, 1.f, group_sort, y, N, reinterpret_cast<float*>(ws), ws_bytes, st);
 }
+
+// ---- fiode_linear_fwd without a caller-supplied workspace -------------------------------------------------------------
+// No counterpart in the reference: added for callers that cannot allocate (code under
+// CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The scratch of fiode_linear_fwd -- the split-K
+// partial sums of the FFMA product, or the fp16-split re-tiled weights of the tensor-core product -- lives in a file-scope device
+// array: every GPU that loads the library holds kLinearStaticBytes (16 MiB) until the process exits.  Nothing in it has to start
+// at zero (both products write every scratch element they later read), so it is not cleared; it keeps the last call's contents,
+// and because every call on a device shares it, two calls that overlap on the GPU (different streams, or graph branches) race.
+constexpr size_t kLinearStaticBytes = (size_t)16 << 20;
+static __device__ __align__(256) unsigned char g_linear_static_scratch[kLinearStaticBytes];
+
+// In host code the array's name is a host-side stand-in, not a device address: resolved once per device, with that device current.
+static void* linear_static_scratch_ptr() {
+    static std::atomic<void*> ptrs[kMaxDevices];
+    int dev = -1;
+    const cudaError_t eg = cudaGetDevice(&dev);
+    if (eg != cudaSuccess) { set_error("fiode_linear_fwd_static: cudaGetDevice failed: %s", cudaGetErrorString(eg)); return nullptr; }
+    if (dev < 0 || dev >= kMaxDevices) { set_error("fiode_linear_fwd_static: device index %d out of range", dev); return nullptr; }
+    void* p = ptrs[dev].load(std::memory_order_acquire);
+    if (p) return p;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_linear_static_scratch);
+    if (e != cudaSuccess || !p) {
+        set_error("fiode_linear_fwd_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+        return nullptr;
+    }
+    ptrs[dev].store(p, std::memory_order_release);      // every thread resolves the same address: a repeated store is harmless
+    return p;
+}
+
+extern "C" size_t fiode_linear_static_max_bytes(void) { return kLinearStaticBytes; }
+
+extern "C" int fiode_linear_fwd_static(const float* X, const float* Q, const float* bias, int M, int N, int K,
+                                       int group_sort, float* y, void* stream) {
+    if (!X || !Q || !y) { set_error("fiode_linear_fwd_static: null pointer"); return -1; }
+    if (M <= 0 || N <= 0 || K <= 0) { set_error("fiode_linear_fwd_static: bad sizes"); return -1; }
+    if (group_sort && (N & 1)) { set_error("fiode_linear_fwd_static: GroupSort needs an even width"); return -1; }
+    // same routing as fiode_linear_fwd; the scratch this call needs is that of the product it takes
+    const bool tcp = mlp_path() == 0 && M >= 1024 && gemm_tc_supported(N, K, group_sort);
+    const size_t need = tcp ? gemm_tc_packed_bytes(N, K) : gemm_nt_workspace(M, N, K);
+    if (need > kLinearStaticBytes) {
+        set_error("fiode_linear_fwd_static: M=%d N=%d K=%d needs %zu bytes of scratch, the built-in array holds %zu; "
+                  "use fiode_linear_fwd with a caller workspace", M, N, K, need, kLinearStaticBytes);
+        return -1;
+    }
+    void* ws = linear_static_scratch_ptr();
+    if (!ws) return -1;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (tcp) {
+        int rc = launch_pack_w(Q, N, K, gemm_tc_tile(N, group_sort), group_sort, ws, st);
+        if (rc) return rc;
+        return launch_linear_tc(X, K, ws, bias, M, N, K, group_sort, y, N, st);
+    }
+    return gemm_nt(X, K, Q, K, M, N, K, bias, 1.f, group_sort, y, N, reinterpret_cast<float*>(ws), kLinearStaticBytes, st);
+}

@@ -121,6 +121,18 @@ FIODE_API int fiode_cayley_conv_fwd(const float* x, const float* Qf, const float
 FIODE_API size_t fiode_linear_workspace_bytes(int M, int N, int K);
 FIODE_API int fiode_linear_fwd(const float* X, const float* Q, const float* bias, int M, int N, int K,
                      int group_sort, float* y, void* ws, size_t ws_bytes, void* stream);
+/* fiode_linear_fwd without a workspace argument.  No counterpart in the reference: added
+ * for callers that cannot allocate (CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  The scratch
+ * (split-K partial sums / re-tiled weights) is a built-in device array of fiode_linear_static_max_bytes() = 16 MiB that every
+ * GPU loading the library holds until exit; the call allocates nothing (no cudaMalloc / cudaFree, no allocating library call)
+ * and fails with a clear fiode_last_error() when the product it takes needs more scratch than that (never more than
+ * fiode_linear_workspace_bytes(M, N, K); e.g. M = 512, N = 512, K = 4096 is 256 bytes over).  All calls on a device
+ * share the array (it keeps the last call's contents; nothing in it needs clearing): calls that overlap on the GPU race.
+ * Same results as fiode_linear_fwd, bit for bit.  Make the first call on each device outside stream capture (it resolves the
+ * array's device address once per device).                                                                                  */
+FIODE_API size_t fiode_linear_static_max_bytes(void);
+FIODE_API int fiode_linear_fwd_static(const float* X, const float* Q, const float* bias, int M, int N, int K,
+                            int group_sort, float* y, void* stream);
 /* stride-2 CayleyConv (StridedConv pre-hook layers.py:24-48 + CayleyConv.forward with k=1, whose
  * spectrum is frequency independent and real): space-to-depth + real orthogonal
  * 1x1 conv + bias (+GroupSort).  x (B,cin,n,n) -> y (B,cout,n/2,n/2); Q (cout, 4*cin).          */
