@@ -2,6 +2,8 @@
 #include "common.cuh"
 #include <cstdarg>
 #include <atomic>
+#include <cstdlib>
+#include <mutex>
 
 namespace fiode {
 static thread_local char g_err[512] = "";
@@ -37,6 +39,49 @@ bool first_use_on_device(std::atomic<bool>* flags) {
     return !flags[current_device()].exchange(true, std::memory_order_acq_rel);
 }
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// ---- fork / join of an internal side stream (common.cuh) ------------------------------------------------------------
+constexpr int kSideSlots = 8;          // callers on different streams mostly get different branches (hashed by stream handle)
+struct SideSlot { cudaStream_t s = nullptr; cudaEvent_t fork = nullptr, join = nullptr; };
+static SideSlot g_side[kMaxDevices][kSideSlots];
+static std::mutex g_side_mu;
+static bool fork_enabled() {
+    static const bool on = [] { const char* e = getenv("FIODE_FORK"); return !(e && e[0] == '0'); }();
+    return on;
+}
+static SideSlot* side_slot(cudaStream_t st) {
+    const int dev = current_device();
+    const size_t h = reinterpret_cast<size_t>(st);
+    SideSlot* sl = &g_side[dev][((h >> 4) ^ (h >> 9) ^ (h >> 14)) % kSideSlots];
+    if (sl->s) return sl;
+    std::lock_guard<std::mutex> lk(g_side_mu);
+    if (sl->s) return sl;
+    cudaStream_t s = nullptr;
+    if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    if (cudaEventCreateWithFlags(&sl->fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&sl->join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    sl->s = s;
+    return sl;
+}
+cudaStream_t fork_side(cudaStream_t st) {
+    if (!fork_enabled()) return st;
+    SideSlot* sl = side_slot(st);
+    if (!sl) { (void)cudaGetLastError(); return st; }          // no branch available: run in line
+    if (cudaEventRecord(sl->fork, st) != cudaSuccess || cudaStreamWaitEvent(sl->s, sl->fork, 0) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return st;
+    }
+    return sl->s;
+}
+int join_side(cudaStream_t st) {
+    if (!fork_enabled()) return 0;
+    SideSlot* sl = side_slot(st);
+    if (!sl) return 0;
+    cudaError_t e = cudaEventRecord(sl->join, sl->s);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(st, sl->join, 0);
+    if (e != cudaSuccess) return cuda_fail(e, "join_side");
+    return 0;
+}
 }  // namespace fiode
 
 extern "C" const char* fiode_last_error(void) { return fiode::g_err; }

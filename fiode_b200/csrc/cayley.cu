@@ -964,17 +964,17 @@ __global__ void __launch_bounds__(256) cayley_bwd_assemble_kernel(const float* _
 }
 // the same for a transposed layer (cin > cout: gWn = [gU ; gV1 + gV2]^T) through 32 x 32 tiles, so that the reads of gU / gV and the
 // writes of gWn both run along contiguous rows; CTA b takes tiles b, b + gridDim.x, ... and leaves one partial of <gWn, W>
-__global__ void __launch_bounds__(256) cayley_bwd_assemble_tr_kernel(const float* __restrict__ gU, const float* __restrict__ gV1,
+__global__ void __launch_bounds__(1024) cayley_bwd_assemble_tr_kernel(const float* __restrict__ gU, const float* __restrict__ gV1,
                                                                      const float* __restrict__ gV2, const float* __restrict__ W,
                                                                      int R, int n, float* __restrict__ gWn,
                                                                      double* __restrict__ part) {
     __shared__ float tile[32][33];
-    __shared__ double sh[8];
-    const int tc = (n + 31) / 32, tr_ = (R + 31) / 32, x = threadIdx.x & 31, y = threadIdx.x >> 5;
+    __shared__ double sh[32];
+    const int tc = (n + 31) / 32, tr_ = (R + 31) / 32, x = threadIdx.x & 31, y = threadIdx.x >> 5;   // 32 x 32 threads: one tile element each
     double acc = 0;
     for (int tI = blockIdx.x; tI < tc * tr_; tI += gridDim.x) {
         const int r0 = (tI / tc) * 32, c0 = (tI % tc) * 32;
-        for (int rl = y; rl < 32; rl += 8) {
+        for (int rl = y; rl < 32; rl += 32) {
             const int r = r0 + rl, c = c0 + x;
             if (r < R && c < n) {
                 float g;
@@ -984,7 +984,7 @@ __global__ void __launch_bounds__(256) cayley_bwd_assemble_tr_kernel(const float
             }
         }
         __syncthreads();
-        for (int cl = y; cl < 32; cl += 8) {
+        for (int cl = y; cl < 32; cl += 32) {
             const int c = c0 + cl, r = r0 + x;             // gWn is (cout = n) x (cin = R): row c, column r
             if (c < n && r < R) {
                 const float g = tile[x][cl];
@@ -1000,7 +1000,7 @@ __global__ void __launch_bounds__(256) cayley_bwd_assemble_tr_kernel(const float
     __syncthreads();
     if (threadIdx.x == 0) {
         double s2 = 0;
-        for (int i = 0; i < 8; ++i) s2 += sh[i];
+        for (int i = 0; i < 32; ++i) s2 += sh[i];
         part[blockIdx.x] = s2;
     }
 }
@@ -1024,6 +1024,7 @@ size_t cayley_linear_bwd_ws(int cout, int cin) {
     b += align256(n * (R - n) * 4 + 4);                   // Gt2
     b += 2 * align256((R - n) * n * 4 + 4);               // gV1, gV2
     b += 8 * align256(n * n * 4);                         // P, gM, T1t, gAt, S, gU, Mt, spare
+    b += align256(gemm_nt_workspace((int)R, (int)n, (int)n));   // split-K partials of the product that runs on the branch
     return b;
 }
 
@@ -1055,6 +1056,8 @@ int cayley_linear_bwd_impl(const float* W, const float* alpha, int cout, int cin
     float* gAt = (float*)take((size_t)n * n * 4);
     float* S = (float*)take((size_t)n * n * 4);
     float* gU = (float*)take((size_t)n * n * 4);
+    const size_t gws2_bytes = align256(gemm_nt_workspace(R, n, n));
+    float* gws2 = (float*)take(gws2_bytes);
     float* gws = (float*)p;
     const size_t gws_bytes = ws_bytes - (size_t)(p - reinterpret_cast<char*>(ws));
     if (gws_bytes < gemm_nt_workspace(R, n, R)) { set_error("cayley_linear_bwd: gemm workspace too small"); return -1; }
@@ -1084,6 +1087,12 @@ int cayley_linear_bwd_impl(const float* W, const float* alpha, int cout, int cin
     count_launch(2);
     const float* V = Ws + (size_t)n * n;
     const float* G2 = G + (size_t)n * n;
+    // -2 G2 M^T needs the incoming gradient and M only: on a branch, beside the chain P -> gM -> gA -> V (gA + gA^T)
+    cudaStream_t sd = st;
+    if (has_v) {
+        sd = fork_side(st);
+        if ((rc = gemm_nt(G2, n, M, n, R - n, n, n, nullptr, -2.f, 0, gV1, n, gws2, gws2_bytes, sd))) return rc;
+    }
     if (has_v && (rc = gemm_nt(Vt, R - n, Gt2, R - n, n, n, R - n, nullptr, 1.f, 0, P, n, gws, gws_bytes, st))) return rc;
     cayley_bwd_gm_kernel<<<nb, 256, 0, st>>>(G, P, n * n, has_v, gM);
     count_launch(1);
@@ -1092,10 +1101,10 @@ int cayley_linear_bwd_impl(const float* W, const float* alpha, int cout, int cin
     cayley_bwd_sym_kernel<<<nb, 256, 0, st>>>(gAt, n, S, gU);
     count_launch(1);
     if (has_v) {
-        if ((rc = gemm_nt(G2, n, M, n, R - n, n, n, nullptr, -2.f, 0, gV1, n, gws, gws_bytes, st))) return rc;   // -2 G2 M^T
         if ((rc = gemm_nt(V, n, S, n, R - n, n, n, nullptr, 1.f, 0, gV2, n, gws, gws_bytes, st))) return rc;     // V (gA + gA^T)
+        if (sd != st && (rc = join_side(st))) return rc;
     }
-    if (tr) cayley_bwd_assemble_tr_kernel<<<kNormBlocks, 256, 0, st>>>(gU, gV1, gV2, W, R, n, gWn, part);
+    if (tr) cayley_bwd_assemble_tr_kernel<<<kNormBlocks, 1024, 0, st>>>(gU, gV1, gV2, W, R, n, gWn, part);
     else cayley_bwd_assemble_kernel<<<kNormBlocks, 256, 0, st>>>(gU, gV1, gV2, W, cout, cin, tr, gWn, part);
     cayley_bwd_finalize_kernel<<<blocks, 256, 0, st>>>(gWn, W, total, part, kNormBlocks, scale, norm_mult, gW, galpha);
     count_launch(2);

@@ -22,6 +22,13 @@ int current_device();
 int sm_count();                 // of the current device (cached per device)
 bool first_use_on_device(std::atomic<bool>* flags /*[kMaxDevices]*/);
 void count_launch(int n);
+// A branch beside the caller's stream, for independent kernels of ONE entry point (a layer's weight gradient next to its data
+// gradient): fork_side(st) returns an internal stream that has waited for everything queued on st so far (call it again to
+// make the branch see later work of st); join_side(st) makes st wait for the branch.  Every fork is joined before the entry
+// point returns, so callers see plain stream semantics and a CUDA-graph capture of st stays closed.  Streams and events are
+// created once per device on first use (outside capture: run one eager call first); FIODE_FORK=0 returns st itself.
+cudaStream_t fork_side(cudaStream_t st);
+int join_side(cudaStream_t st);
 
 // ---- Dormand-Prince(5,4) tableau (torchdiffeq 0.2.2 dopri5.py) -------------
 static __device__ __constant__ const float kBeta[6][6] = {

@@ -293,10 +293,8 @@ extern "C" size_t fiode_fi_loss_workspace_bytes(long long N, int B) {
     b += 2 * al((size_t)N * NM * 4);                             // dz2/da2, dz1/da1
     b += al((size_t)B * NM * 4);                                 // D
     b += 3 * al((size_t)NM * NM * 4);                            // Q3^T, Q2^T, Qx^T
-    size_t g = gemm_nt_workspace((int)N, NM, NM);
-    const size_t g2 = gemm_tn_workspace(NM, NM, N);
-    if (g2 > g) g = g2;
-    return b + al(g);
+    // the data-gradient products and the weight-gradient products run side by side: one split-K workspace each
+    return b + al(gemm_nt_workspace((int)N, NM, NM)) + al(gemm_tn_workspace(NM, NM, N));
 }
 
 extern "C" int fiode_fi_loss_fwd(const fiode_dyn_weights* w, const float* h, const float* s, const int* y, int B, int S,
@@ -373,8 +371,10 @@ extern "C" int fiode_fi_loss_bwd_opt(const fiode_dyn_weights* w, const float* h,
     float* Q3T = take((size_t)NM * NM * 4);
     float* Q2T = take((size_t)NM * NM * 4);
     float* QxT = take((size_t)NM * NM * 4);
-    float* gws = reinterpret_cast<float*>(p);
-    const size_t gwb = ws_bytes - (size_t)(p - reinterpret_cast<char*>(ws));
+    float* gws = reinterpret_cast<float*>(p);                       // data-gradient chain (caller's stream)
+    const size_t gwb = al(gemm_nt_workspace((int)N, NM, NM));
+    float* gws2 = reinterpret_cast<float*>(p + gwb);                // weight / bias gradients (branch)
+    const size_t gwb2 = ws_bytes - (size_t)(p + gwb - reinterpret_cast<char*>(ws));
     const int Ni = (int)N;
     const long long want = (N + 255) / 256;
     const int grid = (int)(want < 4096 ? want : 4096);
@@ -384,23 +384,30 @@ extern "C" int fiode_fi_loss_bwd_opt(const fiode_dyn_weights* w, const float* h,
     small_transpose_kernel<<<64, 256, 0, st>>>(w->Q2, NM, NM, Q2T);
     small_transpose_kernel<<<8, 256, 0, st>>>(w->Qx, NM, NH, QxT);     // (128,10) -> (10,128)
     count_launch(4);
+    // The chain dft -> d2 -> d1 -> D -> ds stays on the caller's stream; each layer's weight and bias gradients (reductions over
+    // all N rows, leaves of the backward pass) go to a branch that re-synchronises with the chain whenever its next input is ready.
     // layer 3
-    if ((rc = gemm_tn(dft, NH, ones, 1, NH, 1, N, 1.f, db3, 1, gws, gwb, st))) return rc;
-    if ((rc = gemm_tn(dft, NH, z2, NM, NH, NM, N, 1.f, dQ3, NM, gws, gwb, st))) return rc;
+    cudaStream_t sd = fork_side(st);
+    if ((rc = gemm_tn(dft, NH, ones, 1, NH, 1, N, 1.f, db3, 1, gws2, gwb2, sd))) return rc;
+    if ((rc = gemm_tn(dft, NH, z2, NM, NH, NM, N, 1.f, dQ3, NM, gws2, gwb2, sd))) return rc;
     if ((rc = gemm_nt(dft, NH, Q3T, NH, Ni, NM, NH, nullptr, 1.f, 0, d2, NM, gws, gwb, st))) return rc;
     relu_mask_bwd_kernel<<<4096, 256, 0, st>>>(d2, z2, m2, dscale, (size_t)N * NM);
     // layer 2
-    if ((rc = gemm_tn(d2, NM, ones, 1, NM, 1, N, 1.f, db2, 1, gws, gwb, st))) return rc;
-    if ((rc = gemm_tn(d2, NM, z1, NM, NM, NM, N, 1.f, dQ2, NM, gws, gwb, st))) return rc;
+    if (sd != st) sd = fork_side(st);
+    if ((rc = gemm_tn(d2, NM, ones, 1, NM, 1, N, 1.f, db2, 1, gws2, gwb2, sd))) return rc;
+    if ((rc = gemm_tn(d2, NM, z1, NM, NM, NM, N, 1.f, dQ2, NM, gws2, gwb2, sd))) return rc;
     if ((rc = gemm_nt(d2, NM, Q2T, NM, Ni, NM, NM, nullptr, 1.f, 0, d1, NM, gws, gwb, st))) return rc;
     relu_mask_bwd_kernel<<<4096, 256, 0, st>>>(d1, z1, m1, dscale, (size_t)N * NM);
     // layer 1: z = Q1 h + b1 + Qx s + bx
-    if ((rc = gemm_tn(d1, NM, h, NH, NM, NH, N, 1.f, dQ1, NH, gws, gwb, st))) return rc;
+    if (sd != st) sd = fork_side(st);
+    if ((rc = gemm_tn(d1, NM, h, NH, NM, NH, N, 1.f, dQ1, NH, gws2, gwb2, sd))) return rc;
     segment_sum_kernel<<<B, NM, 0, st>>>(d1, B, S, D);
     count_launch(3);
-    if ((rc = gemm_tn(D, NM, ones, 1, NM, 1, B, 1.f, db1, 1, gws, gwb, st))) return rc;
-    if ((rc = gemm_tn(D, NM, s, NH, NM, NH, B, 1.f, dQx, NH, gws, gwb, st))) return rc;
+    if (sd != st) sd = fork_side(st);
+    if ((rc = gemm_tn(D, NM, ones, 1, NM, 1, B, 1.f, db1, 1, gws2, gwb2, sd))) return rc;
+    if ((rc = gemm_tn(D, NM, s, NH, NM, NH, B, 1.f, dQx, NH, gws2, gwb2, sd))) return rc;
     if ((rc = gemm_nt(D, NM, QxT, NM, B, NH, NM, nullptr, 1.f, 0, ds, NH, gws, gwb, st))) return rc;
+    if (sd != st && (rc = join_side(st))) return rc;
     FIODE_CUDA(cudaGetLastError());
     return 0;
 }

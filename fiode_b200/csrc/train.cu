@@ -313,7 +313,7 @@ extern "C" int fiode_bias_grad(const float* gy, int B, int C, int inner, float* 
 
 extern "C" size_t fiode_linear_bwd_workspace_bytes(int M, int N, int K) {
     const size_t a = gemm_nt_workspace(M, K, N), b = gemm_tn_workspace(N, K, M);
-    return al256((size_t)N * K * sizeof(float)) + (a > b ? a : b) + 256;
+    return al256((size_t)N * K * sizeof(float)) + al256(a) + al256(b) + 256;      // the two products run side by side
 }
 
 // y = X Q^T + b  (X: M x K, Q: N x K)  ->  gX = gY Q (optional), gQ = gY^T X, gb = column sums of gY (optional)
@@ -323,18 +323,24 @@ extern "C" int fiode_linear_bwd(const float* X, const float* Q, const float* gY,
     if (!X || !Q || !gY || !gQ || !ws) { set_error("fiode_linear_bwd: null pointer"); return -1; }
     if (ws_bytes < fiode_linear_bwd_workspace_bytes(M, N, K)) { set_error("fiode_linear_bwd: workspace too small"); return -1; }
     float* Qt = reinterpret_cast<float*>(ws);
-    float* gws = reinterpret_cast<float*>(reinterpret_cast<char*>(ws) + al256((size_t)N * K * sizeof(float)));
-    const size_t gws_bytes = ws_bytes - al256((size_t)N * K * sizeof(float));
+    char* wp = reinterpret_cast<char*>(ws) + al256((size_t)N * K * sizeof(float));
+    const size_t a_bytes = al256(gemm_nt_workspace(M, K, N));
+    float* gws_x = reinterpret_cast<float*>(wp);
+    float* gws_q = reinterpret_cast<float*>(wp + a_bytes);
+    const size_t gws_q_bytes = ws_bytes - al256((size_t)N * K * sizeof(float)) - a_bytes;
     int rc;
+    // the weight and bias gradients (leaves of the backward pass) on a branch beside the data gradient the next layer waits for
+    cudaStream_t sd = gX ? fork_side(st) : st;
+    if ((rc = gemm_tn(gY, N, X, K, N, K, M, 1.f, gQ, K, gws_q, gws_q_bytes, sd))) return rc;
+    if (gb) {
+        bias_grad_kernel<<<N, kBiasThreads, 0, sd>>>(gY, M, N, 1, gb);
+        count_launch(1);
+    }
     if (gX) {
         transpose2d_kernel<<<dim3((K + 31) / 32, (N + 31) / 32), dim3(32, 8), 0, st>>>(Q, N, K, Qt);   // Qt: K x N
         count_launch(1);
-        if ((rc = gemm_nt(gY, N, Qt, N, M, K, N, nullptr, 1.f, 0, gX, K, gws, gws_bytes, st))) return rc;
-    }
-    if ((rc = gemm_tn(gY, N, X, K, N, K, M, 1.f, gQ, K, gws, gws_bytes, st))) return rc;
-    if (gb) {
-        bias_grad_kernel<<<N, kBiasThreads, 0, st>>>(gY, M, N, 1, gb);
-        count_launch(1);
+        if ((rc = gemm_nt(gY, N, Qt, N, M, K, N, nullptr, 1.f, 0, gX, K, gws_x, a_bytes, st))) return rc;
+        if (sd != st && (rc = join_side(st))) return rc;
     }
     FIODE_CUDA(cudaGetLastError());
     return 0;
@@ -356,18 +362,21 @@ extern "C" int fiode_conv1x1_s2d_bwd(const float* x, const float* Q, const float
     if (!x || !Q || !gy || !gQ || !ws || (n & 1)) { set_error("fiode_conv1x1_s2d_bwd: bad args"); return -1; }
     if (ws_bytes < fiode_conv1x1_s2d_bwd_workspace_bytes(B, cin, cout, n)) { set_error("fiode_conv1x1_s2d_bwd: workspace too small"); return -1; }
     const int P = (n / 2) * (n / 2), cin4 = 4 * cin;
+    cudaStream_t sd = gx ? fork_side(st) : st;      // weight + bias gradients beside the data gradient
+    const int splits = conv1x1_splits(B), bps = (B + splits - 1) / splits;
+    float* part = reinterpret_cast<float*>(ws);
+    conv1x1_bwd_weight_kernel<<<dim3((cin4 + 31) / 32, (cout + 31) / 32, splits), 256, 0, sd>>>(x, gy, B, cin, cout, n, bps, part);
+    sum_partials_kernel<<<nblocks(((size_t)cout * cin4 + 31) / 32 * 256), 256, 0, sd>>>(part, splits, (size_t)cout * cin4, gQ);
+    count_launch(2);
+    if (gb) {
+        bias_grad_kernel<<<cout, kBiasThreads, 0, sd>>>(gy, B, cout, P, gb);
+        count_launch(1);
+    }
     if (gx) {
         conv1x1_bwd_data_kernel<<<nblocks((size_t)B * cin * P), 256, 0, st>>>(Q, gy, B, cin, cout, n, gx);
         count_launch(1);
-    }
-    const int splits = conv1x1_splits(B), bps = (B + splits - 1) / splits;
-    float* part = reinterpret_cast<float*>(ws);
-    conv1x1_bwd_weight_kernel<<<dim3((cin4 + 31) / 32, (cout + 31) / 32, splits), 256, 0, st>>>(x, gy, B, cin, cout, n, bps, part);
-    sum_partials_kernel<<<nblocks(((size_t)cout * cin4 + 31) / 32 * 256), 256, 0, st>>>(part, splits, (size_t)cout * cin4, gQ);
-    count_launch(2);
-    if (gb) {
-        bias_grad_kernel<<<cout, kBiasThreads, 0, st>>>(gy, B, cout, P, gb);
-        count_launch(1);
+        int rc;
+        if (sd != st && (rc = join_side(st))) return rc;
     }
     FIODE_CUDA(cudaGetLastError());
     return 0;
@@ -389,9 +398,17 @@ extern "C" int fiode_cayley_conv_layer_bwd(const float* x, const float* Qf, cons
     float2* GYf = Xf + (size_t)B * cin * F;
     float2* GXf = GYf + (size_t)B * cout * F;
     int rc;
-    if ((rc = launch_rfft2(x, B * cin, cin, n, nullptr, nullptr, Xf, st, false))) return rc;
+    // branch: the input's spectrum, then the weight and bias gradients; the caller's stream: the incoming gradient's spectrum,
+    // then the data gradient the previous layer waits for
+    cudaStream_t sd = fork_side(st);
+    if ((rc = launch_rfft2(x, B * cin, cin, n, nullptr, nullptr, Xf, sd, false))) return rc;
+    if (gb) {
+        bias_grad_kernel<<<cout, kBiasThreads, 0, sd>>>(gy, B, cout, n * n, gb);
+        count_launch(1);
+    }
     if ((rc = launch_rfft2(gy, B * cout, cout, n, nullptr, nullptr, GYf, st, false))) return rc;
-    conv_bwd_weight_kernel<<<nblocks((size_t)((cout + 1) / 2) * ((cin + 1) / 2) * F), 256, 0, st>>>(GYf, Xf, B, cin, cout, n,
+    if (sd != st) sd = fork_side(st);                 // the branch waits for GYf
+    conv_bwd_weight_kernel<<<nblocks((size_t)((cout + 1) / 2) * ((cin + 1) / 2) * F), 256, 0, sd>>>(GYf, Xf, B, cin, cout, n,
                                                                                                  reinterpret_cast<float2*>(gQf));
     count_launch(1);
     if (gx) {
@@ -408,10 +425,7 @@ extern "C" int fiode_cayley_conv_layer_bwd(const float* x, const float* Qf, cons
         }
         if ((rc = launch_irfft2(GXf, Bv, Cv, n, nullptr, 0, gx, st, false))) return rc;
     }
-    if (gb) {
-        bias_grad_kernel<<<cout, kBiasThreads, 0, st>>>(gy, B, cout, n * n, gb);
-        count_launch(1);
-    }
+    if (sd != st && (rc = join_side(st))) return rc;
     FIODE_CUDA(cudaGetLastError());
     return 0;
 }
