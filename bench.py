@@ -289,8 +289,9 @@ def fi_step_bench(device, pk, world, iters=10, warm=8):
                 grad_floats=reducer.numel, allreduce_bytes=4 * reducer.numel,
                 algorithmic_tflops=flop / (ms * 1e-3) / 1e12, loss=float(step().detach()),
                 **({} if graphed else {'graph_error': locals().get('graph_error')}),
-                note='forward + backward to all 33 parameters + one flat all-reduce; kernels are the first correct versions '
-                     '(FFMA GEMMs, per-layer launches), not yet tuned')
+                note='forward + backward to all 33 parameters + one flat all-reduce, replayed from a CUDA graph; the Cayley '
+                     'transforms of all layers are prepared up front on side streams (layers.prefetch_orthogonal), weight gradients '
+                     'run on a branch beside the data gradients; FFMA GEMMs (gradients are not fp16-range safe for the split)')
 
 
 # per image: algorithmic HBM bytes (fp32 activations in + out; spectra complex64) and flops of each backbone stage

@@ -318,83 +318,116 @@ __global__ void __launch_bounds__(256) gj_block_update_kernel(const float* __res
         }
 }
 
-// The same blocked Gauss-Jordan with 32 x 32 pivot blocks and ONE launch per block step.  A 32 x 32 block is inverted by a single
-// warp in registers (lane = column, the 32 pivots fully unrolled: the pivot row is the lane's own register, the multipliers come
-// by shuffle -- no shared memory, no barrier), so every CTA (ib, jb) simply inverts D = X_kk itself, forms
-// T = D^-1 X_kj (or D^-1 when jb = k) and writes its own block: Y_kj = T for the pivot row, Y_ij = X_ij - X_ik T elsewhere
-// (X_ij read as 0 when jb = k).  n = 512: 16 launches of ~15 us instead of 8 x (27 us panel + 10 us update).
-constexpr int GB2 = 32;
-__global__ void __launch_bounds__(256) gj_block32_step_kernel(const float* __restrict__ X, float* __restrict__ Y, int n, int kb) {
-    __shared__ float Ds[GB2][GB2 + 1];
-    __shared__ float Ps[GB2][GB2 + 1];
-    __shared__ float Ls[GB2][GB2 + 1];
-    __shared__ float Ts[GB2][GB2 + 1];
-    const int t = threadIdx.x, jb = blockIdx.x, ib = blockIdx.y, w = t >> 5, l = t & 31;
-    for (int e = t; e < GB2 * GB2; e += 256) {
-        const int i = e >> 5, j = e & 31;
-        Ds[i][j] = X[(size_t)(kb * GB2 + i) * n + kb * GB2 + j];
-        Ps[i][j] = X[(size_t)(kb * GB2 + i) * n + jb * GB2 + j];
-        if (ib != kb) Ls[i][j] = X[(size_t)(ib * GB2 + i) * n + kb * GB2 + j];
+// The panel and the update kernel above as ONE launch per block step: CTA (ib, jb) inverts D = X_kk itself (every CTA does, in
+// parallel: the inversion is a latency chain, not work), forms T = D^-1 X_kj in registers and then writes its own block --
+// T for the pivot row, X_ij - X_ik T elsewhere -- without the round trip of block row k through global memory and the second
+// launch.  Per element the same operations in the same order as panel + update: bit-identical results.
+constexpr size_t kGjStepSmem = (size_t)(2 * GB * GB + GB * (GB + 1) + 2 * GB) * sizeof(float);
+__global__ void __launch_bounds__(256) gj_block_step_kernel(const float* __restrict__ X, float* __restrict__ Y, int n, int kb) {
+    extern __shared__ __align__(16) float gj_sm[];
+    float* D0 = gj_sm;                       // D, then D^-1
+    float* P = D0 + GB * GB;                 // X_kj, then T = D^-1 X_kj
+    float* Ls = P + GB * GB;                 // X_ik, row stride GB + 1
+    float* prow = Ls + GB * (GB + 1);        // two 64-float lines
+    const int t = threadIdx.x, jb = blockIdx.x, ib = blockIdx.y;
+    for (int e = t; e < GB * GB; e += 256) {
+        const int i = e / GB, j = e - i * GB;
+        D0[e] = X[(size_t)(kb * GB + i) * n + kb * GB + j];
+        P[e] = X[(size_t)(kb * GB + i) * n + jb * GB + j];
+        if (ib != kb) Ls[i * (GB + 1) + j] = X[(size_t)(ib * GB + i) * n + kb * GB + j];
     }
     __syncthreads();
-    if (w == 0) {
-        float v[GB2];
+    const int w = t >> 5, l = t & 31;
+    float v0[GB / 8], v1[GB / 8];
 #pragma unroll
-        for (int i = 0; i < GB2; ++i) v[i] = Ds[i][l];
+    for (int a = 0; a < GB / 8; ++a) { v0[a] = D0[(w + 8 * a) * GB + l]; v1[a] = D0[(w + 8 * a) * GB + l + 32]; }
 #pragma unroll
-        for (int k = 0; k < GB2; ++k) {
-            const float ip = 1.f / __shfl_sync(0xffffffffu, v[k], k);
-            const float pk = v[k] * ip;
-            float f[GB2];                                  // column k (M[i][k] before this pivot touches it): all 31 shuffles first,
-#pragma unroll                                             // so that their latencies overlap instead of chaining through one register
-            for (int i = 0; i < GB2; ++i) f[i] = (i == k) ? 0.f : __shfl_sync(0xffffffffu, v[i], k);
+    for (int ka = 0; ka < GB / 8; ++ka) {
+        for (int kk = 0; kk < 8; ++kk) {
+            const int k = 8 * ka + kk;
+            float* pr = prow + (k & 1) * GB;
+            if (w == kk) { pr[l] = v0[ka]; pr[l + 32] = v1[ka]; }
+            __syncthreads();
+            const float ip = 1.f / pr[k];
+            const float pk0 = pr[l] * ip, pk1 = pr[l + 32] * ip;
 #pragma unroll
-            for (int i = 0; i < GB2; ++i) {
-                if (i == k) continue;
-                v[i] = (l == k) ? -f[i] * ip : fmaf(-f[i], pk, v[i]);
+            for (int a = 0; a < GB / 8; ++a) {
+                const int i = w + 8 * a;
+                const float f = __shfl_sync(0xffffffffu, ka < 4 ? v0[a] : v1[a], k & 31);
+                float r0, r1;
+                if (i == k) { r0 = (l == k) ? ip : pk0; r1 = (l + 32 == k) ? ip : pk1; }
+                else {
+                    r0 = (l == k) ? -f * ip : fmaf(-f, pk0, v0[a]);
+                    r1 = (l + 32 == k) ? -f * ip : fmaf(-f, pk1, v1[a]);
+                }
+                v0[a] = r0; v1[a] = r1;
             }
-            v[k] = (l == k) ? ip : pk;
         }
-#pragma unroll
-        for (int i = 0; i < GB2; ++i) Ds[i][l] = v[i];
     }
     __syncthreads();
-    const int r = t >> 3, c0 = 4 * (t & 7);              // thread = one row, four consecutive columns of the 32 x 32 block
-    float acc[4];
+#pragma unroll
+    for (int a = 0; a < GB / 8; ++a) { D0[(w + 8 * a) * GB + l] = v0[a]; D0[(w + 8 * a) * GB + l + 32] = v1[a]; }
+    __syncthreads();
+    const int tx = t & 15, ty = t >> 4;                // thread tile 4 x 4: rows ty + 16 a, columns tx + 16 b
+    float acc[4][4];
     if (jb == kb) {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) acc[q] = Ds[r][c0 + q];
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = D0[(ty + 16 * a) * GB + tx + 16 * b];
     } else {
 #pragma unroll
-        for (int q = 0; q < 4; ++q) acc[q] = 0.f;
-#pragma unroll 8
-        for (int m = 0; m < GB2; ++m) {
-            const float d = Ds[r][m];
+        for (int a = 0; a < 4; ++a)
 #pragma unroll
-            for (int q = 0; q < 4; ++q) acc[q] = fmaf(d, Ps[m][c0 + q], acc[q]);
+            for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+#pragma unroll 4
+        for (int r = 0; r < GB; ++r) {
+            float dl[4], pq[4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) { dl[a] = D0[(ty + 16 * a) * GB + r]; pq[a] = P[r * GB + tx + 16 * a]; }
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(dl[a], pq[b], acc[a][b]);
         }
     }
-    if (ib == kb) {
-        *reinterpret_cast<float4*>(Y + (size_t)(kb * GB2 + r) * n + jb * GB2 + c0) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+    if (ib == kb) {                                    // pivot block row: Y_kj = T (D^-1 itself when jb = k)
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) Y[(size_t)(kb * GB + ty + 16 * a) * n + jb * GB + tx + 16 * b] = acc[a][b];
         return;
     }
+    __syncthreads();                                   // everyone has read P
 #pragma unroll
-    for (int q = 0; q < 4; ++q) Ts[r][c0 + q] = acc[q];
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) P[(ty + 16 * a) * GB + tx + 16 * b] = acc[a][b];
     __syncthreads();
-    float a2[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 8
-    for (int m = 0; m < GB2; ++m) {
-        const float lv = Ls[r][m];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) a2[q] = fmaf(lv, Ts[m][c0 + q], a2[q]);
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+#pragma unroll 4
+    for (int r = 0; r < GB; ++r) {
+        float lv[4], q[4];
+#pragma unroll
+        for (int a = 0; a < 4; ++a) { lv[a] = Ls[(ty + 16 * a) * (GB + 1) + r]; q[a] = P[r * GB + tx + 16 * a]; }
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(lv[a], q[b], acc[a][b]);
     }
-    const size_t o = (size_t)(ib * GB2 + r) * n + jb * GB2 + c0;
-    float4 x4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (jb != kb) x4 = *reinterpret_cast<const float4*>(X + o);
-    *reinterpret_cast<float4*>(Y + o) = make_float4(x4.x - a2[0], x4.y - a2[1], x4.z - a2[2], x4.w - a2[3]);
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+            const size_t o = (size_t)(ib * GB + ty + 16 * a) * n + jb * GB + tx + 16 * b;
+            Y[o] = (jb == kb ? 0.f : X[o]) - acc[a][b];
+        }
 }
-static int gj_block_size() {
-    static const int v = [] { const char* e = getenv("FIODE_GJ_BLOCK"); return (e && atoi(e) == 64) ? 64 : 32; }();
+static bool gj_fused_step() {
+    static const bool v = [] { const char* e = getenv("FIODE_GJ_FUSED"); return !(e && e[0] == '0'); }();
     return v;
 }
 
@@ -405,11 +438,14 @@ static int gj_inverse(float* X, float* Y, int n, float** result, cudaStream_t st
         *result = Y;
         return 0;
     }
-    if (n % GB2 == 0 && gj_block_size() == 32) {
-        const int nb = n / GB2;
+    if (n % GB == 0 && gj_fused_step()) {
+        static std::atomic<bool> attr[kMaxDevices];
+        if (first_use_on_device(attr))
+            FIODE_CUDA(cudaFuncSetAttribute(gj_block_step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGjStepSmem));
+        const int nb = n / GB;
         float *in = X, *out = Y;
         for (int kb = 0; kb < nb; ++kb) {
-            gj_block32_step_kernel<<<dim3(nb, nb), 256, 0, st>>>(in, out, n, kb);
+            gj_block_step_kernel<<<dim3(nb, nb), 256, kGjStepSmem, st>>>(in, out, n, kb);
             float* tmp = in; in = out; out = tmp;
         }
         count_launch(nb);
