@@ -23,6 +23,8 @@ namespace fiode {
 
 int gemm_nt(const float* A, int lda, const float* Bm, int ldb, int M, int N, int K, const float* bias, float alpha,
             int group_sort, float* y, int ldy, float* ws, size_t ws_bytes, cudaStream_t st);
+int gemm_nt_tall(const float* A, int lda, const float* Bm, int ldb, int M, int N, int K, float alpha, float* y, int ldy,
+                 float* ws, size_t ws_bytes, cudaStream_t st);
 size_t gemm_nt_workspace(int M, int N, int K);
 
 // ---- Frobenius norm, deterministic two-stage --------------------------------------------------
@@ -859,7 +861,7 @@ __global__ void conv_alpha_finalize_kernel(const double* __restrict__ part, int 
 
 // One CTA per frequency: Q[phi] = cayley(alpha * wfft[phi] / ||wfft||).  cout >= cin.
 // smem (float2): Wf[cout][cin], X[cin][cin], Y[cin][cin], A[cin][cin]
-__global__ void __launch_bounds__(256) cayley_conv_kernel(const float* __restrict__ w, const float* __restrict__ alpha,
+__global__ void __launch_bounds__(1024) cayley_conv_kernel(const float* __restrict__ w, const float* __restrict__ alpha,
                                                           const double* __restrict__ part, int F, int cout, int cin,
                                                           int k, int n, float2* __restrict__ Qf) {
     extern __shared__ float4 smem4[];
@@ -868,6 +870,7 @@ __global__ void __launch_bounds__(256) cayley_conv_kernel(const float* __restric
     float2* Y = X + cin * cin;
     float2* A = Y + cin * cin;
     __shared__ float sc_sh;
+    const int nt = blockDim.x;   // 128 ... 1024 threads: one frequency per CTA, its matrix elements spread over the threads
     const int t = threadIdx.x, phi = blockIdx.x, H = n / 2 + 1, u = phi / H, v = phi - u * H;
     if (t < 32) {                               // the F per-frequency partials, by one warp (a single thread walking them
         double s = 0;                           // cost every CTA ~8 us before it could start)
@@ -877,14 +880,14 @@ __global__ void __launch_bounds__(256) cayley_conv_kernel(const float* __restric
     }
     __syncthreads();
     const float sc = sc_sh;
-    for (int e = t; e < cout * cin; e += 256) {
+    for (int e = t; e < cout * cin; e += nt) {
         const float2 z = conv_spectrum_at(w + (size_t)e * k * k, k, n, u, v);
         Wf[e] = make_float2(sc * z.x, sc * z.y);
     }
     __syncthreads();
     const int nv = cout - cin;
     // A = U - U^H + V^H V ; X = I + A
-    for (int e = t; e < cin * cin; e += 256) {
+    for (int e = t; e < cin * cin; e += nt) {
         const int i = e / cin, j = e - i * cin;
         const float2 uij = Wf[i * cin + j], uji = Wf[j * cin + i];
         float2 g = make_float2(0.f, 0.f);
@@ -901,7 +904,7 @@ __global__ void __launch_bounds__(256) cayley_conv_kernel(const float* __restric
         const float2 p = in[kk * cin + kk];
         const float den = 1.f / (p.x * p.x + p.y * p.y);
         const float2 ip = make_float2(p.x * den, -p.y * den);
-        for (int e = t; e < cin * cin; e += 256) {
+        for (int e = t; e < cin * cin; e += nt) {
             const int i = e / cin, j = e - i * cin;
             float2 r;
             if (i == kk) r = (j == kk) ? ip : cmul(in[e], ip);
@@ -917,7 +920,7 @@ __global__ void __launch_bounds__(256) cayley_conv_kernel(const float* __restric
     const float2* M = (cin & 1) ? Y : X;
     float2* dst = Qf + (size_t)phi * cout * cin;
     // top: M (I - A) ; bottom: -2 V M
-    for (int e = t; e < cout * cin; e += 256) {
+    for (int e = t; e < cout * cin; e += nt) {
         const int i = e / cin, j = e - i * cin;
         float2 acc = make_float2(0.f, 0.f);
         if (i < cin) {
@@ -1127,7 +1130,7 @@ int cayley_linear_bwd_impl(const float* W, const float* alpha, int cout, int cin
     cudaStream_t sd = st;
     if (has_v) {
         sd = fork_side(st);
-        if ((rc = gemm_nt(G2, n, M, n, R - n, n, n, nullptr, -2.f, 0, gV1, n, gws2, gws2_bytes, sd))) return rc;
+        if ((rc = gemm_nt_tall(G2, n, M, n, R - n, n, n, -2.f, gV1, n, gws2, gws2_bytes, sd))) return rc;
     }
     if (has_v && (rc = gemm_nt(Vt, R - n, Gt2, R - n, n, n, R - n, nullptr, 1.f, 0, P, n, gws, gws_bytes, st))) return rc;
     cayley_bwd_gm_kernel<<<nb, 256, 0, st>>>(G, P, n * n, has_v, gM);
@@ -1137,7 +1140,7 @@ int cayley_linear_bwd_impl(const float* W, const float* alpha, int cout, int cin
     cayley_bwd_sym_kernel<<<nb, 256, 0, st>>>(gAt, n, S, gU);
     count_launch(1);
     if (has_v) {
-        if ((rc = gemm_nt(V, n, S, n, R - n, n, n, nullptr, 1.f, 0, gV2, n, gws, gws_bytes, st))) return rc;     // V (gA + gA^T)
+        if ((rc = gemm_nt_tall(V, n, S, n, R - n, n, n, 1.f, gV2, n, gws, gws_bytes, st))) return rc;     // V (gA + gA^T)
         if (sd != st && (rc = join_side(st))) return rc;
     }
     if (tr) cayley_bwd_assemble_tr_kernel<<<kNormBlocks, 1024, 0, st>>>(gU, gV1, gV2, W, R, n, gWn, part);
@@ -1151,7 +1154,7 @@ int cayley_linear_bwd_impl(const float* W, const float* alpha, int cout, int cin
 
 // ---- convolution (k > 1): one CTA per frequency, everything in shared memory ---------------------------
 // Writes gWn[phi] (cout x cin complex, gradient w.r.t. the scaled spectrum sc * wfft) and dotp[phi] = Re <gWn[phi], wfft[phi]>.
-__global__ void __launch_bounds__(256) cayley_conv_bwd_kernel(const float* __restrict__ w, const float* __restrict__ alpha,
+__global__ void __launch_bounds__(1024) cayley_conv_bwd_kernel(const float* __restrict__ w, const float* __restrict__ alpha,
                                                               const double* __restrict__ part, int F, int cout, int cin,
                                                               int k, int n, const float2* __restrict__ gQf,
                                                               float2* __restrict__ gWn, double* __restrict__ dotp) {
@@ -1164,7 +1167,8 @@ __global__ void __launch_bounds__(256) cayley_conv_bwd_kernel(const float* __res
     float2* T = gM + cin * cin;
     float2* gA = T + cin * cin;
     __shared__ float sc_sh;
-    __shared__ double red[8];
+    __shared__ double red[32];
+    const int nt = blockDim.x;   // 128 ... 1024 threads: one frequency per CTA, its matrix elements spread over the threads
     const int t = threadIdx.x, phi = blockIdx.x, H = n / 2 + 1, u = phi / H, v = phi - u * H;
     if (t < 32) {                               // the F per-frequency partials, by one warp (a single thread walking them
         double s = 0;                           // cost every CTA ~8 us before it could start)
@@ -1175,14 +1179,14 @@ __global__ void __launch_bounds__(256) cayley_conv_bwd_kernel(const float* __res
     __syncthreads();
     const float sc = sc_sh;
     const float2* gsrc = gQf + (size_t)phi * cout * cin;
-    for (int e = t; e < cout * cin; e += 256) {
+    for (int e = t; e < cout * cin; e += nt) {
         const float2 z = conv_spectrum_at(w + (size_t)e * k * k, k, n, u, v);
         Wf[e] = make_float2(sc * z.x, sc * z.y);
         Gq[e] = gsrc[e];
     }
     __syncthreads();
     const int nv = cout - cin;
-    for (int e = t; e < cin * cin; e += 256) {
+    for (int e = t; e < cin * cin; e += nt) {
         const int i = e / cin, j = e - i * cin;
         const float2 uij = Wf[i * cin + j], uji = Wf[j * cin + i];
         float2 g = make_float2(0.f, 0.f);
@@ -1196,7 +1200,7 @@ __global__ void __launch_bounds__(256) cayley_conv_bwd_kernel(const float* __res
         const float2 pv = in[kk * cin + kk];
         const float den = 1.f / (pv.x * pv.x + pv.y * pv.y);
         const float2 ip = make_float2(pv.x * den, -pv.y * den);
-        for (int e = t; e < cin * cin; e += 256) {
+        for (int e = t; e < cin * cin; e += nt) {
             const int i = e / cin, j = e - i * cin;
             float2 r;
             if (i == kk) r = (j == kk) ? ip : cmul(in[e], ip);
@@ -1213,7 +1217,7 @@ __global__ void __launch_bounds__(256) cayley_conv_bwd_kernel(const float* __res
     const float2* V = Wf + cin * cin;
     const float2* G2 = Gq + cin * cin;
     // gM = 2 G1 - 2 V^H G2
-    for (int e = t; e < cin * cin; e += 256) {
+    for (int e = t; e < cin * cin; e += nt) {
         const int i = e / cin, j = e - i * cin;
         float2 acc = make_float2(0.f, 0.f);
         for (int r = 0; r < nv; ++r) cfma(acc, cconj(V[r * cin + i]), G2[r * cin + j]);
@@ -1221,7 +1225,7 @@ __global__ void __launch_bounds__(256) cayley_conv_bwd_kernel(const float* __res
     }
     __syncthreads();
     // T = gM M^H
-    for (int e = t; e < cin * cin; e += 256) {
+    for (int e = t; e < cin * cin; e += nt) {
         const int i = e / cin, j = e - i * cin;
         float2 acc = make_float2(0.f, 0.f);
         for (int r = 0; r < cin; ++r) cfma(acc, gM[i * cin + r], cconj(M[j * cin + r]));
@@ -1229,7 +1233,7 @@ __global__ void __launch_bounds__(256) cayley_conv_bwd_kernel(const float* __res
     }
     __syncthreads();
     // gA = -M^H T
-    for (int e = t; e < cin * cin; e += 256) {
+    for (int e = t; e < cin * cin; e += nt) {
         const int i = e / cin, j = e - i * cin;
         float2 acc = make_float2(0.f, 0.f);
         for (int r = 0; r < cin; ++r) cfma(acc, cconj(M[r * cin + i]), T[r * cin + j]);
@@ -1240,7 +1244,7 @@ __global__ void __launch_bounds__(256) cayley_conv_bwd_kernel(const float* __res
     double dacc = 0;
     float2* dst = gWn + (size_t)phi * cout * cin;
     const float inv_sc = 1.f / sc;
-    for (int e = t; e < cout * cin; e += 256) {
+    for (int e = t; e < cout * cin; e += nt) {
         const int i = e / cin, j = e - i * cin;
         float2 g;
         if (i < cin) {
@@ -1264,7 +1268,7 @@ __global__ void __launch_bounds__(256) cayley_conv_bwd_kernel(const float* __res
     __syncthreads();
     if (t == 0) {
         double s = 0;
-        for (int i = 0; i < 8; ++i) s += red[i];
+        for (int i = 0; i < nt / 32; ++i) s += red[i];
         dotp[phi] = s;
     }
 }
@@ -1346,6 +1350,12 @@ extern "C" int fiode_conv_alpha_init(const float* w, int cout, int cin, int k, i
     return 0;
 }
 
+// threads per frequency CTA of the two kernels above: the 64 x 64 layer's CTA fills an SM's shared memory (seven complex
+// matrices), so how long it sits there decides how long every other kernel of the step is kept off that SM
+static int conv_cayley_threads(int cout, int cin) {
+    const int e = cout * cin;
+    return e >= 4096 ? 1024 : e >= 1024 ? 512 : e >= 256 ? 256 : 128;
+}
 extern "C" size_t fiode_cayley_conv_workspace_bytes(int cout, int cin, int k, int n) {
     if (k == 1) return cayley_linear_ws(cout, cin);
     return conv_part_bytes(n);
@@ -1366,7 +1376,7 @@ extern "C" int fiode_cayley_conv(const float* w, const float* alpha, int cout, i
     if (smem > 200 * 1024) { set_error("fiode_cayley_conv: layer too large for the in-smem solver"); return -1; }
     FIODE_CUDA(cudaFuncSetAttribute(cayley_conv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     conv_spectrum_sumsq_kernel<<<F, 256, 0, st>>>(w, cout, cin, k, n, (double*)ws);
-    cayley_conv_kernel<<<F, 256, smem, st>>>(w, alpha, (const double*)ws, F, cout, cin, k, n,
+    cayley_conv_kernel<<<F, conv_cayley_threads(cout, cin), smem, st>>>(w, alpha, (const double*)ws, F, cout, cin, k, n,
                                              reinterpret_cast<float2*>(Qf));
     FIODE_CUDA(cudaGetLastError());
     count_launch(2);
@@ -1412,7 +1422,7 @@ extern "C" int fiode_cayley_conv_bwd(const float* w, const float* alpha, int cou
     if (smem > 200 * 1024) { set_error("fiode_cayley_conv_bwd: layer too large for the in-smem solver"); return -1; }
     FIODE_CUDA(cudaFuncSetAttribute(cayley_conv_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     conv_spectrum_sumsq_kernel<<<F, 256, 0, st>>>(w, cout, cin, k, n, part);
-    cayley_conv_bwd_kernel<<<F, 256, smem, st>>>(w, alpha, part, F, cout, cin, k, n, reinterpret_cast<const float2*>(gQf), gWn, dotp);
+    cayley_conv_bwd_kernel<<<F, conv_cayley_threads(cout, cin), smem, st>>>(w, alpha, part, F, cout, cin, k, n, reinterpret_cast<const float2*>(gQf), gWn, dotp);
     cayley_conv_bwd_taps_kernel<<<cout * cin, 128, 0, st>>>(w, alpha, part, dotp, F, cout, cin, k, n, gWn, gw, galpha);
     FIODE_CUDA(cudaGetLastError());
     count_launch(3);

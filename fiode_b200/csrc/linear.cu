@@ -154,9 +154,23 @@ size_t gemm_nt_workspace(int M, int N, int K) {
 }
 
 // C = alpha * A B^T (+bias) (+GroupSort), deterministic split-K sized to fill the GPU
+static int gemm_nt_impl(const float* A, int lda, const float* Bm, int ldb, int M, int N, int K, const float* bias, float alpha,
+                        int group_sort, float* y, int ldy, float* ws, size_t ws_bytes, cudaStream_t st, int splits);
 int gemm_nt(const float* A, int lda, const float* Bm, int ldb, int M, int N, int K, const float* bias, float alpha,
             int group_sort, float* y, int ldy, float* ws, size_t ws_bytes, cudaStream_t st) {
-    int splits = gemm_splits(M, N, K);
+    return gemm_nt_impl(A, lda, Bm, ldb, M, N, K, bias, alpha, group_sort, y, ldy, ws, ws_bytes, st, gemm_splits(M, N, K));
+}
+// The same product for the adjoints' tall operands (3584 x 512 x 512: 448 tiles of 64 x 64, three per SM): one pass over K that
+// writes y directly instead of two K halves plus the reduction launch that re-reads both (18 of 90 us).  Not used on the forward
+// path: summing K in one chain instead of two halves changes the last bits of Q.
+int gemm_nt_tall(const float* A, int lda, const float* Bm, int ldb, int M, int N, int K, float alpha, float* y, int ldy,
+                 float* ws, size_t ws_bytes, cudaStream_t st) {
+    const int tiles = ((M + GT - 1) / GT) * ((N + GT - 1) / GT);
+    const int splits = tiles >= 2 * sm_count() ? 1 : gemm_splits(M, N, K);
+    return gemm_nt_impl(A, lda, Bm, ldb, M, N, K, nullptr, alpha, 0, y, ldy, ws, ws_bytes, st, splits);
+}
+static int gemm_nt_impl(const float* A, int lda, const float* Bm, int ldb, int M, int N, int K, const float* bias, float alpha,
+                        int group_sort, float* y, int ldy, float* ws, size_t ws_bytes, cudaStream_t st, int splits) {
     if ((size_t)splits * M * N * sizeof(float) > ws_bytes) { set_error("gemm_nt: workspace too small"); return -1; }
     int kps = (K + splits - 1) / splits;
     kps = (kps + GK - 1) / GK * GK;
