@@ -50,6 +50,7 @@ SIGNATURES = {
     'fiode_version': (I, []),
     'fiode_launch_count': (LL, []),
     'fiode_reset_launch_count': (None, []),
+    'fiode_set_side_streams': (None, [I]),
     'fiode_cayley_linear_workspace_bytes': (SZ, [I, I]),
     'fiode_cayley_linear': (I, [P, P, I, I, P, P, SZ, P]),
     'fiode_conv_alpha_init': (I, [P, I, I, I, I, P, P, SZ, P]),

@@ -45,9 +45,15 @@ constexpr int kSideSlots = 8;          // callers on different streams mostly ge
 struct SideSlot { cudaStream_t s = nullptr; cudaEvent_t fork = nullptr, join = nullptr; };
 static SideSlot g_side[kMaxDevices][kSideSlots];
 static std::mutex g_side_mu;
+static std::atomic<int> g_fork{-1};     // -1: take FIODE_FORK on first use
 static bool fork_enabled() {
-    static const bool on = [] { const char* e = getenv("FIODE_FORK"); return !(e && e[0] == '0'); }();
-    return on;
+    int v = g_fork.load(std::memory_order_relaxed);
+    if (v < 0) {
+        const char* e = getenv("FIODE_FORK");
+        v = !(e && e[0] == '0');
+        g_fork.store(v, std::memory_order_relaxed);
+    }
+    return v != 0;
 }
 static SideSlot* side_slot(cudaStream_t st) {
     const int dev = current_device();
@@ -88,3 +94,4 @@ extern "C" const char* fiode_last_error(void) { return fiode::g_err; }
 extern "C" int fiode_version(void) { return 100; }
 extern "C" long long fiode_launch_count(void) { return fiode::g_launches.load(); }
 extern "C" void fiode_reset_launch_count(void) { fiode::g_launches.store(0); }
+extern "C" void fiode_set_side_streams(int on) { fiode::g_fork.store(on ? 1 : 0); }

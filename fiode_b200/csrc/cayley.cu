@@ -26,6 +26,7 @@ int gemm_nt(const float* A, int lda, const float* Bm, int ldb, int M, int N, int
 int gemm_nt_tall(const float* A, int lda, const float* Bm, int ldb, int M, int N, int K, float alpha, float* y, int ldy,
                  float* ws, size_t ws_bytes, cudaStream_t st);
 size_t gemm_nt_workspace(int M, int N, int K);
+int gemm_nt_gram(const float* A, int lda, int n, int K, float* y, int ldy, float* ws, size_t ws_bytes, cudaStream_t st);
 
 // ---- Frobenius norm, deterministic two-stage --------------------------------------------------
 constexpr int kNormBlocks = 128;
@@ -791,7 +792,7 @@ int cayley_linear_impl(const float* W, const float* alpha, int cout, int cin, fl
     count_launch(3);
     int rc;
     const int has_v = R > n;
-    if (has_v && (rc = gemm_nt(Vt, R - n, Vt, R - n, n, n, R - n, nullptr, 1.f, 0, G, n, gws, gws_bytes, st))) return rc;
+    if (has_v && (rc = gemm_nt_gram(Vt, R - n, n, R - n, G, n, gws, gws_bytes, st))) return rc;
     cayley_prep2_kernel<<<(n * n + 255) / 256, 256, 0, st>>>(Ws, G, n, has_v, X, ImAT);
     count_launch(1);
     float* M = nullptr;

@@ -12,6 +12,7 @@
 #include "common.cuh"
 #include "gemm_tc.cuh"
 #include <cuda_pipeline.h>
+#include <cstdlib>
 
 namespace fiode {
 
@@ -27,6 +28,11 @@ __global__ void __launch_bounds__(GTHREADS) gemm_nt_kernel(const float* __restri
     __shared__ __align__(16) float Bs[2][GT * GS];
     const int t = threadIdx.x;
     const int m0 = blockIdx.y * GT, n0 = blockIdx.x * GT;
+    // bit 1 of vec_ok: the product is a Gram matrix (A == B, M == N): only the tiles on and above the diagonal are computed,
+    // the rest is their mirror image -- exact, because sum_k a_ik a_jk runs over the same products in the same order
+    const bool sym = (vec_ok & 2) != 0;
+    vec_ok &= 1;
+    if (sym && n0 < m0) return;
     const int k_begin = blockIdx.z * k_per_split, k_end = min(K, k_begin + k_per_split);
     const int tn = t & 15, tm = t >> 4;
     float acc[8][4];
@@ -93,7 +99,10 @@ __global__ void __launch_bounds__(GTHREADS) gemm_nt_kernel(const float* __restri
             const int n = n0 + tn + 16 * j;
             if (n < N) {
                 if (DIRECT) part[(size_t)m * ldy + n] = alpha * acc[i][j] + (bias ? bias[n] : 0.f);
-                else dst[(size_t)m * N + n] = acc[i][j];
+                else {
+                    dst[(size_t)m * N + n] = acc[i][j];
+                    if (sym && n0 > m0) dst[(size_t)n * N + m] = acc[i][j];
+                }
             }
         }
     }
@@ -169,8 +178,17 @@ int gemm_nt_tall(const float* A, int lda, const float* Bm, int ldb, int M, int N
     const int splits = tiles >= 2 * sm_count() ? 1 : gemm_splits(M, N, K);
     return gemm_nt_impl(A, lda, Bm, ldb, M, N, K, nullptr, alpha, 0, y, ldy, ws, ws_bytes, st, splits);
 }
+// G = A A^T (n x n, the V^T V of the Cayley transform): same split-K partials and reduction as gemm_nt(A, A), bit for bit, with the
+// tiles below the diagonal mirrored instead of computed
+int gemm_nt_gram(const float* A, int lda, int n, int K, float* y, int ldy, float* ws, size_t ws_bytes, cudaStream_t st) {
+    static const bool off = [] { const char* e = getenv("FIODE_GRAM"); return e && e[0] == '0'; }();   // A/B: the plain product
+    const int splits = gemm_splits(n, n, K);
+    return gemm_nt_impl(A, lda, A, lda, n, n, K, nullptr, 1.f, 0, y, ldy, ws, ws_bytes, st, (splits == 1 || off) ? splits : -splits);
+}
 static int gemm_nt_impl(const float* A, int lda, const float* Bm, int ldb, int M, int N, int K, const float* bias, float alpha,
                         int group_sort, float* y, int ldy, float* ws, size_t ws_bytes, cudaStream_t st, int splits) {
+    const int sym = splits < 0 ? 2 : 0;           // negative split count: Gram product (see gemm_nt_gram)
+    if (splits < 0) splits = -splits;
     if ((size_t)splits * M * N * sizeof(float) > ws_bytes) { set_error("gemm_nt: workspace too small"); return -1; }
     int kps = (K + splits - 1) / splits;
     kps = (kps + GK - 1) / GK * GK;
@@ -186,7 +204,7 @@ static int gemm_nt_impl(const float* A, int lda, const float* Bm, int ldb, int M
         count_launch(1);
         return 0;
     }
-    gemm_nt_kernel<false><<<grid, GTHREADS, 0, st>>>(A, lda, Bm, ldb, M, N, K, kps, vec_ok, ws);
+    gemm_nt_kernel<false><<<grid, GTHREADS, 0, st>>>(A, lda, Bm, ldb, M, N, K, kps, vec_ok | sym, ws);
     const size_t total = group_sort ? (size_t)M * (N / 2) : (size_t)M * N;
     gemm_epilogue_kernel<<<(unsigned)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096), 256, 0, st>>>(
         ws, splits, M, N, bias, alpha, group_sort, y, ldy);

@@ -35,6 +35,11 @@ FIODE_API int fiode_version(void);
  * gpu_launches claim is read from here) */
 FIODE_API long long fiode_launch_count(void);
 FIODE_API void fiode_reset_launch_count(void);
+/* Process-wide A/B switch (default on; env FIODE_FORK=0 = off): the entry points that compute a layer's weight / bias gradient
+ * next to its data gradient (fiode_linear_bwd, fiode_conv1x1_s2d_bwd, fiode_cayley_conv_layer_bwd, fiode_fi_loss_bwd,
+ * fiode_cayley_linear_bwd*) run the two on the caller's stream and on an internal branch stream that is joined before the call
+ * returns.  Results are identical either way (same kernels, same order per output).  No counterpart in the reference.     */
+FIODE_API void fiode_set_side_streams(int on);
 
 /* ---- Cayley transform (weight preparation, cached per weight version by the host) ----------
  * replaces libs/ortho_conv/layers.py:50-60 `cayley` as used by CayleyLinear.forward (:103-104)

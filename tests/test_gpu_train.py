@@ -410,8 +410,9 @@ def test_cayley_small_batch_equals_per_layer():
 
 
 def test_prefetched_cayley_transforms_leave_the_fi_step_unchanged(sd):
-    """layers.prefetch_orthogonal (small layers in one launch, large ones on side streams, adjoints likewise): loss and all 33
-    gradients equal the per-layer step's bit for bit, eager and over repeated steps."""
+    """layers.prefetch_orthogonal (small layers in one launch, large ones on side streams, adjoints likewise) and the library's
+    internal branch streams for weight gradients (fiode_set_side_streams): loss and all 33 gradients equal the serial
+    per-layer step's bit for bit, over repeated steps."""
     from tests.test_gpu_fi import build_learning, dev
     from fiode_b200 import layers
     c = fx.load_golden('fi.pt')['uniform_sn1']
@@ -439,10 +440,17 @@ def test_prefetched_cayley_transforms_leave_the_fi_step_unchanged(sd):
         finally:
             layers._PREFETCH = old
 
-    ref, n0 = run(False)
-    got, n1 = run(True)
+    from fiode_b200._lib import lib
+    lib().fiode_set_side_streams(0)          # serial reference: no prefetch, weight gradients in line on the caller's stream
+    try:
+        ref, n0 = run(False)
+    finally:
+        lib().fiode_set_side_streams(1)
+    branch_only, _ = run(False)              # internal branch streams (fork_side / join_side) on their own
+    got, n1 = run(True)                      # ... and with the Cayley transforms prepared up front on side streams
     assert n0 == 0 and n1 == 11
-    for (l0, g0), (l1, g1) in zip(ref, got):
-        assert torch.equal(l0, l1)
-        for k in g0:
-            assert torch.equal(g0[k], g1[k]), k
+    for other in (branch_only, got):
+        for (l0, g0), (l1, g1) in zip(ref, other):
+            assert torch.equal(l0, l1)
+            for k in g0:
+                assert torch.equal(g0[k], g1[k]), k
