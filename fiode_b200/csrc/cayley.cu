@@ -325,19 +325,32 @@ __global__ void __launch_bounds__(256) gj_block_update_kernel(const float* __res
 // parallel: the inversion is a latency chain, not work), forms T = D^-1 X_kj in registers and then writes its own block --
 // T for the pivot row, X_ij - X_ik T elsewhere -- without the round trip of block row k through global memory and the second
 // launch.  Per element the same operations in the same order as panel + update: bit-identical results.
-constexpr size_t kGjStepSmem = (size_t)(2 * GB * GB + GB * (GB + 1) + 2 * GB) * sizeof(float);
+constexpr int GLS = GB + 4;              // row stride of the X_ik tile: float4 rows, and ty / ty + 1 land on different banks
+constexpr size_t kGjStepSmem = (size_t)(2 * GB * GB + GB * GLS + 2 * GB) * sizeof(float);
 __global__ void __launch_bounds__(256) gj_block_step_kernel(const float* __restrict__ X, float* __restrict__ Y, int n, int kb) {
     extern __shared__ __align__(16) float gj_sm[];
     float* D0 = gj_sm;                       // D, then D^-1
     float* P = D0 + GB * GB;                 // X_kj, then T = D^-1 X_kj
-    float* Ls = P + GB * GB;                 // X_ik, row stride GB + 1
-    float* prow = Ls + GB * (GB + 1);        // two 64-float lines
+    float* Ls = P + GB * GB;                 // X_ik, row stride GLS
+    float* prow = Ls + GB * GLS;             // two 64-float lines
     const int t = threadIdx.x, jb = blockIdx.x, ib = blockIdx.y;
-    for (int e = t; e < GB * GB; e += 256) {
-        const int i = e / GB, j = e - i * GB;
-        D0[e] = X[(size_t)(kb * GB + i) * n + kb * GB + j];
-        P[e] = X[(size_t)(kb * GB + i) * n + jb * GB + j];
-        if (ib != kb) Ls[i * (GB + 1) + j] = X[(size_t)(ib * GB + i) * n + kb * GB + j];
+    {   // the three 64 x 64 tiles: all twelve 16-byte loads of a thread in flight before the first store (the scalar version
+        // spent a quarter of the kernel waiting for them one after the other)
+        float4 d4[4], p4[4], l4[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int e4 = t + 256 * q, i = e4 >> 4, j = (e4 & 15) * 4;
+            d4[q] = *reinterpret_cast<const float4*>(X + (size_t)(kb * GB + i) * n + kb * GB + j);
+            p4[q] = *reinterpret_cast<const float4*>(X + (size_t)(kb * GB + i) * n + jb * GB + j);
+            if (ib != kb) l4[q] = *reinterpret_cast<const float4*>(X + (size_t)(ib * GB + i) * n + kb * GB + j);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int e4 = t + 256 * q, i = e4 >> 4, j = (e4 & 15) * 4;
+            *reinterpret_cast<float4*>(D0 + i * GB + j) = d4[q];
+            *reinterpret_cast<float4*>(P + i * GB + j) = p4[q];
+            if (ib != kb) *reinterpret_cast<float4*>(Ls + i * GLS + j) = l4[q];
+        }
     }
     __syncthreads();
     const int w = t >> 5, l = t & 31;
@@ -415,7 +428,7 @@ __global__ void __launch_bounds__(256) gj_block_step_kernel(const float* __restr
     for (int r = 0; r < GB; ++r) {
         float lv[4], q[4];
 #pragma unroll
-        for (int a = 0; a < 4; ++a) { lv[a] = Ls[(ty + 16 * a) * (GB + 1) + r]; q[a] = P[r * GB + tx + 16 * a]; }
+        for (int a = 0; a < 4; ++a) { lv[a] = Ls[(ty + 16 * a) * GLS + r]; q[a] = P[r * GB + tx + 16 * a]; }
 #pragma unroll
         for (int a = 0; a < 4; ++a)
 #pragma unroll

@@ -13,7 +13,12 @@ start = next(i for i, l in enumerate(lines) if l.startswith('"Address"'))
 rd = list(csv.reader(io.StringIO('\n'.join(lines[start:]))))
 head = rd[0]
 col = {h: i for i, h in enumerate(head)}
-rows = [r for r in rd[1:] if len(r) == len(head)]
+rows = []
+for r in rd[1:]:
+    if r and r[0] == 'Address':      # several launches in the capture: the first one is shown
+        break
+    if len(r) == len(head):
+        rows.append(r)
 S = col['# Samples']
 tot = sum(int(r[S] or 0) for r in rows)
 print('instructions', len(rows), 'samples', tot)
