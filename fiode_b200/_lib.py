@@ -88,6 +88,9 @@ SIGNATURES = {
     'fiode_cayley_linear_bwd': (I, [P, P, I, I, P, P, P, P, SZ, P]),
     'fiode_cayley_linear_save': (I, [P, P, I, I, P, P, P, SZ, P]),
     'fiode_cayley_linear_bwd_saved': (I, [P, P, I, I, P, P, P, P, P, SZ, P]),
+    'fiode_cayley_linear_ctx_floats': (SZ, [I, I]),
+    'fiode_cayley_linear_fwd_ctx': (I, [P, P, I, I, P, P, P, SZ, P]),
+    'fiode_cayley_linear_bwd_ctx': (I, [P, P, I, I, P, P, P, P, P, SZ, P]),
     'fiode_cayley_small_ok': (I, [I, I]),
     'fiode_cayley_small_batch_fwd': (I, [I, P, P, P, P, P, P, P, P]),
     'fiode_cayley_small_batch_bwd': (I, [I, P, P, P, P, P, P, P, P, P, P]),

@@ -22,14 +22,14 @@ class CayleyLinearQ(Function):
         if not _SAVE_MINV:
             ctx.save_for_backward(weight, alpha)
             return ops.cayley_linear(weight, alpha)
-        Q, minv = ops.cayley_linear(weight, alpha, save_minv=True)
-        ctx.save_for_backward(weight, alpha, minv)       # (I + A)^-1: the adjoint does not invert again
+        Q, kept = ops.cayley_linear(weight, alpha, save_ctx=True)
+        ctx.save_for_backward(weight, alpha, kept)       # scale, (I + A)^-1, staged matrices: the adjoint starts at dL/dQ
         return Q
 
     @staticmethod
     def backward(ctx, gQ):
         weight, alpha, *rest = ctx.saved_tensors
-        gW, ga = ops.cayley_linear_bwd(weight, alpha, gQ, minv=rest[0] if rest else None)
+        gW, ga = ops.cayley_linear_bwd(weight, alpha, gQ, ctx=rest[0] if rest else None)
         return gW, ga.reshape(alpha.shape)
 
 

@@ -63,7 +63,10 @@ static SideSlot* side_slot(cudaStream_t st) {
     std::lock_guard<std::mutex> lk(g_side_mu);
     if (sl->s) return sl;
     cudaStream_t s = nullptr;
-    if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+    int lo = 0, hi = 0;                      // branch kernels are on their layer's way to the next layer: highest priority
+    if (cudaDeviceGetStreamPriorityRange(&lo, &hi) != cudaSuccess) { lo = hi = 0; (void)cudaGetLastError(); }
+    static const bool prio = [] { const char* e = getenv("FIODE_GRAPH_PRIO"); return !(e && e[0] == '0'); }();
+    if (cudaStreamCreateWithPriority(&s, cudaStreamNonBlocking, prio ? hi : 0) != cudaSuccess) return nullptr;
     if (cudaEventCreateWithFlags(&sl->fork, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&sl->join, cudaEventDisableTiming) != cudaSuccess) return nullptr;
     sl->s = s;

@@ -5,6 +5,8 @@ layers, per-layer backbone adjoints, the fused FI loss).  Every launch in this p
 host-side launch cost.  Inputs are static device buffers: copy the next batch into them before ``replay()``."""
 from __future__ import annotations
 
+import os
+
 import torch
 
 
@@ -18,6 +20,7 @@ class GraphedStep:
         self.fn, self.warmup, self.key_fn = fn, warmup, key_fn
         self.key = key_fn() if key_fn else None
         self.captures = 0
+        self._stream = None
         self._capture()
 
     def _capture(self):
@@ -31,7 +34,12 @@ class GraphedStep:
         cur.wait_stream(side)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(self.graph):
+        # captured on a high-priority stream: kernel nodes keep the priority of the stream they were captured on, so the step's
+        # main chain (and the library's branch streams, created with the same priority) is scheduled ahead of the Cayley
+        # transforms' side chains whenever both have thread blocks waiting for an SM
+        if self._stream is None:
+            self._stream = torch.cuda.Stream(priority=-1) if os.environ.get('FIODE_GRAPH_PRIO', '1') != '0' else torch.cuda.Stream()
+        with torch.cuda.graph(self.graph, stream=self._stream):
             self.out = fn()
         self.captures += 1
 

@@ -21,15 +21,21 @@ def _ws(nbytes, device):
 
 
 # ---- Cayley weight preparation ------------------------------------------------------------------
-def cayley_linear(weight, alpha, save_minv=False):
+def cayley_linear(weight, alpha, save_minv=False, save_ctx=False):
     """Q = cayley(alpha * W / ||W||)  (libs/ortho_conv/layers.py:103-104).  ``save_minv``: also return (I + A)^-1 for the
-    adjoint (``cayley_linear_bwd(..., minv=)``), as autograd keeps the forward's intermediates."""
+    adjoint (``cayley_linear_bwd(..., minv=)``), as autograd keeps the forward's intermediates; ``save_ctx``: return the
+    library's whole context buffer instead (scale, inverse, staged matrices: ``cayley_linear_bwd(..., ctx=)``)."""
     W = _f32(weight)
     cout, cin = W.shape
     a = _f32(alpha).reshape(1)
     Q = torch.empty_like(W)
     n = lib().fiode_cayley_linear_workspace_bytes(cout, cin)
     ws = _ws(n, W.device)
+    if save_ctx:
+        ctx = torch.empty(lib().fiode_cayley_linear_ctx_floats(cout, cin), dtype=torch.float32, device=W.device)
+        check(lib().fiode_cayley_linear_fwd_ctx(ptr(W), ptr(a), cout, cin, ptr(Q), ptr(ctx), ptr(ws), n, stream_ptr()),
+              'fiode_cayley_linear_fwd_ctx')
+        return Q, ctx
     if save_minv:
         m = min(cout, cin)
         minv = torch.empty(m, m, dtype=torch.float32, device=W.device)
@@ -508,8 +514,9 @@ def cayley_conv_layer_bwd(x, Qf, gy, need_gx=True, need_gb=True):
     return gx, torch.view_as_complex(gQ), gb
 
 
-def cayley_linear_bwd(weight, alpha, gQ, minv=None):
-    """Adjoint of cayley_linear: (gW, galpha).  ``minv``: (I + A)^-1 from ``cayley_linear(..., save_minv=True)``."""
+def cayley_linear_bwd(weight, alpha, gQ, minv=None, ctx=None):
+    """Adjoint of cayley_linear: (gW, galpha).  ``minv``: (I + A)^-1 from ``cayley_linear(..., save_minv=True)``; ``ctx``: the
+    context buffer from ``cayley_linear(..., save_ctx=True)``."""
     W, gQ = _f32(weight), _f32(gQ)
     cout, cin = W.shape
     a = _f32(alpha).reshape(1)
@@ -517,6 +524,10 @@ def cayley_linear_bwd(weight, alpha, gQ, minv=None):
     ga = torch.empty(1, dtype=torch.float32, device=W.device)
     nb = lib().fiode_cayley_linear_bwd_workspace_bytes(cout, cin)
     ws = _ws(nb, W.device)
+    if ctx is not None:
+        check(lib().fiode_cayley_linear_bwd_ctx(ptr(W), ptr(a), cout, cin, ptr(gQ), ptr(ctx), ptr(gW), ptr(ga), ptr(ws), nb,
+                                                stream_ptr()), 'fiode_cayley_linear_bwd_ctx')
+        return gW, ga
     if minv is not None:
         check(lib().fiode_cayley_linear_bwd_saved(ptr(W), ptr(a), cout, cin, ptr(gQ), ptr(_f32(minv)), ptr(gW), ptr(ga), ptr(ws), nb,
                                                   stream_ptr()), 'fiode_cayley_linear_bwd_saved')

@@ -183,6 +183,16 @@ FIODE_API int fiode_cayley_linear_save(const float* W, const float* alpha, int c
                              void* ws, size_t ws_bytes, void* stream);
 FIODE_API int fiode_cayley_linear_bwd_saved(const float* W, const float* alpha, int cout, int cin, const float* gQ,
                                   const float* Minv, float* gW, float* galpha, void* ws, size_t ws_bytes, void* stream);
+/* Training: the forward transform (layers.py:103-104, evaluated in CayleyLinear.forward under autograd) that keeps what its
+ * adjoint needs in ONE caller buffer of fiode_cayley_linear_ctx_floats(cout, cin) floats (16-byte aligned) -- the scale pair,
+ * (I + A)^-1 and its transpose, the scaled working matrix and V^T, as autograd keeps a forward's intermediates; small layers
+ * keep (I + A)^-1 only.  fiode_cayley_linear_bwd_ctx then starts at the incoming gradient.  Same Q as fiode_cayley_linear and
+ * same (gW, galpha) as fiode_cayley_linear_bwd, bit for bit.                                                                */
+FIODE_API size_t fiode_cayley_linear_ctx_floats(int cout, int cin);
+FIODE_API int fiode_cayley_linear_fwd_ctx(const float* W, const float* alpha, int cout, int cin, float* Q, float* ctx,
+                                void* ws, size_t ws_bytes, void* stream);
+FIODE_API int fiode_cayley_linear_bwd_ctx(const float* W, const float* alpha, int cout, int cin, const float* gQ,
+                                const float* ctx, float* gW, float* galpha, void* ws, size_t ws_bytes, void* stream);
 /* Several small layers (fiode_cayley_small_ok: min(cout,cin) <= 64 and max*min <= 16384 -- the dynamics' 128x10 / 10x128
  * layers, fc 10x512, the stride-2 convs' 1x1 matrices) in ONE launch, one CTA per layer: the Cayley transforms of a training
  * step's layers are independent (libs/ortho_conv/layers.py:103-104 / :74-82 evaluate them layer by layer).  The lists are HOST

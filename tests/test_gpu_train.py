@@ -379,6 +379,23 @@ def test_differentiable_solve_beyond_64_attempts(sd):
             assert cos > 0.95 and 0.7 < float(a.norm() / b.norm()) < 1.4, (k, cos, float(a.norm() / b.norm()))
 
 
+@pytest.mark.parametrize('cout,cin', [(128, 10), (128, 128), (512, 512), (512, 4096), (4096, 512)])
+def test_cayley_linear_context_variant_equals_plain_calls(cout, cin):
+    """fiode_cayley_linear_fwd_ctx / _bwd_ctx (the forward keeps scale, inverse and staged matrices in one buffer, the adjoint
+    starts at dL/dQ): Q, gW and galpha are bit-identical with fiode_cayley_linear and fiode_cayley_linear_bwd."""
+    from fiode_b200 import ops
+    W = randn(cout, cin, seed=cout + cin).to(DEV)
+    al = W.norm() * 0.9
+    gQ = randn(cout, cin, seed=7).to(DEV)
+    Q0 = ops.cayley_linear(W, al)
+    gW0, ga0 = ops.cayley_linear_bwd(W, al, gQ)
+    for _ in range(2):
+        Q1, kept = ops.cayley_linear(W, al, save_ctx=True)
+        gW1, ga1 = ops.cayley_linear_bwd(W, al, gQ, ctx=kept)
+        assert torch.equal(Q0, Q1)
+        assert torch.equal(gW0, gW1) and torch.equal(ga0, ga1)
+
+
 def test_cayley_small_batch_equals_per_layer():
     """fiode_cayley_small_batch_fwd / _bwd (one CTA per layer, one launch): Q, Minv-based adjoint and galpha are bit-identical
     with the per-layer calls, for the step's small layers incl. the k = 1 conv matrices (mult = sqrt(F))."""
