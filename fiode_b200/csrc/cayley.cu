@@ -1277,11 +1277,17 @@ __global__ void __launch_bounds__(1024) cayley_conv_bwd_kernel(const float* __re
         gM[e] = make_float2(2.f * (Gq[e].x - acc.x), 2.f * (Gq[e].y - acc.y));
     }
     __syncthreads();
-    // T = gM M^H
+    // T = gM M^H.  Consecutive threads hold consecutive j, so M[j][r] at a common r is a walk down a column: one bank for the
+    // whole warp.  Each thread therefore starts its sum at r = j and wraps around (the lanes then touch 32 different columns);
+    // the order of the sum differs per element but is fixed.
     for (int e = t; e < cin * cin; e += nt) {
         const int i = e / cin, j = e - i * cin;
         float2 acc = make_float2(0.f, 0.f);
-        for (int r = 0; r < cin; ++r) cfma(acc, gM[i * cin + r], cconj(M[j * cin + r]));
+        int r = j;
+        for (int q = 0; q < cin; ++q) {
+            cfma(acc, gM[i * cin + r], cconj(M[j * cin + r]));
+            if (++r == cin) r = 0;
+        }
         T[e] = acc;
     }
     __syncthreads();
