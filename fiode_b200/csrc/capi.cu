@@ -76,6 +76,9 @@ cudaStream_t fork_side(cudaStream_t st) {
     if (!fork_enabled()) return st;
     SideSlot* sl = side_slot(st);
     if (!sl) { (void)cudaGetLastError(); return st; }          // no branch available: run in line
+    // record + wait as one step: a wait refers to the event's latest record, and another host thread whose stream shares this
+    // branch must not re-record the event in between
+    std::lock_guard<std::mutex> lk(g_side_mu);
     if (cudaEventRecord(sl->fork, st) != cudaSuccess || cudaStreamWaitEvent(sl->s, sl->fork, 0) != cudaSuccess) {
         (void)cudaGetLastError();
         return st;
@@ -86,6 +89,7 @@ int join_side(cudaStream_t st) {
     if (!fork_enabled()) return 0;
     SideSlot* sl = side_slot(st);
     if (!sl) return 0;
+    std::lock_guard<std::mutex> lk(g_side_mu);
     cudaError_t e = cudaEventRecord(sl->join, sl->s);
     if (e == cudaSuccess) e = cudaStreamWaitEvent(st, sl->join, 0);
     if (e != cudaSuccess) return cuda_fail(e, "join_side");

@@ -85,7 +85,7 @@ def prefetch_orthogonal(*roots):
     """Every Cayley transform of a training step up front.  The reference evaluates ``cayley(alpha W / ||W||)`` inside each
     layer's forward (libs/ortho_conv/layers.py:74-82, :103-104); the transforms depend on the weights only, so here the small
     layers' go out as ONE launch (``CayleySmallBatchQ``, one CTA per layer, one more launch for all their adjoints at the end of
-    backward) and each large layer's launch chain (Gauss-Jordan on a 512 x 512 matrix is ~16 dependent launches) runs on its
+    backward) and each large layer's chain of ~25 dependent launches (eight for the Gauss-Jordan steps of a 512 x 512 matrix alone) runs on its
     own side stream next to the others; autograd runs each node's backward on the stream of its forward, so the adjoints
     overlap the activation backward the same way.  Values and gradients are those of the per-layer path, bit for bit.
     Each layer's forward picks its Q up and joins that layer's stream there (``_take_prefetch``), so the first layers' activations
