@@ -505,6 +505,9 @@ static int ensure_smem_attr() {
         const int mx = (int)solver_smem_bytes(64);
         FIODE_CUDA(cudaFuncSetAttribute(dopri5_simplex_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
         FIODE_CUDA(cudaFuncSetAttribute(dopri5_simplex_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+        // clusters of 16 CTAs (B up to 1024 rows per solve in the batched launch) are beyond the portable size of 8
+        if (cudaFuncSetAttribute(dopri5_simplex_kernel<true>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess)
+            (void)cudaGetLastError();       // not granted: a launch with 16 then reports its own error
     }
     return 0;
 }
@@ -572,8 +575,8 @@ extern "C" int fiode_dopri5_simplex_batched(const fiode_dyn_weights* w, const fl
     if (s_rows != 1 && s_rows != G * B) { set_error("fiode_dopri5_simplex_batched: s_rows must be 1 or G*B"); return -1; }
     if (w->max_iter < 1 || w->max_iter > kMaxIter) { set_error("fiode_dopri5_simplex_batched: max_iter must be in [1,32]"); return -1; }
     int C = cluster_size;
-    if (C <= 0) { C = 8; while (C > 1 && (B + C - 1) / C < 8) C >>= 1; }     // at least 8 rows per CTA
-    if (C != 1 && C != 2 && C != 4 && C != 8) { set_error("fiode_dopri5_simplex_batched: cluster size must be 1, 2, 4 or 8"); return -1; }
+    if (C <= 0) { C = B > 512 ? 16 : 8; while (C > 1 && (B + C - 1) / C < 8) C >>= 1; }     // at least 8 rows per CTA
+    if (C != 1 && C != 2 && C != 4 && C != 8 && C != 16) { set_error("fiode_dopri5_simplex_batched: cluster size must be 1, 2, 4, 8 or 16"); return -1; }
     const int R = (B + C - 1) / C;
     if (R > 64) { set_error("fiode_dopri5_simplex_batched: B=%d exceeds %d rows (cluster of %d x 64); use fiode_dopri5_simplex", B, C * 64, C); return -2; }
     int rc = ensure_smem_attr();
@@ -599,8 +602,8 @@ extern "C" int fiode_dopri5_simplex_batched(const fiode_dyn_weights* w, const fl
 // more solves than this runs in waves, each wave costing a full solve latency, so callers size G to a multiple of it.
 extern "C" int fiode_dopri5_max_concurrent_solves(int B, int cluster_size) {
     int C = cluster_size;
-    if (C <= 0) { C = 8; while (C > 1 && (B + C - 1) / C < 8) C >>= 1; }
-    if (C != 1 && C != 2 && C != 4 && C != 8) { set_error("fiode_dopri5_max_concurrent_solves: cluster size must be 1, 2, 4 or 8"); return -1; }
+    if (C <= 0) { C = B > 512 ? 16 : 8; while (C > 1 && (B + C - 1) / C < 8) C >>= 1; }
+    if (C != 1 && C != 2 && C != 4 && C != 8 && C != 16) { set_error("fiode_dopri5_max_concurrent_solves: cluster size must be 1, 2, 4, 8 or 16"); return -1; }
     const int R = (B + C - 1) / C;
     if (B <= 0 || R > 64) { set_error("fiode_dopri5_max_concurrent_solves: B=%d does not fit a cluster of %d x 64 rows", B, C); return -2; }
     int rc = ensure_smem_attr();

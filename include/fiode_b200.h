@@ -429,7 +429,8 @@ FIODE_API int fiode_dopri5_simplex_logged(const fiode_dyn_weights* w, const floa
  * cluster per solve, so every solve keeps ITS OWN batch-wide RMS norm and projection stop rule -- the
  * result of solve g equals fiode_dopri5_simplex on rows [g*B, (g+1)*B).  This is how whole batches
  * shard across SMs (and, one level up, across GPUs).  h0, s (1 | G*B rows), out (nt, G*B, 10),
- * stats: G structs.  cluster_size 0 = auto (8 CTAs x 32 rows for B = 256); B <= 64 * cluster_size.   */
+ * stats: G structs.  cluster_size 0 = auto (8 CTAs x 32 rows for B = 256, 16 CTAs for B > 512); 1, 2, 4, 8 or 16 (16 is a
+ * non-portable cluster size: granted on B200); B <= 64 * cluster_size, i.e. up to 1024 rows per solve.   */
 FIODE_API int fiode_dopri5_simplex_batched(const fiode_dyn_weights* w, const float* h0, const float* s, int s_rows,
                                  int G, int B, const double* t, int nt, double rtol, double atol,
                                  long long max_num_steps, float* out, fiode_solve_stats* stats,

@@ -450,7 +450,7 @@ def test_certify_driver_matches_reference(sd):
 
 
 @pytest.mark.parametrize('G,B,tol,cluster', [(5, 256, 1e-3, 0), (3, 64, 1e-5, 0), (7, 1, 1e-3, 0), (2, 96, 1e-4, 4),
-                                             (40, 256, 1e-3, 8)])
+                                             (40, 256, 1e-3, 8), (3, 1024, 1e-3, 0), (2, 700, 1e-4, 16)])
 def test_batched_cluster_solver_equals_single_solves(sd, G, B, tol, cluster):
     """One launch, a thread-block cluster per solve: every solve must reproduce the single-solve kernel on
     its own rows (own batch-wide norm, own projection stop rule) -- bit for bit, counters included."""
