@@ -1,6 +1,6 @@
 """BASELINE config 5: dopri5 batch / tolerance sweep on the CIFAR dynamics (batch 64..8192, rtol = atol 1e-2..1e-5),
 over BOTH solver launches -- `fiode_dopri5_simplex` (one cooperative launch per solve) and
-`fiode_dopri5_simplex_batched` (the cluster-per-solve launch the bench uses; B <= 64 rows x cluster size) -- reporting
+`fiode_dopri5_simplex_batched` (the cluster-per-solve launch the bench uses; B <= 64 rows x cluster size, clusters of 4, 8 and 16) -- reporting
 accepted / rejected steps, NFE, device time per solve, rows/s, achieved FLOP/s (NFE x 37 888 x B) and the algorithmic
 HBM GB/s (120 B per row).  For B <= 256 the oracle's counts (tools/sweep_oracle.py, run on the CPU in the
 build container: the restated torchdiffeq 0.2.2 dopri5 around the reference-pinned RHS) are printed beside every GPU
@@ -73,7 +73,7 @@ def sweep(iters=5, oracle_path=None, batches=BATCHES, tols=TOLS, dev=None):
         for B in batches:
             for tol in tols:
                 launches = [('cooperative', lambda: ops.dopri5_simplex(dw, h_all[:B], s_all[:B], t, tol, tol), 1)]
-                for C in (4, 8):
+                for C in (4, 8, 16):
                     if B % C == 0 and B // C <= 64 and B // C >= 8:
                         G = max(1, ops.dopri5_max_concurrent_solves(B, C))
                         G = min(G, nmax // B)
